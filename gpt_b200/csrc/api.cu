@@ -1,0 +1,1038 @@
+// C-ABI implementation (include/gptb200.h): handle lifetime, host<->device staging and the
+// orchestration of one SGLD step  gather -> K1 fwd -> K2 contract -> K3 bwd -> all-reduce -> K5 update.
+#include <math.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+#include "tc_layout.cuh"
+
+// defined in batch.cu / update.cu
+int gptb_launch_gather_from(gptb_handle *h, const double *Xrm, const double *y, int64_t bs, int64_t mpad, double *Xb,
+                            float *XbF, double *yb);
+int gptb_launch_transpose(gptb_handle *h, const double *Xcm, int64_t N, double *Xrm);
+int gptb_reset_order(gptb_handle *h);
+int gptb_apply_perm(gptb_handle *h, const int64_t *perm_dev);
+size_t gptb_update_small_stride(int r);
+
+static thread_local std::string g_last_error;
+
+void gptb_set_error(const gptb_handle *h, const char *fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (h) h->err = buf;
+    g_last_error = buf;
+}
+
+namespace {
+
+template <typename T>
+int dev_alloc(gptb_handle *h, T **p, size_t count) {
+    if (*p) {
+        cudaFree(*p);
+        *p = nullptr;
+    }
+    if (count == 0) count = 1;
+    cudaError_t e = cudaMalloc((void **)p, count * sizeof(T));
+    if (e != cudaSuccess) {
+        gptb_set_error(h, "cudaMalloc(%zu bytes): %s", count * sizeof(T), cudaGetErrorString(e));
+        *p = nullptr;
+        return e == cudaErrorMemoryAllocation ? GPTB_ERR_NOMEM : GPTB_ERR_CUDA;
+    }
+    return GPTB_OK;
+}
+
+template <typename T>
+void dev_free(T **p) {
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+}
+
+__global__ void d2f_kernel(const double *a, float *b, size_t n) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        b[i] = (float)a[i];
+}
+__global__ void axpy_kernel(const double *x, double *y, double a, size_t n) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        y[i] += a * x[i];
+}
+__global__ void gather_y_kernel(const double *y, const int32_t *rows, int64_t row_base, int64_t bs, int64_t mpad,
+                                double *yb) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < mpad; i += (int64_t)gridDim.x * blockDim.x)
+        yb[i] = i < bs ? y[rows ? (int64_t)rows[i] : row_base + i] : 0.0;
+}
+__global__ void idx64_to_32_kernel(const int64_t *a, int32_t *b, int64_t n, int64_t N, int32_t *bad) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t v = a[i];
+        if (v < 0 || v >= N) {
+            *bad = 1;
+            v = 0;
+        }
+        b[i] = (int32_t)v;
+    }
+}
+
+int check_ready(gptb_handle *h, bool need_train, bool need_params) {
+    if (!h->have_features && !h->have_phi) {
+        gptb_set_error(h, "features not set (gptb_set_features or gptb_set_train_phi)");
+        return GPTB_ERR_STATE;
+    }
+    if (!h->have_index) {
+        gptb_set_error(h, "core index table not set (gptb_set_index)");
+        return GPTB_ERR_STATE;
+    }
+    if (need_train && !h->have_train && !h->have_phi) {
+        gptb_set_error(h, "training set not set (gptb_set_train / gptb_set_train_phi)");
+        return GPTB_ERR_STATE;
+    }
+    if (need_params && !h->have_params) {
+        gptb_set_error(h, "parameters not set (gptb_set_params / gptb_init_params)");
+        return GPTB_ERR_STATE;
+    }
+    return GPTB_OK;
+}
+
+// The dense-phi compatibility path always runs the FP64 kernels (it is HBM-bound on 8*n*D bytes/row).
+inline bool use_fp64(const gptb_handle *h, bool phi_mode) { return phi_mode || h->cfg.precision == GPTB_PREC_FP64; }
+
+int ensure_batch(gptb_handle *h, int64_t bs) {
+    if (bs <= h->cap && h->cap > 0) return GPTB_OK;
+    const gptb_config &c = h->cfg;
+    int64_t cap = std::max<int64_t>(bs, 128);
+    int64_t mpad = (cap + 127) / 128 * 128;
+    GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    GPTB_TRY(dev_alloc(h, &h->Xb, (size_t)c.D * mpad));
+    GPTB_TRY(dev_alloc(h, &h->XbF, (size_t)c.D * mpad));
+    GPTB_TRY(dev_alloc(h, &h->yb, (size_t)mpad));
+    GPTB_TRY(dev_alloc(h, &h->fhat, (size_t)mpad));
+    GPTB_TRY(dev_alloc(h, (double **)&h->T, (size_t)c.D * c.r * mpad));
+    GPTB_TRY(dev_alloc(h, (double **)&h->E, (size_t)c.D * c.r * mpad));
+    GPTB_TRY(dev_alloc(h, &h->idx_dev, (size_t)mpad));
+    if (gptb_is_tc(h)) {
+        size_t eb = gptb_tc_eimg_bytes(h, mpad);
+        GPTB_TRY(dev_alloc(h, (unsigned char **)&h->Eimg, eb));
+        GPTB_CUDA_OK(h, cudaMemsetAsync(h->Eimg, 0, eb, h->stream));
+    }
+    h->cap = cap;
+    h->mpad = mpad;
+    return GPTB_OK;
+}
+
+int ensure_pin(gptb_handle *h, size_t bytes) {
+    if (bytes <= h->pin_bytes) return GPTB_OK;
+    if (h->pin) cudaFreeHost(h->pin);
+    h->pin = nullptr;
+    h->pin_bytes = 0;
+    GPTB_CUDA_OK(h, cudaMallocHost((void **)&h->pin, bytes));
+    h->pin_bytes = bytes;
+    return GPTB_OK;
+}
+
+struct PhaseTimer {
+    gptb_handle *h;
+    explicit PhaseTimer(gptb_handle *hh) : h(hh) {
+        if (h->profiling) cudaEventRecord(h->ev[0], h->stream);
+    }
+    void mark(int phase) {
+        if (h->profiling) cudaEventRecord(h->ev[phase + 1], h->stream);
+        last = phase;
+    }
+    int last = -1;
+    void finish() {
+        if (!h->profiling) return;
+        cudaStreamSynchronize(h->stream);
+        int prev = 0;
+        for (int p = 0; p <= last; ++p) {
+            if (!marked[p]) continue;
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, h->ev[prev], h->ev[p + 1]);
+            h->phase_ms[p] += ms;
+            prev = p + 1;
+        }
+    }
+    bool marked[GPTB_PHASE_COUNT] = {false, false, false, false, false, false};
+    void done(int phase) {
+        mark(phase);
+        marked[phase] = true;
+    }
+};
+
+// Pack / refresh the tensor-core shadows of the sampler's current parameters.
+int refresh_shadows(gptb_handle *h) {
+    if (!gptb_is_tc(h) || h->shadows_valid) return GPTB_OK;
+    GPTB_TRY(gptb_tc_pack_params(h));
+    h->shadows_valid = true;
+    return GPTB_OK;
+}
+
+// Forward for the rows staged in Xb/XbF (or phi rows): T, then fhat (and E / gradw when want_grad).
+int forward_contract(gptb_handle *h, bool phi_mode, const int32_t *rows, const double *w_dev, const double *U_dev,
+                     const void *Uimg, int64_t bs, double escale, bool want_grad, PhaseTimer *pt) {
+    const bool f64 = use_fp64(h, phi_mode);
+    if (f64) {
+        GPTB_TRY(gptb_launch_fwd_fp64(h, h->Xb, phi_mode ? h->phi : nullptr, rows, U_dev, bs, h->mpad, (double *)h->T));
+    } else {
+        GPTB_TRY(gptb_launch_fwd_tc(h, h->XbF, Uimg, bs, h->mpad, (float *)h->T));
+    }
+    if (pt) pt->done(GPTB_PHASE_FWD);
+    if (!f64 && want_grad && !h->tc_emax_valid) {
+        // first step after new parameters: one measuring pass establishes the fp16 scale of the E image
+        GPTB_TRY(gptb_launch_contract(h, h->T, w_dev, h->yb, bs, h->mpad, escale, true, h->fhat, h->grad, nullptr,
+                                      h->Eimg, false));
+        GPTB_CUDA_OK(h, cudaMemsetAsync(h->grad, 0, sizeof(double) * h->cfg.Q, h->stream));
+        h->tc_emax_valid = true;
+    }
+    if (!f64 && want_grad) GPTB_TRY(gptb_tc_update_escale(h));
+    GPTB_TRY(gptb_launch_contract(h, h->T, w_dev, h->yb, bs, h->mpad, escale, want_grad, h->fhat, h->grad,
+                                  f64 ? h->E : nullptr, f64 ? nullptr : h->Eimg, f64));
+    if (pt) pt->done(GPTB_PHASE_CONTRACT);
+    return GPTB_OK;
+}
+
+// Gradient of the rank's share of the minibatch into h->grad (likelihood part only, all-reduced).
+// rows_dev: device row ids of the *global* batch or null (= order[start..] / identity when staged).
+int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int64_t bs, int64_t N_total,
+                 bool staged_host_batch, const double *Xstage_rm, const double *ystage, PhaseTimer &pt) {
+    const gptb_config &c = h->cfg;
+    const bool phi_mode = h->have_phi && !staged_host_batch;
+    const int64_t lo = (int64_t)h->rank * bs / h->nranks, hi = (int64_t)(h->rank + 1) * bs / h->nranks;
+    const int64_t lbs = hi - lo;
+    GPTB_TRY(ensure_batch(h, std::max<int64_t>(lbs, 1)));
+    GPTB_TRY(refresh_shadows(h));
+    const size_t gcount = (size_t)c.Q + (size_t)c.n * c.r * c.D;
+    GPTB_CUDA_OK(h, cudaMemsetAsync(h->grad, 0, gcount * sizeof(double), h->stream));
+    const bool f64 = use_fp64(h, phi_mode);
+    const int32_t *rows = rows_dev ? rows_dev + lo : nullptr;
+    if (staged_host_batch) {
+        GPTB_TRY(gptb_launch_gather_from(h, Xstage_rm + (size_t)lo * c.D, ystage + lo, lbs, h->mpad, f64 ? h->Xb : nullptr,
+                                         f64 ? nullptr : h->XbF, h->yb));
+    } else if (phi_mode) {
+        int blocks = (int)std::min<int64_t>((h->mpad + 255) / 256, 1024);
+        gather_y_kernel<<<blocks, 256, 0, h->stream>>>(h->y, rows, 0, lbs, h->mpad, h->yb);
+        h->launches++;
+    } else {
+        GPTB_TRY(gptb_launch_gather(h, rows, 0, lbs, lo));
+    }
+    pt.done(GPTB_PHASE_GATHER);
+    const double escale = ((double)N_total / (double)bs) / signal_var;  // (N/bs)/signal_var of :393,:407
+    if (lbs > 0) {
+        GPTB_TRY(forward_contract(h, phi_mode, rows, h->w, h->U, h->Uimg, lbs, escale, true, &pt));
+        double *gU = h->grad + c.Q;
+        if (f64) {
+            GPTB_TRY(gptb_launch_bwd_fp64(h, h->Xb, phi_mode ? h->phi : nullptr, rows, (const double *)h->E, lbs,
+                                          h->mpad, gU));
+        } else {
+            GPTB_TRY(gptb_launch_bwd_tc(h, h->XbF, h->Eimg, lbs, h->mpad, gU));
+        }
+    }
+    pt.done(GPTB_PHASE_BWD);
+    GPTB_TRY(gptb_allreduce_grad(h));
+    pt.done(GPTB_PHASE_REDUCE);
+    return GPTB_OK;
+}
+
+// Resolve batch rows on the device: explicit idx (host int64) or a range of the current order.
+int stage_rows(gptb_handle *h, const int64_t *idx, int64_t start, int64_t bs, const int32_t **rows_out) {
+    if (bs <= 0 || (idx == nullptr && (start < 0 || start + bs > h->N))) {
+        gptb_set_error(h, "batch range [%lld, %lld) outside 0..N=%lld", (long long)start, (long long)(start + bs),
+                       (long long)h->N);
+        return GPTB_ERR_ARG;
+    }
+    if (!idx) {
+        *rows_out = h->order + start;
+        return GPTB_OK;
+    }
+    GPTB_TRY(ensure_batch(h, bs));
+    int64_t *tmp = nullptr;
+    GPTB_CUDA_OK(h, cudaMallocAsync((void **)&tmp, sizeof(int64_t) * bs, h->stream));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(tmp, idx, sizeof(int64_t) * bs, cudaMemcpyHostToDevice, h->stream));
+    GPTB_CUDA_OK(h, cudaMemsetAsync(h->nan_flag + 1, 0, sizeof(int32_t), h->stream));
+    idx64_to_32_kernel<<<(int)std::min<int64_t>((bs + 255) / 256, 1024), 256, 0, h->stream>>>(tmp, h->idx_dev, bs, h->N,
+                                                                                              h->nan_flag + 1);
+    h->launches++;
+    GPTB_CUDA_OK(h, cudaFreeAsync(tmp, h->stream));
+    int32_t bad = 0;
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(&bad, h->nan_flag + 1, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    if (bad) {
+        gptb_set_error(h, "batch index outside 0..N-1");
+        return GPTB_ERR_ARG;
+    }
+    *rows_out = h->idx_dev;
+    return GPTB_OK;
+}
+
+int stage_noise(gptb_handle *h, const double *noise_w, const double *noise_U, const double **nw_dev,
+                const double **nU_dev) {
+    const gptb_config &c = h->cfg;
+    *nw_dev = nullptr;
+    *nU_dev = nullptr;
+    if (noise_w) {
+        if (!h->noise_w) GPTB_TRY(dev_alloc(h, &h->noise_w, (size_t)c.Q));
+        GPTB_CUDA_OK(h, cudaMemcpyAsync(h->noise_w, noise_w, sizeof(double) * c.Q, cudaMemcpyHostToDevice, h->stream));
+        *nw_dev = h->noise_w;
+    }
+    if (noise_U) {
+        size_t cnt = (size_t)c.n * c.r * c.D;
+        if (!h->noise_U) GPTB_TRY(dev_alloc(h, &h->noise_U, cnt));
+        GPTB_CUDA_OK(h, cudaMemcpyAsync(h->noise_U, noise_U, sizeof(double) * cnt, cudaMemcpyHostToDevice, h->stream));
+        *nU_dev = h->noise_U;
+    }
+    return GPTB_OK;
+}
+
+int check_nan(gptb_handle *h) {
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->nan_flag_host, h->nan_flag, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    if (*h->nan_flag_host) {
+        // GPT_SGLD.jl:25
+        gptb_set_error(h, "Get NaN when moving along Geodesic. Try smaller epsU");
+        return GPTB_GEODESIC_NAN;
+    }
+    return GPTB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int gptb_version(void) { return GPTB_VERSION; }
+
+const char *gptb_last_error(const gptb_handle *h) { return h ? h->err.c_str() : g_last_error.c_str(); }
+
+int gptb_create(const gptb_config *cfg, gptb_handle **out) {
+    if (!cfg || !out) {
+        gptb_set_error(nullptr, "gptb_create: NULL argument");
+        return GPTB_ERR_ARG;
+    }
+    *out = nullptr;
+    if (cfg->D < 1 || cfg->D > 16 || cfg->n < 1 || cfg->r < 1 || cfg->r > 64 || cfg->Q < 1) {
+        gptb_set_error(nullptr, "gptb_create: need 1<=D<=16, n>=1, 1<=r<=64, Q>=1 (got D=%d n=%d r=%d Q=%d)", cfg->D,
+                       cfg->n, cfg->r, cfg->Q);
+        return GPTB_ERR_SHAPE;
+    }
+    if (cfg->precision < GPTB_PREC_FP64 || cfg->precision > GPTB_PREC_TC1 || cfg->feature_kind < 0 ||
+        cfg->feature_kind > 1) {
+        gptb_set_error(nullptr, "gptb_create: unknown precision / feature kind");
+        return GPTB_ERR_ARG;
+    }
+    if (cfg->feature_kind == GPTB_FEAT_SINCOS && (cfg->n % 2)) {
+        gptb_set_error(nullptr, "n not even");  // GPT_SGLD.jl:90
+        return GPTB_ERR_SHAPE;
+    }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        gptb_set_error(nullptr, "no CUDA device: %s (libgptb200 has no CPU fallback)", cudaGetErrorString(e));
+        return GPTB_ERR_CUDA;
+    }
+    gptb_handle *h = new gptb_handle();
+    h->cfg = *cfg;
+    int dev = cfg->device;
+    if (dev < 0) cudaGetDevice(&dev);
+    h->device = dev;
+#define CREATE_OK(expr)                                                                   \
+    do {                                                                                  \
+        cudaError_t _e = (expr);                                                          \
+        if (_e != cudaSuccess) {                                                          \
+            gptb_set_error(nullptr, "gptb_create: %s -> %s", #expr, cudaGetErrorString(_e)); \
+            gptb_destroy(h);                                                              \
+            return GPTB_ERR_CUDA;                                                         \
+        }                                                                                 \
+    } while (0)
+    CREATE_OK(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    CREATE_OK(cudaGetDeviceProperties(&prop, dev));
+    h->sm_count = prop.multiProcessorCount;
+    if (cfg->precision != GPTB_PREC_FP64 && prop.major != 10) {
+        gptb_set_error(nullptr, "tensor-core modes need an sm_100 device (found sm_%d%d)", prop.major, prop.minor);
+        gptb_destroy(h);
+        return GPTB_ERR_UNSUPPORTED;
+    }
+    CREATE_OK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    h->own_stream = true;
+    for (auto &ev : h->ev) CREATE_OK(cudaEventCreate(&ev));
+    const gptb_config &c = h->cfg;
+    h->npad = (c.n + 127) / 128 * 128;
+    h->rpad = (c.r + 15) / 16 * 16;
+    int st = GPTB_OK;
+    auto A = [&](int s) { if (st == GPTB_OK) st = s; };
+    A(dev_alloc(h, &h->Zt, (size_t)c.D * c.n));
+    A(dev_alloc(h, &h->b, (size_t)c.D * c.n));
+    A(dev_alloc(h, &h->ZtF, (size_t)c.D * h->npad));
+    A(dev_alloc(h, &h->bF, (size_t)c.D * h->npad));
+    A(dev_alloc(h, &h->I, (size_t)c.D * c.Q));
+    A(dev_alloc(h, &h->w, (size_t)c.Q));
+    A(dev_alloc(h, &h->U, (size_t)c.D * c.r * c.n));
+    A(dev_alloc(h, &h->G, (size_t)c.D * c.r * c.n));
+    A(dev_alloc(h, &h->grad, (size_t)c.Q + (size_t)c.D * c.r * c.n));
+    h->small_stride = gptb_update_small_stride(c.r);
+    A(dev_alloc(h, &h->small, h->small_stride * c.D));
+    A(dev_alloc(h, &h->nan_flag, 4));
+    A(dev_alloc(h, &h->tc_state, 16));
+    A(dev_alloc(h, &h->pw, (size_t)c.Q));
+    A(dev_alloc(h, &h->pU, (size_t)c.D * c.r * c.n));
+    if (st == GPTB_OK && gptb_is_tc(h)) {
+        h->Uimg_bytes = gptb_tc_uimg_bytes(h);
+        A(dev_alloc(h, (unsigned char **)&h->Uimg, h->Uimg_bytes));
+        A(dev_alloc(h, (unsigned char **)&h->pUimg, h->Uimg_bytes));
+    }
+    if (st != GPTB_OK) {
+        gptb_destroy(h);
+        return st;
+    }
+    CREATE_OK(cudaMallocHost((void **)&h->nan_flag_host, 4 * sizeof(int32_t)));
+    CREATE_OK(cudaMemsetAsync(h->nan_flag, 0, 4 * sizeof(int32_t), h->stream));
+    CREATE_OK(cudaMemsetAsync(h->tc_state, 0, 16 * sizeof(float), h->stream));
+    CREATE_OK(cudaStreamSynchronize(h->stream));
+#undef CREATE_OK
+    *out = h;
+    return GPTB_OK;
+}
+
+int gptb_destroy(gptb_handle *h) {
+    if (!h) return GPTB_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    gptb_comm_destroy(h);
+    dev_free(&h->Zt); dev_free(&h->b); dev_free(&h->ZtF); dev_free(&h->bF); dev_free(&h->I);
+    dev_free(&h->X); dev_free(&h->y); dev_free(&h->phi); dev_free(&h->order); dev_free(&h->order_tmp);
+    dev_free(&h->sort_keys); dev_free(&h->sort_keys_tmp);
+    if (h->sort_tmp) cudaFree(h->sort_tmp);
+    dev_free(&h->w); dev_free(&h->U); dev_free(&h->wF); dev_free(&h->pw); dev_free(&h->pU);
+    if (h->Uimg) cudaFree(h->Uimg);
+    if (h->pUimg) cudaFree(h->pUimg);
+    if (h->ZbF) cudaFree(h->ZbF);
+    dev_free(&h->stage_cm); dev_free(&h->stage_rm); dev_free(&h->stage_y);
+    dev_free(&h->Xb); dev_free(&h->yb); dev_free(&h->fhat); dev_free(&h->XbF);
+    if (h->T) cudaFree(h->T);
+    if (h->E) cudaFree(h->E);
+    if (h->Eimg) cudaFree(h->Eimg);
+    dev_free(&h->idx_dev); dev_free(&h->grad); dev_free(&h->gradF);
+    if (h->tc_partials) cudaFree(h->tc_partials);
+    dev_free(&h->tc_state);
+    dev_free(&h->G); dev_free(&h->small); dev_free(&h->colnorm); dev_free(&h->nan_flag);
+    dev_free(&h->noise_w); dev_free(&h->noise_U); dev_free(&h->pred_acc);
+    dev_free(&h->store_w); dev_free(&h->store_U);
+    if (h->nan_flag_host) cudaFreeHost(h->nan_flag_host);
+    if (h->pin) cudaFreeHost(h->pin);
+    for (auto &ev : h->ev)
+        if (ev) cudaEventDestroy(ev);
+    if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return GPTB_OK;
+}
+
+int gptb_set_stream(gptb_handle *h, void *cuda_stream) {
+    if (!h) return GPTB_ERR_ARG;
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    if (h->own_stream) cudaStreamDestroy(h->stream);
+    if (cuda_stream) {
+        h->stream = (cudaStream_t)cuda_stream;
+        h->own_stream = false;
+    } else {
+        GPTB_CUDA_OK(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+        h->own_stream = true;
+    }
+    return GPTB_OK;
+}
+
+int gptb_synchronize(gptb_handle *h) {
+    if (!h) return GPTB_ERR_ARG;
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    return GPTB_OK;
+}
+
+int gptb_set_features(gptb_handle *h, const double *Z, const double *b, const double *length_scale, int32_t ls_len,
+                      double sigma_RBF, double phi_scale) {
+    if (!h || !Z || !length_scale) return GPTB_ERR_ARG;
+    const gptb_config &c = h->cfg;
+    if (c.feature_kind == GPTB_FEAT_COS && !b) {
+        gptb_set_error(h, "b is required for cos features");
+        return GPTB_ERR_ARG;
+    }
+    if (ls_len != 1 && ls_len != c.D) {
+        gptb_set_error(h, "dimensions of X and length_scale do not match");  // GPT_SGLD.jl:326
+        return GPTB_ERR_SHAPE;
+    }
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    const size_t cnt = (size_t)c.D * c.n;
+    std::vector<double> zt(cnt), bb(cnt, 0.0);
+    std::vector<float> ztf((size_t)c.D * h->npad, 0.f), bf((size_t)c.D * h->npad, 0.f);
+    for (int k = 0; k < c.D; ++k) {
+        const double inv = 1.0 / length_scale[ls_len == 1 ? 0 : k];  // scale(Z, 1./length_scale), :75
+        for (int j = 0; j < c.n; ++j) {
+            zt[(size_t)k * c.n + j] = Z[(size_t)k * c.n + j] * inv;
+            if (b) bb[(size_t)k * c.n + j] = b[(size_t)k * c.n + j];
+            ztf[(size_t)k * h->npad + j] = (float)zt[(size_t)k * c.n + j];
+            bf[(size_t)k * h->npad + j] = (float)bb[(size_t)k * c.n + j];
+        }
+    }
+    if (c.feature_kind == GPTB_FEAT_COS)
+        h->amp = phi_scale * pow(sigma_RBF, 1.0 / c.D) * sqrt(2.0 / c.n);           // :83
+    else
+        h->amp = phi_scale * pow(sigma_RBF, 1.0 / c.D) / sqrt((double)(c.n / 2));   // :104
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->Zt, zt.data(), cnt * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->b, bb.data(), cnt * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->ZtF, ztf.data(), ztf.size() * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->bF, bf.data(), bf.size() * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    h->have_features = true;
+    h->ZbF_valid = false;
+    return GPTB_OK;
+}
+
+int gptb_set_index(gptb_handle *h, const int32_t *I) {
+    if (!h || !I) return GPTB_ERR_ARG;
+    const gptb_config &c = h->cfg;
+    std::vector<int32_t> z((size_t)c.D * c.Q);
+    for (size_t t = 0; t < z.size(); ++t) {
+        if (I[t] < 1 || I[t] > c.r) {
+            gptb_set_error(h, "I[%zu]=%d outside 1..r=%d", t, I[t], c.r);
+            return GPTB_ERR_SHAPE;
+        }
+        z[t] = I[t] - 1;
+    }
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->I, z.data(), z.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    h->have_index = true;
+    return GPTB_OK;
+}
+
+static int set_train_common(gptb_handle *h, const double *y, int64_t N) {
+    GPTB_TRY(dev_alloc(h, &h->y, (size_t)N));
+    GPTB_TRY(dev_alloc(h, &h->order, (size_t)N));
+    dev_free(&h->order_tmp);
+    dev_free(&h->sort_keys);
+    dev_free(&h->sort_keys_tmp);
+    if (h->sort_tmp) cudaFree(h->sort_tmp);
+    h->sort_tmp = nullptr;
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->y, y, sizeof(double) * N, cudaMemcpyHostToDevice, h->stream));
+    h->N = N;
+    GPTB_TRY(gptb_reset_order(h));
+    h->epoch_counter = 0;
+    h->step_counter = 0;
+    return GPTB_OK;
+}
+
+int gptb_set_train(gptb_handle *h, const double *X, const double *y, int64_t N) {
+    if (!h || !X || !y || N < 1 || N > 2147483647LL) return GPTB_ERR_ARG;
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    const gptb_config &c = h->cfg;
+    dev_free(&h->phi);
+    h->have_phi = false;
+    double *tmp = nullptr;
+    GPTB_TRY(dev_alloc(h, &tmp, (size_t)N * c.D));
+    int st = dev_alloc(h, &h->X, (size_t)N * c.D);
+    if (st == GPTB_OK) {
+        cudaError_t e = cudaMemcpyAsync(tmp, X, sizeof(double) * N * c.D, cudaMemcpyHostToDevice, h->stream);
+        if (e != cudaSuccess) st = GPTB_ERR_CUDA;
+    }
+    if (st == GPTB_OK) st = gptb_launch_transpose(h, tmp, N, h->X);
+    if (st == GPTB_OK) st = set_train_common(h, y, N);
+    cudaStreamSynchronize(h->stream);
+    cudaFree(tmp);
+    if (st != GPTB_OK) return st;
+    h->have_train = true;
+    return GPTB_OK;
+}
+
+int gptb_set_train_phi(gptb_handle *h, const double *phi, const double *y, int64_t N) {
+    if (!h || !phi || !y || N < 1 || N > 2147483647LL) return GPTB_ERR_ARG;
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    const gptb_config &c = h->cfg;
+    dev_free(&h->X);
+    h->have_train = false;
+    size_t cnt = (size_t)N * c.D * c.n;
+    GPTB_TRY(dev_alloc(h, &h->phi, cnt));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->phi, phi, sizeof(double) * cnt, cudaMemcpyHostToDevice, h->stream));
+    GPTB_TRY(set_train_common(h, y, N));
+    GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    h->have_phi = true;
+    return GPTB_OK;
+}
+
+int gptb_set_params(gptb_handle *h, const double *w, const double *U) {
+    if (!h || !w || !U) return GPTB_ERR_ARG;
+    const gptb_config &c = h->cfg;
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->w, w, sizeof(double) * c.Q, cudaMemcpyHostToDevice, h->stream));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->U, U, sizeof(double) * c.n * c.r * c.D, cudaMemcpyHostToDevice, h->stream));
+    GPTB_CUDA_OK(h, cudaMemsetAsync(h->nan_flag, 0, sizeof(int32_t), h->stream));
+    GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    h->have_params = true;
+    h->shadows_valid = false;
+    h->tc_emax_valid = false;
+    return GPTB_OK;
+}
+
+int gptb_get_params(gptb_handle *h, double *w, double *U) {
+    if (!h) return GPTB_ERR_ARG;
+    if (!h->have_params) {
+        gptb_set_error(h, "parameters not set");
+        return GPTB_ERR_STATE;
+    }
+    const gptb_config &c = h->cfg;
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    if (w) GPTB_CUDA_OK(h, cudaMemcpyAsync(w, h->w, sizeof(double) * c.Q, cudaMemcpyDeviceToHost, h->stream));
+    if (U) GPTB_CUDA_OK(h, cudaMemcpyAsync(U, h->U, sizeof(double) * c.n * c.r * c.D, cudaMemcpyDeviceToHost, h->stream));
+    GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    return GPTB_OK;
+}
+
+// Symmetric eigen-decomposition by cyclic Jacobi (host, r x r) for (ZZ')^(-1/2) of :366.
+static void jacobi_eigh(std::vector<double> &A, int r, std::vector<double> &V) {
+    V.assign((size_t)r * r, 0.0);
+    for (int i = 0; i < r; ++i) V[i + (size_t)r * i] = 1.0;
+    for (int sweep = 0; sweep < 60; ++sweep) {
+        double off = 0.0;
+        for (int p = 0; p < r; ++p)
+            for (int q = p + 1; q < r; ++q) off += A[p + (size_t)r * q] * A[p + (size_t)r * q];
+        if (off < 1e-30) break;
+        for (int p = 0; p < r; ++p)
+            for (int q = p + 1; q < r; ++q) {
+                double apq = A[p + (size_t)r * q];
+                if (fabs(apq) < 1e-300) continue;
+                double app = A[p + (size_t)r * p], aqq = A[q + (size_t)r * q];
+                double tau = (aqq - app) / (2 * apq);
+                double t = (tau >= 0 ? 1.0 : -1.0) / (fabs(tau) + sqrt(1 + tau * tau));
+                double cs = 1 / sqrt(1 + t * t), sn = t * cs;
+                for (int k = 0; k < r; ++k) {
+                    double akp = A[k + (size_t)r * p], akq = A[k + (size_t)r * q];
+                    A[k + (size_t)r * p] = cs * akp - sn * akq;
+                    A[k + (size_t)r * q] = sn * akp + cs * akq;
+                }
+                for (int k = 0; k < r; ++k) {
+                    double apk = A[p + (size_t)r * k], aqk = A[q + (size_t)r * k];
+                    A[p + (size_t)r * k] = cs * apk - sn * aqk;
+                    A[q + (size_t)r * k] = sn * apk + cs * aqk;
+                }
+                for (int k = 0; k < r; ++k) {
+                    double vkp = V[k + (size_t)r * p], vkq = V[k + (size_t)r * q];
+                    V[k + (size_t)r * p] = cs * vkp - sn * vkq;
+                    V[k + (size_t)r * q] = sn * vkp + cs * vkq;
+                }
+            }
+    }
+}
+
+int gptb_init_params(gptb_handle *h, uint64_t param_seed, int32_t stiefel) {
+    if (!h) return GPTB_ERR_ARG;
+    const gptb_config &c = h->cfg;
+    const int n = c.n, r = c.r, D = c.D;
+    if (stiefel && r > n) {
+        gptb_set_error(h, "Stiefel initialisation needs r <= n");
+        return GPTB_ERR_SHAPE;
+    }
+    std::vector<double> w(c.Q), U((size_t)n * r * D);
+    for (int q = 0; q < c.Q; q += 2) {
+        double a, b;
+        philox_normal2(param_seed, GPTB_STREAM_INIT_W | (uint64_t)(q / 2), 0, &a, &b);
+        w[q] = a;
+        if (q + 1 < c.Q) w[q + 1] = b;
+    }
+    std::vector<double> Z((size_t)r * n), G((size_t)r * r), V, M((size_t)r * r);
+    for (int k = 0; k < D; ++k) {
+        // Z = randn(r,n) (:365) — or randn(n,r)/sqrt(n) (:368); same draws, column-major fill
+        for (size_t e = 0; e < (size_t)r * n; e += 2) {
+            double a, b;
+            philox_normal2(param_seed, GPTB_STREAM_INIT_U | ((uint64_t)k << 40) | (e / 2), 0, &a, &b);
+            Z[e] = a;
+            if (e + 1 < (size_t)r * n) Z[e + 1] = b;
+        }
+        double *Uk = U.data() + (size_t)n * r * k;
+        if (!stiefel) {
+            for (int l = 0; l < r; ++l)
+                for (int j = 0; j < n; ++j) Uk[j + (size_t)n * l] = Z[j + (size_t)n * l] / sqrt((double)n);
+            continue;
+        }
+        for (int a = 0; a < r; ++a)
+            for (int b = 0; b < r; ++b) {
+                double s = 0.0;
+                for (int j = 0; j < n; ++j) s += Z[a + (size_t)r * j] * Z[b + (size_t)r * j];
+                G[a + (size_t)r * b] = s;
+            }
+        jacobi_eigh(G, r, V);  // G now ~diagonal
+        for (int a = 0; a < r; ++a)
+            for (int b = 0; b < r; ++b) {
+                double s = 0.0;
+                for (int p = 0; p < r; ++p) s += V[a + (size_t)r * p] * V[b + (size_t)r * p] / sqrt(G[p + (size_t)r * p]);
+                M[a + (size_t)r * b] = s;  // (ZZ')^(-1/2)
+            }
+        for (int j = 0; j < n; ++j)
+            for (int l = 0; l < r; ++l) {
+                double s = 0.0;
+                for (int a = 0; a < r; ++a) s += M[l + (size_t)r * a] * Z[a + (size_t)r * j];
+                Uk[j + (size_t)n * l] = s;  // transpose of (ZZ')^(-1/2) Z
+            }
+    }
+    return gptb_set_params(h, w.data(), U.data());
+}
+
+int gptb_features(gptb_handle *h, const double *X, int64_t N, double *phi_out) {
+    if (!h || !X || !phi_out || N < 0) return GPTB_ERR_ARG;
+    if (!h->have_features) {
+        gptb_set_error(h, "features not set");
+        return GPTB_ERR_STATE;
+    }
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    const gptb_config &c = h->cfg;
+    const int64_t chunk = std::max<int64_t>(1, (int64_t)(256ll << 20) / ((int64_t)c.n * c.D * 8));
+    double *xc = nullptr, *xr = nullptr, *ph = nullptr;
+    int st = dev_alloc(h, &xc, (size_t)chunk * c.D);
+    if (st == GPTB_OK) st = dev_alloc(h, &xr, (size_t)chunk * c.D);
+    if (st == GPTB_OK) st = dev_alloc(h, &ph, (size_t)chunk * c.D * c.n);
+    for (int64_t i0 = 0; st == GPTB_OK && i0 < N; i0 += chunk) {
+        int64_t cn = std::min(chunk, N - i0);
+        cudaError_t e = cudaMemcpy2DAsync(xc, cn * sizeof(double), X + i0, N * sizeof(double), cn * sizeof(double), c.D,
+                                          cudaMemcpyHostToDevice, h->stream);
+        if (e != cudaSuccess) { st = GPTB_ERR_CUDA; gptb_set_error(h, "features H2D: %s", cudaGetErrorString(e)); break; }
+        st = gptb_launch_transpose(h, xc, cn, xr);
+        // transpose kernel reads Xcm with leading dimension = its N argument (cn): matches the 2-D copy above
+        if (st == GPTB_OK) st = gptb_launch_features_fp64(h, xr, cn, ph);
+        if (st != GPTB_OK) break;
+        e = cudaMemcpyAsync(phi_out + (size_t)i0 * c.D * c.n, ph, sizeof(double) * cn * c.D * c.n, cudaMemcpyDeviceToHost,
+                            h->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) { st = GPTB_ERR_CUDA; gptb_set_error(h, "features D2H: %s", cudaGetErrorString(e)); }
+    }
+    cudaStreamSynchronize(h->stream);
+    cudaFree(xc); cudaFree(xr); cudaFree(ph);
+    return st;
+}
+
+// Shared by pred / pred_phi / pred_samples: S parameter sets, rows chunked through the batch scratch.
+static int pred_impl(gptb_handle *h, const double *w_store, const double *U_store, int32_t S, const double *Xtest,
+                     const double *phitest, int64_t Nt, double *mean_out, double *per_sample_out) {
+    const gptb_config &c = h->cfg;
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    const bool phi_mode = phitest != nullptr;
+    if (!phi_mode && !h->have_features) {
+        gptb_set_error(h, "features not set");
+        return GPTB_ERR_STATE;
+    }
+    if (!h->have_index) {
+        gptb_set_error(h, "core index table not set");
+        return GPTB_ERR_STATE;
+    }
+    if (Nt == 0) return GPTB_OK;
+    const bool f64 = use_fp64(h, phi_mode);
+    const size_t ucnt = (size_t)c.n * c.r * c.D;
+    int64_t chunk = std::min<int64_t>(Nt, 65536);
+    if (phi_mode) chunk = std::min<int64_t>(chunk, std::max<int64_t>(128, (int64_t)(512ll << 20) / ((int64_t)c.n * c.D * 8)));
+    GPTB_TRY(ensure_batch(h, chunk));
+    double *phichunk = nullptr, *acc = nullptr, *saved_phi = h->phi;
+    if (phi_mode) GPTB_TRY(dev_alloc(h, &phichunk, (size_t)chunk * c.D * c.n));
+    int st = dev_alloc(h, &acc, (size_t)h->mpad);
+    GPTB_TRY(ensure_pin(h, sizeof(double) * chunk));
+    for (int64_t i0 = 0; st == GPTB_OK && i0 < Nt; i0 += chunk) {
+        const int64_t cn = std::min(chunk, Nt - i0);
+        cudaError_t e;
+        if (phi_mode) {
+            e = cudaMemcpyAsync(phichunk, phitest + (size_t)i0 * c.D * c.n, sizeof(double) * cn * c.D * c.n,
+                                cudaMemcpyHostToDevice, h->stream);
+        } else {
+            e = cudaMemcpy2DAsync(h->Xb, h->mpad * sizeof(double), Xtest + i0, Nt * sizeof(double), cn * sizeof(double),
+                                  c.D, cudaMemcpyHostToDevice, h->stream);
+            if (e == cudaSuccess && !f64) {
+                d2f_kernel<<<256, 256, 0, h->stream>>>(h->Xb, h->XbF, (size_t)c.D * h->mpad);
+                h->launches++;
+            }
+        }
+        if (e != cudaSuccess) { st = GPTB_ERR_CUDA; gptb_set_error(h, "pred H2D: %s", cudaGetErrorString(e)); break; }
+        cudaMemsetAsync(acc, 0, sizeof(double) * h->mpad, h->stream);
+        for (int32_t s = 0; st == GPTB_OK && s < S; ++s) {
+            cudaMemcpyAsync(h->pw, w_store + (size_t)s * c.Q, sizeof(double) * c.Q, cudaMemcpyHostToDevice, h->stream);
+            cudaMemcpyAsync(h->pU, U_store + (size_t)s * ucnt, sizeof(double) * ucnt, cudaMemcpyHostToDevice, h->stream);
+            if (!f64) st = gptb_tc_pack_U(h, h->pU, h->pUimg);
+            if (st != GPTB_OK) break;
+            h->phi = phichunk;  // forward_contract reads h->phi in phi mode
+            st = forward_contract(h, phi_mode, nullptr, h->pw, h->pU, h->pUimg, cn, 0.0, false, nullptr);
+            h->phi = saved_phi;
+            if (st != GPTB_OK) break;
+            axpy_kernel<<<64, 256, 0, h->stream>>>(h->fhat, acc, 1.0 / S, (size_t)cn);
+            h->launches++;
+            if (per_sample_out) {
+                e = cudaMemcpyAsync(per_sample_out + (size_t)s * Nt + i0, h->fhat, sizeof(double) * cn,
+                                    cudaMemcpyDeviceToHost, h->stream);
+                if (e != cudaSuccess) { st = GPTB_ERR_CUDA; break; }
+            }
+        }
+        if (st != GPTB_OK) break;
+        if (mean_out) {
+            e = cudaMemcpyAsync(mean_out + i0, acc, sizeof(double) * cn, cudaMemcpyDeviceToHost, h->stream);
+            if (e != cudaSuccess) { st = GPTB_ERR_CUDA; break; }
+        }
+        e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) { st = GPTB_ERR_CUDA; gptb_set_error(h, "pred: %s", cudaGetErrorString(e)); }
+    }
+    cudaStreamSynchronize(h->stream);
+    h->phi = saved_phi;
+    if (phichunk) cudaFree(phichunk);
+    if (acc) cudaFree(acc);
+    return st;
+}
+
+int gptb_pred(gptb_handle *h, const double *w, const double *U, const double *Xtest, int64_t Nt, double *fhat_out) {
+    if (!h || !w || !U || !Xtest || !fhat_out || Nt < 0) return GPTB_ERR_ARG;
+    return pred_impl(h, w, U, 1, Xtest, nullptr, Nt, fhat_out, nullptr);
+}
+
+int gptb_pred_phi(gptb_handle *h, const double *w, const double *U, const double *phitest, int64_t Nt,
+                  double *fhat_out) {
+    if (!h || !w || !U || !phitest || !fhat_out || Nt < 0) return GPTB_ERR_ARG;
+    return pred_impl(h, w, U, 1, nullptr, phitest, Nt, fhat_out, nullptr);
+}
+
+int gptb_pred_samples(gptb_handle *h, const double *w_store, const double *U_store, int32_t S, const double *Xtest,
+                      int64_t Nt, double *mean_out, double *per_sample_out) {
+    if (!h || !w_store || !U_store || !Xtest || S < 1 || Nt < 0 || (!mean_out && !per_sample_out)) return GPTB_ERR_ARG;
+    return pred_impl(h, w_store, U_store, S, Xtest, nullptr, Nt, mean_out, per_sample_out);
+}
+
+int gptb_grad(gptb_handle *h, double signal_var, const int64_t *idx, int64_t start, int64_t bs, double *gradw_out,
+              double *gradU_out, double *fhat_out, int32_t include_prior) {
+    if (!h || !(signal_var > 0)) return GPTB_ERR_ARG;
+    GPTB_TRY(check_ready(h, true, true));
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    const gptb_config &c = h->cfg;
+    const int32_t *rows = nullptr;
+    GPTB_TRY(stage_rows(h, idx, start, bs, &rows));
+    PhaseTimer pt(h);
+    GPTB_TRY(compute_grad(h, signal_var, rows, bs, h->N, false, nullptr, nullptr, pt));
+    pt.finish();
+    const size_t ucnt = (size_t)c.n * c.r * c.D;
+    if (gradw_out) {
+        std::vector<double> w(c.Q);
+        GPTB_CUDA_OK(h, cudaMemcpyAsync(gradw_out, h->grad, sizeof(double) * c.Q, cudaMemcpyDeviceToHost, h->stream));
+        GPTB_CUDA_OK(h, cudaMemcpyAsync(w.data(), h->w, sizeof(double) * c.Q, cudaMemcpyDeviceToHost, h->stream));
+        GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+        if (include_prior)
+            for (int q = 0; q < c.Q; ++q) gradw_out[q] -= w[q];  // - w/sigma_w^2, sigma_w = 1 (:354,:393)
+    }
+    if (gradU_out)
+        GPTB_CUDA_OK(h, cudaMemcpyAsync(gradU_out, h->grad + c.Q, sizeof(double) * ucnt, cudaMemcpyDeviceToHost, h->stream));
+    if (fhat_out) {
+        // fhat of this rank's share only is resident; with one rank that is the whole batch
+        const int64_t lo = (int64_t)h->rank * bs / h->nranks, hi = (int64_t)(h->rank + 1) * bs / h->nranks;
+        GPTB_CUDA_OK(h, cudaMemcpyAsync(fhat_out + lo, h->fhat, sizeof(double) * (hi - lo), cudaMemcpyDeviceToHost,
+                                        h->stream));
+    }
+    GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    return GPTB_OK;
+}
+
+int gptb_proj(int32_t device, int32_t n, int32_t r, const double *U, const double *V, double *out);
+int gptb_geod(int32_t device, int32_t n, int32_t r, const double *U, const double *mom, double t, double *out);
+
+static int proj_geod_host(int32_t device, int32_t n, int32_t r, const double *U, const double *V, double t, double *out,
+                          int mode) {
+    if (!U || !V || !out || n < 1 || r < 1 || r > 64) {
+        gptb_set_error(nullptr, "proj/geod: bad argument (need n>=1, 1<=r<=64)");
+        return GPTB_ERR_ARG;
+    }
+    gptb_handle tmp;  // error sink + scratch owner
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        gptb_set_error(nullptr, "no CUDA device (libgptb200 has no CPU fallback)");
+        return GPTB_ERR_CUDA;
+    }
+    if (device >= 0) cudaSetDevice(device);
+    cudaStream_t s;
+    if (cudaStreamCreate(&s) != cudaSuccess) return GPTB_ERR_CUDA;
+    double *dU = nullptr, *dV = nullptr, *dO = nullptr;
+    int32_t *flag = nullptr;
+    size_t bytes = sizeof(double) * (size_t)n * r;
+    int st = GPTB_OK;
+    if (cudaMalloc(&dU, bytes) != cudaSuccess || cudaMalloc(&dV, bytes) != cudaSuccess ||
+        cudaMalloc(&dO, bytes) != cudaSuccess || cudaMalloc(&flag, sizeof(int32_t)) != cudaSuccess)
+        st = GPTB_ERR_NOMEM;
+    if (st == GPTB_OK) {
+        cudaMemcpyAsync(dU, U, bytes, cudaMemcpyHostToDevice, s);
+        cudaMemcpyAsync(dV, V, bytes, cudaMemcpyHostToDevice, s);
+        cudaMemsetAsync(flag, 0, sizeof(int32_t), s);
+        st = gptb_proj_geod_device(&tmp, s, n, r, dU, dV, t, dO, mode, flag);
+    }
+    int32_t bad = 0;
+    if (st == GPTB_OK) {
+        cudaMemcpyAsync(&bad, flag, sizeof(int32_t), cudaMemcpyDeviceToHost, s);
+        cudaMemcpyAsync(out, dO, bytes, cudaMemcpyDeviceToHost, s);
+        if (cudaStreamSynchronize(s) != cudaSuccess) st = GPTB_ERR_CUDA;
+    }
+    if (st == GPTB_OK && bad) {
+        memset(out, 0, bytes);  // return zeros(n,r), GPT_SGLD.jl:26
+        gptb_set_error(nullptr, "Get NaN when moving along Geodesic. Try smaller epsU");
+        st = GPTB_GEODESIC_NAN;
+    }
+    cudaFree(dU); cudaFree(dV); cudaFree(dO); cudaFree(flag);
+    cudaStreamDestroy(s);
+    return st;
+}
+
+int gptb_proj(int32_t device, int32_t n, int32_t r, const double *U, const double *V, double *out) {
+    return proj_geod_host(device, n, r, U, V, 0.0, out, 0);
+}
+
+int gptb_geod(int32_t device, int32_t n, int32_t r, const double *U, const double *mom, double t, double *out) {
+    return proj_geod_host(device, n, r, U, mom, t, out, 1);
+}
+
+static int step_common(gptb_handle *h, double signal_var, const int32_t *rows, int64_t bs, int64_t N_total,
+                       bool staged, const double *Xstage, const double *ystage, double epsw, double epsU, int32_t flags,
+                       const double *nw_dev, const double *nU_dev) {
+    PhaseTimer pt(h);
+    GPTB_TRY(compute_grad(h, signal_var, rows, bs, N_total, staged, Xstage, ystage, pt));
+    GPTB_TRY(gptb_launch_update(h, epsw, epsU, flags, nw_dev, nU_dev, h->step_counter));
+    pt.done(GPTB_PHASE_UPDATE);
+    pt.finish();
+    h->step_counter++;
+    return GPTB_OK;
+}
+
+int gptb_sgld_step(gptb_handle *h, double signal_var, const int64_t *idx, int64_t start, int64_t bs, double epsw,
+                   double epsU, int32_t flags, const double *noise_w, const double *noise_U) {
+    if (!h || !(signal_var > 0)) return GPTB_ERR_ARG;
+    GPTB_TRY(check_ready(h, true, true));
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    const int32_t *rows = nullptr;
+    GPTB_TRY(stage_rows(h, idx, start, bs, &rows));
+    const double *nw = nullptr, *nU = nullptr;
+    GPTB_TRY(stage_noise(h, noise_w, noise_U, &nw, &nU));
+    GPTB_TRY(step_common(h, signal_var, rows, bs, h->N, false, nullptr, nullptr, epsw, epsU, flags, nw, nU));
+    if (flags & GPTB_FLAG_STIEFEL) return check_nan(h);
+    GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    return GPTB_OK;
+}
+
+int gptb_sgld_step_host(gptb_handle *h, double signal_var, const double *Xb, const double *yb, int64_t bs,
+                        int64_t N_total, double epsw, double epsU, int32_t flags, const double *noise_w,
+                        const double *noise_U, double *w_out) {
+    if (!h || !Xb || !yb || bs < 1 || N_total < 1 || !(signal_var > 0)) return GPTB_ERR_ARG;
+    if (!h->have_features || !h->have_index || !h->have_params) {
+        gptb_set_error(h, "features / index / parameters must be set before gptb_sgld_step_host");
+        return GPTB_ERR_STATE;
+    }
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    const gptb_config &c = h->cfg;
+    // stage the host minibatch: Xb[bs,D] column-major -> device, then row-major rows for the sharded gather
+    if (h->stage_cap < bs) {
+        GPTB_TRY(dev_alloc(h, &h->stage_cm, (size_t)bs * c.D));
+        GPTB_TRY(dev_alloc(h, &h->stage_rm, (size_t)bs * c.D));
+        GPTB_TRY(dev_alloc(h, &h->stage_y, (size_t)bs));
+        h->stage_cap = bs;
+    }
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->stage_cm, Xb, sizeof(double) * bs * c.D, cudaMemcpyHostToDevice, h->stream));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->stage_y, yb, sizeof(double) * bs, cudaMemcpyHostToDevice, h->stream));
+    GPTB_TRY(gptb_launch_transpose(h, h->stage_cm, bs, h->stage_rm));
+    const double *nw = nullptr, *nU = nullptr;
+    GPTB_TRY(stage_noise(h, noise_w, noise_U, &nw, &nU));
+    GPTB_TRY(step_common(h, signal_var, nullptr, bs, N_total, true, h->stage_rm, h->stage_y, epsw, epsU, flags, nw, nU));
+    if (w_out) GPTB_CUDA_OK(h, cudaMemcpyAsync(w_out, h->w, sizeof(double) * c.Q, cudaMemcpyDeviceToHost, h->stream));
+    if (flags & GPTB_FLAG_STIEFEL) return check_nan(h);
+    GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    return GPTB_OK;
+}
+
+int gptb_sgld_run(gptb_handle *h, double signal_var, int64_t m, double epsw, double epsU, int32_t burnin,
+                  int32_t maxepoch, int32_t flags, const int64_t *perms, const double *noise_w, const double *noise_U,
+                  double *w_store, double *U_store) {
+    if (!h || m < 1 || burnin < 0 || maxepoch < 0 || !(signal_var > 0)) return GPTB_ERR_ARG;
+    GPTB_TRY(check_ready(h, true, true));
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    const gptb_config &c = h->cfg;
+    const int64_t N = h->N;
+    const int64_t numbatches = (N + m - 1) / m;  // :353
+    const int64_t T = (int64_t)maxepoch * numbatches;
+    const size_t ucnt = (size_t)c.n * c.r * c.D;
+    const bool keep = (w_store || U_store) && T > 0;
+    // device-side stores so the loop never waits on the host
+    if (keep) {
+        if (w_store) GPTB_TRY(dev_alloc(h, &h->store_w, (size_t)c.Q * T));
+        if (U_store) {
+            int st = dev_alloc(h, &h->store_U, ucnt * (size_t)T);
+            if (st != GPTB_OK) {
+                gptb_set_error(h, "U_store of %lld samples (%zu bytes) does not fit on the device", (long long)T,
+                               ucnt * (size_t)T * 8);
+                return st;
+            }
+        }
+    }
+    int64_t *perm_dev = nullptr;
+    if (perms) GPTB_CUDA_OK(h, cudaMalloc((void **)&perm_dev, sizeof(int64_t) * N));
+    int st = GPTB_OK;
+    uint64_t step = 0;
+    for (int epoch = 1; st == GPTB_OK && epoch <= burnin + maxepoch; ++epoch) {
+        if (perms) {
+            cudaMemcpyAsync(perm_dev, perms + (size_t)(epoch - 1) * N, sizeof(int64_t) * N, cudaMemcpyHostToDevice, h->stream);
+            st = gptb_apply_perm(h, perm_dev);
+        } else {
+            st = gptb_shuffle_order(h, h->epoch_counter);
+        }
+        h->epoch_counter++;
+        for (int64_t batch = 1; st == GPTB_OK && batch <= numbatches; ++batch, ++step) {
+            const int64_t lo = m * (batch - 1), hi = std::min(m * batch, N);  // :379
+            const double *nw = nullptr, *nU = nullptr;
+            st = stage_noise(h, noise_w ? noise_w + (size_t)step * c.Q : nullptr,
+                             noise_U ? noise_U + (size_t)step * ucnt : nullptr, &nw, &nU);
+            if (st != GPTB_OK) break;
+            st = step_common(h, signal_var, h->order + lo, hi - lo, N, false, nullptr, nullptr, epsw, epsU, flags, nw, nU);
+            if (st != GPTB_OK) break;
+            if (epoch > burnin && keep) {
+                const int64_t col = (int64_t)(epoch - burnin - 1) * numbatches + batch - 1;  // :442-443
+                if (w_store) cudaMemcpyAsync(h->store_w + (size_t)col * c.Q, h->w, sizeof(double) * c.Q, cudaMemcpyDeviceToDevice, h->stream);
+                if (U_store) cudaMemcpyAsync(h->store_U + (size_t)col * ucnt, h->U, sizeof(double) * ucnt, cudaMemcpyDeviceToDevice, h->stream);
+            }
+        }
+        // the reference tests for the NaN abort after every geodesic (:422); the device flag is sticky and
+        // freezes the parameters, so looking at it once per epoch returns the same all-zero result
+        if (st == GPTB_OK && (flags & GPTB_FLAG_STIEFEL)) st = check_nan(h);
+    }
+    if (st == GPTB_OK) {
+        cudaError_t e = cudaSuccess;
+        if (keep && w_store) e = cudaMemcpyAsync(w_store, h->store_w, sizeof(double) * c.Q * T, cudaMemcpyDeviceToHost, h->stream);
+        if (e == cudaSuccess && keep && U_store)
+            e = cudaMemcpyAsync(U_store, h->store_U, sizeof(double) * ucnt * T, cudaMemcpyDeviceToHost, h->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) {
+            gptb_set_error(h, "sgld_run: %s", cudaGetErrorString(e));
+            st = GPTB_ERR_CUDA;
+        }
+    } else if (st == GPTB_GEODESIC_NAN) {
+        cudaStreamSynchronize(h->stream);
+        if (w_store) memset(w_store, 0, sizeof(double) * c.Q * T);       // :423
+        if (U_store) memset(U_store, 0, sizeof(double) * ucnt * T);
+    }
+    if (perm_dev) cudaFree(perm_dev);
+    dev_free(&h->store_w);
+    dev_free(&h->store_U);
+    return st;
+}
+
+int gptb_set_profiling(gptb_handle *h, int32_t on) {
+    if (!h) return GPTB_ERR_ARG;
+    h->profiling = on != 0;
+    return GPTB_OK;
+}
+
+int gptb_get_phase_ms(gptb_handle *h, float *ms_out, int64_t *launches_out, int32_t reset) {
+    if (!h) return GPTB_ERR_ARG;
+    if (ms_out)
+        for (int p = 0; p < GPTB_PHASE_COUNT; ++p) ms_out[p] = h->phase_ms[p];
+    if (launches_out) *launches_out = h->launches;
+    if (reset) {
+        for (int p = 0; p < GPTB_PHASE_COUNT; ++p) h->phase_ms[p] = 0.f;
+        h->launches = 0;
+    }
+    return GPTB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,124 @@
+// K4 — gradient all-reduce across ranks (one process per GPU).
+//
+// The reference is single-process; its data-parallel precedent (GPT_SGLD_p.jl:70-108,194-218) splits the
+// minibatch rows over Julia workers that write into SharedArrays.  Here each rank owns one B200, computes
+// the gradient of its share of the minibatch rows and the [gradw | gradU] buffer (Q + n*r*D doubles) is
+// summed with ncclAllReduce over NVLink 5 / NVSwitch, in place, on the handle's stream.
+//
+// NCCL is bound at run time (dlopen of libnccl.so.2 — inside a PyTorch process that resolves to the copy
+// torch already loaded), so libgptb200.so itself has no link-time NCCL dependency and single-GPU users
+// need no NCCL at all.
+#include <dlfcn.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace {
+
+typedef struct { char internal[128]; } ncclUniqueId_t;
+typedef void *ncclComm_p;
+typedef int ncclResult;
+enum { kNcclSum = 0, kNcclFloat32 = 7, kNcclFloat64 = 8 };
+
+struct NcclApi {
+    void *lib = nullptr;
+    ncclResult (*GetUniqueId)(ncclUniqueId_t *) = nullptr;
+    ncclResult (*CommInitRank)(ncclComm_p *, int, ncclUniqueId_t, int) = nullptr;
+    ncclResult (*CommDestroy)(ncclComm_p) = nullptr;
+    ncclResult (*AllReduce)(const void *, void *, size_t, int, int, ncclComm_p, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult) = nullptr;
+    bool ok = false;
+};
+
+NcclApi &api() {
+    static NcclApi a;
+    if (a.lib) return a;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char *nm : names) {
+        a.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+        if (a.lib) break;
+    }
+    if (!a.lib) return a;
+    a.GetUniqueId = (decltype(a.GetUniqueId))dlsym(a.lib, "ncclGetUniqueId");
+    a.CommInitRank = (decltype(a.CommInitRank))dlsym(a.lib, "ncclCommInitRank");
+    a.CommDestroy = (decltype(a.CommDestroy))dlsym(a.lib, "ncclCommDestroy");
+    a.AllReduce = (decltype(a.AllReduce))dlsym(a.lib, "ncclAllReduce");
+    a.GetErrorString = (decltype(a.GetErrorString))dlsym(a.lib, "ncclGetErrorString");
+    a.ok = a.GetUniqueId && a.CommInitRank && a.CommDestroy && a.AllReduce && a.GetErrorString;
+    return a;
+}
+
+}  // namespace
+
+extern "C" int gptb_comm_unique_id(void *id_out_128) {
+    if (!id_out_128) return GPTB_ERR_ARG;
+    NcclApi &a = api();
+    if (!a.ok) {
+        gptb_set_error(nullptr, "NCCL not found (dlopen libnccl.so.2 failed: %s)", dlerror());
+        return GPTB_ERR_NCCL;
+    }
+    ncclUniqueId_t id;
+    ncclResult r = a.GetUniqueId(&id);
+    if (r != 0) {
+        gptb_set_error(nullptr, "ncclGetUniqueId: %s", a.GetErrorString(r));
+        return GPTB_ERR_NCCL;
+    }
+    memcpy(id_out_128, &id, 128);
+    return GPTB_OK;
+}
+
+extern "C" int gptb_comm_init(gptb_handle *h, int32_t nranks, int32_t rank, const void *id_128) {
+    if (!h || !id_128 || nranks < 1 || rank < 0 || rank >= nranks) return GPTB_ERR_ARG;
+    if (h->nccl_comm) {
+        gptb_set_error(h, "communicator already initialised");
+        return GPTB_ERR_STATE;
+    }
+    if (nranks == 1) {
+        h->nranks = 1;
+        h->rank = 0;
+        return GPTB_OK;
+    }
+    NcclApi &a = api();
+    if (!a.ok) {
+        gptb_set_error(h, "NCCL not found (dlopen libnccl.so.2 failed)");
+        return GPTB_ERR_NCCL;
+    }
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    ncclUniqueId_t id;
+    memcpy(&id, id_128, 128);
+    ncclComm_p comm = nullptr;
+    ncclResult r = a.CommInitRank(&comm, nranks, id, rank);
+    if (r != 0) {
+        gptb_set_error(h, "ncclCommInitRank: %s", a.GetErrorString(r));
+        return GPTB_ERR_NCCL;
+    }
+    h->nccl_comm = comm;
+    h->nranks = nranks;
+    h->rank = rank;
+    return GPTB_OK;
+}
+
+extern "C" int gptb_comm_destroy(gptb_handle *h) {
+    if (!h) return GPTB_ERR_ARG;
+    if (h->nccl_comm) {
+        api().CommDestroy((ncclComm_p)h->nccl_comm);
+        h->nccl_comm = nullptr;
+    }
+    h->nranks = 1;
+    h->rank = 0;
+    return GPTB_OK;
+}
+
+// Sum the gradient buffer over ranks, in place (no-op for one rank).
+int gptb_allreduce_grad(gptb_handle *h) {
+    if (h->nranks <= 1) return GPTB_OK;
+    NcclApi &a = api();
+    size_t count = (size_t)h->cfg.Q + (size_t)h->cfg.n * h->cfg.r * h->cfg.D;
+    ncclResult r = a.AllReduce(h->grad, h->grad, count, kNcclFloat64, kNcclSum, (ncclComm_p)h->nccl_comm, h->stream);
+    if (r != 0) {
+        gptb_set_error(h, "ncclAllReduce: %s", a.GetErrorString(r));
+        return GPTB_ERR_NCCL;
+    }
+    h->launches++;
+    return GPTB_OK;
+}

@@ -1,0 +1,215 @@
+// Internal declarations shared by the translation units of libgptb200.so.
+// Not part of the ABI (the ABI is include/gptb200.h).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+
+#include "../../include/gptb200.h"
+
+#define GPTB_CUDA_OK(h, expr)                                                                  \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess) {                                                               \
+            gptb_set_error((h), "%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+            return GPTB_ERR_CUDA;                                                              \
+        }                                                                                      \
+    } while (0)
+
+#define GPTB_TRY(expr)                 \
+    do {                               \
+        int _s = (expr);               \
+        if (_s != GPTB_OK) return _s;  \
+    } while (0)
+
+void gptb_set_error(const gptb_handle *h, const char *fmt, ...);
+
+// ------------------------------------------------------------------------------------------
+// Device-resident model + scratch.  Layouts (device):
+//   Zt, b      double [D][n]        (= Julia Z[j + n*k] order), Zt already divided by length_scale
+//   ZtF, bF    float  [D][npad]     the same in FP32 for the tensor-core path, zero padded
+//   I          int32  [D][Q]        0-based (= Julia I[q + Q*k] - 1)
+//   X          double [N][D]        row-major rows (gather-friendly);  y double [N]
+//   phi        double [N][D][n]     (= Julia phi[j + n*(k + D*i)]), compat path only
+//   order      int32  [N]           current cumulative permutation (GPT_SGLD.jl:373-374)
+//   w          double [Q];  U double [D][r][n]  (= Julia U[j + n*(l + r*k)])
+//   batch scratch, capacity cap rows (mpad = cap rounded up to 128):
+//     Xb   double [D][mpad]  / XbF float [D][mpad];  yb double [mpad]
+//     T    real   [D][r][mpad]     T[k][l][i] = <phi_k(x_i), U^(k)[:,l]>            (phidotU, :193-205)
+//     E    real   [D][r][mpad]     E[k][l][i] = e_i * A[l,k,i]                     (computeA :261-273 times residual)
+//     fhat double [mpad]
+//   grad   double [Q + n*r*D]      [gradw | gradU] in Julia order — the all-reduce buffer
+// ------------------------------------------------------------------------------------------
+struct gptb_handle {
+    gptb_config cfg;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    mutable std::string err;
+
+    // features
+    bool have_features = false, have_index = false, have_train = false, have_phi = false, have_params = false;
+    double amp = 0.0;
+    double *Zt = nullptr, *b = nullptr;
+    float *ZtF = nullptr, *bF = nullptr;
+    int npad = 0;   // n rounded up to 128 (tensor-core M tile of the backward pass / K chunks of the forward)
+    int rpad = 0;   // r rounded up to 16 (UMMA N granularity at M=128)
+    int32_t *I = nullptr;
+
+    // training data
+    int64_t N = 0;
+    double *X = nullptr, *y = nullptr, *phi = nullptr;
+    int32_t *order = nullptr;
+    int32_t *order_tmp = nullptr;
+    uint64_t *sort_keys = nullptr, *sort_keys_tmp = nullptr;
+    void *sort_tmp = nullptr;
+    size_t sort_tmp_bytes = 0;
+
+    // parameters
+    double *w = nullptr, *U = nullptr;
+    float *wF = nullptr;
+    void *Uimg = nullptr;        // tensor-core operand image of U (fp16 hi|lo, UMMA canonical), see tc_layout.cuh
+    size_t Uimg_bytes = 0;
+    bool shadows_valid = false;
+    double *pw = nullptr, *pU = nullptr;   // explicit parameters of pred / pred_samples calls
+    void *pUimg = nullptr;
+    void *ZbF = nullptr;         // float2 [D][npad] interleaved (Zt, b) for the forward generators
+    bool ZbF_valid = false;
+    double *store_w = nullptr, *store_U = nullptr;   // device-side chain stores of gptb_sgld_run
+    double *stage_cm = nullptr, *stage_rm = nullptr, *stage_y = nullptr;  // host-minibatch staging
+    int64_t stage_cap = 0;
+
+    // batch scratch
+    int64_t cap = 0, mpad = 0;
+    double *Xb = nullptr, *yb = nullptr, *fhat = nullptr;
+    float *XbF = nullptr;
+    void *T = nullptr, *E = nullptr;   // real = double (FP64) or float (TC)
+    void *Eimg = nullptr;              // fp16 hi|lo image of E for the backward MMA (TC)
+    int32_t *idx_dev = nullptr;        // explicit batch indices
+    double *grad = nullptr;            // [Q + n r D]
+    float *gradF = nullptr;            // FP32 partial accumulators of the TC path
+    void *tc_partials = nullptr;       // deterministic split-row partials of the backward MMA
+    size_t tc_partials_bytes = 0;
+    float *tc_state = nullptr;         // [0] max|E| of the running step, [1] escale (2^k), [2] 1/escale,
+                                       // [3] uscale (2^k applied to U in Uimg), [4] 1/uscale
+    bool tc_emax_valid = false;
+
+    // update scratch
+    double *G = nullptr;               // [D][r][n]
+    double *small = nullptr;           // per-k r x r reductions and expm workspace
+    size_t small_stride = 0;           // doubles per k
+    double *colnorm = nullptr;         // [D][r]
+    int32_t *nan_flag = nullptr;       // device, sticky
+    int32_t *nan_flag_host = nullptr;  // pinned
+    double *noise_w = nullptr, *noise_U = nullptr;  // staged host-supplied noise
+
+    // multi-sample prediction scratch
+    double *pred_acc = nullptr;
+    int64_t pred_cap = 0;
+
+    // host staging
+    double *pin = nullptr;
+    size_t pin_bytes = 0;
+
+    // comm
+    void *nccl_comm = nullptr;
+    int nranks = 1, rank = 0;
+
+    // bookkeeping
+    uint64_t step_counter = 0;
+    uint64_t epoch_counter = 0;
+    bool profiling = false;
+    float phase_ms[GPTB_PHASE_COUNT] = {0, 0, 0, 0, 0, 0};
+    int64_t launches = 0;
+    cudaEvent_t ev[GPTB_PHASE_COUNT + 1] = {nullptr};
+    int sm_count = 148;
+};
+
+inline bool gptb_is_tc(const gptb_handle *h) { return h->cfg.precision != GPTB_PREC_FP64; }
+
+// ------------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al. 2011) — counter-based, so every rank / every CTA draws the same
+// number for the same (key, counter) regardless of GPU count or launch geometry.
+// ------------------------------------------------------------------------------------------
+struct philox4 {
+    uint32_t x, y, z, w;
+};
+
+__host__ __device__ inline philox4 philox4x32_10(uint64_t key, uint64_t ctr_lo, uint64_t ctr_hi) {
+    uint32_t c0 = (uint32_t)ctr_lo, c1 = (uint32_t)(ctr_lo >> 32), c2 = (uint32_t)ctr_hi, c3 = (uint32_t)(ctr_hi >> 32);
+    uint32_t k0 = (uint32_t)key, k1 = (uint32_t)(key >> 32);
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        uint64_t p0 = (uint64_t)0xD2511F53u * c0;
+        uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
+        uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+        uint32_t n1 = (uint32_t)p1;
+        uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+        uint32_t n3 = (uint32_t)p0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    return philox4{c0, c1, c2, c3};
+}
+
+// Two independent N(0,1) doubles from one Philox block (Box-Muller on two 53-bit uniforms... 32+21 bits each).
+__host__ __device__ inline void philox_normal2(uint64_t key, uint64_t ctr_lo, uint64_t ctr_hi, double *a, double *b) {
+    philox4 p = philox4x32_10(key, ctr_lo, ctr_hi);
+    // u1 in (0,1], u2 in [0,1)
+    double u1 = ((double)(((uint64_t)p.x << 21) | (p.y >> 11)) + 1.0) * (1.0 / 9007199254740992.0);
+    double u2 = (double)(((uint64_t)p.z << 21) | (p.w >> 11)) * (1.0 / 9007199254740992.0);
+    double rad = sqrt(-2.0 * log(u1));
+    double s, c;
+#ifdef __CUDA_ARCH__
+    sincospi(2.0 * u2, &s, &c);
+#else
+    s = sin(6.283185307179586 * u2);
+    c = cos(6.283185307179586 * u2);
+#endif
+    *a = rad * c;
+    *b = rad * s;
+}
+
+// RNG stream ids (upper counter word): keeps noise for w, U^(k), permutations and init apart.
+enum : uint64_t {
+    GPTB_STREAM_NOISE_W = 1ull << 56,
+    GPTB_STREAM_NOISE_U = 2ull << 56,   // + k << 40
+    GPTB_STREAM_PERM = 3ull << 56,
+    GPTB_STREAM_INIT_W = 4ull << 56,
+    GPTB_STREAM_INIT_U = 5ull << 56
+};
+
+// ------------------------------------------------------------------------------------------
+// Kernel launchers (defined in the .cu files named on the right).  All enqueue on h->stream.
+// ------------------------------------------------------------------------------------------
+// fp64_path.cu
+int gptb_launch_features_fp64(gptb_handle *h, const double *Xrm_dev /*[N][D]*/, int64_t N, double *phi_dev);
+int gptb_launch_fwd_fp64(gptb_handle *h, const double *Xb /*[D][mpad]*/, const double *phib /*[bs][D][n] or null*/,
+                         const int32_t *rows /*phi row ids or null*/, const double *U, int64_t bs, int64_t mpad, double *T);
+int gptb_launch_bwd_fp64(gptb_handle *h, const double *Xb, const double *phib, const int32_t *rows, const double *E,
+                         int64_t bs, int64_t mpad, double *gradU /*[D][r][n], accumulated*/);
+// contract.cu
+int gptb_launch_contract(gptb_handle *h, const void *T, const void *w, const double *yb, int64_t bs, int64_t mpad,
+                         double escale, bool want_grad, double *fhat, double *gradw /*accumulated*/, void *E, void *Eimg,
+                         bool real_is_double);
+// update.cu
+int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
+                       const double *noise_U, uint64_t step);
+int gptb_proj_geod_device(gptb_handle *scratch_owner, cudaStream_t s, int n, int r, const double *U, const double *V,
+                          double t, double *out, int mode /*0 proj, 1 geod*/, int32_t *nan_flag);
+// batch.cu
+int gptb_launch_gather(gptb_handle *h, const int32_t *rows, int64_t start, int64_t bs, int64_t row_off);
+int gptb_shuffle_order(gptb_handle *h, uint64_t epoch);
+// tc_path.cu
+int gptb_tc_pack_params(gptb_handle *h);
+int gptb_tc_pack_U(gptb_handle *h, const double *U, void *Uimg);
+int gptb_tc_update_escale(gptb_handle *h);
+int gptb_launch_fwd_tc(gptb_handle *h, const float *XbF, const void *Uimg, int64_t bs, int64_t mpad, float *T);
+int gptb_launch_bwd_tc(gptb_handle *h, const float *XbF, const void *Eimg, int64_t bs, int64_t mpad, double *gradU);
+size_t gptb_tc_uimg_bytes(const gptb_handle *h);
+size_t gptb_tc_eimg_bytes(const gptb_handle *h, int64_t mpad);
+// comm.cu
+int gptb_allreduce_grad(gptb_handle *h);

@@ -1,0 +1,530 @@
+// K5 — SGLD step on w and SGLD-ERM step on every U^(k) (FP64 throughout).
+//
+// Replaces (all /root/reference/GPT_SGLD.jl):
+//   :411-414  w += epsw*gradw/2 + sqrt(epsw)*randn(Q)
+//   :417-439  mom = proj(U_k, sqrt(epsU)*gradU_k/2 + randn(n,r));  U_k = geod(U_k, mom, sqrt(epsU))
+//             (and the Euclidean / no-noise variants)
+//   proj :14-16,  geod :19-37 (expm of the 2r x 2r block matrix, expm(-tA), column renormalisation,
+//             NaN -> zeros + abort).
+//
+// The n x r work is spread over (row-block, k) CTAs in four phases; only r x r quantities cross
+// phases, so the step never serialises on one CTA per factor matrix:
+//   P1 prepare : G = sqrt(epsU)/2*gradU + noise;  partial S1 = U'G, GG = G'G, UU = U'U  (+ the w update)
+//   P2 small   : sym = (S1+S1')/2;  A = U'M = S1 - UU*sym;  M'M = GG - S1'sym - sym S1 + sym UU sym
+//                E = expm(t[[A,-M'M],[I,A]]);  X = expm(-tA);  W = E[:,1:r] X;  C1 = W1 - sym W2, C2 = W2
+//   P3 apply   : Unew = [U M] W = U C1 + G C2   (M = G - U sym is never stored);  column norms
+//   P4 finish  : U = Unew / ||column||, refresh the tensor-core operand image
+// M = proj(U,G) is formed implicitly; the algebra is the reference's, re-associated (agreement ~1e-15).
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+#include "tc_layout.cuh"
+
+namespace {
+
+constexpr int UP_ROWS = 64;      // rows of U per CTA in P1/P3/P4
+constexpr int UP_THREADS = 256;
+
+// layout of the per-k small workspace (doubles)
+struct SmallLayout {
+    int r, r2;
+    size_t S1, GG, UU, CN, C1, C2, sym, A, MM, Tm, E, X, W, ws;  // offsets
+    size_t total;
+    __host__ __device__ explicit SmallLayout(int r_) : r(r_), r2(2 * r_) {
+        size_t o = 0, rr = (size_t)r * r, r22 = (size_t)r2 * r2;
+        S1 = o; o += rr;
+        GG = o; o += rr;
+        UU = o; o += rr;
+        CN = o; o += r;          // column norms^2  (S1..CN are zeroed every step)
+        C1 = o; o += rr;
+        C2 = o; o += rr;
+        sym = o; o += rr;
+        A = o; o += rr;
+        MM = o; o += rr;
+        Tm = o; o += r22;
+        E = o; o += r22;
+        X = o; o += rr;
+        W = o; o += (size_t)r2 * r;
+        ws = o; o += 8 * r22;    // expm workspace
+        total = o;
+    }
+    __host__ __device__ size_t zero_count() const { return 3 * (size_t)r * r + r; }
+};
+
+__device__ __forceinline__ double noise_at(uint64_t key, uint64_t stream, uint64_t step, uint64_t e) {
+    double a, b;
+    philox_normal2(key, stream | (e >> 1), step, &a, &b);
+    return (e & 1) ? b : a;
+}
+
+// ---------------------------------------------------------------- P1
+// grid (ceil(n/UP_ROWS), D + 1); blockIdx.y == D handles w (block x == 0 only).
+__global__ void __launch_bounds__(UP_THREADS)
+k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ w, double *__restrict__ U,
+          double *__restrict__ G, double *__restrict__ small, size_t small_stride, int n, int r, int D, int Q,
+          double epsw, double epsU, int flags, const double *__restrict__ noise_w,
+          const double *__restrict__ noise_U, uint64_t key, uint64_t step, int have_grad) {
+    extern __shared__ double sm[];
+    const int tid = threadIdx.x;
+    const bool langevin = flags & GPTB_FLAG_LANGEVIN, stiefel = flags & GPTB_FLAG_STIEFEL;
+    if (blockIdx.y == D) {
+        if (blockIdx.x != 0 || !have_grad) return;
+        const double sq = sqrt(epsw);
+        for (int q = tid; q < Q; q += UP_THREADS) {
+            double g = grad[q] - w[q];  // prior term of :393 (sigma_w = 1, :354), added once after the all-reduce
+            double z = 0.0;
+            if (langevin) z = noise_w ? noise_w[q] : noise_at(key, GPTB_STREAM_NOISE_W, step, (uint64_t)q);
+            w[q] += epsw * g / 2 + sq * z;
+        }
+        return;
+    }
+    const int k = blockIdx.y;
+    const int j0 = blockIdx.x * UP_ROWS;
+    const int rows = min(UP_ROWS, n - j0);
+    const double *gU = grad + Q + (size_t)k * r * n;
+    double *Uk = U + (size_t)k * r * n, *Gk = G + (size_t)k * r * n;
+    const double sqU = sqrt(epsU);
+    double *Us = sm, *Gs = sm + (size_t)UP_ROWS * r;  // [l][jj]
+    for (int t = tid; t < UP_ROWS * r; t += UP_THREADS) {
+        int jj = t % UP_ROWS, l = t / UP_ROWS, j = j0 + jj;
+        double u = 0.0, g = 0.0;
+        if (jj < rows) {
+            size_t e = (size_t)l * n + j;
+            u = Uk[e];
+            double z = 0.0;
+            if (langevin)
+                z = noise_U ? noise_U[(size_t)k * r * n + e]
+                            : noise_at(key, GPTB_STREAM_NOISE_U | ((uint64_t)k << 40), step, (uint64_t)e);
+            double gr = have_grad ? gU[e] : 0.0;
+            if (stiefel) {
+                g = sqU * gr / 2 + z;                       // :420 argument of proj
+                Gk[e] = g;
+            } else {
+                Uk[e] = u + epsU * (gr - n * u) / 2 + sqU * z;  // :426 / :437
+            }
+        }
+        Us[(size_t)l * UP_ROWS + jj] = u;
+        Gs[(size_t)l * UP_ROWS + jj] = g;
+    }
+    if (!stiefel) return;
+    __syncthreads();
+    double *sk = small + (size_t)k * small_stride;
+    SmallLayout L(r);
+    for (int t = tid; t < r * r; t += UP_THREADS) {
+        int a = t % r, b = t / r;
+        const double *ua = Us + (size_t)a * UP_ROWS, *ub = Us + (size_t)b * UP_ROWS;
+        const double *ga = Gs + (size_t)a * UP_ROWS, *gb = Gs + (size_t)b * UP_ROWS;
+        double s1 = 0.0, gg = 0.0, uu = 0.0;
+        for (int jj = 0; jj < UP_ROWS; ++jj) {
+            s1 = fma(ua[jj], gb[jj], s1);
+            gg = fma(ga[jj], gb[jj], gg);
+            uu = fma(ua[jj], ub[jj], uu);
+        }
+        atomicAdd(&sk[L.S1 + a + (size_t)r * b], s1);
+        atomicAdd(&sk[L.GG + a + (size_t)r * b], gg);
+        atomicAdd(&sk[L.UU + a + (size_t)r * b], uu);
+    }
+}
+
+// ---------------------------------------------------------------- P2 helpers (one CTA, col-major)
+__device__ void bmm(const double *A, const double *B, double *C, int m, int kk, int n2) {
+    for (int t = threadIdx.x; t < m * n2; t += blockDim.x) {
+        int i = t % m, j = t / m;
+        double s = 0.0;
+        for (int p = 0; p < kk; ++p) s = fma(A[i + (size_t)m * p], B[p + (size_t)kk * j], s);
+        C[t] = s;
+    }
+    __syncthreads();
+}
+
+// In-place Gaussian elimination with partial pivoting: A X = B (n2 x n2 each).  Returns via *bad.
+__device__ void bsolve(double *A, double *B, int n2, int *bad_s) {
+    __shared__ int piv;
+    for (int c = 0; c < n2; ++c) {
+        if (threadIdx.x == 0) {
+            int p = c;
+            double best = fabs(A[c + (size_t)n2 * c]);
+            for (int i = c + 1; i < n2; ++i) {
+                double v = fabs(A[i + (size_t)n2 * c]);
+                if (v > best) { best = v; p = i; }
+            }
+            piv = p;
+            if (!(best > 0.0)) *bad_s = 1;
+        }
+        __syncthreads();
+        int p = piv;
+        if (p != c) {
+            for (int j = threadIdx.x; j < 2 * n2; j += blockDim.x) {
+                double *M = j < n2 ? A : B;
+                int jc = j < n2 ? j : j - n2;
+                double tmp = M[c + (size_t)n2 * jc];
+                M[c + (size_t)n2 * jc] = M[p + (size_t)n2 * jc];
+                M[p + (size_t)n2 * jc] = tmp;
+            }
+        }
+        __syncthreads();
+        const double d = A[c + (size_t)n2 * c];
+        // eliminate below the pivot: columns c+1.. of A and all of B (column c of A is left as is)
+        int nrow = n2 - c - 1, ncolA = n2 - c - 1;
+        for (int t = threadIdx.x; t < nrow * (ncolA + n2); t += blockDim.x) {
+            int i = c + 1 + t % nrow, jj = t / nrow;
+            double f = A[i + (size_t)n2 * c] / d;
+            if (jj < ncolA) {
+                int j = c + 1 + jj;
+                A[i + (size_t)n2 * j] -= f * A[c + (size_t)n2 * j];
+            } else {
+                int j = jj - ncolA;
+                B[i + (size_t)n2 * j] -= f * B[c + (size_t)n2 * j];
+            }
+        }
+        __syncthreads();
+    }
+    for (int j = threadIdx.x; j < n2; j += blockDim.x) {
+        for (int i = n2 - 1; i >= 0; --i) {
+            double s = B[i + (size_t)n2 * j];
+            for (int p = i + 1; p < n2; ++p) s -= A[i + (size_t)n2 * p] * B[p + (size_t)n2 * j];
+            B[i + (size_t)n2 * j] = s / A[i + (size_t)n2 * i];
+        }
+    }
+    __syncthreads();
+}
+
+// expm by scaling and squaring with a diagonal Pade approximant (Higham 2005) — the algorithm behind
+// Julia 0.3 Base.expm at GPT_SGLD.jl:23,28: degree 3/5/7/9 for small 1-norms, degree 13 with scaling
+// above 2.1.  M (n2 x n2, col-major) is overwritten by exp(M).  ws: 8*n2*n2 doubles.
+__device__ void bexpm(double *M, int n2, double *ws, int *bad_s) {
+    __shared__ double nrm_s;
+    __shared__ int s_s;
+    const size_t sz = (size_t)n2 * n2;
+    double *A2 = ws, *A4 = A2 + sz, *A6 = A4 + sz, *Um = A6 + sz, *Vm = Um + sz, *T1 = Vm + sz, *T2 = T1 + sz,
+           *A8 = T2 + sz;
+    if (threadIdx.x == 0) {
+        double nrm = 0.0;
+        bool nan = false;
+        for (int j = 0; j < n2; ++j) {
+            double s = 0.0;
+            for (int i = 0; i < n2; ++i) s += fabs(M[i + (size_t)n2 * j]);
+            if (s != s || isinf(s)) nan = true;
+            nrm = fmax(nrm, s);
+        }
+        if (nan) *bad_s = 1;
+        nrm_s = nrm;
+        int s = 0;
+        if (nrm > 5.371920351148152) s = max(0, (int)ceil(log2(nrm / 5.371920351148152)));
+        s_s = s;
+    }
+    __syncthreads();
+    if (*bad_s) return;
+    const double nrm = nrm_s;
+    const int s = s_s;
+    int deg = 13;
+    if (nrm <= 1.495585217958292e-2) deg = 3;
+    else if (nrm <= 2.539398330063230e-1) deg = 5;
+    else if (nrm <= 9.504178996162932e-1) deg = 7;
+    else if (nrm <= 2.097847961257068e0) deg = 9;
+    if (s > 0) {
+        double f = ldexp(1.0, -s);
+        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) M[t] *= f;
+        __syncthreads();
+    }
+    bmm(M, M, A2, n2, n2, n2);
+    if (deg >= 5) bmm(A2, A2, A4, n2, n2, n2);
+    if (deg >= 7) bmm(A4, A2, A6, n2, n2, n2);
+    if (deg == 9) bmm(A6, A2, A8, n2, n2, n2);
+    if (deg == 13) {
+        const double c[14] = {64764752532480000., 32382376266240000., 7771770303897600., 1187353796428800.,
+                              129060195264000.,   10559470521600.,    670442572800.,     33522128640.,
+                              1323241920.,        40840800.,          960960.,           16380.,
+                              182.,               1.};
+        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) T1[t] = c[13] * A6[t] + c[11] * A4[t] + c[9] * A2[t];
+        __syncthreads();
+        bmm(A6, T1, T2, n2, n2, n2);
+        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) {
+            int i = t % n2, j = t / n2;
+            T2[t] += c[7] * A6[t] + c[5] * A4[t] + c[3] * A2[t] + (i == j ? c[1] : 0.0);
+        }
+        __syncthreads();
+        bmm(M, T2, Um, n2, n2, n2);
+        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) T1[t] = c[12] * A6[t] + c[10] * A4[t] + c[8] * A2[t];
+        __syncthreads();
+        bmm(A6, T1, Vm, n2, n2, n2);
+        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) {
+            int i = t % n2, j = t / n2;
+            Vm[t] += c[6] * A6[t] + c[4] * A4[t] + c[2] * A2[t] + (i == j ? c[0] : 0.0);
+        }
+        __syncthreads();
+    } else {
+        // U = M * (sum_{odd} c_i M^(i-1)),  V = sum_{even} c_i M^i
+        double c[10];
+        if (deg == 3) { const double cc[4] = {120., 60., 12., 1.}; for (int i = 0; i < 4; ++i) c[i] = cc[i]; }
+        else if (deg == 5) { const double cc[6] = {30240., 15120., 3360., 420., 30., 1.}; for (int i = 0; i < 6; ++i) c[i] = cc[i]; }
+        else if (deg == 7) { const double cc[8] = {17297280., 8648640., 1995840., 277200., 25200., 1512., 56., 1.}; for (int i = 0; i < 8; ++i) c[i] = cc[i]; }
+        else { const double cc[10] = {17643225600., 8821612800., 2075673600., 302702400., 30270240., 2162160., 110880., 3960., 90., 1.}; for (int i = 0; i < 10; ++i) c[i] = cc[i]; }
+        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) {
+            int i = t % n2, j = t / n2;
+            double u = (i == j ? c[1] : 0.0) + c[3] * A2[t];
+            double v = (i == j ? c[0] : 0.0) + c[2] * A2[t];
+            if (deg >= 5) { u += c[5] * A4[t]; v += c[4] * A4[t]; }
+            if (deg >= 7) { u += c[7] * A6[t]; v += c[6] * A6[t]; }
+            if (deg >= 9) { u += c[9] * A8[t]; v += c[8] * A8[t]; }
+            T2[t] = u;
+            Vm[t] = v;
+        }
+        __syncthreads();
+        bmm(M, T2, Um, n2, n2, n2);
+    }
+    for (size_t t = threadIdx.x; t < sz; t += blockDim.x) {
+        T1[t] = Vm[t] - Um[t];
+        T2[t] = Vm[t] + Um[t];
+    }
+    __syncthreads();
+    bsolve(T1, T2, n2, bad_s);
+    for (int q = 0; q < s; ++q) {
+        bmm(T2, T2, T1, n2, n2, n2);
+        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) T2[t] = T1[t];
+        __syncthreads();
+    }
+    for (size_t t = threadIdx.x; t < sz; t += blockDim.x) M[t] = T2[t];
+    __syncthreads();
+}
+
+// ---------------------------------------------------------------- P2
+// grid (D).  use_sym = 1: G is the un-projected direction (SGLD-ERM step);  0: G already is the
+// tangent vector `mom` of geod(U,mom,t) (GPT_SGLD.jl:19-37 called directly).
+__global__ void __launch_bounds__(1024)
+k_small(double *__restrict__ small, size_t small_stride, int r, double t, int use_sym, int32_t *nan_flag) {
+    __shared__ int bad;
+    double *sk = small + (size_t)blockIdx.x * small_stride;
+    SmallLayout L(r);
+    const int r2 = 2 * r, rr = r * r;
+    if (threadIdx.x == 0) bad = 0;
+    __syncthreads();
+    double *S1 = sk + L.S1, *GG = sk + L.GG, *UU = sk + L.UU, *sym = sk + L.sym, *A = sk + L.A, *MM = sk + L.MM;
+    double *Tm = sk + L.Tm, *X = sk + L.X, *W = sk + L.W, *C1 = sk + L.C1, *C2 = sk + L.C2, *ws = sk + L.ws;
+    double *tmp = sk + L.E, *tmp2 = sk + L.E + rr;  // E region doubles as scratch before expm
+    for (int i = threadIdx.x; i < rr; i += blockDim.x) {
+        int a = i % r, b = i / r;
+        sym[i] = use_sym ? (S1[a + r * b] + S1[b + r * a]) / 2 : 0.0;
+    }
+    __syncthreads();
+    bmm(UU, sym, tmp, r, r, r);        // UU*sym
+    bmm(sym, tmp, tmp2, r, r, r);      // sym*UU*sym
+    for (int i = threadIdx.x; i < rr; i += blockDim.x) A[i] = S1[i] - tmp[i];
+    __syncthreads();
+    // S1'*sym  -> tmp ; sym*S1 is its transpose (sym symmetric)
+    for (int i = threadIdx.x; i < rr; i += blockDim.x) {
+        int a = i % r, b = i / r;
+        double s = 0.0;
+        for (int p = 0; p < r; ++p) s = fma(S1[p + r * a], sym[p + r * b], s);
+        tmp[i] = s;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < rr; i += blockDim.x) {
+        int a = i % r, b = i / r;
+        MM[i] = GG[i] - tmp[a + r * b] - tmp[b + r * a] + tmp2[i];
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < r2 * r2; i += blockDim.x) {
+        int a = i % r2, b = i / r2;
+        double v;
+        if (a < r && b < r) v = A[a + r * b];
+        else if (a < r) v = -MM[a + r * (b - r)];
+        else if (b < r) v = (a - r == b) ? 1.0 : 0.0;
+        else v = A[(a - r) + r * (b - r)];
+        Tm[i] = t * v;
+    }
+    for (int i = threadIdx.x; i < rr; i += blockDim.x) X[i] = -t * A[i];
+    __syncthreads();
+    bexpm(Tm, r2, ws, &bad);
+    if (!bad) {
+        // "if sum(isnan(E))>0" (:24)
+        int local = 0;
+        for (int i = threadIdx.x; i < r2 * r2; i += blockDim.x)
+            if (Tm[i] != Tm[i]) local = 1;
+        if (local) bad = 1;
+    }
+    __syncthreads();
+    if (bad) {
+        if (threadIdx.x == 0) atomicExch(nan_flag, 1);
+        return;
+    }
+    bexpm(X, r, ws, &bad);
+    if (bad) {
+        if (threadIdx.x == 0) atomicExch(nan_flag, 1);
+        return;
+    }
+    bmm(Tm, X, W, r2, r, r);  // first r columns of E are the first r2*r entries (col-major)
+    // C1 = W1 - sym*W2, C2 = W2
+    for (int i = threadIdx.x; i < rr; i += blockDim.x) {
+        int a = i % r, b = i / r;
+        double s = 0.0;
+        for (int p = 0; p < r; ++p) s = fma(sym[a + r * p], W[(p + r) + r2 * b], s);
+        C1[i] = W[a + r2 * b] - s;
+        C2[i] = W[(a + r) + r2 * b];
+    }
+}
+
+// ---------------------------------------------------------------- P3: Unew = U C1 + G C2 -> G ; column norms
+__global__ void __launch_bounds__(UP_THREADS)
+k_apply(const double *__restrict__ U, double *__restrict__ G, double *__restrict__ small, size_t small_stride, int n,
+        int r, const int32_t *__restrict__ nan_flag) {
+    if (*nan_flag) return;
+    extern __shared__ double sm[];
+    const int k = blockIdx.y, j0 = blockIdx.x * UP_ROWS, tid = threadIdx.x;
+    const int rows = min(UP_ROWS, n - j0);
+    double *sk = small + (size_t)k * small_stride;
+    SmallLayout L(r);
+    double *Us = sm, *Gs = Us + (size_t)UP_ROWS * r, *C1 = Gs + (size_t)UP_ROWS * r, *C2 = C1 + r * r,
+           *cn = C2 + r * r;
+    const double *Uk = U + (size_t)k * r * n;
+    double *Gk = G + (size_t)k * r * n;
+    for (int t = tid; t < UP_ROWS * r; t += UP_THREADS) {
+        int jj = t % UP_ROWS, l = t / UP_ROWS;
+        bool ok = jj < rows;
+        Us[t] = ok ? Uk[(size_t)l * n + j0 + jj] : 0.0;
+        Gs[t] = ok ? Gk[(size_t)l * n + j0 + jj] : 0.0;
+    }
+    for (int t = tid; t < r * r; t += UP_THREADS) {
+        C1[t] = sk[L.C1 + t];
+        C2[t] = sk[L.C2 + t];
+    }
+    for (int t = tid; t < r; t += UP_THREADS) cn[t] = 0.0;
+    __syncthreads();
+    for (int t = tid; t < UP_ROWS * r; t += UP_THREADS) {
+        int jj = t % UP_ROWS, l = t / UP_ROWS;
+        double s = 0.0;
+        for (int a = 0; a < r; ++a)
+            s += Us[(size_t)a * UP_ROWS + jj] * C1[a + r * l] + Gs[(size_t)a * UP_ROWS + jj] * C2[a + r * l];
+        if (jj < rows) {
+            Gk[(size_t)l * n + j0 + jj] = s;
+            atomicAdd(&cn[l], s * s);
+        }
+    }
+    __syncthreads();
+    for (int t = tid; t < r; t += UP_THREADS) atomicAdd(&sk[L.CN + t], cn[t]);
+}
+
+// ---------------------------------------------------------------- P4: U = Unew / ||col||
+__global__ void k_finish(double *__restrict__ U, const double *__restrict__ G, const double *__restrict__ small,
+                         size_t small_stride, int n, int r, const int32_t *__restrict__ nan_flag) {
+    if (*nan_flag) return;
+    const int k = blockIdx.y;
+    SmallLayout L(r);
+    const double *cn = small + (size_t)k * small_stride + L.CN;
+    size_t total = (size_t)r * n;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        int l = (int)(e / n);
+        U[(size_t)k * total + e] = G[(size_t)k * total + e] / sqrt(cn[l]);
+    }
+}
+
+// out = V - U * (S1 + S1')/2   (proj, :14-16), S1 = U'V accumulated by k_prepare-style reduction
+__global__ void k_proj_apply(const double *__restrict__ U, const double *__restrict__ V, const double *__restrict__ S1,
+                             int n, int r, double *__restrict__ out) {
+    size_t total = (size_t)r * n;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        int j = (int)(e % n), l = (int)(e / n);
+        double s = 0.0;
+        for (int a = 0; a < r; ++a) s += U[(size_t)a * n + j] * (S1[a + r * l] + S1[l + r * a]) / 2;
+        out[e] = V[e] - s;
+    }
+}
+
+// reductions only (S1 = U'G, GG = G'G, UU = U'U) for the standalone proj/geod entries
+__global__ void __launch_bounds__(UP_THREADS)
+k_reduce_only(const double *__restrict__ U, const double *__restrict__ G, double *__restrict__ small, int n, int r) {
+    extern __shared__ double sm[];
+    const int tid = threadIdx.x, j0 = blockIdx.x * UP_ROWS;
+    const int rows = min(UP_ROWS, n - j0);
+    double *Us = sm, *Gs = sm + (size_t)UP_ROWS * r;
+    for (int t = tid; t < UP_ROWS * r; t += UP_THREADS) {
+        int jj = t % UP_ROWS, l = t / UP_ROWS;
+        bool ok = jj < rows;
+        Us[t] = ok ? U[(size_t)l * n + j0 + jj] : 0.0;
+        Gs[t] = ok ? G[(size_t)l * n + j0 + jj] : 0.0;
+    }
+    __syncthreads();
+    SmallLayout L(r);
+    for (int t = tid; t < r * r; t += UP_THREADS) {
+        int a = t % r, b = t / r;
+        double s1 = 0.0, gg = 0.0, uu = 0.0;
+        for (int jj = 0; jj < UP_ROWS; ++jj) {
+            double ua = Us[(size_t)a * UP_ROWS + jj], ub = Us[(size_t)b * UP_ROWS + jj];
+            double ga = Gs[(size_t)a * UP_ROWS + jj], gb = Gs[(size_t)b * UP_ROWS + jj];
+            s1 = fma(ua, gb, s1);
+            gg = fma(ga, gb, gg);
+            uu = fma(ua, ub, uu);
+        }
+        atomicAdd(&small[L.S1 + t], s1);
+        atomicAdd(&small[L.GG + t], gg);
+        atomicAdd(&small[L.UU + t], uu);
+    }
+}
+
+}  // namespace
+
+size_t gptb_update_small_stride(int r) { return SmallLayout(r).total; }
+
+static int zero_small(gptb_handle *h, double *small, size_t stride, int D, int r) {
+    SmallLayout L(r);
+    GPTB_CUDA_OK(h, cudaMemset2DAsync(small, stride * sizeof(double), 0, L.zero_count() * sizeof(double), D, h->stream));
+    return GPTB_OK;
+}
+
+int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
+                       const double *noise_U, uint64_t step) {
+    const gptb_config &c = h->cfg;
+    const int nb = (c.n + UP_ROWS - 1) / UP_ROWS;
+    const bool stiefel = flags & GPTB_FLAG_STIEFEL;
+    if (stiefel) GPTB_TRY(zero_small(h, h->small, h->small_stride, c.D, c.r));
+    size_t sm1 = 2 * (size_t)UP_ROWS * c.r * sizeof(double);
+    k_prepare<<<dim3(nb, c.D + 1), UP_THREADS, sm1, h->stream>>>(h->grad, h->w, h->U, h->G, h->small, h->small_stride,
+                                                                c.n, c.r, c.D, c.Q, epsw, epsU, flags, noise_w,
+                                                                noise_U, c.seed, step, 1);
+    h->launches++;
+    if (stiefel) {
+        k_small<<<c.D, 1024, 0, h->stream>>>(h->small, h->small_stride, c.r, sqrt(epsU), 1, h->nan_flag);
+        size_t sm3 = (2 * (size_t)UP_ROWS * c.r + 2 * (size_t)c.r * c.r + c.r) * sizeof(double);
+        k_apply<<<dim3(nb, c.D), UP_THREADS, sm3, h->stream>>>(h->U, h->G, h->small, h->small_stride, c.n, c.r,
+                                                              h->nan_flag);
+        int fb = (int)std::min<size_t>(((size_t)c.r * c.n + 255) / 256, 64);
+        k_finish<<<dim3(fb, c.D), 256, 0, h->stream>>>(h->U, h->G, h->small, h->small_stride, c.n, c.r, h->nan_flag);
+        h->launches += 3;
+    }
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    h->shadows_valid = false;
+    return GPTB_OK;
+}
+
+// Standalone proj (mode 0) / geod (mode 1) on device buffers U, V (n x r col-major); scratch from `h`.
+int gptb_proj_geod_device(gptb_handle *h, cudaStream_t s, int n, int r, const double *U, const double *V, double t,
+                          double *out, int mode, int32_t *nan_flag) {
+    SmallLayout L(r);
+    double *small = nullptr;
+    GPTB_CUDA_OK(h, cudaMalloc(&small, L.total * sizeof(double)));
+    cudaMemsetAsync(small, 0, L.zero_count() * sizeof(double), s);
+    const int nb = (n + UP_ROWS - 1) / UP_ROWS;
+    size_t sm1 = 2 * (size_t)UP_ROWS * r * sizeof(double);
+    k_reduce_only<<<nb, UP_THREADS, sm1, s>>>(U, V, small, n, r);
+    if (mode == 0) {
+        int fb = (int)std::min<size_t>(((size_t)r * n + 255) / 256, 1024);
+        k_proj_apply<<<fb, 256, 0, s>>>(U, V, small + L.S1, n, r, out);
+    } else {
+        k_small<<<1, 1024, 0, s>>>(small, L.total, r, t, 0, nan_flag);
+        // Unew = U C1 + V C2 written over a copy of V (k_apply overwrites its G argument)
+        cudaMemcpyAsync(out, V, sizeof(double) * (size_t)n * r, cudaMemcpyDeviceToDevice, s);
+        size_t sm3 = (2 * (size_t)UP_ROWS * r + 2 * (size_t)r * r + r) * sizeof(double);
+        k_apply<<<dim3(nb, 1), UP_THREADS, sm3, s>>>(U, out, small, L.total, n, r, nan_flag);
+        // normalise in place: k_finish reads G (= out) and writes U (= out)
+        int fb = (int)std::min<size_t>(((size_t)r * n + 255) / 256, 64);
+        k_finish<<<dim3(fb, 1), 256, 0, s>>>(out, out, small, L.total, n, r, nan_flag);
+    }
+    cudaError_t e = cudaGetLastError();
+    cudaError_t e2 = cudaStreamSynchronize(s);
+    cudaFree(small);
+    if (e != cudaSuccess || e2 != cudaSuccess) {
+        gptb_set_error(h, "proj/geod kernels: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
+        return GPTB_ERR_CUDA;
+    }
+    return GPTB_OK;
+}

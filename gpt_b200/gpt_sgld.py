@@ -1,0 +1,418 @@
+"""Host-side mirror of the reference's Julia module `GPT_SGLD` (/root/reference/GPT_SGLD.jl:5).
+
+Same exported names, same positional arguments, same array orientation (Julia shapes, column-major
+Float64; `I` is Int32 and 1-based), so code written against the reference reads the same here:
+
+    phi   = feature(X, length_scale, sigma_RBF, phi_scale, Z, b)          # GPT_SGLD.jl:71
+    I     = samplenz(r, D, Q)                                              # :181
+    w_store, U_store = GPTregression(phi, y, signal_var, I, r, Q, m, epsw, epsU,
+                                     burnin, maxepoch, param_seed)         # :345
+    fhat  = pred(w, U, I, phitest)                                         # :233
+
+The one deliberate difference: `feature` returns a lazy `RFFFeatures` handle (X, Z, b and the
+hyper-parameters) instead of the materialised n x D x N array — the kernels generate the features on
+the fly and never write them to memory.  `np.asarray(handle)` / `handle.materialize()` gives the dense
+array; functions also accept a dense `phi` (compatibility path, FP64, HBM-bound).
+
+Everything numerical happens in libgptb200.so through the C ABI (include/gptb200.h); this module only
+marshals arguments.  Host-side helpers that the reference also runs on the host (samplenz,
+datawhitening) are plain NumPy.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _lib as L
+
+__all__ = ["feature", "feature2", "samplenz", "pred", "pred_samples", "GPTregression", "proj", "geod",
+           "datawhitening", "RFFFeatures", "Model", "GptbError", "GeodesicNaN"]
+
+
+class GptbError(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__(f"libgptb200 status {status}: {msg}")
+        self.status = status
+
+
+class GeodesicNaN(GptbError):
+    """expm produced NaN inside geod (GPT_SGLD.jl:24-26)."""
+
+
+_default_precision = L.PREC_TC3
+_default_device = -1
+
+
+def set_default_precision(p: int) -> None:
+    """L.PREC_FP64 (validation), L.PREC_TC3 (default: tensor cores, split operands), L.PREC_TC1 (fast)."""
+    global _default_precision
+    _default_precision = int(p)
+
+
+def set_default_device(d: int) -> None:
+    global _default_device
+    _default_device = int(d)
+
+
+def _f64(a, order="F"):
+    return np.require(a, dtype=np.float64, requirements=["F_CONTIGUOUS" if order == "F" else "C_CONTIGUOUS", "ALIGNED"])
+
+
+def _dp(a):
+    return a.ctypes.data_as(L.c_double_p) if a is not None else None
+
+
+def _check(status: int, handle=None):
+    if status == L.OK:
+        return
+    msg = L.load().gptb_last_error(handle)
+    msg = msg.decode() if msg else ""
+    if status == L.GEODESIC_NAN:
+        raise GeodesicNaN(status, msg)
+    raise GptbError(status, msg)
+
+
+class RFFFeatures:
+    """Lazy result of `feature` / `feature2`: the inputs of GPT_SGLD.jl:71-105, not the n x D x N array."""
+
+    def __init__(self, X, length_scale, sigma_RBF, phi_scale, Z, b, kind):
+        self.X = _f64(np.atleast_2d(X))
+        self.length_scale = np.atleast_1d(np.asarray(length_scale, dtype=np.float64))
+        self.sigma_RBF = float(sigma_RBF)
+        self.phi_scale = float(phi_scale)
+        self.Z = _f64(Z)
+        self.b = None if b is None else _f64(b)
+        self.kind = kind
+        N, D = self.X.shape
+        if self.Z.ndim != 2 or self.Z.shape[1] != D:
+            raise ValueError("Z must be n x D")
+        if self.length_scale.size not in (1, D):
+            raise ValueError("dimensions of X and length_scale do not match")   # GPT_SGLD.jl:326
+        if kind == L.FEAT_SINCOS and self.Z.shape[0] % 2 == 1:
+            raise ValueError("n not even")                                       # GPT_SGLD.jl:90
+        if kind == L.FEAT_COS and (self.b is None or self.b.shape != self.Z.shape):
+            raise ValueError("b must be n x D")
+
+    @property
+    def shape(self):
+        return (self.Z.shape[0], self.X.shape[1], self.X.shape[0])  # size(phi) = (n, D, N)
+
+    def with_X(self, X) -> "RFFFeatures":
+        return RFFFeatures(X, self.length_scale, self.sigma_RBF, self.phi_scale, self.Z, self.b, self.kind)
+
+    def materialize(self, precision: Optional[int] = None) -> np.ndarray:
+        n, D, N = self.shape
+        with Model(D, n, 1, 1, precision=L.PREC_FP64, feature_kind=self.kind) as mdl:
+            mdl.set_features(self)
+            out = np.empty((n, D, N), order="F")
+            _check(L.load().gptb_features(mdl.h, _dp(self.X), N, _dp(out)), mdl.h)
+        return out
+
+    def __array__(self, dtype=None, copy=None):
+        a = self.materialize()
+        return a if dtype is None else a.astype(dtype)
+
+
+def feature(X, length_scale, sigma_RBF, phi_scale, Z, b) -> RFFFeatures:
+    """GPT_SGLD.jl:71-84.  Use Z=randn(n,D), b=2*pi*rand(n,D), phi_scale=sqrt(n/Q^(1/D)) (:70,:306)."""
+    return RFFFeatures(X, length_scale, sigma_RBF, phi_scale, Z, b, L.FEAT_COS)
+
+
+def feature2(X, length_scale, sigma_RBF, phi_scale, Z) -> RFFFeatures:
+    """GPT_SGLD.jl:88-105 (sin/cos pairs; raises "n not even" for odd n)."""
+    return RFFFeatures(X, length_scale, sigma_RBF, phi_scale, Z, None, L.FEAT_SINCOS)
+
+
+def tgp_feature(x, n, sigmaRBF, Z, b01) -> RFFFeatures:
+    """TGP.jl:6-14 with its draws passed in: Z=randn(n,D) (divided by sigmaRBF here), b01=rand(n,D)."""
+    x = np.atleast_2d(np.asarray(x, dtype=np.float64))
+    return RFFFeatures(x, float(sigmaRBF), 1.0, 1.0, Z, 2 * np.pi * np.asarray(b01), L.FEAT_COS)
+
+
+def samplenz(r: int, D: int, Q: int, rng: Optional[np.random.Generator] = None) -> np.ndarray:
+    """GPT_SGLD.jl:181-190: Q distinct cells of the r^D lattice, little-endian base-r digits + 1 (Int32).
+    Host-side like the reference; `rng` replaces Julia's global RNG (seed it for reproducibility)."""
+    rng = np.random.default_rng() if rng is None else rng
+    total = int(r) ** int(D)
+    if Q > total:
+        raise ValueError("Q exceeds r^D")
+    if total <= 10_000_000:
+        L_ = [int(v) for v in rng.choice(total, size=Q, replace=False)]
+    else:
+        seen, L_ = set(), []
+        while len(L_) < Q:
+            v = int(rng.integers(0, total, dtype=np.uint64)) if total < 2 ** 63 else int(rng.integers(0, 2 ** 62)) % total
+            if v not in seen:
+                seen.add(v)
+                L_.append(v)
+    I = np.empty((Q, D), dtype=np.int32, order="F")
+    for q, v in enumerate(L_):
+        for k in range(D):
+            I[q, k] = v % r + 1
+            v //= r
+    return I
+
+
+def datawhitening(X):
+    """GPT_SGLD.jl:62-67: in-place per-column (x-mean)/std (n-1 denominator).  Host preprocessing."""
+    for i in range(X.shape[1]):
+        X[:, i] = (X[:, i] - X[:, i].mean()) / X[:, i].std(ddof=1)
+    return X
+
+
+class Model:
+    """One libgptb200 handle (device state of one chain).  The module-level functions build these on demand;
+    long-running programs (bench, multi-GPU) hold one explicitly."""
+
+    def __init__(self, D, n, r, Q, precision=None, feature_kind=L.FEAT_COS, device=None, seed=0):
+        self.lib = L.load()
+        cfg = L.Config(D=int(D), n=int(n), r=int(r), Q=int(Q),
+                       precision=_default_precision if precision is None else int(precision),
+                       feature_kind=int(feature_kind), device=_default_device if device is None else int(device),
+                       reserved=0, seed=int(seed))
+        self.cfg = cfg
+        self.h = L.H()
+        st = self.lib.gptb_create(C.byref(cfg), C.byref(self.h))
+        if st != L.OK:
+            self.h = None
+            _check(st, None)
+
+    # -- lifetime
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.gptb_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- definition
+    def set_features(self, f: RFFFeatures):
+        _check(self.lib.gptb_set_features(self.h, _dp(f.Z), _dp(f.b), _dp(f.length_scale), f.length_scale.size,
+                                          f.sigma_RBF, f.phi_scale), self.h)
+
+    def set_index(self, I):
+        I = np.require(I, dtype=np.int32, requirements=["F_CONTIGUOUS"])
+        if I.shape != (self.cfg.Q, self.cfg.D):
+            raise ValueError(f"I must be Q x D = {self.cfg.Q} x {self.cfg.D}")
+        _check(self.lib.gptb_set_index(self.h, I.ctypes.data_as(L.c_int32_p)), self.h)
+
+    def set_train(self, X, y):
+        X = _f64(X); y = _f64(np.ravel(y))
+        if X.shape[0] != y.size:
+            raise ValueError("X and y disagree on N")
+        _check(self.lib.gptb_set_train(self.h, _dp(X), _dp(y), X.shape[0]), self.h)
+
+    def set_train_phi(self, phi, y):
+        phi = _f64(phi); y = _f64(np.ravel(y))
+        _check(self.lib.gptb_set_train_phi(self.h, _dp(phi), _dp(y), phi.shape[2]), self.h)
+
+    def set_params(self, w, U):
+        w = _f64(np.ravel(w)); U = _f64(U)
+        if w.size != self.cfg.Q or U.shape != (self.cfg.n, self.cfg.r, self.cfg.D):
+            raise ValueError("w must have Q entries and U must be n x r x D")
+        _check(self.lib.gptb_set_params(self.h, _dp(w), _dp(U)), self.h)
+
+    def get_params(self):
+        w = np.empty(self.cfg.Q)
+        U = np.empty((self.cfg.n, self.cfg.r, self.cfg.D), order="F")
+        _check(self.lib.gptb_get_params(self.h, _dp(w), _dp(U)), self.h)
+        return w, U
+
+    def init_params(self, param_seed: int, stiefel: bool = True):
+        _check(self.lib.gptb_init_params(self.h, int(param_seed), int(bool(stiefel))), self.h)
+
+    # -- compute
+    def pred(self, w, U, Xtest):
+        w = _f64(np.ravel(w)); U = _f64(U); Xtest = _f64(np.atleast_2d(Xtest))
+        out = np.empty(Xtest.shape[0])
+        _check(self.lib.gptb_pred(self.h, _dp(w), _dp(U), _dp(Xtest), Xtest.shape[0], _dp(out)), self.h)
+        return out
+
+    def pred_phi(self, w, U, phitest):
+        w = _f64(np.ravel(w)); U = _f64(U); phitest = _f64(phitest)
+        out = np.empty(phitest.shape[2])
+        _check(self.lib.gptb_pred_phi(self.h, _dp(w), _dp(U), _dp(phitest), phitest.shape[2], _dp(out)), self.h)
+        return out
+
+    def pred_samples(self, w_store, U_store, Xtest, per_sample=False):
+        w_store = _f64(np.atleast_2d(w_store.T).T if w_store.ndim == 1 else w_store)
+        U_store = _f64(U_store if U_store.ndim == 4 else U_store[..., None])
+        Xtest = _f64(np.atleast_2d(Xtest))
+        S = w_store.shape[1]
+        Nt = Xtest.shape[0]
+        mean = np.empty(Nt)
+        per = np.empty((Nt, S), order="F") if per_sample else None
+        _check(self.lib.gptb_pred_samples(self.h, _dp(w_store), _dp(U_store), S, _dp(Xtest), Nt, _dp(mean), _dp(per)),
+               self.h)
+        return (mean, per) if per_sample else mean
+
+    def grad(self, signal_var, idx=None, start=0, bs=None, include_prior=True, want_fhat=True):
+        if idx is not None:
+            idx = np.require(idx, dtype=np.int64, requirements=["C_CONTIGUOUS"])
+            bs = idx.size
+        gw = np.empty(self.cfg.Q)
+        gU = np.empty((self.cfg.n, self.cfg.r, self.cfg.D), order="F")
+        fh = np.empty(bs) if want_fhat else None
+        _check(self.lib.gptb_grad(self.h, float(signal_var), idx.ctypes.data_as(L.c_int64_p) if idx is not None else None,
+                                  int(start), int(bs), _dp(gw), _dp(gU), _dp(fh), int(bool(include_prior))), self.h)
+        return gw, gU, fh
+
+    def sgld_step(self, signal_var, epsw, epsU, idx=None, start=0, bs=None, langevin=True, stiefel=True,
+                  noise_w=None, noise_U=None):
+        if idx is not None:
+            idx = np.require(idx, dtype=np.int64, requirements=["C_CONTIGUOUS"])
+            bs = idx.size
+        nw = _f64(noise_w) if noise_w is not None else None
+        nU = _f64(noise_U) if noise_U is not None else None
+        flags = (L.FLAG_LANGEVIN if langevin else 0) | (L.FLAG_STIEFEL if stiefel else 0)
+        _check(self.lib.gptb_sgld_step(self.h, float(signal_var), idx.ctypes.data_as(L.c_int64_p) if idx is not None else None,
+                                       int(start), int(bs), float(epsw), float(epsU), flags, _dp(nw), _dp(nU)), self.h)
+
+    def sgld_step_host(self, signal_var, Xb, yb, N_total, epsw, epsU, langevin=True, stiefel=True, noise_w=None,
+                       noise_U=None, w_out=None):
+        """Loop body with the minibatch passed from the host.  Xb must be F-contiguous float64 (bs x D)."""
+        nw = _f64(noise_w) if noise_w is not None else None
+        nU = _f64(noise_U) if noise_U is not None else None
+        flags = (L.FLAG_LANGEVIN if langevin else 0) | (L.FLAG_STIEFEL if stiefel else 0)
+        _check(self.lib.gptb_sgld_step_host(self.h, float(signal_var), _dp(Xb), _dp(yb), Xb.shape[0], int(N_total),
+                                            float(epsw), float(epsU), flags, _dp(nw), _dp(nU), _dp(w_out)), self.h)
+
+    def sgld_run(self, signal_var, m, epsw, epsU, burnin, maxepoch, langevin=True, stiefel=True, perms=None,
+                 noise_w=None, noise_U=None, store=True, N=None):
+        Q, n, r, D = self.cfg.Q, self.cfg.n, self.cfg.r, self.cfg.D
+        flags = (L.FLAG_LANGEVIN if langevin else 0) | (L.FLAG_STIEFEL if stiefel else 0)
+        numbatches = -(-int(N) // int(m))
+        T = maxepoch * numbatches
+        w_store = np.zeros((Q, T), order="F") if store else None
+        U_store = np.zeros((n, r, D, T), order="F") if store else None
+        pp = None
+        if perms is not None:
+            pp = np.require(np.asarray(perms), dtype=np.int64, requirements=["C_CONTIGUOUS"])
+            if pp.shape != (burnin + maxepoch, N):
+                raise ValueError("perms must be (burnin+maxepoch) x N")
+        nw = np.require(noise_w, dtype=np.float64, requirements=["C_CONTIGUOUS"]) if noise_w is not None else None
+        nU = None
+        if noise_U is not None:   # [step][n,r,D] with each step's block in Julia (F) order
+            nU = np.ascontiguousarray(np.stack([np.asarray(a, dtype=np.float64).ravel(order="F") for a in noise_U]))
+        st = self.lib.gptb_sgld_run(self.h, float(signal_var), int(m), float(epsw), float(epsU), int(burnin),
+                                    int(maxepoch), flags, pp.ctypes.data_as(L.c_int64_p) if pp is not None else None,
+                                    _dp(nw), _dp(nU), _dp(w_store), _dp(U_store))
+        if st == L.GEODESIC_NAN:
+            # GPT_SGLD.jl:25, :422-424 — print the warning and hand back all-zero stores
+            print("Get NaN when moving along Geodesic. Try smaller epsU")
+            return w_store, U_store
+        _check(st, self.h)
+        return w_store, U_store
+
+    # -- multi-GPU / introspection
+    def comm_init(self, nranks: int, rank: int, unique_id: bytes):
+        buf = C.create_string_buffer(unique_id, 128)
+        _check(self.lib.gptb_comm_init(self.h, int(nranks), int(rank), buf), self.h)
+
+    def set_stream(self, cuda_stream_ptr: int):
+        _check(self.lib.gptb_set_stream(self.h, C.c_void_p(cuda_stream_ptr)), self.h)
+
+    def synchronize(self):
+        _check(self.lib.gptb_synchronize(self.h), self.h)
+
+    def set_profiling(self, on: bool):
+        _check(self.lib.gptb_set_profiling(self.h, int(on)), self.h)
+
+    def phase_ms(self, reset=False):
+        ms = (C.c_float * len(L.PHASES))()
+        n = C.c_int64(0)
+        _check(self.lib.gptb_get_phase_ms(self.h, ms, C.byref(n), int(reset)), self.h)
+        return dict(zip(L.PHASES, [float(v) for v in ms])), int(n.value)
+
+
+def comm_unique_id() -> bytes:
+    buf = C.create_string_buffer(128)
+    _check(L.load().gptb_comm_unique_id(buf), None)
+    return buf.raw
+
+
+def _model_for(phi, r, Q, I, precision=None, seed=0) -> Model:
+    if isinstance(phi, RFFFeatures):
+        n, D, _ = phi.shape
+        mdl = Model(D, n, r, Q, precision=precision, feature_kind=phi.kind, seed=seed)
+        mdl.set_features(phi)
+    else:
+        n, D, _ = phi.shape
+        mdl = Model(D, n, r, Q, precision=precision, seed=seed)
+    mdl.set_index(I)
+    return mdl
+
+
+def pred(w, U, I, phitest, precision: Optional[int] = None):
+    """GPT_SGLD.jl:233-243.  phitest: RFFFeatures (lazy) or a dense n x D x Nt array."""
+    U = np.asarray(U)
+    w = np.ravel(w)
+    with _model_for(phitest, U.shape[1], w.size, I, precision) as mdl:
+        if isinstance(phitest, RFFFeatures):
+            return mdl.pred(w, U, phitest.X)
+        return mdl.pred_phi(w, U, phitest)
+
+
+def pred_samples(w_store, U_store, I, phitest: RFFFeatures, cols: Optional[Sequence[int]] = None,
+                 per_sample=False, precision: Optional[int] = None):
+    """kin40kExperiment.jl:75-87 / GPT_SGLD_p.jl:124-132: mean over stored samples of pred(w_s,U_s,I,phitest)."""
+    if cols is not None:
+        w_store = w_store[:, list(cols)]
+        U_store = U_store[:, :, :, list(cols)]
+    with _model_for(phitest, U_store.shape[1], w_store.shape[0], I, precision) as mdl:
+        return mdl.pred_samples(np.asfortranarray(w_store), np.asfortranarray(U_store), phitest.X, per_sample)
+
+
+def GPTregression(phi, y, signal_var, I, r, Q, m, epsw, epsU, burnin, maxepoch, param_seed, langevin=True,
+                  stiefel=True, *, precision: Optional[int] = None, w0=None, U0=None, perms=None, noise_w=None,
+                  noise_U=None):
+    """GPT_SGLD.jl:345-448.  Returns (w_store[Q,T], U_store[n,r,D,T]), T = maxepoch*ceil(N/m); all zeros (after
+    printing the reference's warning) if the geodesic produced NaN.
+
+    Keyword-only extras (not in the reference): precision; w0/U0 to start from given parameters instead of the
+    param_seed draw; perms / noise_w / noise_U to inject the random draws (parity tests)."""
+    y = np.ravel(np.asarray(y, dtype=np.float64))
+    N = y.size
+    with _model_for(phi, r, Q, I, precision, seed=int(param_seed)) as mdl:
+        if isinstance(phi, RFFFeatures):
+            mdl.set_train(phi.X, y)
+        else:
+            mdl.set_train_phi(phi, y)
+        if w0 is not None:
+            mdl.set_params(w0, U0)
+        else:
+            mdl.init_params(param_seed, stiefel)
+        return mdl.sgld_run(signal_var, m, epsw, epsU, burnin, maxepoch, langevin, stiefel, perms, noise_w, noise_U,
+                            store=True, N=N)
+
+
+def proj(U, V):
+    """GPT_SGLD.jl:14-16."""
+    U = _f64(U); V = _f64(V)
+    out = np.empty(U.shape, order="F")
+    _check(L.load().gptb_proj(_default_device, U.shape[0], U.shape[1], _dp(U), _dp(V), _dp(out)), None)
+    return out
+
+
+def geod(U, mom, t):
+    """GPT_SGLD.jl:19-37.  On NaN prints the reference's warning and returns zeros(n,r)."""
+    U = _f64(U); mom = _f64(mom)
+    out = np.empty(U.shape, order="F")
+    st = L.load().gptb_geod(_default_device, U.shape[0], U.shape[1], _dp(U), _dp(mom), float(t), _dp(out))
+    if st == L.GEODESIC_NAN:
+        print("Get NaN when moving along Geodesic. Try smaller epsU")
+        return out
+    _check(st, None)
+    return out

@@ -1,0 +1,189 @@
+/*
+ * gptb200.h — C ABI of libgptb200.so: the B200-native hot path of hyunjik11/GPT
+ * (tensor-structured random-Fourier-feature GP regression sampled by SGLD on a Stiefel manifold).
+ *
+ * The reference has no FFI of its own: its boundary is the exported function set of the Julia
+ * module GPT_SGLD (/root/reference/GPT_SGLD.jl:5).  Each entry point below names the reference
+ * function (file:line) it replaces; julia/GPT_SGLD.jl and gpt_b200/gpt_sgld.py are the host
+ * modules that keep the reference's names and argument order and `ccall`/ctypes into this ABI.
+ *
+ * Conventions
+ *   - Plain C, no exceptions.  Every call returns an int status (GPTB_OK == 0).
+ *   - All array arguments are HOST pointers owned by the caller, Julia layout: column-major
+ *     Float64 (first index fastest); the core index table I is Int32, 1-based, I[q + Q*k].
+ *   - The handle owns all device memory, streams and communicators.  A handle is not
+ *     thread-safe; different handles are independent.
+ *   - There is no CPU fallback: without a CUDA device every compute call fails with
+ *     GPTB_ERR_CUDA.
+ */
+#ifndef GPTB200_H
+#define GPTB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GPTB_VERSION 100
+
+typedef struct gptb_handle gptb_handle;
+
+enum gptb_status {
+    GPTB_OK = 0,
+    GPTB_ERR_ARG = 1,         /* NULL pointer / value out of range                              */
+    GPTB_ERR_SHAPE = 2,       /* inconsistent sizes (e.g. I entry outside 1..r, odd n for sin/cos) */
+    GPTB_ERR_STATE = 3,       /* call order (features / index / train / params not set yet)       */
+    GPTB_ERR_CUDA = 4,        /* CUDA runtime error, or no device                                */
+    GPTB_ERR_NCCL = 5,        /* NCCL error / library not found                                   */
+    GPTB_ERR_NOMEM = 6,
+    GPTB_GEODESIC_NAN = 7,    /* expm produced NaN: GPT_SGLD.jl:24-26 prints the warning and returns
+                                 zeros(n,r); :422-424 then returns all-zero stores.  Outputs are zero-filled. */
+    GPTB_ERR_UNSUPPORTED = 8
+};
+
+enum gptb_precision {
+    GPTB_PREC_FP64 = 0,  /* FP64 CUDA cores end to end (validation mode, <=1e-10 vs the reference)       */
+    GPTB_PREC_TC3 = 1,   /* tcgen05 tensor cores, operands split hi+lo (3 MMA passes), FP32 accumulate;
+                            <=1e-4 relative vs the reference.  Parameters stay FP64, update in FP64.    */
+    GPTB_PREC_TC1 = 2    /* tcgen05 single pass (hi only): fastest, ~1e-3 relative (not a parity mode)   */
+};
+
+enum gptb_feature_kind {
+    GPTB_FEAT_COS = 0,    /* feature  GPT_SGLD.jl:71-84 : amp*cos(x*Zt+b)                */
+    GPTB_FEAT_SINCOS = 1  /* feature2 GPT_SGLD.jl:88-105: amp2*{sin,cos}(x*Zt), n even   */
+};
+
+enum gptb_flags {
+    GPTB_FLAG_LANGEVIN = 1, /* keyword langevin of GPTregression (GPT_SGLD.jl:345)        */
+    GPTB_FLAG_STIEFEL = 2   /* keyword stiefel                                             */
+};
+
+typedef struct gptb_config {
+    int32_t D;            /* input dimensions                                   */
+    int32_t n;            /* random Fourier features per dimension              */
+    int32_t r;            /* Tucker rank (columns of each U^(k))                */
+    int32_t Q;            /* non-zeros of the core w                            */
+    int32_t precision;    /* enum gptb_precision                                */
+    int32_t feature_kind; /* enum gptb_feature_kind                             */
+    int32_t device;       /* CUDA device ordinal, -1 = current device           */
+    int32_t reserved;
+    uint64_t seed;        /* Philox key for production-mode noise and permutations */
+} gptb_config;
+
+/* ---- lifetime ------------------------------------------------------------------------------ */
+int gptb_version(void);
+int gptb_create(const gptb_config *cfg, gptb_handle **out);
+int gptb_destroy(gptb_handle *h);
+/* Message of the last failing call on h (h == NULL: last failing gptb_create / handle-less call). */
+const char *gptb_last_error(const gptb_handle *h);
+/* Run all of this handle's work on an existing cudaStream_t (pass it as void*); NULL = own stream. */
+int gptb_set_stream(gptb_handle *h, void *cuda_stream);
+/* Blocks until all work queued by this handle has finished. */
+int gptb_synchronize(gptb_handle *h);
+
+/* ---- model definition ---------------------------------------------------------------------- */
+/* Random-feature draws and hyper-parameters of `feature` (GPT_SGLD.jl:71-84) / `feature2` (:88-105).
+ * Z[n,D]; b[n,D] (ignored, may be NULL, for GPTB_FEAT_SINCOS); length_scale has ls_len = 1 or D
+ * entries (Zt = scale(Z, 1./length_scale), :75).  The amplitude phi_scale*sigma_RBF^(1/D)*sqrt(2/n)
+ * (:83; sqrt(1/(n/2)) for feature2, :104) is applied inside the kernels.
+ * TGP.feature (TGP.jl:6-14) is this call with length_scale=sigmaRBF, sigma_RBF=1, phi_scale=1, b=2*pi*rand. */
+int gptb_set_features(gptb_handle *h, const double *Z, const double *b, const double *length_scale,
+                      int32_t ls_len, double sigma_RBF, double phi_scale);
+/* Core sparsity pattern produced by `samplenz` (GPT_SGLD.jl:181-190): I[Q,D], 1-based. */
+int gptb_set_index(gptb_handle *h, const int32_t *I);
+/* Training set: raw inputs X[N,D] (features are generated on the fly, never stored) and y[N]. */
+int gptb_set_train(gptb_handle *h, const double *X, const double *y, int64_t N);
+/* Compatibility: a materialised phi[n,D,N] exactly as `feature` returns it (GPT_SGLD.jl:345 takes phi). */
+int gptb_set_train_phi(gptb_handle *h, const double *phi, const double *y, int64_t N);
+
+/* ---- parameters ---------------------------------------------------------------------------- */
+int gptb_set_params(gptb_handle *h, const double *w /*Q*/, const double *U /*n,r,D*/);
+int gptb_get_params(gptb_handle *h, double *w, double *U);
+/* GPT_SGLD.jl:357-369: w = randn(Q); U^(k) = ((ZZ')^(-1/2) Z)' with Z = randn(r,n) (stiefel != 0) or
+ * randn(n,r,D)/sqrt(n).  Julia's dSFMT stream is not reproducible; draws come from Philox(param_seed). */
+int gptb_init_params(gptb_handle *h, uint64_t param_seed, int32_t stiefel);
+
+/* ---- features / prediction ----------------------------------------------------------------- */
+/* `feature` / `feature2` materialised: phi_out[n,D,N] (GPT_SGLD.jl:71-105). */
+int gptb_features(gptb_handle *h, const double *X, int64_t N, double *phi_out);
+/* `pred(w,U,I,phitest)` (GPT_SGLD.jl:233-243) with phitest = feature(Xtest,...) generated on the fly. */
+int gptb_pred(gptb_handle *h, const double *w, const double *U, const double *Xtest, int64_t Nt,
+              double *fhat_out);
+/* Same with a materialised phitest[n,D,Nt]. */
+int gptb_pred_phi(gptb_handle *h, const double *w, const double *U, const double *phitest, int64_t Nt,
+                  double *fhat_out);
+/* Posterior-predictive sweep (kin40kExperiment.jl:75-87, GPT_SGLD_p.jl:124-132): pred for S stored
+ * samples w_store[Q,S], U_store[n,r,D,S]; mean_out[Nt] = average over samples; per_sample_out[Nt,S]
+ * optional (NULL to skip). */
+int gptb_pred_samples(gptb_handle *h, const double *w_store, const double *U_store, int32_t S,
+                      const double *Xtest, int64_t Nt, double *mean_out, double *per_sample_out);
+
+/* ---- gradients ----------------------------------------------------------------------------- */
+/* Minibatch gradients of the log posterior at the handle's current (w,U), GPT_SGLD.jl:384-408:
+ *   gradw = (N/bs) V (y_b - fhat)/signal_var [- w]      (:393, the prior term when include_prior != 0)
+ *   gradU[:,:,k] = reshape((N/bs) Psi[:,:,k] (y_b - fhat)/signal_var, n, r)            (:405-408)
+ * Batch rows: idx[bs] (0-based rows of the training set) or, when idx == NULL, the contiguous range
+ * [start, start+bs) of the current (permuted) order.  fhat_out[bs] optional. */
+int gptb_grad(gptb_handle *h, double signal_var, const int64_t *idx, int64_t start, int64_t bs,
+              double *gradw_out, double *gradU_out, double *fhat_out, int32_t include_prior);
+
+/* ---- Stiefel manifold ---------------------------------------------------------------------- */
+/* proj(U,V) = V - U(U'V+V'U)/2, GPT_SGLD.jl:14-16.  Uses device `device` (-1 = current). */
+int gptb_proj(int32_t device, int32_t n, int32_t r, const double *U, const double *V, double *out);
+/* geod(U,mom,t), GPT_SGLD.jl:19-37.  Returns GPTB_GEODESIC_NAN and zeros(n,r) when expm gives NaN. */
+int gptb_geod(int32_t device, int32_t n, int32_t r, const double *U, const double *mom, double t, double *out);
+
+/* ---- sampler ------------------------------------------------------------------------------- */
+/* One loop body of GPTregression (GPT_SGLD.jl:378-439) on the resident training set.
+ * noise_w[Q], noise_U[n,r,D]: the randn draws of :412/:420 supplied by the caller (test mode);
+ * NULL = draw from Philox(seed, step).  Returns GPTB_GEODESIC_NAN if the geodesic failed (params
+ * are left untouched in that case). */
+int gptb_sgld_step(gptb_handle *h, double signal_var, const int64_t *idx, int64_t start, int64_t bs,
+                   double epsw, double epsU, int32_t flags, const double *noise_w, const double *noise_U);
+/* Same loop body with the minibatch passed from the host: Xb[bs,D], yb[bs]; N_total is the N of :393.
+ * w_out[Q] (optional) receives the updated w.  This is the end-to-end entry bench.py times. */
+int gptb_sgld_step_host(gptb_handle *h, double signal_var, const double *Xb, const double *yb, int64_t bs,
+                        int64_t N_total, double epsw, double epsU, int32_t flags, const double *noise_w,
+                        const double *noise_U, double *w_out);
+/* The whole of GPTregression (GPT_SGLD.jl:345-448) on the resident training set.
+ *   numbatches = ceil(N/m) (:353); each epoch permutes the data cumulatively (:373-374);
+ *   perms: (burnin+maxepoch) x N 0-based permutations, row-major per epoch, or NULL (Philox shuffle);
+ *   noise_w / noise_U: per-step draws, [Q] / [n,r,D] per step, steps counted over all epochs, or NULL;
+ *   w_store[Q,T], U_store[n,r,D,T], T = maxepoch*numbatches, column (epoch-burnin-1)*numbatches+batch
+ *   (:441-444).  Either may be NULL (nothing kept — what a burn-in epoch does).
+ * On GPTB_GEODESIC_NAN the stores are zero-filled (:422-424). */
+int gptb_sgld_run(gptb_handle *h, double signal_var, int64_t m, double epsw, double epsU, int32_t burnin,
+                  int32_t maxepoch, int32_t flags, const int64_t *perms, const double *noise_w,
+                  const double *noise_U, double *w_store, double *U_store);
+
+/* ---- multi-GPU (one process per GPU) ---------------------------------------------------------- */
+/* Row-sharded data parallelism (the CPU precedent is GPT_SGLD_p.jl:70-108,194-218): every rank holds
+ * the full training set and parameters, computes the gradient of rows [g*bs/G,(g+1)*bs/G) of the global
+ * minibatch, and the [gradw|gradU] buffer is all-reduced (sum) over NVLink.  All ranks then apply the
+ * identical update (same Philox counters), so parameters never need a broadcast.
+ * id is an opaque 128-byte NCCL unique id made by rank 0 and distributed by the host program. */
+int gptb_comm_unique_id(void *id_out_128);
+int gptb_comm_init(gptb_handle *h, int32_t nranks, int32_t rank, const void *id_128);
+int gptb_comm_destroy(gptb_handle *h);
+
+/* ---- introspection (bench / tests) ------------------------------------------------------------ */
+/* Per-phase device time (ms) accumulated since the last reset, measured with CUDA events on the
+ * handle's stream when profiling is on.  Phases: see GPTB_PHASE_*.  launches_out (optional) receives
+ * the number of kernel launches issued by this library since the last reset. */
+enum gptb_phase {
+    GPTB_PHASE_GATHER = 0,   /* batch gather / conversions                        */
+    GPTB_PHASE_FWD = 1,      /* K1 feature x factor forward                       */
+    GPTB_PHASE_CONTRACT = 2, /* K2 core contraction, residual, leave-one-out      */
+    GPTB_PHASE_BWD = 3,      /* K3 factor-gradient back-projection                */
+    GPTB_PHASE_REDUCE = 4,   /* gradient finalisation + all-reduce                */
+    GPTB_PHASE_UPDATE = 5,   /* K5 SGLD / Stiefel update                          */
+    GPTB_PHASE_COUNT = 6
+};
+int gptb_set_profiling(gptb_handle *h, int32_t on);
+int gptb_get_phase_ms(gptb_handle *h, float *ms_out /*GPTB_PHASE_COUNT*/, int64_t *launches_out, int32_t reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPTB200_H */

@@ -1,0 +1,299 @@
+"""CPU restatement (NumPy/SciPy, Float64) of the reference's tensor-RFF GP SGLD path.
+
+TEST INFRASTRUCTURE ONLY.  Nothing under gpt_b200/ may import this module; only tests/,
+__graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs do, and there
+only as the checker (or as the timed CPU baseline), never as the product.
+
+Every function follows one function of /root/reference/GPT_SGLD.jl (Julia 0.3, column-major
+Float64, 1-based Int32 index table I) and cites it.  Arrays keep the *Julia* shapes:
+
+    X[N,D]  Z[n,D]  b[n,D]  phi[n,D,N]  U[n,r,D]  w[Q]  I[Q,D] (1-based)  temp[D,r,N]
+    V[Q,N]  U_phi[Q,N,D]  A[r,D,N]  Psi[n*r,N,D]
+
+Pinning status (see tests/test_oracle_golden.py):
+  * `pred`        — pinned by TensorSynthData{5,10}D100N.h5 (y_j - pred(w,U,I,phi) is the
+                    N(0, 0.1/0.01/0.001) noise MakeSynthData.jl:11-13 added).
+  * `feature`     — functional form and amplitude pinned by the same files (phi[j,k,:] is an
+                    exact cosine in X[:,k] of amplitude phi_scale*sqrt(2/n)); Z,b were not saved.
+  * gradients     — pinned against finite differences of the reference's own log-likelihood
+                    restatement (Diagnostic_gradients.jl:5-37, :133-150).
+  * `geod`/`expm`/`sqrtm`/RNG — **parity unpinned**: Julia 0.3 Base `expm` (Pade-13 scaling and
+                    squaring) is replaced by scipy.linalg.expm (same algorithm family); the
+                    reference holds no known-answer test for these call sites
+                    (GPT_SGLD.jl:23,28,366).  Checked through invariants instead.
+"""
+from __future__ import annotations
+
+import numpy as np
+from scipy.linalg import expm as _expm
+
+
+# --------------------------------------------------------------------------- features
+def feature(X, length_scale, sigma_RBF, phi_scale, Z, b):
+    """GPT_SGLD.jl:71-84.  phi[j,k,i] = phi_scale*sigma_RBF^(1/D)*sqrt(2/n)*cos(X[i,k]*Zt[j,k]+b[j,k]),
+    Zt = scale(Z, 1./length_scale) (:75) — scalar length_scale divides every column."""
+    X = np.asarray(X, dtype=np.float64)
+    Z = np.asarray(Z, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    N, D = X.shape
+    n = Z.shape[0]
+    Zt = Z * (1.0 / np.broadcast_to(np.asarray(length_scale, dtype=np.float64), (D,)))[None, :]
+    # phi[j,k,i] : (n,D,N)
+    phi = np.cos(X.T[None, :, :] * Zt[:, :, None] + b[:, :, None])
+    return phi_scale * sigma_RBF ** (1.0 / D) * np.sqrt(2.0 / n) * phi
+
+
+def feature2(X, length_scale, sigma_RBF, phi_scale, Z):
+    """GPT_SGLD.jl:88-105.  sin/cos pairs from the first n/2 rows of Z; errors when n is odd (:89-91)."""
+    Z = np.asarray(Z, dtype=np.float64)
+    if Z.shape[0] % 2 == 1:
+        raise ValueError("n not even")
+    half_n = Z.shape[0] // 2
+    X = np.asarray(X, dtype=np.float64)
+    N, D = X.shape
+    Zt = Z * (1.0 / np.broadcast_to(np.asarray(length_scale, dtype=np.float64), (D,)))[None, :]
+    arg = X.T[None, :, :] * Zt[:half_n, :, None]          # (half_n, D, N)
+    phi = np.empty((2 * half_n, D, N))
+    phi[0::2] = np.sin(arg)                               # Julia rows 2j-1
+    phi[1::2] = np.cos(arg)                               # Julia rows 2j
+    return phi_scale * sigma_RBF ** (1.0 / D) * phi / np.sqrt(half_n)
+
+
+def tgp_feature(x, Z_over_sigma, b01):
+    """TGP.jl:6-14 for one row x[D]: sqrt(2/n)*cos(x .* Z + 2*pi*b) with Z=randn(n,D)/sigmaRBF and
+    b=rand(n,D) supplied by the caller (the reference reseeds Julia's RNG; its stream cannot be
+    reproduced here)."""
+    Z = np.asarray(Z_over_sigma, dtype=np.float64)
+    n = Z.shape[0]
+    return np.sqrt(2.0 / n) * np.cos(np.asarray(x, dtype=np.float64)[None, :] * Z + 2 * np.pi * np.asarray(b01))
+
+
+def datawhitening(X):
+    """GPT_SGLD.jl:62-67: per-column (x-mean)/std with Julia's std (n-1 denominator); in place."""
+    X = np.asarray(X, dtype=np.float64)
+    for i in range(X.shape[1]):
+        X[:, i] = (X[:, i] - X[:, i].mean()) / X[:, i].std(ddof=1)
+    return X
+
+
+def samplenz(r, D, Q, rng):
+    """GPT_SGLD.jl:181-190: Q distinct cells L of 0:(r^D-1); I[q,:] = digits(L[q], r, D)+1
+    (little-endian base-r digits).  `rng` is a numpy Generator (Julia's sample() stream is not
+    reproducible); the digit convention and distinctness are what is restated."""
+    total = r ** D
+    if total <= 2 ** 62 and total <= 10_000_000:
+        L = rng.choice(total, size=Q, replace=False)
+    else:
+        seen = set()
+        while len(seen) < Q:
+            seen.add(int(rng.integers(0, total)))
+        L = np.array(sorted(seen), dtype=object)
+        rng.shuffle(L)
+    I = np.empty((Q, D), dtype=np.int32)
+    for q in range(Q):
+        v = int(L[q])
+        for k in range(D):
+            I[q, k] = v % r + 1
+            v //= r
+    return I
+
+
+def stiefel_from_gaussian(Zrn):
+    """GPT_SGLD.jl:365-366: U = transpose(sqrtm(Z*Z') \\ Z) for Z = randn(r,n): uniform on V_{n,r}."""
+    Zrn = np.asarray(Zrn, dtype=np.float64)
+    G = Zrn @ Zrn.T
+    lam, Vv = np.linalg.eigh(G)
+    inv_sqrt = (Vv / np.sqrt(lam)) @ Vv.T
+    return (inv_sqrt @ Zrn).T
+
+
+# --------------------------------------------------------------------------- forward model
+def phidotU(U, phi):
+    """GPT_SGLD.jl:193-205: temp[k,l,i] = dot(phi[:,k,i], U[:,l,k])."""
+    return np.einsum("jki,jlk->kli", phi, U, optimize=True)
+
+
+def computeV(temp, I):
+    """GPT_SGLD.jl:208-220: V[q,i] = prod_k temp[k, I[q,k], i]."""
+    Q, D = I.shape
+    V = np.ones((Q, temp.shape[2]))
+    for k in range(D):
+        V *= temp[k, I[:, k] - 1, :]
+    return V
+
+
+def computefhat(V, w):
+    """GPT_SGLD.jl:223-230: fhat[i] = dot(V[:,i], w)."""
+    return V.T @ w
+
+
+def pred(w, U, I, phitest):
+    """GPT_SGLD.jl:233-243."""
+    return computefhat(computeV(phidotU(U, phitest), I), w)
+
+
+# --------------------------------------------------------------------------- gradient pieces
+def computeU_phi(V, temp, I):
+    """GPT_SGLD.jl:246-258: U_phi[q,i,k] = V[q,i] / temp[k, I[q,k], i]  (division, as the reference)."""
+    Q, D = I.shape
+    out = np.empty((Q, V.shape[1], D))
+    for k in range(D):
+        out[:, :, k] = V / temp[k, I[:, k] - 1, :]
+    return out
+
+
+def computeA(U_phi, w, I, r):
+    """GPT_SGLD.jl:261-273: A[l,k,i] = sum_{q: I[q,k]=l} U_phi[q,i,k]*w[q]; unused l stay 0 (:263)."""
+    Q, N, D = U_phi.shape
+    A = np.zeros((r, D, N))
+    for k in range(D):
+        np.add.at(A[:, k, :], I[:, k] - 1, U_phi[:, :, k] * w[:, None])
+    return A
+
+
+def computePsi(A, phi):
+    """GPT_SGLD.jl:276-286: Psi[:,i,k] = kron(A[:,k,i], phi[:,k,i])  (block l = A[l]*phi)."""
+    r, D, N = A.shape
+    n = phi.shape[0]
+    return np.einsum("lki,jki->ljik", A, phi).reshape(r * n, N, D)   # row index l*n + j
+
+
+def gradients(phi_batch, y_batch, w, U, I, N_total, signal_var, sigma_w=1.0):
+    """GPT_SGLD.jl:384-408 for one minibatch.  Returns (gradw, gradU, fhat).
+
+    gradw = (N/bs) V (y-fhat)/signal_var - w/sigma_w^2                      (:393)
+    gradU[:,:,k] = reshape((N/bs) Psi[:,:,k] (y-fhat)/signal_var, n, r)     (:405-408)
+    Psi is never formed: Psi[:,:,k] e == vec(phi_k diag(e) A_k') (block l = sum_i A[l,k,i] e_i phi[:,k,i])."""
+    n, D, bs = phi_batch.shape
+    r = U.shape[1]
+    temp = phidotU(U, phi_batch)
+    V = computeV(temp, I)
+    fhat = computefhat(V, w)
+    e = (N_total / bs) * (y_batch - fhat) / signal_var
+    gradw = V @ e - w / sigma_w ** 2
+    A = computeA(computeU_phi(V, temp, I), w, I, r)
+    gradU = np.einsum("jki,lki,i->jlk", phi_batch, A, e, optimize=True)
+    return gradw, gradU, fhat
+
+
+def gradients_literal(phi_batch, y_batch, w, U, I, N_total, signal_var, sigma_w=1.0):
+    """Same as `gradients` but through the literal Psi array (GPT_SGLD.jl:402,405-408); small cases only."""
+    n, D, bs = phi_batch.shape
+    r = U.shape[1]
+    temp = phidotU(U, phi_batch)
+    V = computeV(temp, I)
+    fhat = computefhat(V, w)
+    gradw = (N_total / bs) * V @ (y_batch - fhat) / signal_var - w / sigma_w ** 2
+    A = computeA(computeU_phi(V, temp, I), w, I, r)
+    Psi = np.empty((n * r, bs, D))
+    for i in range(bs):
+        for k in range(D):
+            Psi[:, i, k] = np.kron(A[:, k, i], phi_batch[:, k, i])
+    gradU = np.empty((n, r, D))
+    for k in range(D):
+        gradU[:, :, k] = ((N_total / bs) * Psi[:, :, k] @ (y_batch - fhat) / signal_var).reshape(n, r, order="F")
+    return gradw, gradU, fhat
+
+
+def loglik(phi, y, w, U, I, sigma):
+    """Diagnostic_gradients.jl:5-37: log p(y|x,w,U) = -||y - fhat||^2 / (2 sigma^2)."""
+    return -np.sum((y - pred(w, U, I, phi)) ** 2) / (2 * sigma ** 2)
+
+
+# --------------------------------------------------------------------------- Stiefel manifold
+def proj(U, V):
+    """GPT_SGLD.jl:14-16: V - U (U'V + V'U)/2."""
+    return V - U @ (U.T @ V + V.T @ U) / 2
+
+
+def geod(U, mom, t):
+    """GPT_SGLD.jl:19-37.  Returns (Unew, nan_flag); on NaN in expm the reference prints a warning and
+    returns zeros(n,r) (:24-26)."""
+    n, r = U.shape
+    A = U.T @ mom
+    temp = np.block([[A, -mom.T @ mom], [np.eye(r), A]])
+    with np.errstate(all="ignore"):
+        E = _expm(t * temp)
+    if np.isnan(E).any():
+        return np.zeros((n, r)), True
+    mexp = _expm(-t * A)
+    tmpU = np.hstack([U, mom]) @ E[:, :r] @ mexp
+    return tmpU / np.linalg.norm(tmpU, axis=0, keepdims=True), False
+
+
+# --------------------------------------------------------------------------- sampler
+def sgld_step(phi_batch, y_batch, w, U, I, N_total, signal_var, epsw, epsU,
+              noise_w=None, noise_U=None, langevin=True, stiefel=True):
+    """One iteration of the loop body GPT_SGLD.jl:378-439.  noise_w[Q], noise_U[n,r,D] are the
+    randn draws of :412 and :420/:426 (supplied by the caller).  Returns (w, U, fhat, nan_flag).
+    Gradients use the pre-update w (:399 precedes :412)."""
+    n, r, D = U.shape
+    gradw, gradU, fhat = gradients(phi_batch, y_batch, w, U, I, N_total, signal_var)
+    if langevin:
+        w_new = w + epsw * gradw / 2 + np.sqrt(epsw) * noise_w
+    else:
+        w_new = w + epsw * gradw / 2
+    U_new = U.copy()
+    if stiefel:
+        for k in range(D):
+            G = np.sqrt(epsU) * gradU[:, :, k] / 2
+            if langevin:
+                G = G + noise_U[:, :, k]
+            mom = proj(U[:, :, k], G)
+            Uk, bad = geod(U[:, :, k], mom, np.sqrt(epsU))
+            if bad:
+                return w_new, U_new, fhat, True
+            U_new[:, :, k] = Uk
+    else:
+        U_new = U + epsU * (gradU - n * U) / 2
+        if langevin:
+            U_new = U_new + np.sqrt(epsU) * noise_U
+    return w_new, U_new, fhat, False
+
+
+def GPTregression(phi, y, signal_var, I, r, Q, m, epsw, epsU, burnin, maxepoch,
+                  w0, U0, perms, noise_w=None, noise_U=None, langevin=True, stiefel=True):
+    """GPT_SGLD.jl:345-448 with the random draws made explicit.
+
+    w0[Q], U0[n,r,D] replace the srand/randn initialisation (:357-369);
+    perms[epoch] (0-based permutation of N) replaces randperm (:373) and is applied cumulatively (:374);
+    noise_w[step][Q], noise_U[step][n,r,D] replace the per-step randn calls, step counted from 0
+    over all burnin+maxepoch epochs.  Returns (w_store[Q,T], U_store[n,r,D,T]) with
+    T = maxepoch*numbatches, column (epoch-burnin-1)*numbatches+batch (:441-444); all zeros if the
+    geodesic produced NaN (:422-424)."""
+    phi = np.array(phi, dtype=np.float64, order="F")
+    y = np.array(y, dtype=np.float64)
+    n, D, N = phi.shape
+    numbatches = int(np.ceil(N / m))
+    T = maxepoch * numbatches
+    w_store = np.zeros((Q, T))
+    U_store = np.zeros((n, r, D, T))
+    w = np.array(w0, dtype=np.float64)
+    U = np.array(U0, dtype=np.float64)
+    step = 0
+    for epoch in range(1, burnin + maxepoch + 1):
+        perm = perms[epoch - 1]
+        phi = phi[:, :, perm]
+        y = y[perm]
+        for batch in range(1, numbatches + 1):
+            lo, hi = m * (batch - 1), min(m * batch, N)
+            nw = None if noise_w is None else noise_w[step]
+            nU = None if noise_U is None else noise_U[step]
+            w, U, _, bad = sgld_step(phi[:, :, lo:hi], y[lo:hi], w, U, I, N, signal_var,
+                                     epsw, epsU, nw, nU, langevin, stiefel)
+            if bad:
+                return np.zeros((Q, T)), np.zeros((n, r, D, T))
+            if epoch > burnin:
+                col = (epoch - burnin - 1) * numbatches + batch - 1
+                w_store[:, col] = w
+                U_store[:, :, :, col] = U
+            step += 1
+    return w_store, U_store
+
+
+def posterior_mean_pred(w_store, U_store, I, phitest, cols):
+    """kin40kExperiment.jl:75-87: mean over the listed store columns of pred(w_s,U_s,I,phitest)."""
+    acc = np.zeros(phitest.shape[2])
+    for c in cols:
+        acc += pred(w_store[:, c], U_store[:, :, :, c], I, phitest)
+    return acc / len(cols)

@@ -1,0 +1,301 @@
+"""Parity of the CUDA path (through the C ABI) with the CPU oracle — needs a B200.
+
+Tolerances (BASELINE.json north_star): <=1e-10 relative in GPTB_PREC_FP64, <=1e-4 relative in the
+tensor-core parity mode GPTB_PREC_TC3; norm-wise per array."""
+import numpy as np
+import pytest
+
+import gpt_oracle as o
+from gpt_b200 import _lib as L
+from gpt_b200 import gpt_sgld as G
+from util import load_golden, make_problem, relerr
+
+pytestmark = pytest.mark.gpu
+
+TOL = {L.PREC_FP64: 1e-10, L.PREC_TC3: 1e-4}
+PRECS = [L.PREC_FP64, L.PREC_TC3]
+IDS = ["fp64", "tc3"]
+
+
+def _feat(P, X=None):
+    X = P["X"] if X is None else X
+    if P["feature2"]:
+        return G.feature2(X, P["ls"], P["sigma_RBF"], P["phi_scale"], P["Z"])
+    return G.feature(X, P["ls"], P["sigma_RBF"], P["phi_scale"], P["Z"], P["b"])
+
+
+def _model(P, prec, train=True, phi_mode=False):
+    kind = L.FEAT_SINCOS if P["feature2"] else L.FEAT_COS
+    m = G.Model(P["D"], P["n"], P["r"], P["Q"], precision=prec, feature_kind=kind, seed=123)
+    m.set_features(_feat(P))
+    m.set_index(P["I"])
+    if train:
+        if phi_mode:
+            m.set_train_phi(P["phi_fn"](P["X"]), P["y"])
+        else:
+            m.set_train(P["X"], P["y"])
+    m.set_params(P["w0"], P["U0"])
+    return m
+
+
+# ------------------------------------------------------------------ features
+@pytest.mark.parametrize("name", ["tensorsynth5d.npz", "tensorsynth10d.npz"])
+def test_feature_known_answer(name):
+    d = load_golden(name)
+    phi = G.feature(d["X"], d["length_scale"], 1.0, float(d["phi_scale"]), d["Z_rec"], d["b_rec"]).materialize()
+    assert phi.shape == d["phi"].shape
+    assert np.abs(phi - d["phi"]).max() < 1e-12
+
+
+def test_feature_variants_vs_oracle():
+    P = make_problem(3, 301, 14, 3, Q=10, seed=5)
+    assert np.abs(_feat(P).materialize() - P["phi_fn"](P["X"])).max() < 1e-13
+    f2 = G.feature2(P["X"], P["ls"], 1.7, P["phi_scale"], P["Z"]).materialize()
+    assert np.abs(f2 - o.feature2(P["X"], P["ls"], 1.7, P["phi_scale"], P["Z"])).max() < 1e-13
+    fs = G.feature(P["X"], 0.8, 1.0, 1.0, P["Z"], P["b"]).materialize()   # scalar length scale
+    assert np.abs(fs - o.feature(P["X"], 0.8, 1.0, 1.0, P["Z"], P["b"])).max() < 1e-13
+    # TGP.feature (TGP.jl:6-14): sqrt(2/n)*cos(x.*Z/sigma + 2 pi b)
+    b01 = P["b"] / (2 * np.pi)
+    t = G.tgp_feature(P["X"][:1], P["n"], 1.4, P["Z"], b01).materialize()[:, :, 0]
+    assert np.abs(t - o.tgp_feature(P["X"][0], P["Z"] / 1.4, b01)).max() < 1e-13
+
+
+# ------------------------------------------------------------------ prediction
+@pytest.mark.parametrize("prec", PRECS, ids=IDS)
+@pytest.mark.parametrize("name", ["tensorsynth5d.npz", "tensorsynth10d.npz"])
+def test_pred_known_answer(name, prec):
+    """pred on the reference's fixture, lazy features (recovered Z,b) and dense phi; residuals are the noise."""
+    d = load_golden(name)
+    want = o.pred(d["w"], d["U"], d["I"], d["phi"])
+    f = G.feature(d["X"], d["length_scale"], 1.0, float(d["phi_scale"]), d["Z_rec"], d["b_rec"])
+    got = G.pred(d["w"], d["U"], d["I"], f, precision=prec)
+    assert relerr(got, want) < TOL[prec]
+    dense = G.pred(d["w"], d["U"], d["I"], d["phi"], precision=prec)
+    assert relerr(dense, want) < 1e-12                                   # dense-phi path is FP64
+    assert abs(np.std(d["y3"] - got) / np.sqrt(1e-3) - 1) < 0.25
+
+
+SHAPES = {  # reduced-N versions of BASELINE configs C1..C4 + odd sizes
+    "c1": dict(D=4, N=700, n=50, r=10),
+    "c2": dict(D=8, N=1100, n=100, r=20),
+    "c3": dict(D=10, N=300, n=500, r=20),
+    "c4": dict(D=10, N=260, n=1000, r=32),
+    "ragged": dict(D=3, N=131, n=37, r=5, Q=40),
+    "one_row": dict(D=2, N=1, n=8, r=2, Q=4),
+}
+
+
+@pytest.mark.parametrize("prec", PRECS, ids=IDS)
+@pytest.mark.parametrize("shape", list(SHAPES))
+def test_pred_vs_oracle(shape, prec):
+    P = make_problem(seed=1, **SHAPES[shape])
+    want = o.pred(P["w0"], P["U0"], P["I"], P["phi_fn"](P["X"]))
+    got = G.pred(P["w0"], P["U0"], P["I"], _feat(P), precision=prec)
+    assert relerr(got, want) < TOL[prec]
+
+
+@pytest.mark.parametrize("prec", PRECS, ids=IDS)
+def test_pred_feature2_and_samples(prec):
+    P = make_problem(4, 500, 24, 4, Q=30, seed=3, feature2=True)
+    want = o.pred(P["w0"], P["U0"], P["I"], P["phi_fn"](P["X"]))
+    assert relerr(G.pred(P["w0"], P["U0"], P["I"], _feat(P), precision=prec), want) < TOL[prec]
+    rng = np.random.default_rng(0)
+    S = 5
+    ws = np.asfortranarray(rng.standard_normal((P["Q"], S)))
+    Us = np.asfortranarray(np.stack([np.stack([o.stiefel_from_gaussian(rng.standard_normal((P["r"], P["n"])))
+                                               for _ in range(P["D"])], 2) for _ in range(S)], 3))
+    phi = P["phi_fn"](P["X"])
+    per_want = np.stack([o.pred(ws[:, s], Us[:, :, :, s], P["I"], phi) for s in range(S)], 1)
+    mean, per = G.pred_samples(ws, Us, P["I"], _feat(P), per_sample=True, precision=prec)
+    assert relerr(per, per_want) < TOL[prec] and relerr(mean, per_want.mean(1)) < TOL[prec]
+    sub = G.pred_samples(ws, Us, P["I"], _feat(P), cols=[1, 3], precision=prec)
+    assert relerr(sub, per_want[:, [1, 3]].mean(1)) < TOL[prec]
+
+
+# ------------------------------------------------------------------ gradients
+@pytest.mark.parametrize("prec", PRECS, ids=IDS)
+@pytest.mark.parametrize("shape", list(SHAPES))
+def test_grad_vs_oracle(shape, prec):
+    P = make_problem(seed=2, **SHAPES[shape])
+    N = P["N"]
+    with _model(P, prec) as m:
+        # explicit row list (ragged minibatch) and contiguous range
+        rng = np.random.default_rng(0)
+        idx = rng.permutation(N)[: max(1, (2 * N) // 3)]
+        phi = P["phi_fn"](P["X"][idx])
+        want = o.gradients(phi, P["y"][idx], P["w0"], P["U0"], P["I"], N, P["signal_var"])
+        gw, gU, fh = m.grad(P["signal_var"], idx=idx)
+        assert relerr(fh, want[2]) < TOL[prec]
+        assert relerr(gw, want[0]) < TOL[prec]
+        assert relerr(gU, want[1]) < TOL[prec]
+        gw2, _, _ = m.grad(P["signal_var"], idx=idx, include_prior=False)
+        assert relerr(gw2, want[0] + P["w0"]) < TOL[prec]
+        lo, bs = 0, N
+        want = o.gradients(P["phi_fn"](P["X"][lo:lo + bs]), P["y"][lo:lo + bs], P["w0"], P["U0"], P["I"], N,
+                           P["signal_var"])
+        gw, gU, fh = m.grad(P["signal_var"], start=lo, bs=bs)
+        assert relerr(gw, want[0]) < TOL[prec] and relerr(gU, want[1]) < TOL[prec]
+
+
+def test_grad_dense_phi_and_errors():
+    P = make_problem(3, 90, 10, 3, Q=12, seed=6)
+    with _model(P, L.PREC_FP64, phi_mode=True) as m:
+        want = o.gradients(P["phi_fn"](P["X"][10:70]), P["y"][10:70], P["w0"], P["U0"], P["I"], P["N"], 1e-3)
+        gw, gU, fh = m.grad(1e-3, start=10, bs=60)
+        assert relerr(gw, want[0]) < 1e-10 and relerr(gU, want[1]) < 1e-10 and relerr(fh, want[2]) < 1e-10
+        with pytest.raises(G.GptbError):
+            m.grad(1e-3, start=80, bs=20)                                 # range outside N
+        with pytest.raises(G.GptbError):
+            m.grad(1e-3, idx=np.array([0, 95]))                           # index outside N
+    with G.Model(3, 10, 3, 12, precision=L.PREC_FP64) as m:
+        with pytest.raises(G.GptbError):
+            m.grad(1e-3, start=0, bs=4)                                   # nothing set yet
+        with pytest.raises(G.GptbError):
+            m.set_index(np.full((12, 3), 4, dtype=np.int32))              # I outside 1..r
+
+
+@pytest.mark.parametrize("prec", PRECS, ids=IDS)
+def test_grad_vs_finite_differences(prec):
+    """Diagnostic_gradients.jl on its own data: analytic (GPU) vs forward differences of the log-likelihood."""
+    d = load_golden("synth_fd.npz")
+    rng = np.random.default_rng(17)
+    X, y = d["Xtrain"], d["ytrain"]
+    N, D = X.shape
+    n, r, Q, sigma = 10, 5, 10, 0.2
+    Z = rng.standard_normal((n, D)); b = 2 * np.pi * rng.random((n, D))
+    I = o.samplenz(r, D, Q, rng)
+    U = np.stack([o.stiefel_from_gaussian(rng.standard_normal((r, n))) for _ in range(D)], 2)
+    w = rng.standard_normal(Q)
+    phi = o.feature(X, 1.4, 1.0, 1.0, Z, b)
+    with G.Model(D, n, r, Q, precision=prec) as m:
+        m.set_features(G.feature(X, 1.4, 1.0, 1.0, Z, b)); m.set_index(I); m.set_train(X, y); m.set_params(w, U)
+        gw, gU, _ = m.grad(sigma ** 2, start=0, bs=N, include_prior=False)
+    ll = o.loglik(phi, y, w, U, I, sigma)
+    h = 1e-6
+    fdw = np.array([(o.loglik(phi, y, w + h * np.eye(Q)[q], U, I, sigma) - ll) / h for q in range(Q)])
+    assert relerr(gw, fdw) < 2e-4
+    fdU = np.zeros_like(U)
+    for k in range(D):
+        for l in range(r):
+            for j in range(n):
+                U2 = U.copy(); U2[j, l, k] += h
+                fdU[j, l, k] = (o.loglik(phi, y, w, U2, I, sigma) - ll) / h
+    assert relerr(gU, fdU) < 2e-4
+
+
+# ------------------------------------------------------------------ Stiefel ops
+def test_proj_geod_vs_oracle():
+    rng = np.random.default_rng(9)
+    for n, r in ((50, 10), (1000, 32), (37, 5), (8, 8)):
+        U = o.stiefel_from_gaussian(rng.standard_normal((r, n)))
+        V = rng.standard_normal((n, r))
+        M = G.proj(U, V)
+        assert relerr(M, o.proj(U, V)) < 1e-12
+        assert np.abs(U.T @ M + M.T @ U).max() < 1e-11
+        for t in (1e-4, 3e-3, 0.2):
+            Un = G.geod(U, M, t)
+            want, _ = o.geod(U, M, t)
+            assert relerr(Un, want) < 1e-10
+            assert np.abs(Un.T @ Un - np.eye(r)).max() < 1e-10
+    Z = G.geod(U, M * 1e200, 1e200)                                       # NaN -> warning + zeros (:24-26)
+    assert Z.shape == U.shape and not Z.any()
+
+
+# ------------------------------------------------------------------ sampler
+@pytest.mark.parametrize("prec", PRECS, ids=IDS)
+@pytest.mark.parametrize("langevin,stiefel", [(True, True), (False, True), (True, False), (False, False)])
+def test_sgld_step_vs_oracle(prec, langevin, stiefel):
+    P = make_problem(4, 400, 50, 10, Q=60, seed=7)
+    rng = np.random.default_rng(1)
+    nw = rng.standard_normal(P["Q"]); nU = np.asfortranarray(rng.standard_normal((P["n"], P["r"], P["D"])))
+    epsw, epsU = 1e-5, 1e-8
+    idx = rng.permutation(P["N"])[:150]
+    want = o.sgld_step(P["phi_fn"](P["X"][idx]), P["y"][idx], P["w0"], P["U0"], P["I"], P["N"], P["signal_var"],
+                       epsw, epsU, nw, nU, langevin, stiefel)
+    with _model(P, prec) as m:
+        m.sgld_step(P["signal_var"], epsw, epsU, idx=idx, langevin=langevin, stiefel=stiefel, noise_w=nw, noise_U=nU)
+        w, U = m.get_params()
+    # the update is FP64 in every mode; in TC3 only the gradient carries 1e-4, scaled by eps/2
+    dw = relerr(w - P["w0"], want[0] - P["w0"]); dU = relerr(U - P["U0"], want[1] - P["U0"])
+    assert dw < max(TOL[prec], 1e-9) and dU < max(TOL[prec], 1e-7)
+    assert relerr(w, want[0]) < 1e-9 if prec == L.PREC_FP64 else relerr(w, want[0]) < 1e-5
+    if stiefel:
+        for k in range(P["D"]):
+            assert np.abs(U[:, :, k].T @ U[:, :, k] - np.eye(P["r"])).max() < 1e-10
+
+
+@pytest.mark.parametrize("prec", PRECS, ids=IDS)
+@pytest.mark.parametrize("phi_mode", [False, True], ids=["lazy", "densephi"])
+def test_GPTregression_vs_oracle(prec, phi_mode):
+    """Whole sampler with injected draws: epochs, cumulative permutations, short last batch, burn-in, store layout."""
+    P = make_problem(3, 150, 16, 4, Q=20, seed=8)
+    N, m, burnin, maxepoch = 150, 64, 1, 2
+    nb = 3
+    rng = np.random.default_rng(2)
+    perms = [rng.permutation(N) for _ in range(burnin + maxepoch)]
+    steps = (burnin + maxepoch) * nb
+    NW = rng.standard_normal((steps, P["Q"])); NU = rng.standard_normal((steps, P["n"], P["r"], P["D"]))
+    phi = P["phi_fn"](P["X"])
+    ws, Us = o.GPTregression(phi, P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m, 1e-5, 1e-8, burnin, maxepoch,
+                             P["w0"], P["U0"], perms, NW, NU)
+    src = phi if phi_mode else _feat(P)
+    gw, gU = G.GPTregression(src, P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m, 1e-5, 1e-8, burnin, maxepoch, 1,
+                             precision=prec, w0=P["w0"], U0=P["U0"], perms=np.stack(perms), noise_w=NW, noise_U=NU)
+    assert gw.shape == ws.shape and gU.shape == Us.shape
+    tol = 1e-8 if (prec == L.PREC_FP64 or phi_mode) else 1e-4
+    assert relerr(gw, ws) < tol and relerr(gU, Us) < tol
+
+
+def test_GPTregression_production_mode_and_nan_abort():
+    P = make_problem(3, 300, 16, 4, Q=20, seed=10)
+    f = _feat(P)
+    a = G.GPTregression(f, P["y"], P["signal_var"], P["I"], P["r"], P["Q"], 100, 1e-5, 1e-8, 1, 2, 7, precision=L.PREC_FP64)
+    b = G.GPTregression(f, P["y"], P["signal_var"], P["I"], P["r"], P["Q"], 100, 1e-5, 1e-8, 1, 2, 7, precision=L.PREC_FP64)
+    assert a[0].shape == (P["Q"], 6) and a[1].shape == (P["n"], P["r"], P["D"], 6)
+    assert relerr(a[0], b[0]) < 1e-12 and relerr(a[1], b[1]) < 1e-12      # counter-based RNG: reproducible
+    assert np.isfinite(a[0]).all() and a[0].any()
+    c = G.GPTregression(f, P["y"], P["signal_var"], P["I"], P["r"], P["Q"], 100, 1e-5, 1e-8, 1, 2, 8, precision=L.PREC_FP64)
+    assert relerr(c[0], a[0]) > 1e-3                                      # different param_seed, different chain
+    for k in range(P["D"]):
+        Uk = a[1][:, :, k, -1]
+        assert np.abs(Uk.T @ Uk - np.eye(P["r"])).max() < 1e-10
+    z = G.GPTregression(f, P["y"], P["signal_var"], P["I"], P["r"], P["Q"], 100, 1e-5, 1e300, 0, 1, 7, precision=L.PREC_FP64)
+    assert not z[0].any() and not z[1].any()                               # :422-424
+
+
+def test_philox_noise_statistics():
+    """Production-mode noise: w_{t+1}-w_t with zero step size on the gradient is sqrt(epsw)*N(0,1)."""
+    P = make_problem(2, 64, 8, 2, Q=4, seed=11)
+    with G.Model(2, 8, 2, 4, precision=L.PREC_FP64, seed=99) as m:
+        m.set_features(_feat(P)); m.set_index(P["I"]); m.set_train(P["X"], P["y"] * 0)
+        draws = []
+        for _ in range(400):
+            m.set_params(np.zeros(4), P["U0"])
+            m.sgld_step(1e30, 1.0, 1e-30, start=0, bs=64)                 # signal_var huge: gradient ~ 0
+            draws.append(m.get_params()[0])
+        z = np.concatenate(draws)
+    assert abs(z.mean()) < 0.1 and abs(z.std() - 1) < 0.06
+    assert abs(np.mean(z ** 4) - 3) < 0.6
+
+
+# ------------------------------------------------------------------ size-independent properties at full scale
+@pytest.mark.parametrize("prec", [L.PREC_TC3], ids=["tc3"])
+def test_full_size_properties_c2(prec):
+    """C2 at full size (D=8, N=10000, n=100, r=20, m=1000): f-hat is linear in w; the minibatch gradient over a
+    partition of the data adds up to the full-batch gradient; parameters stay on the manifold."""
+    P = make_problem(8, 10000, 100, 20, seed=12)
+    with _model(P, prec) as m:
+        f1 = m.pred(P["w0"], P["U0"], P["X"])
+        f2 = m.pred(2.5 * P["w0"], P["U0"], P["X"])
+        assert relerr(f2, 2.5 * f1) < 1e-6
+        full = m.grad(P["signal_var"], start=0, bs=10000, include_prior=False, want_fhat=False)
+        acc_w = np.zeros(P["Q"]); acc_U = np.zeros_like(P["U0"])
+        for s in range(0, 10000, 1000):
+            gw, gU, _ = m.grad(P["signal_var"], start=s, bs=1000, include_prior=False, want_fhat=False)
+            acc_w += gw / 10; acc_U += gU / 10                             # each batch is scaled by N/bs = 10
+        assert relerr(acc_w, full[0]) < 1e-4 and relerr(acc_U, full[1]) < 1e-4
+        for _ in range(3):
+            m.sgld_step(P["signal_var"], 1e-5, 1e-8, start=0, bs=1000)
+        _, U = m.get_params()
+        for k in range(8):
+            assert np.abs(U[:, :, k].T @ U[:, :, k] - np.eye(20)).max() < 1e-9

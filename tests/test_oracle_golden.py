@@ -1,0 +1,171 @@
+"""Pins the CPU oracle (oracle/gpt_oracle.py + oracle/gpt_oracle.c) against the reference's own fixtures
+ — runs without a GPU."""
+import numpy as np
+import pytest
+from scipy.linalg import expm
+
+import c_oracle as co
+import gpt_oracle as o
+from util import load_golden, make_problem, relerr
+
+
+@pytest.mark.parametrize("name,D,Q", [("tensorsynth5d.npz", 5, 32), ("tensorsynth10d.npz", 10, 100)])
+def test_pred_known_answer(name, D, Q):
+    """y_j = pred(w,U,I,phi) + sqrt(v_j) randn (MakeSynthData.jl:10-13): residuals must be that noise."""
+    d = load_golden(name)
+    for impl in (o.pred, co.pred):
+        p = impl(d["w"], d["U"], d["I"], d["phi"])
+        for key, v in (("y1", 0.1), ("y2", 0.01), ("y3", 0.001)):
+            res = d[key] - p
+            assert abs(np.std(res) / np.sqrt(v) - 1) < 0.25, (key, np.std(res))
+            assert abs(np.mean(res)) < 4 * np.sqrt(v / res.size)
+        # the three noisy copies share one noiseless y: differences are pure noise of known variance
+        assert abs(np.std(d["y1"] - d["y2"]) / np.sqrt(0.11) - 1) < 0.25
+
+
+@pytest.mark.parametrize("name", ["tensorsynth5d.npz", "tensorsynth10d.npz"])
+def test_feature_known_answer(name):
+    """feature(X, length_scale, 1, phi_scale, Z_rec, b_rec) reproduces the phi the reference stored
+    (Z,b recovered by tests/golden/make_golden.py; GPT_SGLD.jl:71-84)."""
+    d = load_golden(name)
+    for impl in (o.feature, co.feature):
+        phi = impl(d["X"], d["length_scale"], 1.0, float(d["phi_scale"]), d["Z_rec"], d["b_rec"])
+        assert np.abs(phi - d["phi"]).max() < 1e-12
+    n = d["phi"].shape[0]
+    assert np.abs(d["phi"]).max() <= float(d["phi_scale"]) * np.sqrt(2.0 / n) * (1 + 1e-12)
+
+
+@pytest.mark.parametrize("name,r", [("tensorsynth5d.npz", 2), ("tensorsynth10d.npz", 2)])
+def test_fixture_invariants(name, r):
+    d = load_golden(name)
+    Q, D = d["I"].shape
+    assert d["I"].min() >= 1 and d["I"].max() <= r                       # samplenz range (:185)
+    assert len({tuple(row) for row in d["I"]}) == Q                      # sampled without replacement (:182)
+    for k in range(D):
+        assert np.abs(d["U"][:, :, k].T @ d["U"][:, :, k] - np.eye(r)).max() < 1e-13   # Stiefel init (:366)
+
+
+def test_samplenz_digits():
+    rng = np.random.default_rng(3)
+    I = o.samplenz(3, 4, 50, rng)
+    assert I.dtype == np.int32 and I.shape == (50, 4)
+    L = ((I - 1) * 3 ** np.arange(4)).sum(1)                            # little-endian base-r digits
+    assert len(set(L.tolist())) == 50 and L.max() < 3 ** 4
+    I = o.samplenz(32, 10, 200, rng)                                     # r^D = 2^50 lattice
+    assert I.min() >= 1 and I.max() <= 32 and len({tuple(r_) for r_ in I}) == 200
+
+
+def test_c_oracle_matches_numpy_oracle():
+    P = make_problem(4, 37, 12, 3, Q=20, seed=1)
+    phi = P["phi_fn"](P["X"])
+    assert np.abs(co.feature(P["X"], P["ls"], 1.0, P["phi_scale"], P["Z"], P["b"], 2) - phi).max() < 1e-14
+    assert np.abs(co.feature2(P["X"], P["ls"], 1.3, P["phi_scale"], P["Z"]) -
+                  o.feature2(P["X"], P["ls"], 1.3, P["phi_scale"], P["Z"])).max() < 1e-14
+    assert relerr(co.pred(P["w0"], P["U0"], P["I"], phi, 3), o.pred(P["w0"], P["U0"], P["I"], phi)) < 1e-13
+    g_np = o.gradients(phi, P["y"], P["w0"], P["U0"], P["I"], 1000, 0.01)
+    g_lit = o.gradients_literal(phi, P["y"], P["w0"], P["U0"], P["I"], 1000, 0.01)
+    g_c = co.gradients(phi, P["y"], P["w0"], P["U0"], P["I"], 1000, 0.01, 4)
+    for a, b, c in zip(g_np, g_lit, g_c):
+        assert relerr(a, b) < 1e-12 and relerr(c, b) < 1e-12
+    with pytest.raises(ValueError):
+        o.feature2(P["X"], P["ls"], 1.0, 1.0, P["Z"][:11])               # "n not even" (:90)
+    with pytest.raises(ValueError):
+        co.feature2(P["X"], P["ls"], 1.0, 1.0, P["Z"][:11])
+
+
+def test_gradients_vs_finite_differences():
+    """Diagnostic_gradients.jl:107-158 on its own data (first 200 rows of 10000SynthData.h5), n=10,r=5,Q=10,
+    sigma=0.2, forward differences h=1e-6."""
+    d = load_golden("synth_fd.npz")
+    rng = np.random.default_rng(17)
+    X, y = d["Xtrain"], d["ytrain"]
+    N, D = X.shape
+    n, r, Q, sigma = 10, 5, 10, 0.2
+    Z = rng.standard_normal((n, D)); b = 2 * np.pi * rng.random((n, D))
+    phi = o.feature(X, 1.4, 1.0, 1.0, Z, b)
+    I = o.samplenz(r, D, Q, rng)
+    U = np.stack([o.stiefel_from_gaussian(rng.standard_normal((r, n))) for _ in range(D)], 2)
+    w = np.sqrt(n ** D / Q) * rng.standard_normal(Q)                    # Diagnostic_gradients.jl:116,130
+    ll = o.loglik(phi, y, w, U, I, sigma)
+    gw, gU, _ = o.gradients(phi, y, w, U, I, N, sigma ** 2)             # N/bs = 1: full-batch likelihood gradient
+    gw = gw + w                                                          # remove the prior term of :393
+    h = 1e-6
+    fdw = np.array([(o.loglik(phi, y, w + h * np.eye(Q)[q], U, I, sigma) - ll) / h for q in range(Q)])
+    assert relerr(gw, fdw) < 1e-4
+    fdU = np.zeros_like(U)
+    for k in range(D):
+        for l in range(r):
+            for j in range(n):
+                U2 = U.copy(); U2[j, l, k] += h
+                fdU[j, l, k] = (o.loglik(phi, y, w, U2, I, sigma) - ll) / h
+    assert relerr(gU, fdU) < 1e-4
+    gwc, gUc, _ = co.gradients(phi, y, w, U, I, N, sigma ** 2)
+    assert relerr(gwc + w, fdw) < 1e-4 and relerr(gUc, fdU) < 1e-4
+
+
+def test_expm_c_vs_scipy():
+    rng = np.random.default_rng(5)
+    for scale in (1e-3, 0.3, 2.0, 30.0):
+        A = scale * rng.standard_normal((12, 12))
+        assert relerr(co.expm(A), expm(A)) < 1e-11
+    assert np.isnan(co.expm(np.full((4, 4), np.nan))).all()
+
+
+def test_proj_geod_invariants_and_c():
+    rng = np.random.default_rng(7)
+    n, r = 40, 6
+    U = o.stiefel_from_gaussian(rng.standard_normal((r, n)))
+    V = rng.standard_normal((n, r))
+    M = o.proj(U, V)
+    assert np.abs(U.T @ M + M.T @ U).max() < 1e-12                       # tangent: U'M skew
+    assert np.abs(o.proj(U, M) - M).max() < 1e-12                        # idempotent
+    assert np.abs(co.proj(U, V) - M).max() < 1e-13
+    for t in (1e-4, 1e-2, 0.3):
+        Un, bad = o.geod(U, M, t)
+        assert not bad and np.abs(Un.T @ Un - np.eye(r)).max() < 1e-10   # stays on the manifold
+        Uc, badc = co.geod(U, M, t)
+        assert not badc and np.abs(Uc - Un).max() < 1e-11
+    # small-t series: U(t) = U + t M + O(t^2)
+    Un, _ = o.geod(U, M, 1e-6)
+    assert np.abs(Un - U - 1e-6 * M).max() < 1e-9
+    Z, bad = o.geod(U, M * 1e200, 1e200)
+    assert bad and not Z.any()                                           # NaN -> zeros (:24-26)
+    Zc, badc = co.geod(U, M * 1e200, 1e200)
+    assert badc and not Zc.any()
+
+
+def test_sgld_step_c_vs_numpy_and_store_layout():
+    P = make_problem(3, 50, 8, 3, Q=12, seed=2)
+    phi = P["phi_fn"](P["X"])
+    rng = np.random.default_rng(0)
+    nw = rng.standard_normal(P["Q"]); nU = rng.standard_normal((P["n"], P["r"], P["D"]))
+    for stiefel in (True, False):
+        a = o.sgld_step(phi, P["y"], P["w0"], P["U0"], P["I"], 500, 0.01, 1e-5, 1e-8, nw, nU, True, stiefel)
+        c = co.sgld_step(phi, P["y"], P["w0"], P["U0"], P["I"], 500, 0.01, 1e-5, 1e-8, nw, nU, stiefel)
+        assert relerr(c[0], a[0]) < 1e-13 and relerr(c[1], a[1]) < 1e-13
+    # GPTregression: T = maxepoch*ceil(N/m), short last batch, burn-in epochs not stored (:353,:379-381,:441-444)
+    N, m, burnin, maxepoch = 50, 16, 1, 2
+    nb = 4
+    perms = [rng.permutation(N) for _ in range(burnin + maxepoch)]
+    steps = (burnin + maxepoch) * nb
+    NW = rng.standard_normal((steps, P["Q"])); NU = rng.standard_normal((steps, P["n"], P["r"], P["D"]))
+    ws, Us = o.GPTregression(phi, P["y"], 0.01, P["I"], P["r"], P["Q"], m, 1e-5, 1e-8, burnin, maxepoch,
+                             P["w0"], P["U0"], perms, NW, NU)
+    assert ws.shape == (P["Q"], maxepoch * nb) and Us.shape == (P["n"], P["r"], P["D"], maxepoch * nb)
+    # replay by hand
+    w, U = P["w0"].copy(), P["U0"].copy()
+    ph, yy = phi.copy(), P["y"].copy()
+    s = 0
+    for ep in range(burnin + maxepoch):
+        ph, yy = ph[:, :, perms[ep]], yy[perms[ep]]
+        for bidx in range(nb):
+            lo, hi = bidx * m, min((bidx + 1) * m, N)
+            w, U, _, _ = o.sgld_step(ph[:, :, lo:hi], yy[lo:hi], w, U, P["I"], N, 0.01, 1e-5, 1e-8, NW[s], NU[s])
+            if ep >= burnin:
+                col = (ep - burnin) * nb + bidx
+                assert relerr(ws[:, col], w) < 1e-12 and relerr(Us[:, :, :, col], U) < 1e-12
+            s += 1
+    # NaN abort returns all-zero stores (:422-424)
+    ws, Us = o.GPTregression(phi, P["y"], 0.01, P["I"], P["r"], P["Q"], m, 1e-5, 1e300, 0, 1, P["w0"], P["U0"],
+                             perms, NW, NU)
+    assert not ws.any() and not Us.any()
