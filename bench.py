@@ -1,0 +1,355 @@
+#!/usr/bin/env python
+"""bench.py — SGLD steps/s of the tensor-RFF GP hot path on N B200s (and the C5 prediction sweep).
+
+    python bench.py --gpus 1 --steps 100 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...      # the reference path's CPU restatement on the host cores
+
+Workload = BASELINE.json configs[3] "C4" (the shape the north star's scaling target is quoted on; it fits one
+GPU): D=10, N=10M training rows, n=1000 RFF/dim, r=32, Q=200, minibatch 65536.  A step is one loop body of
+GPTregression (GPT_SGLD.jl:378-439): gather -> K1 forward -> K2 contraction -> K3 factor gradient ->
+(all-reduce) -> K5 SGLD/Stiefel update.  Multi-GPU = the same global minibatch row-sharded over ranks
+(strong scaling), gradients all-reduced with NCCL.
+
+Prints ONE JSON line (rank 0).  `value` = steps/s with the training set resident in HBM (device-timed, max over
+ranks); `e2e` = the same loop body through gptb_sgld_step_host with the minibatch in pinned HOST memory
+(H2D + D2H inside the timed region)."""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+WORKLOADS = {
+    "C1": dict(D=4, N=9568, n=50, r=10, m=500, desc="PowerPlant CCPP shape"),
+    "C2": dict(D=8, N=10000, n=100, r=20, m=1000, desc="kin40k shape"),
+    "C3": dict(D=10, N=32000, n=500, r=20, m=1000, desc="tensorsynth 10D"),
+    "C4": dict(D=10, N=10_000_000, n=1000, r=32, m=65536, desc="synthetic D=10, N=10M"),
+}
+C5 = dict(D=8, Nt=1_000_000, S=200, n=500, r=20)
+Q = 200
+SIGNAL_VAR, EPSW, EPSU = 1e-3, 1e-5, 1e-8   # SynthDataExperiment.jl:7,37-38
+
+
+def synth_model(D, n, r, seed):
+    """Model draws in the reference's conventions."""
+    from gpt_b200 import gpt_sgld as G
+    rng = np.random.default_rng(seed)
+    ls = np.maximum(1.0 + 0.2 * rng.standard_normal(D), 0.3)
+    Z = np.asfortranarray(rng.standard_normal((n, D)))
+    b = np.asfortranarray(2 * np.pi * rng.random((n, D)))
+    phi_scale = np.sqrt(n / Q ** (1.0 / D))
+    I = G.samplenz(r, D, Q, rng)
+    # uniform draws from the Stiefel manifold V_{n,r} (QR of a Gaussian matrix, sign-fixed)
+    def stie():
+        out = np.empty((n, r, D), order="F")
+        for k in range(D):
+            q_, r_ = np.linalg.qr(rng.standard_normal((n, r)))
+            out[:, :, k] = q_ * np.sign(np.diag(r_))
+        return out
+    return dict(ls=ls, Z=Z, b=b, phi_scale=phi_scale, I=I, w_true=rng.standard_normal(Q), U_true=stie(),
+                w0=rng.standard_normal(Q), U0=stie(), rng=rng)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, gpu_index):
+        self.rows, self.stop, self.idx = [], threading.Event(), gpu_index
+        self.t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            self.stop.wait(0.1)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.t.join(6)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [nm for i, nm in enumerate(names) if any(len(r) > 3 + i and r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def cpu_reference_steps_per_sec(W, mdl, budget_s=20.0, sample_rows=2048):
+    """The reference path's CPU restatement (oracle/gpt_oracle.c, FP64, OpenMP over rows like GPT_SGLD_p.jl) timed
+    on the host cores on a bounded row sample of the same workload, scaled linearly in rows to the full minibatch."""
+    import c_oracle as co
+    D, n, r, m = W["D"], W["n"], W["r"], W["m"]
+    ms = min(m, sample_rows)
+    rng = np.random.default_rng(7)
+    X = rng.standard_normal((ms, D))
+    y = rng.standard_normal(ms)
+    threads = co.max_threads()
+    phi = co.feature(X, mdl["ls"], 1.0, mdl["phi_scale"], mdl["Z"], mdl["b"], threads)
+    nw = rng.standard_normal(Q); nU = rng.standard_normal((n, r, D))
+    w, U = mdl["w0"].copy(), mdl["U0"].copy()
+    t0 = time.perf_counter()
+    w, U, _, _ = co.sgld_step(phi, y, w, U, mdl["I"], W["N"], SIGNAL_VAR, EPSW, EPSU, nw, nU, True, threads)  # warm
+    t_first = time.perf_counter() - t0
+    reps = int(max(1, min(20, budget_s / max(t_first, 1e-3) - 1)))
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        w, U, _, _ = co.sgld_step(phi, y, w, U, mdl["I"], W["N"], SIGNAL_VAR, EPSW, EPSU, nw, nU, True, threads)
+    t_step = (time.perf_counter() - t0) / reps
+    full = t_step * (m / ms)
+    return 1.0 / full, threads, f"{reps} steps on {ms} of {m} minibatch rows (features precomputed as the reference does), scaled x{m / ms:g} in rows"
+
+
+def run_reference(args, W):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    mdl = synth_model(W["D"], W["n"], W["r"], seed=3)
+    K = max(1, args.steps)
+    t0 = time.perf_counter()
+    v, threads, sample = cpu_reference_steps_per_sec(W, mdl, budget_s=min(60.0, 4.0 * K))
+    line = {
+        "impl": "reference", "metric": "sgld_steps_per_sec", "value": v, "unit": "steps/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / v, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, W),
+        "cpu_baseline": {"value": v, "unit": "steps/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference Julia 0.3 runtime unavailable on this box; timed: oracle/gpt_oracle.c (loop-faithful C "
+                "restatement of GPT_SGLD.jl:378-439, OpenMP over minibatch rows)",
+        "wall_s": time.perf_counter() - t0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, W):
+    return {"workload": f"{args.workload}: {W['desc']}, D={W['D']} N={W['N']} n={W['n']} r={W['r']} Q={Q} minibatch={W['m']}",
+            "precision": args.precision, "langevin": True, "stiefel": True,
+            "l2": "inputs larger than L2: resident X is %.0f MB and every step gathers different random rows" % (W["N"] * W["D"] * 8 / 1e6),
+            "parallelism": f"row-sharded minibatch x{args.gpus} + NCCL all-reduce of Q+n*r*D doubles"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C4", choices=list(WORKLOADS))
+    ap.add_argument("--precision", default="tc3", choices=["tc3", "tc1", "fp64"])
+    ap.add_argument("--no-pred", action="store_true", help="skip the C5 prediction sweep")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline")
+    ap.add_argument("--pred-samples", type=int, default=C5["S"])
+    args = ap.parse_args()
+    W = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        return run_reference(args, W)
+
+    import torch
+    from gpt_b200 import _lib as L
+    from gpt_b200 import gpt_sgld as G
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if rank == 0:
+            print(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run", file=sys.stderr)
+        if args.gpus > 1 and world == 1:
+            sys.exit(2)
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    prec = {"tc3": L.PREC_TC3, "tc1": L.PREC_TC1, "fp64": L.PREC_FP64}[args.precision]
+    D, N, n, r, m = W["D"], W["N"], W["n"], W["r"], W["m"]
+    mdl = synth_model(D, n, r, seed=3)
+    rng = np.random.default_rng(11)          # same data on every rank
+    X = np.asfortranarray(rng.standard_normal((N, D)))
+    feat = G.feature(X, mdl["ls"], 1.0, mdl["phi_scale"], mdl["Z"], mdl["b"])
+
+    model = G.Model(D, n, r, Q, precision=prec, device=local, seed=1234)
+    stream = torch.cuda.Stream(device=dev)
+    model.set_stream(stream.cuda_stream)
+    model.set_features(feat)
+    model.set_index(mdl["I"])
+    # y = f*(X) + sqrt(signal_var) noise, f* evaluated with the library itself (data generation, untimed)
+    y = model.pred(mdl["w_true"], mdl["U_true"], X) + np.sqrt(SIGNAL_VAR) * rng.standard_normal(N)
+    model.set_train(X, y)
+    model.set_params(mdl["w0"], mdl["U0"])
+    if world > 1:
+        idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(G.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        model.comm_init(world, rank, bytes(idt.cpu().numpy().tobytes()))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ------------------------------------------------------------------ resident-data steps/s (device timed)
+    model.sgld_advance(SIGNAL_VAR, m, EPSW, EPSU, max(3, args.warmup))
+    model.synchronize()
+    model.set_profiling(True)
+    model.phase_ms(reset=True)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    with ClockSampler(local) as clk:
+        with torch.cuda.stream(stream):
+            ev0.record(stream)
+            model.sgld_advance(SIGNAL_VAR, m, EPSW, EPSU, args.steps)
+            ev1.record(stream)
+        model.synchronize()
+        barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    phases, launches = model.phase_ms(reset=True)
+    model.set_profiling(False)
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    ms_step = ms_total / args.steps
+    value = 1e3 / ms_step
+
+    # ------------------------------------------------------------------ e2e: host minibatches through the C ABI
+    ke = max(3, min(args.steps, 30))
+    Xb = [torch.empty((D, m), dtype=torch.float64).pin_memory() for _ in range(2)]   # (D,m) C-order == (m,D) F-order
+    yb = [torch.empty(m, dtype=torch.float64).pin_memory() for _ in range(2)]
+    w_out = torch.empty(Q, dtype=torch.float64).pin_memory()
+    rows = [np.sort(rng.choice(N, size=m, replace=False)) for _ in range(2)]
+    for s in range(2):
+        Xb[s].numpy()[...] = X[rows[s]].T
+        yb[s].numpy()[...] = y[rows[s]]
+    xb_np = [np.asfortranarray(Xb[s].numpy().T) for s in range(2)]   # F-contiguous views of the pinned buffers
+    assert all(a.ctypes.data == Xb[s].data_ptr() for s, a in enumerate(xb_np))
+    for s in range(3):
+        model.sgld_step_host(SIGNAL_VAR, xb_np[s % 2], yb[s % 2].numpy(), N, EPSW, EPSU, w_out=w_out.numpy())
+    barrier()
+    t0 = time.perf_counter()
+    for s in range(ke):
+        model.sgld_step_host(SIGNAL_VAR, xb_np[s % 2], yb[s % 2].numpy(), N, EPSW, EPSU, w_out=w_out.numpy())
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / ke
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_s = float(te.item())
+
+    # ------------------------------------------------------------------ C5 posterior-predictive sweep (rows sharded)
+    pred = None
+    if not args.no_pred:
+        S = args.pred_samples
+        pm = synth_model(C5["D"], C5["n"], C5["r"], seed=5)
+        prng = np.random.default_rng(13)
+        lo, hi = rank * C5["Nt"] // world, (rank + 1) * C5["Nt"] // world
+        Xt = np.asfortranarray(prng.standard_normal((C5["Nt"], C5["D"]))[lo:hi])
+        ws = np.asfortranarray(pm["w_true"][:, None] + 0.05 * prng.standard_normal((Q, S)))
+        Us = np.empty((C5["n"], C5["r"], C5["D"], S), order="F")
+        for s in range(S):                      # perturbations of U*, re-orthonormalised
+            for k in range(C5["D"]):
+                q_, _ = np.linalg.qr(pm["U_true"][:, :, k] + 0.01 * prng.standard_normal((C5["n"], C5["r"])))
+                Us[:, :, k, s] = q_
+        pf = G.feature(Xt, pm["ls"], 1.0, pm["phi_scale"], pm["Z"], pm["b"])
+        with G.Model(C5["D"], C5["n"], C5["r"], Q, precision=prec, device=local) as pmodel:
+            pmodel.set_features(pf); pmodel.set_index(pm["I"])
+            pmodel.pred_samples(ws[:, :2], Us[:, :, :, :2], Xt[:4096])      # warm-up
+            barrier()
+            t0 = time.perf_counter()
+            mean = pmodel.pred_samples(ws, Us, Xt)
+            barrier()
+            dt = time.perf_counter() - t0
+        tp = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tp, op=dist.ReduceOp.MAX)
+        dt = float(tp.item())
+        pred = {"metric": "predictions_per_sec", "value": C5["Nt"] * S / dt, "unit": "predictions/s", "seconds": dt,
+                "config": {"workload": f"C5: D={C5['D']} Nt={C5['Nt']} S={S} n={C5['n']} r={C5['r']} Q={Q}, test rows sharded x{world}, host buffers in/out"},
+                "checksum": float(np.abs(mean).sum())}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ------------------------------------------------------------------ roofline of the dominant kernel
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    bf16_sust = peaks.get("bf16_tflops_sustained", 1400.0)
+    which_peak = "measured (MEASURED_PEAKS.json bf16_tflops_sustained / 2 = TF32-class dense rate, SURVEY.md §8d)" if peaks \
+        else "fallback (B200_PROFILING.md 1.4 PF sustained / 2)"
+    ml = m / world                                     # rows per rank
+    per_launch_flops = 2.0 * ml * n * r * D            # algorithmic tensor flops of ONE K1 or K3 launch
+    dom = "bwd" if phases["bwd"] >= phases["fwd"] else "fwd"
+    dom_ms = phases[dom] / args.steps
+    ach = per_launch_flops / (dom_ms * 1e-3) / 1e12 if dom_ms > 0 else None
+    peak_tf = bf16_sust / 2.0
+    sm_mhz = clk.summary()["sm_mhz"] or 1965.0
+    cos_peak = 16 * 148 * sm_mhz * 1e6                  # MUFU.COS: 16 / clk / SM (nominal), at the clock seen
+    roofline = {"kernel": {"fwd": "fwd_tc_kernel (K1)", "bwd": "bwd_tc_kernel (K3)"}[dom], "bound": "tensor",
+                "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": (ach / peak_tf) if ach else None,
+                "traffic": None, "peak_source": which_peak, "avg_launch_ms": dom_ms,
+                "algorithmic_flops_per_launch": per_launch_flops,
+                "sfu": {"cos_per_launch": ml * n * D, "achieved_Tcos_s": ml * n * D / (dom_ms * 1e-3) / 1e12 if dom_ms else None,
+                        "peak_Tcos_s": cos_peak / 1e12, "frac": (ml * n * D / (dom_ms * 1e-3)) / cos_peak if dom_ms else None,
+                        "peak_source": "nominal 16 MUFU/clk/SM x 148 SMs x sampled SM clock"},
+                "step": {"t_roof_us": max(4.0 * ml * n * r * D / (peak_tf * 1e12), ml * n * D / cos_peak) * 1e6,
+                         "t_step_us": ms_step * 1e3,
+                         "frac": max(4.0 * ml * n * r * D / (peak_tf * 1e12), ml * n * D / cos_peak) * 1e3 / ms_step,
+                         "definition": "SURVEY.md §8d: max(4mnrD/P_tc, mnD/P_sfu) / measured step; each feature credited once "
+                                       "although K3 re-evaluates it"},
+                "phase_ms_per_step": {k: v / args.steps for k, v in phases.items()}}
+
+    cpu = None
+    if not args.no_cpu:
+        v, threads, sample = cpu_reference_steps_per_sec(W, mdl)
+        cpu = {"value": v, "unit": "steps/s", "cores": threads, "kind": "port", "sample": sample}
+
+    line = {
+        "metric": "sgld_steps_per_sec", "value": value, "unit": "steps/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None,
+        "dtype": {"tc3": "fp16x3-split operands, fp32 accumulate (tcgen05); fp64 parameters and update",
+                  "tc1": "fp16 operands, fp32 accumulate (tcgen05); fp64 update", "fp64": "f64"}[args.precision],
+        "data": "synthetic", "config": workload_config(args, W), "clocks": clk.summary(),
+        "e2e": {"value": 1.0 / e2e_s, "unit": "steps/s", "h2d_bytes_per_step": int(m * (D + 1) * 8),
+                "d2h_bytes_per_step": int(Q * 8), "steps": ke,
+                "api": "gptb_sgld_step_host (pinned host minibatch in, updated w out, every step)"},
+        "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "pred": pred,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -54,6 +54,7 @@ PROTOTYPES = {
                                       C.c_double, C.c_int32, c_double_p, c_double_p, c_double_p]),
     "gptb_sgld_run": (C.c_int, [H, C.c_double, C.c_int64, C.c_double, C.c_double, C.c_int32, C.c_int32, C.c_int32,
                                 c_int64_p, c_double_p, c_double_p, c_double_p, c_double_p]),
+    "gptb_sgld_advance": (C.c_int, [H, C.c_double, C.c_int64, C.c_double, C.c_double, C.c_int32, C.c_int64]),
     "gptb_comm_unique_id": (C.c_int, [C.c_void_p]),
     "gptb_comm_init": (C.c_int, [H, C.c_int32, C.c_int32, C.c_void_p]),
     "gptb_comm_destroy": (C.c_int, [H]),

@@ -134,33 +134,43 @@ int ensure_pin(gptb_handle *h, size_t bytes) {
     return GPTB_OK;
 }
 
+// Per-phase timing without host synchronisation: events go into a pool as the step is enqueued and
+// are read back (after one stream sync) by drain_timers().
+static void record_ev(gptb_handle *h, int tag) {
+    if (h->ev_used == h->evpool.size()) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        h->evpool.push_back(e);
+        h->evtag.push_back(tag);
+    }
+    h->evtag[h->ev_used] = tag;
+    cudaEventRecord(h->evpool[h->ev_used], h->stream);
+    h->ev_used++;
+}
+
+static void drain_timers(gptb_handle *h) {
+    if (h->ev_used == 0) return;
+    cudaStreamSynchronize(h->stream);
+    for (size_t i = 1; i < h->ev_used; ++i) {
+        if (h->evtag[i] < 0) continue;
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, h->evpool[i - 1], h->evpool[i]) == cudaSuccess) h->phase_ms[h->evtag[i]] += ms;
+    }
+    h->ev_used = 0;
+}
+
 struct PhaseTimer {
     gptb_handle *h;
     explicit PhaseTimer(gptb_handle *hh) : h(hh) {
-        if (h->profiling) cudaEventRecord(h->ev[0], h->stream);
-    }
-    void mark(int phase) {
-        if (h->profiling) cudaEventRecord(h->ev[phase + 1], h->stream);
-        last = phase;
-    }
-    int last = -1;
-    void finish() {
-        if (!h->profiling) return;
-        cudaStreamSynchronize(h->stream);
-        int prev = 0;
-        for (int p = 0; p <= last; ++p) {
-            if (!marked[p]) continue;
-            float ms = 0.f;
-            cudaEventElapsedTime(&ms, h->ev[prev], h->ev[p + 1]);
-            h->phase_ms[p] += ms;
-            prev = p + 1;
+        if (h->profiling) {
+            if (h->ev_used > 60000) drain_timers(h);
+            record_ev(h, -1);
         }
     }
-    bool marked[GPTB_PHASE_COUNT] = {false, false, false, false, false, false};
     void done(int phase) {
-        mark(phase);
-        marked[phase] = true;
+        if (h->profiling) record_ev(h, phase);
     }
+    void finish() {}
 };
 
 // Pack / refresh the tensor-core shadows of the sampler's current parameters.
@@ -357,7 +367,6 @@ int gptb_create(const gptb_config *cfg, gptb_handle **out) {
     }
     CREATE_OK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     h->own_stream = true;
-    for (auto &ev : h->ev) CREATE_OK(cudaEventCreate(&ev));
     const gptb_config &c = h->cfg;
     h->npad = (c.n + 127) / 128 * 128;
     h->rpad = (c.r + 15) / 16 * 16;
@@ -422,8 +431,7 @@ int gptb_destroy(gptb_handle *h) {
     dev_free(&h->store_w); dev_free(&h->store_U);
     if (h->nan_flag_host) cudaFreeHost(h->nan_flag_host);
     if (h->pin) cudaFreeHost(h->pin);
-    for (auto &ev : h->ev)
-        if (ev) cudaEventDestroy(ev);
+    for (auto &ev : h->evpool) cudaEventDestroy(ev);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return GPTB_OK;
@@ -447,6 +455,7 @@ int gptb_set_stream(gptb_handle *h, void *cuda_stream) {
 int gptb_synchronize(gptb_handle *h) {
     if (!h) return GPTB_ERR_ARG;
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    if (h->have_params) return check_nan(h);   // also reports a geodesic NaN raised by queued steps
     GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
     return GPTB_OK;
 }
@@ -521,6 +530,7 @@ static int set_train_common(gptb_handle *h, const double *y, int64_t N) {
     GPTB_TRY(gptb_reset_order(h));
     h->epoch_counter = 0;
     h->step_counter = 0;
+    h->batch_cursor = 0;
     return GPTB_OK;
 }
 
@@ -1017,6 +1027,26 @@ int gptb_sgld_run(gptb_handle *h, double signal_var, int64_t m, double epsw, dou
     return st;
 }
 
+int gptb_sgld_advance(gptb_handle *h, double signal_var, int64_t m, double epsw, double epsU, int32_t flags,
+                      int64_t nsteps) {
+    if (!h || m < 1 || nsteps < 0 || !(signal_var > 0)) return GPTB_ERR_ARG;
+    GPTB_TRY(check_ready(h, true, true));
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    const int64_t N = h->N;
+    const int64_t numbatches = (N + m - 1) / m;
+    for (int64_t s = 0; s < nsteps; ++s) {
+        if (h->batch_cursor == 0) {
+            GPTB_TRY(gptb_shuffle_order(h, h->epoch_counter));   // perm=randperm(N), :373
+            h->epoch_counter++;
+        }
+        const int64_t lo = m * h->batch_cursor, hi = std::min(m * (h->batch_cursor + 1), N);
+        GPTB_TRY(step_common(h, signal_var, h->order + lo, hi - lo, N, false, nullptr, nullptr, epsw, epsU, flags,
+                             nullptr, nullptr));
+        h->batch_cursor = (h->batch_cursor + 1) % numbatches;
+    }
+    return GPTB_OK;
+}
+
 int gptb_set_profiling(gptb_handle *h, int32_t on) {
     if (!h) return GPTB_ERR_ARG;
     h->profiling = on != 0;
@@ -1025,6 +1055,8 @@ int gptb_set_profiling(gptb_handle *h, int32_t on) {
 
 int gptb_get_phase_ms(gptb_handle *h, float *ms_out, int64_t *launches_out, int32_t reset) {
     if (!h) return GPTB_ERR_ARG;
+    cudaSetDevice(h->device);
+    drain_timers(h);
     if (ms_out)
         for (int p = 0; p < GPTB_PHASE_COUNT; ++p) ms_out[p] = h->phase_ms[p];
     if (launches_out) *launches_out = h->launches;

@@ -6,6 +6,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string>
+#include <vector>
 
 #include "../../include/gptb200.h"
 
@@ -123,7 +124,11 @@ struct gptb_handle {
     bool profiling = false;
     float phase_ms[GPTB_PHASE_COUNT] = {0, 0, 0, 0, 0, 0};
     int64_t launches = 0;
-    cudaEvent_t ev[GPTB_PHASE_COUNT + 1] = {nullptr};
+    // profiling: events are recorded without synchronising; gptb_get_phase_ms drains them
+    std::vector<cudaEvent_t> evpool;
+    std::vector<int> evtag;            // -1 = step start, else phase id
+    size_t ev_used = 0;
+    int64_t batch_cursor = 0;          // position inside the current epoch (gptb_sgld_advance)
     int sm_count = 148;
 };
 

@@ -465,6 +465,16 @@ k_reduce_only(const double *__restrict__ U, const double *__restrict__ G, double
 
 size_t gptb_update_small_stride(int r) { return SmallLayout(r).total; }
 
+// k_prepare / k_apply / k_reduce_only use up to ~99 KB of dynamic shared memory at r = 64: opt in once.
+static void optin_smem() {
+    static bool done = false;
+    if (done) return;
+    cudaFuncSetAttribute(k_prepare, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    cudaFuncSetAttribute(k_apply, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    cudaFuncSetAttribute(k_reduce_only, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    done = true;
+}
+
 static int zero_small(gptb_handle *h, double *small, size_t stride, int D, int r) {
     SmallLayout L(r);
     GPTB_CUDA_OK(h, cudaMemset2DAsync(small, stride * sizeof(double), 0, L.zero_count() * sizeof(double), D, h->stream));
@@ -476,6 +486,7 @@ int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, cons
     const gptb_config &c = h->cfg;
     const int nb = (c.n + UP_ROWS - 1) / UP_ROWS;
     const bool stiefel = flags & GPTB_FLAG_STIEFEL;
+    optin_smem();
     if (stiefel) GPTB_TRY(zero_small(h, h->small, h->small_stride, c.D, c.r));
     size_t sm1 = 2 * (size_t)UP_ROWS * c.r * sizeof(double);
     k_prepare<<<dim3(nb, c.D + 1), UP_THREADS, sm1, h->stream>>>(h->grad, h->w, h->U, h->G, h->small, h->small_stride,
@@ -501,6 +512,7 @@ int gptb_proj_geod_device(gptb_handle *h, cudaStream_t s, int n, int r, const do
                           double *out, int mode, int32_t *nan_flag) {
     SmallLayout L(r);
     double *small = nullptr;
+    optin_smem();
     GPTB_CUDA_OK(h, cudaMalloc(&small, L.total * sizeof(double)));
     cudaMemsetAsync(small, 0, L.zero_count() * sizeof(double), s);
     const int nb = (n + UP_ROWS - 1) / UP_ROWS;

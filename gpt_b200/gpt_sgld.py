@@ -316,6 +316,12 @@ class Model:
         _check(st, self.h)
         return w_store, U_store
 
+    def sgld_advance(self, signal_var, m, epsw, epsU, nsteps, langevin=True, stiefel=True):
+        """Queue the next nsteps loop bodies (no store, no host sync); call synchronize() to wait."""
+        flags = (L.FLAG_LANGEVIN if langevin else 0) | (L.FLAG_STIEFEL if stiefel else 0)
+        _check(self.lib.gptb_sgld_advance(self.h, float(signal_var), int(m), float(epsw), float(epsU), flags,
+                                          int(nsteps)), self.h)
+
     # -- multi-GPU / introspection
     def comm_init(self, nranks: int, rank: int, unique_id: bytes):
         buf = C.create_string_buffer(unique_id, 128)

@@ -79,7 +79,7 @@ int gptb_destroy(gptb_handle *h);
 const char *gptb_last_error(const gptb_handle *h);
 /* Run all of this handle's work on an existing cudaStream_t (pass it as void*); NULL = own stream. */
 int gptb_set_stream(gptb_handle *h, void *cuda_stream);
-/* Blocks until all work queued by this handle has finished. */
+/* Blocks until all work queued by this handle has finished; returns GPTB_GEODESIC_NAN if a queued step hit it. */
 int gptb_synchronize(gptb_handle *h);
 
 /* ---- model definition ---------------------------------------------------------------------- */
@@ -156,6 +156,12 @@ int gptb_sgld_step_host(gptb_handle *h, double signal_var, const double *Xb, con
 int gptb_sgld_run(gptb_handle *h, double signal_var, int64_t m, double epsw, double epsU, int32_t burnin,
                   int32_t maxepoch, int32_t flags, const int64_t *perms, const double *noise_w,
                   const double *noise_U, double *w_store, double *U_store);
+
+/* The next nsteps loop bodies of the same sampler, continuing the epoch structure where the previous call
+ * stopped (a fresh Philox permutation whenever an epoch starts), nothing stored — what burn-in epochs do.
+ * Asynchronous: work is only queued; gptb_synchronize() waits and reports GPTB_GEODESIC_NAN. */
+int gptb_sgld_advance(gptb_handle *h, double signal_var, int64_t m, double epsw, double epsU, int32_t flags,
+                      int64_t nsteps);
 
 /* ---- multi-GPU (one process per GPU) ---------------------------------------------------------- */
 /* Row-sharded data parallelism (the CPU precedent is GPT_SGLD_p.jl:70-108,194-218): every rank holds
