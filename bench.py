@@ -38,7 +38,14 @@ WORKLOADS = {
 }
 C5 = dict(D=8, Nt=1_000_000, S=200, n=500, r=20)
 Q = 200
-SIGNAL_VAR, EPSW, EPSU = 1e-3, 1e-5, 1e-8   # SynthDataExperiment.jl:7,37-38
+SIGNAL_VAR = 1e-3                            # SynthDataExperiment.jl:7
+
+
+def eps_for(N):
+    """Step sizes.  SynthDataExperiment.jl:37-38 uses epsw=1e-5, epsU=1e-8 on Ntrain=50 points; the likelihood
+    gradient scales with N/signal_var, so the same eps*N product keeps the chain stable at any N (the 50-point
+    values diverge to NaN within a few steps at N=10M)."""
+    return 1e-5 * 50.0 / N, 1e-8 * 50.0 / N
 
 
 def synth_model(D, n, r, seed):
@@ -109,6 +116,7 @@ def cpu_reference_steps_per_sec(W, mdl, budget_s=20.0, sample_rows=2048):
     X = rng.standard_normal((ms, D))
     y = rng.standard_normal(ms)
     threads = co.max_threads()
+    EPSW, EPSU = eps_for(W["N"])
     phi = co.feature(X, mdl["ls"], 1.0, mdl["phi_scale"], mdl["Z"], mdl["b"], threads)
     nw = rng.standard_normal(Q); nU = rng.standard_normal((n, r, D))
     w, U = mdl["w0"].copy(), mdl["U0"].copy()
@@ -149,6 +157,7 @@ def run_reference(args, W):
 def workload_config(args, W):
     return {"workload": f"{args.workload}: {W['desc']}, D={W['D']} N={W['N']} n={W['n']} r={W['r']} Q={Q} minibatch={W['m']}",
             "precision": args.precision, "langevin": True, "stiefel": True,
+            "signal_var": SIGNAL_VAR, "epsw": eps_for(W["N"])[0], "epsU": eps_for(W["N"])[1],
             "l2": "inputs larger than L2: resident X is %.0f MB and every step gathers different random rows" % (W["N"] * W["D"] * 8 / 1e6),
             "parallelism": f"row-sharded minibatch x{args.gpus} + NCCL all-reduce of Q+n*r*D doubles"}
 
@@ -188,6 +197,7 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     prec = {"tc3": L.PREC_TC3, "tc1": L.PREC_TC1, "fp64": L.PREC_FP64}[args.precision]
     D, N, n, r, m = W["D"], W["N"], W["n"], W["r"], W["m"]
+    EPSW, EPSU = eps_for(N)
     mdl = synth_model(D, n, r, seed=3)
     rng = np.random.default_rng(11)          # same data on every rank
     X = np.asfortranarray(rng.standard_normal((N, D)))
