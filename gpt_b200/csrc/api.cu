@@ -322,7 +322,7 @@ int gptb_create(const gptb_config *cfg, gptb_handle **out) {
         return GPTB_ERR_ARG;
     }
     *out = nullptr;
-    if (cfg->D < 1 || cfg->D > 16 || cfg->n < 1 || cfg->r < 1 || cfg->r > 64 || cfg->Q < 1) {
+    if (cfg->D < 1 || cfg->D > 16 || cfg->n < 1 || cfg->r < 1 || cfg->r > 64 || cfg->Q < 1 || cfg->Q > 65535) {
         gptb_set_error(nullptr, "gptb_create: need 1<=D<=16, n>=1, 1<=r<=64, Q>=1 (got D=%d n=%d r=%d Q=%d)", cfg->D,
                        cfg->n, cfg->r, cfg->Q);
         return GPTB_ERR_SHAPE;
@@ -377,6 +377,8 @@ int gptb_create(const gptb_config *cfg, gptb_handle **out) {
     A(dev_alloc(h, &h->ZtF, (size_t)c.D * h->npad));
     A(dev_alloc(h, &h->bF, (size_t)c.D * h->npad));
     A(dev_alloc(h, &h->I, (size_t)c.D * c.Q));
+    A(dev_alloc(h, &h->grp_ptr, (size_t)c.D * h->rpad + 1));
+    A(dev_alloc(h, &h->grp_q, (size_t)c.Q * c.D));
     A(dev_alloc(h, &h->w, (size_t)c.Q));
     A(dev_alloc(h, &h->U, (size_t)c.D * c.r * c.n));
     A(dev_alloc(h, &h->G, (size_t)c.D * c.r * c.n));
@@ -410,7 +412,7 @@ int gptb_destroy(gptb_handle *h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     gptb_comm_destroy(h);
-    dev_free(&h->Zt); dev_free(&h->b); dev_free(&h->ZtF); dev_free(&h->bF); dev_free(&h->I);
+    dev_free(&h->Zt); dev_free(&h->b); dev_free(&h->ZtF); dev_free(&h->bF); dev_free(&h->I); dev_free(&h->grp_ptr); dev_free(&h->grp_q);
     dev_free(&h->X); dev_free(&h->y); dev_free(&h->phi); dev_free(&h->order); dev_free(&h->order_tmp);
     dev_free(&h->sort_keys); dev_free(&h->sort_keys_tmp);
     if (h->sort_tmp) cudaFree(h->sort_tmp);
@@ -512,6 +514,19 @@ int gptb_set_index(gptb_handle *h, const int32_t *I) {
     }
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
     GPTB_CUDA_OK(h, cudaMemcpyAsync(h->I, z.data(), z.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    // CSR over (k,l): the q with I[q,k] = l, in increasing q (the order computeA's findin visits them, :267)
+    std::vector<int32_t> ptr((size_t)c.D * h->rpad + 1, 0);
+    std::vector<uint16_t> gq((size_t)c.Q * c.D);
+    for (int k = 0; k < c.D; ++k)
+        for (int q = 0; q < c.Q; ++q) ptr[(size_t)k * h->rpad + z[(size_t)k * c.Q + q] + 1]++;
+    for (size_t g = 0; g + 1 < ptr.size(); ++g) ptr[g + 1] += ptr[g];
+    {
+        std::vector<int32_t> fill(ptr.begin(), ptr.end() - 1);
+        for (int k = 0; k < c.D; ++k)
+            for (int q = 0; q < c.Q; ++q) gq[fill[(size_t)k * h->rpad + z[(size_t)k * c.Q + q]]++] = (uint16_t)q;
+    }
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->grp_ptr, ptr.data(), ptr.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->grp_q, gq.data(), gq.size() * sizeof(uint16_t), cudaMemcpyHostToDevice, h->stream));
     GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
     h->have_index = true;
     return GPTB_OK;

@@ -58,6 +58,8 @@ struct gptb_handle {
     int npad = 0;   // n rounded up to 128 (tensor-core M tile of the backward pass / K chunks of the forward)
     int rpad = 0;   // r rounded up to 16 (UMMA N granularity at M=128)
     int32_t *I = nullptr;
+    int32_t *grp_ptr = nullptr;   // [D*rpad+1] CSR over (k,l): which q have I[q,k] = l (contract.cu pass 2)
+    uint16_t *grp_q = nullptr;    // [Q*D]
 
     // training data
     int64_t N = 0;

@@ -246,7 +246,9 @@ template <int RPAD, bool THREE>
 __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     constexpr int NB = THREE ? 2 * RPAD : RPAD;
-    constexpr int B_STAGE_BYTES = 2 * RPAD * KC * 2;
+    constexpr int B_IMG_BYTES = 2 * RPAD * KC * 2;
+    constexpr int X_BYTES = KC * 4;                         // the chunk's 64 input values ride in the same stage
+    constexpr int B_STAGE_BYTES = B_IMG_BYTES + X_BYTES;
     constexpr int ACC_COLS = NB;
     unsigned char *sB = smem_raw;
     Bars *bars = reinterpret_cast<Bars *>(smem_raw + NSTB * B_STAGE_BYTES);
@@ -299,13 +301,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
             mbar_wait(&bars->a_empty[sa], ((cnt / NSTA) & 1) ^ 1);
             fence_after_sync();
             const uint32_t st_addr = tmem + lane_addr + sa * 64;
-            const float4 *xr = reinterpret_cast<const float4 *>(p.XbF + (size_t)k * p.mpad + (size_t)ch * KC);
+            const int sbx = cnt % NSTB;
+            mbar_wait(&bars->b_full[sbx], (cnt / NSTB) & 1);
+            const float4 *xr = reinterpret_cast<const float4 *>(sB + sbx * B_STAGE_BYTES + B_IMG_BYTES);
 #pragma unroll
             for (int half = 0; half < 2; ++half) {
                 uint32_t hi[16], lo[16];
 #pragma unroll
                 for (int c = 0; c < 16; c += 2) {
-                    float4 xx = __ldg(xr + half * 8 + c / 2);
+                    float4 xx = xr[half * 8 + c / 2];
                     float a0, a1, a2, a3;
                     if (!p.sincos) {
                         a0 = __cosf(fmaf(xx.x, zt, bb)); a1 = __cosf(fmaf(xx.y, zt, bb));
@@ -375,7 +379,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
                 const int sb = cnt % NSTB;
                 mbar_wait(&bars->b_empty[sb], ((cnt / NSTB) & 1) ^ 1);
                 mbar_expect_tx(&bars->b_full[sb], B_STAGE_BYTES);
-                bulk_g2s(sB + sb * B_STAGE_BYTES, src, B_STAGE_BYTES, &bars->b_full[sb]);
+                bulk_g2s(sB + sb * B_STAGE_BYTES + B_IMG_BYTES, p.XbF + (size_t)k * p.mpad + (size_t)ch * KC, X_BYTES, &bars->b_full[sb]);
+                bulk_g2s(sB + sb * B_STAGE_BYTES, src, B_IMG_BYTES, &bars->b_full[sb]);
             }
         }
         __syncwarp();

@@ -288,11 +288,119 @@ __device__ void bexpm(double *M, int n2, double *ws, int *bad_s) {
     __syncthreads();
 }
 
+// ---------------------------------------------------------------- shared-memory expm (n2 <= 96)
+// C = A*B, all ld x ld col-major in shared memory (ld multiple of 4, zero padded); 4x4 register tiles.
+__device__ void smm(const double *__restrict__ A, const double *__restrict__ B, double *__restrict__ C, int ld, int kk) {
+    const int nt = ld >> 2;
+    for (int t = threadIdx.x; t < nt * nt; t += blockDim.x) {
+        const int i0 = (t % nt) * 4, j0 = (t / nt) * 4;
+        double acc[4][4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+        for (int p = 0; p < kk; ++p) {
+            const double2 a01 = *reinterpret_cast<const double2 *>(A + i0 + (size_t)ld * p);
+            const double2 a23 = *reinterpret_cast<const double2 *>(A + i0 + 2 + (size_t)ld * p);
+            const double av[4] = {a01.x, a01.y, a23.x, a23.y};
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const double bv = B[p + (size_t)ld * (j0 + b)];
+#pragma unroll
+                for (int a = 0; a < 4; ++a) acc[a][b] = fma(av[a], bv, acc[a][b]);
+            }
+        }
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+#pragma unroll
+            for (int a = 0; a < 4; ++a) C[i0 + a + (size_t)ld * (j0 + b)] = acc[a][b];
+    }
+    __syncthreads();
+}
+
+// exp(M) for an n2 x n2 matrix in global memory, evaluated entirely in shared memory (6 buffers of ld*ld doubles):
+// scaling and squaring around a Taylor polynomial of degree m in {4,8,12,16,20} evaluated by Paterson-Stockmeyer
+// in powers of X^4 (3 + m/4 - 1 matrix products, no linear solve — the Pade solve is a 64-step serial chain on a
+// single CTA).  m and the scaling s are chosen so the truncation error is below 1.1e-16 * ||exp||; agreement with
+// Julia/SciPy's Pade-13 expm (GPT_SGLD.jl:23,28) is ~1e-15 relative.  NaN/Inf input sets *bad_s (:24).
+__device__ void sexpm(double *M, int n2, double *buf, int *bad_s) {
+    __shared__ double nrm_s;
+    __shared__ int s_s, m_s;
+    const int ld = (n2 + 3) & ~3;
+    const size_t sz = (size_t)ld * ld;
+    double *X = buf, *X2 = X + sz, *X3 = X2 + sz, *X4 = X3 + sz, *P = X4 + sz, *Tm = P + sz;
+    for (size_t t = threadIdx.x; t < sz; t += blockDim.x) {
+        int i = t % ld, j = t / ld;
+        X[t] = (i < n2 && j < n2) ? M[i + (size_t)n2 * j] : 0.0;
+    }
+    if (threadIdx.x == 0) nrm_s = 0.0;
+    __syncthreads();
+    if (threadIdx.x < n2) {
+        double s = 0.0;
+        for (int i = 0; i < n2; ++i) s += fabs(X[i + (size_t)ld * threadIdx.x]);
+        if (s != s || isinf(s)) *bad_s = 1;
+        else atomicMax(reinterpret_cast<unsigned long long *>(&nrm_s), (unsigned long long)__double_as_longlong(s));
+    }
+    __syncthreads();
+    if (*bad_s) return;
+    if (threadIdx.x == 0) {
+        const double nrm = nrm_s;
+        int m = 20, s = 0;
+        if (nrm <= 1.7e-3) m = 4;
+        else if (nrm <= 7.0e-2) m = 8;
+        else if (nrm <= 3.3e-1) m = 12;
+        else if (nrm <= 8.2e-1) m = 16;
+        else if (nrm > 1.5) s = max(0, (int)ceil(log2(nrm / 1.5)));
+        m_s = m;
+        s_s = s;
+    }
+    __syncthreads();
+    const int m = m_s, s = s_s;
+    if (s > 0) {
+        const double f = ldexp(1.0, -s);
+        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) X[t] *= f;
+        __syncthreads();
+    }
+    smm(X, X, X2, ld, n2);
+    smm(X2, X, X3, ld, n2);
+    smm(X2, X2, X4, ld, n2);
+    double c[21];
+    c[0] = 1.0;
+    for (int j = 1; j <= 20; ++j) c[j] = c[j - 1] / j;
+    const int nb = m / 4;
+    // block i: B_i = c[4i] I + c[4i+1] X + c[4i+2] X2 + c[4i+3] X3
+    for (size_t t = threadIdx.x; t < sz; t += blockDim.x) {
+        const int i = t % ld, j = t / ld, b0 = 4 * (nb - 1);
+        P[t] = ((i == j && i < n2) ? c[b0] : 0.0) + c[b0 + 1] * X[t] + c[b0 + 2] * X2[t] + c[b0 + 3] * X3[t] + c[m] * X4[t];
+    }
+    __syncthreads();
+    for (int bi = nb - 2; bi >= 0; --bi) {
+        smm(X4, P, Tm, ld, n2);
+        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) {
+            const int i = t % ld, j = t / ld, b0 = 4 * bi;
+            P[t] = Tm[t] + ((i == j && i < n2) ? c[b0] : 0.0) + c[b0 + 1] * X[t] + c[b0 + 2] * X2[t] + c[b0 + 3] * X3[t];
+        }
+        __syncthreads();
+    }
+    double *cur = P, *oth = Tm;
+    for (int q = 0; q < s; ++q) {
+        smm(cur, cur, oth, ld, n2);
+        double *sw = cur; cur = oth; oth = sw;
+    }
+    for (size_t t = threadIdx.x; t < (size_t)n2 * n2; t += blockDim.x) {
+        int i = t % n2, j = t / n2;
+        M[t] = cur[i + (size_t)ld * j];
+    }
+    __syncthreads();
+}
+
 // ---------------------------------------------------------------- P2
 // grid (D).  use_sym = 1: G is the un-projected direction (SGLD-ERM step);  0: G already is the
 // tangent vector `mom` of geod(U,mom,t) (GPT_SGLD.jl:19-37 called directly).
 __global__ void __launch_bounds__(1024)
-k_small(double *__restrict__ small, size_t small_stride, int r, double t, int use_sym, int32_t *nan_flag) {
+k_small(double *__restrict__ small, size_t small_stride, int r, double t, int use_sym, int32_t *nan_flag,
+        int use_smem) {
+    extern __shared__ double sm[];
     __shared__ int bad;
     double *sk = small + (size_t)blockIdx.x * small_stride;
     SmallLayout L(r);
@@ -335,7 +443,8 @@ k_small(double *__restrict__ small, size_t small_stride, int r, double t, int us
     }
     for (int i = threadIdx.x; i < rr; i += blockDim.x) X[i] = -t * A[i];
     __syncthreads();
-    bexpm(Tm, r2, ws, &bad);
+    if (use_smem) sexpm(Tm, r2, sm, &bad);
+    else bexpm(Tm, r2, ws, &bad);
     if (!bad) {
         // "if sum(isnan(E))>0" (:24)
         int local = 0;
@@ -348,7 +457,9 @@ k_small(double *__restrict__ small, size_t small_stride, int r, double t, int us
         if (threadIdx.x == 0) atomicExch(nan_flag, 1);
         return;
     }
-    bexpm(X, r, ws, &bad);
+    if (use_smem) sexpm(X, r, sm, &bad);
+    else bexpm(X, r, ws, &bad);
+    __syncthreads();
     if (bad) {
         if (threadIdx.x == 0) atomicExch(nan_flag, 1);
         return;
@@ -472,7 +583,15 @@ static void optin_smem() {
     cudaFuncSetAttribute(k_prepare, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(k_apply, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(k_reduce_only, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    cudaFuncSetAttribute(k_small, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     done = true;
+}
+
+// shared-memory expm workspace for the 2r x 2r exponential (0 = does not fit, use the global-memory Pade path)
+static size_t small_smem_bytes(int r) {
+    size_t ld = (size_t)((2 * r + 3) & ~3);
+    size_t b = 6 * ld * ld * sizeof(double);
+    return b <= 200 * 1024 ? b : 0;
 }
 
 static int zero_small(gptb_handle *h, double *small, size_t stride, int D, int r) {
@@ -494,7 +613,10 @@ int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, cons
                                                                 noise_U, c.seed, step, 1);
     h->launches++;
     if (stiefel) {
-        k_small<<<c.D, 1024, 0, h->stream>>>(h->small, h->small_stride, c.r, sqrt(epsU), 1, h->nan_flag);
+        {
+            size_t sb = small_smem_bytes(c.r);
+            k_small<<<c.D, 1024, sb, h->stream>>>(h->small, h->small_stride, c.r, sqrt(epsU), 1, h->nan_flag, sb ? 1 : 0);
+        }
         size_t sm3 = (2 * (size_t)UP_ROWS * c.r + 2 * (size_t)c.r * c.r + c.r) * sizeof(double);
         k_apply<<<dim3(nb, c.D), UP_THREADS, sm3, h->stream>>>(h->U, h->G, h->small, h->small_stride, c.n, c.r,
                                                               h->nan_flag);
@@ -522,7 +644,10 @@ int gptb_proj_geod_device(gptb_handle *h, cudaStream_t s, int n, int r, const do
         int fb = (int)std::min<size_t>(((size_t)r * n + 255) / 256, 1024);
         k_proj_apply<<<fb, 256, 0, s>>>(U, V, small + L.S1, n, r, out);
     } else {
-        k_small<<<1, 1024, 0, s>>>(small, L.total, r, t, 0, nan_flag);
+        {
+            size_t sb = small_smem_bytes(r);
+            k_small<<<1, 1024, sb, s>>>(small, L.total, r, t, 0, nan_flag, sb ? 1 : 0);
+        }
         // Unew = U C1 + V C2 written over a copy of V (k_apply overwrites its G argument)
         cudaMemcpyAsync(out, V, sizeof(double) * (size_t)n * r, cudaMemcpyDeviceToDevice, s);
         size_t sm3 = (2 * (size_t)UP_ROWS * r + 2 * (size_t)r * r + r) * sizeof(double);
