@@ -8,19 +8,26 @@
 // Neither the N x D x n feature tensor (phi) nor Psi ever exists in memory.  In both kernels the
 // features are the A operand of the MMA and are written by the generator warps straight into
 // TENSOR MEMORY (tcgen05.st), never through shared memory: with N = r <= 64 the MMA would
-// otherwise be bound by the shared-memory reads of A (4 KB per 16-deep K step).  Shared memory
-// only carries the small B operand (U or E image chunks, 1-D bulk copies, see tc_layout.cuh).
+// otherwise be bound by the shared-memory reads of A (4 KB per 16-deep K step).
 //
-// Precision: fp16 x fp16 -> fp32 MMAs at twice the TF32 rate.  A single pass carries 2^-11 operand
-// rounding (~1e-3 after the D-fold product), so the parity mode TC3 splits both operands,
-// a = hi + lo (fp16 each), and issues hi*[hi|lo] (N = 2*rpad) and lo*hi (N = rpad):
-// 22+ significant bits at 1.5x the cost of one TF32 pass.  cos is MUFU.COS on an FP32 argument.
+// Both kernels are bound by MUFU.COS (16/clk/SM) when the B operand stays out of the way, so the
+// B operand is made to move as little as possible (measured: streaming U chunks per 128-row tile
+// made K1 L2-bound at 4.3 TB/s):
+//   K1  a CTA owns a contiguous range of (k, row tile) units in k-major order and keeps the whole
+//       operand image of U^(k) resident in shared memory (reloaded only when k changes);
+//   K3  a CTA owns a contiguous range of (k, feature-block group, row chunk) and uses every E chunk
+//       it loads for all feature blocks of the group (one accumulator per block in TMEM).
 //
-// CTA = 512 threads, one CTA per SM (persistent):
+// Precision: fp16 x fp16 -> fp32 MMAs.  A single pass carries 2^-11 operand rounding (~1e-3 after
+// the D-fold product), so the parity mode TC3 splits both operands, a = hi + lo (fp16 each), and
+// accumulates hi*hi + hi*lo + lo*hi into the same fp32 accumulator: 22 significant bits.
+// cos is MUFU.COS on an FP32 argument.
+//
+// CTA = 768 threads, one CTA per SM (persistent):
 //   warps 0-3   epilogue (TMEM -> registers -> global), one TMEM lane quarter each
 //   warp  4     MMA issuer (one elected lane), also owns the TMEM allocation
 //   warp  5     B-operand loader (cp.async.bulk + mbarrier)
-//   warps 8-15  two generator warpgroups, alternating K chunks of 64
+//   warps 8-23  four generator warpgroups, taking K chunks of 64 round-robin
 #include <cuda_fp16.h>
 
 #include "common.cuh"
@@ -31,14 +38,20 @@ namespace {
 
 using namespace tcx;
 
-constexpr int TC_THREADS = 512;
+constexpr int NGEN = 4;       // generator warpgroups (4 warps each, one per TMEM lane quarter)
+constexpr int TC_THREADS = 256 + 128 * NGEN;
 constexpr int KC = 64;        // K elements per chunk (4 MMA K-steps of 16)
-constexpr int NSTA = 4;       // A stages in TMEM (64 columns each: 32 hi + 32 lo)
-constexpr int NSTB = 4;       // B stages in shared memory
-constexpr int A_COLS = NSTA * 64;
+constexpr int SA_COLS = 64;   // TMEM columns of one A stage (32 hi + 32 lo, two fp16 per column)
+constexpr int NSTA_MAX = 8;
+constexpr int NSTB = 8;       // B stages in shared memory (streaming kernels)
+
+__host__ __device__ constexpr int nsta_for(int acc_cols) {
+    return (512 - acc_cols) / SA_COLS > NSTA_MAX ? NSTA_MAX : (512 - acc_cols) / SA_COLS;
+}
 
 struct Bars {
-    uint64_t a_full[NSTA], a_empty[NSTA], b_full[NSTB], b_empty[NSTB], acc_full[2], acc_empty[2];
+    uint64_t a_full[NSTA_MAX], a_empty[NSTA_MAX], b_full[NSTB], b_empty[NSTB], acc_full[2], acc_empty[2];
+    uint64_t u_full, u_empty;
     uint32_t tmem_base;
     uint32_t pad;
 };
@@ -56,6 +69,22 @@ __device__ __forceinline__ void split_pack(float a0, float a1, uint32_t &hi, uin
     }
 }
 
+// The MMAs of one 16-deep K step, all into accumulator d (RPAD columns):
+//   A_hi*B_hi (+ A_hi*B_lo + A_lo*B_hi in TC3).  b_addr = shared address of the K step's image rows.
+template <int RPAD, bool THREE, int B_MN_MAJOR>
+__device__ __forceinline__ void mma_kstep(uint32_t d, uint32_t a_hi, uint32_t a_lo, uint32_t b_addr, uint32_t acc) {
+    constexpr uint32_t idesc = make_idesc_f16(128, RPAD, B_MN_MAJOR);
+    constexpr uint32_t lbo = (2 * RPAD / 8) * 128, sbo = 128;
+    const uint64_t bd_hi = make_desc(b_addr, lbo, sbo);
+    mma_f16_ts(d, a_hi, bd_hi, idesc, acc);
+    if (THREE) {
+        const uint64_t bd_lo = make_desc(b_addr + (RPAD / 8) * 128, lbo, sbo);
+        mma_f16_ts(d, a_hi, bd_lo, idesc, 1);
+        mma_f16_ts(d, a_lo, bd_hi, idesc, 1);
+    }
+}
+
+// ============================================================================================ K1
 struct FwdParams {
     const float *XbF;      // [D][mpad]
     const __half *Uimg;    // see tc_layout.cuh
@@ -66,29 +95,61 @@ struct FwdParams {
     int D, n, npad, r;
     int64_t bs, mpad, mext;   // live rows, row stride of XbF/T, rows processed (bs rounded up to 128)
     int sincos;
-    int swap_lbo_sbo;      // probe switch
+    int exp;               // experiment bits (GPTB_TC_EXP): 1 = generators skip the math, 2 = issuer skips the MMAs
+    int P, NCHp;           // K split: P parts of NCHp chunks each (P > 1 only when the image of U^(k) exceeds shared memory;
+                           // T is then accumulated with atomics into a zeroed buffer)
 };
 
+// 64 features of one row -> the hi / lo words of one A stage.
+template <bool THREE>
+__device__ __forceinline__ void gen_fwd_chunk(const float2 *zb64, float x, bool sincos, uint32_t st_addr) {
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+        uint32_t hi[16], lo[16];
+        if (!sincos) {
+            const float4 *zb = reinterpret_cast<const float4 *>(zb64 + half * 32);
+#pragma unroll
+            for (int c = 0; c < 16; ++c) {
+                const float4 v = zb[c];
+                split_pack<THREE>(__cosf(fmaf(x, v.x, v.y)), __cosf(fmaf(x, v.z, v.w)), hi[c], lo[c]);
+            }
+        } else {
+            const float2 *zb = zb64 + half * 16;   // pair p of this chunk -> features 2p (sin), 2p+1 (cos)
+#pragma unroll
+            for (int c = 0; c < 16; ++c) {
+                const float a = x * zb[c].x;
+                split_pack<THREE>(__sinf(a), __cosf(a), hi[c], lo[c]);
+            }
+        }
+        tmem_st16(st_addr + half * 16, hi);
+        if (THREE) tmem_st16(st_addr + 32 + half * 16, lo);
+    }
+}
+
+// Resident-U forward.  Units u = (k*P + part)*ntiles + tile, CTA c owns [nunits*c/G, nunits*(c+1)/G).
 template <int RPAD, bool THREE>
 __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    constexpr int NB = THREE ? 2 * RPAD : RPAD;          // MMA N of the wide pass / accumulator width
-    constexpr int B_STAGE_BYTES = 2 * RPAD * KC * 2;     // image always carries hi|lo
-    constexpr int ACC_COLS = NB;
-    unsigned char *sB = smem_raw;
-    float2 *sZb = reinterpret_cast<float2 *>(smem_raw + NSTB * B_STAGE_BYTES);
-    Bars *bars = reinterpret_cast<Bars *>(smem_raw + NSTB * B_STAGE_BYTES + (size_t)p.D * p.npad * sizeof(float2));
+    constexpr int NSTA = nsta_for(2 * RPAD);
+    constexpr int ACC_BASE = NSTA * SA_COLS;
+    constexpr int ROW_BYTES = 2 * RPAD * 2;                  // image bytes per feature j (hi|lo)
+    const size_t u_cap = (size_t)p.NCHp * KC * ROW_BYTES;   // shared-memory bytes of one K part of the image
+    unsigned char *sU = smem_raw;
+    float2 *sZb = reinterpret_cast<float2 *>(smem_raw + u_cap);
+    Bars *bars = reinterpret_cast<Bars *>(smem_raw + u_cap + (size_t)p.NCHp * KC * sizeof(float2));
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int ntiles = (int)(p.mext / 128);
-    const int nunits = ntiles * p.D;
+    const int nunits = ntiles * p.D * p.P;
     const int NCH = p.npad / KC;
+    const int u0 = (int)((int64_t)nunits * blockIdx.x / gridDim.x);
+    const int u1 = (int)((int64_t)nunits * (blockIdx.x + 1) / gridDim.x);
 
-    for (int t = tid; t < p.D * p.npad; t += TC_THREADS) sZb[t] = p.ZbF[t];
     if (tid == 0) {
-        for (int s = 0; s < NSTA; ++s) { mbar_init(&bars->a_full[s], 128); mbar_init(&bars->a_empty[s], 1); }
-        for (int s = 0; s < NSTB; ++s) { mbar_init(&bars->b_full[s], 1); mbar_init(&bars->b_empty[s], 1); }
+        for (int s = 0; s < NSTA_MAX; ++s) { mbar_init(&bars->a_full[s], 128); mbar_init(&bars->a_empty[s], 1); }
         for (int s = 0; s < 2; ++s) { mbar_init(&bars->acc_full[s], 1); mbar_init(&bars->acc_empty[s], 128); }
+        mbar_init(&bars->u_full, 1);
+        mbar_init(&bars->u_empty, 1);
         fence_barrier_init();
     }
     if (warp == 4) tmem_alloc(&bars->tmem_base, 512);
@@ -96,98 +157,113 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
     __syncthreads();
     fence_after_sync();
     const uint32_t tmem = bars->tmem_base;
-    const uint32_t acc_base = tmem + A_COLS;
+    const uint32_t acc_base = tmem + ACC_BASE;
 
     if (warp >= 8) {
-        // ---------------------------------------------------------------- feature generators
+        // ---------------------------------------------------------------- feature generators (lane = row)
         const int g = (warp - 8) >> 2;
         const int q = warp & 3;
         const int row = q * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
-        uint32_t cg = 0;
-        for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
-            const int tile = u / p.D, k = u % p.D;
-            const float x = p.XbF[(size_t)k * p.mpad + (size_t)tile * 128 + row];
-            for (int ch = 0; ch < NCH; ++ch, ++cg) {
-                if ((int)(cg & 1) != g) continue;
-                const int sa = cg % NSTA;
-                mbar_wait(&bars->a_empty[sa], ((cg / NSTA) & 1) ^ 1);
-                fence_after_sync();
-                const uint32_t st_addr = tmem + lane_addr + sa * 64;
-#pragma unroll
-                for (int half = 0; half < 2; ++half) {
-                    uint32_t hi[16], lo[16];
-                    if (!p.sincos) {
-                        const float4 *zb = reinterpret_cast<const float4 *>(sZb + (size_t)k * p.npad + ch * KC + half * 32);
-#pragma unroll
-                        for (int c = 0; c < 16; ++c) {
-                            float4 v = zb[c];
-                            float a0 = __cosf(fmaf(x, v.x, v.y));
-                            float a1 = __cosf(fmaf(x, v.z, v.w));
-                            split_pack<THREE>(a0, a1, hi[c], lo[c]);
-                        }
-                    } else {
-                        const float2 *zb = sZb + (size_t)k * p.npad + (ch * KC + half * 32) / 2;
-#pragma unroll
-                        for (int c = 0; c < 16; ++c) {
-                            float a = x * zb[c].x;
-                            split_pack<THREE>(__sinf(a), __cosf(a), hi[c], lo[c]);
-                        }
-                    }
-                    tmem_st16(st_addr + half * 16, hi);
-                    if (THREE) tmem_st16(st_addr + 32 + half * 16, lo);
+        // this warpgroup takes chunks cg = g, g+NGEN, ... of the CTA's chunk sequence; (u, ch) follow incrementally
+        uint32_t gen = 0;
+        int u = u0, ch = g, cur_grp = -1, nch = 0, sa = g % NSTA;
+        uint32_t pa = ((g / NSTA) & 1) ^ 1;
+        float x = 0.f;
+        bool fresh = true;
+        while (u < u1) {
+            if (fresh) {
+                fresh = false;
+                const int grp = u / ntiles, tile = u - grp * ntiles, k = grp / p.P;
+                if (grp != cur_grp) {   // the (zt, b) table of this K part arrives with the U image
+                    cur_grp = grp;
+                    mbar_wait(&bars->u_full, gen & 1);
+                    ++gen;
+                    nch = min(p.NCHp, NCH - (grp - k * p.P) * p.NCHp);
                 }
-                wait_st();
-                fence_before_sync();
-                mbar_arrive(&bars->a_full[sa]);
+                x = p.XbF[(size_t)k * p.mpad + (size_t)tile * 128 + row];
             }
+            if (ch >= nch) { ch -= nch; ++u; fresh = true; continue; }
+            mbar_wait(&bars->a_empty[sa], pa);
+            fence_after_sync();
+            const uint32_t st_addr = tmem + lane_addr + sa * SA_COLS;
+            if (p.exp & 1) {
+                uint32_t z[16];
+#pragma unroll
+                for (int c = 0; c < 16; ++c) z[c] = 0x3c003c00u;
+                tmem_st16(st_addr, z); tmem_st16(st_addr + 16, z);
+                if (THREE) { tmem_st16(st_addr + 32, z); tmem_st16(st_addr + 48, z); }
+            } else {
+                gen_fwd_chunk<THREE>(sZb + (p.sincos ? ch * KC / 2 : ch * KC), x, p.sincos != 0, st_addr);
+            }
+            wait_st();
+            fence_before_sync();
+            mbar_arrive(&bars->a_full[sa]);
+            ch += NGEN;
+            sa += NGEN;
+            if (sa >= NSTA) { sa -= NSTA; pa ^= 1; }
         }
     } else if (warp == 4) {
-        // ---------------------------------------------------------------- MMA issuer
-        if (lane == 0) {
-            constexpr uint32_t idesc_wide = make_idesc_f16(128, NB, 0);
-            constexpr uint32_t idesc_narrow = make_idesc_f16(128, RPAD, 0);
-            uint32_t lbo = (2 * RPAD / 8) * 128, sbo = 128;
-            if (p.swap_lbo_sbo) { uint32_t t2 = lbo; lbo = sbo; sbo = t2; }
-            uint32_t cg = 0, it = 0;
-            for (int u = blockIdx.x; u < nunits; u += gridDim.x, ++it) {
-                const uint32_t ab = it & 1;
-                mbar_wait(&bars->acc_empty[ab], ((it >> 1) & 1) ^ 1);
+        // ---------------------------------------------------------------- MMA issuer (whole warp runs the loop)
+        uint32_t it = 0, gen = 0, pa = 0;
+        int cur_k = -1, sa = 0;
+        for (int u = u0; u < u1; ++u, ++it) {
+            const int grp = u / ntiles;
+            if (grp != cur_k) {
+                cur_k = grp;
+                mbar_wait(&bars->u_full, gen & 1);
+                ++gen;
+            }
+            const int nch = min(p.NCHp, NCH - (grp % p.P) * p.NCHp);
+            const bool last_of_k = (u + 1 == u1) || ((u + 1) / ntiles != grp);
+            const uint32_t ab = it & 1;
+            mbar_wait(&bars->acc_empty[ab], ((it >> 1) & 1) ^ 1);
+            fence_after_sync();
+            const uint32_t d = acc_base + ab * RPAD;
+            for (int ch = 0; ch < nch; ++ch) {
+                mbar_wait(&bars->a_full[sa], pa);
                 fence_after_sync();
-                const uint32_t d = acc_base + ab * ACC_COLS;
-                for (int ch = 0; ch < NCH; ++ch, ++cg) {
-                    const int sa = cg % NSTA, sb = cg % NSTB;
-                    mbar_wait(&bars->b_full[sb], (cg / NSTB) & 1);
-                    mbar_wait(&bars->a_full[sa], (cg / NSTA) & 1);
-                    fence_after_sync();
-                    const uint32_t a_hi = tmem + sa * 64, a_lo = a_hi + 32;
-                    const uint32_t b_addr = smem_u32(sB + sb * B_STAGE_BYTES);
+                const uint32_t a_hi = tmem + sa * SA_COLS, a_lo = a_hi + 32;
+                const uint32_t b_addr = smem_u32(sU + (size_t)ch * KC * ROW_BYTES);
+                if (elect_one()) {
+                    if (!(p.exp & 2)) {
 #pragma unroll
-                    for (int s4 = 0; s4 < KC / 16; ++s4) {
-                        const uint64_t bd = make_desc(b_addr + s4 * 2 * ((2 * RPAD / 8) * 128), lbo, sbo);
-                        mma_f16_ts(d, a_hi + s4 * 8, bd, idesc_wide, (ch | s4) != 0);
-                        if (THREE) mma_f16_ts(d, a_lo + s4 * 8, bd, idesc_narrow, 1);
+                        for (int s4 = 0; s4 < KC / 16; ++s4)
+                            mma_kstep<RPAD, THREE, 0>(d, a_hi + s4 * 8, a_lo + s4 * 8, b_addr + s4 * 16 * ROW_BYTES,
+                                                      (ch | s4) != 0);
                     }
                     mma_commit(&bars->a_empty[sa]);
-                    mma_commit(&bars->b_empty[sb]);
+                    if (ch == nch - 1) {
+                        mma_commit(&bars->acc_full[ab]);
+                        if (last_of_k) mma_commit(&bars->u_empty);
+                    }
                 }
-                mma_commit(&bars->acc_full[ab]);
+                __syncwarp();
+                if (++sa == NSTA) { sa = 0; pa ^= 1; }
             }
         }
-        __syncwarp();
     } else if (warp == 5) {
-        // ---------------------------------------------------------------- B loader
+        // ---------------------------------------------------------------- U / (zt,b) loader: once per k
         if (lane == 0) {
-            uint32_t cg = 0;
-            for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
-                const int k = u % p.D;
-                const __half *src = p.Uimg + (size_t)k * p.npad * 2 * RPAD;
-                for (int ch = 0; ch < NCH; ++ch, ++cg) {
-                    const int sb = cg % NSTB;
-                    mbar_wait(&bars->b_empty[sb], ((cg / NSTB) & 1) ^ 1);
-                    mbar_expect_tx(&bars->b_full[sb], B_STAGE_BYTES);
-                    bulk_g2s(sB + sb * B_STAGE_BYTES, src + (size_t)ch * KC * 2 * RPAD, B_STAGE_BYTES, &bars->b_full[sb]);
+            uint32_t gen = 0;
+            int cur_k = -1;
+            for (int u = u0; u < u1; ++u) {
+                const int grp = u / ntiles;
+                if (grp == cur_k) continue;
+                cur_k = grp;
+                const int k = grp / p.P, ch0 = (grp - k * p.P) * p.NCHp, nch = min(p.NCHp, NCH - ch0);
+                mbar_wait(&bars->u_empty, (gen & 1) ^ 1);
+                const size_t u_bytes = (size_t)nch * KC * ROW_BYTES;
+                const uint32_t zb_bytes = (uint32_t)(nch * KC * sizeof(float2)) / (p.sincos ? 2 : 1);
+                mbar_expect_tx(&bars->u_full, (uint32_t)u_bytes + zb_bytes);
+                const unsigned char *src = reinterpret_cast<const unsigned char *>(p.Uimg) +
+                                           ((size_t)k * p.npad + (size_t)ch0 * KC) * ROW_BYTES;
+                for (size_t off = 0; off < u_bytes; off += 32768) {
+                    const uint32_t nb = (uint32_t)(u_bytes - off < 32768 ? u_bytes - off : 32768);
+                    bulk_g2s(sU + off, src + off, nb, &bars->u_full);
                 }
+                bulk_g2s(sZb, p.ZbF + (size_t)k * p.npad + (size_t)ch0 * KC / (p.sincos ? 2 : 1), zb_bytes, &bars->u_full);
+                ++gen;
             }
         }
         __syncwarp();
@@ -197,27 +273,28 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
         const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
         const float scale = p.amp * p.uscale[1];
         uint32_t it = 0;
-        for (int u = blockIdx.x; u < nunits; u += gridDim.x, ++it) {
-            const int tile = u / p.D, k = u % p.D;
+        for (int u = u0; u < u1; ++u, ++it) {
+            const int grp = u / ntiles, tile = u - grp * ntiles, k = grp / p.P;
             const uint32_t ab = it & 1;
             mbar_wait(&bars->acc_full[ab], (it >> 1) & 1);
             fence_after_sync();
-            const uint32_t d = acc_base + ab * ACC_COLS + lane_addr;
+            const uint32_t d = acc_base + ab * RPAD + lane_addr;
             const int64_t i = (int64_t)tile * 128 + row;
             const bool live = i < p.bs;
             float *Tk = p.T + (size_t)k * p.r * p.mpad + i;
 #pragma unroll
             for (int c0 = 0; c0 < RPAD; c0 += 16) {
-                uint32_t v[16], v2[16];
+                uint32_t v[16];
                 tmem_ld16(d + c0, v);
-                if (THREE) tmem_ld16(d + RPAD + c0, v2);
                 wait_ld();
 #pragma unroll
                 for (int c = 0; c < 16; ++c) {
                     const int l = c0 + c;
-                    float val = __uint_as_float(v[c]);
-                    if (THREE) val += __uint_as_float(v2[c]);
-                    if (l < p.r) Tk[(size_t)l * p.mpad] = live ? val * scale : 0.f;
+                    if (l < p.r) {
+                        const float val = live ? __uint_as_float(v[c]) * scale : 0.f;
+                        if (p.P == 1) Tk[(size_t)l * p.mpad] = val;
+                        else atomicAdd(Tk + (size_t)l * p.mpad, val);
+                    }
                 }
             }
             fence_before_sync();
@@ -229,40 +306,53 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
     if (warp == 4) tmem_dealloc(tmem, 512);
 }
 
+// ============================================================================================ K3
 struct BwdParams {
     const float *XbF;      // [D][mpad]
     const __half *Eimg;    // see tc_layout.cuh
     const float *ZtF, *bF; // [D][npad]
     const float *escale;   // -> {escale, 1/escale}
-    double *gradU;         // [D][r][n], accumulated with atomics
+    float *gradF;          // [D][npad][RPAD] fp32 partial sums, reduced with vector RED; finalize_grad_kernel folds
+                           // them into the FP64 gradient and clears them
     float amp;
     int D, n, npad, r;
     int64_t mpad, mext;
     int sincos;
-    int swap_lbo_sbo;
+    int JG, NJG;           // feature blocks (128 features) per group, groups per dimension
+    int nsta;              // A stages that fit beside the JG accumulators
 };
 
+__device__ __forceinline__ void red_add_v4(float *addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// Work items it = (k*NJG + jg)*NCH + ch, CTA c owns [total*c/G, total*(c+1)/G).  For every item the loader
+// brings one 64-row chunk of the E image (and the 64 inputs x_ik) and the generators / issuer run JG
+// "A steps" on it, one per 128-feature block of the group.
 template <int RPAD, bool THREE>
 __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    constexpr int NB = THREE ? 2 * RPAD : RPAD;
     constexpr int B_IMG_BYTES = 2 * RPAD * KC * 2;
     constexpr int X_BYTES = KC * 4;                         // the chunk's 64 input values ride in the same stage
     constexpr int B_STAGE_BYTES = B_IMG_BYTES + X_BYTES;
-    constexpr int ACC_COLS = NB;
+    constexpr int ROW_BYTES = 2 * RPAD * 2;
     unsigned char *sB = smem_raw;
     Bars *bars = reinterpret_cast<Bars *>(smem_raw + NSTB * B_STAGE_BYTES);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int JB = p.npad / 128;
+    const int JB = p.npad / 128, JG = p.JG, NJG = p.NJG, NSTA = p.nsta;
     const int NCH = (int)(p.mext / KC);
-    const int64_t total = (int64_t)p.D * JB * NCH;
+    const int64_t total = (int64_t)p.D * NJG * NCH;
     const int64_t it0 = total * blockIdx.x / gridDim.x, it1 = total * (blockIdx.x + 1) / gridDim.x;
+    const int grp0 = (int)(it0 / NCH), ch0 = (int)(it0 - (int64_t)grp0 * NCH);
+    const uint32_t n_it = (uint32_t)(it1 - it0);
+    const uint32_t n_as = n_it * JG;
 
     if (tid == 0) {
-        for (int s = 0; s < NSTA; ++s) { mbar_init(&bars->a_full[s], 128); mbar_init(&bars->a_empty[s], 1); }
+        for (int s = 0; s < NSTA_MAX; ++s) { mbar_init(&bars->a_full[s], 128); mbar_init(&bars->a_empty[s], 1); }
         for (int s = 0; s < NSTB; ++s) { mbar_init(&bars->b_full[s], 1); mbar_init(&bars->b_empty[s], 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(&bars->acc_full[s], 1); mbar_init(&bars->acc_empty[s], 128); }
+        mbar_init(&bars->acc_full[0], 1);
+        mbar_init(&bars->acc_empty[0], 128);
         fence_barrier_init();
     }
     if (warp == 4) tmem_alloc(&bars->tmem_base, 512);
@@ -270,7 +360,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
     __syncthreads();
     fence_after_sync();
     const uint32_t tmem = bars->tmem_base;
-    const uint32_t acc_base = tmem + A_COLS;
+    const uint32_t acc_base = tmem + NSTA * SA_COLS;
 
     if (warp >= 8) {
         // ---------------------------------------------------------------- feature generators (lane = feature)
@@ -278,38 +368,36 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
         const int q = warp & 3;
         const int jl = q * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
-        int cur_grp = -1;
-        float zt = 0.f, bb = 0.f;
-        int k = 0;
-        uint32_t cnt = 0;
-        for (int64_t it = it0; it < it1; ++it, ++cnt) {
-            const int grp = (int)(it / NCH), ch = (int)(it % NCH);
-            if (grp != cur_grp) {
-                cur_grp = grp;
-                k = grp / JB;
-                const int j = (grp % JB) * 128 + jl;
-                if (!p.sincos) {
-                    zt = p.ZtF[(size_t)k * p.npad + j];
-                    bb = p.bF[(size_t)k * p.npad + j];
-                } else {  // rows 2p / 2p+1 are sin / cos of x*Zt[p]:  cos(a) = sin(a + pi/2)
-                    zt = p.ZtF[(size_t)k * p.npad + (j >> 1)];
-                    bb = (j & 1) ? 1.5707963267948966f : 0.f;
-                }
+        // position of A step `as`: item lit (-> grp, ch) and block jbl
+        int jbl = g, ch = ch0, grp = grp0;
+        uint32_t lit = 0;
+        while (jbl >= JG) { jbl -= JG; ++lit; if (++ch == NCH) { ch = 0; ++grp; } }
+        int sa = g % NSTA;
+        uint32_t pa = ((g / NSTA) & 1) ^ 1;
+        for (uint32_t as = g; as < n_as; as += NGEN) {
+            const int k = grp / NJG, jg = grp - k * NJG;
+            int j = (jg * JG + jbl) * 128 + jl;
+            if (j >= p.npad) j = p.npad - 1;    // padding block of a ragged last group: computed, never stored
+            float zt, bb;
+            if (!p.sincos) {
+                zt = p.ZtF[(size_t)k * p.npad + j];
+                bb = p.bF[(size_t)k * p.npad + j];
+            } else {  // rows 2p / 2p+1 are sin / cos of x*Zt[p]:  cos(a) = sin(a + pi/2)
+                zt = p.ZtF[(size_t)k * p.npad + (j >> 1)];
+                bb = (j & 1) ? 1.5707963267948966f : 0.f;
             }
-            if ((int)(cnt & 1) != g) continue;
-            const int sa = cnt % NSTA;
-            mbar_wait(&bars->a_empty[sa], ((cnt / NSTA) & 1) ^ 1);
+            const int sb = lit % NSTB;
+            mbar_wait(&bars->a_empty[sa], pa);
             fence_after_sync();
-            const uint32_t st_addr = tmem + lane_addr + sa * 64;
-            const int sbx = cnt % NSTB;
-            mbar_wait(&bars->b_full[sbx], (cnt / NSTB) & 1);
-            const float4 *xr = reinterpret_cast<const float4 *>(sB + sbx * B_STAGE_BYTES + B_IMG_BYTES);
+            mbar_wait(&bars->b_full[sb], (lit / NSTB) & 1);
+            const uint32_t st_addr = tmem + lane_addr + sa * SA_COLS;
+            const float4 *xr = reinterpret_cast<const float4 *>(sB + sb * B_STAGE_BYTES + B_IMG_BYTES);
 #pragma unroll
             for (int half = 0; half < 2; ++half) {
                 uint32_t hi[16], lo[16];
 #pragma unroll
                 for (int c = 0; c < 16; c += 2) {
-                    float4 xx = xr[half * 8 + c / 2];
+                    const float4 xx = xr[half * 8 + c / 2];
                     float a0, a1, a2, a3;
                     if (!p.sincos) {
                         a0 = __cosf(fmaf(xx.x, zt, bb)); a1 = __cosf(fmaf(xx.y, zt, bb));
@@ -327,60 +415,62 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
             wait_st();
             fence_before_sync();
             mbar_arrive(&bars->a_full[sa]);
+            jbl += NGEN;
+            while (jbl >= JG) { jbl -= JG; ++lit; if (++ch == NCH) { ch = 0; ++grp; } }
+            sa += NGEN;
+            while (sa >= NSTA) { sa -= NSTA; pa ^= 1; }
         }
     } else if (warp == 4) {
-        // ---------------------------------------------------------------- MMA issuer
-        if (lane == 0) {
-            constexpr uint32_t idesc_wide = make_idesc_f16(128, NB, 1);
-            constexpr uint32_t idesc_narrow = make_idesc_f16(128, RPAD, 1);
-            uint32_t lbo = (2 * RPAD / 8) * 128, sbo = 128;
-            if (p.swap_lbo_sbo) { uint32_t t2 = lbo; lbo = sbo; sbo = t2; }
-            uint32_t cnt = 0, seg = 0;
-            bool fresh = true;
-            for (int64_t it = it0; it < it1; ++it, ++cnt) {
-                const int ch = (int)(it % NCH);
-                const uint32_t ab = seg & 1;
-                if (fresh) {
-                    mbar_wait(&bars->acc_empty[ab], ((seg >> 1) & 1) ^ 1);
-                    fence_after_sync();
-                }
-                const uint32_t d = acc_base + ab * ACC_COLS;
-                const int sa = cnt % NSTA, sb = cnt % NSTB;
-                mbar_wait(&bars->b_full[sb], (cnt / NSTB) & 1);
-                mbar_wait(&bars->a_full[sa], (cnt / NSTA) & 1);
+        // ---------------------------------------------------------------- MMA issuer (whole warp runs the loop)
+        uint32_t seg = 0, pa = 0;
+        int ch = ch0, sa = 0;
+        bool fresh = true;
+        for (uint32_t lit = 0; lit < n_it; ++lit) {
+            if (fresh) {
+                mbar_wait(&bars->acc_empty[0], (seg & 1) ^ 1);
                 fence_after_sync();
-                const uint32_t a_hi = tmem + sa * 64, a_lo = a_hi + 32;
-                const uint32_t b_addr = smem_u32(sB + sb * B_STAGE_BYTES);
-#pragma unroll
-                for (int s4 = 0; s4 < KC / 16; ++s4) {
-                    const uint64_t bd = make_desc(b_addr + s4 * 2 * ((2 * RPAD / 8) * 128), lbo, sbo);
-                    mma_f16_ts(d, a_hi + s4 * 8, bd, idesc_wide, (!fresh || s4 != 0) ? 1u : 0u);
-                    if (THREE) mma_f16_ts(d, a_lo + s4 * 8, bd, idesc_narrow, 1);
-                }
-                fresh = false;
-                mma_commit(&bars->a_empty[sa]);
-                mma_commit(&bars->b_empty[sb]);
-                if (ch == NCH - 1 || it == it1 - 1) {
-                    mma_commit(&bars->acc_full[ab]);
-                    ++seg;
-                    fresh = true;
-                }
             }
+            const int sb = lit % NSTB;
+            mbar_wait(&bars->b_full[sb], (lit / NSTB) & 1);
+            const uint32_t b_addr = smem_u32(sB + sb * B_STAGE_BYTES);
+            const bool last = (ch == NCH - 1) || (lit == n_it - 1);
+            for (int jbl = 0; jbl < JG; ++jbl) {
+                mbar_wait(&bars->a_full[sa], pa);
+                fence_after_sync();
+                const uint32_t a_hi = tmem + sa * SA_COLS, a_lo = a_hi + 32;
+                const uint32_t d = acc_base + jbl * RPAD;
+                if (elect_one()) {
+#pragma unroll
+                    for (int s4 = 0; s4 < KC / 16; ++s4)
+                        mma_kstep<RPAD, THREE, 1>(d, a_hi + s4 * 8, a_lo + s4 * 8, b_addr + s4 * 16 * ROW_BYTES,
+                                                  (!fresh || s4 != 0) ? 1u : 0u);
+                    mma_commit(&bars->a_empty[sa]);
+                    if (jbl == JG - 1) {
+                        mma_commit(&bars->b_empty[sb]);
+                        if (last) mma_commit(&bars->acc_full[0]);
+                    }
+                }
+                __syncwarp();
+                if (++sa == NSTA) { sa = 0; pa ^= 1; }
+            }
+            fresh = false;
+            ++ch;
+            if (last) { ch = 0; ++seg; fresh = true; }
         }
-        __syncwarp();
     } else if (warp == 5) {
         // ---------------------------------------------------------------- B loader
         if (lane == 0) {
-            uint32_t cnt = 0;
-            for (int64_t it = it0; it < it1; ++it, ++cnt) {
-                const int grp = (int)(it / NCH), ch = (int)(it % NCH);
-                const int k = grp / JB;
+            int grp = grp0, ch = ch0;
+            for (uint32_t lit = 0; lit < n_it; ++lit) {
+                const int k = grp / NJG;
+                const int sb = lit % NSTB;
                 const __half *src = p.Eimg + (size_t)k * p.mpad * 2 * RPAD + (size_t)ch * KC * 2 * RPAD;
-                const int sb = cnt % NSTB;
-                mbar_wait(&bars->b_empty[sb], ((cnt / NSTB) & 1) ^ 1);
+                mbar_wait(&bars->b_empty[sb], ((lit / NSTB) & 1) ^ 1);
                 mbar_expect_tx(&bars->b_full[sb], B_STAGE_BYTES);
-                bulk_g2s(sB + sb * B_STAGE_BYTES + B_IMG_BYTES, p.XbF + (size_t)k * p.mpad + (size_t)ch * KC, X_BYTES, &bars->b_full[sb]);
+                bulk_g2s(sB + sb * B_STAGE_BYTES + B_IMG_BYTES, p.XbF + (size_t)k * p.mpad + (size_t)ch * KC, X_BYTES,
+                         &bars->b_full[sb]);
                 bulk_g2s(sB + sb * B_STAGE_BYTES, src, B_IMG_BYTES, &bars->b_full[sb]);
+                if (++ch == NCH) { ch = 0; ++grp; }
             }
         }
         __syncwarp();
@@ -391,36 +481,48 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
         uint32_t seg = 0;
         for (int64_t it = it0; it < it1; ++seg) {
             const int grp = (int)(it / NCH);
-            const int64_t seg_end = min((long long)it1, (long long)(grp + 1) * NCH);
-            it = seg_end;
-            const int k = grp / JB;
-            const int j = (grp % JB) * 128 + warp * 32 + lane;
-            const uint32_t ab = seg & 1;
-            mbar_wait(&bars->acc_full[ab], (seg >> 1) & 1);
+            it = min((long long)it1, (long long)(grp + 1) * NCH);
+            const int k = grp / NJG, jg = grp - k * NJG;
+            mbar_wait(&bars->acc_full[0], seg & 1);
             fence_after_sync();
-            const uint32_t d = acc_base + ab * ACC_COLS + lane_addr;
-            double *gk = p.gradU + (size_t)k * p.r * p.n + j;
+            for (int jbl = 0; jbl < JG; ++jbl) {
+                const int jb = jg * JG + jbl;
+                if (jb >= JB) break;
+                const int j = jb * 128 + warp * 32 + lane;
+                float *gk = p.gradF + ((size_t)k * p.npad + j) * RPAD;
+                const uint32_t d = acc_base + jbl * RPAD + lane_addr;
 #pragma unroll
-            for (int c0 = 0; c0 < RPAD; c0 += 16) {
-                uint32_t v[16], v2[16];
-                tmem_ld16(d + c0, v);
-                if (THREE) tmem_ld16(d + RPAD + c0, v2);
-                wait_ld();
+                for (int c0 = 0; c0 < RPAD; c0 += 16) {
+                    uint32_t v[16];
+                    tmem_ld16(d + c0, v);
+                    wait_ld();
 #pragma unroll
-                for (int c = 0; c < 16; ++c) {
-                    const int l = c0 + c;
-                    float val = __uint_as_float(v[c]);
-                    if (THREE) val += __uint_as_float(v2[c]);
-                    if (l < p.r && j < p.n) atomicAdd(gk + (size_t)l * p.n, (double)(val * scale));
+                    for (int c = 0; c < 16; c += 4)
+                        red_add_v4(gk + c0 + c, __uint_as_float(v[c]) * scale, __uint_as_float(v[c + 1]) * scale,
+                                   __uint_as_float(v[c + 2]) * scale, __uint_as_float(v[c + 3]) * scale);
                 }
             }
             fence_before_sync();
-            mbar_arrive(&bars->acc_empty[ab]);
+            mbar_arrive(&bars->acc_empty[0]);
         }
     }
     fence_before_sync();
     __syncthreads();
     if (warp == 4) tmem_dealloc(tmem, 512);
+}
+
+// gradU[k][l][j] (FP64, Julia order) += gradF[k][j][l]; gradF is cleared for the next step.
+__global__ void finalize_grad_kernel(float *__restrict__ gradF, double *__restrict__ gradU, int D, int n, int npad, int r,
+                                     int rpad) {
+    const size_t total = (size_t)D * npad * rpad;
+    for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const int l = (int)(t % rpad);
+        const int j = (int)((t / rpad) % npad);
+        const int k = (int)(t / ((size_t)rpad * npad));
+        const float v = gradF[t];
+        gradF[t] = 0.f;
+        if (l < r && j < n) gradU[((size_t)k * r + l) * n + j] += (double)v;
+    }
 }
 
 // ------------------------------------------------------------------------------------------- packing
@@ -469,11 +571,11 @@ __global__ void interleave_zb_kernel(const float *zt, const float *b, size_t n, 
         out[i] = make_float2(zt[i], b[i]);
 }
 
-int probe_swap() {
+int probe_exp() {
     static int v = -1;
     if (v < 0) {
-        const char *e = getenv("GPTB_TC_SWAP_LBO_SBO");
-        v = (e && e[0] == '1') ? 1 : 0;
+        const char *e = getenv("GPTB_TC_EXP");
+        v = e ? atoi(e) : 0;
     }
     return v;
 }
@@ -567,22 +669,25 @@ int gptb_launch_fwd_tc(gptb_handle *h, const float *XbF, const void *Uimg, int64
     p.mpad = mpad;
     p.mext = (bs + 127) / 128 * 128;   // only the 128-row tiles that hold live rows are generated
     p.sincos = c.feature_kind == GPTB_FEAT_SINCOS;
-    p.swap_lbo_sbo = probe_swap();
-    const int nunits = (int)(p.mext / 128) * c.D;
-    const FwdParams &q = p;
+    p.exp = probe_exp();
+    // K parts: the image of one part (plus its (zt,b) table) must fit in shared memory
+    const int NCH = h->npad / KC;
+    const size_t chunk_bytes = (size_t)KC * (2 * h->rpad * 2 + sizeof(float2));
+    const size_t budget = 227 * 1024 - sizeof(Bars) - 1024;
+    const int max_chunks = (int)(budget / chunk_bytes);
+    p.P = (NCH + max_chunks - 1) / max_chunks;
+    p.NCHp = (NCH + p.P - 1) / p.P;
+    if (p.P > 1) GPTB_CUDA_OK(h, cudaMemsetAsync(T, 0, sizeof(float) * (size_t)c.D * c.r * mpad, h->stream));
+    const int nunits = (int)(p.mext / 128) * c.D * p.P;
     const int grid = std::max(1, std::min(h->sm_count, nunits));
     // at least 120 KB so that two CTAs (each wants all 512 TMEM columns) never share an SM
-    const size_t smem = std::max<size_t>((size_t)NSTB * (2 * h->rpad * KC * 2) + (size_t)c.D * h->npad * sizeof(float2) + sizeof(Bars) + 64, 120 * 1024);
-    if (smem > 227 * 1024) {
-        gptb_set_error(h, "tensor-core forward: D*n=%d too large for the shared-memory feature table", c.D * h->npad);
-        return GPTB_ERR_UNSUPPORTED;
-    }
+    const size_t smem = std::max<size_t>((size_t)p.NCHp * chunk_bytes + sizeof(Bars) + 64, 120 * 1024);
     int st;
     switch (h->rpad) {
-        case 16: st = launch_fwd_r<16>(h, q, grid, smem); break;
-        case 32: st = launch_fwd_r<32>(h, q, grid, smem); break;
-        case 48: st = launch_fwd_r<48>(h, q, grid, smem); break;
-        default: st = launch_fwd_r<64>(h, q, grid, smem); break;
+        case 16: st = launch_fwd_r<16>(h, p, grid, smem); break;
+        case 32: st = launch_fwd_r<32>(h, p, grid, smem); break;
+        case 48: st = launch_fwd_r<48>(h, p, grid, smem); break;
+        default: st = launch_fwd_r<64>(h, p, grid, smem); break;
     }
     GPTB_TRY(st);
     h->launches++;
@@ -592,6 +697,11 @@ int gptb_launch_fwd_tc(gptb_handle *h, const float *XbF, const void *Uimg, int64
 
 int gptb_launch_bwd_tc(gptb_handle *h, const float *XbF, const void *Eimg, int64_t bs, int64_t mpad, double *gradU) {
     const gptb_config &c = h->cfg;
+    const size_t gf = (size_t)c.D * h->npad * h->rpad;
+    if (!h->gradF) {
+        GPTB_CUDA_OK(h, cudaMalloc((void **)&h->gradF, gf * sizeof(float)));
+        GPTB_CUDA_OK(h, cudaMemsetAsync(h->gradF, 0, gf * sizeof(float), h->stream));
+    }
     BwdParams p;
     p.mext = (bs + 127) / 128 * 128;
     p.XbF = XbF;
@@ -599,15 +709,19 @@ int gptb_launch_bwd_tc(gptb_handle *h, const float *XbF, const void *Eimg, int64
     p.ZtF = h->ZtF;
     p.bF = h->bF;
     p.escale = h->tc_state + 1;
-    p.gradU = gradU;
+    p.gradF = h->gradF;
     p.amp = (float)h->amp;
     p.D = c.D; p.n = c.n; p.npad = h->npad; p.r = c.r;
     p.mpad = mpad;
     p.sincos = c.feature_kind == GPTB_FEAT_SINCOS;
-    p.swap_lbo_sbo = probe_swap();
-    const int64_t total = (int64_t)c.D * (h->npad / 128) * (p.mext / KC);
+    const int JB = h->npad / 128;
+    const int jg_max = 256 / h->rpad;                 // accumulators take at most half of TMEM
+    p.NJG = (JB + jg_max - 1) / jg_max;
+    p.JG = (JB + p.NJG - 1) / p.NJG;
+    p.nsta = nsta_for(p.JG * h->rpad);
+    const int64_t total = (int64_t)c.D * p.NJG * (p.mext / KC);
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(h->sm_count, total));
-    const size_t smem = std::max<size_t>((size_t)NSTB * (2 * h->rpad * KC * 2) + sizeof(Bars) + 64, 120 * 1024);
+    const size_t smem = std::max<size_t>((size_t)NSTB * (2 * h->rpad * KC * 2 + KC * 4) + sizeof(Bars) + 64, 120 * 1024);
     int st;
     switch (h->rpad) {
         case 16: st = launch_bwd_r<16>(h, p, grid, smem); break;
@@ -616,7 +730,9 @@ int gptb_launch_bwd_tc(gptb_handle *h, const float *XbF, const void *Eimg, int64
         default: st = launch_bwd_r<64>(h, p, grid, smem); break;
     }
     GPTB_TRY(st);
-    h->launches++;
+    finalize_grad_kernel<<<(int)std::min<size_t>((gf + 255) / 256, (size_t)h->sm_count * 4), 256, 0, h->stream>>>(
+        h->gradF, gradU, c.D, c.n, h->npad, c.r, h->rpad);
+    h->launches += 2;
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;
 }
