@@ -413,6 +413,7 @@ int gptb_destroy(gptb_handle *h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     gptb_comm_destroy(h);
     dev_free(&h->Zt); dev_free(&h->b); dev_free(&h->ZtF); dev_free(&h->bF); dev_free(&h->I); dev_free(&h->grp_ptr); dev_free(&h->grp_q);
+    dev_free(&h->ct_off1); dev_free(&h->ct_lptr); dev_free(&h->ct_lists);
     dev_free(&h->X); dev_free(&h->y); dev_free(&h->phi); dev_free(&h->order); dev_free(&h->order_tmp);
     dev_free(&h->sort_keys); dev_free(&h->sort_keys_tmp);
     if (h->sort_tmp) cudaFree(h->sort_tmp);
@@ -430,6 +431,7 @@ int gptb_destroy(gptb_handle *h) {
     dev_free(&h->tc_state);
     dev_free(&h->G); dev_free(&h->small); dev_free(&h->colnorm); dev_free(&h->nan_flag);
     dev_free(&h->noise_w); dev_free(&h->noise_U); dev_free(&h->pred_acc);
+    dev_free(&h->gen_noise_w); dev_free(&h->gen_noise_U);
     dev_free(&h->store_w); dev_free(&h->store_U);
     if (h->nan_flag_host) cudaFreeHost(h->nan_flag_host);
     if (h->pin) cudaFreeHost(h->pin);
@@ -528,6 +530,7 @@ int gptb_set_index(gptb_handle *h, const int32_t *I) {
     GPTB_CUDA_OK(h, cudaMemcpyAsync(h->grp_ptr, ptr.data(), ptr.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
     GPTB_CUDA_OK(h, cudaMemcpyAsync(h->grp_q, gq.data(), gq.size() * sizeof(uint16_t), cudaMemcpyHostToDevice, h->stream));
     GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    if (gptb_is_tc(h)) GPTB_TRY(gptb_contract_tc_build_tables(h, z.data()));
     h->have_index = true;
     return GPTB_OK;
 }

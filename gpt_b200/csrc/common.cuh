@@ -60,6 +60,7 @@ struct gptb_handle {
     int32_t *I = nullptr;
     int32_t *grp_ptr = nullptr;   // [D*rpad+1] CSR over (k,l): which q have I[q,k] = l (contract.cu pass 2)
     uint16_t *grp_q = nullptr;    // [Q*D]
+    int32_t *ct_off1 = nullptr, *ct_lptr = nullptr, *ct_lists = nullptr;   // offset tables of contract_tc.cu
 
     // training data
     int64_t N = 0;
@@ -107,6 +108,7 @@ struct gptb_handle {
     int32_t *nan_flag = nullptr;       // device, sticky
     int32_t *nan_flag_host = nullptr;  // pinned
     double *noise_w = nullptr, *noise_U = nullptr;  // staged host-supplied noise
+    double *gen_noise_w = nullptr, *gen_noise_U = nullptr;   // production-mode draws of the running step (k_noise)
 
     // multi-sample prediction scratch
     double *pred_acc = nullptr;
@@ -202,6 +204,10 @@ int gptb_launch_bwd_fp64(gptb_handle *h, const double *Xb, const double *phib, c
 int gptb_launch_contract(gptb_handle *h, const void *T, const void *w, const double *yb, int64_t bs, int64_t mpad,
                          double escale, bool want_grad, double *fhat, double *gradw /*accumulated*/, void *E, void *Eimg,
                          bool real_is_double);
+// contract_tc.cu
+int gptb_contract_tc_build_tables(gptb_handle *h, const int32_t *Iz /*[D][Q] 0-based, host*/);
+int gptb_launch_contract_tc(gptb_handle *h, const float *T, const double *w, const double *yb, int64_t bs, int64_t mpad,
+                            double escale, bool want_grad, double *fhat, double *gradw, void *Eimg);
 // update.cu
 int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
                        const double *noise_U, uint64_t step);

@@ -213,6 +213,11 @@ int gptb_launch_contract(gptb_handle *h, const void *T, const void *w, const dou
                          double escale, bool want_grad, double *fhat, double *gradw, void *E, void *Eimg,
                          bool real_is_double) {
     if (bs <= 0) return GPTB_OK;
+    if (!real_is_double) {
+        const int st = gptb_launch_contract_tc(h, (const float *)T, (const double *)w, yb, bs, mpad, escale, want_grad, fhat,
+                                               gradw, Eimg);
+        if (st != GPTB_ERR_UNSUPPORTED) return st;   // shapes that do not fit its shared-memory tile fall through
+    }
     ContractParams p;
     p.T = T;
     p.w = (const double *)w;

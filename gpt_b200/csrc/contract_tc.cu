@@ -1,0 +1,296 @@
+// K2 (tensor-core path) — core contraction, residual and leave-one-out back-projection in FP32,
+// two minibatch rows per thread.
+//
+// Replaces (all /root/reference/GPT_SGLD.jl):
+//   computeV     :208-220   V[q,i]   = prod_k T[k, I[q,k], i]
+//   computefhat  :223-230   fhat[i]  = sum_q w[q] V[q,i]
+//   grad-w       :393       gradw   += sum_i e_i V[:,i],      e_i = (N/bs)(y_i - fhat_i)/signal_var
+//   computeU_phi :246-258   U_phi[q,i,k] = V[q,i] / T[k, I[q,k], i]
+//   computeA     :261-273   A[l,k,i] = sum_{q: I[q,k]=l} w[q] U_phi[q,i,k]
+// and emits the fp16 hi|lo operand image of E[k][l][i] = e_i * A[l,k,i] for K3 (tc_layout.cuh).
+//
+// The kernel is a gather machine: per row 2*Q*D shared-memory reads whose index (I[q,k]) is the same for
+// every row, so rows sit on the lanes (conflict-free, unit stride) and the bound is shared-memory bandwidth
+// (8*Q*D bytes per row) as long as the instruction count per gather stays near one.  Hence:
+//   * a CTA owns 64 rows and a lane two adjacent rows: every gather is one LDS.64 feeding packed FP32 math
+//     (FMUL2 / FADD2), and the pre-multiplied offset tables are read four at a time (one 16-byte uniform load);
+//   * pass 1: warp s forms V[q,:] for q = s, s+8, ... and its share of fhat; V goes to shared memory;
+//   * gradw: a warp reduces e_i V[q,i] for up to 32 of its q at once with a 31-shuffle transpose-reduction;
+//   * pass 2: every (k,l) owns the list of q with I[q,k] = l (built in gptb_set_index), so
+//     A[l,k,i] = (sum_{q in list} w_q V[q,i]) / T[k,l,i] — the reference's own division (:253) taken once per
+//     (k,l).  If T[k,l,i] is exactly 0 the quotient is replaced by the explicit leave-one-out product (the
+//     reference would produce Inf/NaN there).  A warp handles 8 consecutive l at a time, so it writes whole
+//     32-byte pieces (two rows x 8 fp16) of the MMA operand image.
+#include <cuda_fp16.h>
+
+#include <vector>
+
+#include "common.cuh"
+#include "tc_layout.cuh"
+
+namespace {
+
+constexpr int CRB = 64;          // rows per CTA
+constexpr int CNW = 16;          // warps per CTA: the gathers are latency-bound chains (offset load -> LDS -> FMUL2),
+                                 // and 128+ KB of tiles allow one CTA per SM, so the CTA itself must bring the warps
+constexpr int CT_THREADS = 32 * CNW;
+
+struct ContractTcParams {
+    const float *T;          // [D][r][mpad]
+    const double *w;
+    const int32_t *off1;     // [Q][DP]  (k*r + I[q,k]) * 32  (float2 index into Ts), DP = D rounded up to 4
+    const int32_t *lptr;     // [D*rpad + 1] start of each (k,l) list in `lists` (lists padded to multiples of 4)
+    const int32_t *lists;    // q * 32 (float2 index into Vs) for the q of each list; padding entries -> zero row q = Q
+    const double *yb;
+    double *fhat, *gradw;
+    __half *Eimg;
+    const float *escale_img;
+    float *emax_out;
+    int64_t bs, mpad;
+    double escale;
+    int DP, r, rpad, Q, want_grad;
+};
+
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
+
+template <int DT>
+__global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const ContractTcParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int D = DT;
+    constexpr int DP4 = (DT + 3) / 4;
+    const int r = p.r, rpad = p.rpad, Q = p.Q, DR = D * r;
+    const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    const int64_t i0 = (int64_t)blockIdx.x * CRB + 2 * lane;     // this lane's rows: i0, i0 + 1
+    const bool live0 = i0 < p.bs, live1 = i0 + 1 < p.bs;
+
+    float2 *Ts = reinterpret_cast<float2 *>(smem_raw);           // [DR][32]
+    float2 *Vs = Ts + (size_t)DR * 32;                           // [Q + 1][32], row Q is zero
+    float *ws = reinterpret_cast<float *>(Vs + (size_t)(Q + 1) * 32);   // [Q rounded up to 4]
+    float2 *Fs = reinterpret_cast<float2 *>(ws + ((Q + 3) & ~3)); // [CNW][32]
+
+    for (int t = tid; t < Q; t += CT_THREADS) ws[t] = (float)p.w[t];
+    if (wp == 0) Vs[(size_t)Q * 32 + lane] = make_float2(0.f, 0.f);
+    for (int c = wp; c < DR; c += CNW)
+        Ts[(size_t)c * 32 + lane] = *reinterpret_cast<const float2 *>(p.T + (size_t)c * p.mpad + i0);
+    __syncthreads();
+
+    // ---- pass 1: V and fhat
+    const float2 *Trow = Ts + lane;
+    float2 f = make_float2(0.f, 0.f);
+#pragma unroll 2
+    for (int q = wp; q < Q; q += CNW) {
+        const int4 *o = reinterpret_cast<const int4 *>(p.off1) + (size_t)q * DP4;
+        float2 v = make_float2(1.f, 1.f);
+#pragma unroll
+        for (int g4 = 0; g4 < DP4; ++g4) {
+            const int4 oo = __ldg(o + g4);
+            if (g4 * 4 + 0 < D) v = mul2(v, Trow[oo.x]);
+            if (g4 * 4 + 1 < D) v = mul2(v, Trow[oo.y]);
+            if (g4 * 4 + 2 < D) v = mul2(v, Trow[oo.z]);
+            if (g4 * 4 + 3 < D) v = mul2(v, Trow[oo.w]);
+        }
+        Vs[(size_t)q * 32 + lane] = v;
+        const float wq = ws[q];
+        f = __ffma2_rn(make_float2(wq, wq), v, f);
+    }
+    Fs[wp * 32 + lane] = f;
+    __syncthreads();
+    f = Fs[lane];
+#pragma unroll
+    for (int t = 1; t < CNW; ++t) f = add2(f, Fs[t * 32 + lane]);
+    if (wp == 0) {
+        if (live0) p.fhat[i0] = (double)f.x;
+        if (live1) p.fhat[i0 + 1] = (double)f.y;
+    }
+    if (!p.want_grad) return;
+    float2 e;
+    e.x = live0 ? (float)(p.escale * (p.yb[i0] - (double)f.x)) : 0.f;
+    e.y = live1 ? (float)(p.escale * (p.yb[i0 + 1] - (double)f.y)) : 0.f;
+
+    // ---- gradw: sum over the CTA's rows of e_i V[q,i]; V[q,i] <- w_q V[q,i] in place for pass 2
+    constexpr int NB = 16;   // q per warp and batch
+    for (int qb = wp; qb < Q; qb += CNW * NB) {
+        float v[NB];
+#pragma unroll
+        for (int j = 0; j < NB; ++j) {
+            const int q = qb + CNW * j;
+            float val = 0.f;
+            if (q < Q) {
+                const float2 vv = Vs[(size_t)q * 32 + lane];
+                val = fmaf(e.x, vv.x, e.y * vv.y);
+                const float wq = ws[q];
+                Vs[(size_t)q * 32 + lane] = mul2(vv, make_float2(wq, wq));
+            }
+            v[j] = val;
+        }
+        // transpose-reduction: after the steps lane L holds the sum over all lanes of v[L % NB]
+#pragma unroll
+        for (int off = NB / 2; off >= 1; off >>= 1) {
+            const bool up = (lane & off) != 0;
+#pragma unroll
+            for (int j = 0; j < off; ++j) {
+                const float keep = up ? v[j + off] : v[j];
+                const float send = up ? v[j] : v[j + off];
+                v[j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+            }
+        }
+#pragma unroll
+        for (int off = NB; off < 32; off <<= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], off);
+        const int q = qb + CNW * (lane % NB);
+        if (lane < NB && q < Q) atomicAdd(&p.gradw[q], (double)v[0]);
+    }
+    __syncthreads();
+
+    // ---- pass 2: E[k][l][i] = e_i * (sum_{q: I[q,k]=l} w_q V[q,i]) / T[k][l][i]
+    const int nlb = rpad / 8;
+    const float sc = *p.escale_img;
+    const float2 *Vrow = Vs + lane;
+    float mx = 0.f;
+    for (int u = wp; u < D * nlb; u += CNW) {
+        const int k = u / nlb, lb = u - k * nlb;
+        float2 out[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int l = lb * 8 + j;
+            const int p0 = __ldg(p.lptr + k * rpad + l), p1 = __ldg(p.lptr + k * rpad + l + 1);
+            float2 val = make_float2(0.f, 0.f);
+            if (p1 > p0) {  // uniform across the CTA
+                float2 sum = make_float2(0.f, 0.f);
+                for (int pp = p0; pp < p1; pp += 4) {
+                    const int4 oo = __ldg(reinterpret_cast<const int4 *>(p.lists + pp));
+                    sum = add2(sum, add2(add2(Vrow[oo.x], Vrow[oo.y]), add2(Vrow[oo.z], Vrow[oo.w])));
+                }
+                const float2 t = Trow[(k * r + l) * 32];
+                if (t.x != 0.f && t.y != 0.f) {
+                    val.x = e.x * __fdividef(sum.x, t.x);
+                    val.y = e.y * __fdividef(sum.y, t.y);
+                } else {  // exact zero factor: explicit leave-one-out products
+                    float2 acc = make_float2(0.f, 0.f);
+                    for (int pp = p0; pp < p1; ++pp) {
+                        const int q = __ldg(p.lists + pp) >> 5;
+                        if (q >= Q) continue;
+                        float2 v = make_float2(ws[q], ws[q]);
+                        for (int kk = 0; kk < D; ++kk)
+                            if (kk != k) v = mul2(v, Trow[__ldg(p.off1 + (size_t)q * p.DP + kk)]);
+                        acc = add2(acc, v);
+                    }
+                    val.x = live0 ? (t.x != 0.f ? e.x * __fdividef(sum.x, t.x) : e.x * acc.x) : 0.f;
+                    val.y = live1 ? (t.y != 0.f ? e.y * __fdividef(sum.y, t.y) : e.y * acc.y) : 0.f;
+                }
+            }
+            out[j] = val;
+        }
+        // fp16 hi|lo operand image for the backward MMA (tc_layout.cuh); the power-of-two scale comes from the
+        // previous step's max|E| and keeps the entries in fp16's normal range.  Rows i0 and i0+1 are adjacent
+        // 16-byte rows of the same core matrix: one 32-byte store each for hi and lo.
+        __align__(16) __half hi[16], lo[16];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            mx = fmaxf(mx, fmaxf(fabsf(out[j].x), fabsf(out[j].y)));
+            const float v0 = out[j].x * sc, v1 = out[j].y * sc;
+            const __half h0 = __float2half_rn(v0), h1 = __float2half_rn(v1);
+            hi[j] = h0;
+            hi[8 + j] = h1;
+            lo[j] = __float2half_rn(v0 - __half2float(h0));
+            lo[8 + j] = __float2half_rn(v1 - __half2float(h1));
+        }
+        __half *base = p.Eimg + gptb_eimg_offset(k, i0, p.mpad, rpad);
+        uint4 *dh = reinterpret_cast<uint4 *>(base + (size_t)lb * 64);
+        uint4 *dl = reinterpret_cast<uint4 *>(base + (size_t)(nlb + lb) * 64);
+        dh[0] = reinterpret_cast<const uint4 *>(hi)[0];
+        dh[1] = reinterpret_cast<const uint4 *>(hi)[1];
+        dl[0] = reinterpret_cast<const uint4 *>(lo)[0];
+        dl[1] = reinterpret_cast<const uint4 *>(lo)[1];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0 && mx > 0.f) atomicMax(reinterpret_cast<int *>(p.emax_out), __float_as_int(mx));
+}
+
+}  // namespace
+
+// Offset tables of the kernel above, from the 0-based core index table Iz[D][Q] (host).
+int gptb_contract_tc_build_tables(gptb_handle *h, const int32_t *Iz) {
+    const gptb_config &c = h->cfg;
+    const int DP = (c.D + 3) & ~3;
+    std::vector<int32_t> off1((size_t)c.Q * DP, 0);
+    for (int q = 0; q < c.Q; ++q)
+        for (int k = 0; k < c.D; ++k) off1[(size_t)q * DP + k] = (k * c.r + Iz[(size_t)k * c.Q + q]) * 32;
+    // CSR over (k,l): the q with I[q,k] = l in increasing q (the order computeA's findin visits them, :267),
+    // every list padded to a multiple of four entries that address the all-zero row q = Q
+    const size_t ngrp = (size_t)c.D * h->rpad;
+    std::vector<int32_t> cnt(ngrp, 0), ptr(ngrp + 1, 0);
+    for (int k = 0; k < c.D; ++k)
+        for (int q = 0; q < c.Q; ++q) cnt[(size_t)k * h->rpad + Iz[(size_t)k * c.Q + q]]++;
+    for (size_t g = 0; g < ngrp; ++g) ptr[g + 1] = ptr[g] + ((cnt[g] + 3) & ~3);
+    std::vector<int32_t> lists((size_t)ptr[ngrp] + 4, c.Q * 32);
+    {
+        std::vector<int32_t> fill(ptr.begin(), ptr.end() - 1);
+        for (int k = 0; k < c.D; ++k)
+            for (int q = 0; q < c.Q; ++q) lists[fill[(size_t)k * h->rpad + Iz[(size_t)k * c.Q + q]]++] = q * 32;
+    }
+    if (h->ct_off1) cudaFree(h->ct_off1);
+    if (h->ct_lptr) cudaFree(h->ct_lptr);
+    if (h->ct_lists) cudaFree(h->ct_lists);
+    h->ct_off1 = h->ct_lptr = h->ct_lists = nullptr;
+    GPTB_CUDA_OK(h, cudaMalloc((void **)&h->ct_off1, off1.size() * sizeof(int32_t)));
+    GPTB_CUDA_OK(h, cudaMalloc((void **)&h->ct_lptr, ptr.size() * sizeof(int32_t)));
+    GPTB_CUDA_OK(h, cudaMalloc((void **)&h->ct_lists, lists.size() * sizeof(int32_t)));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->ct_off1, off1.data(), off1.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->ct_lptr, ptr.data(), ptr.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->ct_lists, lists.data(), lists.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    return GPTB_OK;
+}
+
+size_t gptb_contract_tc_smem(const gptb_handle *h) {
+    const gptb_config &c = h->cfg;
+    return ((size_t)c.D * c.r * 32 + (size_t)(c.Q + 1) * 32 + (size_t)CNW * 32) * sizeof(float2) +
+           (size_t)((c.Q + 3) & ~3) * sizeof(float) + 64;
+}
+
+// Returns GPTB_ERR_UNSUPPORTED (without an error message) when the shape does not fit; the caller then
+// uses the generic kernel of contract.cu.
+int gptb_launch_contract_tc(gptb_handle *h, const float *T, const double *w, const double *yb, int64_t bs, int64_t mpad,
+                            double escale, bool want_grad, double *fhat, double *gradw, void *Eimg) {
+    const gptb_config &c = h->cfg;
+    const size_t smem = gptb_contract_tc_smem(h);
+    if (smem > 227 * 1024 || c.D > 16 || !h->ct_off1) return GPTB_ERR_UNSUPPORTED;
+    ContractTcParams p;
+    p.T = T;
+    p.w = w;
+    p.off1 = h->ct_off1;
+    p.lptr = h->ct_lptr;
+    p.lists = h->ct_lists;
+    p.yb = yb;
+    p.fhat = fhat;
+    p.gradw = gradw;
+    p.Eimg = (__half *)Eimg;
+    p.escale_img = h->tc_state + 1;
+    p.emax_out = h->tc_state + 0;
+    p.bs = bs;
+    p.mpad = mpad;
+    p.escale = escale;
+    p.DP = (c.D + 3) & ~3; p.r = c.r; p.rpad = h->rpad; p.Q = c.Q;
+    p.want_grad = want_grad ? 1 : 0;
+    const int64_t mext = (bs + 127) / 128 * 128;  // rows beyond bs inside the last 128-tile are dead (zeros)
+    dim3 grid((unsigned)(mext / CRB));
+#define GPTB_CONTRACT_CASE(DT)                                                                              \
+    case DT: {                                                                                              \
+        auto kfn = contract_tc_kernel<DT>;                                                                  \
+        GPTB_CUDA_OK(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        kfn<<<grid, CT_THREADS, smem, h->stream>>>(p);                                                      \
+    } break;
+    switch (c.D) {
+        GPTB_CONTRACT_CASE(1) GPTB_CONTRACT_CASE(2) GPTB_CONTRACT_CASE(3) GPTB_CONTRACT_CASE(4)
+        GPTB_CONTRACT_CASE(5) GPTB_CONTRACT_CASE(6) GPTB_CONTRACT_CASE(7) GPTB_CONTRACT_CASE(8)
+        GPTB_CONTRACT_CASE(9) GPTB_CONTRACT_CASE(10) GPTB_CONTRACT_CASE(11) GPTB_CONTRACT_CASE(12)
+        GPTB_CONTRACT_CASE(13) GPTB_CONTRACT_CASE(14) GPTB_CONTRACT_CASE(15) GPTB_CONTRACT_CASE(16)
+        default: return GPTB_ERR_UNSUPPORTED;
+    }
+#undef GPTB_CONTRACT_CASE
+    h->launches++;
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    return GPTB_OK;
+}

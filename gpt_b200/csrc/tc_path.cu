@@ -58,14 +58,16 @@ struct Bars {
 
 __device__ __forceinline__ uint32_t h2_u32(__half2 h) { return *reinterpret_cast<uint32_t *>(&h); }
 
-// hi/lo fp16 split of two fp32 values, packed (first value in the low half).
+// hi/lo fp16 split of two fp32 values, packed (first value in the low half).  The generators are bound by
+// instruction issue as much as by MUFU, so everything that can is done two features per instruction
+// (FFMA2 / F2FP pack): per feature 0.5 FFMA2 + FMUL + MUFU + 0.5 F2FP + HADD2.F32 + 0.5 FFMA2 + 0.5 F2FP.
 template <bool THREE>
-__device__ __forceinline__ void split_pack(float a0, float a1, uint32_t &hi, uint32_t &lo) {
-    __half2 h = __floats2half2_rn(a0, a1);
+__device__ __forceinline__ void split_pack(float2 a, uint32_t &hi, uint32_t &lo) {
+    const __half2 h = __float22half2_rn(a);
     hi = h2_u32(h);
     if (THREE) {
-        float2 hf = __half22float2(h);
-        lo = h2_u32(__floats2half2_rn(a0 - hf.x, a1 - hf.y));
+        const float2 l = __ffma2_rn(__half22float2(h), make_float2(-1.f, -1.f), a);
+        lo = h2_u32(__float22half2_rn(l));
     }
 }
 
@@ -101,8 +103,10 @@ struct FwdParams {
 };
 
 // 64 features of one row -> the hi / lo words of one A stage.
+// cos features: table entry p (float4) = (zt[2p], zt[2p+1], b[2p], b[2p+1]);  sin/cos: entry p (float2) = (zt[p], -).
 template <bool THREE>
 __device__ __forceinline__ void gen_fwd_chunk(const float2 *zb64, float x, bool sincos, uint32_t st_addr) {
+    const float2 x2 = make_float2(x, x);
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
         uint32_t hi[16], lo[16];
@@ -111,14 +115,15 @@ __device__ __forceinline__ void gen_fwd_chunk(const float2 *zb64, float x, bool 
 #pragma unroll
             for (int c = 0; c < 16; ++c) {
                 const float4 v = zb[c];
-                split_pack<THREE>(__cosf(fmaf(x, v.x, v.y)), __cosf(fmaf(x, v.z, v.w)), hi[c], lo[c]);
+                const float2 arg = __ffma2_rn(x2, make_float2(v.x, v.y), make_float2(v.z, v.w));
+                split_pack<THREE>(make_float2(__cosf(arg.x), __cosf(arg.y)), hi[c], lo[c]);
             }
         } else {
             const float2 *zb = zb64 + half * 16;   // pair p of this chunk -> features 2p (sin), 2p+1 (cos)
 #pragma unroll
             for (int c = 0; c < 16; ++c) {
                 const float a = x * zb[c].x;
-                split_pack<THREE>(__sinf(a), __cosf(a), hi[c], lo[c]);
+                split_pack<THREE>(make_float2(__sinf(a), __cosf(a)), hi[c], lo[c]);
             }
         }
         tmem_st16(st_addr + half * 16, hi);
@@ -146,7 +151,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
     const int u1 = (int)((int64_t)nunits * (blockIdx.x + 1) / gridDim.x);
 
     if (tid == 0) {
-        for (int s = 0; s < NSTA_MAX; ++s) { mbar_init(&bars->a_full[s], 128); mbar_init(&bars->a_empty[s], 1); }
+        for (int s = 0; s < NSTA_MAX; ++s) { mbar_init(&bars->a_full[s], 4); mbar_init(&bars->a_empty[s], 1); }
         for (int s = 0; s < 2; ++s) { mbar_init(&bars->acc_full[s], 1); mbar_init(&bars->acc_empty[s], 128); }
         mbar_init(&bars->u_full, 1);
         mbar_init(&bars->u_empty, 1);
@@ -198,7 +203,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
             }
             wait_st();
             fence_before_sync();
-            mbar_arrive(&bars->a_full[sa]);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars->a_full[sa]);   // one arrival per warp: 32 lanes on one mbarrier serialise
+
             ch += NGEN;
             sa += NGEN;
             if (sa >= NSTA) { sa -= NSTA; pa ^= 1; }
@@ -349,7 +356,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
     const uint32_t n_as = n_it * JG;
 
     if (tid == 0) {
-        for (int s = 0; s < NSTA_MAX; ++s) { mbar_init(&bars->a_full[s], 128); mbar_init(&bars->a_empty[s], 1); }
+        for (int s = 0; s < NSTA_MAX; ++s) { mbar_init(&bars->a_full[s], 4); mbar_init(&bars->a_empty[s], 1); }
         for (int s = 0; s < NSTB; ++s) { mbar_init(&bars->b_full[s], 1); mbar_init(&bars->b_empty[s], 1); }
         mbar_init(&bars->acc_full[0], 1);
         mbar_init(&bars->acc_empty[0], 128);
@@ -386,6 +393,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
                 zt = p.ZtF[(size_t)k * p.npad + (j >> 1)];
                 bb = (j & 1) ? 1.5707963267948966f : 0.f;
             }
+            const float2 zt2 = make_float2(zt, zt), bb2 = make_float2(bb, bb);
             const int sb = lit % NSTB;
             mbar_wait(&bars->a_empty[sa], pa);
             fence_after_sync();
@@ -398,23 +406,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
 #pragma unroll
                 for (int c = 0; c < 16; c += 2) {
                     const float4 xx = xr[half * 8 + c / 2];
-                    float a0, a1, a2, a3;
+                    const float2 g0 = __ffma2_rn(make_float2(xx.x, xx.y), zt2, bb2);
+                    const float2 g1 = __ffma2_rn(make_float2(xx.z, xx.w), zt2, bb2);
                     if (!p.sincos) {
-                        a0 = __cosf(fmaf(xx.x, zt, bb)); a1 = __cosf(fmaf(xx.y, zt, bb));
-                        a2 = __cosf(fmaf(xx.z, zt, bb)); a3 = __cosf(fmaf(xx.w, zt, bb));
+                        split_pack<THREE>(make_float2(__cosf(g0.x), __cosf(g0.y)), hi[c], lo[c]);
+                        split_pack<THREE>(make_float2(__cosf(g1.x), __cosf(g1.y)), hi[c + 1], lo[c + 1]);
                     } else {
-                        a0 = __sinf(fmaf(xx.x, zt, bb)); a1 = __sinf(fmaf(xx.y, zt, bb));
-                        a2 = __sinf(fmaf(xx.z, zt, bb)); a3 = __sinf(fmaf(xx.w, zt, bb));
+                        split_pack<THREE>(make_float2(__sinf(g0.x), __sinf(g0.y)), hi[c], lo[c]);
+                        split_pack<THREE>(make_float2(__sinf(g1.x), __sinf(g1.y)), hi[c + 1], lo[c + 1]);
                     }
-                    split_pack<THREE>(a0, a1, hi[c], lo[c]);
-                    split_pack<THREE>(a2, a3, hi[c + 1], lo[c + 1]);
                 }
                 tmem_st16(st_addr + half * 16, hi);
                 if (THREE) tmem_st16(st_addr + 32 + half * 16, lo);
             }
             wait_st();
             fence_before_sync();
-            mbar_arrive(&bars->a_full[sa]);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars->a_full[sa]);   // one arrival per warp: 32 lanes on one mbarrier serialise
+
             jbl += NGEN;
             while (jbl >= JG) { jbl -= JG; ++lit; if (++ch == NCH) { ch = 0; ++grp; } }
             sa += NGEN;
@@ -566,9 +575,17 @@ __global__ void pack_U_kernel(const double *__restrict__ U /*[D][r][n]*/, int D,
     }
 }
 
-__global__ void interleave_zb_kernel(const float *zt, const float *b, size_t n, float2 *out) {
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-        out[i] = make_float2(zt[i], b[i]);
+// (zt, b) table of the forward generators: cos features -> float4 per feature pair (zt0, zt1, b0, b1);
+// sin/cos features -> float2 (zt[p], b[p]) per frequency p.
+__global__ void interleave_zb_kernel(const float *zt, const float *b, size_t n, int pair_layout, float2 *out) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        if (!pair_layout) {
+            out[i] = make_float2(zt[i], b[i]);
+        } else {
+            const size_t pr = i >> 1;
+            out[i] = (i & 1) ? make_float2(b[2 * pr], b[2 * pr + 1]) : make_float2(zt[2 * pr], zt[2 * pr + 1]);
+        }
+    }
 }
 
 int probe_exp() {
@@ -617,7 +634,8 @@ int gptb_tc_update_escale(gptb_handle *h) {
 int gptb_tc_prepare_features(gptb_handle *h) {
     const size_t cnt = (size_t)h->cfg.D * h->npad;
     if (!h->ZbF) GPTB_CUDA_OK(h, cudaMalloc((void **)&h->ZbF, cnt * sizeof(float2)));
-    interleave_zb_kernel<<<64, 256, 0, h->stream>>>(h->ZtF, h->bF, cnt, (float2 *)h->ZbF);
+    interleave_zb_kernel<<<64, 256, 0, h->stream>>>(h->ZtF, h->bF, cnt, h->cfg.feature_kind == GPTB_FEAT_COS ? 1 : 0,
+                                                    (float2 *)h->ZbF);
     h->launches++;
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;

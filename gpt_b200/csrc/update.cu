@@ -572,6 +572,194 @@ k_reduce_only(const double *__restrict__ U, const double *__restrict__ G, double
     }
 }
 
+
+// ================================================================================================
+// Fast path of the sampler's update (r <= 32): noise -> prepare -> small2 -> apply2.
+// ================================================================================================
+
+// Production-mode noise of one step, two draws per Philox block (same counters as noise_at()).
+// grid.y = D + 1; row D is the w noise.
+__global__ void k_noise(double *__restrict__ noise_w, double *__restrict__ noise_U, int Q, size_t per_k, int D,
+                        uint64_t key, uint64_t step) {
+    const int k = blockIdx.y;
+    const size_t cnt = k == D ? (size_t)Q : per_k;
+    const uint64_t stream = k == D ? GPTB_STREAM_NOISE_W : (GPTB_STREAM_NOISE_U | ((uint64_t)k << 40));
+    double *out = k == D ? noise_w : noise_U + (size_t)k * per_k;
+    for (size_t pe = blockIdx.x * (size_t)blockDim.x + threadIdx.x; 2 * pe < cnt; pe += (size_t)gridDim.x * blockDim.x) {
+        double a, b;
+        philox_normal2(key, stream | pe, step, &a, &b);
+        out[2 * pe] = a;
+        if (2 * pe + 1 < cnt) out[2 * pe + 1] = b;
+    }
+}
+
+// C[m x n] = A[m x kk] * B[kk x n]; col-major, dense leading dimensions, shared memory.
+__device__ void smm_s(const double *__restrict__ A, const double *__restrict__ B, double *__restrict__ C, int m, int kk,
+                      int n) {
+    for (int t = threadIdx.x; t < m * n; t += blockDim.x) {
+        const int i = t % m, j = t / m;
+        double s0 = 0.0, s1 = 0.0;
+        int pp = 0;
+        for (; pp + 1 < kk; pp += 2) {
+            s0 = fma(A[i + (size_t)m * pp], B[pp + (size_t)kk * j], s0);
+            s1 = fma(A[i + (size_t)m * (pp + 1)], B[pp + 1 + (size_t)kk * j], s1);
+        }
+        if (pp < kk) s0 = fma(A[i + (size_t)m * pp], B[pp + (size_t)kk * j], s0);
+        C[t] = s0 + s1;
+    }
+    __syncthreads();
+}
+
+// P2' : like k_small, with the r x r algebra in shared memory and the column norms of Unew = U C1 + G C2
+// taken from the r x r Gram matrices, so that C1, C2 leave already divided by the norms (:30-35) and the
+// apply kernel writes the final U in one pass.  Requires the shared-memory expm (2r <= 64).
+__global__ void __launch_bounds__(1024)
+k_small2(double *__restrict__ small, size_t small_stride, int r, double t, int32_t *nan_flag) {
+    extern __shared__ double sm[];
+    __shared__ int bad;
+    double *sk = small + (size_t)blockIdx.x * small_stride;
+    SmallLayout L(r);
+    const int r2 = 2 * r, rr = r * r, tid = threadIdx.x, nt = blockDim.x;
+    if (tid == 0) bad = 0;
+    double *S1 = sm, *S1t = sm + rr, *UU = sm + 2 * rr, *GG = sm + 3 * rr, *sym = sm + 4 * rr, *t1 = sm + 5 * rr,
+           *t2 = sm + 6 * rr, *t3 = sm + 7 * rr;
+    for (int i = tid; i < rr; i += nt) {
+        const int a = i % r, b = i / r;
+        const double s = sk[L.S1 + i];
+        S1[i] = s;
+        S1t[b + r * a] = s;
+        UU[i] = sk[L.UU + i];
+        GG[i] = sk[L.GG + i];
+    }
+    __syncthreads();
+    for (int i = tid; i < rr; i += nt) sym[i] = (S1[i] + S1t[i]) / 2;
+    __syncthreads();
+    smm_s(UU, sym, t1, r, r, r);      // UU*sym
+    smm_s(sym, t1, t2, r, r, r);      // sym*UU*sym
+    smm_s(S1t, sym, t3, r, r, r);     // S1'*sym  (sym*S1 is its transpose)
+    double *Tm = sk + L.Tm, *X = sk + L.X;
+    for (int i = tid; i < r2 * r2; i += nt) {
+        const int a = i % r2, b = i / r2;
+        double v;
+        if (a < r && b < r) v = S1[a + r * b] - t1[a + r * b];                                   // A = U'M
+        else if (a < r) {                                                                          // -M'M
+            const int bb = b - r;
+            v = -(GG[a + r * bb] - t3[a + r * bb] - t3[bb + r * a] + t2[a + r * bb]);
+        } else if (b < r) v = (a - r == b) ? 1.0 : 0.0;
+        else v = S1[(a - r) + r * (b - r)] - t1[(a - r) + r * (b - r)];
+        Tm[i] = t * v;
+    }
+    for (int i = tid; i < rr; i += nt) X[i] = -t * (S1[i] - t1[i]);
+    __syncthreads();
+    sexpm(Tm, r2, sm, &bad);
+    if (!bad) {
+        int local = 0;                 // "if sum(isnan(E))>0" (:24)
+        for (int i = tid; i < r2 * r2; i += nt)
+            if (Tm[i] != Tm[i]) local = 1;
+        if (local) bad = 1;
+    }
+    __syncthreads();
+    if (!bad) sexpm(X, r, sm, &bad);
+    __syncthreads();
+    if (bad) {
+        if (tid == 0) atomicExch(nan_flag, 1);
+        return;
+    }
+    // W = E[:,1:r] * expm(-tA); C1 = W1 - sym*W2, C2 = W2
+    double *E1 = sm, *Xs = sm + r2 * r, *W = Xs + rr, *W1 = W + r2 * r, *W2 = W1 + rr, *C1 = W2 + rr, *symb = C1 + rr,
+           *P1 = symb + rr, *P2 = P1 + rr, *P3 = P2 + rr, *M1 = P3 + rr, *M2 = M1 + rr, *M3 = M2 + rr, *cn = M3 + rr;
+    for (int i = tid; i < r2 * r; i += nt) E1[i] = Tm[i];   // first r columns of E (col-major)
+    for (int i = tid; i < rr; i += nt) {
+        Xs[i] = X[i];
+        const int a = i % r, b = i / r;
+        const double s = sk[L.S1 + i];
+        M2[i] = s;
+        symb[i] = (s + sk[L.S1 + b + r * a]) / 2;
+        M1[i] = sk[L.UU + i];
+        M3[i] = sk[L.GG + i];
+    }
+    __syncthreads();
+    smm_s(E1, Xs, W, r2, r, r);
+    for (int i = tid; i < rr; i += nt) {
+        const int a = i % r, b = i / r;
+        W1[i] = W[a + r2 * b];
+        W2[i] = W[(a + r) + r2 * b];
+    }
+    __syncthreads();
+    smm_s(symb, W2, P1, r, r, r);
+    for (int i = tid; i < rr; i += nt) C1[i] = W1[i] - P1[i];
+    __syncthreads();
+    // squared column norms of U C1 + G C2:  diag(C1'UU C1 + 2 C1'S1 C2 + C2'GG C2)
+    smm_s(M1, C1, P1, r, r, r);
+    smm_s(M2, W2, P2, r, r, r);
+    smm_s(M3, W2, P3, r, r, r);
+    for (int l = tid; l < r; l += nt) {
+        double s = 0.0;
+        for (int a = 0; a < r; ++a) {
+            const int i = a + r * l;
+            s += C1[i] * (P1[i] + 2.0 * P2[i]) + W2[i] * P3[i];
+        }
+        cn[l] = 1.0 / sqrt(s);
+    }
+    __syncthreads();
+    for (int i = tid; i < rr; i += nt) {
+        const int l = i / r;
+        sk[L.C1 + i] = C1[i] * cn[l];
+        sk[L.C2 + i] = W2[i] * cn[l];
+    }
+}
+
+// P3' : U <- U C1 + G C2 (C1, C2 pre-divided by the column norms), plus the fp16 hi|lo operand image of the new U
+// with the fixed scale 2^8 (|U| <= 1 once the columns are unit vectors).
+constexpr float UIMG_FIXED_SCALE = 256.f;
+__global__ void __launch_bounds__(UP_THREADS)
+k_apply2(double *__restrict__ U, const double *__restrict__ G, const double *__restrict__ small, size_t small_stride, int n,
+         int r, const int32_t *__restrict__ nan_flag, __half *__restrict__ Uimg, int npad, int rpad,
+         float *__restrict__ uscale_out) {
+    if (*nan_flag) return;
+    extern __shared__ double sm[];
+    const int k = blockIdx.y, j0 = blockIdx.x * UP_ROWS, tid = threadIdx.x;
+    const int rows = min(UP_ROWS, n - j0);
+    const double *sk = small + (size_t)k * small_stride;
+    SmallLayout L(r);
+    double *Us = sm, *Gs = Us + (size_t)UP_ROWS * r, *C1 = Gs + (size_t)UP_ROWS * r, *C2 = C1 + r * r;
+    double *Uk = U + (size_t)k * r * n;
+    const double *Gk = G + (size_t)k * r * n;
+    if (uscale_out && blockIdx.x == 0 && k == 0 && tid == 0) {
+        uscale_out[0] = UIMG_FIXED_SCALE;
+        uscale_out[1] = 1.f / UIMG_FIXED_SCALE;
+    }
+    for (int t = tid; t < UP_ROWS * r; t += UP_THREADS) {
+        const int jj = t % UP_ROWS, l = t / UP_ROWS;
+        const bool ok = jj < rows;
+        Us[t] = ok ? Uk[(size_t)l * n + j0 + jj] : 0.0;
+        Gs[t] = ok ? Gk[(size_t)l * n + j0 + jj] : 0.0;
+    }
+    for (int t = tid; t < r * r; t += UP_THREADS) {
+        C1[t] = sk[L.C1 + t];
+        C2[t] = sk[L.C2 + t];
+    }
+    __syncthreads();
+    for (int t = tid; t < UP_ROWS * r; t += UP_THREADS) {
+        const int jj = t % UP_ROWS, l = t / UP_ROWS;
+        double s0 = 0.0, s1 = 0.0;
+        for (int a = 0; a < r; ++a) {
+            s0 = fma(Us[(size_t)a * UP_ROWS + jj], C1[a + r * l], s0);
+            s1 = fma(Gs[(size_t)a * UP_ROWS + jj], C2[a + r * l], s1);
+        }
+        const double s = s0 + s1;
+        if (jj < rows) {
+            Uk[(size_t)l * n + j0 + jj] = s;
+            if (Uimg) {
+                const float v = (float)s * UIMG_FIXED_SCALE;
+                const __half hh = __float2half_rn(v);
+                Uimg[gptb_uimg_offset(k, j0 + jj, l, npad, rpad)] = hh;
+                Uimg[gptb_uimg_offset(k, j0 + jj, rpad + l, npad, rpad)] = __float2half_rn(v - __half2float(hh));
+            }
+        }
+    }
+}
+
 }  // namespace
 
 size_t gptb_update_small_stride(int r) { return SmallLayout(r).total; }
@@ -584,6 +772,8 @@ static void optin_smem() {
     cudaFuncSetAttribute(k_apply, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(k_reduce_only, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(k_small, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(k_small2, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(k_apply2, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     done = true;
 }
 
@@ -604,28 +794,48 @@ int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, cons
                        const double *noise_U, uint64_t step) {
     const gptb_config &c = h->cfg;
     const int nb = (c.n + UP_ROWS - 1) / UP_ROWS;
-    const bool stiefel = flags & GPTB_FLAG_STIEFEL;
+    const bool stiefel = flags & GPTB_FLAG_STIEFEL, langevin = flags & GPTB_FLAG_LANGEVIN;
+    const size_t per_k = (size_t)c.r * c.n;
     optin_smem();
     if (stiefel) GPTB_TRY(zero_small(h, h->small, h->small_stride, c.D, c.r));
+    if (langevin && (!noise_w || !noise_U)) {
+        // production mode: the step's draws are generated up front by a grid-wide kernel (two per Philox block)
+        if (!h->gen_noise_w) GPTB_CUDA_OK(h, cudaMalloc((void **)&h->gen_noise_w, sizeof(double) * (c.Q + 2)));
+        if (!h->gen_noise_U) GPTB_CUDA_OK(h, cudaMalloc((void **)&h->gen_noise_U, sizeof(double) * (per_k * c.D + 2)));
+        const int gx = (int)std::min<size_t>((per_k / 2 + 255) / 256, 64);
+        k_noise<<<dim3(gx, c.D + 1), 256, 0, h->stream>>>(h->gen_noise_w, h->gen_noise_U, c.Q, per_k, c.D, c.seed, step);
+        h->launches++;
+        if (!noise_w) noise_w = h->gen_noise_w;
+        if (!noise_U) noise_U = h->gen_noise_U;
+    }
     size_t sm1 = 2 * (size_t)UP_ROWS * c.r * sizeof(double);
     k_prepare<<<dim3(nb, c.D + 1), UP_THREADS, sm1, h->stream>>>(h->grad, h->w, h->U, h->G, h->small, h->small_stride,
                                                                 c.n, c.r, c.D, c.Q, epsw, epsU, flags, noise_w,
                                                                 noise_U, c.seed, step, 1);
     h->launches++;
+    h->shadows_valid = false;
     if (stiefel) {
-        {
-            size_t sb = small_smem_bytes(c.r);
+        const size_t sb = small_smem_bytes(c.r);
+        if (sb && c.r <= 32) {
+            k_small2<<<c.D, 1024, sb, h->stream>>>(h->small, h->small_stride, c.r, sqrt(epsU), h->nan_flag);
+            const bool tc = gptb_is_tc(h);
+            size_t sm3 = (2 * (size_t)UP_ROWS * c.r + 2 * (size_t)c.r * c.r) * sizeof(double);
+            k_apply2<<<dim3(nb, c.D), UP_THREADS, sm3, h->stream>>>(h->U, h->G, h->small, h->small_stride, c.n, c.r,
+                                                                   h->nan_flag, tc ? (__half *)h->Uimg : nullptr, h->npad,
+                                                                   h->rpad, tc ? h->tc_state + 4 : nullptr);
+            h->launches += 2;
+            if (tc) h->shadows_valid = true;   // k_apply2 refreshed the operand image
+        } else {
             k_small<<<c.D, 1024, sb, h->stream>>>(h->small, h->small_stride, c.r, sqrt(epsU), 1, h->nan_flag, sb ? 1 : 0);
+            size_t sm3 = (2 * (size_t)UP_ROWS * c.r + 2 * (size_t)c.r * c.r + c.r) * sizeof(double);
+            k_apply<<<dim3(nb, c.D), UP_THREADS, sm3, h->stream>>>(h->U, h->G, h->small, h->small_stride, c.n, c.r,
+                                                                  h->nan_flag);
+            int fb = (int)std::min<size_t>(((size_t)c.r * c.n + 255) / 256, 64);
+            k_finish<<<dim3(fb, c.D), 256, 0, h->stream>>>(h->U, h->G, h->small, h->small_stride, c.n, c.r, h->nan_flag);
+            h->launches += 3;
         }
-        size_t sm3 = (2 * (size_t)UP_ROWS * c.r + 2 * (size_t)c.r * c.r + c.r) * sizeof(double);
-        k_apply<<<dim3(nb, c.D), UP_THREADS, sm3, h->stream>>>(h->U, h->G, h->small, h->small_stride, c.n, c.r,
-                                                              h->nan_flag);
-        int fb = (int)std::min<size_t>(((size_t)c.r * c.n + 255) / 256, 64);
-        k_finish<<<dim3(fb, c.D), 256, 0, h->stream>>>(h->U, h->G, h->small, h->small_stride, c.n, c.r, h->nan_flag);
-        h->launches += 3;
     }
     GPTB_CUDA_OK(h, cudaGetLastError());
-    h->shadows_valid = false;
     return GPTB_OK;
 }
 
