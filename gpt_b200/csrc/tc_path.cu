@@ -521,16 +521,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
 }
 
 // gradU[k][l][j] (FP64, Julia order) += gradF[k][j][l]; gradF is cleared for the next step.
-__global__ void finalize_grad_kernel(float *__restrict__ gradF, double *__restrict__ gradU, int D, int n, int npad, int r,
-                                     int rpad) {
-    const size_t total = (size_t)D * npad * rpad;
-    for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
-        const int l = (int)(t % rpad);
-        const int j = (int)((t / rpad) % npad);
-        const int k = (int)(t / ((size_t)rpad * npad));
-        const float v = gradF[t];
-        gradF[t] = 0.f;
-        if (l < r && j < n) gradU[((size_t)k * r + l) * n + j] += (double)v;
+// One CTA per (k, 32-feature block): coalesced reads along l, transposed through shared memory, coalesced
+// writes along j.
+__global__ void __launch_bounds__(256) finalize_grad_kernel(float *__restrict__ gradF, double *__restrict__ gradU, int n,
+                                                            int npad, int r, int rpad) {
+    __shared__ float tile[32][65];
+    const int k = blockIdx.y, j0 = blockIdx.x * 32;
+    float *src = gradF + ((size_t)k * npad + j0) * rpad;
+    for (int t = threadIdx.x; t < 32 * rpad; t += 256) {
+        const int jj = t / rpad, l = t - jj * rpad;
+        tile[jj][l] = src[t];
+        src[t] = 0.f;
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < 32 * r; t += 256) {
+        const int l = t >> 5, jj = t & 31;
+        if (j0 + jj < n) gradU[((size_t)k * r + l) * n + j0 + jj] += (double)tile[jj][l];
     }
 }
 
@@ -748,8 +754,7 @@ int gptb_launch_bwd_tc(gptb_handle *h, const float *XbF, const void *Eimg, int64
         default: st = launch_bwd_r<64>(h, p, grid, smem); break;
     }
     GPTB_TRY(st);
-    finalize_grad_kernel<<<(int)std::min<size_t>((gf + 255) / 256, (size_t)h->sm_count * 4), 256, 0, h->stream>>>(
-        h->gradF, gradU, c.D, c.n, h->npad, c.r, h->rpad);
+    finalize_grad_kernel<<<dim3(h->npad / 32, c.D), 256, 0, h->stream>>>(h->gradF, gradU, c.n, h->npad, c.r, h->rpad);
     h->launches += 2;
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;

@@ -84,7 +84,8 @@ k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ 
     const double *gU = grad + Q + (size_t)k * r * n;
     double *Uk = U + (size_t)k * r * n, *Gk = G + (size_t)k * r * n;
     const double sqU = sqrt(epsU);
-    double *Us = sm, *Gs = sm + (size_t)UP_ROWS * r;  // [l][jj]
+    const int ldt = r + 1;                             // tile layout [jj][l], padded: the Gram loops walk l across lanes
+    double *Us = sm, *Gs = sm + (size_t)UP_ROWS * ldt;
     for (int t = tid; t < UP_ROWS * r; t += UP_THREADS) {
         int jj = t % UP_ROWS, l = t / UP_ROWS, j = j0 + jj;
         double u = 0.0, g = 0.0;
@@ -103,8 +104,8 @@ k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ 
                 Uk[e] = u + epsU * (gr - n * u) / 2 + sqU * z;  // :426 / :437
             }
         }
-        Us[(size_t)l * UP_ROWS + jj] = u;
-        Gs[(size_t)l * UP_ROWS + jj] = g;
+        Us[(size_t)jj * ldt + l] = u;
+        Gs[(size_t)jj * ldt + l] = g;
     }
     if (!stiefel) return;
     __syncthreads();
@@ -112,13 +113,14 @@ k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ 
     SmallLayout L(r);
     for (int t = tid; t < r * r; t += UP_THREADS) {
         int a = t % r, b = t / r;
-        const double *ua = Us + (size_t)a * UP_ROWS, *ub = Us + (size_t)b * UP_ROWS;
-        const double *ga = Gs + (size_t)a * UP_ROWS, *gb = Gs + (size_t)b * UP_ROWS;
         double s1 = 0.0, gg = 0.0, uu = 0.0;
+#pragma unroll 4
         for (int jj = 0; jj < UP_ROWS; ++jj) {
-            s1 = fma(ua[jj], gb[jj], s1);
-            gg = fma(ga[jj], gb[jj], gg);
-            uu = fma(ua[jj], ub[jj], uu);
+            const double ua = Us[(size_t)jj * ldt + a], ub = Us[(size_t)jj * ldt + b];
+            const double ga = Gs[(size_t)jj * ldt + a], gb = Gs[(size_t)jj * ldt + b];
+            s1 = fma(ua, gb, s1);
+            gg = fma(ga, gb, gg);
+            uu = fma(ua, ub, uu);
         }
         atomicAdd(&sk[L.S1 + a + (size_t)r * b], s1);
         atomicAdd(&sk[L.GG + a + (size_t)r * b], gg);
@@ -593,36 +595,170 @@ __global__ void k_noise(double *__restrict__ noise_w, double *__restrict__ noise
     }
 }
 
-// C[m x n] = A[m x kk] * B[kk x n]; col-major, dense leading dimensions, shared memory.
-__device__ void smm_s(const double *__restrict__ A, const double *__restrict__ B, double *__restrict__ C, int m, int kk,
-                      int n) {
+// C[m x n] = A[m x kk] * B[kk x n]; col-major with leading dimensions lda/ldb/ldc, shared memory.
+__device__ void smm_s(const double *__restrict__ A, int lda, const double *__restrict__ B, int ldb, double *__restrict__ C,
+                      int ldc, int m, int kk, int n) {
     for (int t = threadIdx.x; t < m * n; t += blockDim.x) {
         const int i = t % m, j = t / m;
         double s0 = 0.0, s1 = 0.0;
         int pp = 0;
         for (; pp + 1 < kk; pp += 2) {
-            s0 = fma(A[i + (size_t)m * pp], B[pp + (size_t)kk * j], s0);
-            s1 = fma(A[i + (size_t)m * (pp + 1)], B[pp + 1 + (size_t)kk * j], s1);
+            s0 = fma(A[i + (size_t)lda * pp], B[pp + (size_t)ldb * j], s0);
+            s1 = fma(A[i + (size_t)lda * (pp + 1)], B[pp + 1 + (size_t)ldb * j], s1);
         }
-        if (pp < kk) s0 = fma(A[i + (size_t)m * pp], B[pp + (size_t)kk * j], s0);
-        C[t] = s0 + s1;
+        if (pp < kk) s0 = fma(A[i + (size_t)lda * pp], B[pp + (size_t)ldb * j], s0);
+        C[i + (size_t)ldc * j] = s0 + s1;
     }
     __syncthreads();
 }
 
-// P2' : like k_small, with the r x r algebra in shared memory and the column norms of Unew = U C1 + G C2
-// taken from the r x r Gram matrices, so that C1, C2 leave already divided by the norms (:30-35) and the
-// apply kernel writes the final U in one pass.  Requires the shared-memory expm (2r <= 64).
+// ---- FP64 tensor-core matrix product for the expm chain -----------------------------------------
+// The scalar smm() above leaves the SM latency-bound (8 warps, long index chains); DMMA m8n8k4 issues
+// 256 FMAs per instruction, so a 64^3 product is ~130 instructions per warp.
+__device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(d0), "+d"(d1)
+                 : "d"(a), "d"(b));
+}
+// leading dimension that keeps the 8x4 / 4x8 fragment loads at the 2-wavefront minimum (column stride = 8 banks mod 32)
+__host__ __device__ inline int dmm_ld(int np) { return np + 4; }
+
+// C = A*B for np x np matrices (np a multiple of 16, zero padded), col-major with leading dimension ld, in shared
+// memory; one 16x16 block of C per warp and pass.  kk = inner extent (multiple of 4).
+__device__ void dmm(const double *__restrict__ A, const double *__restrict__ B, double *__restrict__ C, int np, int kk, int ld) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tg = lane & 3, nw = blockDim.x >> 5;
+    const int nb = np / 16;
+    for (int blk = warp; blk < nb * nb; blk += nw) {
+        const int i0 = (blk % nb) * 16, j0 = (blk / nb) * 16;
+        double c00a = 0, c00b = 0, c01a = 0, c01b = 0, c10a = 0, c10b = 0, c11a = 0, c11b = 0;
+        const double *Ap = A + i0 + g + (size_t)ld * tg;
+        const double *Bp = B + tg + (size_t)ld * (j0 + g);
+#pragma unroll 4
+        for (int p0 = 0; p0 < kk; p0 += 4) {
+            const double a0 = Ap[(size_t)ld * p0], a1 = Ap[(size_t)ld * p0 + 8];
+            const double b0 = Bp[p0], b1 = Bp[p0 + (size_t)ld * 8];
+            dmma884(c00a, c00b, a0, b0);
+            dmma884(c01a, c01b, a0, b1);
+            dmma884(c10a, c10b, a1, b0);
+            dmma884(c11a, c11b, a1, b1);
+        }
+        double *Cp = C + i0 + g + (size_t)ld * (j0 + 2 * tg);
+        Cp[0] = c00a; Cp[ld] = c00b;
+        Cp[(size_t)ld * 8] = c01a; Cp[(size_t)ld * 9] = c01b;
+        Cp[8] = c10a; Cp[8 + ld] = c10b;
+        Cp[8 + (size_t)ld * 8] = c11a; Cp[8 + (size_t)ld * 9] = c11b;
+    }
+    __syncthreads();
+}
+
+// exp(X) for the n2 x n2 matrix held (zero padded to np x np, leading dimension ld) in buf[0]; the result is left
+// in the buffer whose pointer is returned.  Same algorithm as sexpm (Taylor / Paterson-Stockmeyer + squaring);
+// buf holds six np*ld blocks.  NaN/Inf input sets *bad_s.
+__device__ double *sexpm2(double *buf, int n2, int np, int ld, int *bad_s) {
+    __shared__ double nrm2_s;
+    __shared__ int s2_s, m2_s;
+    const size_t sz = (size_t)ld * np;
+    const int kk = (n2 + 3) & ~3;
+    double *X = buf, *X2 = X + sz, *X3 = X2 + sz, *X4 = X3 + sz, *P = X4 + sz, *Tm = P + sz;
+    if (threadIdx.x == 0) nrm2_s = 0.0;
+    __syncthreads();
+    for (int c0 = (threadIdx.x >> 5) * 4; c0 < n2; c0 += (blockDim.x >> 5) * 4) {   // 1-norm: eight lanes per column
+        const int c = c0 + ((threadIdx.x & 31) >> 3);
+        double s = 0.0;
+        if (c < n2)
+            for (int i = threadIdx.x & 7; i < n2; i += 8) s += fabs(X[i + (size_t)ld * c]);
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        s += __shfl_xor_sync(0xffffffffu, s, 2);
+        s += __shfl_xor_sync(0xffffffffu, s, 4);
+        if ((threadIdx.x & 7) == 0 && c < n2) {
+            if (s != s || isinf(s)) *bad_s = 1;
+            else atomicMax(reinterpret_cast<unsigned long long *>(&nrm2_s), (unsigned long long)__double_as_longlong(s));
+        }
+    }
+    __syncthreads();
+    if (*bad_s) return X;
+    if (threadIdx.x == 0) {
+        const double nrm = nrm2_s;
+        int m = 20, s = 0;
+        if (nrm <= 1.7e-3) m = 4;
+        else if (nrm <= 7.0e-2) m = 8;
+        else if (nrm <= 3.3e-1) m = 12;
+        else if (nrm <= 8.2e-1) m = 16;
+        else if (nrm > 1.5) s = max(0, (int)ceil(log2(nrm / 1.5)));
+        m2_s = m;
+        s2_s = s;
+    }
+    __syncthreads();
+    const int m = m2_s, s = s2_s;
+    if (s > 0) {
+        const double f = ldexp(1.0, -s);
+        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) X[t] *= f;
+        __syncthreads();
+    }
+    dmm(X, X, X2, np, kk, ld);
+    dmm(X2, X, X3, np, kk, ld);
+    dmm(X2, X2, X4, np, kk, ld);
+    const double inv_fact[21] = {1.0, 1.0, 0.5, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040, 1.0 / 40320,
+                                 1.0 / 362880, 1.0 / 3628800, 1.0 / 39916800, 1.0 / 479001600, 1.0 / 6227020800.0,
+                                 1.0 / 87178291200.0, 1.0 / 1307674368000.0, 1.0 / 20922789888000.0,
+                                 1.0 / 355687428096000.0, 1.0 / 6402373705728000.0, 1.0 / 121645100408832000.0,
+                                 1.0 / 2432902008176640000.0};
+    const int nbk = m / 4;
+    {   // top block, with the X^m term folded in
+        const int b0 = 4 * (nbk - 1);
+        const double c0 = inv_fact[b0], c1 = inv_fact[b0 + 1], c2 = inv_fact[b0 + 2], c3 = inv_fact[b0 + 3], c4 = inv_fact[m];
+        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) {
+            const int i = (int)(t % ld), j = (int)(t / ld);
+            P[t] = ((i == j && i < n2) ? c0 : 0.0) + c1 * X[t] + c2 * X2[t] + c3 * X3[t] + c4 * X4[t];
+        }
+        __syncthreads();
+    }
+    for (int bi = nbk - 2; bi >= 0; --bi) {
+        dmm(X4, P, Tm, np, kk, ld);
+        const int b0 = 4 * bi;
+        const double c0 = inv_fact[b0], c1 = inv_fact[b0 + 1], c2 = inv_fact[b0 + 2], c3 = inv_fact[b0 + 3];
+        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) {
+            const int i = (int)(t % ld), j = (int)(t / ld);
+            P[t] = Tm[t] + ((i == j && i < n2) ? c0 : 0.0) + c1 * X[t] + c2 * X2[t] + c3 * X3[t];
+        }
+        __syncthreads();
+    }
+    double *cur = P, *oth = Tm;
+    for (int q = 0; q < s; ++q) {
+        dmm(cur, cur, oth, np, kk, ld);
+        double *sw = cur; cur = oth; oth = sw;
+    }
+    return cur;
+}
+
+// P2' : like k_small, with everything in shared memory, the matrix exponentials on the FP64 tensor cores, and the
+// column norms of Unew = U C1 + G C2 taken from the r x r Gram matrices, so that C1, C2 leave already divided by
+// the norms (:30-35) and the apply kernel writes the final U in one pass.
+struct Small2Geo {
+    int r2, np2, ld2, npr, ldr;
+    size_t sz2, szr;
+    __host__ __device__ explicit Small2Geo(int r) {
+        r2 = 2 * r;
+        np2 = (r2 + 15) & ~15; ld2 = dmm_ld(np2); sz2 = (size_t)ld2 * np2;
+        npr = (r + 15) & ~15; ldr = dmm_ld(npr); szr = (size_t)ldr * npr;
+    }
+    __host__ __device__ bool ok(int r) const { return 6 * szr <= 4 * sz2 && 10 * (size_t)r * r <= 4 * sz2; }
+    __host__ __device__ size_t bytes() const { return 6 * sz2 * sizeof(double); }
+};
+
 __global__ void __launch_bounds__(1024)
 k_small2(double *__restrict__ small, size_t small_stride, int r, double t, int32_t *nan_flag) {
     extern __shared__ double sm[];
     __shared__ int bad;
     double *sk = small + (size_t)blockIdx.x * small_stride;
     SmallLayout L(r);
-    const int r2 = 2 * r, rr = r * r, tid = threadIdx.x, nt = blockDim.x;
+    const Small2Geo g(r);
+    const int r2 = g.r2, rr = r * r, tid = threadIdx.x, nt = blockDim.x;
     if (tid == 0) bad = 0;
-    double *S1 = sm, *S1t = sm + rr, *UU = sm + 2 * rr, *GG = sm + 3 * rr, *sym = sm + 4 * rr, *t1 = sm + 5 * rr,
-           *t2 = sm + 6 * rr, *t3 = sm + 7 * rr;
+    // ---- phase 1: r x r algebra in blocks 1..5, the 2r x 2r argument of expm straight into block 0
+    double *Xb = sm;
+    double *S1 = sm + g.sz2, *S1t = S1 + rr, *UU = S1t + rr, *GG = UU + rr, *sym = GG + rr, *t1 = sym + rr, *t2 = t1 + rr,
+           *t3 = t2 + rr;
     for (int i = tid; i < rr; i += nt) {
         const int a = i % r, b = i / r;
         const double s = sk[L.S1 + i];
@@ -632,80 +768,91 @@ k_small2(double *__restrict__ small, size_t small_stride, int r, double t, int32
         GG[i] = sk[L.GG + i];
     }
     __syncthreads();
-    for (int i = tid; i < rr; i += nt) sym[i] = (S1[i] + S1t[i]) / 2;
-    __syncthreads();
-    smm_s(UU, sym, t1, r, r, r);      // UU*sym
-    smm_s(sym, t1, t2, r, r, r);      // sym*UU*sym
-    smm_s(S1t, sym, t3, r, r, r);     // S1'*sym  (sym*S1 is its transpose)
-    double *Tm = sk + L.Tm, *X = sk + L.X;
-    for (int i = tid; i < r2 * r2; i += nt) {
-        const int a = i % r2, b = i / r2;
-        double v;
-        if (a < r && b < r) v = S1[a + r * b] - t1[a + r * b];                                   // A = U'M
-        else if (a < r) {                                                                          // -M'M
-            const int bb = b - r;
-            v = -(GG[a + r * bb] - t3[a + r * bb] - t3[bb + r * a] + t2[a + r * bb]);
-        } else if (b < r) v = (a - r == b) ? 1.0 : 0.0;
-        else v = S1[(a - r) + r * (b - r)] - t1[(a - r) + r * (b - r)];
-        Tm[i] = t * v;
+    for (int i = tid; i < rr; i += nt) {
+        const double v = (S1[i] + S1t[i]) / 2;
+        sym[i] = v;
+        sk[L.sym + i] = v;
     }
-    for (int i = tid; i < rr; i += nt) X[i] = -t * (S1[i] - t1[i]);
     __syncthreads();
-    sexpm(Tm, r2, sm, &bad);
+    smm_s(UU, r, sym, r, t1, r, r, r, r);      // UU*sym
+    smm_s(sym, r, t1, r, t2, r, r, r, r);      // sym*UU*sym
+    smm_s(S1t, r, sym, r, t3, r, r, r, r);     // S1'*sym  (sym*S1 is its transpose)
+    for (size_t i = tid; i < g.sz2; i += nt) {
+        const int a = (int)(i % g.ld2), b = (int)(i / g.ld2);
+        double v = 0.0;
+        if (a < r2 && b < r2) {
+            if (a < r && b < r) v = S1[a + r * b] - t1[a + r * b];                               // A = U'M
+            else if (a < r) {                                                                      // -M'M
+                const int bb = b - r;
+                v = -(GG[a + r * bb] - t3[a + r * bb] - t3[bb + r * a] + t2[a + r * bb]);
+            } else if (b < r) v = (a - r == b) ? 1.0 : 0.0;
+            else v = S1[(a - r) + r * (b - r)] - t1[(a - r) + r * (b - r)];
+        }
+        Xb[i] = t * v;
+    }
+    for (int i = tid; i < rr; i += nt) sk[L.X + i] = -t * (S1[i] - t1[i]);
+    __syncthreads();
+    // ---- phase 2: E = expm(t [[A, -M'M], [I, A]])
+    double *E = sexpm2(sm, r2, g.np2, g.ld2, &bad);
     if (!bad) {
         int local = 0;                 // "if sum(isnan(E))>0" (:24)
-        for (int i = tid; i < r2 * r2; i += nt)
-            if (Tm[i] != Tm[i]) local = 1;
+        for (int i = tid; i < r2 * r2; i += nt) {
+            const double v = E[(i % r2) + (size_t)g.ld2 * (i / r2)];
+            if (v != v) local = 1;
+        }
         if (local) bad = 1;
     }
-    __syncthreads();
-    if (!bad) sexpm(X, r, sm, &bad);
     __syncthreads();
     if (bad) {
         if (tid == 0) atomicExch(nan_flag, 1);
         return;
     }
-    // W = E[:,1:r] * expm(-tA); C1 = W1 - sym*W2, C2 = W2
-    double *E1 = sm, *Xs = sm + r2 * r, *W = Xs + rr, *W1 = W + r2 * r, *W2 = W1 + rr, *C1 = W2 + rr, *symb = C1 + rr,
-           *P1 = symb + rr, *P2 = P1 + rr, *P3 = P2 + rr, *M1 = P3 + rr, *M2 = M1 + rr, *M3 = M2 + rr, *cn = M3 + rr;
-    for (int i = tid; i < r2 * r; i += nt) E1[i] = Tm[i];   // first r columns of E (col-major)
+    // ---- phase 3: expm(-tA) in blocks 0..3 (E sits in block 4 or 5), parked in the other of blocks 4/5
+    for (size_t i = tid; i < g.szr; i += nt) {
+        const int a = (int)(i % g.ldr), b = (int)(i / g.ldr);
+        sm[i] = (a < r && b < r) ? sk[L.X + a + r * b] : 0.0;
+    }
+    __syncthreads();
+    double *Xe0 = sexpm2(sm, r, g.npr, g.ldr, &bad);
+    if (bad) {
+        if (tid == 0) atomicExch(nan_flag, 1);
+        return;
+    }
+    double *Xe = (E == sm + 4 * g.sz2) ? sm + 5 * g.sz2 : sm + 4 * g.sz2;
+    for (size_t i = tid; i < g.szr; i += nt) Xe[i] = Xe0[i];
+    __syncthreads();
+    // ---- phase 4: W = E[:,1:r] * expm(-tA); C1 = W1 - sym*W2, C2 = W2; column norms; blocks 0..3 are scratch
+    double *W = sm, *C1 = W + (size_t)r2 * r, *symb = C1 + rr, *P1 = symb + rr, *P2 = P1 + rr, *P3 = P2 + rr,
+           *M1 = P3 + rr, *M2 = M1 + rr, *M3 = M2 + rr;
+    __shared__ double cn[64];
     for (int i = tid; i < rr; i += nt) {
-        Xs[i] = X[i];
-        const int a = i % r, b = i / r;
-        const double s = sk[L.S1 + i];
-        M2[i] = s;
-        symb[i] = (s + sk[L.S1 + b + r * a]) / 2;
+        symb[i] = sk[L.sym + i];
         M1[i] = sk[L.UU + i];
+        M2[i] = sk[L.S1 + i];
         M3[i] = sk[L.GG + i];
     }
-    __syncthreads();
-    smm_s(E1, Xs, W, r2, r, r);
-    for (int i = tid; i < rr; i += nt) {
-        const int a = i % r, b = i / r;
-        W1[i] = W[a + r2 * b];
-        W2[i] = W[(a + r) + r2 * b];
-    }
-    __syncthreads();
-    smm_s(symb, W2, P1, r, r, r);
-    for (int i = tid; i < rr; i += nt) C1[i] = W1[i] - P1[i];
+    smm_s(E, g.ld2, Xe, g.ldr, W, r2, r2, r, r);          // (also orders the loads above)
+    const double *W1 = W, *W2 = W + r;                    // leading dimension r2
+    smm_s(symb, r, W2, r2, P1, r, r, r, r);
+    for (int i = tid; i < rr; i += nt) C1[i] = W1[(i % r) + (size_t)r2 * (i / r)] - P1[i];
     __syncthreads();
     // squared column norms of U C1 + G C2:  diag(C1'UU C1 + 2 C1'S1 C2 + C2'GG C2)
-    smm_s(M1, C1, P1, r, r, r);
-    smm_s(M2, W2, P2, r, r, r);
-    smm_s(M3, W2, P3, r, r, r);
+    smm_s(M1, r, C1, r, P1, r, r, r, r);
+    smm_s(M2, r, W2, r2, P2, r, r, r, r);
+    smm_s(M3, r, W2, r2, P3, r, r, r, r);
     for (int l = tid; l < r; l += nt) {
         double s = 0.0;
         for (int a = 0; a < r; ++a) {
             const int i = a + r * l;
-            s += C1[i] * (P1[i] + 2.0 * P2[i]) + W2[i] * P3[i];
+            s += C1[i] * (P1[i] + 2.0 * P2[i]) + W2[a + (size_t)r2 * l] * P3[i];
         }
         cn[l] = 1.0 / sqrt(s);
     }
     __syncthreads();
     for (int i = tid; i < rr; i += nt) {
-        const int l = i / r;
+        const int a = i % r, l = i / r;
         sk[L.C1 + i] = C1[i] * cn[l];
-        sk[L.C2 + i] = W2[i] * cn[l];
+        sk[L.C2 + i] = W2[a + (size_t)r2 * l] * cn[l];
     }
 }
 
@@ -772,7 +919,7 @@ static void optin_smem() {
     cudaFuncSetAttribute(k_apply, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(k_reduce_only, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(k_small, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    cudaFuncSetAttribute(k_small2, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(k_small2, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024);
     cudaFuncSetAttribute(k_apply2, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     done = true;
 }
@@ -808,7 +955,7 @@ int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, cons
         if (!noise_w) noise_w = h->gen_noise_w;
         if (!noise_U) noise_U = h->gen_noise_U;
     }
-    size_t sm1 = 2 * (size_t)UP_ROWS * c.r * sizeof(double);
+    size_t sm1 = 2 * (size_t)UP_ROWS * (c.r + 1) * sizeof(double);
     k_prepare<<<dim3(nb, c.D + 1), UP_THREADS, sm1, h->stream>>>(h->grad, h->w, h->U, h->G, h->small, h->small_stride,
                                                                 c.n, c.r, c.D, c.Q, epsw, epsU, flags, noise_w,
                                                                 noise_U, c.seed, step, 1);
@@ -816,8 +963,9 @@ int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, cons
     h->shadows_valid = false;
     if (stiefel) {
         const size_t sb = small_smem_bytes(c.r);
-        if (sb && c.r <= 32) {
-            k_small2<<<c.D, 1024, sb, h->stream>>>(h->small, h->small_stride, c.r, sqrt(epsU), h->nan_flag);
+        const Small2Geo sg(c.r);
+        if (sg.ok(c.r) && sg.bytes() <= 225 * 1024) {
+            k_small2<<<c.D, 1024, sg.bytes(), h->stream>>>(h->small, h->small_stride, c.r, sqrt(epsU), h->nan_flag);
             const bool tc = gptb_is_tc(h);
             size_t sm3 = (2 * (size_t)UP_ROWS * c.r + 2 * (size_t)c.r * c.r) * sizeof(double);
             k_apply2<<<dim3(nb, c.D), UP_THREADS, sm3, h->stream>>>(h->U, h->G, h->small, h->small_stride, c.n, c.r,
