@@ -97,7 +97,6 @@ struct FwdParams {
     int D, n, npad, r;
     int64_t bs, mpad, mext;   // live rows, row stride of XbF/T, rows processed (bs rounded up to 128)
     int sincos;
-    int exp;               // experiment bits (GPTB_TC_EXP): 1 = generators skip the math, 2 = issuer skips the MMAs
     int P, NCHp;           // K split: P parts of NCHp chunks each (P > 1 only when the image of U^(k) exceeds shared memory;
                            // T is then accumulated with atomics into a zeroed buffer)
 };
@@ -174,38 +173,37 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
         uint32_t gen = 0;
         int u = u0, ch = g, cur_grp = -1, nch = 0, sa = g % NSTA;
         uint32_t pa = ((g / NSTA) & 1) ^ 1;
-        float x = 0.f;
+        float x = 0.f, x_next = 0.f;
+        {   // x of the first unit; afterwards the next unit's x is fetched one unit ahead
+            const int grp = u0 / ntiles, tile = u0 - grp * ntiles, k = grp / p.P;
+            if (u0 < u1) x_next = p.XbF[(size_t)k * p.mpad + (size_t)tile * 128 + row];
+        }
         bool fresh = true;
         while (u < u1) {
             if (fresh) {
                 fresh = false;
-                const int grp = u / ntiles, tile = u - grp * ntiles, k = grp / p.P;
+                const int grp = u / ntiles, k = grp / p.P;
                 if (grp != cur_grp) {   // the (zt, b) table of this K part arrives with the U image
                     cur_grp = grp;
                     mbar_wait(&bars->u_full, gen & 1);
                     ++gen;
                     nch = min(p.NCHp, NCH - (grp - k * p.P) * p.NCHp);
                 }
-                x = p.XbF[(size_t)k * p.mpad + (size_t)tile * 128 + row];
+                x = x_next;
+                if (u + 1 < u1) {
+                    const int grp1 = (u + 1) / ntiles, tile1 = (u + 1) - grp1 * ntiles, k1 = grp1 / p.P;
+                    x_next = p.XbF[(size_t)k1 * p.mpad + (size_t)tile1 * 128 + row];
+                }
             }
             if (ch >= nch) { ch -= nch; ++u; fresh = true; continue; }
             mbar_wait(&bars->a_empty[sa], pa);
             fence_after_sync();
             const uint32_t st_addr = tmem + lane_addr + sa * SA_COLS;
-            if (p.exp & 1) {
-                uint32_t z[16];
-#pragma unroll
-                for (int c = 0; c < 16; ++c) z[c] = 0x3c003c00u;
-                tmem_st16(st_addr, z); tmem_st16(st_addr + 16, z);
-                if (THREE) { tmem_st16(st_addr + 32, z); tmem_st16(st_addr + 48, z); }
-            } else {
-                gen_fwd_chunk<THREE>(sZb + (p.sincos ? ch * KC / 2 : ch * KC), x, p.sincos != 0, st_addr);
-            }
+            gen_fwd_chunk<THREE>(sZb + (p.sincos ? ch * KC / 2 : ch * KC), x, p.sincos != 0, st_addr);
             wait_st();
             fence_before_sync();
             __syncwarp();
             if (lane == 0) mbar_arrive(&bars->a_full[sa]);   // one arrival per warp: 32 lanes on one mbarrier serialise
-
             ch += NGEN;
             sa += NGEN;
             if (sa >= NSTA) { sa -= NSTA; pa ^= 1; }
@@ -233,12 +231,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
                 const uint32_t a_hi = tmem + sa * SA_COLS, a_lo = a_hi + 32;
                 const uint32_t b_addr = smem_u32(sU + (size_t)ch * KC * ROW_BYTES);
                 if (elect_one()) {
-                    if (!(p.exp & 2)) {
 #pragma unroll
-                        for (int s4 = 0; s4 < KC / 16; ++s4)
-                            mma_kstep<RPAD, THREE, 0>(d, a_hi + s4 * 8, a_lo + s4 * 8, b_addr + s4 * 16 * ROW_BYTES,
-                                                      (ch | s4) != 0);
-                    }
+                    for (int s4 = 0; s4 < KC / 16; ++s4)
+                        mma_kstep<RPAD, THREE, 0>(d, a_hi + s4 * 8, a_lo + s4 * 8, b_addr + s4 * 16 * ROW_BYTES,
+                                                  (ch | s4) != 0);
                     mma_commit(&bars->a_empty[sa]);
                     if (ch == nch - 1) {
                         mma_commit(&bars->acc_full[ab]);
@@ -594,15 +590,6 @@ __global__ void interleave_zb_kernel(const float *zt, const float *b, size_t n, 
     }
 }
 
-int probe_exp() {
-    static int v = -1;
-    if (v < 0) {
-        const char *e = getenv("GPTB_TC_EXP");
-        v = e ? atoi(e) : 0;
-    }
-    return v;
-}
-
 }  // namespace
 
 size_t gptb_tc_uimg_bytes(const gptb_handle *h) { return (size_t)h->cfg.D * h->npad * 2 * h->rpad * sizeof(__half); }
@@ -693,7 +680,6 @@ int gptb_launch_fwd_tc(gptb_handle *h, const float *XbF, const void *Uimg, int64
     p.mpad = mpad;
     p.mext = (bs + 127) / 128 * 128;   // only the 128-row tiles that hold live rows are generated
     p.sincos = c.feature_kind == GPTB_FEAT_SINCOS;
-    p.exp = probe_exp();
     // K parts: the image of one part (plus its (zt,b) table) must fit in shared memory
     const int NCH = h->npad / KC;
     const size_t chunk_bytes = (size_t)KC * (2 * h->rpad * 2 + sizeof(float2));
