@@ -1,0 +1,194 @@
+# GPT_SGLD.jl — drop-in host module for the hot path of hyunjik11/GPT, backed by libgptb200.so (B200, sm_100a).
+#
+# Same exported names and positional signatures as the reference module (/root/reference/GPT_SGLD.jl:5):
+#   datawhitening, feature, feature2, samplenz, pred, GPTregression, proj, geod
+# Every method `ccall`s one entry point of include/gptb200.h; arrays cross the boundary as Julia stores them
+# (column-major Float64, I::Matrix{Int32} 1-based), so nothing is copied or transposed on the Julia side.
+#
+# Differences a caller can see:
+#   * feature/feature2 return an RFFFeatures handle (X, Z, b, length_scale, sigma_RBF, phi_scale) instead of the
+#     n x D x N array; GPTregression/pred dispatch on it and the kernels generate the features on the fly.
+#     Array(f::RFFFeatures) materialises it (gptb_features) for code that indexes phi directly.
+#     Methods taking a dense phi::Array{Float64,3} are kept (the reference's calling convention).
+#   * Julia 0.3's dSFMT stream cannot be reproduced: w0/U0, permutations and noise come from Philox(param_seed)
+#     unless passed explicitly with the keyword arguments w0, U0, perms, noise_w, noise_U (test mode).
+#   * On a geodesic NaN the library returns GPTB_GEODESIC_NAN; this module prints the reference's warning and
+#     returns zero-filled stores, as GPT_SGLD.jl:24-26,422-424 does.
+# Written for Julia >= 1.6 (the reference itself is Julia 0.3 and does not load on 1.x).  Not executed in the
+# build container (no julia binary there); the Python mirror gpt_b200/gpt_sgld.py is what the tests drive.
+module GPT_SGLD
+
+export datawhitening, feature, feature2, samplenz, pred, GPTregression, proj, geod, RFFFeatures
+
+using Random, Statistics
+
+const LIB = get(ENV, "GPTB200_LIB", joinpath(@__DIR__, "..", "gpt_b200", "lib", "libgptb200.so"))
+
+const GPTB_OK = Cint(0)
+const GPTB_GEODESIC_NAN = Cint(7)
+const PREC_FP64, PREC_TC3, PREC_TC1 = Cint(0), Cint(1), Cint(2)
+const FEAT_COS, FEAT_SINCOS = Cint(0), Cint(1)
+const FLAG_LANGEVIN, FLAG_STIEFEL = Cint(1), Cint(2)
+
+struct Config            # mirrors struct gptb_config
+    D::Int32; n::Int32; r::Int32; Q::Int32
+    precision::Int32; feature_kind::Int32; device::Int32; reserved::Int32
+    seed::UInt64
+end
+
+struct RFFFeatures
+    X::Matrix{Float64}; length_scale::Vector{Float64}; sigma_RBF::Float64; phi_scale::Float64
+    Z::Matrix{Float64}; b::Matrix{Float64}; kind::Cint
+end
+Base.size(f::RFFFeatures) = (f.kind == FEAT_COS ? size(f.Z, 1) : size(f.Z, 1), size(f.X, 2), size(f.X, 1))
+
+lasterr(h) = unsafe_string(ccall((:gptb_last_error, LIB), Cstring, (Ptr{Cvoid},), h))
+function check(st::Cint, h = C_NULL)
+    st == GPTB_OK || error("libgptb200: status $st: $(lasterr(h))")
+    nothing
+end
+
+function create(D, n, r, Q; precision = PREC_TC3, kind = FEAT_COS, device = -1, seed = 0)
+    h = Ref{Ptr{Cvoid}}(C_NULL)
+    cfg = Ref(Config(D, n, r, Q, precision, kind, device, 0, UInt64(seed)))
+    check(ccall((:gptb_create, LIB), Cint, (Ref{Config}, Ref{Ptr{Cvoid}}), cfg, h))
+    h[]
+end
+destroy(h) = ccall((:gptb_destroy, LIB), Cint, (Ptr{Cvoid},), h)
+
+function set_features!(h, f::RFFFeatures)
+    ls = f.length_scale
+    check(ccall((:gptb_set_features, LIB), Cint,
+                (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Int32, Float64, Float64),
+                h, f.Z, f.kind == FEAT_COS ? pointer(f.b) : Ptr{Float64}(C_NULL), ls, length(ls), f.sigma_RBF, f.phi_scale), h)
+end
+
+# GPT_SGLD.jl:62-67 — host preprocessing, in place like the reference
+function datawhitening(X::Array)
+    for i = 1:size(X, 2)
+        X[:, i] = (X[:, i] .- mean(X[:, i])) ./ std(X[:, i])
+    end
+    X
+end
+
+# GPT_SGLD.jl:71-84 / :88-105 — lazy handles
+feature(X::Array, length_scale, sigma_RBF::Real, phi_scale::Real, Z::Array, b::Array) =
+    RFFFeatures(Matrix{Float64}(X), Float64[length_scale...], sigma_RBF, phi_scale, Matrix{Float64}(Z), Matrix{Float64}(b), FEAT_COS)
+function feature2(X::Array, length_scale, sigma_RBF::Real, phi_scale::Real, Z::Array)
+    iseven(size(Z, 1)) || error("n not even")                     # :89-91
+    # the library reads the first n/2 rows of Z as the frequencies, exactly as :94 does
+    RFFFeatures(Matrix{Float64}(X), Float64[length_scale...], sigma_RBF, phi_scale, Matrix{Float64}(Z), zeros(size(Z)), FEAT_SINCOS)
+end
+
+function Base.Array(f::RFFFeatures)
+    n, D, N = size(f)
+    h = create(D, n, 1, 1; precision = PREC_FP64, kind = f.kind)
+    try
+        set_features!(h, f)
+        phi = Array{Float64}(undef, n, D, N)
+        check(ccall((:gptb_features, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Int64, Ptr{Float64}), h, f.X, N, phi), h)
+        return phi
+    finally
+        destroy(h)
+    end
+end
+
+# GPT_SGLD.jl:181-190 — Q distinct cells of the r^D lattice, little-endian base-r digits + 1
+function samplenz(r::Integer, D::Integer, Q::Integer; rng = Random.default_rng())
+    L = Set{Int64}()
+    while length(L) < Q
+        push!(L, rand(rng, 0:Int64(r)^D - 1))
+    end
+    I = Array{Int32}(undef, Q, D)
+    for (q, l) in enumerate(sort!(collect(L)))
+        I[q, :] = digits(l, base = r, pad = D) .+ 1
+    end
+    I
+end
+
+# GPT_SGLD.jl:233-243
+function pred(w::Array, U::Array, I::Array, phitest::Union{RFFFeatures,Array{Float64,3}}; precision = PREC_TC3)
+    n, r, D = size(U); Q = length(w)
+    lazy = phitest isa RFFFeatures
+    h = create(D, n, r, Q; precision = lazy ? precision : PREC_FP64, kind = lazy ? phitest.kind : FEAT_COS)
+    try
+        check(ccall((:gptb_set_index, LIB), Cint, (Ptr{Cvoid}, Ptr{Int32}), h, Matrix{Int32}(I)), h)
+        if lazy
+            set_features!(h, phitest)
+            Nt = size(phitest.X, 1); fhat = Vector{Float64}(undef, Nt)
+            check(ccall((:gptb_pred, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Int64, Ptr{Float64}),
+                        h, w, U, phitest.X, Nt, fhat), h)
+        else
+            Nt = size(phitest, 3); fhat = Vector{Float64}(undef, Nt)
+            check(ccall((:gptb_pred_phi, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Int64, Ptr{Float64}),
+                        h, w, U, phitest, Nt, fhat), h)
+        end
+        return fhat
+    finally
+        destroy(h)
+    end
+end
+
+# GPT_SGLD.jl:345-448
+function GPTregression(phi::Union{RFFFeatures,Array{Float64,3}}, y::Array, signal_var::Real, I::Array, r::Integer,
+                       Q::Integer, m::Integer, epsw::Real, epsU::Real, burnin::Integer, maxepoch::Integer,
+                       param_seed::Integer; langevin::Bool = true, stiefel::Bool = true, precision = PREC_TC3,
+                       w0 = nothing, U0 = nothing, perms = nothing, noise_w = nothing, noise_U = nothing)
+    n, D, N = size(phi)
+    lazy = phi isa RFFFeatures
+    h = create(D, n, r, Q; precision = lazy ? precision : PREC_FP64, kind = lazy ? phi.kind : FEAT_COS, seed = param_seed)
+    try
+        check(ccall((:gptb_set_index, LIB), Cint, (Ptr{Cvoid}, Ptr{Int32}), h, Matrix{Int32}(I)), h)
+        yv = Vector{Float64}(vec(y))
+        if lazy
+            set_features!(h, phi)
+            check(ccall((:gptb_set_train, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int64), h, phi.X, yv, N), h)
+        else
+            check(ccall((:gptb_set_train_phi, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int64), h, phi, yv, N), h)
+        end
+        if w0 === nothing
+            check(ccall((:gptb_init_params, LIB), Cint, (Ptr{Cvoid}, UInt64, Int32), h, param_seed, stiefel ? 1 : 0), h)   # :357-369
+        else
+            check(ccall((:gptb_set_params, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}), h, w0, U0), h)
+        end
+        numbatches = cld(N, m)                                     # :353
+        T = maxepoch * numbatches
+        w_store = zeros(Q, T); U_store = zeros(n, r, D, T)         # :358-359
+        flags = (langevin ? FLAG_LANGEVIN : Cint(0)) | (stiefel ? FLAG_STIEFEL : Cint(0))
+        p(x) = x === nothing ? Ptr{Float64}(C_NULL) : pointer(x)
+        pp = perms === nothing ? Ptr{Int64}(C_NULL) : pointer(perms)   # (burnin+maxepoch) x N, 0-based, row-major per epoch
+        st = ccall((:gptb_sgld_run, LIB), Cint,
+                   (Ptr{Cvoid}, Float64, Int64, Float64, Float64, Int32, Int32, Int32, Ptr{Int64}, Ptr{Float64}, Ptr{Float64},
+                    Ptr{Float64}, Ptr{Float64}),
+                   h, signal_var, m, epsw, epsU, burnin, maxepoch, flags, pp, p(noise_w), p(noise_U), w_store, U_store)
+        if st == GPTB_GEODESIC_NAN
+            println("Get NaN when moving along Geodesic. Try smaller epsU")    # :25
+            return w_store, U_store                                            # zero-filled, :422-424
+        end
+        check(st, h)
+        return w_store, U_store
+    finally
+        destroy(h)
+    end
+end
+
+# GPT_SGLD.jl:14-16
+function proj(U::Array, V::Array)
+    n, r = size(U); out = similar(U)
+    check(ccall((:gptb_proj, LIB), Cint, (Int32, Int32, Int32, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}), -1, n, r, U, V, out))
+    out
+end
+
+# GPT_SGLD.jl:19-37
+function geod(U::Array, mom::Array, t::Real)
+    n, r = size(U); out = similar(U)
+    st = ccall((:gptb_geod, LIB), Cint, (Int32, Int32, Int32, Ptr{Float64}, Ptr{Float64}, Float64, Ptr{Float64}), -1, n, r, U, mom, t, out)
+    if st == GPTB_GEODESIC_NAN
+        println("Get NaN when moving along Geodesic. Try smaller epsU")        # :25
+        return zeros(n, r)                                                      # :26
+    end
+    check(st)
+    out
+end
+
+end # module
