@@ -165,7 +165,7 @@ def workload_config(args, W):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C4", choices=list(WORKLOADS))
@@ -289,19 +289,22 @@ def main():
         pf = G.feature(Xt, pm["ls"], 1.0, pm["phi_scale"], pm["Z"], pm["b"])
         with G.Model(C5["D"], C5["n"], C5["r"], Q, precision=prec, device=local) as pmodel:
             pmodel.set_features(pf); pmodel.set_index(pm["I"])
-            pmodel.pred_samples(ws[:, :2], Us[:, :, :, :2], Xt[:4096])      # warm-up
+            pmodel.pred_samples(ws[:, :8], Us[:, :, :, :8], Xt[:4096])      # warm-up (same sample-group geometry)
             barrier()
-            t0 = time.perf_counter()
-            mean = pmodel.pred_samples(ws, Us, Xt)
-            barrier()
-            dt = time.perf_counter() - t0
+            dts = []
+            for _ in range(2):                  # the first full-size call also pays one-time allocations
+                t0 = time.perf_counter()
+                mean = pmodel.pred_samples(ws, Us, Xt)
+                barrier()
+                dts.append(time.perf_counter() - t0)
+            dt = min(dts)
         tp = torch.tensor([dt], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tp, op=dist.ReduceOp.MAX)
         dt = float(tp.item())
         pred = {"metric": "predictions_per_sec", "value": C5["Nt"] * S / dt, "unit": "predictions/s", "seconds": dt,
                 "config": {"workload": f"C5: D={C5['D']} Nt={C5['Nt']} S={S} n={C5['n']} r={C5['r']} Q={Q}, test rows sharded x{world}, host buffers in/out"},
-                "checksum": float(np.abs(mean).sum())}
+                "checksum": float(np.abs(mean).sum()), "seconds_each_call": dts}
 
     if rank != 0:
         if world > 1:
@@ -315,14 +318,14 @@ def main():
     except Exception:
         pass
     bf16_sust = peaks.get("bf16_tflops_sustained", 1400.0)
-    which_peak = "measured (MEASURED_PEAKS.json bf16_tflops_sustained / 2 = TF32-class dense rate, SURVEY.md §8d)" if peaks \
-        else "fallback (B200_PROFILING.md 1.4 PF sustained / 2)"
+    which_peak = "measured (MEASURED_PEAKS.json bf16_tflops_sustained: the kernels issue kind::f16 MMAs inside a long step)" \
+        if peaks else "fallback (B200_PROFILING.md 1.4 PF sustained)"
     ml = m / world                                     # rows per rank
     per_launch_flops = 2.0 * ml * n * r * D            # algorithmic tensor flops of ONE K1 or K3 launch
     dom = "bwd" if phases["bwd"] >= phases["fwd"] else "fwd"
     dom_ms = phases[dom] / args.steps
     ach = per_launch_flops / (dom_ms * 1e-3) / 1e12 if dom_ms > 0 else None
-    peak_tf = bf16_sust / 2.0
+    peak_tf = bf16_sust
     sm_mhz = clk.summary()["sm_mhz"] or 1965.0
     cos_peak = 16 * 148 * sm_mhz * 1e6                  # MUFU.COS: 16 / clk / SM (nominal), at the clock seen
     roofline = {"kernel": {"fwd": "fwd_tc_kernel (K1)", "bwd": "bwd_tc_kernel (K3)"}[dom], "bound": "tensor",

@@ -738,6 +738,90 @@ int gptb_features(gptb_handle *h, const double *X, int64_t N, double *phi_out) {
     return st;
 }
 
+// Posterior-predictive sweep on the tensor-core path (K6): the factors of Sg samples sit side by side in one operand
+// image, so K1 generates each feature once per sample group, and the forward-only contraction handles the group's
+// samples in one launch.  Row chunks are sized so that the group's T block stays in L2 between the two kernels.
+static int pred_tc_grouped(gptb_handle *h, const double *w_store, const double *U_store, int32_t S, const double *Xtest,
+                           int64_t Nt, double *mean_out, double *per_sample_out) {
+    const gptb_config &c = h->cfg;
+    const size_t ucnt = (size_t)c.n * c.r * c.D;
+    // widest image that stays resident in shared memory (see gptb_launch_fwd_tc_cols)
+    const size_t budget = 227 * 1024 - 2048;
+    int nc_max = (int)(((budget / h->npad) - sizeof(float2)) / 4) / 16 * 16;
+    nc_max = std::min(nc_max, 128);
+    int Sg = std::max(1, nc_max / c.r);
+    Sg = std::min<int>(Sg, S);
+    const int NC = std::max(h->rpad, (Sg * c.r + 15) / 16 * 16);
+    const int ngroups = (S + Sg - 1) / Sg;
+    const size_t img_elems = (size_t)c.D * h->npad * 2 * NC;
+    if ((size_t)S * ucnt * 8 > (size_t)8 << 30 || img_elems * 2 * ngroups > (size_t)8 << 30) return GPTB_ERR_UNSUPPORTED;
+    int64_t chunk = (int64_t)((size_t)(48 << 20) / ((size_t)c.D * Sg * c.r * 4)) / 128 * 128;
+    chunk = std::max<int64_t>(128, std::min<int64_t>(chunk, 65536));
+    chunk = std::min<int64_t>(chunk, (Nt + 127) / 128 * 128);
+    GPTB_TRY(ensure_batch(h, chunk));
+    const int64_t mpad = h->mpad;
+    double *Ud = nullptr, *wd = nullptr, *acc = nullptr, *fh = nullptr;
+    float *Tg = nullptr;
+    unsigned char *imgs = nullptr;
+    int st = dev_alloc(h, &Ud, (size_t)S * ucnt);
+    if (st == GPTB_OK) st = dev_alloc(h, &wd, (size_t)S * c.Q);
+    if (st == GPTB_OK) st = dev_alloc(h, &imgs, img_elems * 2 * ngroups);
+    if (st == GPTB_OK) st = dev_alloc(h, &Tg, (size_t)c.D * Sg * c.r * mpad);
+    if (st == GPTB_OK) st = dev_alloc(h, &acc, (size_t)mpad);
+    if (st == GPTB_OK && per_sample_out) st = dev_alloc(h, &fh, (size_t)S * mpad);
+    auto cleanup = [&]() {
+        cudaStreamSynchronize(h->stream);
+        dev_free(&Ud); dev_free(&wd); dev_free(&imgs); dev_free(&Tg); dev_free(&acc); dev_free(&fh);
+    };
+    if (st != GPTB_OK) { cleanup(); return st; }
+#define PRED_OK(expr)                                                                     \
+    do {                                                                                  \
+        cudaError_t _e = (expr);                                                          \
+        if (_e != cudaSuccess) {                                                          \
+            gptb_set_error(h, "pred_samples: %s -> %s", #expr, cudaGetErrorString(_e));   \
+            cleanup();                                                                    \
+            return GPTB_ERR_CUDA;                                                         \
+        }                                                                                 \
+    } while (0)
+#define PRED_TRY(expr)                 \
+    do {                               \
+        int _s = (expr);               \
+        if (_s != GPTB_OK) { cleanup(); return _s; } \
+    } while (0)
+    PRED_OK(cudaMemcpyAsync(Ud, U_store, sizeof(double) * S * ucnt, cudaMemcpyHostToDevice, h->stream));
+    PRED_OK(cudaMemcpyAsync(wd, w_store, sizeof(double) * S * c.Q, cudaMemcpyHostToDevice, h->stream));
+    PRED_TRY(gptb_tc_pred_scale(h, Ud, (size_t)S * ucnt, true));
+    PRED_TRY(gptb_tc_pred_scale_commit(h));
+    for (int g = 0; g < ngroups; ++g) {
+        const int sg = std::min(Sg, S - g * Sg);
+        PRED_TRY(gptb_tc_pack_group(h, Ud + (size_t)g * Sg * ucnt, sg, NC, imgs + (size_t)g * img_elems * 2));
+    }
+    for (int64_t i0 = 0; i0 < Nt; i0 += chunk) {
+        const int64_t cn = std::min(chunk, Nt - i0);
+        PRED_OK(cudaMemcpy2DAsync(h->Xb, mpad * sizeof(double), Xtest + i0, Nt * sizeof(double), cn * sizeof(double), c.D,
+                                  cudaMemcpyHostToDevice, h->stream));
+        d2f_kernel<<<256, 256, 0, h->stream>>>(h->Xb, h->XbF, (size_t)c.D * mpad);
+        h->launches++;
+        PRED_OK(cudaMemsetAsync(acc, 0, sizeof(double) * mpad, h->stream));
+        for (int g = 0; g < ngroups; ++g) {
+            const int sg = std::min(Sg, S - g * Sg);
+            PRED_TRY(gptb_launch_fwd_tc_cols(h, h->XbF, imgs + (size_t)g * img_elems * 2, h->tc_state + 7, cn, mpad, Tg,
+                                             sg * c.r, NC));
+            PRED_TRY(gptb_launch_contract_fwd(h, Tg, wd + (size_t)g * Sg * c.Q, sg, cn, mpad, sg * c.r,
+                                              fh ? fh + (size_t)g * Sg * mpad : nullptr, mean_out ? acc : nullptr, 1.0 / S));
+        }
+        if (mean_out) PRED_OK(cudaMemcpyAsync(mean_out + i0, acc, sizeof(double) * cn, cudaMemcpyDeviceToHost, h->stream));
+        if (per_sample_out)
+            PRED_OK(cudaMemcpy2DAsync(per_sample_out + i0, Nt * sizeof(double), fh, mpad * sizeof(double), cn * sizeof(double), S,
+                                      cudaMemcpyDeviceToHost, h->stream));
+        PRED_OK(cudaStreamSynchronize(h->stream));
+    }
+#undef PRED_OK
+#undef PRED_TRY
+    cleanup();
+    return GPTB_OK;
+}
+
 // Shared by pred / pred_phi / pred_samples: S parameter sets, rows chunked through the batch scratch.
 static int pred_impl(gptb_handle *h, const double *w_store, const double *U_store, int32_t S, const double *Xtest,
                      const double *phitest, int64_t Nt, double *mean_out, double *per_sample_out) {
@@ -754,6 +838,10 @@ static int pred_impl(gptb_handle *h, const double *w_store, const double *U_stor
     }
     if (Nt == 0) return GPTB_OK;
     const bool f64 = use_fp64(h, phi_mode);
+    if (!f64) {
+        const int st = pred_tc_grouped(h, w_store, U_store, S, Xtest, Nt, mean_out, per_sample_out);
+        if (st != GPTB_ERR_UNSUPPORTED) return st;   // shapes it does not cover use the per-sample path below
+    }
     const size_t ucnt = (size_t)c.n * c.r * c.D;
     int64_t chunk = std::min<int64_t>(Nt, 65536);
     if (phi_mode) chunk = std::min<int64_t>(chunk, std::max<int64_t>(128, (int64_t)(512ll << 20) / ((int64_t)c.n * c.D * 8)));

@@ -221,6 +221,14 @@ int gptb_tc_pack_params(gptb_handle *h);
 int gptb_tc_pack_U(gptb_handle *h, const double *U, void *Uimg);
 int gptb_tc_update_escale(gptb_handle *h);
 int gptb_launch_fwd_tc(gptb_handle *h, const float *XbF, const void *Uimg, int64_t bs, int64_t mpad, float *T);
+int gptb_launch_fwd_tc_cols(gptb_handle *h, const float *XbF, const void *Uimg, const float *uscale, int64_t bs,
+                            int64_t mpad, float *T, int ncols, int NC);
+int gptb_tc_pred_scale(gptb_handle *h, const double *U, size_t cnt, bool first);
+int gptb_tc_pred_scale_commit(gptb_handle *h);
+int gptb_tc_pack_group(gptb_handle *h, const double *Ug, int Sg, int NC, void *img);
+int gptb_launch_contract_fwd(gptb_handle *h, const float *T, const double *w_group, int Sg, int64_t bs, int64_t mpad,
+                             int ncols_total, double *fh_group /*[Sg][mpad] or null*/, double *mean_acc /*[mpad] or null*/,
+                             double mean_scale);
 int gptb_launch_bwd_tc(gptb_handle *h, const float *XbF, const void *Eimg, int64_t bs, int64_t mpad, double *gradU);
 size_t gptb_tc_uimg_bytes(const gptb_handle *h);
 size_t gptb_tc_eimg_bytes(const gptb_handle *h, int64_t mpad);

@@ -294,3 +294,109 @@ int gptb_launch_contract_tc(gptb_handle *h, const float *T, const double *w, con
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Forward-only contraction of the posterior-predictive sweep: fhat_s[i] = sum_q w_s[q] prod_k T[k, s*r + I[q,k], i]
+// for the Sg samples whose factor products sit side by side in T ([D][ncols_total][mpad], K1 with a grouped image).
+// grid = (row blocks of 64, Sg).  Only the T tile lives in shared memory (no V), so several CTAs share an SM and
+// hide the gather latency.  Optionally accumulates mean_acc[i] += mean_scale * fhat_s[i] (pred_samples' average).
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+struct ContractFwdParams {
+    const float *T;
+    const double *w;         // [Sg][Q]
+    const int32_t *off1;     // [Q][DP]
+    double *fh;              // [Sg][mpad] or null
+    double *mean_acc;        // [mpad] or null
+    double mean_scale;
+    int64_t bs, mpad;
+    int DP, r, Q, ncols_total;
+};
+
+template <int DT>
+__global__ void __launch_bounds__(256) contract_fwd_kernel(const ContractFwdParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int D = DT;
+    constexpr int DP4 = (DT + 3) / 4;
+    constexpr int NW = 8;
+    const int r = p.r, Q = p.Q, DR = D * r;
+    const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5, s = blockIdx.y;
+    const int64_t i0 = (int64_t)blockIdx.x * CRB + 2 * lane;
+    float2 *Ts = reinterpret_cast<float2 *>(smem_raw);           // [DR][32]
+    float *ws = reinterpret_cast<float *>(Ts + (size_t)DR * 32); // [Q rounded up to 4]
+    float2 *Fs = reinterpret_cast<float2 *>(ws + ((Q + 3) & ~3)); // [NW][32]
+    for (int t = tid; t < Q; t += 256) ws[t] = (float)p.w[(size_t)s * Q + t];
+    for (int c = wp; c < DR; c += NW) {
+        const int k = c / r, l = c - k * r;
+        Ts[(size_t)c * 32 + lane] =
+            *reinterpret_cast<const float2 *>(p.T + ((size_t)k * p.ncols_total + (size_t)s * r + l) * p.mpad + i0);
+    }
+    __syncthreads();
+    const float2 *Trow = Ts + lane;
+    float2 f = make_float2(0.f, 0.f);
+#pragma unroll 2
+    for (int q = wp; q < Q; q += NW) {
+        const int4 *o = reinterpret_cast<const int4 *>(p.off1) + (size_t)q * DP4;
+        float2 v = make_float2(1.f, 1.f);
+#pragma unroll
+        for (int g4 = 0; g4 < DP4; ++g4) {
+            const int4 oo = __ldg(o + g4);
+            if (g4 * 4 + 0 < D) v = mul2(v, Trow[oo.x]);
+            if (g4 * 4 + 1 < D) v = mul2(v, Trow[oo.y]);
+            if (g4 * 4 + 2 < D) v = mul2(v, Trow[oo.z]);
+            if (g4 * 4 + 3 < D) v = mul2(v, Trow[oo.w]);
+        }
+        const float wq = ws[q];
+        f = __ffma2_rn(make_float2(wq, wq), v, f);
+    }
+    Fs[wp * 32 + lane] = f;
+    __syncthreads();
+    if (wp == 0) {
+        f = Fs[lane];
+#pragma unroll
+        for (int t = 1; t < NW; ++t) f = add2(f, Fs[t * 32 + lane]);
+        const bool live0 = i0 < p.bs, live1 = i0 + 1 < p.bs;
+        if (p.fh) {
+            if (live0) p.fh[(size_t)s * p.mpad + i0] = (double)f.x;
+            if (live1) p.fh[(size_t)s * p.mpad + i0 + 1] = (double)f.y;
+        }
+        if (p.mean_acc) {
+            if (live0) atomicAdd(&p.mean_acc[i0], p.mean_scale * (double)f.x);
+            if (live1) atomicAdd(&p.mean_acc[i0 + 1], p.mean_scale * (double)f.y);
+        }
+    }
+}
+
+}  // namespace
+
+int gptb_launch_contract_fwd(gptb_handle *h, const float *T, const double *w_group, int Sg, int64_t bs, int64_t mpad,
+                             int ncols_total, double *fh_group, double *mean_acc, double mean_scale) {
+    const gptb_config &c = h->cfg;
+    const size_t smem = (size_t)c.D * c.r * 32 * sizeof(float2) + (size_t)((c.Q + 3) & ~3) * sizeof(float) +
+                        8 * 32 * sizeof(float2) + 64;
+    if (smem > 227 * 1024 || !h->ct_off1) return GPTB_ERR_UNSUPPORTED;
+    ContractFwdParams p;
+    p.T = T; p.w = w_group; p.off1 = h->ct_off1; p.fh = fh_group; p.mean_acc = mean_acc; p.mean_scale = mean_scale;
+    p.bs = bs; p.mpad = mpad;
+    p.DP = (c.D + 3) & ~3; p.r = c.r; p.Q = c.Q; p.ncols_total = ncols_total;
+    const int64_t mext = (bs + 127) / 128 * 128;
+    dim3 grid((unsigned)(mext / CRB), (unsigned)Sg);
+#define GPTB_CONTRACT_CASE(DT)                                                                              \
+    case DT: {                                                                                              \
+        auto kfn = contract_fwd_kernel<DT>;                                                                 \
+        GPTB_CUDA_OK(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        kfn<<<grid, 256, smem, h->stream>>>(p);                                                             \
+    } break;
+    switch (c.D) {
+        GPTB_CONTRACT_CASE(1) GPTB_CONTRACT_CASE(2) GPTB_CONTRACT_CASE(3) GPTB_CONTRACT_CASE(4)
+        GPTB_CONTRACT_CASE(5) GPTB_CONTRACT_CASE(6) GPTB_CONTRACT_CASE(7) GPTB_CONTRACT_CASE(8)
+        GPTB_CONTRACT_CASE(9) GPTB_CONTRACT_CASE(10) GPTB_CONTRACT_CASE(11) GPTB_CONTRACT_CASE(12)
+        GPTB_CONTRACT_CASE(13) GPTB_CONTRACT_CASE(14) GPTB_CONTRACT_CASE(15) GPTB_CONTRACT_CASE(16)
+        default: return GPTB_ERR_UNSUPPORTED;
+    }
+#undef GPTB_CONTRACT_CASE
+    h->launches++;
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    return GPTB_OK;
+}

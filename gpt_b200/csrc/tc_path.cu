@@ -662,7 +662,11 @@ static int launch_bwd_r(gptb_handle *h, const BwdParams &p, int grid, size_t sme
     return GPTB_OK;
 }
 
-int gptb_launch_fwd_tc(gptb_handle *h, const float *XbF, const void *Uimg, int64_t bs, int64_t mpad, float *T) {
+// Forward with an explicit operand geometry: the image has NC columns per hi / lo half (NC a multiple of 16, at most
+// 128), `ncols` of them live; T is [D][ncols][mpad].  The sampler uses (r, rpad); the posterior-predictive sweep packs
+// several samples' factors side by side (ncols = Sg*r), so the features are generated once per sample group.
+int gptb_launch_fwd_tc_cols(gptb_handle *h, const float *XbF, const void *Uimg, const float *uscale, int64_t bs,
+                            int64_t mpad, float *T, int ncols, int NC) {
     const gptb_config &c = h->cfg;
     if (!h->ZbF_valid) {
         GPTB_TRY(gptb_tc_prepare_features(h));
@@ -672,34 +676,87 @@ int gptb_launch_fwd_tc(gptb_handle *h, const float *XbF, const void *Uimg, int64
     p.XbF = XbF;
     p.Uimg = (const __half *)Uimg;
     p.ZbF = (const float2 *)h->ZbF;
-    p.uscale = h->tc_state + (Uimg == h->Uimg ? 4 : 7);
+    p.uscale = uscale;
     p.T = T;
     p.amp = (float)h->amp;
-    p.D = c.D; p.n = c.n; p.npad = h->npad; p.r = c.r;
+    p.D = c.D; p.n = c.n; p.npad = h->npad; p.r = ncols;
     p.bs = bs;
     p.mpad = mpad;
     p.mext = (bs + 127) / 128 * 128;   // only the 128-row tiles that hold live rows are generated
     p.sincos = c.feature_kind == GPTB_FEAT_SINCOS;
     // K parts: the image of one part (plus its (zt,b) table) must fit in shared memory
     const int NCH = h->npad / KC;
-    const size_t chunk_bytes = (size_t)KC * (2 * h->rpad * 2 + sizeof(float2));
+    const size_t chunk_bytes = (size_t)KC * (2 * NC * 2 + sizeof(float2));
     const size_t budget = 227 * 1024 - sizeof(Bars) - 1024;
     const int max_chunks = (int)(budget / chunk_bytes);
     p.P = (NCH + max_chunks - 1) / max_chunks;
     p.NCHp = (NCH + p.P - 1) / p.P;
-    if (p.P > 1) GPTB_CUDA_OK(h, cudaMemsetAsync(T, 0, sizeof(float) * (size_t)c.D * c.r * mpad, h->stream));
+    if (p.P > 1) GPTB_CUDA_OK(h, cudaMemsetAsync(T, 0, sizeof(float) * (size_t)c.D * ncols * mpad, h->stream));
     const int nunits = (int)(p.mext / 128) * c.D * p.P;
     const int grid = std::max(1, std::min(h->sm_count, nunits));
     // at least 120 KB so that two CTAs (each wants all 512 TMEM columns) never share an SM
     const size_t smem = std::max<size_t>((size_t)p.NCHp * chunk_bytes + sizeof(Bars) + 64, 120 * 1024);
     int st;
-    switch (h->rpad) {
+    switch (NC) {
         case 16: st = launch_fwd_r<16>(h, p, grid, smem); break;
         case 32: st = launch_fwd_r<32>(h, p, grid, smem); break;
         case 48: st = launch_fwd_r<48>(h, p, grid, smem); break;
-        default: st = launch_fwd_r<64>(h, p, grid, smem); break;
+        case 64: st = launch_fwd_r<64>(h, p, grid, smem); break;
+        case 80: st = launch_fwd_r<80>(h, p, grid, smem); break;
+        case 96: st = launch_fwd_r<96>(h, p, grid, smem); break;
+        case 112: st = launch_fwd_r<112>(h, p, grid, smem); break;
+        case 128: st = launch_fwd_r<128>(h, p, grid, smem); break;
+        default:
+            gptb_set_error(h, "tensor-core forward: unsupported operand width %d", NC);
+            return GPTB_ERR_UNSUPPORTED;
     }
     GPTB_TRY(st);
+    h->launches++;
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    return GPTB_OK;
+}
+
+int gptb_launch_fwd_tc(gptb_handle *h, const float *XbF, const void *Uimg, int64_t bs, int64_t mpad, float *T) {
+    return gptb_launch_fwd_tc_cols(h, XbF, Uimg, h->tc_state + (Uimg == h->Uimg ? 4 : 7), bs, mpad, T, h->cfg.r, h->rpad);
+}
+
+// Operand image of a group of Sg posterior samples side by side: column s*r + l of dimension k is U_s[:, l, k].
+__global__ void pack_Ugroup_kernel(const double *__restrict__ Ug /*[Sg][D][r][n]*/, int Sg, int D, int n, int r, int npad,
+                                   int NC, const float *__restrict__ scale, __half *__restrict__ img) {
+    const float sc = scale[0];
+    const size_t total = (size_t)D * npad * NC;
+    for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const int j = (int)(t % npad);
+        const int nn = (int)((t / npad) % NC);
+        const int k = (int)(t / ((size_t)npad * NC));
+        const int s = nn / r, l = nn - s * r;
+        float v = 0.f;
+        if (j < n && s < Sg) v = (float)(Ug[(((size_t)s * D + k) * r + l) * n + j] * (double)sc);
+        const __half hh = __float2half_rn(v);
+        img[gptb_uimg_offset(k, j, nn, npad, NC)] = hh;
+        img[gptb_uimg_offset(k, j, NC + nn, npad, NC)] = __float2half_rn(v - __half2float(hh));
+    }
+}
+
+// max|U| over `cnt` doubles -> power-of-two scale in tc_state[7..8] (prediction slot)
+int gptb_tc_pred_scale(gptb_handle *h, const double *U, size_t cnt, bool first) {
+    if (first) GPTB_CUDA_OK(h, cudaMemsetAsync(h->tc_state + 6, 0, sizeof(float), h->stream));
+    absmax_kernel<<<std::min<int>(h->sm_count, (int)((cnt + 1023) / 1024)), 1024, 0, h->stream>>>(U, cnt, h->tc_state + 6);
+    h->launches++;
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    return GPTB_OK;
+}
+int gptb_tc_pred_scale_commit(gptb_handle *h) {
+    set_scale_kernel<<<1, 1, 0, h->stream>>>(h->tc_state + 6, h->tc_state + 7, 0);
+    h->launches++;
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    return GPTB_OK;
+}
+int gptb_tc_pack_group(gptb_handle *h, const double *Ug, int Sg, int NC, void *img) {
+    const gptb_config &c = h->cfg;
+    const size_t total = (size_t)c.D * h->npad * NC;
+    pack_Ugroup_kernel<<<(int)std::min<size_t>((total + 255) / 256, (size_t)h->sm_count * 8), 256, 0, h->stream>>>(
+        Ug, Sg, c.D, c.n, c.r, h->npad, NC, h->tc_state + 7, (__half *)img);
     h->launches++;
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;
