@@ -61,6 +61,7 @@ struct gptb_handle {
     int32_t *grp_ptr = nullptr;   // [D*rpad+1] CSR over (k,l): which q have I[q,k] = l (contract.cu pass 2)
     uint16_t *grp_q = nullptr;    // [Q*D]
     int32_t *ct_off1 = nullptr, *ct_lptr = nullptr, *ct_lists = nullptr;   // offset tables of contract_tc.cu
+    int ct_nlists = 0;
 
     // training data
     int64_t N = 0;

@@ -31,7 +31,7 @@
 namespace {
 
 constexpr int CRB = 64;          // rows per CTA
-constexpr int CNW = 16;          // warps per CTA: the gathers are latency-bound chains (offset load -> LDS -> FMUL2),
+constexpr int CNW = 24;          // warps per CTA: the gathers are latency-bound chains (offset load -> LDS -> FMUL2),
                                  // and 128+ KB of tiles allow one CTA per SM, so the CTA itself must bring the warps
 constexpr int CT_THREADS = 32 * CNW;
 
@@ -49,6 +49,7 @@ struct ContractTcParams {
     int64_t bs, mpad;
     double escale;
     int DP, r, rpad, Q, want_grad;
+    int n_lists;             // entries of `lists` (multiple of 4)
 };
 
 __device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
@@ -68,6 +69,13 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     float2 *Vs = Ts + (size_t)DR * 32;                           // [Q + 1][32], row Q is zero
     float *ws = reinterpret_cast<float *>(Vs + (size_t)(Q + 1) * 32);   // [Q rounded up to 4]
     float2 *Fs = reinterpret_cast<float2 *>(ws + ((Q + 3) & ~3)); // [CNW][32]
+    // the (uniform) gather offsets, staged once per CTA: every use is then an LDS broadcast instead of a global load
+    int4 *off1s = reinterpret_cast<int4 *>(Fs + CNW * 32);       // [Q][DP4]
+    int4 *lists_s = off1s + (size_t)Q * DP4;                     // [n_lists / 4]
+    int *lptr_s = reinterpret_cast<int *>(lists_s + p.n_lists / 4);   // [D*rpad + 1]
+    for (int t = tid; t < Q * DP4; t += CT_THREADS) off1s[t] = __ldg(reinterpret_cast<const int4 *>(p.off1) + t);
+    for (int t = tid; t < p.n_lists / 4; t += CT_THREADS) lists_s[t] = __ldg(reinterpret_cast<const int4 *>(p.lists) + t);
+    for (int t = tid; t <= D * rpad; t += CT_THREADS) lptr_s[t] = __ldg(p.lptr + t);
 
     for (int t = tid; t < Q; t += CT_THREADS) ws[t] = (float)p.w[t];
     if (wp == 0) Vs[(size_t)Q * 32 + lane] = make_float2(0.f, 0.f);
@@ -78,21 +86,27 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     // ---- pass 1: V and fhat
     const float2 *Trow = Ts + lane;
     float2 f = make_float2(0.f, 0.f);
-#pragma unroll 2
-    for (int q = wp; q < Q; q += CNW) {
-        const int4 *o = reinterpret_cast<const int4 *>(p.off1) + (size_t)q * DP4;
-        float2 v = make_float2(1.f, 1.f);
+    for (int q0 = wp; q0 < Q; q0 += 2 * CNW) {       // two independent product chains per iteration
+        const int q1 = q0 + CNW;
+        const bool has1 = q1 < Q;
+        const int4 *o0 = off1s + (size_t)q0 * DP4, *o1 = off1s + (size_t)(has1 ? q1 : q0) * DP4;
+        float2 v0 = make_float2(1.f, 1.f), v1 = make_float2(1.f, 1.f);
 #pragma unroll
         for (int g4 = 0; g4 < DP4; ++g4) {
-            const int4 oo = __ldg(o + g4);
-            if (g4 * 4 + 0 < D) v = mul2(v, Trow[oo.x]);
-            if (g4 * 4 + 1 < D) v = mul2(v, Trow[oo.y]);
-            if (g4 * 4 + 2 < D) v = mul2(v, Trow[oo.z]);
-            if (g4 * 4 + 3 < D) v = mul2(v, Trow[oo.w]);
+            const int4 a = o0[g4], b = o1[g4];
+            if (g4 * 4 + 0 < D) { v0 = mul2(v0, Trow[a.x]); v1 = mul2(v1, Trow[b.x]); }
+            if (g4 * 4 + 1 < D) { v0 = mul2(v0, Trow[a.y]); v1 = mul2(v1, Trow[b.y]); }
+            if (g4 * 4 + 2 < D) { v0 = mul2(v0, Trow[a.z]); v1 = mul2(v1, Trow[b.z]); }
+            if (g4 * 4 + 3 < D) { v0 = mul2(v0, Trow[a.w]); v1 = mul2(v1, Trow[b.w]); }
         }
-        Vs[(size_t)q * 32 + lane] = v;
-        const float wq = ws[q];
-        f = __ffma2_rn(make_float2(wq, wq), v, f);
+        Vs[(size_t)q0 * 32 + lane] = v0;
+        const float w0 = ws[q0];
+        f = __ffma2_rn(make_float2(w0, w0), v0, f);
+        if (has1) {
+            Vs[(size_t)q1 * 32 + lane] = v1;
+            const float w1 = ws[q1];
+            f = __ffma2_rn(make_float2(w1, w1), v1, f);
+        }
     }
     Fs[wp * 32 + lane] = f;
     __syncthreads();
@@ -150,21 +164,36 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     for (int u = wp; u < D * nlb; u += CNW) {
         const int k = u / nlb, lb = u - k * nlb;
         float2 out[8];
+        // the eight lists of this unit advance together (independent gathers); exhausted lists read the zero row
+        int pb[9];
+#pragma unroll
+        for (int j = 0; j < 9; ++j) pb[j] = lptr_s[k * rpad + lb * 8 + j];
+        int maxlen = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) maxlen = max(maxlen, pb[j + 1] - pb[j]);
+        float2 sum[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sum[j] = make_float2(0.f, 0.f);
+        const int zq = Q * 32;
+        for (int g = 0; g < maxlen; g += 4) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int pp = pb[j] + g;
+                int4 oo = make_int4(zq, zq, zq, zq);
+                if (pp < pb[j + 1]) oo = lists_s[pp >> 2];
+                sum[j] = add2(sum[j], add2(add2(Vrow[oo.x], Vrow[oo.y]), add2(Vrow[oo.z], Vrow[oo.w])));
+            }
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const int l = lb * 8 + j;
-            const int p0 = __ldg(p.lptr + k * rpad + l), p1 = __ldg(p.lptr + k * rpad + l + 1);
+            const int p0 = pb[j], p1 = pb[j + 1];
             float2 val = make_float2(0.f, 0.f);
             if (p1 > p0) {  // uniform across the CTA
-                float2 sum = make_float2(0.f, 0.f);
-                for (int pp = p0; pp < p1; pp += 4) {
-                    const int4 oo = __ldg(reinterpret_cast<const int4 *>(p.lists + pp));
-                    sum = add2(sum, add2(add2(Vrow[oo.x], Vrow[oo.y]), add2(Vrow[oo.z], Vrow[oo.w])));
-                }
                 const float2 t = Trow[(k * r + l) * 32];
                 if (t.x != 0.f && t.y != 0.f) {
-                    val.x = e.x * __fdividef(sum.x, t.x);
-                    val.y = e.y * __fdividef(sum.y, t.y);
+                    val.x = e.x * __fdividef(sum[j].x, t.x);
+                    val.y = e.y * __fdividef(sum[j].y, t.y);
                 } else {  // exact zero factor: explicit leave-one-out products
                     float2 acc = make_float2(0.f, 0.f);
                     for (int pp = p0; pp < p1; ++pp) {
@@ -175,8 +204,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
                             if (kk != k) v = mul2(v, Trow[__ldg(p.off1 + (size_t)q * p.DP + kk)]);
                         acc = add2(acc, v);
                     }
-                    val.x = live0 ? (t.x != 0.f ? e.x * __fdividef(sum.x, t.x) : e.x * acc.x) : 0.f;
-                    val.y = live1 ? (t.y != 0.f ? e.y * __fdividef(sum.y, t.y) : e.y * acc.y) : 0.f;
+                    val.x = live0 ? (t.x != 0.f ? e.x * __fdividef(sum[j].x, t.x) : e.x * acc.x) : 0.f;
+                    val.y = live1 ? (t.y != 0.f ? e.y * __fdividef(sum[j].y, t.y) : e.y * acc.y) : 0.f;
                 }
             }
             out[j] = val;
@@ -225,6 +254,7 @@ int gptb_contract_tc_build_tables(gptb_handle *h, const int32_t *Iz) {
         for (int q = 0; q < c.Q; ++q) cnt[(size_t)k * h->rpad + Iz[(size_t)k * c.Q + q]]++;
     for (size_t g = 0; g < ngrp; ++g) ptr[g + 1] = ptr[g] + ((cnt[g] + 3) & ~3);
     std::vector<int32_t> lists((size_t)ptr[ngrp] + 4, c.Q * 32);
+    h->ct_nlists = (int)lists.size();
     {
         std::vector<int32_t> fill(ptr.begin(), ptr.end() - 1);
         for (int k = 0; k < c.D; ++k)
@@ -246,8 +276,10 @@ int gptb_contract_tc_build_tables(gptb_handle *h, const int32_t *Iz) {
 
 size_t gptb_contract_tc_smem(const gptb_handle *h) {
     const gptb_config &c = h->cfg;
+    const size_t DP4 = (c.D + 3) / 4;
     return ((size_t)c.D * c.r * 32 + (size_t)(c.Q + 1) * 32 + (size_t)CNW * 32) * sizeof(float2) +
-           (size_t)((c.Q + 3) & ~3) * sizeof(float) + 64;
+           (size_t)((c.Q + 3) & ~3) * sizeof(float) + (size_t)c.Q * DP4 * 16 + (size_t)h->ct_nlists * 4 +
+           ((size_t)c.D * h->rpad + 4) * 4 + 64;
 }
 
 // Returns GPTB_ERR_UNSUPPORTED (without an error message) when the shape does not fit; the caller then
@@ -274,6 +306,7 @@ int gptb_launch_contract_tc(gptb_handle *h, const float *T, const double *w, con
     p.escale = escale;
     p.DP = (c.D + 3) & ~3; p.r = c.r; p.rpad = h->rpad; p.Q = c.Q;
     p.want_grad = want_grad ? 1 : 0;
+    p.n_lists = h->ct_nlists;
     const int64_t mext = (bs + 127) / 128 * 128;  // rows beyond bs inside the last 128-tile are dead (zeros)
     dim3 grid((unsigned)(mext / CRB));
 #define GPTB_CONTRACT_CASE(DT)                                                                              \
