@@ -5,7 +5,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libgptb200.so")
+# GPTB200_LIB: developer override used to time two builds of the library in the same process environment
+LIB_PATH = os.environ.get("GPTB200_LIB") or os.path.join(_HERE, "lib", "libgptb200.so")
 
 c_double_p = C.POINTER(C.c_double)
 c_int32_p = C.POINTER(C.c_int32)

@@ -38,8 +38,11 @@ namespace {
 
 using namespace tcx;
 
-constexpr int NGEN = 4;       // generator warpgroups (4 warps each, one per TMEM lane quarter)
-constexpr int TC_THREADS = 256 + 128 * NGEN;
+constexpr int HSPLIT = 1;     // warps per TMEM lane quarter that share one chunk (each takes 64/HSPLIT of its K columns)
+constexpr int NGEN = 4 / HSPLIT;   // generator groups (4*HSPLIT warps each); chunks go to the groups round-robin.
+                              // Fewer, wider groups keep fewer A stages "in generation" and leave more of the ring
+                              // as slack between the generators and the MMA issuers.
+constexpr int TC_THREADS = 256 + 512;
 constexpr int KC = 64;        // K elements per chunk (4 MMA K-steps of 16)
 constexpr int SA_COLS = 64;   // TMEM columns of one A stage (32 hi + 32 lo, two fp16 per column)
 constexpr int NSTA_MAX = 8;
@@ -104,10 +107,11 @@ struct FwdParams {
 // 64 features of one row -> the hi / lo words of one A stage.
 // cos features: table entry p (float4) = (zt[2p], zt[2p+1], b[2p], b[2p+1]);  sin/cos: entry p (float2) = (zt[p], -).
 template <bool THREE>
-__device__ __forceinline__ void gen_fwd_chunk(const float2 *zb64, float x, bool sincos, uint32_t st_addr) {
+__device__ __forceinline__ void gen_fwd_chunk(const float2 *zb64, float x, bool sincos, uint32_t st_addr, int half0) {
     const float2 x2 = make_float2(x, x);
 #pragma unroll
-    for (int half = 0; half < 2; ++half) {
+    for (int hh = 0; hh < 2 / HSPLIT; ++hh) {
+        const int half = half0 + hh;
         uint32_t hi[16], lo[16];
         if (!sincos) {
             const float4 *zb = reinterpret_cast<const float4 *>(zb64 + half * 32);
@@ -131,10 +135,17 @@ __device__ __forceinline__ void gen_fwd_chunk(const float2 *zb64, float x, bool 
 }
 
 // Resident-U forward.  Units u = (k*P + part)*ntiles + tile, CTA c owns [nunits*c/G, nunits*(c+1)/G).
+//
+// One thread can issue a small-N tcgen05.mma only every ~44 clk (~65 clk while the generators keep its SM
+// sub-partition busy; tools/ubench/mma.cu), three times the tensor pipe's N/2 clk floor at N = 32, and twelve of
+// them per chunk made the single issuer the bottleneck of the kernel.  For RPAD <= 64 two warps issue (NI = 2):
+// issuer w takes the chunks ch = w (mod 2) of every unit and accumulates into its own columns, the epilogue adds
+// the two partial tiles.
 template <int RPAD, bool THREE>
 __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    constexpr int NSTA = nsta_for(2 * RPAD);
+    constexpr int NI = RPAD <= 64 ? 2 : 1;
+    constexpr int NSTA = nsta_for(2 * NI * RPAD);
     constexpr int ACC_BASE = NSTA * SA_COLS;
     constexpr int ROW_BYTES = 2 * RPAD * 2;                  // image bytes per feature j (hi|lo)
     const size_t u_cap = (size_t)p.NCHp * KC * ROW_BYTES;   // shared-memory bytes of one K part of the image
@@ -150,10 +161,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
     const int u1 = (int)((int64_t)nunits * (blockIdx.x + 1) / gridDim.x);
 
     if (tid == 0) {
-        for (int s = 0; s < NSTA_MAX; ++s) { mbar_init(&bars->a_full[s], 4); mbar_init(&bars->a_empty[s], 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(&bars->acc_full[s], 1); mbar_init(&bars->acc_empty[s], 128); }
+        for (int s = 0; s < NSTA_MAX; ++s) { mbar_init(&bars->a_full[s], 4 * HSPLIT); mbar_init(&bars->a_empty[s], 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&bars->acc_full[s], NI); mbar_init(&bars->acc_empty[s], 128); }
         mbar_init(&bars->u_full, 1);
-        mbar_init(&bars->u_empty, 1);
+        mbar_init(&bars->u_empty, NI);
         fence_barrier_init();
     }
     if (warp == 4) tmem_alloc(&bars->tmem_base, 512);
@@ -165,8 +176,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
 
     if (warp >= 8) {
         // ---------------------------------------------------------------- feature generators (lane = row)
-        const int g = (warp - 8) >> 2;
+        const int g = (warp - 8) / (4 * HSPLIT);
         const int q = warp & 3;
+        const int half0 = (((warp - 8) >> 2) % HSPLIT) * (2 / HSPLIT);
         const int row = q * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
         // this warpgroup takes chunks cg = g, g+NGEN, ... of the CTA's chunk sequence; (u, ch) follow incrementally
@@ -199,7 +211,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
             mbar_wait(&bars->a_empty[sa], pa);
             fence_after_sync();
             const uint32_t st_addr = tmem + lane_addr + sa * SA_COLS;
-            gen_fwd_chunk<THREE>(sZb + (p.sincos ? ch * KC / 2 : ch * KC), x, p.sincos != 0, st_addr);
+            gen_fwd_chunk<THREE>(sZb + (p.sincos ? ch * KC / 2 : ch * KC), x, p.sincos != 0, st_addr, half0);
             wait_st();
             fence_before_sync();
             __syncwarp();
@@ -208,10 +220,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
             sa += NGEN;
             if (sa >= NSTA) { sa -= NSTA; pa ^= 1; }
         }
-    } else if (warp == 4) {
-        // ---------------------------------------------------------------- MMA issuer (whole warp runs the loop)
-        uint32_t it = 0, gen = 0, pa = 0;
-        int cur_k = -1, sa = 0;
+    } else if (warp == 4 || (NI == 2 && warp == 6)) {
+        // ---------------------------------------------------------------- MMA issuers (whole warp runs the loop)
+        const int w = (warp - 4) >> 1;
+        uint32_t it = 0, gen = 0, cbase = 0;   // cbase: chunks of the CTA before this unit (-> A stage and parity)
+        int cur_k = -1;
         for (int u = u0; u < u1; ++u, ++it) {
             const int grp = u / ntiles;
             if (grp != cur_k) {
@@ -224,8 +237,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
             const uint32_t ab = it & 1;
             mbar_wait(&bars->acc_empty[ab], ((it >> 1) & 1) ^ 1);
             fence_after_sync();
-            const uint32_t d = acc_base + ab * RPAD;
-            for (int ch = 0; ch < nch; ++ch) {
+            const uint32_t d = acc_base + (ab * NI + w) * RPAD;
+            for (int ch = w; ch < nch; ch += NI) {
+                const uint32_t c = cbase + ch, sa = c % NSTA, pa = (c / NSTA) & 1;
                 mbar_wait(&bars->a_full[sa], pa);
                 fence_after_sync();
                 const uint32_t a_hi = tmem + sa * SA_COLS, a_lo = a_hi + 32;
@@ -234,16 +248,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
 #pragma unroll
                     for (int s4 = 0; s4 < KC / 16; ++s4)
                         mma_kstep<RPAD, THREE, 0>(d, a_hi + s4 * 8, a_lo + s4 * 8, b_addr + s4 * 16 * ROW_BYTES,
-                                                  (ch | s4) != 0);
+                                                  (ch >= NI || s4 != 0) ? 1u : 0u);
                     mma_commit(&bars->a_empty[sa]);
-                    if (ch == nch - 1) {
-                        mma_commit(&bars->acc_full[ab]);
-                        if (last_of_k) mma_commit(&bars->u_empty);
-                    }
                 }
                 __syncwarp();
-                if (++sa == NSTA) { sa = 0; pa ^= 1; }
             }
+            if (elect_one()) {
+                // an issuer without a chunk in this unit (nch < NI) has nothing to track: commit arrives at once
+                mma_commit(&bars->acc_full[ab]);
+                if (last_of_k) mma_commit(&bars->u_empty);
+            }
+            __syncwarp();
+            cbase += nch;
         }
     } else if (warp == 5) {
         // ---------------------------------------------------------------- U / (zt,b) loader: once per k
@@ -281,20 +297,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
             const uint32_t ab = it & 1;
             mbar_wait(&bars->acc_full[ab], (it >> 1) & 1);
             fence_after_sync();
-            const uint32_t d = acc_base + ab * RPAD + lane_addr;
+            const uint32_t d = acc_base + ab * NI * RPAD + lane_addr;
+            const bool two = NI == 2 && min(p.NCHp, NCH - (grp % p.P) * p.NCHp) >= 2;
             const int64_t i = (int64_t)tile * 128 + row;
             const bool live = i < p.bs;
             float *Tk = p.T + (size_t)k * p.r * p.mpad + i;
 #pragma unroll
             for (int c0 = 0; c0 < RPAD; c0 += 16) {
-                uint32_t v[16];
+                uint32_t v[16], v1[16];
                 tmem_ld16(d + c0, v);
+                if (two) tmem_ld16(d + RPAD + c0, v1);
                 wait_ld();
 #pragma unroll
                 for (int c = 0; c < 16; ++c) {
                     const int l = c0 + c;
                     if (l < p.r) {
-                        const float val = live ? __uint_as_float(v[c]) * scale : 0.f;
+                        float acc = __uint_as_float(v[c]);
+                        if (two) acc += __uint_as_float(v1[c]);
+                        const float val = live ? acc * scale : 0.f;
                         if (p.P == 1) Tk[(size_t)l * p.mpad] = val;
                         else atomicAdd(Tk + (size_t)l * p.mpad, val);
                     }
@@ -343,6 +363,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
     Bars *bars = reinterpret_cast<Bars *>(smem_raw + NSTB * B_STAGE_BYTES);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    constexpr int NIB = 2;   // MMA issuers (see fwd_tc_kernel): issuer w takes the feature blocks jbl = w (mod 2)
     const int JB = p.npad / 128, JG = p.JG, NJG = p.NJG, NSTA = p.nsta;
     const int NCH = (int)(p.mext / KC);
     const int64_t total = (int64_t)p.D * NJG * NCH;
@@ -352,9 +373,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
     const uint32_t n_as = n_it * JG;
 
     if (tid == 0) {
-        for (int s = 0; s < NSTA_MAX; ++s) { mbar_init(&bars->a_full[s], 4); mbar_init(&bars->a_empty[s], 1); }
-        for (int s = 0; s < NSTB; ++s) { mbar_init(&bars->b_full[s], 1); mbar_init(&bars->b_empty[s], 1); }
-        mbar_init(&bars->acc_full[0], 1);
+        for (int s = 0; s < NSTA_MAX; ++s) { mbar_init(&bars->a_full[s], 4 * HSPLIT); mbar_init(&bars->a_empty[s], 1); }
+        for (int s = 0; s < NSTB; ++s) { mbar_init(&bars->b_full[s], 1); mbar_init(&bars->b_empty[s], NIB); }
+        mbar_init(&bars->acc_full[0], NIB);
         mbar_init(&bars->acc_empty[0], 128);
         fence_barrier_init();
     }
@@ -367,8 +388,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
 
     if (warp >= 8) {
         // ---------------------------------------------------------------- feature generators (lane = feature)
-        const int g = (warp - 8) >> 2;
+        const int g = (warp - 8) / (4 * HSPLIT);
         const int q = warp & 3;
+        const int half0 = (((warp - 8) >> 2) % HSPLIT) * (2 / HSPLIT);
         const int jl = q * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
         // position of A step `as`: item lit (-> grp, ch) and block jbl
@@ -377,11 +399,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
         while (jbl >= JG) { jbl -= JG; ++lit; if (++ch == NCH) { ch = 0; ++grp; } }
         int sa = g % NSTA;
         uint32_t pa = ((g / NSTA) & 1) ^ 1;
-        for (uint32_t as = g; as < n_as; as += NGEN) {
-            const int k = grp / NJG, jg = grp - k * NJG;
-            int j = (jg * JG + jbl) * 128 + jl;
+        // (zt, b) of this lane's feature in A step (grp, jbl).  (Fetching them one step ahead was measured 20%
+        // slower for the whole kernel, A/B in the same run; the load latency here overlaps the barrier waits.)
+        auto load_zb = [&](int grp_, int jbl_, float &zt, float &bb) {
+            const int k = grp_ / NJG, jg = grp_ - k * NJG;
+            int j = (jg * JG + jbl_) * 128 + jl;
             if (j >= p.npad) j = p.npad - 1;    // padding block of a ragged last group: computed, never stored
-            float zt, bb;
             if (!p.sincos) {
                 zt = p.ZtF[(size_t)k * p.npad + j];
                 bb = p.bF[(size_t)k * p.npad + j];
@@ -389,15 +412,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
                 zt = p.ZtF[(size_t)k * p.npad + (j >> 1)];
                 bb = (j & 1) ? 1.5707963267948966f : 0.f;
             }
+        };
+        for (uint32_t as = g; as < n_as; as += NGEN) {
+            float zt, bb;
+            load_zb(grp, jbl, zt, bb);
             const float2 zt2 = make_float2(zt, zt), bb2 = make_float2(bb, bb);
             const int sb = lit % NSTB;
+            const uint32_t lit_cur = lit;
+            jbl += NGEN;
+            while (jbl >= JG) { jbl -= JG; ++lit; if (++ch == NCH) { ch = 0; ++grp; } }
             mbar_wait(&bars->a_empty[sa], pa);
             fence_after_sync();
-            mbar_wait(&bars->b_full[sb], (lit / NSTB) & 1);
+            mbar_wait(&bars->b_full[sb], (lit_cur / NSTB) & 1);
             const uint32_t st_addr = tmem + lane_addr + sa * SA_COLS;
             const float4 *xr = reinterpret_cast<const float4 *>(sB + sb * B_STAGE_BYTES + B_IMG_BYTES);
 #pragma unroll
-            for (int half = 0; half < 2; ++half) {
+            for (int hh = 0; hh < 2 / HSPLIT; ++hh) {
+                const int half = half0 + hh;
                 uint32_t hi[16], lo[16];
 #pragma unroll
                 for (int c = 0; c < 16; c += 2) {
@@ -419,16 +450,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
             fence_before_sync();
             __syncwarp();
             if (lane == 0) mbar_arrive(&bars->a_full[sa]);   // one arrival per warp: 32 lanes on one mbarrier serialise
-
-            jbl += NGEN;
-            while (jbl >= JG) { jbl -= JG; ++lit; if (++ch == NCH) { ch = 0; ++grp; } }
             sa += NGEN;
             while (sa >= NSTA) { sa -= NSTA; pa ^= 1; }
         }
-    } else if (warp == 4) {
-        // ---------------------------------------------------------------- MMA issuer (whole warp runs the loop)
-        uint32_t seg = 0, pa = 0;
-        int ch = ch0, sa = 0;
+    } else if (warp == 4 || warp == 6) {
+        // ---------------------------------------------------------------- MMA issuers (whole warp runs the loop)
+        const int w = (warp - 4) >> 1;
+        uint32_t seg = 0;
+        int ch = ch0;
         bool fresh = true;
         for (uint32_t lit = 0; lit < n_it; ++lit) {
             if (fresh) {
@@ -439,7 +468,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
             mbar_wait(&bars->b_full[sb], (lit / NSTB) & 1);
             const uint32_t b_addr = smem_u32(sB + sb * B_STAGE_BYTES);
             const bool last = (ch == NCH - 1) || (lit == n_it - 1);
-            for (int jbl = 0; jbl < JG; ++jbl) {
+            for (int jbl = w; jbl < JG; jbl += NIB) {
+                const uint32_t as = lit * JG + jbl, sa = as % (uint32_t)NSTA, pa = (as / (uint32_t)NSTA) & 1;
                 mbar_wait(&bars->a_full[sa], pa);
                 fence_after_sync();
                 const uint32_t a_hi = tmem + sa * SA_COLS, a_lo = a_hi + 32;
@@ -450,14 +480,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
                         mma_kstep<RPAD, THREE, 1>(d, a_hi + s4 * 8, a_lo + s4 * 8, b_addr + s4 * 16 * ROW_BYTES,
                                                   (!fresh || s4 != 0) ? 1u : 0u);
                     mma_commit(&bars->a_empty[sa]);
-                    if (jbl == JG - 1) {
-                        mma_commit(&bars->b_empty[sb]);
-                        if (last) mma_commit(&bars->acc_full[0]);
-                    }
                 }
                 __syncwarp();
-                if (++sa == NSTA) { sa = 0; pa ^= 1; }
             }
+            if (elect_one()) {   // (an issuer without a block of its own, JG == 1, tracks nothing: arrives at once)
+                mma_commit(&bars->b_empty[sb]);
+                if (last) mma_commit(&bars->acc_full[0]);
+            }
+            __syncwarp();
             fresh = false;
             ++ch;
             if (last) { ch = 0; ++seg; fresh = true; }
