@@ -53,6 +53,9 @@ PROTOTYPES = {
                                  c_double_p, c_double_p]),
     "gptb_sgld_step_host": (C.c_int, [H, C.c_double, c_double_p, c_double_p, C.c_int64, C.c_int64, C.c_double,
                                       C.c_double, C.c_int32, c_double_p, c_double_p, c_double_p]),
+    "gptb_sgld_step_host_submit": (C.c_int, [H, C.c_double, c_double_p, c_double_p, C.c_int64, C.c_int64, C.c_double,
+                                      C.c_double, C.c_int32, c_double_p, c_double_p, c_double_p]),
+    "gptb_sgld_step_host_wait": (C.c_int, [H]),
     "gptb_sgld_run": (C.c_int, [H, C.c_double, C.c_int64, C.c_double, C.c_double, C.c_int32, C.c_int32, C.c_int32,
                                 c_int64_p, c_double_p, c_double_p, c_double_p, c_double_p]),
     "gptb_sgld_advance": (C.c_int, [H, C.c_double, C.c_int64, C.c_double, C.c_double, C.c_int32, C.c_int64]),

@@ -422,6 +422,13 @@ int gptb_destroy(gptb_handle *h) {
     if (h->pUimg) cudaFree(h->pUimg);
     if (h->ZbF) cudaFree(h->ZbF);
     dev_free(&h->stage_cm); dev_free(&h->stage_rm); dev_free(&h->stage_y);
+    for (int i = 0; i < 2; ++i) {
+        dev_free(&h->pipe_cm[i]); dev_free(&h->pipe_y[i]);
+        if (h->pipe_staged[i]) cudaEventDestroy(h->pipe_staged[i]);
+        if (h->pipe_done[i]) cudaEventDestroy(h->pipe_done[i]);
+    }
+    if (h->pipe_nan_host) cudaFreeHost(h->pipe_nan_host);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     dev_free(&h->Xb); dev_free(&h->yb); dev_free(&h->fhat); dev_free(&h->XbF);
     if (h->T) cudaFree(h->T);
     if (h->E) cudaFree(h->E);
@@ -1056,6 +1063,84 @@ int gptb_sgld_step_host(gptb_handle *h, double signal_var, const double *Xb, con
     if (flags & GPTB_FLAG_STIEFEL) return check_nan(h);
     GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
     return GPTB_OK;
+}
+
+static int pipe_wait_oldest(gptb_handle *h, int *step_status) {
+    const int slot = (int)(h->pipe_waited & 1);
+    GPTB_CUDA_OK(h, cudaEventSynchronize(h->pipe_done[slot]));
+    ++h->pipe_waited;
+    *step_status = GPTB_OK;
+    if (h->pipe_stiefel[slot] && h->pipe_nan_host[slot]) {
+        gptb_set_error(h, "Get NaN when moving along Geodesic. Try smaller epsU");   // GPT_SGLD.jl:25
+        *step_status = GPTB_GEODESIC_NAN;
+    }
+    return GPTB_OK;
+}
+
+int gptb_sgld_step_host_submit(gptb_handle *h, double signal_var, const double *Xb, const double *yb, int64_t bs,
+                               int64_t N_total, double epsw, double epsU, int32_t flags, const double *noise_w,
+                               const double *noise_U, double *w_out) {
+    if (!h || !Xb || !yb || bs < 1 || N_total < 1 || !(signal_var > 0)) return GPTB_ERR_ARG;
+    if (!h->have_features || !h->have_index || !h->have_params) {
+        gptb_set_error(h, "features / index / parameters must be set before gptb_sgld_step_host_submit");
+        return GPTB_ERR_STATE;
+    }
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    const gptb_config &c = h->cfg;
+    if (!h->copy_stream) {
+        GPTB_CUDA_OK(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        for (int s = 0; s < 2; ++s) {
+            GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&h->pipe_staged[s], cudaEventDisableTiming));
+            GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&h->pipe_done[s], cudaEventDisableTiming));
+        }
+        GPTB_CUDA_OK(h, cudaMallocHost((void **)&h->pipe_nan_host, 2 * sizeof(int32_t)));
+        h->pipe_nan_host[0] = h->pipe_nan_host[1] = 0;
+    }
+    if (h->pipe_submitted - h->pipe_waited >= 2) {   // both slots busy: retire the oldest (status kept sticky on the device)
+        int st_old;
+        GPTB_TRY(pipe_wait_oldest(h, &st_old));
+    }
+    if (h->pipe_cap < bs || h->stage_cap < bs) {
+        GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+        GPTB_CUDA_OK(h, cudaStreamSynchronize(h->copy_stream));
+        for (int s = 0; s < 2; ++s) {
+            GPTB_TRY(dev_alloc(h, &h->pipe_cm[s], (size_t)bs * c.D));
+            GPTB_TRY(dev_alloc(h, &h->pipe_y[s], (size_t)bs));
+        }
+        GPTB_TRY(dev_alloc(h, &h->stage_cm, (size_t)bs * c.D));
+        GPTB_TRY(dev_alloc(h, &h->stage_rm, (size_t)bs * c.D));
+        GPTB_TRY(dev_alloc(h, &h->stage_y, (size_t)bs));
+        h->pipe_cap = h->stage_cap = bs;
+    }
+    const int slot = (int)(h->pipe_submitted & 1);
+    // the slot's previous occupant (two submissions ago) has been waited for or retired above, so the copy may start now
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->pipe_cm[slot], Xb, sizeof(double) * bs * c.D, cudaMemcpyHostToDevice, h->copy_stream));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->pipe_y[slot], yb, sizeof(double) * bs, cudaMemcpyHostToDevice, h->copy_stream));
+    GPTB_CUDA_OK(h, cudaEventRecord(h->pipe_staged[slot], h->copy_stream));
+    GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->pipe_staged[slot], 0));
+    GPTB_TRY(gptb_launch_transpose(h, h->pipe_cm[slot], bs, h->stage_rm));
+    const double *nw = nullptr, *nU = nullptr;
+    GPTB_TRY(stage_noise(h, noise_w, noise_U, &nw, &nU));
+    GPTB_TRY(step_common(h, signal_var, nullptr, bs, N_total, true, h->stage_rm, h->pipe_y[slot], epsw, epsU, flags, nw, nU));
+    if (w_out) GPTB_CUDA_OK(h, cudaMemcpyAsync(w_out, h->w, sizeof(double) * c.Q, cudaMemcpyDeviceToHost, h->stream));
+    h->pipe_stiefel[slot] = (flags & GPTB_FLAG_STIEFEL) != 0;
+    if (h->pipe_stiefel[slot])
+        GPTB_CUDA_OK(h, cudaMemcpyAsync(h->pipe_nan_host + slot, h->nan_flag, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    GPTB_CUDA_OK(h, cudaEventRecord(h->pipe_done[slot], h->stream));
+    ++h->pipe_submitted;
+    return GPTB_OK;
+}
+
+int gptb_sgld_step_host_wait(gptb_handle *h) {
+    if (!h) return GPTB_ERR_ARG;
+    if (h->pipe_submitted == h->pipe_waited) {
+        gptb_set_error(h, "gptb_sgld_step_host_wait: no step in flight");
+        return GPTB_ERR_STATE;
+    }
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    int st;
+    GPTB_TRY(pipe_wait_oldest(h, &st));
+    return st;
 }
 
 int gptb_sgld_run(gptb_handle *h, double signal_var, int64_t m, double epsw, double epsU, int32_t burnin,

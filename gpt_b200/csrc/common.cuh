@@ -85,6 +85,14 @@ struct gptb_handle {
     double *store_w = nullptr, *store_U = nullptr;   // device-side chain stores of gptb_sgld_run
     double *stage_cm = nullptr, *stage_rm = nullptr, *stage_y = nullptr;  // host-minibatch staging
     int64_t stage_cap = 0;
+    // pipelined host steps (gptb_sgld_step_host_submit / _wait): two staging slots filled on a copy stream
+    cudaStream_t copy_stream = nullptr;
+    double *pipe_cm[2] = {nullptr, nullptr}, *pipe_y[2] = {nullptr, nullptr};
+    int64_t pipe_cap = 0;
+    cudaEvent_t pipe_staged[2] = {nullptr, nullptr}, pipe_done[2] = {nullptr, nullptr};
+    int32_t *pipe_nan_host = nullptr;   // pinned, one flag per slot
+    uint64_t pipe_submitted = 0, pipe_waited = 0;
+    bool pipe_stiefel[2] = {false, false};
 
     // batch scratch
     int64_t cap = 0, mpad = 0;

@@ -289,6 +289,20 @@ class Model:
         _check(self.lib.gptb_sgld_step_host(self.h, float(signal_var), _dp(Xb), _dp(yb), Xb.shape[0], int(N_total),
                                             float(epsw), float(epsU), flags, _dp(nw), _dp(nU), _dp(w_out)), self.h)
 
+    def sgld_step_host_submit(self, signal_var, Xb, yb, N_total, epsw, epsU, langevin=True, stiefel=True, noise_w=None,
+                              noise_U=None, w_out=None):
+        """Pipelined sgld_step_host: queues the copy of (Xb, yb) and the step, returns at once.  The arrays must be
+        pinned host memory and stay alive until the matching sgld_step_host_wait()."""
+        nw = _f64(noise_w) if noise_w is not None else None
+        nU = _f64(noise_U) if noise_U is not None else None
+        flags = (L.FLAG_LANGEVIN if langevin else 0) | (L.FLAG_STIEFEL if stiefel else 0)
+        _check(self.lib.gptb_sgld_step_host_submit(self.h, float(signal_var), _dp(Xb), _dp(yb), Xb.shape[0], int(N_total),
+                                                   float(epsw), float(epsU), flags, _dp(nw), _dp(nU), _dp(w_out)), self.h)
+
+    def sgld_step_host_wait(self):
+        """Waits for the oldest submitted host step; raises on a geodesic NaN like sgld_step_host."""
+        _check(self.lib.gptb_sgld_step_host_wait(self.h), self.h)
+
     def sgld_run(self, signal_var, m, epsw, epsU, burnin, maxepoch, langevin=True, stiefel=True, perms=None,
                  noise_w=None, noise_U=None, store=True, N=None):
         Q, n, r, D = self.cfg.Q, self.cfg.n, self.cfg.r, self.cfg.D

@@ -146,6 +146,17 @@ int gptb_sgld_step(gptb_handle *h, double signal_var, const int64_t *idx, int64_
 int gptb_sgld_step_host(gptb_handle *h, double signal_var, const double *Xb, const double *yb, int64_t bs,
                         int64_t N_total, double epsw, double epsU, int32_t flags, const double *noise_w,
                         const double *noise_U, double *w_out);
+/* Pipelined form of gptb_sgld_step_host for a caller that forms minibatch t+1 on the host while step t runs
+ * (the batch of GPT_SGLD.jl:379-381 does not depend on the parameters).  _submit copies Xb, yb (pinned host
+ * memory) on a copy stream into one of two device staging slots, queues the loop body behind the copy and
+ * returns without waiting; Xb, yb and w_out must stay valid until the matching _wait.  _wait blocks until the
+ * OLDEST submitted step has finished: its w_out is then valid and its status (GPTB_OK / GPTB_GEODESIC_NAN) is
+ * returned.  At most two steps are in flight; a third _submit first waits for the oldest (its status is then
+ * reported by the next _wait).  Returns GPTB_ERR_STATE from _wait when nothing is in flight. */
+int gptb_sgld_step_host_submit(gptb_handle *h, double signal_var, const double *Xb, const double *yb, int64_t bs,
+                               int64_t N_total, double epsw, double epsU, int32_t flags, const double *noise_w,
+                               const double *noise_U, double *w_out);
+int gptb_sgld_step_host_wait(gptb_handle *h);
 /* The whole of GPTregression (GPT_SGLD.jl:345-448) on the resident training set.
  *   numbatches = ceil(N/m) (:353); each epoch permutes the data cumulatively (:373-374);
  *   perms: (burnin+maxepoch) x N 0-based permutations, row-major per epoch, or NULL (Philox shuffle);

@@ -225,6 +225,50 @@ def test_sgld_step_vs_oracle(prec, langevin, stiefel):
 
 
 @pytest.mark.parametrize("prec", PRECS, ids=IDS)
+def test_sgld_step_host_and_pipelined(prec):
+    """Host-minibatch loop body (gptb_sgld_step_host) against an oracle chain, and the pipelined submit / wait
+    form against the blocking one (same operations in the same order)."""
+    P = make_problem(4, 400, 50, 10, Q=60, seed=9)
+    rng = np.random.default_rng(3)
+    T, bs, epsw, epsU = 5, 150, 1e-5, 1e-8
+    idx = [rng.permutation(P["N"])[:bs] for _ in range(T)]
+    nw = [rng.standard_normal(P["Q"]) for _ in range(T)]
+    nU = [np.asfortranarray(rng.standard_normal((P["n"], P["r"], P["D"]))) for _ in range(T)]
+    Xb = [np.asfortranarray(P["X"][i]) for i in idx]
+    yb = [np.ascontiguousarray(P["y"][i]) for i in idx]
+    w, U = P["w0"], P["U0"]
+    for t in range(T):
+        w, U = o.sgld_step(P["phi_fn"](P["X"][idx[t]]), P["y"][idx[t]], w, U, P["I"], P["N"], P["signal_var"], epsw, epsU,
+                           nw[t], nU[t], True, True)[:2]
+    wo = np.zeros(P["Q"])
+    with _model(P, prec, train=False) as m:
+        for t in range(T):
+            m.sgld_step_host(P["signal_var"], Xb[t], yb[t], P["N"], epsw, epsU, noise_w=nw[t], noise_U=nU[t], w_out=wo)
+        w1, U1 = m.get_params()
+    assert np.array_equal(wo, w1)
+    assert relerr(w1 - P["w0"], w - P["w0"]) < max(TOL[prec], 1e-8) * 10
+    assert relerr(U1 - P["U0"], U - P["U0"]) < max(TOL[prec], 1e-7) * 10
+    wouts = [np.zeros(P["Q"]) for _ in range(T)]
+    with _model(P, prec, train=False) as m:
+        with pytest.raises(G.GptbError):
+            m.sgld_step_host_wait()                       # nothing in flight
+        m.sgld_step_host_submit(P["signal_var"], Xb[0], yb[0], P["N"], epsw, epsU, noise_w=nw[0], noise_U=nU[0], w_out=wouts[0])
+        for t in range(1, T):
+            m.sgld_step_host_submit(P["signal_var"], Xb[t], yb[t], P["N"], epsw, epsU, noise_w=nw[t], noise_U=nU[t],
+                                    w_out=wouts[t])
+            if t != 2:                                    # once, let a third submit retire the oldest by itself
+                m.sgld_step_host_wait()
+        m.sgld_step_host_wait()
+        with pytest.raises(G.GptbError):
+            m.sgld_step_host_wait()
+        w2, U2 = m.get_params()
+    # (sums over rows use floating-point atomics, so two runs agree to rounding, not bit for bit)
+    tol = 1e-9 if prec == L.PREC_FP64 else 1e-5     # of the accumulated update; TC3 sums the gradient with fp32 atomics
+    assert relerr(w2 - P["w0"], w1 - P["w0"]) < tol and relerr(U2 - P["U0"], U1 - P["U0"]) < tol
+    assert np.array_equal(wouts[-1], w2)
+
+
+@pytest.mark.parametrize("prec", PRECS, ids=IDS)
 @pytest.mark.parametrize("phi_mode", [False, True], ids=["lazy", "densephi"])
 def test_GPTregression_vs_oracle(prec, phi_mode):
     """Whole sampler with injected draws: epochs, cumulative permutations, short last batch, burn-in, store layout."""
