@@ -595,145 +595,177 @@ __global__ void k_noise(double *__restrict__ noise_w, double *__restrict__ noise
     }
 }
 
-// C[m x n] = A[m x kk] * B[kk x n]; col-major with leading dimensions lda/ldb/ldc, shared memory.
-__device__ void smm_s(const double *__restrict__ A, int lda, const double *__restrict__ B, int ldb, double *__restrict__ C,
-                      int ldc, int m, int kk, int n) {
-    for (int t = threadIdx.x; t < m * n; t += blockDim.x) {
-        const int i = t % m, j = t / m;
-        double s0 = 0.0, s1 = 0.0;
-        int pp = 0;
-        for (; pp + 1 < kk; pp += 2) {
-            s0 = fma(A[i + (size_t)lda * pp], B[pp + (size_t)ldb * j], s0);
-            s1 = fma(A[i + (size_t)lda * (pp + 1)], B[pp + 1 + (size_t)ldb * j], s1);
-        }
-        if (pp < kk) s0 = fma(A[i + (size_t)lda * pp], B[pp + (size_t)ldb * j], s0);
-        C[i + (size_t)ldc * j] = s0 + s1;
-    }
-    __syncthreads();
-}
-
-// ---- FP64 tensor-core matrix product for the expm chain -----------------------------------------
-// The scalar smm() above leaves the SM latency-bound (8 warps, long index chains); DMMA m8n8k4 issues
-// 256 FMAs per instruction, so a 64^3 product is ~130 instructions per warp.
+// ---- FP64 tensor-core products for the r x r / 2r x 2r algebra of the Stiefel step ----------------
+// DMMA m8n8k4 issues 256 FMAs per instruction (64 FMA/clk/SM, the same peak as DFMA) with a fraction of the
+// instruction and shared-memory traffic of a scalar product loop.
 __device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
                  : "+d"(d0), "+d"(d1)
                  : "d"(a), "d"(b));
 }
-// leading dimension that keeps the 8x4 / 4x8 fragment loads at the 2-wavefront minimum (column stride = 8 banks mod 32)
+// leading dimension = 4 (mod 16): the 8x4 / 4x8 fragment loads then touch every bank pair once per half warp
 __host__ __device__ inline int dmm_ld(int np) { return np + 4; }
 
-// C = A*B for np x np matrices (np a multiple of 16, zero padded), col-major with leading dimension ld, in shared
-// memory; one 16x16 block of C per warp and pass.  kk = inner extent (multiple of 4).
-__device__ void dmm(const double *__restrict__ A, const double *__restrict__ B, double *__restrict__ C, int np, int kk, int ld) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tg = lane & 3, nw = blockDim.x >> 5;
-    const int nb = np / 16;
-    for (int blk = warp; blk < nb * nb; blk += nw) {
-        const int i0 = (blk % nb) * 16, j0 = (blk / nb) * 16;
-        double c00a = 0, c00b = 0, c01a = 0, c01b = 0, c10a = 0, c10b = 0, c11a = 0, c11b = 0;
-        const double *Ap = A + i0 + g + (size_t)ld * tg;
-        const double *Bp = B + tg + (size_t)ld * (j0 + g);
-#pragma unroll 4
-        for (int p0 = 0; p0 < kk; p0 += 4) {
-            const double a0 = Ap[(size_t)ld * p0], a1 = Ap[(size_t)ld * p0 + 8];
-            const double b0 = Bp[p0], b1 = Bp[p0 + (size_t)ld * 8];
-            dmma884(c00a, c00b, a0, b0);
-            dmma884(c01a, c01b, a0, b1);
-            dmma884(c10a, c10b, a1, b0);
-            dmma884(c11a, c11b, a1, b1);
+// C[M x N] = A[M x K] * B[K x N]: col-major in shared memory, leading dimensions from dmm_ld; M a multiple of
+// 8*TM, N of 8, K of 4 (zero padded).  Tiles of (8*TM) x 8, one per warp and pass over the warps [w0, w0+nw) of
+// the CTA, two accumulator chains per tile row block.  No barrier inside: independent products share a stage.
+template <int TM>
+__device__ __forceinline__ void dmm_t(const double *__restrict__ A, int lda, const double *__restrict__ B, int ldb,
+                                      double *__restrict__ C, int ldc, int M, int N, int K, int w0, int nw,
+                                      const double *__restrict__ Dm = nullptr, int ldd = 0 /* C = Dm - A*B */) {
+    const int warp = (int)(threadIdx.x >> 5) - w0, lane = threadIdx.x & 31, g = lane >> 2, tg = lane & 3;
+    if (warp < 0 || warp >= nw) return;
+    const int mb = M / (8 * TM), nt = mb * (N >> 3);
+    for (int t = warp; t < nt; t += nw) {
+        const int tj = t / mb, i0 = (t - tj * mb) * 8 * TM, j0 = tj << 3;
+        const double *Ap = A + i0 + g + (size_t)lda * tg;
+        const double *Bp = B + tg + (size_t)ldb * (j0 + g);
+        double ca[2][TM], cb[2][TM];
+#pragma unroll
+        for (int i = 0; i < TM; ++i) ca[0][i] = cb[0][i] = ca[1][i] = cb[1][i] = 0.0;
+        int p0 = 0;
+#pragma unroll 2
+        for (; p0 + 8 <= K; p0 += 8) {
+            const double b0 = Bp[p0], b1 = Bp[p0 + 4];
+#pragma unroll
+            for (int i = 0; i < TM; ++i) {
+                dmma884(ca[0][i], cb[0][i], Ap[(size_t)lda * p0 + 8 * i], b0);
+                dmma884(ca[1][i], cb[1][i], Ap[(size_t)lda * (p0 + 4) + 8 * i], b1);
+            }
         }
-        double *Cp = C + i0 + g + (size_t)ld * (j0 + 2 * tg);
-        Cp[0] = c00a; Cp[ld] = c00b;
-        Cp[(size_t)ld * 8] = c01a; Cp[(size_t)ld * 9] = c01b;
-        Cp[8] = c10a; Cp[8 + ld] = c10b;
-        Cp[8 + (size_t)ld * 8] = c11a; Cp[8 + (size_t)ld * 9] = c11b;
+        if (p0 < K) {
+            const double b0 = Bp[p0];
+#pragma unroll
+            for (int i = 0; i < TM; ++i) dmma884(ca[0][i], cb[0][i], Ap[(size_t)lda * p0 + 8 * i], b0);
+        }
+        double *Cp = C + i0 + g + (size_t)ldc * (j0 + 2 * tg);
+#pragma unroll
+        for (int i = 0; i < TM; ++i) {
+            double va = ca[0][i] + ca[1][i], vb = cb[0][i] + cb[1][i];
+            if (Dm) {
+                const double *Dp = Dm + i0 + g + 8 * i + (size_t)ldd * (j0 + 2 * tg);
+                va = Dp[0] - va;
+                vb = Dp[ldd] - vb;
+            }
+            Cp[8 * i] = va;
+            Cp[8 * i + ldc] = vb;
+        }
     }
-    __syncthreads();
 }
 
-// exp(X) for the n2 x n2 matrix held (zero padded to np x np, leading dimension ld) in buf[0]; the result is left
-// in the buffer whose pointer is returned.  Same algorithm as sexpm (Taylor / Paterson-Stockmeyer + squaring);
-// buf holds six np*ld blocks.  NaN/Inf input sets *bad_s.
-__device__ double *sexpm2(double *buf, int n2, int np, int ld, int *bad_s) {
-    __shared__ double nrm2_s;
-    __shared__ int s2_s, m2_s;
+__constant__ double c_inv_fact[21] = {1.0, 1.0, 0.5, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040, 1.0 / 40320,
+                                      1.0 / 362880, 1.0 / 3628800, 1.0 / 39916800, 1.0 / 479001600, 1.0 / 6227020800.0,
+                                      1.0 / 87178291200.0, 1.0 / 1307674368000.0, 1.0 / 20922789888000.0,
+                                      1.0 / 355687428096000.0, 1.0 / 6402373705728000.0, 1.0 / 121645100408832000.0,
+                                      1.0 / 2432902008176640000.0};
+
+// exp(X) for the n2 x n2 matrix held zero padded to np x np (np a multiple of 8*TM, leading dimension ld) in buf[0];
+// the result is left in the buffer whose pointer is returned.  Taylor / Paterson-Stockmeyer + squaring as in sexpm;
+// buf holds six np*ld blocks; slot selects the function's shared scalars.  NaN/Inf input sets *bad_s.
+template <int TM>
+__device__ double *sexpm3(double *buf, int n2, int np, int ld, int *bad_s) {
+    __shared__ double nrm3_s;
+    __shared__ int s3_s, m3_s;
     const size_t sz = (size_t)ld * np;
-    const int kk = (n2 + 3) & ~3;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
     double *X = buf, *X2 = X + sz, *X3 = X2 + sz, *X4 = X3 + sz, *P = X4 + sz, *Tm = P + sz;
-    if (threadIdx.x == 0) nrm2_s = 0.0;
+#ifdef GPTB_K5_DBG
+    long long te[8];
+    int ne = 0;
+#define K5E() do { te[ne++] = clock64(); } while (0)
+#else
+#define K5E() do {} while (0)
+#endif
+    K5E();
+    if (threadIdx.x == 0) nrm3_s = 0.0;
     __syncthreads();
-    for (int c0 = (threadIdx.x >> 5) * 4; c0 < n2; c0 += (blockDim.x >> 5) * 4) {   // 1-norm: eight lanes per column
-        const int c = c0 + ((threadIdx.x & 31) >> 3);
-        double s = 0.0;
-        if (c < n2)
-            for (int i = threadIdx.x & 7; i < n2; i += 8) s += fabs(X[i + (size_t)ld * c]);
-        s += __shfl_xor_sync(0xffffffffu, s, 1);
-        s += __shfl_xor_sync(0xffffffffu, s, 2);
-        s += __shfl_xor_sync(0xffffffffu, s, 4);
-        if ((threadIdx.x & 7) == 0 && c < n2) {
-            if (s != s || isinf(s)) *bad_s = 1;
-            else atomicMax(reinterpret_cast<unsigned long long *>(&nrm2_s), (unsigned long long)__double_as_longlong(s));
+    for (int c = warp; c < n2; c += nw) {   // 1-norm: one warp per column
+        double sc = 0.0;
+        for (int i = lane; i < n2; i += 32) sc += fabs(X[i + (size_t)ld * c]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sc += __shfl_xor_sync(0xffffffffu, sc, o);
+        if (lane == 0) {
+            if (sc != sc || isinf(sc)) *bad_s = 1;
+            else atomicMax(reinterpret_cast<unsigned long long *>(&nrm3_s), (unsigned long long)__double_as_longlong(sc));
         }
     }
     __syncthreads();
     if (*bad_s) return X;
     if (threadIdx.x == 0) {
-        const double nrm = nrm2_s;
-        int m = 20, s = 0;
+        const double nrm = nrm3_s;
+        int m = 20, sq = 0;
         if (nrm <= 1.7e-3) m = 4;
         else if (nrm <= 7.0e-2) m = 8;
         else if (nrm <= 3.3e-1) m = 12;
         else if (nrm <= 8.2e-1) m = 16;
-        else if (nrm > 1.5) s = max(0, (int)ceil(log2(nrm / 1.5)));
-        m2_s = m;
-        s2_s = s;
+        else if (nrm > 1.5) sq = max(0, (int)ceil(log2(nrm / 1.5)));
+        m3_s = m;
+        s3_s = sq;
     }
     __syncthreads();
-    const int m = m2_s, s = s2_s;
-    if (s > 0) {
-        const double f = ldexp(1.0, -s);
-        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) X[t] *= f;
+    const int m = m3_s, sq = s3_s;
+    K5E();
+    if (sq > 0) {
+        const double f = ldexp(1.0, -sq);
+        for (int c = warp; c < n2; c += nw)
+            for (int i = lane; i < n2; i += 32) X[i + (size_t)ld * c] *= f;
         __syncthreads();
     }
-    dmm(X, X, X2, np, kk, ld);
-    dmm(X2, X, X3, np, kk, ld);
-    dmm(X2, X2, X4, np, kk, ld);
-    const double inv_fact[21] = {1.0, 1.0, 0.5, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040, 1.0 / 40320,
-                                 1.0 / 362880, 1.0 / 3628800, 1.0 / 39916800, 1.0 / 479001600, 1.0 / 6227020800.0,
-                                 1.0 / 87178291200.0, 1.0 / 1307674368000.0, 1.0 / 20922789888000.0,
-                                 1.0 / 355687428096000.0, 1.0 / 6402373705728000.0, 1.0 / 121645100408832000.0,
-                                 1.0 / 2432902008176640000.0};
+    dmm_t<TM>(X, ld, X, ld, X2, ld, np, np, np, 0, nw);
+    __syncthreads();
+    K5E();
+    {   // X3 = X2 X and X4 = X2 X2 in one stage
+        const int h = nw / 2;
+        dmm_t<TM>(X2, ld, X, ld, X3, ld, np, np, np, 0, h);
+        dmm_t<TM>(X2, ld, X2, ld, X4, ld, np, np, np, h, nw - h);
+    }
+    __syncthreads();
+    K5E();
+    const double *inv_fact = c_inv_fact;   // (a per-thread copy of the table in local memory cost ~6k clk per call)
     const int nbk = m / 4;
     {   // top block, with the X^m term folded in
         const int b0 = 4 * (nbk - 1);
         const double c0 = inv_fact[b0], c1 = inv_fact[b0 + 1], c2 = inv_fact[b0 + 2], c3 = inv_fact[b0 + 3], c4 = inv_fact[m];
-        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) {
-            const int i = (int)(t % ld), j = (int)(t / ld);
-            P[t] = ((i == j && i < n2) ? c0 : 0.0) + c1 * X[t] + c2 * X2[t] + c3 * X3[t] + c4 * X4[t];
-        }
+        for (int c = warp; c < np; c += nw)
+            for (int i = lane; i < np; i += 32) {
+                const size_t t = i + (size_t)ld * c;
+                P[t] = ((i == c && i < n2) ? c0 : 0.0) + c1 * X[t] + c2 * X2[t] + c3 * X3[t] + c4 * X4[t];
+            }
         __syncthreads();
     }
+    K5E();
     for (int bi = nbk - 2; bi >= 0; --bi) {
-        dmm(X4, P, Tm, np, kk, ld);
+        dmm_t<TM>(X4, ld, P, ld, Tm, ld, np, np, np, 0, nw);
+        __syncthreads();
         const int b0 = 4 * bi;
         const double c0 = inv_fact[b0], c1 = inv_fact[b0 + 1], c2 = inv_fact[b0 + 2], c3 = inv_fact[b0 + 3];
-        for (size_t t = threadIdx.x; t < sz; t += blockDim.x) {
-            const int i = (int)(t % ld), j = (int)(t / ld);
-            P[t] = Tm[t] + ((i == j && i < n2) ? c0 : 0.0) + c1 * X[t] + c2 * X2[t] + c3 * X3[t];
-        }
+        for (int c = warp; c < np; c += nw)
+            for (int i = lane; i < np; i += 32) {
+                const size_t t = i + (size_t)ld * c;
+                P[t] = Tm[t] + ((i == c && i < n2) ? c0 : 0.0) + c1 * X[t] + c2 * X2[t] + c3 * X3[t];
+            }
         __syncthreads();
     }
+    K5E();
+#ifdef GPTB_K5_DBG
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        printf("[k5 dbg] expm n=%d m=%d: norm %lld, X2 %lld, X3|X4 %lld, top %lld, horner %lld\n", n2, m, te[1] - te[0],
+               te[2] - te[1], te[3] - te[2], te[4] - te[3], te[5] - te[4]);
+#endif
+#undef K5E
     double *cur = P, *oth = Tm;
-    for (int q = 0; q < s; ++q) {
-        dmm(cur, cur, oth, np, kk, ld);
+    for (int q = 0; q < sq; ++q) {
+        dmm_t<TM>(cur, ld, cur, ld, oth, ld, np, np, np, 0, nw);
+        __syncthreads();
         double *sw = cur; cur = oth; oth = sw;
     }
     return cur;
 }
 
-// P2' : like k_small, with everything in shared memory, the matrix exponentials on the FP64 tensor cores, and the
-// column norms of Unew = U C1 + G C2 taken from the r x r Gram matrices, so that C1, C2 leave already divided by
-// the norms (:30-35) and the apply kernel writes the final U in one pass.
+// P2' : the r x r / 2r x 2r algebra of geod() (GPT_SGLD.jl:19-37) for one k per CTA, entirely in shared memory on
+// the FP64 tensor cores.  The column norms of Unew = U C1 + G C2 come from the r x r Gram matrices, so C1, C2 leave
+// already divided by the norms (:30-35) and the apply kernel writes the final U in one pass.
+//   in : small[S1 = U'G, UU = U'U, GG = G'G]          out : small[C1, C2]
 struct Small2Geo {
     int r2, np2, ld2, npr, ldr;
     size_t sz2, szr;
@@ -742,7 +774,11 @@ struct Small2Geo {
         np2 = (r2 + 15) & ~15; ld2 = dmm_ld(np2); sz2 = (size_t)ld2 * np2;
         npr = (r + 15) & ~15; ldr = dmm_ld(npr); szr = (size_t)ldr * npr;
     }
-    __host__ __device__ bool ok(int r) const { return 6 * szr <= 4 * sz2 && 10 * (size_t)r * r <= 4 * sz2; }
+    // phase 1 keeps eight r x r blocks beside X, the small exponential six beside E, phase 4 nine plus W (np2 x npr)
+    __host__ __device__ bool ok(int) const {
+        return 8 * szr <= 5 * sz2 && 6 * szr <= 4 * sz2 && 9 * szr + (size_t)ld2 * npr <= 4 * sz2 &&
+               npr * npr <= 2 * 1024 /* -tA waits in two registers per thread */;
+    }
     __host__ __device__ size_t bytes() const { return 6 * sz2 * sizeof(double); }
 };
 
@@ -750,56 +786,78 @@ __global__ void __launch_bounds__(1024)
 k_small2(double *__restrict__ small, size_t small_stride, int r, double t, int32_t *nan_flag) {
     extern __shared__ double sm[];
     __shared__ int bad;
+    __shared__ double cn[64];
     double *sk = small + (size_t)blockIdx.x * small_stride;
     SmallLayout L(r);
     const Small2Geo g(r);
-    const int r2 = g.r2, rr = r * r, tid = threadIdx.x, nt = blockDim.x;
+    const int r2 = g.r2, npr = g.npr, ldr = g.ldr, np2 = g.np2, ld2 = g.ld2;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nw = blockDim.x >> 5;
     if (tid == 0) bad = 0;
-    // ---- phase 1: r x r algebra in blocks 1..5, the 2r x 2r argument of expm straight into block 0
+#ifdef GPTB_K5_DBG   // per-phase clocks of CTA 0 (build with EXTRA_NVCC_FLAGS=-DGPTB_K5_DBG)
+    long long tq[8];
+    int nq = 0;
+#define K5T() do { __syncthreads(); tq[nq++] = clock64(); } while (0)
+#else
+#define K5T() do {} while (0)
+#endif
+    K5T();
+    // ---- phase 1: r x r algebra in blocks 1..5 (padded, leading dimension ldr), X straight into block 0
     double *Xb = sm;
-    double *S1 = sm + g.sz2, *S1t = S1 + rr, *UU = S1t + rr, *GG = UU + rr, *sym = GG + rr, *t1 = sym + rr, *t2 = t1 + rr,
-           *t3 = t2 + rr;
-    for (int i = tid; i < rr; i += nt) {
-        const int a = i % r, b = i / r;
-        const double s = sk[L.S1 + i];
-        S1[i] = s;
-        S1t[b + r * a] = s;
-        UU[i] = sk[L.UU + i];
-        GG[i] = sk[L.GG + i];
-    }
-    __syncthreads();
-    for (int i = tid; i < rr; i += nt) {
-        const double v = (S1[i] + S1t[i]) / 2;
-        sym[i] = v;
-        sk[L.sym + i] = v;
-    }
-    __syncthreads();
-    smm_s(UU, r, sym, r, t1, r, r, r, r);      // UU*sym
-    smm_s(sym, r, t1, r, t2, r, r, r, r);      // sym*UU*sym
-    smm_s(S1t, r, sym, r, t3, r, r, r, r);     // S1'*sym  (sym*S1 is its transpose)
-    for (size_t i = tid; i < g.sz2; i += nt) {
-        const int a = (int)(i % g.ld2), b = (int)(i / g.ld2);
-        double v = 0.0;
-        if (a < r2 && b < r2) {
-            if (a < r && b < r) v = S1[a + r * b] - t1[a + r * b];                               // A = U'M
-            else if (a < r) {                                                                      // -M'M
-                const int bb = b - r;
-                v = -(GG[a + r * bb] - t3[a + r * bb] - t3[bb + r * a] + t2[a + r * bb]);
-            } else if (b < r) v = (a - r == b) ? 1.0 : 0.0;
-            else v = S1[(a - r) + r * (b - r)] - t1[(a - r) + r * (b - r)];
+    double *S1 = sm + g.sz2, *S1t = S1 + g.szr, *UU = S1t + g.szr, *GG = UU + g.szr, *sym = GG + g.szr, *t1 = sym + g.szr,
+           *t2 = t1 + g.szr, *t3 = t2 + g.szr;
+    for (int c = warp; c < npr; c += nw)
+        for (int a = lane; a < npr; a += 32) {
+            const bool in = a < r && c < r;
+            const double s1 = in ? sk[L.S1 + a + r * c] : 0.0, s1t = in ? sk[L.S1 + c + r * a] : 0.0;
+            const size_t o = a + (size_t)ldr * c;
+            S1[o] = s1;
+            S1t[o] = s1t;
+            sym[o] = (s1 + s1t) / 2;
+            UU[o] = in ? sk[L.UU + a + r * c] : 0.0;
+            GG[o] = in ? sk[L.GG + a + r * c] : 0.0;
         }
-        Xb[i] = t * v;
-    }
-    for (int i = tid; i < rr; i += nt) sk[L.X + i] = -t * (S1[i] - t1[i]);
     __syncthreads();
+    K5T();
+    {
+        const int h = nw / 2;
+        dmm_t<1>(UU, ldr, sym, ldr, t1, ldr, npr, npr, npr, 0, h);         // UU*sym
+        dmm_t<1>(S1t, ldr, sym, ldr, t3, ldr, npr, npr, npr, h, nw - h);   // S1'*sym  (sym*S1 is its transpose)
+    }
+    __syncthreads();
+    dmm_t<1>(sym, ldr, t1, ldr, t2, ldr, npr, npr, npr, 0, nw);            // sym*UU*sym
+    __syncthreads();
+    for (int b = warp; b < np2; b += nw)
+        for (int a = lane; a < np2; a += 32) {
+            double v = 0.0;
+            if (a < r2 && b < r2) {
+                if (a < r && b < r) v = S1[a + ldr * b] - t1[a + ldr * b];                              // A = U'M
+                else if (a < r) {                                                                       // -M'M
+                    const int bb = b - r;
+                    v = -(GG[a + ldr * bb] - t3[a + ldr * bb] - t3[bb + ldr * a] + t2[a + ldr * bb]);
+                } else if (b < r) v = (a - r == b) ? 1.0 : 0.0;
+                else v = S1[(a - r) + ldr * (b - r)] - t1[(a - r) + ldr * (b - r)];
+            }
+            Xb[a + (size_t)ld2 * b] = t * v;
+        }
+    // -tA for phase 3 waits in the registers of the threads that will store it (blocks 0..3 are busy until then)
+    double xs_keep[2] = {0.0, 0.0};
+    {
+        int q = 0;
+        for (int c = warp; c < npr; c += nw)
+            for (int a = lane; a < npr; a += 32, ++q)
+                if (q < 2) xs_keep[q] = (a < r && c < r) ? -t * (S1[a + ldr * c] - t1[a + ldr * c]) : 0.0;
+    }
+    __syncthreads();
+    K5T();
     // ---- phase 2: E = expm(t [[A, -M'M], [I, A]])
-    double *E = sexpm2(sm, r2, g.np2, g.ld2, &bad);
+    double *E = sexpm3<2>(sm, r2, np2, ld2, &bad);
     if (!bad) {
         int local = 0;                 // "if sum(isnan(E))>0" (:24)
-        for (int i = tid; i < r2 * r2; i += nt) {
-            const double v = E[(i % r2) + (size_t)g.ld2 * (i / r2)];
-            if (v != v) local = 1;
-        }
+        for (int c = warp; c < r2; c += nw)
+            for (int a = lane; a < r2; a += 32) {
+                const double v = E[a + (size_t)ld2 * c];
+                if (v != v) local = 1;
+            }
         if (local) bad = 1;
     }
     __syncthreads();
@@ -807,53 +865,82 @@ k_small2(double *__restrict__ small, size_t small_stride, int r, double t, int32
         if (tid == 0) atomicExch(nan_flag, 1);
         return;
     }
+    K5T();
     // ---- phase 3: expm(-tA) in blocks 0..3 (E sits in block 4 or 5), parked in the other of blocks 4/5
-    for (size_t i = tid; i < g.szr; i += nt) {
-        const int a = (int)(i % g.ldr), b = (int)(i / g.ldr);
-        sm[i] = (a < r && b < r) ? sk[L.X + a + r * b] : 0.0;
+    {
+        int q = 0;
+        for (int c = warp; c < npr; c += nw)
+            for (int a = lane; a < npr; a += 32, ++q) sm[a + (size_t)ldr * c] = q < 2 ? xs_keep[q] : 0.0;
     }
     __syncthreads();
-    double *Xe0 = sexpm2(sm, r, g.npr, g.ldr, &bad);
+    double *Xe0 = sexpm3<1>(sm, r, npr, ldr, &bad);
     if (bad) {
         if (tid == 0) atomicExch(nan_flag, 1);
         return;
     }
     double *Xe = (E == sm + 4 * g.sz2) ? sm + 5 * g.sz2 : sm + 4 * g.sz2;
-    for (size_t i = tid; i < g.szr; i += nt) Xe[i] = Xe0[i];
+    for (int c = warp; c < npr; c += nw)
+        for (int a = lane; a < npr; a += 32) Xe[a + (size_t)ldr * c] = Xe0[a + (size_t)ldr * c];
     __syncthreads();
+    K5T();
     // ---- phase 4: W = E[:,1:r] * expm(-tA); C1 = W1 - sym*W2, C2 = W2; column norms; blocks 0..3 are scratch
-    double *W = sm, *C1 = W + (size_t)r2 * r, *symb = C1 + rr, *P1 = symb + rr, *P2 = P1 + rr, *P3 = P2 + rr,
-           *M1 = P3 + rr, *M2 = M1 + rr, *M3 = M2 + rr;
-    __shared__ double cn[64];
-    for (int i = tid; i < rr; i += nt) {
-        symb[i] = sk[L.sym + i];
-        M1[i] = sk[L.UU + i];
-        M2[i] = sk[L.S1 + i];
-        M3[i] = sk[L.GG + i];
-    }
-    smm_s(E, g.ld2, Xe, g.ldr, W, r2, r2, r, r);          // (also orders the loads above)
-    const double *W1 = W, *W2 = W + r;                    // leading dimension r2
-    smm_s(symb, r, W2, r2, P1, r, r, r, r);
-    for (int i = tid; i < rr; i += nt) C1[i] = W1[(i % r) + (size_t)r2 * (i / r)] - P1[i];
-    __syncthreads();
-    // squared column norms of U C1 + G C2:  diag(C1'UU C1 + 2 C1'S1 C2 + C2'GG C2)
-    smm_s(M1, r, C1, r, P1, r, r, r, r);
-    smm_s(M2, r, W2, r2, P2, r, r, r, r);
-    smm_s(M3, r, W2, r2, P3, r, r, r, r);
-    for (int l = tid; l < r; l += nt) {
-        double s = 0.0;
-        for (int a = 0; a < r; ++a) {
-            const int i = a + r * l;
-            s += C1[i] * (P1[i] + 2.0 * P2[i]) + W2[a + (size_t)r2 * l] * P3[i];
+    double *W = sm, *W2 = W + (size_t)ld2 * npr, *C1 = W2 + g.szr, *symb = C1 + g.szr, *M1 = symb + g.szr, *M2 = M1 + g.szr,
+           *M3 = M2 + g.szr, *P1 = M3 + g.szr, *P2 = P1 + g.szr, *P3 = P2 + g.szr;
+    for (int c = warp; c < npr; c += nw)
+        for (int a = lane; a < npr; a += 32) {
+            const bool in = a < r && c < r;
+            const size_t o = a + (size_t)ldr * c;
+            const double s1 = in ? sk[L.S1 + a + r * c] : 0.0, s1t = in ? sk[L.S1 + c + r * a] : 0.0;
+            symb[o] = (s1 + s1t) / 2;
+            M1[o] = in ? sk[L.UU + a + r * c] : 0.0;
+            M2[o] = s1;
+            M3[o] = in ? sk[L.GG + a + r * c] : 0.0;
         }
-        cn[l] = 1.0 / sqrt(s);
+    dmm_t<1>(E, ld2, Xe, ldr, W, ld2, np2, npr, npr, 0, nw);   // (Xe is zero outside r x r, so the extra columns of E drop out)
+    __syncthreads();
+    int ldw2 = ldr;
+    if (r == npr) {                                            // rows r..2r-1 of W are a padded block as they stand
+        W2 = W + r;
+        ldw2 = ld2;
+    } else {
+        for (int c = warp; c < npr; c += nw)
+            for (int a = lane; a < npr; a += 32)
+                W2[a + (size_t)ldr * c] = (a < r && c < r) ? W[r + a + (size_t)ld2 * c] : 0.0;
+        __syncthreads();
+    }
+    // C1 = W1 - sym*W2 (rows/columns >= r of W1 are zero: E and Xe are zero padded)
+    dmm_t<1>(symb, ldr, W2, ldw2, C1, ldr, npr, npr, npr, 0, nw, W, ld2);
+    __syncthreads();
+    {   // squared column norms of U C1 + G C2:  diag(C1'UU C1 + 2 C1'S1 C2 + C2'GG C2)
+        const int h = nw / 3;
+        dmm_t<1>(M1, ldr, C1, ldr, P1, ldr, npr, npr, npr, 0, h);
+        dmm_t<1>(M2, ldr, W2, ldw2, P2, ldr, npr, npr, npr, h, h);
+        dmm_t<1>(M3, ldr, W2, ldw2, P3, ldr, npr, npr, npr, 2 * h, nw - 2 * h);
     }
     __syncthreads();
-    for (int i = tid; i < rr; i += nt) {
-        const int a = i % r, l = i / r;
-        sk[L.C1 + i] = C1[i] * cn[l];
-        sk[L.C2 + i] = W2[a + (size_t)r2 * l] * cn[l];
+    for (int l = warp; l < r; l += nw) {
+        double sc = 0.0;
+        for (int a = lane; a < r; a += 32) {
+            const size_t o = a + (size_t)ldr * l;
+            sc += C1[o] * (P1[o] + 2.0 * P2[o]) + W2[a + (size_t)ldw2 * l] * P3[o];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sc += __shfl_xor_sync(0xffffffffu, sc, o);
+        if (lane == 0) cn[l] = 1.0 / sqrt(sc);
     }
+    __syncthreads();
+    for (int l = warp; l < r; l += nw)
+        for (int a = lane; a < r; a += 32) {
+            sk[L.C1 + a + r * l] = C1[a + (size_t)ldr * l] * cn[l];
+            sk[L.C2 + a + r * l] = W2[a + (size_t)ldw2 * l] * cn[l];
+        }
+    K5T();
+#ifdef GPTB_K5_DBG
+    if (blockIdx.x == 0 && tid == 0)
+        printf("[k5 dbg] clk: load %lld, phase1 %lld, expm(2r) %lld, expm(r) %lld, phase4 %lld\n", tq[1] - tq[0],
+               tq[2] - tq[1], tq[3] - tq[2], tq[4] - tq[3], tq[5] - tq[4]);
+#endif
+#undef K5T
 }
 
 // P3' : U <- U C1 + G C2 (C1, C2 pre-divided by the column norms), plus the fp16 hi|lo operand image of the new U
