@@ -57,6 +57,64 @@ __device__ __forceinline__ double noise_at(uint64_t key, uint64_t stream, uint64
     return (e & 1) ? b : a;
 }
 
+// ---- FP64 tensor-core products for the r x r / 2r x 2r algebra of the Stiefel step ----------------
+// DMMA m8n8k4 issues 256 FMAs per instruction (64 FMA/clk/SM, the same peak as DFMA) with a fraction of the
+// instruction and shared-memory traffic of a scalar product loop.
+__device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(d0), "+d"(d1)
+                 : "d"(a), "d"(b));
+}
+// leading dimension = 4 (mod 16): the 8x4 / 4x8 fragment loads then touch every bank pair once per half warp
+__host__ __device__ inline int dmm_ld(int np) { return np + 4; }
+
+// C[M x N] = A[M x K] * B[K x N]: col-major in shared memory, leading dimensions from dmm_ld; M a multiple of
+// 8*TM, N of 8, K of 4 (zero padded).  Tiles of (8*TM) x 8, one per warp and pass over the warps [w0, w0+nw) of
+// the CTA, two accumulator chains per tile row block.  No barrier inside: independent products share a stage.
+template <int TM>
+__device__ __forceinline__ void dmm_t(const double *__restrict__ A, int lda, const double *__restrict__ B, int ldb,
+                                      double *__restrict__ C, int ldc, int M, int N, int K, int w0, int nw,
+                                      const double *__restrict__ Dm = nullptr, int ldd = 0 /* C = Dm - A*B */) {
+    const int warp = (int)(threadIdx.x >> 5) - w0, lane = threadIdx.x & 31, g = lane >> 2, tg = lane & 3;
+    if (warp < 0 || warp >= nw) return;
+    const int mb = M / (8 * TM), nt = mb * (N >> 3);
+    for (int t = warp; t < nt; t += nw) {
+        const int tj = t / mb, i0 = (t - tj * mb) * 8 * TM, j0 = tj << 3;
+        const double *Ap = A + i0 + g + (size_t)lda * tg;
+        const double *Bp = B + tg + (size_t)ldb * (j0 + g);
+        double ca[2][TM], cb[2][TM];
+#pragma unroll
+        for (int i = 0; i < TM; ++i) ca[0][i] = cb[0][i] = ca[1][i] = cb[1][i] = 0.0;
+        int p0 = 0;
+#pragma unroll 2
+        for (; p0 + 8 <= K; p0 += 8) {
+            const double b0 = Bp[p0], b1 = Bp[p0 + 4];
+#pragma unroll
+            for (int i = 0; i < TM; ++i) {
+                dmma884(ca[0][i], cb[0][i], Ap[(size_t)lda * p0 + 8 * i], b0);
+                dmma884(ca[1][i], cb[1][i], Ap[(size_t)lda * (p0 + 4) + 8 * i], b1);
+            }
+        }
+        if (p0 < K) {
+            const double b0 = Bp[p0];
+#pragma unroll
+            for (int i = 0; i < TM; ++i) dmma884(ca[0][i], cb[0][i], Ap[(size_t)lda * p0 + 8 * i], b0);
+        }
+        double *Cp = C + i0 + g + (size_t)ldc * (j0 + 2 * tg);
+#pragma unroll
+        for (int i = 0; i < TM; ++i) {
+            double va = ca[0][i] + ca[1][i], vb = cb[0][i] + cb[1][i];
+            if (Dm) {
+                const double *Dp = Dm + i0 + g + 8 * i + (size_t)ldd * (j0 + 2 * tg);
+                va = Dp[0] - va;
+                vb = Dp[ldd] - vb;
+            }
+            Cp[8 * i] = va;
+            Cp[8 * i + ldc] = vb;
+        }
+    }
+}
+
 // ---------------------------------------------------------------- P1
 // grid (ceil(n/UP_ROWS), D + 1); blockIdx.y == D handles w (block x == 0 only).
 __global__ void __launch_bounds__(UP_THREADS)
@@ -84,12 +142,12 @@ k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ 
     const double *gU = grad + Q + (size_t)k * r * n;
     double *Uk = U + (size_t)k * r * n, *Gk = G + (size_t)k * r * n;
     const double sqU = sqrt(epsU);
-    const int ldt = r + 1;                             // tile layout [jj][l], padded: the Gram loops walk l across lanes
+    const int npr = (r + 15) & ~15, ldt = dmm_ld(npr);   // tile layout [jj][l], zero padded to npr columns
     double *Us = sm, *Gs = sm + (size_t)UP_ROWS * ldt;
-    for (int t = tid; t < UP_ROWS * r; t += UP_THREADS) {
+    for (int t = tid; t < UP_ROWS * npr; t += UP_THREADS) {
         int jj = t % UP_ROWS, l = t / UP_ROWS, j = j0 + jj;
         double u = 0.0, g = 0.0;
-        if (jj < rows) {
+        if (jj < rows && l < r) {
             size_t e = (size_t)l * n + j;
             u = Uk[e];
             double z = 0.0;
@@ -111,20 +169,42 @@ k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ 
     __syncthreads();
     double *sk = small + (size_t)k * small_stride;
     SmallLayout L(r);
-    for (int t = tid; t < r * r; t += UP_THREADS) {
-        int a = t % r, b = t / r;
-        double s1 = 0.0, gg = 0.0, uu = 0.0;
-#pragma unroll 4
-        for (int jj = 0; jj < UP_ROWS; ++jj) {
-            const double ua = Us[(size_t)jj * ldt + a], ub = Us[(size_t)jj * ldt + b];
-            const double ga = Gs[(size_t)jj * ldt + a], gb = Gs[(size_t)jj * ldt + b];
-            s1 = fma(ua, gb, s1);
-            gg = fma(ga, gb, gg);
-            uu = fma(ua, ub, uu);
+    // Gram sums of this row block on the FP64 tensor cores (8x8 tiles, K = UP_ROWS): S1 = U'G in full, GG = G'G and
+    // UU = U'U by their upper triangles, mirrored on the way out.  (The scalar loop this replaces was bound by its
+    // four shared-memory loads per three FMAs.)
+    const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, tg = lane & 3;
+    const int nbt = npr >> 3, ntri = nbt * (nbt + 1) / 2, nitems = nbt * nbt + 2 * ntri;
+    for (int it = warp; it < nitems; it += UP_THREADS / 32) {
+        int prod = 0, ti, tj;
+        if (it < nbt * nbt) {
+            tj = it / nbt;
+            ti = it - tj * nbt;
+        } else {
+            int u = it - nbt * nbt;
+            if (u >= ntri) { prod = 2; u -= ntri; } else prod = 1;
+            tj = 0;
+            while (u > tj) { u -= tj + 1; ++tj; }
+            ti = u;                                   // ti <= tj
         }
-        atomicAdd(&sk[L.S1 + a + (size_t)r * b], s1);
-        atomicAdd(&sk[L.GG + a + (size_t)r * b], gg);
-        atomicAdd(&sk[L.UU + a + (size_t)r * b], uu);
+        const double *At = prod == 1 ? Gs : Us;       // S1 = U'G, GG = G'G, UU = U'U
+        const double *Bt = prod == 2 ? Us : Gs;
+        const double *Ap = At + ti * 8 + g + (size_t)ldt * tg;   // A[m][k] = At[m + ldt k],  B[k][n] = Bt[n + ldt k]
+        const double *Bp = Bt + tj * 8 + g + (size_t)ldt * tg;
+        double c0a = 0.0, c0b = 0.0, c1a = 0.0, c1b = 0.0;
+#pragma unroll 4
+        for (int p0 = 0; p0 < UP_ROWS; p0 += 8) {
+            dmma884(c0a, c0b, Ap[(size_t)ldt * p0], Bp[(size_t)ldt * p0]);
+            dmma884(c1a, c1b, Ap[(size_t)ldt * (p0 + 4)], Bp[(size_t)ldt * (p0 + 4)]);
+        }
+        const double va = c0a + c1a, vb = c0b + c1b;
+        const int a = ti * 8 + g, b = tj * 8 + 2 * tg;
+        double *o = sk + (prod == 0 ? L.S1 : prod == 1 ? L.GG : L.UU);
+        if (a < r && b < r) atomicAdd(&o[a + (size_t)r * b], va);
+        if (a < r && b + 1 < r) atomicAdd(&o[a + (size_t)r * (b + 1)], vb);
+        if (prod != 0 && ti != tj) {
+            if (a < r && b < r) atomicAdd(&o[b + (size_t)r * a], va);
+            if (a < r && b + 1 < r) atomicAdd(&o[b + 1 + (size_t)r * a], vb);
+        }
     }
 }
 
@@ -595,64 +675,6 @@ __global__ void k_noise(double *__restrict__ noise_w, double *__restrict__ noise
     }
 }
 
-// ---- FP64 tensor-core products for the r x r / 2r x 2r algebra of the Stiefel step ----------------
-// DMMA m8n8k4 issues 256 FMAs per instruction (64 FMA/clk/SM, the same peak as DFMA) with a fraction of the
-// instruction and shared-memory traffic of a scalar product loop.
-__device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-                 : "+d"(d0), "+d"(d1)
-                 : "d"(a), "d"(b));
-}
-// leading dimension = 4 (mod 16): the 8x4 / 4x8 fragment loads then touch every bank pair once per half warp
-__host__ __device__ inline int dmm_ld(int np) { return np + 4; }
-
-// C[M x N] = A[M x K] * B[K x N]: col-major in shared memory, leading dimensions from dmm_ld; M a multiple of
-// 8*TM, N of 8, K of 4 (zero padded).  Tiles of (8*TM) x 8, one per warp and pass over the warps [w0, w0+nw) of
-// the CTA, two accumulator chains per tile row block.  No barrier inside: independent products share a stage.
-template <int TM>
-__device__ __forceinline__ void dmm_t(const double *__restrict__ A, int lda, const double *__restrict__ B, int ldb,
-                                      double *__restrict__ C, int ldc, int M, int N, int K, int w0, int nw,
-                                      const double *__restrict__ Dm = nullptr, int ldd = 0 /* C = Dm - A*B */) {
-    const int warp = (int)(threadIdx.x >> 5) - w0, lane = threadIdx.x & 31, g = lane >> 2, tg = lane & 3;
-    if (warp < 0 || warp >= nw) return;
-    const int mb = M / (8 * TM), nt = mb * (N >> 3);
-    for (int t = warp; t < nt; t += nw) {
-        const int tj = t / mb, i0 = (t - tj * mb) * 8 * TM, j0 = tj << 3;
-        const double *Ap = A + i0 + g + (size_t)lda * tg;
-        const double *Bp = B + tg + (size_t)ldb * (j0 + g);
-        double ca[2][TM], cb[2][TM];
-#pragma unroll
-        for (int i = 0; i < TM; ++i) ca[0][i] = cb[0][i] = ca[1][i] = cb[1][i] = 0.0;
-        int p0 = 0;
-#pragma unroll 2
-        for (; p0 + 8 <= K; p0 += 8) {
-            const double b0 = Bp[p0], b1 = Bp[p0 + 4];
-#pragma unroll
-            for (int i = 0; i < TM; ++i) {
-                dmma884(ca[0][i], cb[0][i], Ap[(size_t)lda * p0 + 8 * i], b0);
-                dmma884(ca[1][i], cb[1][i], Ap[(size_t)lda * (p0 + 4) + 8 * i], b1);
-            }
-        }
-        if (p0 < K) {
-            const double b0 = Bp[p0];
-#pragma unroll
-            for (int i = 0; i < TM; ++i) dmma884(ca[0][i], cb[0][i], Ap[(size_t)lda * p0 + 8 * i], b0);
-        }
-        double *Cp = C + i0 + g + (size_t)ldc * (j0 + 2 * tg);
-#pragma unroll
-        for (int i = 0; i < TM; ++i) {
-            double va = ca[0][i] + ca[1][i], vb = cb[0][i] + cb[1][i];
-            if (Dm) {
-                const double *Dp = Dm + i0 + g + 8 * i + (size_t)ldd * (j0 + 2 * tg);
-                va = Dp[0] - va;
-                vb = Dp[ldd] - vb;
-            }
-            Cp[8 * i] = va;
-            Cp[8 * i + ldc] = vb;
-        }
-    }
-}
-
 __constant__ double c_inv_fact[21] = {1.0, 1.0, 0.5, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040, 1.0 / 40320,
                                       1.0 / 362880, 1.0 / 3628800, 1.0 / 39916800, 1.0 / 479001600, 1.0 / 6227020800.0,
                                       1.0 / 87178291200.0, 1.0 / 1307674368000.0, 1.0 / 20922789888000.0,
@@ -952,44 +974,53 @@ k_apply2(double *__restrict__ U, const double *__restrict__ G, const double *__r
          float *__restrict__ uscale_out) {
     if (*nan_flag) return;
     extern __shared__ double sm[];
-    const int k = blockIdx.y, j0 = blockIdx.x * UP_ROWS, tid = threadIdx.x;
+    const int tid = threadIdx.x, k = blockIdx.y, j0 = blockIdx.x * UP_ROWS;
     const int rows = min(UP_ROWS, n - j0);
     const double *sk = small + (size_t)k * small_stride;
     SmallLayout L(r);
-    double *Us = sm, *Gs = Us + (size_t)UP_ROWS * r, *C1 = Gs + (size_t)UP_ROWS * r, *C2 = C1 + r * r;
+    // one product [U | G] (UP_ROWS x 2 npr) * [C1 ; C2] (2 npr x npr) on the FP64 tensor cores
+    const int npr = (r + 15) & ~15, lda = dmm_ld(UP_ROWS), ldb = dmm_ld(2 * npr), ldc = lda;
+    double *As = sm, *Bs = As + (size_t)lda * 2 * npr, *Cs = Bs + (size_t)ldb * npr;
     double *Uk = U + (size_t)k * r * n;
     const double *Gk = G + (size_t)k * r * n;
     if (uscale_out && blockIdx.x == 0 && k == 0 && tid == 0) {
         uscale_out[0] = UIMG_FIXED_SCALE;
         uscale_out[1] = 1.f / UIMG_FIXED_SCALE;
     }
-    for (int t = tid; t < UP_ROWS * r; t += UP_THREADS) {
+    for (int t = tid; t < UP_ROWS * npr; t += UP_THREADS) {
         const int jj = t % UP_ROWS, l = t / UP_ROWS;
-        const bool ok = jj < rows;
-        Us[t] = ok ? Uk[(size_t)l * n + j0 + jj] : 0.0;
-        Gs[t] = ok ? Gk[(size_t)l * n + j0 + jj] : 0.0;
+        const bool ok = jj < rows && l < r;
+        As[jj + (size_t)lda * l] = ok ? Uk[(size_t)l * n + j0 + jj] : 0.0;
+        As[jj + (size_t)lda * (npr + l)] = ok ? Gk[(size_t)l * n + j0 + jj] : 0.0;
     }
-    for (int t = tid; t < r * r; t += UP_THREADS) {
-        C1[t] = sk[L.C1 + t];
-        C2[t] = sk[L.C2 + t];
+    for (int t = tid; t < npr * npr; t += UP_THREADS) {
+        const int a = t % npr, l = t / npr;
+        const bool ok = a < r && l < r;
+        Bs[a + (size_t)ldb * l] = ok ? sk[L.C1 + a + r * l] : 0.0;
+        Bs[npr + a + (size_t)ldb * l] = ok ? sk[L.C2 + a + r * l] : 0.0;
     }
+    __syncthreads();
+    dmm_t<1>(As, lda, Bs, ldb, Cs, ldc, UP_ROWS, npr, 2 * npr, 0, UP_THREADS / 32);
     __syncthreads();
     for (int t = tid; t < UP_ROWS * r; t += UP_THREADS) {
         const int jj = t % UP_ROWS, l = t / UP_ROWS;
-        double s0 = 0.0, s1 = 0.0;
-        for (int a = 0; a < r; ++a) {
-            s0 = fma(Us[(size_t)a * UP_ROWS + jj], C1[a + r * l], s0);
-            s1 = fma(Gs[(size_t)a * UP_ROWS + jj], C2[a + r * l], s1);
-        }
-        const double s = s0 + s1;
-        if (jj < rows) {
-            Uk[(size_t)l * n + j0 + jj] = s;
-            if (Uimg) {
-                const float v = (float)s * UIMG_FIXED_SCALE;
-                const __half hh = __float2half_rn(v);
-                Uimg[gptb_uimg_offset(k, j0 + jj, l, npad, rpad)] = hh;
-                Uimg[gptb_uimg_offset(k, j0 + jj, rpad + l, npad, rpad)] = __float2half_rn(v - __half2float(hh));
+        if (jj < rows) Uk[(size_t)l * n + j0 + jj] = Cs[jj + (size_t)ldc * l];
+    }
+    if (Uimg) {
+        // image rows [j/8][nn/8][nn%8][j%8]: one 16-byte store per (8-row block, nn); rows past n and columns past r
+        // are zero in Cs (zero padded operands), which is what the image's padding must hold
+        for (int t = tid; t < (UP_ROWS / 8) * rpad; t += UP_THREADS) {
+            const int l = t % rpad, jb = t / rpad;
+            if (j0 + jb * 8 >= npad) continue;
+            __align__(16) __half hi[8], lo[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const float v = l < npr ? (float)Cs[jb * 8 + e + (size_t)ldc * l] * UIMG_FIXED_SCALE : 0.f;
+                hi[e] = __float2half_rn(v);
+                lo[e] = __float2half_rn(v - __half2float(hi[e]));
             }
+            *reinterpret_cast<uint4 *>(Uimg + gptb_uimg_offset(k, j0 + jb * 8, l, npad, rpad)) = *reinterpret_cast<uint4 *>(hi);
+            *reinterpret_cast<uint4 *>(Uimg + gptb_uimg_offset(k, j0 + jb * 8, rpad + l, npad, rpad)) = *reinterpret_cast<uint4 *>(lo);
         }
     }
 }
@@ -1042,7 +1073,7 @@ int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, cons
         if (!noise_w) noise_w = h->gen_noise_w;
         if (!noise_U) noise_U = h->gen_noise_U;
     }
-    size_t sm1 = 2 * (size_t)UP_ROWS * (c.r + 1) * sizeof(double);
+    size_t sm1 = 2 * (size_t)UP_ROWS * dmm_ld((c.r + 15) & ~15) * sizeof(double);
     k_prepare<<<dim3(nb, c.D + 1), UP_THREADS, sm1, h->stream>>>(h->grad, h->w, h->U, h->G, h->small, h->small_stride,
                                                                 c.n, c.r, c.D, c.Q, epsw, epsU, flags, noise_w,
                                                                 noise_U, c.seed, step, 1);
@@ -1054,7 +1085,8 @@ int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, cons
         if (sg.ok(c.r) && sg.bytes() <= 225 * 1024) {
             k_small2<<<c.D, 1024, sg.bytes(), h->stream>>>(h->small, h->small_stride, c.r, sqrt(epsU), h->nan_flag);
             const bool tc = gptb_is_tc(h);
-            size_t sm3 = (2 * (size_t)UP_ROWS * c.r + 2 * (size_t)c.r * c.r) * sizeof(double);
+            const int npr = (c.r + 15) & ~15;
+            size_t sm3 = ((size_t)dmm_ld(UP_ROWS) * 3 * npr + (size_t)dmm_ld(2 * npr) * npr) * sizeof(double);
             k_apply2<<<dim3(nb, c.D), UP_THREADS, sm3, h->stream>>>(h->U, h->G, h->small, h->small_stride, c.n, c.r,
                                                                    h->nan_flag, tc ? (__half *)h->Uimg : nullptr, h->npad,
                                                                    h->rpad, tc ? h->tc_state + 4 : nullptr);
