@@ -27,12 +27,17 @@
 
 #include "common.cuh"
 #include "tc_layout.cuh"
+#include "tc_ptx.cuh"
 
 namespace {
 
 constexpr int CRB = 64;          // rows per CTA
-constexpr int CNW = 24;          // warps per CTA: the gathers are latency-bound chains (offset load -> LDS -> FMUL2),
-                                 // and 128+ KB of tiles allow one CTA per SM, so the CTA itself must bring the warps
+#ifndef GPTB_CNW
+#define GPTB_CNW 20
+#endif
+constexpr int CNW = GPTB_CNW;    // warps per CTA.  The tiles (128+ KB at C4) allow one CTA per SM, so the CTA itself
+                                 // brings the warps that hide the LDS -> FMUL2 / FADD2 chains; 20 divides the work of
+                                 // the headline shape evenly (Q = 200 -> 10 q per warp, D*rpad/8 = 40 units -> 2 per warp)
 constexpr int CT_THREADS = 32 * CNW;
 
 struct ContractTcParams {
@@ -54,10 +59,12 @@ struct ContractTcParams {
 
 __device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
 __device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
+// shared-memory gather of this lane's two rows: `base` already carries the lane offset, `off` is a byte offset
+__device__ __forceinline__ float2 lds2(const char *base, int off) { return *reinterpret_cast<const float2 *>(base + off); }
 
 template <int DT>
 __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const ContractTcParams p) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr int D = DT;
     constexpr int DP4 = (DT + 3) / 4;
     const int r = p.r, rpad = p.rpad, Q = p.Q, DR = D * r;
@@ -69,22 +76,49 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     float2 *Vs = Ts + (size_t)DR * 32;                           // [Q + 1][32], row Q is zero
     float *ws = reinterpret_cast<float *>(Vs + (size_t)(Q + 1) * 32);   // [Q rounded up to 4]
     float2 *Fs = reinterpret_cast<float2 *>(ws + ((Q + 3) & ~3)); // [CNW][32]
-    // the (uniform) gather offsets, staged once per CTA: every use is then an LDS broadcast instead of a global load
+    // the (uniform) gather offsets, staged once per CTA as BYTE offsets: every use is an LDS broadcast
     int4 *off1s = reinterpret_cast<int4 *>(Fs + CNW * 32);       // [Q][DP4]
     int4 *lists_s = off1s + (size_t)Q * DP4;                     // [n_lists / 4]
     int *lptr_s = reinterpret_cast<int *>(lists_s + p.n_lists / 4);   // [D*rpad + 1]
-    for (int t = tid; t < Q * DP4; t += CT_THREADS) off1s[t] = __ldg(reinterpret_cast<const int4 *>(p.off1) + t);
-    for (int t = tid; t < p.n_lists / 4; t += CT_THREADS) lists_s[t] = __ldg(reinterpret_cast<const int4 *>(p.lists) + t);
-    for (int t = tid; t <= D * rpad; t += CT_THREADS) lptr_s[t] = __ldg(p.lptr + t);
 
+    // ---- prologue: the 64-row tile of T (one 256-byte row piece per (k,l)) arrives by 16-byte cp.async, all pieces in
+    // flight at once and no registers held; the tables are staged meanwhile
+    {
+        const float *src = p.T + (size_t)blockIdx.x * CRB;
+        const uint32_t dst = tcx::smem_u32(Ts);
+        for (int t = tid; t < DR * 16; t += CT_THREADS) {
+            const int c = t >> 4, part = t & 15;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (uint32_t)t * 16u),
+                         "l"(src + (size_t)c * p.mpad + part * 4)
+                         : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    for (int t = tid; t < Q * DP4; t += CT_THREADS) {
+        int4 v = __ldg(reinterpret_cast<const int4 *>(p.off1) + t);
+        v.x <<= 3; v.y <<= 3; v.z <<= 3; v.w <<= 3;
+        off1s[t] = v;
+    }
+    for (int t = tid; t < p.n_lists / 4; t += CT_THREADS) {
+        int4 v = __ldg(reinterpret_cast<const int4 *>(p.lists) + t);
+        v.x <<= 3; v.y <<= 3; v.z <<= 3; v.w <<= 3;
+        lists_s[t] = v;
+    }
+    for (int t = tid; t <= D * rpad; t += CT_THREADS) lptr_s[t] = __ldg(p.lptr + t);
     for (int t = tid; t < Q; t += CT_THREADS) ws[t] = (float)p.w[t];
     if (wp == 0) Vs[(size_t)Q * 32 + lane] = make_float2(0.f, 0.f);
-    for (int c = wp; c < DR; c += CNW)
-        Ts[(size_t)c * 32 + lane] = *reinterpret_cast<const float2 *>(p.T + (size_t)c * p.mpad + i0);
+    // the residual's inputs, fetched before the wait so that their latency is hidden too
+    double y0 = 0.0, y1 = 0.0;
+    if (p.want_grad) {
+        if (live0) y0 = p.yb[i0];
+        if (live1) y1 = p.yb[i0 + 1];
+    }
+    const float sc = *p.escale_img;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
 
     // ---- pass 1: V and fhat
-    const float2 *Trow = Ts + lane;
+    const char *Tb = reinterpret_cast<const char *>(Ts + lane);
     float2 f = make_float2(0.f, 0.f);
     for (int q0 = wp; q0 < Q; q0 += 2 * CNW) {       // two independent product chains per iteration
         const int q1 = q0 + CNW;
@@ -94,10 +128,10 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
 #pragma unroll
         for (int g4 = 0; g4 < DP4; ++g4) {
             const int4 a = o0[g4], b = o1[g4];
-            if (g4 * 4 + 0 < D) { v0 = mul2(v0, Trow[a.x]); v1 = mul2(v1, Trow[b.x]); }
-            if (g4 * 4 + 1 < D) { v0 = mul2(v0, Trow[a.y]); v1 = mul2(v1, Trow[b.y]); }
-            if (g4 * 4 + 2 < D) { v0 = mul2(v0, Trow[a.z]); v1 = mul2(v1, Trow[b.z]); }
-            if (g4 * 4 + 3 < D) { v0 = mul2(v0, Trow[a.w]); v1 = mul2(v1, Trow[b.w]); }
+            if (g4 * 4 + 0 < D) { v0 = mul2(v0, lds2(Tb, a.x)); v1 = mul2(v1, lds2(Tb, b.x)); }
+            if (g4 * 4 + 1 < D) { v0 = mul2(v0, lds2(Tb, a.y)); v1 = mul2(v1, lds2(Tb, b.y)); }
+            if (g4 * 4 + 2 < D) { v0 = mul2(v0, lds2(Tb, a.z)); v1 = mul2(v1, lds2(Tb, b.z)); }
+            if (g4 * 4 + 3 < D) { v0 = mul2(v0, lds2(Tb, a.w)); v1 = mul2(v1, lds2(Tb, b.w)); }
         }
         Vs[(size_t)q0 * 32 + lane] = v0;
         const float w0 = ws[q0];
@@ -119,8 +153,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     }
     if (!p.want_grad) return;
     float2 e;
-    e.x = live0 ? (float)(p.escale * (p.yb[i0] - (double)f.x)) : 0.f;
-    e.y = live1 ? (float)(p.escale * (p.yb[i0 + 1] - (double)f.y)) : 0.f;
+    e.x = live0 ? (float)(p.escale * (y0 - (double)f.x)) : 0.f;
+    e.y = live1 ? (float)(p.escale * (y1 - (double)f.y)) : 0.f;
 
     // ---- gradw: sum over the CTA's rows of e_i V[q,i]; V[q,i] <- w_q V[q,i] in place for pass 2
     constexpr int NB = 16;   // q per warp and batch
@@ -157,43 +191,47 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     __syncthreads();
 
     // ---- pass 2: E[k][l][i] = e_i * (sum_{q: I[q,k]=l} w_q V[q,i]) / T[k][l][i]
-    const int nlb = rpad / 8;
-    const float sc = *p.escale_img;
-    const float2 *Vrow = Vs + lane;
+    // A warp takes 4 consecutive l at a time (8-byte pieces of the operand image's 16-byte rows).  The four lists
+    // advance together, each at its own length (padded to 4 entries that address the zero row), so up to 16
+    // independent gathers are in flight per warp.
+    constexpr int LU = 4;
+    const int nlu = rpad / LU, nlb = rpad / 8;
+    const char *Vb = reinterpret_cast<const char *>(Vs + lane);
     float mx = 0.f;
-    for (int u = wp; u < D * nlb; u += CNW) {
-        const int k = u / nlb, lb = u - k * nlb;
-        float2 out[8];
-        // the eight lists of this unit advance together (independent gathers); exhausted lists read the zero row
-        int pb[9];
+    for (int u = wp; u < D * nlu; u += CNW) {
+        const int k = u / nlu, lu = u - k * nlu;
+        float2 out[LU];
+        int pb[LU + 1];
 #pragma unroll
-        for (int j = 0; j < 9; ++j) pb[j] = lptr_s[k * rpad + lb * 8 + j];
+        for (int j = 0; j <= LU; ++j) pb[j] = lptr_s[k * rpad + lu * LU + j];
         int maxlen = 0;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) maxlen = max(maxlen, pb[j + 1] - pb[j]);
-        float2 sum[8];
+        for (int j = 0; j < LU; ++j) maxlen = max(maxlen, pb[j + 1] - pb[j]);
+        float2 s0[LU], s1[LU];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) sum[j] = make_float2(0.f, 0.f);
-        const int zq = Q * 32;
+        for (int j = 0; j < LU; ++j) s0[j] = s1[j] = make_float2(0.f, 0.f);
         for (int g = 0; g < maxlen; g += 4) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
+            for (int j = 0; j < LU; ++j) {
                 const int pp = pb[j] + g;
-                int4 oo = make_int4(zq, zq, zq, zq);
-                if (pp < pb[j + 1]) oo = lists_s[pp >> 2];
-                sum[j] = add2(sum[j], add2(add2(Vrow[oo.x], Vrow[oo.y]), add2(Vrow[oo.z], Vrow[oo.w])));
+                if (pp < pb[j + 1]) {   // warp-uniform
+                    const int4 oo = lists_s[pp >> 2];
+                    s0[j] = add2(s0[j], add2(lds2(Vb, oo.x), lds2(Vb, oo.y)));
+                    s1[j] = add2(s1[j], add2(lds2(Vb, oo.z), lds2(Vb, oo.w)));
+                }
             }
         }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int l = lb * 8 + j;
+        for (int j = 0; j < LU; ++j) {
+            const int l = lu * LU + j;
             const int p0 = pb[j], p1 = pb[j + 1];
+            const float2 sum = add2(s0[j], s1[j]);
             float2 val = make_float2(0.f, 0.f);
             if (p1 > p0) {  // uniform across the CTA
-                const float2 t = Trow[(k * r + l) * 32];
+                const float2 t = Ts[(size_t)(k * r + l) * 32 + lane];
                 if (t.x != 0.f && t.y != 0.f) {
-                    val.x = e.x * __fdividef(sum[j].x, t.x);
-                    val.y = e.y * __fdividef(sum[j].y, t.y);
+                    val.x = e.x * __fdividef(sum.x, t.x);
+                    val.y = e.y * __fdividef(sum.y, t.y);
                 } else {  // exact zero factor: explicit leave-one-out products
                     float2 acc = make_float2(0.f, 0.f);
                     for (int pp = p0; pp < p1; ++pp) {
@@ -201,36 +239,41 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
                         if (q >= Q) continue;
                         float2 v = make_float2(ws[q], ws[q]);
                         for (int kk = 0; kk < D; ++kk)
-                            if (kk != k) v = mul2(v, Trow[__ldg(p.off1 + (size_t)q * p.DP + kk)]);
+                            if (kk != k) v = mul2(v, Ts[__ldg(p.off1 + (size_t)q * p.DP + kk) + lane]);
                         acc = add2(acc, v);
                     }
-                    val.x = live0 ? (t.x != 0.f ? e.x * __fdividef(sum[j].x, t.x) : e.x * acc.x) : 0.f;
-                    val.y = live1 ? (t.y != 0.f ? e.y * __fdividef(sum[j].y, t.y) : e.y * acc.y) : 0.f;
+                    val.x = live0 ? (t.x != 0.f ? e.x * __fdividef(sum.x, t.x) : e.x * acc.x) : 0.f;
+                    val.y = live1 ? (t.y != 0.f ? e.y * __fdividef(sum.y, t.y) : e.y * acc.y) : 0.f;
                 }
             }
             out[j] = val;
         }
         // fp16 hi|lo operand image for the backward MMA (tc_layout.cuh); the power-of-two scale comes from the
         // previous step's max|E| and keeps the entries in fp16's normal range.  Rows i0 and i0+1 are adjacent
-        // 16-byte rows of the same core matrix: one 32-byte store each for hi and lo.
-        __align__(16) __half hi[16], lo[16];
+        // 16-byte rows of the same core matrix; this unit owns 8 bytes (4 values of l) of each.
+        uint32_t hi[LU], lo[LU];   // [0..1]: row i0, l pairs; [2..3]: row i0 + 1
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            mx = fmaxf(mx, fmaxf(fabsf(out[j].x), fabsf(out[j].y)));
-            const float v0 = out[j].x * sc, v1 = out[j].y * sc;
-            const __half h0 = __float2half_rn(v0), h1 = __float2half_rn(v1);
-            hi[j] = h0;
-            hi[8 + j] = h1;
-            lo[j] = __float2half_rn(v0 - __half2float(h0));
-            lo[8 + j] = __float2half_rn(v1 - __half2float(h1));
+        for (int j = 0; j < LU; j += 2) {
+            mx = fmaxf(mx, fmaxf(fmaxf(fabsf(out[j].x), fabsf(out[j].y)), fmaxf(fabsf(out[j + 1].x), fabsf(out[j + 1].y))));
+            const float2 a0 = make_float2(out[j].x * sc, out[j + 1].x * sc);   // row i0, l = j, j+1
+            const float2 a1 = make_float2(out[j].y * sc, out[j + 1].y * sc);   // row i0 + 1
+            const __half2 h0 = __float22half2_rn(a0), h1 = __float22half2_rn(a1);
+            const float2 g0 = __half22float2(h0), g1 = __half22float2(h1);
+            const __half2 l0 = __float22half2_rn(make_float2(a0.x - g0.x, a0.y - g0.y));
+            const __half2 l1 = __float22half2_rn(make_float2(a1.x - g1.x, a1.y - g1.y));
+            hi[j / 2] = *reinterpret_cast<const uint32_t *>(&h0);
+            hi[LU / 2 + j / 2] = *reinterpret_cast<const uint32_t *>(&h1);
+            lo[j / 2] = *reinterpret_cast<const uint32_t *>(&l0);
+            lo[LU / 2 + j / 2] = *reinterpret_cast<const uint32_t *>(&l1);
         }
-        __half *base = p.Eimg + gptb_eimg_offset(k, i0, p.mpad, rpad);
-        uint4 *dh = reinterpret_cast<uint4 *>(base + (size_t)lb * 64);
-        uint4 *dl = reinterpret_cast<uint4 *>(base + (size_t)(nlb + lb) * 64);
-        dh[0] = reinterpret_cast<const uint4 *>(hi)[0];
-        dh[1] = reinterpret_cast<const uint4 *>(hi)[1];
-        dl[0] = reinterpret_cast<const uint4 *>(lo)[0];
-        dl[1] = reinterpret_cast<const uint4 *>(lo)[1];
+        const int lb = (lu * LU) >> 3, lin = (lu * LU) & 7;
+        __half *base = p.Eimg + gptb_eimg_offset(k, i0, p.mpad, rpad) + lin;
+        uint2 *dh = reinterpret_cast<uint2 *>(base + (size_t)lb * 64);
+        uint2 *dl = reinterpret_cast<uint2 *>(base + (size_t)(nlb + lb) * 64);
+        dh[0] = make_uint2(hi[0], hi[1]);
+        dh[2] = make_uint2(hi[2], hi[3]);    // row i0 + 1: 16 bytes on
+        dl[0] = make_uint2(lo[0], lo[1]);
+        dl[2] = make_uint2(lo[2], lo[3]);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));

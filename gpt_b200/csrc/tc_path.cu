@@ -38,7 +38,10 @@ namespace {
 
 using namespace tcx;
 
-constexpr int HSPLIT = 1;     // warps per TMEM lane quarter that share one chunk (each takes 64/HSPLIT of its K columns)
+#ifndef GPTB_HSPLIT
+#define GPTB_HSPLIT 1
+#endif
+constexpr int HSPLIT = GPTB_HSPLIT;     // warps per TMEM lane quarter that share one chunk (each takes 64/HSPLIT of its K columns)
 constexpr int NGEN = 4 / HSPLIT;   // generator groups (4*HSPLIT warps each); chunks go to the groups round-robin.
                               // Fewer, wider groups keep fewer A stages "in generation" and leave more of the ring
                               // as slack between the generators and the MMA issuers.
@@ -295,7 +298,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
         for (int u = u0; u < u1; ++u, ++it) {
             const int grp = u / ntiles, tile = u - grp * ntiles, k = grp / p.P;
             const uint32_t ab = it & 1;
-            mbar_wait(&bars->acc_full[ab], (it >> 1) & 1);
+            mbar_wait_relaxed(&bars->acc_full[ab], (it >> 1) & 1);
             fence_after_sync();
             const uint32_t d = acc_base + ab * NI * RPAD + lane_addr;
             const bool two = NI == 2 && min(p.NCHp, NCH - (grp % p.P) * p.NCHp) >= 2;
@@ -518,7 +521,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
             const int grp = (int)(it / NCH);
             it = min((long long)it1, (long long)(grp + 1) * NCH);
             const int k = grp / NJG, jg = grp - k * NJG;
-            mbar_wait(&bars->acc_full[0], seg & 1);
+            mbar_wait_relaxed(&bars->acc_full[0], seg & 1);
             fence_after_sync();
             for (int jbl = 0; jbl < JG; ++jbl) {
                 const int jb = jg * JG + jbl;

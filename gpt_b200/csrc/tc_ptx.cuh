@@ -50,6 +50,30 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {
     }
 }
+// Wait of a role that is off the critical path (epilogue warps waiting for a whole tile): a plain test and a
+// sleep between polls, so that the poll loop does not take issue slots from the generator warps of the same SM
+// sub-partition (the suspended try_wait above wakes every ~150 clk in practice).
+#ifndef GPTB_RELAXED_NS
+#define GPTB_RELAXED_NS 0
+#endif
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t *bar, uint32_t parity) {
+#if GPTB_RELAXED_NS > 0
+    for (;;) {
+        uint32_t ok;
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+        if (ok) break;
+        __nanosleep(GPTB_RELAXED_NS);
+    }
+#else
+    mbar_wait(bar, parity);
+#endif
+}
 
 // ---- bulk async copy global -> shared, completion on an mbarrier -----------------------------
 __device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar) {
