@@ -227,19 +227,27 @@ def main():
     # ------------------------------------------------------------------ resident-data steps/s (device timed)
     model.sgld_advance(SIGNAL_VAR, m, EPSW, EPSU, max(3, args.warmup))
     model.synchronize()
-    model.set_profiling(True)
-    model.phase_ms(reset=True)
+    model.phase_ms(reset=True)               # zero the launch counter
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     with ClockSampler(local) as clk:
         with torch.cuda.stream(stream):
             ev0.record(stream)
-            model.sgld_advance(SIGNAL_VAR, m, EPSW, EPSU, args.steps)
+            model.sgld_advance(SIGNAL_VAR, m, EPSW, EPSU, args.steps)   # returns with the stream ordered after the last update
             ev1.record(stream)
         model.synchronize()
         barrier()
     ms_total = ev0.elapsed_time(ev1)
-    phases, launches = model.phase_ms(reset=True)
+    _, launches = model.phase_ms(reset=True)
+    # per-phase device times come from a second, untimed pass: the phase events live on the main stream, so the
+    # profiled step is the one-stream step (no dimension-group pipelining)
+    kp = max(3, min(args.steps, 50))
+    model.set_profiling(True)
+    model.phase_ms(reset=True)
+    model.sgld_advance(SIGNAL_VAR, m, EPSW, EPSU, kp)
+    model.synchronize()
+    phases, _ = model.phase_ms(reset=True)
+    phases = {k: v * args.steps / kp for k, v in phases.items()}   # (the code below divides by args.steps)
     model.set_profiling(False)
     t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
     if world > 1:
@@ -343,7 +351,11 @@ def main():
     cos_peak = 16 * 148 * sm_mhz * 1e6                  # MUFU.COS: 16 / clk / SM (nominal), at the clock seen
     roofline = {"kernel": {"fwd": "fwd_tc_kernel (K1)", "bwd": "bwd_tc_kernel (K3)"}[dom], "bound": "tensor",
                 "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": (ach / peak_tf) if ach else None,
-                "traffic": None, "peak_source": which_peak, "avg_launch_ms": dom_ms,
+                # dram__bytes_read.sum + dram__bytes_write.sum of one K3 launch at this exact shape (ncu --set full,
+                # profiles/r1g_ncu_full_summary_C4_tc3.txt): 87.9 MB read (the E image, once per feature-block group)
+                # + 3.5 MB written; algorithmic bytes are 84 MB of E image + 2.6 MB of inputs + 1.3 MB of gradient
+                "traffic": 91461632 if (world == 1 and args.workload == "C4" and dom == "bwd") else None,
+                "peak_source": which_peak, "avg_launch_ms": dom_ms,
                 "algorithmic_flops_per_launch": per_launch_flops,
                 "sfu": {"cos_per_launch": ml * n * D, "achieved_Tcos_s": ml * n * D / (dom_ms * 1e-3) / 1e12 if dom_ms else None,
                         "peak_Tcos_s": cos_peak / 1e12, "frac": (ml * n * D / (dom_ms * 1e-3)) / cos_peak if dom_ms else None,

@@ -183,9 +183,11 @@ int refresh_shadows(gptb_handle *h) {
 
 // Forward for the rows staged in Xb/XbF (or phi rows): T, then fhat (and E / gradw when want_grad).
 int forward_contract(gptb_handle *h, bool phi_mode, const int32_t *rows, const double *w_dev, const double *U_dev,
-                     const void *Uimg, int64_t bs, double escale, bool want_grad, PhaseTimer *pt) {
+                     const void *Uimg, int64_t bs, double escale, bool want_grad, PhaseTimer *pt, bool fwd_done = false) {
     const bool f64 = use_fp64(h, phi_mode);
-    if (f64) {
+    if (fwd_done) {
+        // the pipelined step has launched the forward pass group by group
+    } else if (f64) {
         GPTB_TRY(gptb_launch_fwd_fp64(h, h->Xb, phi_mode ? h->phi : nullptr, rows, U_dev, bs, h->mpad, (double *)h->T));
     } else {
         GPTB_TRY(gptb_launch_fwd_tc(h, h->XbF, Uimg, bs, h->mpad, (float *)h->T));
@@ -247,6 +249,174 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
     return GPTB_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------------------------
+// Dimension-group pipeline of the SGLD step (tensor-core path, Stiefel update).
+//
+// The update of U^(k) (K5: a latency-bound chain of small FP64 kernels that occupies a handful of SMs) depends only
+// on the gradient of dimension k, and the next step's forward pass of dimension k only on the new U^(k).  The D
+// dimensions are therefore split into G groups; on the main stream the step runs
+//     gather, K1_0 .. K1_{G-1}, K2, K3_0 .. K3_{G-1}
+// and the update of group g runs on its own side stream as soon as K3_g is done, i.e. under K3_{g+1}.. and under
+// the next step's gather and K1_0 .. K1_{g-1}.  K1_g of the next step waits for the update of group g only.
+// Results do not depend on G: every kernel addresses parameters, gradients and Philox streams by the global k.
+// With several ranks each group's gradient slice is all-reduced on one dedicated NCCL stream.
+// ------------------------------------------------------------------------------------------------------------
+// G = 2 unless GPTB_PIPE_GROUPS says otherwise (0 or 1 switches the pipeline off; setting it also forces the
+// pipeline on for the small and multi-rank steps it is normally not used for — that is how the tests drive it).
+static int pipe_groups_for(gptb_handle *h) {
+    if (h->pipe_groups < 0) {
+        int g = 2;
+        if (const char *e = getenv("GPTB_PIPE_GROUPS")) {
+            g = atoi(e);
+            h->pipe_forced = true;
+        }
+        h->pipe_groups = std::max(0, std::min(g, (int)gptb_handle::PIPE_MAX));
+    }
+    return h->pipe_groups;
+}
+
+// Streams and events are created on first use and only as many as needed: streams beyond the device's hardware
+// queues (CUDA_DEVICE_MAX_CONNECTIONS, 8 by default) share a queue and serialise behind each other.
+static int pipe_init(gptb_handle *h, int G) {
+    for (int g = 0; g < G; ++g) {
+        if (h->side[g]) continue;
+        GPTB_CUDA_OK(h, cudaStreamCreateWithFlags(&h->side[g], cudaStreamNonBlocking));
+        GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&h->evG[g], cudaEventDisableTiming));
+        GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&h->evU[g], cudaEventDisableTiming));
+        GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&h->evR[g], cudaEventDisableTiming));
+    }
+    if (h->nranks > 1 && !h->ar_stream) GPTB_CUDA_OK(h, cudaStreamCreateWithFlags(&h->ar_stream, cudaStreamNonBlocking));
+    return GPTB_OK;
+}
+static int pipe_tail_init(gptb_handle *h) {
+    if (h->tail_stream) return GPTB_OK;
+    GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&h->evTail, cudaEventDisableTiming));
+    GPTB_CUDA_OK(h, cudaStreamCreateWithFlags(&h->tail_stream, cudaStreamNonBlocking));
+    return GPTB_OK;
+}
+
+// Order the main stream after everything the pipeline still has in flight.  Every entry point that reads or
+// writes parameters outside the step itself calls this first.
+int pipe_join(gptb_handle *h) {
+    for (int g = 0; g < gptb_handle::PIPE_MAX; ++g)
+        if (h->pendU[g]) {
+            GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->evU[g], 0));
+            h->pendU[g] = false;
+        }
+    if (h->tail_pending) {
+        GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->evTail, 0));
+        h->tail_pending = false;
+    }
+    return GPTB_OK;
+}
+
+// Stream for work that must follow the whole step (copies of the updated parameters, the NaN flag) without
+// holding the main stream back: the tail stream, ordered after every pending group update.
+static int pipe_tail_begin(gptb_handle *h, cudaStream_t *out) {
+    bool any = false;
+    for (int g = 0; g < gptb_handle::PIPE_MAX; ++g) any = any || h->pendU[g];
+    if (!any) {
+        *out = h->stream;
+        return GPTB_OK;
+    }
+    GPTB_TRY(pipe_tail_init(h));
+    for (int g = 0; g < gptb_handle::PIPE_MAX; ++g)
+        if (h->pendU[g]) GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->tail_stream, h->evU[g], 0));
+    *out = h->tail_stream;
+    return GPTB_OK;
+}
+static int pipe_tail_end(gptb_handle *h, cudaStream_t s) {
+    if (!h->tail_stream || s != h->tail_stream) return GPTB_OK;
+    GPTB_CUDA_OK(h, cudaEventRecord(h->evTail, s));
+    h->tail_pending = true;
+    return GPTB_OK;
+}
+
+static bool pipe_usable(gptb_handle *h, int64_t bs, bool staged_host_batch, int32_t flags) {
+    const bool phi_mode = h->have_phi && !staged_host_batch;
+    const int G = pipe_groups_for(h);
+    if (!(G >= 2 && h->cfg.D >= G && !h->profiling && !use_fp64(h, phi_mode) && (flags & GPTB_FLAG_STIEFEL) &&
+          bs >= h->nranks))
+        return false;
+    // Measured on B200 (C4, one rank): 668 -> 652 us per step with G = 2 and 5 SMs left to the update.  The update of a
+    // group is slower on the few SMs it gets (its row-block kernels cannot share an SM with the register-hungry
+    // persistent kernels), so it only hides under a back-projection of >= ~100 us: large single-rank batches.
+    return h->pipe_forced || (h->nranks == 1 && bs >= 32768);
+}
+
+// One SGLD step, pipelined over dimension groups (see above).  Same arguments as step_common.
+static int step_pipelined(gptb_handle *h, double signal_var, const int32_t *rows_dev, int64_t bs, int64_t N_total,
+                          bool staged_host_batch, const double *Xstage_rm, const double *ystage, double epsw, double epsU,
+                          int32_t flags, const double *nw_dev, const double *nU_dev) {
+    const gptb_config &c = h->cfg;
+    const int G = pipe_groups_for(h);
+    GPTB_TRY(pipe_init(h, G));
+    if ((flags & GPTB_FLAG_LANGEVIN) && (!nw_dev || !nU_dev)) GPTB_TRY(gptb_update_alloc_noise(h));
+    const int64_t lo = (int64_t)h->rank * bs / h->nranks, hi = (int64_t)(h->rank + 1) * bs / h->nranks;
+    const int64_t lbs = hi - lo;
+    if (h->cap < std::max<int64_t>(lbs, 1) || !h->shadows_valid) GPTB_TRY(pipe_join(h));   // (re)allocation / repacking read U
+    GPTB_TRY(ensure_batch(h, std::max<int64_t>(lbs, 1)));
+    GPTB_TRY(refresh_shadows(h));
+    const int32_t *rows = rows_dev ? rows_dev + lo : nullptr;
+    if (staged_host_batch) {
+        GPTB_TRY(gptb_launch_gather_from(h, Xstage_rm + (size_t)lo * c.D, ystage + lo, lbs, h->mpad, nullptr, h->XbF, h->yb));
+    } else {
+        GPTB_TRY(gptb_launch_gather(h, rows, 0, lbs, lo));
+    }
+    const double escale = ((double)N_total / (double)bs) / signal_var;  // (N/bs)/signal_var of :393,:407
+    int k0s[gptb_handle::PIPE_MAX + 1];
+    for (int g = 0; g <= G; ++g) k0s[g] = (int)((int64_t)c.D * g / G);
+    // The expm kernel of the update takes one whole SM per dimension (200 KB of shared memory), and the forward /
+    // backward kernels are persistent grids that would otherwise hold every SM until they end: they leave as many SMs
+    // free as one group has dimensions.
+    struct ReserveGuard {
+        gptb_handle *h;
+        ~ReserveGuard() { h->sm_reserve = 0; }
+    } guard{h};
+    {
+        int rsv = (c.D + G - 1) / G;
+        if (const char *e = getenv("GPTB_PIPE_RESERVE")) rsv = atoi(e);
+        h->sm_reserve = std::max(0, std::min(rsv, h->sm_count / 4));
+    }
+    // forward, group by group: K1_g needs the previous step's update of group g only
+    for (int g = 0; g < G; ++g) {
+        if (h->pendU[g]) {
+            GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->evU[g], 0));
+            h->pendU[g] = false;
+        }
+        GPTB_TRY(gptb_launch_fwd_tc_range(h, h->XbF, h->Uimg, lbs, h->mpad, (float *)h->T, k0s[g], k0s[g + 1] - k0s[g]));
+    }
+    // (group 0 carries w: from here on the previous step's w update is complete and gradw may be cleared)
+    GPTB_CUDA_OK(h, cudaMemsetAsync(h->grad, 0, sizeof(double) * c.Q, h->stream));
+    GPTB_TRY(forward_contract(h, false, rows, h->w, h->U, h->Uimg, lbs, escale, true, nullptr, true));
+    double *gU = h->grad + c.Q;
+    const size_t per_k = (size_t)c.r * c.n;
+    for (int g = 0; g < G; ++g) {
+        const int k0 = k0s[g], kn = k0s[g + 1] - k0s[g];
+        GPTB_CUDA_OK(h, cudaMemsetAsync(gU + (size_t)k0 * per_k, 0, sizeof(double) * per_k * kn, h->stream));
+        GPTB_TRY(gptb_launch_bwd_tc_range(h, h->XbF, h->Eimg, lbs, h->mpad, gU, k0, kn));
+        GPTB_CUDA_OK(h, cudaEventRecord(h->evG[g], h->stream));
+        cudaStream_t s = h->side[g];
+        if (h->tail_pending) GPTB_CUDA_OK(h, cudaStreamWaitEvent(s, h->evTail, 0));   // last step's parameter copies
+        if (h->nranks > 1) {
+            GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->ar_stream, h->evG[g], 0));
+            double *buf = g == 0 ? h->grad : gU + (size_t)k0 * per_k;
+            const size_t cnt = per_k * kn + (g == 0 ? (size_t)c.Q : 0);
+            GPTB_TRY(gptb_allreduce_range(h, buf, cnt, h->ar_stream));
+            GPTB_CUDA_OK(h, cudaEventRecord(h->evR[g], h->ar_stream));
+            GPTB_CUDA_OK(h, cudaStreamWaitEvent(s, h->evR[g], 0));
+        } else {
+            GPTB_CUDA_OK(h, cudaStreamWaitEvent(s, h->evG[g], 0));
+        }
+        GPTB_TRY(gptb_launch_update_range(h, epsw, epsU, flags, nw_dev, nU_dev, h->step_counter, k0, kn, g == 0, s));
+        GPTB_CUDA_OK(h, cudaEventRecord(h->evU[g], s));
+        h->pendU[g] = true;
+    }
+    h->step_counter++;
+    return GPTB_OK;
+}
+
 // Resolve batch rows on the device: explicit idx (host int64) or a range of the current order.
 int stage_rows(gptb_handle *h, const int64_t *idx, int64_t start, int64_t bs, const int32_t **rows_out) {
     if (bs <= 0 || (idx == nullptr && (start < 0 || start + bs > h->N))) {
@@ -283,6 +453,7 @@ int stage_noise(gptb_handle *h, const double *noise_w, const double *noise_U, co
     const gptb_config &c = h->cfg;
     *nw_dev = nullptr;
     *nU_dev = nullptr;
+    if (noise_w || noise_U) GPTB_TRY(pipe_join(h));   // the previous step's update may still be reading the staged draws
     if (noise_w) {
         if (!h->noise_w) GPTB_TRY(dev_alloc(h, &h->noise_w, (size_t)c.Q));
         GPTB_CUDA_OK(h, cudaMemcpyAsync(h->noise_w, noise_w, sizeof(double) * c.Q, cudaMemcpyHostToDevice, h->stream));
@@ -298,6 +469,7 @@ int stage_noise(gptb_handle *h, const double *noise_w, const double *noise_U, co
 }
 
 int check_nan(gptb_handle *h) {
+    GPTB_TRY(pipe_join(h));
     GPTB_CUDA_OK(h, cudaMemcpyAsync(h->nan_flag_host, h->nan_flag, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
     GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
     if (*h->nan_flag_host) {
@@ -410,7 +582,19 @@ int gptb_create(const gptb_config *cfg, gptb_handle **out) {
 int gptb_destroy(gptb_handle *h) {
     if (!h) return GPTB_OK;
     cudaSetDevice(h->device);
+    pipe_join(h);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    for (int g = 0; g < gptb_handle::PIPE_MAX; ++g)
+        if (h->side[g]) {
+            cudaStreamSynchronize(h->side[g]);
+            cudaStreamDestroy(h->side[g]);
+            cudaEventDestroy(h->evG[g]); cudaEventDestroy(h->evU[g]); cudaEventDestroy(h->evR[g]);
+        }
+    if (h->ar_stream) { cudaStreamSynchronize(h->ar_stream); cudaStreamDestroy(h->ar_stream); }
+    if (h->tail_stream) {
+        cudaStreamSynchronize(h->tail_stream); cudaStreamDestroy(h->tail_stream);
+        cudaEventDestroy(h->evTail);
+    }
     gptb_comm_destroy(h);
     dev_free(&h->Zt); dev_free(&h->b); dev_free(&h->ZtF); dev_free(&h->bF); dev_free(&h->I); dev_free(&h->grp_ptr); dev_free(&h->grp_q);
     dev_free(&h->ct_off1); dev_free(&h->ct_lptr); dev_free(&h->ct_lists);
@@ -451,6 +635,7 @@ int gptb_destroy(gptb_handle *h) {
 int gptb_set_stream(gptb_handle *h, void *cuda_stream) {
     if (!h) return GPTB_ERR_ARG;
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
     if (h->own_stream) cudaStreamDestroy(h->stream);
     if (cuda_stream) {
@@ -466,6 +651,7 @@ int gptb_set_stream(gptb_handle *h, void *cuda_stream) {
 int gptb_synchronize(gptb_handle *h) {
     if (!h) return GPTB_ERR_ARG;
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     if (h->have_params) return check_nan(h);   // also reports a geodesic NaN raised by queued steps
     GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
     return GPTB_OK;
@@ -484,6 +670,7 @@ int gptb_set_features(gptb_handle *h, const double *Z, const double *b, const do
         return GPTB_ERR_SHAPE;
     }
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     const size_t cnt = (size_t)c.D * c.n;
     std::vector<double> zt(cnt), bb(cnt, 0.0);
     std::vector<float> ztf((size_t)c.D * h->npad, 0.f), bf((size_t)c.D * h->npad, 0.f);
@@ -522,6 +709,7 @@ int gptb_set_index(gptb_handle *h, const int32_t *I) {
         z[t] = I[t] - 1;
     }
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     GPTB_CUDA_OK(h, cudaMemcpyAsync(h->I, z.data(), z.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
     // CSR over (k,l): the q with I[q,k] = l, in increasing q (the order computeA's findin visits them, :267)
     std::vector<int32_t> ptr((size_t)c.D * h->rpad + 1, 0);
@@ -562,6 +750,7 @@ static int set_train_common(gptb_handle *h, const double *y, int64_t N) {
 int gptb_set_train(gptb_handle *h, const double *X, const double *y, int64_t N) {
     if (!h || !X || !y || N < 1 || N > 2147483647LL) return GPTB_ERR_ARG;
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     const gptb_config &c = h->cfg;
     dev_free(&h->phi);
     h->have_phi = false;
@@ -584,6 +773,7 @@ int gptb_set_train(gptb_handle *h, const double *X, const double *y, int64_t N) 
 int gptb_set_train_phi(gptb_handle *h, const double *phi, const double *y, int64_t N) {
     if (!h || !phi || !y || N < 1 || N > 2147483647LL) return GPTB_ERR_ARG;
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     const gptb_config &c = h->cfg;
     dev_free(&h->X);
     h->have_train = false;
@@ -600,6 +790,7 @@ int gptb_set_params(gptb_handle *h, const double *w, const double *U) {
     if (!h || !w || !U) return GPTB_ERR_ARG;
     const gptb_config &c = h->cfg;
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     GPTB_CUDA_OK(h, cudaMemcpyAsync(h->w, w, sizeof(double) * c.Q, cudaMemcpyHostToDevice, h->stream));
     GPTB_CUDA_OK(h, cudaMemcpyAsync(h->U, U, sizeof(double) * c.n * c.r * c.D, cudaMemcpyHostToDevice, h->stream));
     GPTB_CUDA_OK(h, cudaMemsetAsync(h->nan_flag, 0, sizeof(int32_t), h->stream));
@@ -618,6 +809,7 @@ int gptb_get_params(gptb_handle *h, double *w, double *U) {
     }
     const gptb_config &c = h->cfg;
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     if (w) GPTB_CUDA_OK(h, cudaMemcpyAsync(w, h->w, sizeof(double) * c.Q, cudaMemcpyDeviceToHost, h->stream));
     if (U) GPTB_CUDA_OK(h, cudaMemcpyAsync(U, h->U, sizeof(double) * c.n * c.r * c.D, cudaMemcpyDeviceToHost, h->stream));
     GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
@@ -720,6 +912,7 @@ int gptb_features(gptb_handle *h, const double *X, int64_t N, double *phi_out) {
         return GPTB_ERR_STATE;
     }
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     const gptb_config &c = h->cfg;
     const int64_t chunk = std::max<int64_t>(1, (int64_t)(256ll << 20) / ((int64_t)c.n * c.D * 8));
     double *xc = nullptr, *xr = nullptr, *ph = nullptr;
@@ -834,6 +1027,7 @@ static int pred_impl(gptb_handle *h, const double *w_store, const double *U_stor
                      const double *phitest, int64_t Nt, double *mean_out, double *per_sample_out) {
     const gptb_config &c = h->cfg;
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     const bool phi_mode = phitest != nullptr;
     if (!phi_mode && !h->have_features) {
         gptb_set_error(h, "features not set");
@@ -927,6 +1121,7 @@ int gptb_grad(gptb_handle *h, double signal_var, const int64_t *idx, int64_t sta
     if (!h || !(signal_var > 0)) return GPTB_ERR_ARG;
     GPTB_TRY(check_ready(h, true, true));
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     const gptb_config &c = h->cfg;
     const int32_t *rows = nullptr;
     GPTB_TRY(stage_rows(h, idx, start, bs, &rows));
@@ -1012,6 +1207,9 @@ int gptb_geod(int32_t device, int32_t n, int32_t r, const double *U, const doubl
 static int step_common(gptb_handle *h, double signal_var, const int32_t *rows, int64_t bs, int64_t N_total,
                        bool staged, const double *Xstage, const double *ystage, double epsw, double epsU, int32_t flags,
                        const double *nw_dev, const double *nU_dev) {
+    if (pipe_usable(h, bs, staged, flags))
+        return step_pipelined(h, signal_var, rows, bs, N_total, staged, Xstage, ystage, epsw, epsU, flags, nw_dev, nU_dev);
+    GPTB_TRY(pipe_join(h));
     PhaseTimer pt(h);
     GPTB_TRY(compute_grad(h, signal_var, rows, bs, N_total, staged, Xstage, ystage, pt));
     GPTB_TRY(gptb_launch_update(h, epsw, epsU, flags, nw_dev, nU_dev, h->step_counter));
@@ -1026,12 +1224,14 @@ int gptb_sgld_step(gptb_handle *h, double signal_var, const int64_t *idx, int64_
     if (!h || !(signal_var > 0)) return GPTB_ERR_ARG;
     GPTB_TRY(check_ready(h, true, true));
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     const int32_t *rows = nullptr;
     GPTB_TRY(stage_rows(h, idx, start, bs, &rows));
     const double *nw = nullptr, *nU = nullptr;
     GPTB_TRY(stage_noise(h, noise_w, noise_U, &nw, &nU));
     GPTB_TRY(step_common(h, signal_var, rows, bs, h->N, false, nullptr, nullptr, epsw, epsU, flags, nw, nU));
     if (flags & GPTB_FLAG_STIEFEL) return check_nan(h);
+    GPTB_TRY(pipe_join(h));
     GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
     return GPTB_OK;
 }
@@ -1045,6 +1245,7 @@ int gptb_sgld_step_host(gptb_handle *h, double signal_var, const double *Xb, con
         return GPTB_ERR_STATE;
     }
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     const gptb_config &c = h->cfg;
     // stage the host minibatch: Xb[bs,D] column-major -> device, then row-major rows for the sharded gather
     if (h->stage_cap < bs) {
@@ -1059,6 +1260,7 @@ int gptb_sgld_step_host(gptb_handle *h, double signal_var, const double *Xb, con
     const double *nw = nullptr, *nU = nullptr;
     GPTB_TRY(stage_noise(h, noise_w, noise_U, &nw, &nU));
     GPTB_TRY(step_common(h, signal_var, nullptr, bs, N_total, true, h->stage_rm, h->stage_y, epsw, epsU, flags, nw, nU));
+    GPTB_TRY(pipe_join(h));
     if (w_out) GPTB_CUDA_OK(h, cudaMemcpyAsync(w_out, h->w, sizeof(double) * c.Q, cudaMemcpyDeviceToHost, h->stream));
     if (flags & GPTB_FLAG_STIEFEL) return check_nan(h);
     GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
@@ -1122,11 +1324,15 @@ int gptb_sgld_step_host_submit(gptb_handle *h, double signal_var, const double *
     const double *nw = nullptr, *nU = nullptr;
     GPTB_TRY(stage_noise(h, noise_w, noise_U, &nw, &nU));
     GPTB_TRY(step_common(h, signal_var, nullptr, bs, N_total, true, h->stage_rm, h->pipe_y[slot], epsw, epsU, flags, nw, nU));
-    if (w_out) GPTB_CUDA_OK(h, cudaMemcpyAsync(w_out, h->w, sizeof(double) * c.Q, cudaMemcpyDeviceToHost, h->stream));
+    // the step's read-backs follow its last group update on the tail stream; the main stream is free for the next step
+    cudaStream_t ts = nullptr;
+    GPTB_TRY(pipe_tail_begin(h, &ts));
+    if (w_out) GPTB_CUDA_OK(h, cudaMemcpyAsync(w_out, h->w, sizeof(double) * c.Q, cudaMemcpyDeviceToHost, ts));
     h->pipe_stiefel[slot] = (flags & GPTB_FLAG_STIEFEL) != 0;
     if (h->pipe_stiefel[slot])
-        GPTB_CUDA_OK(h, cudaMemcpyAsync(h->pipe_nan_host + slot, h->nan_flag, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
-    GPTB_CUDA_OK(h, cudaEventRecord(h->pipe_done[slot], h->stream));
+        GPTB_CUDA_OK(h, cudaMemcpyAsync(h->pipe_nan_host + slot, h->nan_flag, sizeof(int32_t), cudaMemcpyDeviceToHost, ts));
+    GPTB_CUDA_OK(h, cudaEventRecord(h->pipe_done[slot], ts));
+    GPTB_TRY(pipe_tail_end(h, ts));
     ++h->pipe_submitted;
     return GPTB_OK;
 }
@@ -1149,6 +1355,7 @@ int gptb_sgld_run(gptb_handle *h, double signal_var, int64_t m, double epsw, dou
     if (!h || m < 1 || burnin < 0 || maxepoch < 0 || !(signal_var > 0)) return GPTB_ERR_ARG;
     GPTB_TRY(check_ready(h, true, true));
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     const gptb_config &c = h->cfg;
     const int64_t N = h->N;
     const int64_t numbatches = (N + m - 1) / m;  // :353
@@ -1189,14 +1396,20 @@ int gptb_sgld_run(gptb_handle *h, double signal_var, int64_t m, double epsw, dou
             if (st != GPTB_OK) break;
             if (epoch > burnin && keep) {
                 const int64_t col = (int64_t)(epoch - burnin - 1) * numbatches + batch - 1;  // :442-443
-                if (w_store) cudaMemcpyAsync(h->store_w + (size_t)col * c.Q, h->w, sizeof(double) * c.Q, cudaMemcpyDeviceToDevice, h->stream);
-                if (U_store) cudaMemcpyAsync(h->store_U + (size_t)col * ucnt, h->U, sizeof(double) * ucnt, cudaMemcpyDeviceToDevice, h->stream);
+                cudaStream_t ts = nullptr;
+                st = pipe_tail_begin(h, &ts);
+                if (st != GPTB_OK) break;
+                if (w_store) cudaMemcpyAsync(h->store_w + (size_t)col * c.Q, h->w, sizeof(double) * c.Q, cudaMemcpyDeviceToDevice, ts);
+                if (U_store) cudaMemcpyAsync(h->store_U + (size_t)col * ucnt, h->U, sizeof(double) * ucnt, cudaMemcpyDeviceToDevice, ts);
+                st = pipe_tail_end(h, ts);
+                if (st != GPTB_OK) break;
             }
         }
         // the reference tests for the NaN abort after every geodesic (:422); the device flag is sticky and
         // freezes the parameters, so looking at it once per epoch returns the same all-zero result
         if (st == GPTB_OK && (flags & GPTB_FLAG_STIEFEL)) st = check_nan(h);
     }
+    if (pipe_join(h) != GPTB_OK && st == GPTB_OK) st = GPTB_ERR_CUDA;
     if (st == GPTB_OK) {
         cudaError_t e = cudaSuccess;
         if (keep && w_store) e = cudaMemcpyAsync(w_store, h->store_w, sizeof(double) * c.Q * T, cudaMemcpyDeviceToHost, h->stream);
@@ -1223,6 +1436,7 @@ int gptb_sgld_advance(gptb_handle *h, double signal_var, int64_t m, double epsw,
     if (!h || m < 1 || nsteps < 0 || !(signal_var > 0)) return GPTB_ERR_ARG;
     GPTB_TRY(check_ready(h, true, true));
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
     const int64_t N = h->N;
     const int64_t numbatches = (N + m - 1) / m;
     for (int64_t s = 0; s < nsteps; ++s) {
@@ -1235,11 +1449,14 @@ int gptb_sgld_advance(gptb_handle *h, double signal_var, int64_t m, double epsw,
                              nullptr, nullptr));
         h->batch_cursor = (h->batch_cursor + 1) % numbatches;
     }
+    GPTB_TRY(pipe_join(h));   // work queued on the caller's stream after this call sees the final parameters
     return GPTB_OK;
 }
 
 int gptb_set_profiling(gptb_handle *h, int32_t on) {
     if (!h) return GPTB_ERR_ARG;
+    cudaSetDevice(h->device);
+    GPTB_TRY(pipe_join(h));   // the profiled step is the unpipelined one (phase timers live on the main stream)
     h->profiling = on != 0;
     return GPTB_OK;
 }

@@ -122,3 +122,17 @@ int gptb_allreduce_grad(gptb_handle *h) {
     h->launches++;
     return GPTB_OK;
 }
+
+// The same for a slice of the gradient buffer on a given stream (the dimension-group pipeline reduces each group's
+// slice on its own NCCL stream, in the same order on every rank).
+int gptb_allreduce_range(gptb_handle *h, double *buf, size_t count, cudaStream_t stream) {
+    if (h->nranks <= 1 || count == 0) return GPTB_OK;
+    NcclApi &a = api();
+    ncclResult r = a.AllReduce(buf, buf, count, kNcclFloat64, kNcclSum, (ncclComm_p)h->nccl_comm, stream);
+    if (r != 0) {
+        gptb_set_error(h, "ncclAllReduce: %s", a.GetErrorString(r));
+        return GPTB_ERR_NCCL;
+    }
+    h->launches++;
+    return GPTB_OK;
+}

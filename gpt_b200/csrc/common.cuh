@@ -119,6 +119,19 @@ struct gptb_handle {
     double *noise_w = nullptr, *noise_U = nullptr;  // staged host-supplied noise
     double *gen_noise_w = nullptr, *gen_noise_U = nullptr;   // production-mode draws of the running step (k_noise)
 
+    // dimension-group pipeline of the SGLD step (api.cu: step_pipelined): the update of group g runs on side[g] while
+    // the main stream goes on with the next group's back-projection / the next step's forward pass
+    static constexpr int PIPE_MAX = 4;
+    int pipe_groups = -1;              // -1: not decided yet; 0/1: off
+    bool pipe_forced = false;          // GPTB_PIPE_GROUPS set: use the pipeline for every eligible step
+    cudaStream_t side[PIPE_MAX] = {nullptr, nullptr, nullptr, nullptr};
+    cudaStream_t tail_stream = nullptr, ar_stream = nullptr;
+    cudaEvent_t evG[PIPE_MAX] = {}, evU[PIPE_MAX] = {}, evR[PIPE_MAX] = {};
+    cudaEvent_t evTail = nullptr;
+    bool pendU[PIPE_MAX] = {false, false, false, false};
+    bool tail_pending = false;
+    int sm_reserve = 0;                // SMs the persistent K1 / K3 grids leave to the concurrent group update
+
     // multi-sample prediction scratch
     double *pred_acc = nullptr;
     int64_t pred_cap = 0;
@@ -220,6 +233,9 @@ int gptb_launch_contract_tc(gptb_handle *h, const float *T, const double *w, con
 // update.cu
 int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
                        const double *noise_U, uint64_t step);
+int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
+                             const double *noise_U, uint64_t step, int k0, int kn, bool with_w, cudaStream_t s);
+int gptb_update_alloc_noise(gptb_handle *h);
 int gptb_proj_geod_device(gptb_handle *scratch_owner, cudaStream_t s, int n, int r, const double *U, const double *V,
                           double t, double *out, int mode /*0 proj, 1 geod*/, int32_t *nan_flag);
 // batch.cu
@@ -239,7 +255,13 @@ int gptb_launch_contract_fwd(gptb_handle *h, const float *T, const double *w_gro
                              int ncols_total, double *fh_group /*[Sg][mpad] or null*/, double *mean_acc /*[mpad] or null*/,
                              double mean_scale);
 int gptb_launch_bwd_tc(gptb_handle *h, const float *XbF, const void *Eimg, int64_t bs, int64_t mpad, double *gradU);
+// the same for the dimensions [k0, k0 + kn) only (all pointers are those of the full problem)
+int gptb_launch_bwd_tc_range(gptb_handle *h, const float *XbF, const void *Eimg, int64_t bs, int64_t mpad, double *gradU,
+                             int k0, int kn);
+int gptb_launch_fwd_tc_range(gptb_handle *h, const float *XbF, const void *Uimg, int64_t bs, int64_t mpad, float *T, int k0,
+                             int kn);
 size_t gptb_tc_uimg_bytes(const gptb_handle *h);
 size_t gptb_tc_eimg_bytes(const gptb_handle *h, int64_t mpad);
 // comm.cu
 int gptb_allreduce_grad(gptb_handle *h);
+int gptb_allreduce_range(gptb_handle *h, double *buf, size_t count, cudaStream_t stream);

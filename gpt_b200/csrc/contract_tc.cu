@@ -392,7 +392,7 @@ struct ContractFwdParams {
 
 template <int DT>
 __global__ void __launch_bounds__(256) contract_fwd_kernel(const ContractFwdParams p) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr int D = DT;
     constexpr int DP4 = (DT + 3) / 4;
     constexpr int NW = 8;

@@ -698,21 +698,31 @@ static int launch_bwd_r(gptb_handle *h, const BwdParams &p, int grid, size_t sme
 // Forward with an explicit operand geometry: the image has NC columns per hi / lo half (NC a multiple of 16, at most
 // 128), `ncols` of them live; T is [D][ncols][mpad].  The sampler uses (r, rpad); the posterior-predictive sweep packs
 // several samples' factors side by side (ncols = Sg*r), so the features are generated once per sample group.
+static int launch_fwd_tc_cols_range(gptb_handle *h, const float *XbF, const void *Uimg, const float *uscale, int64_t bs,
+                                    int64_t mpad, float *T, int ncols, int NC, int k0, int kn);
+
 int gptb_launch_fwd_tc_cols(gptb_handle *h, const float *XbF, const void *Uimg, const float *uscale, int64_t bs,
                             int64_t mpad, float *T, int ncols, int NC) {
+    return launch_fwd_tc_cols_range(h, XbF, Uimg, uscale, bs, mpad, T, ncols, NC, 0, h->cfg.D);
+}
+
+// Dimensions [k0, k0 + kn) of the forward pass: every per-dimension array is entered at k0, the kernel sees D = kn.
+static int launch_fwd_tc_cols_range(gptb_handle *h, const float *XbF, const void *Uimg, const float *uscale, int64_t bs,
+                                    int64_t mpad, float *T, int ncols, int NC, int k0, int kn) {
     const gptb_config &c = h->cfg;
     if (!h->ZbF_valid) {
         GPTB_TRY(gptb_tc_prepare_features(h));
         h->ZbF_valid = true;
     }
     FwdParams p;
-    p.XbF = XbF;
-    p.Uimg = (const __half *)Uimg;
-    p.ZbF = (const float2 *)h->ZbF;
+    p.XbF = XbF + (size_t)k0 * mpad;
+    p.Uimg = (const __half *)Uimg + (size_t)k0 * h->npad * 2 * NC;
+    p.ZbF = (const float2 *)h->ZbF + (size_t)k0 * h->npad;
     p.uscale = uscale;
+    T += (size_t)k0 * ncols * mpad;
     p.T = T;
     p.amp = (float)h->amp;
-    p.D = c.D; p.n = c.n; p.npad = h->npad; p.r = ncols;
+    p.D = kn; p.n = c.n; p.npad = h->npad; p.r = ncols;
     p.bs = bs;
     p.mpad = mpad;
     p.mext = (bs + 127) / 128 * 128;   // only the 128-row tiles that hold live rows are generated
@@ -724,9 +734,9 @@ int gptb_launch_fwd_tc_cols(gptb_handle *h, const float *XbF, const void *Uimg, 
     const int max_chunks = (int)(budget / chunk_bytes);
     p.P = (NCH + max_chunks - 1) / max_chunks;
     p.NCHp = (NCH + p.P - 1) / p.P;
-    if (p.P > 1) GPTB_CUDA_OK(h, cudaMemsetAsync(T, 0, sizeof(float) * (size_t)c.D * ncols * mpad, h->stream));
-    const int nunits = (int)(p.mext / 128) * c.D * p.P;
-    const int grid = std::max(1, std::min(h->sm_count, nunits));
+    if (p.P > 1) GPTB_CUDA_OK(h, cudaMemsetAsync(T, 0, sizeof(float) * (size_t)kn * ncols * mpad, h->stream));
+    const int nunits = (int)(p.mext / 128) * kn * p.P;
+    const int grid = std::max(1, std::min(h->sm_count - h->sm_reserve, nunits));
     // at least 120 KB so that two CTAs (each wants all 512 TMEM columns) never share an SM
     const size_t smem = std::max<size_t>((size_t)p.NCHp * chunk_bytes + sizeof(Bars) + 64, 120 * 1024);
     int st;
@@ -751,6 +761,11 @@ int gptb_launch_fwd_tc_cols(gptb_handle *h, const float *XbF, const void *Uimg, 
 
 int gptb_launch_fwd_tc(gptb_handle *h, const float *XbF, const void *Uimg, int64_t bs, int64_t mpad, float *T) {
     return gptb_launch_fwd_tc_cols(h, XbF, Uimg, h->tc_state + (Uimg == h->Uimg ? 4 : 7), bs, mpad, T, h->cfg.r, h->rpad);
+}
+int gptb_launch_fwd_tc_range(gptb_handle *h, const float *XbF, const void *Uimg, int64_t bs, int64_t mpad, float *T, int k0,
+                             int kn) {
+    return launch_fwd_tc_cols_range(h, XbF, Uimg, h->tc_state + (Uimg == h->Uimg ? 4 : 7), bs, mpad, T, h->cfg.r, h->rpad, k0,
+                                    kn);
 }
 
 // Operand image of a group of Sg posterior samples side by side: column s*r + l of dimension k is U_s[:, l, k].
@@ -796,6 +811,11 @@ int gptb_tc_pack_group(gptb_handle *h, const double *Ug, int Sg, int NC, void *i
 }
 
 int gptb_launch_bwd_tc(gptb_handle *h, const float *XbF, const void *Eimg, int64_t bs, int64_t mpad, double *gradU) {
+    return gptb_launch_bwd_tc_range(h, XbF, Eimg, bs, mpad, gradU, 0, h->cfg.D);
+}
+
+int gptb_launch_bwd_tc_range(gptb_handle *h, const float *XbF, const void *Eimg, int64_t bs, int64_t mpad, double *gradU,
+                             int k0, int kn) {
     const gptb_config &c = h->cfg;
     const size_t gf = (size_t)c.D * h->npad * h->rpad;
     if (!h->gradF) {
@@ -804,14 +824,15 @@ int gptb_launch_bwd_tc(gptb_handle *h, const float *XbF, const void *Eimg, int64
     }
     BwdParams p;
     p.mext = (bs + 127) / 128 * 128;
-    p.XbF = XbF;
-    p.Eimg = (const __half *)Eimg;
-    p.ZtF = h->ZtF;
-    p.bF = h->bF;
+    float *gradF_g = h->gradF + (size_t)k0 * h->npad * h->rpad;
+    p.XbF = XbF + (size_t)k0 * mpad;
+    p.Eimg = (const __half *)Eimg + (size_t)k0 * mpad * 2 * h->rpad;
+    p.ZtF = h->ZtF + (size_t)k0 * h->npad;
+    p.bF = h->bF + (size_t)k0 * h->npad;
     p.escale = h->tc_state + 1;
-    p.gradF = h->gradF;
+    p.gradF = gradF_g;
     p.amp = (float)h->amp;
-    p.D = c.D; p.n = c.n; p.npad = h->npad; p.r = c.r;
+    p.D = kn; p.n = c.n; p.npad = h->npad; p.r = c.r;
     p.mpad = mpad;
     p.sincos = c.feature_kind == GPTB_FEAT_SINCOS;
     const int JB = h->npad / 128;
@@ -819,8 +840,8 @@ int gptb_launch_bwd_tc(gptb_handle *h, const float *XbF, const void *Eimg, int64
     p.NJG = (JB + jg_max - 1) / jg_max;
     p.JG = (JB + p.NJG - 1) / p.NJG;
     p.nsta = nsta_for(p.JG * h->rpad);
-    const int64_t total = (int64_t)c.D * p.NJG * (p.mext / KC);
-    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(h->sm_count, total));
+    const int64_t total = (int64_t)kn * p.NJG * (p.mext / KC);
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(h->sm_count - h->sm_reserve, total));
     const size_t smem = std::max<size_t>((size_t)NSTB * (2 * h->rpad * KC * 2 + KC * 4) + sizeof(Bars) + 64, 120 * 1024);
     int st;
     switch (h->rpad) {
@@ -830,7 +851,8 @@ int gptb_launch_bwd_tc(gptb_handle *h, const float *XbF, const void *Eimg, int64
         default: st = launch_bwd_r<64>(h, p, grid, smem); break;
     }
     GPTB_TRY(st);
-    finalize_grad_kernel<<<dim3(h->npad / 32, c.D), 256, 0, h->stream>>>(h->gradF, gradU, c.n, h->npad, c.r, h->rpad);
+    finalize_grad_kernel<<<dim3(h->npad / 32, kn), 256, 0, h->stream>>>(gradF_g, gradU + (size_t)k0 * c.r * c.n, c.n, h->npad,
+                                                                       c.r, h->rpad);
     h->launches += 2;
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;

@@ -121,11 +121,13 @@ __global__ void __launch_bounds__(UP_THREADS)
 k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ w, double *__restrict__ U,
           double *__restrict__ G, double *__restrict__ small, size_t small_stride, int n, int r, int D, int Q,
           double epsw, double epsU, int flags, const double *__restrict__ noise_w,
-          const double *__restrict__ noise_U, uint64_t key, uint64_t step, int have_grad) {
+          const double *__restrict__ noise_U, uint64_t key, uint64_t step, int have_grad, int k0, int kn) {
+    // grid.y = kn (+ 1): rows 0..kn-1 are the dimensions k0.., row kn (if launched) is w
     extern __shared__ double sm[];
     const int tid = threadIdx.x;
     const bool langevin = flags & GPTB_FLAG_LANGEVIN, stiefel = flags & GPTB_FLAG_STIEFEL;
-    if (blockIdx.y == D) {
+    (void)D;
+    if ((int)blockIdx.y == kn) {
         if (blockIdx.x != 0 || !have_grad) return;
         const double sq = sqrt(epsw);
         for (int q = tid; q < Q; q += UP_THREADS) {
@@ -136,7 +138,7 @@ k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ 
         }
         return;
     }
-    const int k = blockIdx.y;
+    const int k = k0 + blockIdx.y;
     const int j0 = blockIdx.x * UP_ROWS;
     const int rows = min(UP_ROWS, n - j0);
     const double *gU = grad + Q + (size_t)k * r * n;
@@ -661,12 +663,14 @@ k_reduce_only(const double *__restrict__ U, const double *__restrict__ G, double
 
 // Production-mode noise of one step, two draws per Philox block (same counters as noise_at()).
 // grid.y = D + 1; row D is the w noise.
-__global__ void k_noise(double *__restrict__ noise_w, double *__restrict__ noise_U, int Q, size_t per_k, int D,
+__global__ void k_noise(double *__restrict__ noise_w, double *__restrict__ noise_U, int Q, size_t per_k, int k0, int kn,
                         uint64_t key, uint64_t step) {
-    const int k = blockIdx.y;
-    const size_t cnt = k == D ? (size_t)Q : per_k;
-    const uint64_t stream = k == D ? GPTB_STREAM_NOISE_W : (GPTB_STREAM_NOISE_U | ((uint64_t)k << 40));
-    double *out = k == D ? noise_w : noise_U + (size_t)k * per_k;
+    // grid.y = kn (+ 1): rows 0..kn-1 are the dimensions k0.., row kn (if launched) is the w noise
+    const bool is_w = (int)blockIdx.y == kn;
+    const int k = k0 + blockIdx.y;
+    const size_t cnt = is_w ? (size_t)Q : per_k;
+    const uint64_t stream = is_w ? GPTB_STREAM_NOISE_W : (GPTB_STREAM_NOISE_U | ((uint64_t)k << 40));
+    double *out = is_w ? noise_w : noise_U + (size_t)k * per_k;
     for (size_t pe = blockIdx.x * (size_t)blockDim.x + threadIdx.x; 2 * pe < cnt; pe += (size_t)gridDim.x * blockDim.x) {
         double a, b;
         philox_normal2(key, stream | pe, step, &a, &b);
@@ -1049,61 +1053,75 @@ static size_t small_smem_bytes(int r) {
     return b <= 200 * 1024 ? b : 0;
 }
 
-static int zero_small(gptb_handle *h, double *small, size_t stride, int D, int r) {
-    SmallLayout L(r);
-    GPTB_CUDA_OK(h, cudaMemset2DAsync(small, stride * sizeof(double), 0, L.zero_count() * sizeof(double), D, h->stream));
+int gptb_update_alloc_noise(gptb_handle *h) {
+    const gptb_config &c = h->cfg;
+    const size_t per_k = (size_t)c.r * c.n;
+    if (!h->gen_noise_w) GPTB_CUDA_OK(h, cudaMalloc((void **)&h->gen_noise_w, sizeof(double) * (c.Q + 2)));
+    if (!h->gen_noise_U) GPTB_CUDA_OK(h, cudaMalloc((void **)&h->gen_noise_U, sizeof(double) * (per_k * c.D + 2)));
     return GPTB_OK;
 }
 
-int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
-                       const double *noise_U, uint64_t step) {
+// The update of the dimensions [k0, k0 + kn) (and of w when with_w) on stream s.  The kernels address everything by
+// the global k, so that the Philox streams and hence the chain do not depend on how the dimensions are grouped.
+int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
+                             const double *noise_U, uint64_t step, int k0, int kn, bool with_w, cudaStream_t s) {
     const gptb_config &c = h->cfg;
     const int nb = (c.n + UP_ROWS - 1) / UP_ROWS;
     const bool stiefel = flags & GPTB_FLAG_STIEFEL, langevin = flags & GPTB_FLAG_LANGEVIN;
     const size_t per_k = (size_t)c.r * c.n;
+    const int gy = kn + (with_w ? 1 : 0);
     optin_smem();
-    if (stiefel) GPTB_TRY(zero_small(h, h->small, h->small_stride, c.D, c.r));
+    double *small_g = h->small + (size_t)k0 * h->small_stride;
+    if (stiefel) {
+        SmallLayout L(c.r);
+        GPTB_CUDA_OK(h, cudaMemset2DAsync(small_g, h->small_stride * sizeof(double), 0, L.zero_count() * sizeof(double), kn, s));
+    }
     if (langevin && (!noise_w || !noise_U)) {
         // production mode: the step's draws are generated up front by a grid-wide kernel (two per Philox block)
-        if (!h->gen_noise_w) GPTB_CUDA_OK(h, cudaMalloc((void **)&h->gen_noise_w, sizeof(double) * (c.Q + 2)));
-        if (!h->gen_noise_U) GPTB_CUDA_OK(h, cudaMalloc((void **)&h->gen_noise_U, sizeof(double) * (per_k * c.D + 2)));
+        GPTB_TRY(gptb_update_alloc_noise(h));
         const int gx = (int)std::min<size_t>((per_k / 2 + 255) / 256, 64);
-        k_noise<<<dim3(gx, c.D + 1), 256, 0, h->stream>>>(h->gen_noise_w, h->gen_noise_U, c.Q, per_k, c.D, c.seed, step);
+        k_noise<<<dim3(gx, gy), 256, 0, s>>>(h->gen_noise_w, h->gen_noise_U, c.Q, per_k, k0, kn, c.seed, step);
         h->launches++;
         if (!noise_w) noise_w = h->gen_noise_w;
         if (!noise_U) noise_U = h->gen_noise_U;
     }
     size_t sm1 = 2 * (size_t)UP_ROWS * dmm_ld((c.r + 15) & ~15) * sizeof(double);
-    k_prepare<<<dim3(nb, c.D + 1), UP_THREADS, sm1, h->stream>>>(h->grad, h->w, h->U, h->G, h->small, h->small_stride,
-                                                                c.n, c.r, c.D, c.Q, epsw, epsU, flags, noise_w,
-                                                                noise_U, c.seed, step, 1);
+    k_prepare<<<dim3(nb, gy), UP_THREADS, sm1, s>>>(h->grad, h->w, h->U, h->G, h->small, h->small_stride, c.n, c.r, c.D, c.Q,
+                                                   epsw, epsU, flags, noise_w, noise_U, c.seed, step, 1, k0, kn);
     h->launches++;
     h->shadows_valid = false;
     if (stiefel) {
         const size_t sb = small_smem_bytes(c.r);
         const Small2Geo sg(c.r);
+        const size_t koff = (size_t)k0 * c.r * c.n;
         if (sg.ok(c.r) && sg.bytes() <= 225 * 1024) {
-            k_small2<<<c.D, 1024, sg.bytes(), h->stream>>>(h->small, h->small_stride, c.r, sqrt(epsU), h->nan_flag);
+            k_small2<<<kn, 1024, sg.bytes(), s>>>(small_g, h->small_stride, c.r, sqrt(epsU), h->nan_flag);
             const bool tc = gptb_is_tc(h);
             const int npr = (c.r + 15) & ~15;
             size_t sm3 = ((size_t)dmm_ld(UP_ROWS) * 3 * npr + (size_t)dmm_ld(2 * npr) * npr) * sizeof(double);
-            k_apply2<<<dim3(nb, c.D), UP_THREADS, sm3, h->stream>>>(h->U, h->G, h->small, h->small_stride, c.n, c.r,
-                                                                   h->nan_flag, tc ? (__half *)h->Uimg : nullptr, h->npad,
-                                                                   h->rpad, tc ? h->tc_state + 4 : nullptr);
+            __half *img = tc ? (__half *)h->Uimg + (size_t)k0 * h->npad * 2 * h->rpad : nullptr;
+            k_apply2<<<dim3(nb, kn), UP_THREADS, sm3, s>>>(h->U + koff, h->G + koff, small_g, h->small_stride, c.n, c.r,
+                                                          h->nan_flag, img, h->npad, h->rpad,
+                                                          tc ? h->tc_state + 4 : nullptr);
             h->launches += 2;
             if (tc) h->shadows_valid = true;   // k_apply2 refreshed the operand image
         } else {
-            k_small<<<c.D, 1024, sb, h->stream>>>(h->small, h->small_stride, c.r, sqrt(epsU), 1, h->nan_flag, sb ? 1 : 0);
+            k_small<<<kn, 1024, sb, s>>>(small_g, h->small_stride, c.r, sqrt(epsU), 1, h->nan_flag, sb ? 1 : 0);
             size_t sm3 = (2 * (size_t)UP_ROWS * c.r + 2 * (size_t)c.r * c.r + c.r) * sizeof(double);
-            k_apply<<<dim3(nb, c.D), UP_THREADS, sm3, h->stream>>>(h->U, h->G, h->small, h->small_stride, c.n, c.r,
-                                                                  h->nan_flag);
+            k_apply<<<dim3(nb, kn), UP_THREADS, sm3, s>>>(h->U + koff, h->G + koff, small_g, h->small_stride, c.n, c.r,
+                                                         h->nan_flag);
             int fb = (int)std::min<size_t>(((size_t)c.r * c.n + 255) / 256, 64);
-            k_finish<<<dim3(fb, c.D), 256, 0, h->stream>>>(h->U, h->G, h->small, h->small_stride, c.n, c.r, h->nan_flag);
+            k_finish<<<dim3(fb, kn), 256, 0, s>>>(h->U + koff, h->G + koff, small_g, h->small_stride, c.n, c.r, h->nan_flag);
             h->launches += 3;
         }
     }
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;
+}
+
+int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
+                       const double *noise_U, uint64_t step) {
+    return gptb_launch_update_range(h, epsw, epsU, flags, noise_w, noise_U, step, 0, h->cfg.D, true, h->stream);
 }
 
 // Standalone proj (mode 0) / geod (mode 1) on device buffers U, V (n x r col-major); scratch from `h`.

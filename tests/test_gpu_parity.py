@@ -307,6 +307,55 @@ def test_GPTregression_production_mode_and_nan_abort():
     assert not z[0].any() and not z[1].any()                               # :422-424
 
 
+@pytest.mark.parametrize("groups", [2, 3])
+def test_dimension_group_pipeline(groups, monkeypatch):
+    """The dimension-group pipeline of the step (api.cu: step_pipelined — the update of a group of dimensions runs on
+    a side stream under the next group's back-projection and the next step's forward pass) must not change the
+    chain: same Philox draws, same parameters as the one-stream step, in every driver of the step."""
+    P = make_problem(6, 700, 64, 8, Q=50, seed=21)
+    f = _feat(P)
+    epsw, epsU, m_ = 1e-6, 1e-9, 256
+    rng = np.random.default_rng(4)
+    idx = [rng.permutation(P["N"])[:200] for _ in range(4)]
+    Xb = [np.asfortranarray(P["X"][i]) for i in idx]
+    yb = [np.ascontiguousarray(P["y"][i]) for i in idx]
+
+    def drive(g):
+        monkeypatch.setenv("GPTB_PIPE_GROUPS", str(g))
+        out = {}
+        with _model(P, L.PREC_TC3) as m:                       # resident data, library-side loop
+            m.sgld_advance(P["signal_var"], m_, epsw, epsU, 7)
+            out["advance"] = m.get_params()
+        wouts = [np.zeros(P["Q"]) for _ in idx]
+        with _model(P, L.PREC_TC3, train=False) as m:          # host minibatches, submit / wait
+            m.sgld_step_host_submit(P["signal_var"], Xb[0], yb[0], P["N"], epsw, epsU, w_out=wouts[0])
+            for t in range(1, len(idx)):
+                m.sgld_step_host_submit(P["signal_var"], Xb[t], yb[t], P["N"], epsw, epsU, w_out=wouts[t])
+                m.sgld_step_host_wait()
+            m.sgld_step_host_wait()
+            out["host"] = m.get_params()
+            assert np.array_equal(wouts[-1], out["host"][0])
+        out["host_w"] = np.stack(wouts)
+        out["run"] = G.GPTregression(f, P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m_, epsw, epsU, 1, 2, 7,
+                                     precision=L.PREC_TC3)
+        z = G.GPTregression(f, P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m_, epsw, 1e300, 0, 1, 7,
+                            precision=L.PREC_TC3)
+        assert not z[0].any() and not z[1].any()               # NaN abort (:422-424) through the pipeline
+        return out
+
+    ref, got = drive(0), drive(groups)
+    tol = 2e-5   # of the accumulated update: the gradient sums use fp32 atomics, two runs agree to rounding only
+    for key in ("advance", "host"):
+        assert relerr(got[key][0] - P["w0"], ref[key][0] - P["w0"]) < tol, key
+        assert relerr(got[key][1] - P["U0"], ref[key][1] - P["U0"]) < tol, key
+    assert relerr(got["host_w"] - P["w0"], ref["host_w"] - P["w0"]) < tol
+    assert got["run"][0].shape == ref["run"][0].shape
+    assert relerr(got["run"][0], ref["run"][0]) < 1e-5 and relerr(got["run"][1], ref["run"][1]) < 1e-5
+    for k in range(P["D"]):
+        Uk = got["advance"][1][:, :, k]
+        assert np.abs(Uk.T @ Uk - np.eye(P["r"])).max() < 1e-10
+
+
 def test_philox_noise_statistics():
     """Production-mode noise: w_{t+1}-w_t with zero step size on the gradient is sqrt(epsw)*N(0,1)."""
     P = make_problem(2, 64, 8, 2, Q=4, seed=11)

@@ -39,6 +39,12 @@ def main():
             model.set_params(mdl["w0"], mdl["U0"])
             model.sgld_advance(B.SIGNAL_VAR, m, EPSW, EPSU, 5)
             model.synchronize()
+            import time
+            t0 = time.perf_counter()
+            model.sgld_advance(B.SIGNAL_VAR, m, EPSW, EPSU, a.steps)
+            model.synchronize()
+            print(pname, "unprofiled ms/step %.4f (pipelined when GPTB_PIPE_GROUPS >= 2, default 2)" %
+                  ((time.perf_counter() - t0) * 1e3 / a.steps), flush=True)
             model.set_profiling(True)
             model.phase_ms(reset=True)
             model.sgld_advance(B.SIGNAL_VAR, m, EPSW, EPSU, a.steps)
