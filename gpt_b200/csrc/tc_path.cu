@@ -188,40 +188,45 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
         uint32_t gen = 0;
         int u = u0, ch = g, cur_grp = -1, nch = 0, sa = g % NSTA;
         uint32_t pa = ((g / NSTA) & 1) ^ 1;
-        float x = 0.f, x_next = 0.f;
-        {   // x of the first unit; afterwards the next unit's x is fetched one unit ahead
-            const int grp = u0 / ntiles, tile = u0 - grp * ntiles, k = grp / p.P;
-            if (u0 < u1) x_next = p.XbF[(size_t)k * p.mpad + (size_t)tile * 128 + row];
-        }
-        bool fresh = true;
-        while (u < u1) {
-            if (fresh) {
-                fresh = false;
-                const int grp = u / ntiles, k = grp / p.P;
-                if (grp != cur_grp) {   // the (zt, b) table of this K part arrives with the U image
-                    cur_grp = grp;
-                    mbar_wait(&bars->u_full, gen & 1);
-                    ++gen;
-                    nch = min(p.NCHp, NCH - (grp - k * p.P) * p.NCHp);
-                }
-                x = x_next;
-                if (u + 1 < u1) {
-                    const int grp1 = (u + 1) / ntiles, tile1 = (u + 1) - grp1 * ntiles, k1 = grp1 / p.P;
-                    x_next = p.XbF[(size_t)k1 * p.mpad + (size_t)tile1 * 128 + row];
-                }
+        float x_next = 0.f;
+        // (grp, tile, k) of unit u and of unit u + 1, kept incrementally (the divisions cost ~100 issue slots per unit)
+        int grp_c = u0 / ntiles;
+        int grp_n = grp_c, tile_n = u0 - grp_c * ntiles, k_n = grp_c / p.P;
+        if (u0 < u1) x_next = p.XbF[(size_t)k_n * p.mpad + (size_t)tile_n * 128 + row];   // x of the first unit
+        auto advance_next = [&]() {
+            if (++tile_n == ntiles) {
+                tile_n = 0;
+                ++grp_n;
+                k_n = grp_n / p.P;
             }
-            if (ch >= nch) { ch -= nch; ++u; fresh = true; continue; }
-            mbar_wait(&bars->a_empty[sa], pa);
-            fence_after_sync();
-            const uint32_t st_addr = tmem + lane_addr + sa * SA_COLS;
-            gen_fwd_chunk<THREE>(sZb + (p.sincos ? ch * KC / 2 : ch * KC), x, p.sincos != 0, st_addr, half0);
-            wait_st();
-            fence_before_sync();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&bars->a_full[sa]);   // one arrival per warp: 32 lanes on one mbarrier serialise
-            ch += NGEN;
-            sa += NGEN;
-            if (sa >= NSTA) { sa -= NSTA; pa ^= 1; }
+        };
+        advance_next();   // (grp_n, tile_n, k_n) now describe unit u0 + 1
+        for (; u < u1; ++u) {
+            const int grp = grp_c;
+            if (grp != cur_grp) {   // the (zt, b) table of this K part arrives with the U image
+                cur_grp = grp;
+                mbar_wait(&bars->u_full, gen & 1);
+                ++gen;
+                const int k = grp / p.P;
+                nch = min(p.NCHp, NCH - (grp - k * p.P) * p.NCHp);
+            }
+            const float x = x_next;
+            if (u + 1 < u1) x_next = p.XbF[(size_t)k_n * p.mpad + (size_t)tile_n * 128 + row];   // one unit ahead
+            grp_c = grp_n;
+            advance_next();
+            for (; ch < nch; ch += NGEN) {
+                mbar_wait(&bars->a_empty[sa], pa);
+                fence_after_sync();
+                const uint32_t st_addr = tmem + lane_addr + sa * SA_COLS;
+                gen_fwd_chunk<THREE>(sZb + (p.sincos ? ch * KC / 2 : ch * KC), x, p.sincos != 0, st_addr, half0);
+                wait_st();
+                fence_before_sync();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bars->a_full[sa]);   // one arrival per warp: 32 lanes on one mbarrier serialise
+                sa += NGEN;
+                if (sa >= NSTA) { sa -= NSTA; pa ^= 1; }
+            }
+            ch -= nch;
         }
     } else if (warp == 4 || (NI == 2 && warp == 6)) {
         // ---------------------------------------------------------------- MMA issuers (whole warp runs the loop)
@@ -397,36 +402,38 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
         const int jl = q * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
         // position of A step `as`: item lit (-> grp, ch) and block jbl
-        int jbl = g, ch = ch0, grp = grp0;
-        uint32_t lit = 0;
-        while (jbl >= JG) { jbl -= JG; ++lit; if (++ch == NCH) { ch = 0; ++grp; } }
+        int jbl = g, ch = ch0;
+        int kk = grp0 / NJG, jg = grp0 - kk * NJG;   // (k, feature-block group) of the current item, kept incrementally:
+        uint32_t lit = 0;                            // two integer divisions per A step were 5% of the kernel's instructions
+        auto next_item = [&]() {
+            ++lit;
+            if (++ch == NCH) {
+                ch = 0;
+                if (++jg == NJG) { jg = 0; ++kk; }
+            }
+        };
+        while (jbl >= JG) { jbl -= JG; next_item(); }
         int sa = g % NSTA;
         uint32_t pa = ((g / NSTA) & 1) ^ 1;
-        // (zt, b) of this lane's feature in A step (grp, jbl).  (Fetching them one step ahead was measured 20%
-        // slower for the whole kernel, A/B in the same run; the load latency here overlaps the barrier waits.)
-        auto load_zb = [&](int grp_, int jbl_, float &zt, float &bb) {
-            const int k = grp_ / NJG, jg = grp_ - k * NJG;
-            int j = (jg * JG + jbl_) * 128 + jl;
+        // (zt, b) of this lane's feature in A step (k, jg, jbl); the load latency overlaps the barrier waits
+        auto load_zb = [&](int k, int jg_, int jbl_, float &zt, float &bb) {
+            int j = (jg_ * JG + jbl_) * 128 + jl;
             if (j >= p.npad) j = p.npad - 1;    // padding block of a ragged last group: computed, never stored
+            const size_t base = (size_t)k * p.npad;
             if (!p.sincos) {
-                zt = p.ZtF[(size_t)k * p.npad + j];
-                bb = p.bF[(size_t)k * p.npad + j];
+                zt = p.ZtF[base + j];
+                bb = p.bF[base + j];
             } else {  // rows 2p / 2p+1 are sin / cos of x*Zt[p]:  cos(a) = sin(a + pi/2)
-                zt = p.ZtF[(size_t)k * p.npad + (j >> 1)];
+                zt = p.ZtF[base + (j >> 1)];
                 bb = (j & 1) ? 1.5707963267948966f : 0.f;
             }
         };
-        for (uint32_t as = g; as < n_as; as += NGEN) {
-            float zt, bb;
-            load_zb(grp, jbl, zt, bb);
+        // one A step: 64 rows x this lane's feature -> stage sa (hi | lo words), then hand the stage to the issuers
+        auto a_step = [&](float zt, float bb, int sb, uint32_t lit_cur, bool wait_b) {
             const float2 zt2 = make_float2(zt, zt), bb2 = make_float2(bb, bb);
-            const int sb = lit % NSTB;
-            const uint32_t lit_cur = lit;
-            jbl += NGEN;
-            while (jbl >= JG) { jbl -= JG; ++lit; if (++ch == NCH) { ch = 0; ++grp; } }
             mbar_wait(&bars->a_empty[sa], pa);
             fence_after_sync();
-            mbar_wait(&bars->b_full[sb], (lit_cur / NSTB) & 1);
+            if (wait_b) mbar_wait(&bars->b_full[sb], (lit_cur / NSTB) & 1);
             const uint32_t st_addr = tmem + lane_addr + sa * SA_COLS;
             const float4 *xr = reinterpret_cast<const float4 *>(sB + sb * B_STAGE_BYTES + B_IMG_BYTES);
 #pragma unroll
@@ -455,6 +462,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bwd_tc_kernel(const BwdParams p
             if (lane == 0) mbar_arrive(&bars->a_full[sa]);   // one arrival per warp: 32 lanes on one mbarrier serialise
             sa += NGEN;
             while (sa >= NSTA) { sa -= NSTA; pa ^= 1; }
+        };
+        // (Keeping the (zt, b) of the group's blocks in registers across items instead of re-reading them here was
+        // measured 20% SLOWER for the whole kernel, twice, A/B in the same run — as was fetching them one step ahead.)
+        for (uint32_t as = g; as < n_as; as += NGEN) {
+            float zt, bb;
+            load_zb(kk, jg, jbl, zt, bb);
+            const int sb = lit % NSTB;
+            const uint32_t lit_cur = lit;
+            jbl += NGEN;
+            while (jbl >= JG) { jbl -= JG; next_item(); }
+            a_step(zt, bb, sb, lit_cur, true);
         }
     } else if (warp == 4 || warp == 6) {
         // ---------------------------------------------------------------- MMA issuers (whole warp runs the loop)
@@ -836,7 +854,10 @@ int gptb_launch_bwd_tc_range(gptb_handle *h, const float *XbF, const void *Eimg,
     p.mpad = mpad;
     p.sincos = c.feature_kind == GPTB_FEAT_SINCOS;
     const int JB = h->npad / 128;
-    const int jg_max = 256 / h->rpad;                 // accumulators take at most half of TMEM
+#ifndef GPTB_K3_ACC_COLS
+#define GPTB_K3_ACC_COLS 256
+#endif
+    const int jg_max = GPTB_K3_ACC_COLS / h->rpad;    // accumulators take at most half of TMEM
     p.NJG = (JB + jg_max - 1) / jg_max;
     p.JG = (JB + p.NJG - 1) / p.NJG;
     p.nsta = nsta_for(p.JG * h->rpad);
