@@ -313,7 +313,7 @@ def main():
             pmodel.pred_samples(ws[:, :8], Us[:, :, :, :8], Xt[:4096])      # warm-up (same sample-group geometry)
             barrier()
             dts = []
-            for _ in range(2):                  # the first full-size call also pays one-time allocations
+            for _ in range(3):                  # the first full-size call also pays one-time allocations
                 t0 = time.perf_counter()
                 mean = pmodel.pred_samples(ws, Us, Xt)
                 barrier()
