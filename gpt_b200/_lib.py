@@ -62,6 +62,17 @@ PROTOTYPES = {
     "gptb_comm_unique_id": (C.c_int, [C.c_void_p]),
     "gptb_comm_init": (C.c_int, [H, C.c_int32, C.c_int32, C.c_void_p]),
     "gptb_comm_destroy": (C.c_int, [H]),
+    # full-theta ("no tensor") RFF model
+    "gptb_nt_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_uint64, C.POINTER(H)]),
+    "gptb_nt_destroy": (C.c_int, [H]),
+    "gptb_nt_last_error": (C.c_char_p, [H]),
+    "gptb_nt_set_features": (C.c_int, [H, c_double_p, c_double_p, c_double_p, C.c_int32, C.c_double]),
+    "gptb_nt_features": (C.c_int, [H, c_double_p, C.c_int64, c_double_p]),
+    "gptb_nt_set_train": (C.c_int, [H, c_double_p, c_double_p, C.c_int64]),
+    "gptb_nt_pred": (C.c_int, [H, c_double_p, c_double_p, C.c_int64, c_double_p]),
+    "gptb_nt_run": (C.c_int, [H, C.c_double, C.c_double, C.c_int64, C.c_double, C.c_double, C.c_int32, C.c_int32,
+                              C.c_uint64, c_double_p, c_int64_p, c_double_p, c_double_p]),
+    "gptb_nt_last_run_stats": (C.c_int, [H, c_double_p, c_int64_p, c_int64_p]),
     "gptb_set_profiling": (C.c_int, [H, C.c_int32]),
     "gptb_get_phase_ms": (C.c_int, [H, c_float_p, c_int64_p, C.c_int32]),
 }

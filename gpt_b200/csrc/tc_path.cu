@@ -46,6 +46,13 @@ constexpr int NGEN = 4 / HSPLIT;   // generator groups (4*HSPLIT warps each); ch
                               // Fewer, wider groups keep fewer A stages "in generation" and leave more of the ring
                               // as slack between the generators and the MMA issuers.
 constexpr int TC_THREADS = 256 + 512;
+// K1 may run more generator groups than K3: the generator warps are bound one by one (dependent chains, barrier round
+// trips), not by the SM sub-partition, and K1 has the A stages for a fifth group (K3's TMEM is half accumulators).
+#ifndef GPTB_NGEN_FWD
+#define GPTB_NGEN_FWD 4
+#endif
+constexpr int NGEN_F = GPTB_NGEN_FWD / HSPLIT;
+constexpr int TC_THREADS_F = 256 + 128 * GPTB_NGEN_FWD;
 constexpr int KC = 64;        // K elements per chunk (4 MMA K-steps of 16)
 constexpr int SA_COLS = 64;   // TMEM columns of one A stage (32 hi + 32 lo, two fp16 per column)
 constexpr int NSTA_MAX = 8;
@@ -145,7 +152,7 @@ __device__ __forceinline__ void gen_fwd_chunk(const float2 *zb64, float x, bool 
 // issuer w takes the chunks ch = w (mod 2) of every unit and accumulates into its own columns, the epilogue adds
 // the two partial tiles.
 template <int RPAD, bool THREE>
-__global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p) {
+__global__ void __launch_bounds__(TC_THREADS_F, 1) fwd_tc_kernel(const FwdParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     constexpr int NI = RPAD <= 64 ? 2 : 1;
     constexpr int NSTA = nsta_for(2 * NI * RPAD);
@@ -214,7 +221,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
             if (u + 1 < u1) x_next = p.XbF[(size_t)k_n * p.mpad + (size_t)tile_n * 128 + row];   // one unit ahead
             grp_c = grp_n;
             advance_next();
-            for (; ch < nch; ch += NGEN) {
+            for (; ch < nch; ch += NGEN_F) {
                 mbar_wait(&bars->a_empty[sa], pa);
                 fence_after_sync();
                 const uint32_t st_addr = tmem + lane_addr + sa * SA_COLS;
@@ -223,7 +230,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) fwd_tc_kernel(const FwdParams p
                 fence_before_sync();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bars->a_full[sa]);   // one arrival per warp: 32 lanes on one mbarrier serialise
-                sa += NGEN;
+                sa += NGEN_F;
                 if (sa >= NSTA) { sa -= NSTA; pa ^= 1; }
             }
             ch -= nch;
@@ -690,11 +697,11 @@ static int launch_fwd_r(gptb_handle *h, const FwdParams &p, int grid, size_t sme
     if (h->cfg.precision == GPTB_PREC_TC3) {
         auto k = fwd_tc_kernel<RPAD, true>;
         GPTB_CUDA_OK(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k<<<grid, TC_THREADS, smem, h->stream>>>(p);
+        k<<<grid, TC_THREADS_F, smem, h->stream>>>(p);
     } else {
         auto k = fwd_tc_kernel<RPAD, false>;
         GPTB_CUDA_OK(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k<<<grid, TC_THREADS, smem, h->stream>>>(p);
+        k<<<grid, TC_THREADS_F, smem, h->stream>>>(p);
     }
     return GPTB_OK;
 }

@@ -436,3 +436,130 @@ def geod(U, mom, t):
         return out
     _check(st, None)
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# Full-theta ("no tensor") RFF model — GPT_SGLD.jl:109-120, :809-847 (gptb_nt_* in include/gptb200.h)
+# ------------------------------------------------------------------------------------------------
+class NTFeatures:
+    """Lazy result of `featureNotensor`: its inputs, not the n x N matrix.  np.asarray(f) materialises it."""
+
+    def __init__(self, X, length_scale, sigma_RBF, Z, b):
+        self.X = _f64(np.atleast_2d(X))
+        self.length_scale = np.atleast_1d(np.asarray(length_scale, dtype=np.float64))
+        self.sigma_RBF = float(sigma_RBF)
+        self.Z = _f64(Z)
+        self.b = np.ascontiguousarray(np.ravel(b), dtype=np.float64)
+        N, D = self.X.shape
+        if self.Z.ndim != 2 or self.Z.shape[1] != D or self.b.size != self.Z.shape[0]:
+            raise ValueError("Z must be n x D and b of length n")
+        if self.length_scale.size not in (1, D):
+            raise ValueError("dimensions of X and length_scale do not match")
+
+    @property
+    def shape(self):
+        return (self.Z.shape[0], self.X.shape[0])   # size(phi) = (n, N)
+
+    def with_X(self, X) -> "NTFeatures":
+        return NTFeatures(X, self.length_scale, self.sigma_RBF, self.Z, self.b)
+
+    def __array__(self, dtype=None, copy=None):
+        with NTModel(self) as mdl:
+            a = mdl.features(self.X)
+        return a if dtype is None else a.astype(dtype)
+
+
+class NTModel:
+    """Handle of the full-theta model (gptb_nt_handle)."""
+
+    def __init__(self, f: NTFeatures, precision: Optional[int] = None, device: Optional[int] = None, seed: int = 0):
+        self.lib = L.load()
+        self.n, self.D = f.Z.shape
+        self.h = L.H()
+        prec = L.PREC_TC3 if precision is None else int(precision)
+        st = self.lib.gptb_nt_create(self.D, self.n, prec, _default_device if device is None else int(device), int(seed),
+                                     C.byref(self.h))
+        _check(st, None)
+        ls = np.ascontiguousarray(f.length_scale)
+        self._check(self.lib.gptb_nt_set_features(self.h, _dp(f.Z), _dp(f.b), _dp(ls), int(ls.size), f.sigma_RBF))
+
+    def _check(self, st):
+        if st == L.OK:
+            return
+        msg = self.lib.gptb_nt_last_error(self.h)
+        msg = msg.decode() if msg else ""
+        raise (GeodesicNaN if st == L.GEODESIC_NAN else GptbError)(st, msg)
+
+    def close(self):
+        if self.h:
+            self.lib.gptb_nt_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def features(self, X):
+        X = _f64(np.atleast_2d(X))
+        out = np.empty((self.n, X.shape[0]), order="F")
+        self._check(self.lib.gptb_nt_features(self.h, _dp(X), X.shape[0], _dp(out)))
+        return out
+
+    def set_train(self, X, y):
+        X = _f64(np.atleast_2d(X)); y = np.ascontiguousarray(np.ravel(y), dtype=np.float64)
+        if y.size != X.shape[0]:
+            raise ValueError("X and y disagree on N")
+        self._check(self.lib.gptb_nt_set_train(self.h, _dp(X), _dp(y), X.shape[0]))
+        self.N = X.shape[0]
+
+    def pred(self, theta, Xtest):
+        X = _f64(np.atleast_2d(Xtest)); th = np.ascontiguousarray(np.ravel(theta), dtype=np.float64)
+        out = np.empty(X.shape[0])
+        self._check(self.lib.gptb_nt_pred(self.h, _dp(th), _dp(X), X.shape[0], _dp(out)))
+        return out
+
+    def run(self, signal_var, sigma_theta, m, eps_theta, decay_rate, burnin, maxepoch, param_seed, theta0=None,
+            perms=None, noise=None):
+        T = (int(maxepoch) + int(burnin)) * (-(-self.N // int(m)))
+        store = np.zeros((self.n, T), order="F")
+        th0 = None if theta0 is None else np.ascontiguousarray(np.ravel(theta0), dtype=np.float64)
+        pm = None if perms is None else np.ascontiguousarray(perms, dtype=np.int64)
+        nz = None if noise is None else np.ascontiguousarray(noise, dtype=np.float64)     # [T, n] C order = n fastest
+        st = self.lib.gptb_nt_run(self.h, float(signal_var), float(sigma_theta), int(m), float(eps_theta), float(decay_rate),
+                                  int(burnin), int(maxepoch), int(param_seed), _dp(th0),
+                                  pm.ctypes.data_as(L.c_int64_p) if pm is not None else None, _dp(nz), _dp(store))
+        if st == L.GEODESIC_NAN:
+            print("Get NaN in theta. Try smaller epsilon")        # GPT_SGLD.jl:840
+            return np.zeros(self.n)                               # :841
+        self._check(st)
+        return store
+
+    def last_run_stats(self):
+        ms, ln, stp = C.c_double(), C.c_int64(), C.c_int64()
+        self._check(self.lib.gptb_nt_last_run_stats(self.h, C.byref(ms), C.byref(ln), C.byref(stp)))
+        return ms.value, ln.value, stp.value
+
+
+def featureNotensor(X, length_scale, sigma_RBF, Z, b) -> NTFeatures:
+    """GPT_SGLD.jl:109-120.  Use Z=randn(n,D) and b=2*pi*rand(n) (:108)."""
+    return NTFeatures(X, length_scale, sigma_RBF, Z, b)
+
+
+def GPNT_SGLD(phi: NTFeatures, y, signal_var, sigma_theta, m, eps_theta, decay_rate, burnin, maxepoch, param_seed, *,
+              precision: Optional[int] = None, theta0=None, perms=None, noise=None):
+    """GPT_SGLD.jl:809-847.  Returns theta_store[n, (maxepoch+burnin)*ceil(N/m)] (every step, burn-in included), or
+    zeros(n) after printing the reference's warning if theta became NaN.  `phi` is the lazy handle of featureNotensor.
+    Keyword-only extras (not in the reference): precision; theta0 / perms / noise inject the random draws."""
+    if not isinstance(phi, NTFeatures):
+        raise TypeError("GPNT_SGLD takes the handle returned by featureNotensor (the n x N matrix is never formed)")
+    with NTModel(phi, precision=precision, seed=int(param_seed)) as mdl:
+        mdl.set_train(phi.X, y)
+        return mdl.run(signal_var, sigma_theta, m, eps_theta, decay_rate, burnin, maxepoch, param_seed, theta0, perms, noise)
+
+
+def pred_notensor(theta, phitest: NTFeatures, precision: Optional[int] = None):
+    """phitest' * theta (PowerPlantNoTensorExperiment.jl / kin40kNoTensorExperiment.jl test-time prediction)."""
+    with NTModel(phitest, precision=precision) as mdl:
+        return mdl.pred(theta, phitest.X)

@@ -184,6 +184,39 @@ int gptb_comm_unique_id(void *id_out_128);
 int gptb_comm_init(gptb_handle *h, int32_t nranks, int32_t rank, const void *id_128);
 int gptb_comm_destroy(gptb_handle *h);
 
+/* ---- full-theta ("no tensor") RFF model: the comparator of the tensor model ----------------------
+ * featureNotensor GPT_SGLD.jl:109-120 and GPNT_SGLD GPT_SGLD.jl:809-847 (PowerPlantNoTensorExperiment.jl,
+ * kin40kNoTensorExperiment.jl; BASELINE config 3 "tensor vs full-theta RFF SGLD").
+ *   phi[j,i] = sqrt(2/n)*sigma_RBF*cos(sum_d X[i,d]*Z[j,d]/length_scale[d] + b[j])            (n x N, never stored)
+ *   grad     = -theta/sigma_theta^2 + (N/bs)*phi_b*(y_b - phi_b'*theta)/signal_var,  eps_t = eps_theta*t^(-decay_rate)
+ *   theta   += eps_t*grad/2 + sqrt(eps_t)*randn(n)
+ * The features are generated on the fly in both passes of a step (forward phi_b'*theta, back-projection phi_b*e).
+ * precision: GPTB_PREC_FP64 (<=1e-10 vs the reference arithmetic) or GPTB_PREC_TC3 = FP32 arithmetic with
+ * MUFU.COS (<=1e-4; no tensor cores: the contraction dimension of the feature argument is D <= 16).
+ * Arrays as Julia stores them: X[N,D], Z[n,D] column-major Float64; b[n]; theta_store[n,T]. */
+typedef struct gptb_nt_handle gptb_nt_handle;
+int gptb_nt_create(int32_t D, int32_t n, int32_t precision, int32_t device, uint64_t seed, gptb_nt_handle **out);
+int gptb_nt_destroy(gptb_nt_handle *h);
+const char *gptb_nt_last_error(const gptb_nt_handle *h);
+/* featureNotensor's parameters (:109): length_scale scalar (ls_len = 1) or per dimension (ls_len = D). */
+int gptb_nt_set_features(gptb_nt_handle *h, const double *Z, const double *b, const double *length_scale, int32_t ls_len,
+                         double sigma_RBF);
+/* featureNotensor materialised (:109-120): phi_out[n,N]. */
+int gptb_nt_features(gptb_nt_handle *h, const double *X, int64_t N, double *phi_out);
+int gptb_nt_set_train(gptb_nt_handle *h, const double *X, const double *y, int64_t N);
+/* fhat[i] = phi(Xtest)[:,i]' * theta  (PowerPlantNoTensorExperiment.jl: phitest'*theta_store[:,t]). */
+int gptb_nt_pred(gptb_nt_handle *h, const double *theta, const double *Xtest, int64_t Nt, double *fhat_out);
+/* GPNT_SGLD (:809-847).  theta0 NULL = sigma_theta*randn(n) from Philox(param_seed) (:815-816); perms NULL = a fresh
+ * permutation per epoch (:824), else int64[(maxepoch+burnin)*N] 0-based, applied cumulatively; noise NULL = Philox,
+ * else double[T*n] standard normals.  theta_store_out[n,T], T = (maxepoch+burnin)*ceil(N/m): every step is stored,
+ * burn-in included (:818,:838).  NaN in theta (:839-842) -> returns GPTB_GEODESIC_NAN ("Get NaN in theta. Try
+ * smaller epsilon") with theta_store_out zero-filled. */
+int gptb_nt_run(gptb_nt_handle *h, double signal_var, double sigma_theta, int64_t m, double eps_theta, double decay_rate,
+                int32_t burnin, int32_t maxepoch, uint64_t param_seed, const double *theta0, const int64_t *perms,
+                const double *noise, double *theta_store_out);
+/* Device time (ms) of the steps of the last gptb_nt_run and the number of kernel launches it issued. */
+int gptb_nt_last_run_stats(gptb_nt_handle *h, double *ms_out, int64_t *launches_out, int64_t *steps_out);
+
 /* ---- introspection (bench / tests) ------------------------------------------------------------ */
 /* Per-phase device time (ms) accumulated since the last reset, measured with CUDA events on the
  * handle's stream when profiling is on.  Phases: see GPTB_PHASE_*.  launches_out (optional) receives

@@ -18,7 +18,8 @@
 # build container (no julia binary there); the Python mirror gpt_b200/gpt_sgld.py is what the tests drive.
 module GPT_SGLD
 
-export datawhitening, feature, feature2, samplenz, pred, GPTregression, proj, geod, RFFFeatures
+export datawhitening, feature, feature2, samplenz, pred, GPTregression, proj, geod, RFFFeatures,
+       featureNotensor, GPNT_SGLD, NTFeatures
 
 using Random, Statistics
 
@@ -189,6 +190,59 @@ function geod(U::Array, mom::Array, t::Real)
     end
     check(st)
     out
+end
+
+# ---- full-theta ("no tensor") model: GPT_SGLD.jl:109-120, :809-847 ---------------------------------------------
+struct NTFeatures            # lazy result of featureNotensor: its inputs, not the n x N matrix
+    X::Matrix{Float64}; length_scale::Vector{Float64}; sigma_RBF::Float64; Z::Matrix{Float64}; b::Vector{Float64}
+end
+Base.size(f::NTFeatures) = (size(f.Z, 1), size(f.X, 1))
+
+# GPT_SGLD.jl:109  featureNotensor(X,length_scale,sigma_RBF,Z,b), Z=randn(n,D), b=2*pi*rand(n)
+featureNotensor(X::Array, length_scale, sigma_RBF::Real, Z::Array, b::Array) =
+    NTFeatures(Matrix{Float64}(X), Float64[length_scale...], Float64(sigma_RBF), Matrix{Float64}(Z), vec(Float64.(b)))
+
+function nt_create(f::NTFeatures; precision = PREC_TC3, device = -1, seed = 0)
+    n, D = size(f.Z); h = Ref{Ptr{Cvoid}}(C_NULL)
+    check(ccall((:gptb_nt_create, LIB), Cint, (Int32, Int32, Int32, Int32, UInt64, Ref{Ptr{Cvoid}}), D, n, precision, device, seed, h))
+    st = ccall((:gptb_nt_set_features, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Int32, Float64),
+               h[], f.Z, f.b, f.length_scale, length(f.length_scale), f.sigma_RBF)
+    st == 0 || error(unsafe_string(ccall((:gptb_nt_last_error, LIB), Cstring, (Ptr{Cvoid},), h[])))
+    return h[]
+end
+
+function Base.Array(f::NTFeatures)
+    h = nt_create(f); n, N = size(f); phi = Matrix{Float64}(undef, n, N)
+    try
+        st = ccall((:gptb_nt_features, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Int64, Ptr{Float64}), h, f.X, N, phi)
+        st == 0 || error(unsafe_string(ccall((:gptb_nt_last_error, LIB), Cstring, (Ptr{Cvoid},), h)))
+        return phi
+    finally
+        ccall((:gptb_nt_destroy, LIB), Cint, (Ptr{Cvoid},), h)
+    end
+end
+
+# GPT_SGLD.jl:809  GPNT_SGLD(phi,y,signal_var,sigma_theta,m,eps_theta,decay_rate,burnin,maxepoch,param_seed)
+function GPNT_SGLD(phi::NTFeatures, y::Array, signal_var::Real, sigma_theta::Real, m::Integer, eps_theta::Real,
+                   decay_rate::Real, burnin::Integer, maxepoch::Integer, param_seed::Integer; precision = PREC_TC3)
+    n, N = size(phi); T = (maxepoch + burnin) * cld(N, m)
+    h = nt_create(phi; precision = precision, seed = param_seed)
+    try
+        st = ccall((:gptb_nt_set_train, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int64), h, phi.X, vec(Float64.(y)), N)
+        st == 0 || error(unsafe_string(ccall((:gptb_nt_last_error, LIB), Cstring, (Ptr{Cvoid},), h)))
+        store = zeros(n, T)
+        st = ccall((:gptb_nt_run, LIB), Cint,
+                   (Ptr{Cvoid}, Float64, Float64, Int64, Float64, Float64, Int32, Int32, UInt64, Ptr{Float64}, Ptr{Int64}, Ptr{Float64}, Ptr{Float64}),
+                   h, signal_var, sigma_theta, m, eps_theta, decay_rate, burnin, maxepoch, param_seed, C_NULL, C_NULL, C_NULL, store)
+        if st == GEODESIC_NAN
+            println("Get NaN in theta. Try smaller epsilon")      # GPT_SGLD.jl:840
+            return zeros(n)                                       # :841
+        end
+        st == 0 || error(unsafe_string(ccall((:gptb_nt_last_error, LIB), Cstring, (Ptr{Cvoid},), h)))
+        return store
+    finally
+        ccall((:gptb_nt_destroy, LIB), Cint, (Ptr{Cvoid},), h)
+    end
 end
 
 end # module

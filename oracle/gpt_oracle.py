@@ -297,3 +297,57 @@ def posterior_mean_pred(w_store, U_store, I, phitest, cols):
     for c in cols:
         acc += pred(w_store[:, c], U_store[:, :, :, c], I, phitest)
     return acc / len(cols)
+
+
+# ------------------------------------------------------------------------------------------------
+# Full-theta ("no tensor") RFF model — the comparator of the tensor model.
+# Shapes: Z[n,D], b[n], phi[n,N], theta[n].  Pinning: **parity unpinned** beyond the formulas — the reference
+# holds no fixture or known-answer test for these two functions (only plots); the restatement is checked against
+# finite differences of its own log posterior (tests/test_oracle_golden.py).
+# ------------------------------------------------------------------------------------------------
+def featureNotensor(X, length_scale, sigma_RBF, Z, b):
+    """GPT_SGLD.jl:109-120: phi[j,i] = sqrt(2/n)*sigma_RBF*cos(sum_d X[i,d]*Z[j,d]/length_scale[d] + b[j])."""
+    X = np.asarray(X, dtype=np.float64)
+    Z = np.asarray(Z, dtype=np.float64)
+    n = Z.shape[0]
+    Zt = Z / np.asarray(length_scale, dtype=np.float64)          # scale(Z, 1./length_scale), :113
+    return np.sqrt(2.0 / n) * sigma_RBF * np.cos(Zt @ X.T + np.asarray(b, dtype=np.float64)[:, None])
+
+
+def nt_grad(phi_batch, y_batch, theta, N_total, signal_var, sigma_theta):
+    """GPT_SGLD.jl:833: -theta/sigma_theta^2 + (N/batch_size)*phi_batch*(y_batch - phi_batch'*theta)/signal_var."""
+    bs = y_batch.size
+    return -theta / sigma_theta ** 2 + (N_total / bs) * (phi_batch @ (y_batch - phi_batch.T @ theta)) / signal_var
+
+
+def nt_logpost(phi, y, theta, signal_var, sigma_theta):
+    """Log posterior whose gradient nt_grad is at full batch (up to constants)."""
+    res = y - phi.T @ theta
+    return -0.5 * res @ res / signal_var - 0.5 * theta @ theta / sigma_theta ** 2
+
+
+def GPNT_SGLD(phi, y, signal_var, sigma_theta, m, eps_theta, decay_rate, burnin, maxepoch, theta0, perms, noise):
+    """GPT_SGLD.jl:809-847 with the random draws injected: theta0[n] (= sigma_theta*randn(n), :816), one permutation
+    per epoch applied cumulatively (:824-825), noise[T, n] standard normals (:835).  Every step is stored, burn-in
+    included (:818, :838); returns theta_store[n, (maxepoch+burnin)*numbatches], or zeros(n) after a NaN (:839-842)."""
+    phi = np.array(phi, dtype=np.float64)
+    y = np.array(y, dtype=np.float64).ravel()
+    n, N = phi.shape
+    numbatches = int(np.ceil(N / m))
+    theta = np.array(theta0, dtype=np.float64).copy()
+    store = np.zeros((n, (maxepoch + burnin) * numbatches))
+    t = 0
+    for epoch in range(maxepoch + burnin):
+        perm = np.asarray(perms[epoch])
+        phi = phi[:, perm]
+        y = y[perm]
+        for batch in range(numbatches):
+            t += 1
+            lo, hi = m * batch, min(m * (batch + 1), N)
+            epsilon = eps_theta * float(t) ** (-decay_rate)                       # :832
+            g = nt_grad(phi[:, lo:hi], y[lo:hi], theta, N, signal_var, sigma_theta)
+            theta = theta + epsilon * g / 2 + np.sqrt(epsilon) * np.asarray(noise[t - 1])
+            store[:, t - 1] = theta
+            if np.isnan(theta).any():
+                return np.zeros(n)
+    return store

@@ -392,3 +392,62 @@ def test_full_size_properties_c2(prec):
         _, U = m.get_params()
         for k in range(8):
             assert np.abs(U[:, :, k].T @ U[:, :, k] - np.eye(20)).max() < 1e-9
+
+
+# ------------------------------------------------------------------ full-theta comparator (GPT_SGLD.jl:109-120, :809-847)
+def _nt_problem(seed=31, N=700, D=5, n=300):
+    rng = np.random.default_rng(seed)
+    X = np.asfortranarray(rng.standard_normal((N, D)))
+    Z = np.asfortranarray(rng.standard_normal((n, D)))
+    b = 2 * np.pi * rng.random(n)
+    ls = np.maximum(1.0 + 0.2 * rng.standard_normal(D), 0.3)
+    th_true = rng.standard_normal(n)
+    phi = o.featureNotensor(X, ls, 1.3, Z, b)
+    y = phi.T @ th_true + 0.05 * rng.standard_normal(N)
+    return dict(X=X, Z=Z, b=b, ls=ls, sig=1.3, phi=phi, y=y, rng=rng, N=N, D=D, n=n)
+
+
+@pytest.mark.parametrize("prec", PRECS, ids=["fp64", "fp32"])
+def test_fulltheta_features_pred_and_chain(prec):
+    P = _nt_problem()
+    tol = 1e-10 if prec == L.PREC_FP64 else 1e-4
+    f = G.featureNotensor(P["X"], P["ls"], P["sig"], P["Z"], P["b"])
+    assert f.shape == (P["n"], P["N"])
+    assert relerr(np.asarray(f), P["phi"]) < 1e-12                      # materialisation is FP64 in both modes
+    th = P["rng"].standard_normal(P["n"])
+    assert relerr(G.pred_notensor(th, f, precision=prec), P["phi"].T @ th) < tol
+    burnin, maxepoch, m = 1, 2, 256                                     # 3 batches per epoch, the last one short
+    nb = -(-P["N"] // m)
+    perms = np.stack([P["rng"].permutation(P["N"]) for _ in range(burnin + maxepoch)])
+    noise = P["rng"].standard_normal(((burnin + maxepoch) * nb, P["n"]))
+    th0 = 0.5 * P["rng"].standard_normal(P["n"])
+    want = o.GPNT_SGLD(P["phi"], P["y"], 0.01, 1.0, m, 2e-6, 0.3, burnin, maxepoch, th0, perms, noise)
+    got = G.GPNT_SGLD(f, P["y"], 0.01, 1.0, m, 2e-6, 0.3, burnin, maxepoch, 7, precision=prec, theta0=th0, perms=perms,
+                      noise=noise)
+    assert got.shape == want.shape
+    assert relerr(got - th0[:, None], want - th0[:, None]) < tol
+    # scalar length scale and a single-row batch
+    f1 = G.featureNotensor(P["X"][:129], 0.8, 1.0, P["Z"], P["b"])
+    want1 = o.GPNT_SGLD(o.featureNotensor(P["X"][:129], 0.8, 1.0, P["Z"], P["b"]), P["y"][:129], 0.01, 2.0, 128, 1e-6, 0.0, 0, 1,
+                        th0, [np.arange(129)], noise[:2])
+    got1 = G.GPNT_SGLD(f1, P["y"][:129], 0.01, 2.0, 128, 1e-6, 0.0, 0, 1, 7, precision=prec, theta0=th0,
+                       perms=np.arange(129)[None, :], noise=noise[:2])
+    assert relerr(got1 - th0[:, None], want1 - th0[:, None]) < tol
+
+
+def test_fulltheta_production_mode_and_nan_abort():
+    P = _nt_problem(seed=32, N=500, D=4, n=130)
+    f = G.featureNotensor(P["X"], P["ls"], P["sig"], P["Z"], P["b"])
+    a = G.GPNT_SGLD(f, P["y"], 0.01, 1.0, 200, 1e-6, 0.2, 1, 2, 11, precision=L.PREC_FP64)
+    b = G.GPNT_SGLD(f, P["y"], 0.01, 1.0, 200, 1e-6, 0.2, 1, 2, 11, precision=L.PREC_FP64)
+    assert a.shape == (P["n"], 9) and np.isfinite(a).all()
+    assert relerr(a, b) < 1e-12                                            # counter-based RNG: reproducible
+    c = G.GPNT_SGLD(f, P["y"], 0.01, 1.0, 200, 1e-6, 0.2, 1, 2, 12, precision=L.PREC_FP64)
+    assert relerr(c, a) > 1e-3
+    # the chain moves towards the data: residual of the last sample well below that of the first
+    r0 = np.linalg.norm(P["y"] - P["phi"].T @ a[:, 0]); r1 = np.linalg.norm(P["y"] - P["phi"].T @ a[:, -1])
+    assert r1 < r0
+    z = G.GPNT_SGLD(f, P["y"], 0.01, 1.0, 200, 1e300, 0.0, 0, 1, 11, precision=L.PREC_FP64)
+    assert z.shape == (P["n"],) and not z.any()                            # :839-842
+    with pytest.raises(ValueError):
+        G.featureNotensor(P["X"], np.ones(3), 1.0, P["Z"], P["b"])

@@ -169,3 +169,32 @@ def test_sgld_step_c_vs_numpy_and_store_layout():
     ws, Us = o.GPTregression(phi, P["y"], 0.01, P["I"], P["r"], P["Q"], m, 1e-5, 1e300, 0, 1, P["w0"], P["U0"],
                              perms, NW, NU)
     assert not ws.any() and not Us.any()
+
+
+def test_fulltheta_oracle_gradient_and_chain():
+    """Full-theta comparator (GPT_SGLD.jl:109-120, :809-847): no reference fixture exists for it (parity unpinned), so
+    the restatement is checked against finite differences of its own log posterior and for the store layout."""
+    rng = np.random.default_rng(5)
+    N, D, n = 60, 3, 24
+    X = rng.standard_normal((N, D)); Z = rng.standard_normal((n, D)); b = 2 * np.pi * rng.random(n)
+    phi = o.featureNotensor(X, np.array([1.0, 0.7, 1.3]), 1.2, Z, b)
+    assert phi.shape == (n, N) and np.abs(phi).max() <= np.sqrt(2.0 / n) * 1.2 + 1e-15
+    # literal loop of :114-118 on a few entries
+    for (j, i) in [(0, 0), (5, 17), (23, 59)]:
+        want = np.sqrt(2.0 / n) * 1.2 * np.cos(np.sum(X[i] * Z[j] / np.array([1.0, 0.7, 1.3])) + b[j])
+        assert abs(phi[j, i] - want) < 1e-14
+    y = rng.standard_normal(N); th = rng.standard_normal(n)
+    g = o.nt_grad(phi, y, th, N, 0.1, 1.5)
+    eye = np.eye(n)
+    fd = np.array([(o.nt_logpost(phi, y, th + 1e-6 * eye[j], 0.1, 1.5) - o.nt_logpost(phi, y, th - 1e-6 * eye[j], 0.1, 1.5)) / 2e-6
+                   for j in range(n)])
+    assert np.abs(g - fd).max() / np.abs(g).max() < 1e-7
+    perms = [rng.permutation(N) for _ in range(3)]
+    noise = rng.standard_normal((3 * 4, n))
+    st = o.GPNT_SGLD(phi, y, 0.1, 1.5, 16, 1e-4, 0.5, 1, 2, th, perms, noise)
+    assert st.shape == (n, 12)
+    # first step by hand: eps = eps_theta * 1^(-decay) (:832), batch = first 16 columns of phi[:, perm]
+    p0 = perms[0][:16]
+    g0 = o.nt_grad(phi[:, p0], y[p0], th, N, 0.1, 1.5)
+    assert np.allclose(st[:, 0], th + 1e-4 * g0 / 2 + np.sqrt(1e-4) * noise[0], rtol=0, atol=1e-14)
+    assert not o.GPNT_SGLD(phi, y, 0.1, 1.5, 16, 1e300, 0.0, 0, 1, th, perms, noise).any()      # NaN -> zeros(n), :839-842
