@@ -229,9 +229,10 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
             float2 val = make_float2(0.f, 0.f);
             if (p1 > p0) {  // uniform across the CTA
                 const float2 t = Ts[(size_t)(k * r + l) * 32 + lane];
-                if (t.x != 0.f && t.y != 0.f) {
-                    val.x = e.x * __fdividef(sum.x, t.x);
-                    val.y = e.y * __fdividef(sum.y, t.y);
+                // (dead rows of a ragged last tile hold T = 0: they must not send the warp down the slow path)
+                if (!((live0 && t.x == 0.f) || (live1 && t.y == 0.f))) {
+                    val.x = live0 ? e.x * __fdividef(sum.x, t.x) : 0.f;
+                    val.y = live1 ? e.y * __fdividef(sum.y, t.y) : 0.f;
                 } else {  // exact zero factor: explicit leave-one-out products
                     float2 acc = make_float2(0.f, 0.f);
                     for (int pp = p0; pp < p1; ++pp) {

@@ -797,8 +797,14 @@ struct Small2Geo {
     size_t sz2, szr;
     __host__ __device__ explicit Small2Geo(int r) {
         r2 = 2 * r;
-        np2 = (r2 + 15) & ~15; ld2 = dmm_ld(np2); sz2 = (size_t)ld2 * np2;
         npr = (r + 15) & ~15; ldr = dmm_ld(npr); szr = (size_t)ldr * npr;
+        np2 = (r2 + 15) & ~15; ld2 = dmm_ld(np2); sz2 = (size_t)ld2 * np2;
+        // the r x r scratch of phases 1, 3, 4 lives in the 2r x 2r blocks: when 2r rounds up much less than r does
+        // (r = 20: 48 vs 32) the blocks are too small, and a wider zero padding of the 2r x 2r problem is far cheaper
+        // than the scalar fallback (k_small + k_apply + k_finish: 82 us against 35 us at r = 20)
+        while (!ok(r) && np2 < 2 * npr) {
+            np2 += 16; ld2 = dmm_ld(np2); sz2 = (size_t)ld2 * np2;
+        }
     }
     // phase 1 keeps eight r x r blocks beside X, the small exponential six beside E, phase 4 nine plus W (np2 x npr)
     __host__ __device__ bool ok(int) const {

@@ -234,7 +234,7 @@ function GPNT_SGLD(phi::NTFeatures, y::Array, signal_var::Real, sigma_theta::Rea
         st = ccall((:gptb_nt_run, LIB), Cint,
                    (Ptr{Cvoid}, Float64, Float64, Int64, Float64, Float64, Int32, Int32, UInt64, Ptr{Float64}, Ptr{Int64}, Ptr{Float64}, Ptr{Float64}),
                    h, signal_var, sigma_theta, m, eps_theta, decay_rate, burnin, maxepoch, param_seed, C_NULL, C_NULL, C_NULL, store)
-        if st == GEODESIC_NAN
+        if st == GPTB_GEODESIC_NAN
             println("Get NaN in theta. Try smaller epsilon")      # GPT_SGLD.jl:840
             return zeros(n)                                       # :841
         end

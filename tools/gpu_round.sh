@@ -1,3 +1,5 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -n 15
-timeout 600 python tools/nt_time.py > gpurun_out/r1i_fulltheta_C3.jsonl 2> gpurun_out/r1i_fulltheta.err; echo "nt rc=$?"; cat gpurun_out/r1i_fulltheta_C3.jsonl; tail -n 5 gpurun_out/r1i_fulltheta.err
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -n 3
+for w in C1 C2 C3; do
+  timeout 600 python bench.py --workload $w --no-pred --no-cpu --steps 300 --warmup 10 > gpurun_out/r1j_bench_$w.json 2> gpurun_out/r1j_bench_$w.err; echo "$w rc=$?"
+done
