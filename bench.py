@@ -132,7 +132,7 @@ def cpu_reference_steps_per_sec(W, mdl, budget_s=20.0, sample_rows=2048):
     return 1.0 / full, threads, f"{reps} steps on {ms} of {m} minibatch rows (features precomputed as the reference does), scaled x{m / ms:g} in rows"
 
 
-def run_reference(args, W):
+def run_reference(args, W, emit):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -151,7 +151,7 @@ def run_reference(args, W):
                 "restatement of GPT_SGLD.jl:378-439, OpenMP over minibatch rows)",
         "wall_s": time.perf_counter() - t0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(args, W):
@@ -175,8 +175,17 @@ def main():
     ap.add_argument("--pred-samples", type=int, default=C5["S"])
     args = ap.parse_args()
     W = WORKLOADS[args.workload]
+    # stdout carries exactly ONE line (the JSON): libraries that print to fd 1 (NCCL's "NCCL version ..." banner under
+    # torchrun, for one) are sent to stderr for the whole run
+    sys.stdout.flush()
+    _json_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        os.write(_json_fd, (json.dumps(obj) + "\n").encode())
+
     if args.impl == "reference":
-        return run_reference(args, W)
+        return run_reference(args, W, emit)
 
     import torch
     from gpt_b200 import _lib as L
@@ -386,7 +395,7 @@ def main():
                 "blocking_api_value": 1.0 / e2e_blocking_s},
         "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "pred": pred,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 

@@ -1211,7 +1211,22 @@ static int step_common(gptb_handle *h, double signal_var, const int32_t *rows, i
         return step_pipelined(h, signal_var, rows, bs, N_total, staged, Xstage, ystage, epsw, epsU, flags, nw_dev, nU_dev);
     GPTB_TRY(pipe_join(h));
     PhaseTimer pt(h);
+    // production-mode draws of this step: generated on a side stream under the gradient kernels (they depend on the
+    // step counter only; the previous step's update, earlier on the main stream, has consumed the buffer)
+    const bool side_noise = (flags & GPTB_FLAG_LANGEVIN) && !nw_dev && !nU_dev && !h->profiling;
+    if (side_noise) {
+        GPTB_TRY(pipe_init(h, 1));
+        GPTB_CUDA_OK(h, cudaEventRecord(h->evG[0], h->stream));
+        GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->side[0], h->evG[0], 0));
+        GPTB_TRY(gptb_launch_noise_range(h, h->step_counter, 0, h->cfg.D, true, h->side[0]));
+        GPTB_CUDA_OK(h, cudaEventRecord(h->evR[0], h->side[0]));
+    }
     GPTB_TRY(compute_grad(h, signal_var, rows, bs, N_total, staged, Xstage, ystage, pt));
+    if (side_noise) {
+        GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->evR[0], 0));
+        GPTB_TRY(gptb_launch_update_range(h, epsw, epsU, flags, nw_dev, nU_dev, h->step_counter, 0, h->cfg.D, true, h->stream,
+                                          true));
+    } else
     GPTB_TRY(gptb_launch_update(h, epsw, epsU, flags, nw_dev, nU_dev, h->step_counter));
     pt.done(GPTB_PHASE_UPDATE);
     pt.finish();

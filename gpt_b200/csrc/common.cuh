@@ -234,7 +234,9 @@ int gptb_launch_contract_tc(gptb_handle *h, const float *T, const double *w, con
 int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
                        const double *noise_U, uint64_t step);
 int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
-                             const double *noise_U, uint64_t step, int k0, int kn, bool with_w, cudaStream_t s);
+                             const double *noise_U, uint64_t step, int k0, int kn, bool with_w, cudaStream_t s,
+                             bool noise_ready = false);
+int gptb_launch_noise_range(gptb_handle *h, uint64_t step, int k0, int kn, bool with_w, cudaStream_t s);
 int gptb_update_alloc_noise(gptb_handle *h);
 int gptb_proj_geod_device(gptb_handle *scratch_owner, cudaStream_t s, int n, int r, const double *U, const double *V,
                           double t, double *out, int mode /*0 proj, 1 geod*/, int32_t *nan_flag);

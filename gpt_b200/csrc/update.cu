@@ -1069,8 +1069,22 @@ int gptb_update_alloc_noise(gptb_handle *h) {
 
 // The update of the dimensions [k0, k0 + kn) (and of w when with_w) on stream s.  The kernels address everything by
 // the global k, so that the Philox streams and hence the chain do not depend on how the dimensions are grouped.
+// The step's production-mode draws for the dimensions [k0, k0 + kn) (and w): they depend on the step counter only, so
+// the one-stream step generates them on a side stream under the forward / backward kernels.
+int gptb_launch_noise_range(gptb_handle *h, uint64_t step, int k0, int kn, bool with_w, cudaStream_t s) {
+    const gptb_config &c = h->cfg;
+    const size_t per_k = (size_t)c.r * c.n;
+    GPTB_TRY(gptb_update_alloc_noise(h));
+    const int gx = (int)std::min<size_t>((per_k / 2 + 255) / 256, 64);
+    k_noise<<<dim3(gx, kn + (with_w ? 1 : 0)), 256, 0, s>>>(h->gen_noise_w, h->gen_noise_U, c.Q, per_k, k0, kn, c.seed, step);
+    h->launches++;
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    return GPTB_OK;
+}
+
 int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
-                             const double *noise_U, uint64_t step, int k0, int kn, bool with_w, cudaStream_t s) {
+                             const double *noise_U, uint64_t step, int k0, int kn, bool with_w, cudaStream_t s,
+                             bool noise_ready) {
     const gptb_config &c = h->cfg;
     const int nb = (c.n + UP_ROWS - 1) / UP_ROWS;
     const bool stiefel = flags & GPTB_FLAG_STIEFEL, langevin = flags & GPTB_FLAG_LANGEVIN;
@@ -1084,10 +1098,7 @@ int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags
     }
     if (langevin && (!noise_w || !noise_U)) {
         // production mode: the step's draws are generated up front by a grid-wide kernel (two per Philox block)
-        GPTB_TRY(gptb_update_alloc_noise(h));
-        const int gx = (int)std::min<size_t>((per_k / 2 + 255) / 256, 64);
-        k_noise<<<dim3(gx, gy), 256, 0, s>>>(h->gen_noise_w, h->gen_noise_U, c.Q, per_k, k0, kn, c.seed, step);
-        h->launches++;
+        if (!noise_ready) GPTB_TRY(gptb_launch_noise_range(h, step, k0, kn, with_w, s));
         if (!noise_w) noise_w = h->gen_noise_w;
         if (!noise_U) noise_U = h->gen_noise_U;
     }
@@ -1127,7 +1138,7 @@ int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags
 
 int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
                        const double *noise_U, uint64_t step) {
-    return gptb_launch_update_range(h, epsw, epsU, flags, noise_w, noise_U, step, 0, h->cfg.D, true, h->stream);
+    return gptb_launch_update_range(h, epsw, epsU, flags, noise_w, noise_U, step, 0, h->cfg.D, true, h->stream, false);
 }
 
 // Standalone proj (mode 0) / geod (mode 1) on device buffers U, V (n x r col-major); scratch from `h`.
