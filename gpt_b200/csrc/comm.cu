@@ -136,3 +136,15 @@ int gptb_allreduce_range(gptb_handle *h, double *buf, size_t count, cudaStream_t
     h->launches++;
     return GPTB_OK;
 }
+
+int gptb_allreduce_range_f32(gptb_handle *h, float *buf, size_t count, cudaStream_t stream) {
+    if (h->nranks <= 1 || count == 0) return GPTB_OK;
+    NcclApi &a = api();
+    ncclResult r = a.AllReduce(buf, buf, count, kNcclFloat32, kNcclSum, (ncclComm_p)h->nccl_comm, stream);
+    if (r != 0) {
+        gptb_set_error(h, "ncclAllReduce: %s", a.GetErrorString(r));
+        return GPTB_ERR_NCCL;
+    }
+    h->launches++;
+    return GPTB_OK;
+}

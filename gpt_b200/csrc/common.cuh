@@ -102,7 +102,12 @@ struct gptb_handle {
     void *Eimg = nullptr;              // fp16 hi|lo image of E for the backward MMA (TC)
     int32_t *idx_dev = nullptr;        // explicit batch indices
     double *grad = nullptr;            // [Q + n r D]
-    float *gradF = nullptr;            // FP32 partial accumulators of the TC path
+    float *gradF = nullptr;            // FP32 partial accumulators of the TC path: [D][npad][rpad], = gradFbase + qpad
+    float *gradFbase = nullptr;        // [qpad | D npad rpad]: the first qpad floats take gradw in the FP32 gradient flow
+    int gradF_qpad = 0;                // = GPTB_GW_SLOTS * gradF_qstride
+    int gradF_qstride = 0;             // Q rounded up to 32
+    bool f32_grad = false;             // set for the duration of a step: K2 sums gradw into gradFbase, K3's sums are not
+                                       // folded into the FP64 buffer, the all-reduce and the update work on gradFbase
     void *tc_partials = nullptr;       // deterministic split-row partials of the backward MMA
     size_t tc_partials_bytes = 0;
     float *tc_state = nullptr;         // [0] max|E| of the running step, [1] escale (2^k), [2] 1/escale,
@@ -159,6 +164,10 @@ struct gptb_handle {
 };
 
 inline bool gptb_is_tc(const gptb_handle *h) { return h->cfg.precision != GPTB_PREC_FP64; }
+
+// gradw of the FP32 gradient flow is summed into GPTB_GW_SLOTS copies (CTA b of K2 adds to copy b % SLOTS) that the
+// update adds up: 1024 CTAs x 200 atomics on the 7 cache lines of one copy serialise in the L2 atomic unit.
+constexpr int GPTB_GW_SLOTS = 32;
 
 // ------------------------------------------------------------------------------------------
 // Philox4x32-10 (Salmon et al. 2011) — counter-based, so every rank / every CTA draws the same
@@ -267,3 +276,6 @@ size_t gptb_tc_eimg_bytes(const gptb_handle *h, int64_t mpad);
 // comm.cu
 int gptb_allreduce_grad(gptb_handle *h);
 int gptb_allreduce_range(gptb_handle *h, double *buf, size_t count, cudaStream_t stream);
+int gptb_allreduce_range_f32(gptb_handle *h, float *buf, size_t count, cudaStream_t stream);
+int gptb_tc_ensure_gradF(gptb_handle *h);
+bool gptb_contract_tc_usable(const gptb_handle *h);

@@ -48,6 +48,8 @@ struct ContractTcParams {
     const int32_t *lists;    // q * 32 (float2 index into Vs) for the q of each list; padding entries -> zero row q = Q
     const double *yb;
     double *fhat, *gradw;
+    float *gradwF;           // FP32 gradient flow: gradw is summed here instead (one all-reduce buffer with gradF),
+    int gw_stride;           //   into copy blockIdx.x % GPTB_GW_SLOTS (stride gw_stride floats)
     __half *Eimg;
     const float *escale_img;
     float *emax_out;
@@ -186,7 +188,10 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
 #pragma unroll
         for (int off = NB; off < 32; off <<= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], off);
         const int q = qb + CNW * (lane % NB);
-        if (lane < NB && q < Q) atomicAdd(&p.gradw[q], (double)v[0]);
+        if (lane < NB && q < Q) {
+            if (p.gradwF) atomicAdd(&p.gradwF[(size_t)(blockIdx.x % GPTB_GW_SLOTS) * p.gw_stride + q], v[0]);
+            else atomicAdd(&p.gradw[q], (double)v[0]);
+        }
     }
     __syncthreads();
 
@@ -318,6 +323,11 @@ int gptb_contract_tc_build_tables(gptb_handle *h, const int32_t *Iz) {
     return GPTB_OK;
 }
 
+size_t gptb_contract_tc_smem(const gptb_handle *h);
+bool gptb_contract_tc_usable(const gptb_handle *h) {
+    return h->ct_off1 && h->cfg.D <= 16 && gptb_contract_tc_smem(h) <= 227 * 1024;
+}
+
 size_t gptb_contract_tc_smem(const gptb_handle *h) {
     const gptb_config &c = h->cfg;
     const size_t DP4 = (c.D + 3) / 4;
@@ -342,6 +352,8 @@ int gptb_launch_contract_tc(gptb_handle *h, const float *T, const double *w, con
     p.yb = yb;
     p.fhat = fhat;
     p.gradw = gradw;
+    p.gradwF = (h->f32_grad && want_grad) ? h->gradFbase : nullptr;
+    p.gw_stride = h->gradF_qstride;
     p.Eimg = (__half *)Eimg;
     p.escale_img = h->tc_state + 1;
     p.emax_out = h->tc_state + 0;

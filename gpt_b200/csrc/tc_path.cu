@@ -835,6 +835,17 @@ int gptb_tc_pack_group(gptb_handle *h, const double *Ug, int Sg, int NC, void *i
     return GPTB_OK;
 }
 
+int gptb_tc_ensure_gradF(gptb_handle *h) {
+    if (h->gradFbase) return GPTB_OK;
+    const size_t gf = (size_t)h->cfg.D * h->npad * h->rpad;
+    h->gradF_qstride = (h->cfg.Q + 31) & ~31;
+    h->gradF_qpad = GPTB_GW_SLOTS * h->gradF_qstride;
+    GPTB_CUDA_OK(h, cudaMalloc((void **)&h->gradFbase, (gf + h->gradF_qpad) * sizeof(float)));
+    GPTB_CUDA_OK(h, cudaMemsetAsync(h->gradFbase, 0, (gf + h->gradF_qpad) * sizeof(float), h->stream));
+    h->gradF = h->gradFbase + h->gradF_qpad;
+    return GPTB_OK;
+}
+
 int gptb_launch_bwd_tc(gptb_handle *h, const float *XbF, const void *Eimg, int64_t bs, int64_t mpad, double *gradU) {
     return gptb_launch_bwd_tc_range(h, XbF, Eimg, bs, mpad, gradU, 0, h->cfg.D);
 }
@@ -842,11 +853,7 @@ int gptb_launch_bwd_tc(gptb_handle *h, const float *XbF, const void *Eimg, int64
 int gptb_launch_bwd_tc_range(gptb_handle *h, const float *XbF, const void *Eimg, int64_t bs, int64_t mpad, double *gradU,
                              int k0, int kn) {
     const gptb_config &c = h->cfg;
-    const size_t gf = (size_t)c.D * h->npad * h->rpad;
-    if (!h->gradF) {
-        GPTB_CUDA_OK(h, cudaMalloc((void **)&h->gradF, gf * sizeof(float)));
-        GPTB_CUDA_OK(h, cudaMemsetAsync(h->gradF, 0, gf * sizeof(float), h->stream));
-    }
+    GPTB_TRY(gptb_tc_ensure_gradF(h));
     BwdParams p;
     p.mext = (bs + 127) / 128 * 128;
     float *gradF_g = h->gradF + (size_t)k0 * h->npad * h->rpad;
@@ -879,9 +886,12 @@ int gptb_launch_bwd_tc_range(gptb_handle *h, const float *XbF, const void *Eimg,
         default: st = launch_bwd_r<64>(h, p, grid, smem); break;
     }
     GPTB_TRY(st);
-    finalize_grad_kernel<<<dim3(h->npad / 32, kn), 256, 0, h->stream>>>(gradF_g, gradU + (size_t)k0 * c.r * c.n, c.n, h->npad,
-                                                                       c.r, h->rpad);
-    h->launches += 2;
+    if (!h->f32_grad) {   // (in the FP32 gradient flow the update reads and clears gradF itself)
+        finalize_grad_kernel<<<dim3(h->npad / 32, kn), 256, 0, h->stream>>>(gradF_g, gradU + (size_t)k0 * c.r * c.n, c.n,
+                                                                           h->npad, c.r, h->rpad);
+        h->launches++;
+    }
+    h->launches++;
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;
 }

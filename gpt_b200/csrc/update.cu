@@ -121,7 +121,10 @@ __global__ void __launch_bounds__(UP_THREADS)
 k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ w, double *__restrict__ U,
           double *__restrict__ G, double *__restrict__ small, size_t small_stride, int n, int r, int D, int Q,
           double epsw, double epsU, int flags, const double *__restrict__ noise_w,
-          const double *__restrict__ noise_U, uint64_t key, uint64_t step, int have_grad, int k0, int kn) {
+          const double *__restrict__ noise_U, uint64_t key, uint64_t step, int have_grad, int k0, int kn,
+          float *__restrict__ gradFbase, int qpad, int qstride, int npad, int rpad) {
+    // gradFbase != null: the FP32 gradient flow — gradw in gradFbase[0..Q), gradU as K3 left it in
+    // gradFbase + qpad ([D][npad][rpad]); every entry is read once here and cleared for the next step
     // grid.y = kn (+ 1): rows 0..kn-1 are the dimensions k0.., row kn (if launched) is w
     extern __shared__ double sm[];
     const int tid = threadIdx.x;
@@ -131,7 +134,15 @@ k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ 
         if (blockIdx.x != 0 || !have_grad) return;
         const double sq = sqrt(epsw);
         for (int q = tid; q < Q; q += UP_THREADS) {
-            double g = grad[q] - w[q];  // prior term of :393 (sigma_w = 1, :354), added once after the all-reduce
+            double gl = grad[q];
+            if (gradFbase) {   // the GPTB_GW_SLOTS partial copies K2 summed into
+                gl = 0.0;
+                for (int s_ = 0; s_ < GPTB_GW_SLOTS; ++s_) {
+                    gl += (double)gradFbase[(size_t)s_ * qstride + q];
+                    gradFbase[(size_t)s_ * qstride + q] = 0.f;
+                }
+            }
+            double g = gl - w[q];  // prior term of :393 (sigma_w = 1, :354), added once after the all-reduce
             double z = 0.0;
             if (langevin) z = noise_w ? noise_w[q] : noise_at(key, GPTB_STREAM_NOISE_W, step, (uint64_t)q);
             w[q] += epsw * g / 2 + sq * z;
@@ -146,9 +157,26 @@ k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ 
     const double sqU = sqrt(epsU);
     const int npr = (r + 15) & ~15, ldt = dmm_ld(npr);   // tile layout [jj][l], zero padded to npr columns
     double *Us = sm, *Gs = sm + (size_t)UP_ROWS * ldt;
+    // FP32 gradient flow: this CTA's rows of gradF ([j][l], contiguous) are staged through shared memory with
+    // coalesced 16-byte loads and cleared the same way (per-element strided loads + 4-byte clears took 60 us)
+    float *gst = reinterpret_cast<float *>(sm + 2 * (size_t)UP_ROWS * ldt);   // [UP_ROWS][rpad + 1]
+    if (gradFbase) {
+        const int nrow = min(UP_ROWS, npad - j0);
+        float4 *src = reinterpret_cast<float4 *>(gradFbase + qpad + ((size_t)k * npad + j0) * rpad);
+        for (int t = tid; t < nrow * rpad / 4; t += UP_THREADS) {
+            const float4 v = src[t];
+            src[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+            const int row = (4 * t) / rpad, col = (4 * t) - row * rpad;
+            float *d = gst + row * (rpad + 1) + col;
+            d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+        }
+        __syncthreads();
+    }
     for (int t = tid; t < UP_ROWS * npr; t += UP_THREADS) {
         int jj = t % UP_ROWS, l = t / UP_ROWS, j = j0 + jj;
         double u = 0.0, g = 0.0;
+        double grF = 0.0;
+        if (gradFbase && j < npad && l < rpad) grF = (double)gst[jj * (rpad + 1) + l];
         if (jj < rows && l < r) {
             size_t e = (size_t)l * n + j;
             u = Uk[e];
@@ -157,6 +185,7 @@ k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ 
                 z = noise_U ? noise_U[(size_t)k * r * n + e]
                             : noise_at(key, GPTB_STREAM_NOISE_U | ((uint64_t)k << 40), step, (uint64_t)e);
             double gr = have_grad ? gU[e] : 0.0;
+            if (gradFbase) gr = grF;
             if (stiefel) {
                 g = sqU * gr / 2 + z;                       // :420 argument of proj
                 Gk[e] = g;
@@ -1102,9 +1131,12 @@ int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags
         if (!noise_w) noise_w = h->gen_noise_w;
         if (!noise_U) noise_U = h->gen_noise_U;
     }
-    size_t sm1 = 2 * (size_t)UP_ROWS * dmm_ld((c.r + 15) & ~15) * sizeof(double);
+    size_t sm1 = 2 * (size_t)UP_ROWS * dmm_ld((c.r + 15) & ~15) * sizeof(double) +
+                 (h->f32_grad ? (size_t)UP_ROWS * (h->rpad + 1) * sizeof(float) : 0);
     k_prepare<<<dim3(nb, gy), UP_THREADS, sm1, s>>>(h->grad, h->w, h->U, h->G, h->small, h->small_stride, c.n, c.r, c.D, c.Q,
-                                                   epsw, epsU, flags, noise_w, noise_U, c.seed, step, 1, k0, kn);
+                                                   epsw, epsU, flags, noise_w, noise_U, c.seed, step, 1, k0, kn,
+                                                   h->f32_grad ? h->gradFbase : nullptr, h->gradF_qpad, h->gradF_qstride,
+                                                   h->npad, h->rpad);
     h->launches++;
     h->shadows_valid = false;
     if (stiefel) {
