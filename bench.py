@@ -361,9 +361,9 @@ def main():
     roofline = {"kernel": {"fwd": "fwd_tc_kernel (K1)", "bwd": "bwd_tc_kernel (K3)"}[dom], "bound": "tensor",
                 "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": (ach / peak_tf) if ach else None,
                 # dram__bytes_read.sum + dram__bytes_write.sum of one K3 launch at this exact shape (ncu --set full,
-                # profiles/r1g_ncu_full_summary_C4_tc3.txt): 87.9 MB read (the E image, once per feature-block group)
-                # + 3.5 MB written; algorithmic bytes are 84 MB of E image + 2.6 MB of inputs + 1.3 MB of gradient
-                "traffic": 91461632 if (world == 1 and args.workload == "C4" and dom == "bwd") else None,
+                # profiles/r1l_ncu_full_summary_C4_tc3.txt): 87.9 MB read (the E image, once per feature-block group)
+                # + 3.1 MB written; algorithmic bytes are 84 MB of E image + 2.6 MB of inputs + 1.3 MB of gradient
+                "traffic": 91066624 if (world == 1 and args.workload == "C4" and dom == "bwd") else None,
                 "peak_source": which_peak, "avg_launch_ms": dom_ms,
                 "algorithmic_flops_per_launch": per_launch_flops,
                 "sfu": {"cos_per_launch": ml * n * D, "achieved_Tcos_s": ml * n * D / (dom_ms * 1e-3) / 1e12 if dom_ms else None,

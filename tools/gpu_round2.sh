@@ -1,7 +1,7 @@
+#!/bin/bash
+# Multi-GPU bench line on NG GPUs of one box (run through `gpurun --gpus NG`), launched as the driver launches it.
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -n 3
-GPTB_PIPE_GROUPS=0 timeout 300 python tools/phase_times.py --steps 100 2>&1 | grep "unprofiled" | sed "s/^/G0 /"
-timeout 300 python tools/phase_times.py --steps 100 2>&1 | grep "unprofiled" | sed "s/^/auto /"
-N=2
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --steps 200 --warmup 5 > gpurun_out/r1k_bench_n$N.json 2> gpurun_out/r1k_bench_n$N.err; echo "rc=$?"
-wc -l gpurun_out/r1k_bench_n$N.json; head -c 200 gpurun_out/r1k_bench_n$N.json
+N=${NG:-2}
+T=${TAG:-r1}
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --steps 200 --warmup 5 > gpurun_out/${T}_bench_n$N.json 2> gpurun_out/${T}_bench_n$N.err; echo "rc=$?" >> gpurun_out/${T}_bench_n$N.err
+tail -n 3 gpurun_out/${T}_bench_n$N.err; wc -l gpurun_out/${T}_bench_n$N.json; head -c 300 gpurun_out/${T}_bench_n$N.json
