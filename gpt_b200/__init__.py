@@ -7,5 +7,5 @@ There is no CPU fallback: importing works anywhere, computing needs a B200.
 from . import gpt_sgld  # noqa: F401
 from .gpt_sgld import (  # noqa: F401
     GPTregression, RFFFeatures, datawhitening, feature, feature2, geod, pred, pred_samples, proj, samplenz,
-    GeodesicNaN, GptbError, GPNT_SGLD, NTFeatures, featureNotensor, pred_notensor,
+    GeodesicNaN, GptbError, GPNT_SGLD, GPT_SGLDERMw, NTFeatures, featureNotensor, pred_notensor,
 )

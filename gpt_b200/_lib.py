@@ -24,7 +24,7 @@ class Config(C.Structure):
 OK, ERR_ARG, ERR_SHAPE, ERR_STATE, ERR_CUDA, ERR_NCCL, ERR_NOMEM, GEODESIC_NAN, ERR_UNSUPPORTED = range(9)
 PREC_FP64, PREC_TC3, PREC_TC1 = 0, 1, 2
 FEAT_COS, FEAT_SINCOS = 0, 1
-FLAG_LANGEVIN, FLAG_STIEFEL = 1, 2
+FLAG_LANGEVIN, FLAG_STIEFEL, FLAG_FIX_U = 1, 2, 4
 PHASES = ("gather", "fwd", "contract", "bwd", "reduce", "update")
 
 H = C.c_void_p

@@ -211,7 +211,8 @@ int forward_contract(gptb_handle *h, bool phi_mode, const int32_t *rows, const d
 // Gradient of the rank's share of the minibatch into h->grad (likelihood part only, all-reduced).
 // rows_dev: device row ids of the *global* batch or null (= order[start..] / identity when staged).
 int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int64_t bs, int64_t N_total,
-                 bool staged_host_batch, const double *Xstage_rm, const double *ystage, PhaseTimer &pt) {
+                 bool staged_host_batch, const double *Xstage_rm, const double *ystage, PhaseTimer &pt,
+                 bool skip_bwd = false) {
     const gptb_config &c = h->cfg;
     const bool phi_mode = h->have_phi && !staged_host_batch;
     const int64_t lo = (int64_t)h->rank * bs / h->nranks, hi = (int64_t)(h->rank + 1) * bs / h->nranks;
@@ -238,7 +239,9 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
     if (lbs > 0) {
         GPTB_TRY(forward_contract(h, phi_mode, rows, h->w, h->U, h->Uimg, lbs, escale, true, &pt));
         double *gU = h->grad + c.Q;
-        if (f64) {
+        if (skip_bwd) {
+            // GPTB_FLAG_FIX_U: the w-only sampler needs fhat and gradw only
+        } else if (f64) {
             GPTB_TRY(gptb_launch_bwd_fp64(h, h->Xb, phi_mode ? h->phi : nullptr, rows, (const double *)h->E, lbs,
                                           h->mpad, gU));
         } else {
@@ -341,6 +344,7 @@ static int pipe_tail_end(gptb_handle *h, cudaStream_t s) {
 static bool pipe_usable(gptb_handle *h, int64_t bs, bool staged_host_batch, int32_t flags) {
     const bool phi_mode = h->have_phi && !staged_host_batch;
     const int G = pipe_groups_for(h);
+    if (flags & GPTB_FLAG_FIX_U) return false;
     if (!(G >= 2 && h->cfg.D >= G && !h->profiling && !use_fp64(h, phi_mode) && (flags & GPTB_FLAG_STIEFEL) &&
           bs >= h->nranks))
         return false;
@@ -1238,16 +1242,15 @@ static int step_common(gptb_handle *h, double signal_var, const int32_t *rows, i
         GPTB_TRY(pipe_init(h, 1));
         GPTB_CUDA_OK(h, cudaEventRecord(h->evG[0], h->stream));
         GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->side[0], h->evG[0], 0));
-        GPTB_TRY(gptb_launch_noise_range(h, h->step_counter, 0, h->cfg.D, true, h->side[0]));
+        GPTB_TRY(gptb_launch_noise_range(h, h->step_counter, 0, (flags & GPTB_FLAG_FIX_U) ? 0 : h->cfg.D, true, h->side[0]));
         GPTB_CUDA_OK(h, cudaEventRecord(h->evR[0], h->side[0]));
     }
-    GPTB_TRY(compute_grad(h, signal_var, rows, bs, N_total, staged, Xstage, ystage, pt));
-    if (side_noise) {
-        GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->evR[0], 0));
-        GPTB_TRY(gptb_launch_update_range(h, epsw, epsU, flags, nw_dev, nU_dev, h->step_counter, 0, h->cfg.D, true, h->stream,
-                                          true));
-    } else
-    GPTB_TRY(gptb_launch_update(h, epsw, epsU, flags, nw_dev, nU_dev, h->step_counter));
+    const bool fix_U = (flags & GPTB_FLAG_FIX_U) != 0;
+    const int kn_upd = fix_U ? 0 : h->cfg.D;          // GPT_SGLDERMw: only w moves (:1108)
+    GPTB_TRY(compute_grad(h, signal_var, rows, bs, N_total, staged, Xstage, ystage, pt, fix_U));
+    if (side_noise) GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->evR[0], 0));
+    GPTB_TRY(gptb_launch_update_range(h, epsw, epsU, flags, nw_dev, nU_dev, h->step_counter, 0, kn_upd, true, h->stream,
+                                      side_noise));
     pt.done(GPTB_PHASE_UPDATE);
     pt.finish();
     h->step_counter++;

@@ -1121,7 +1121,7 @@ int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags
     const int gy = kn + (with_w ? 1 : 0);
     optin_smem();
     double *small_g = h->small + (size_t)k0 * h->small_stride;
-    if (stiefel) {
+    if (stiefel && kn > 0) {
         SmallLayout L(c.r);
         GPTB_CUDA_OK(h, cudaMemset2DAsync(small_g, h->small_stride * sizeof(double), 0, L.zero_count() * sizeof(double), kn, s));
     }
@@ -1138,8 +1138,8 @@ int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags
                                                    h->f32_grad ? h->gradFbase : nullptr, h->gradF_qpad, h->gradF_qstride,
                                                    h->npad, h->rpad);
     h->launches++;
-    h->shadows_valid = false;
-    if (stiefel) {
+    if (kn > 0) h->shadows_valid = false;
+    if (stiefel && kn > 0) {
         const size_t sb = small_smem_bytes(c.r);
         const Small2Geo sg(c.r);
         const size_t koff = (size_t)k0 * c.r * c.n;

@@ -304,13 +304,13 @@ class Model:
         _check(self.lib.gptb_sgld_step_host_wait(self.h), self.h)
 
     def sgld_run(self, signal_var, m, epsw, epsU, burnin, maxepoch, langevin=True, stiefel=True, perms=None,
-                 noise_w=None, noise_U=None, store=True, N=None):
+                 noise_w=None, noise_U=None, store=True, N=None, fix_U=False):
         Q, n, r, D = self.cfg.Q, self.cfg.n, self.cfg.r, self.cfg.D
-        flags = (L.FLAG_LANGEVIN if langevin else 0) | (L.FLAG_STIEFEL if stiefel else 0)
+        flags = (L.FLAG_LANGEVIN if langevin else 0) | (L.FLAG_STIEFEL if stiefel else 0) | (L.FLAG_FIX_U if fix_U else 0)
         numbatches = -(-int(N) // int(m))
         T = maxepoch * numbatches
         w_store = np.zeros((Q, T), order="F") if store else None
-        U_store = np.zeros((n, r, D, T), order="F") if store else None
+        U_store = np.zeros((n, r, D, T), order="F") if (store and not fix_U) else None
         pp = None
         if perms is not None:
             pp = np.require(np.asarray(perms), dtype=np.int64, requirements=["C_CONTIGUOUS"])
@@ -416,6 +416,27 @@ def GPTregression(phi, y, signal_var, I, r, Q, m, epsw, epsU, burnin, maxepoch, 
             mdl.init_params(param_seed, stiefel)
         return mdl.sgld_run(signal_var, m, epsw, epsU, burnin, maxepoch, langevin, stiefel, perms, noise_w, noise_U,
                             store=True, N=N)
+
+
+def GPT_SGLDERMw(phi, y, signal_var, I, r, Q, m, epsw, burnin, maxepoch, param_seed=0, *, precision: Optional[int] = None,
+                 w0=None, U0=None, perms=None, noise_w=None):
+    """GPT_SGLD.jl:1065-1118: SGLD on the core w only; the factors stay at their (Stiefel) initial draw.  Returns
+    (w_store[Q, maxepoch*ceil(N/m)], U).  The reference takes its draws from the global RNG; here param_seed names
+    them (keyword-only extras as in GPTregression)."""
+    y = np.ravel(np.asarray(y, dtype=np.float64))
+    N = y.size
+    with _model_for(phi, r, Q, I, precision, seed=int(param_seed)) as mdl:
+        if isinstance(phi, RFFFeatures):
+            mdl.set_train(phi.X, y)
+        else:
+            mdl.set_train_phi(phi, y)
+        if w0 is not None:
+            mdl.set_params(w0, U0)
+        else:
+            mdl.init_params(param_seed, True)
+        w_store, _ = mdl.sgld_run(signal_var, m, epsw, 0.0, burnin, maxepoch, True, True, perms, noise_w, None, store=True,
+                                  N=N, fix_U=True)
+        return w_store, mdl.get_params()[1]
 
 
 def proj(U, V):

@@ -56,7 +56,9 @@ enum gptb_feature_kind {
 
 enum gptb_flags {
     GPTB_FLAG_LANGEVIN = 1, /* keyword langevin of GPTregression (GPT_SGLD.jl:345)        */
-    GPTB_FLAG_STIEFEL = 2   /* keyword stiefel                                             */
+    GPTB_FLAG_STIEFEL = 2,  /* keyword stiefel                                             */
+    GPTB_FLAG_FIX_U = 4     /* GPT_SGLDERMw (GPT_SGLD.jl:1065-1118): SGLD on w only, the factors U stay as they are
+                               (no factor gradient, no U update; U_store may be NULL)      */
 };
 
 typedef struct gptb_config {

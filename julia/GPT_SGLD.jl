@@ -19,7 +19,7 @@
 module GPT_SGLD
 
 export datawhitening, feature, feature2, samplenz, pred, GPTregression, proj, geod, RFFFeatures,
-       featureNotensor, GPNT_SGLD, NTFeatures
+       featureNotensor, GPNT_SGLD, NTFeatures, GPT_SGLDERMw
 
 using Random, Statistics
 
@@ -190,6 +190,37 @@ function geod(U::Array, mom::Array, t::Real)
     end
     check(st)
     out
+end
+
+# GPT_SGLD.jl:1065-1118  GPT_SGLDERMw(phi,y,signal_var,I,r,Q,m,epsw,burnin,maxepoch): SGLD on w only, U fixed at its
+# Stiefel draw (GPTB_FLAG_FIX_U).  param_seed names the draws the reference takes from the global RNG.
+const FLAG_FIX_U = Cint(4)
+function GPT_SGLDERMw(phi::Union{RFFFeatures,Array{Float64,3}}, y::Array, signal_var::Real, I::Array, r::Integer, Q::Integer,
+                      m::Integer, epsw::Real, burnin::Integer, maxepoch::Integer; param_seed::Integer = 0, precision = PREC_TC3)
+    n, D, N = size(phi)
+    lazy = phi isa RFFFeatures
+    h = create(D, n, r, Q; precision = lazy ? precision : PREC_FP64, kind = lazy ? phi.kind : FEAT_COS, seed = param_seed)
+    try
+        check(ccall((:gptb_set_index, LIB), Cint, (Ptr{Cvoid}, Ptr{Int32}), h, Matrix{Int32}(I)), h)
+        yv = Vector{Float64}(vec(y))
+        if lazy
+            set_features!(h, phi)
+            check(ccall((:gptb_set_train, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int64), h, phi.X, yv, N), h)
+        else
+            check(ccall((:gptb_set_train_phi, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int64), h, phi, yv, N), h)
+        end
+        check(ccall((:gptb_init_params, LIB), Cint, (Ptr{Cvoid}, UInt64, Int32), h, param_seed, 1), h)      # :1076-1084
+        w_store = zeros(Q, maxepoch * cld(N, m)); U = zeros(n, r, D); w = zeros(Q)
+        check(ccall((:gptb_sgld_run, LIB), Cint,
+                    (Ptr{Cvoid}, Float64, Int64, Float64, Float64, Int32, Int32, Int32, Ptr{Int64}, Ptr{Float64}, Ptr{Float64},
+                     Ptr{Float64}, Ptr{Float64}),
+                    h, signal_var, m, epsw, 0.0, burnin, maxepoch, FLAG_LANGEVIN | FLAG_STIEFEL | FLAG_FIX_U, C_NULL, C_NULL, C_NULL,
+                    w_store, C_NULL), h)
+        check(ccall((:gptb_get_params, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}), h, w, U), h)
+        return w_store, U                                                                                 # :1117
+    finally
+        destroy(h)
+    end
 end
 
 # ---- full-theta ("no tensor") model: GPT_SGLD.jl:109-120, :809-847 ---------------------------------------------

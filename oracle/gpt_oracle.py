@@ -351,3 +351,30 @@ def GPNT_SGLD(phi, y, signal_var, sigma_theta, m, eps_theta, decay_rate, burnin,
             if np.isnan(theta).any():
                 return np.zeros(n)
     return store
+
+
+def GPT_SGLDERMw(phi, y, signal_var, I, r, Q, m, epsw, burnin, maxepoch, w0, U0, perms, noise_w):
+    """GPT_SGLD.jl:1065-1118 with the draws injected: SGLD on w only, U fixed at U0 (= the Stiefel draw of :1080-1084).
+    Returns (w_store[Q, maxepoch*numbatches], U)."""
+    phi = np.array(phi, dtype=np.float64, order="F")
+    y = np.array(y, dtype=np.float64)
+    n, D, N = phi.shape
+    numbatches = int(np.ceil(N / m))
+    w = np.array(w0, dtype=np.float64)
+    U = np.array(U0, dtype=np.float64)
+    w_store = np.zeros((Q, maxepoch * numbatches))
+    step = 0
+    for epoch in range(1, burnin + maxepoch + 1):
+        perm = perms[epoch - 1]
+        phi = phi[:, :, perm]
+        y = y[perm]
+        for batch in range(1, numbatches + 1):
+            lo, hi = m * (batch - 1), min(m * batch, N)
+            V = computeV(phidotU(U, phi[:, :, lo:hi]), I)                                   # :1097-1100
+            fhat = computefhat(V, w)                                                        # :1103
+            gradw = (N / (hi - lo)) * (V @ (y[lo:hi] - fhat)) / signal_var - w              # :1106 (sigma_w = 1)
+            w = w + epsw * gradw / 2 + np.sqrt(epsw) * np.asarray(noise_w[step])            # :1109
+            if epoch > burnin:
+                w_store[:, (epoch - burnin - 1) * numbatches + batch - 1] = w               # :1111-1113
+            step += 1
+    return w_store, U

@@ -451,3 +451,29 @@ def test_fulltheta_production_mode_and_nan_abort():
     assert z.shape == (P["n"],) and not z.any()                            # :839-842
     with pytest.raises(ValueError):
         G.featureNotensor(P["X"], np.ones(3), 1.0, P["Z"], P["b"])
+
+
+@pytest.mark.parametrize("prec", PRECS, ids=IDS)
+def test_GPT_SGLDERMw_vs_oracle(prec):
+    """w-only sampler (GPT_SGLD.jl:1065-1118, GPTB_FLAG_FIX_U): chain of w against the oracle with injected draws; U
+    must come back untouched."""
+    P = make_problem(3, 230, 16, 4, Q=20, seed=12)
+    N, m, burnin, maxepoch = 230, 100, 1, 2
+    nb = 3
+    rng = np.random.default_rng(6)
+    perms = [rng.permutation(N) for _ in range(burnin + maxepoch)]
+    NW = rng.standard_normal(((burnin + maxepoch) * nb, P["Q"]))
+    phi = P["phi_fn"](P["X"])
+    ws, U = o.GPT_SGLDERMw(phi, P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m, 1e-5, burnin, maxepoch, P["w0"], P["U0"],
+                           perms, NW)
+    gw, gU = G.GPT_SGLDERMw(_feat(P), P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m, 1e-5, burnin, maxepoch, 3,
+                            precision=prec, w0=P["w0"], U0=P["U0"], perms=np.stack(perms), noise_w=NW)
+    assert gw.shape == ws.shape == (P["Q"], maxepoch * nb)
+    assert relerr(gw, ws) < (1e-9 if prec == L.PREC_FP64 else 1e-4)
+    assert np.array_equal(gU, P["U0"])
+    # production mode: reproducible, U stays on the manifold it was drawn from
+    a = G.GPT_SGLDERMw(_feat(P), P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m, 1e-5, 0, 2, 5, precision=prec)
+    b = G.GPT_SGLDERMw(_feat(P), P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m, 1e-5, 0, 2, 5, precision=prec)
+    assert relerr(a[0], b[0]) < 1e-5 and np.array_equal(a[1], b[1])
+    for k in range(P["D"]):
+        assert np.abs(a[1][:, :, k].T @ a[1][:, :, k] - np.eye(P["r"])).max() < 1e-10
