@@ -158,42 +158,63 @@ k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ 
     const int npr = (r + 15) & ~15, ldt = dmm_ld(npr);   // tile layout [jj][l], zero padded to npr columns
     double *Us = sm, *Gs = sm + (size_t)UP_ROWS * ldt;
     // FP32 gradient flow: this CTA's rows of gradF ([j][l], contiguous) are staged through shared memory with
-    // coalesced 16-byte loads and cleared the same way (per-element strided loads + 4-byte clears took 60 us)
+    // coalesced 16-byte loads and cleared the same way (per-element strided loads + 4-byte clears took 60 us).  The
+    // loads are issued first and land while pass A below fetches U and the noise.
     float *gst = reinterpret_cast<float *>(sm + 2 * (size_t)UP_ROWS * ldt);   // [UP_ROWS][rpad + 1]
+    float4 pre[4];
+    float4 *src = nullptr;
+    int cnt4 = 0;
     if (gradFbase) {
-        const int nrow = min(UP_ROWS, npad - j0);
-        float4 *src = reinterpret_cast<float4 *>(gradFbase + qpad + ((size_t)k * npad + j0) * rpad);
-        for (int t = tid; t < nrow * rpad / 4; t += UP_THREADS) {
-            const float4 v = src[t];
-            src[t] = make_float4(0.f, 0.f, 0.f, 0.f);
-            const int row = (4 * t) / rpad, col = (4 * t) - row * rpad;
-            float *d = gst + row * (rpad + 1) + col;
-            d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
-        }
-        __syncthreads();
+        src = reinterpret_cast<float4 *>(gradFbase + qpad + ((size_t)k * npad + j0) * rpad);
+        cnt4 = min(UP_ROWS, npad - j0) * rpad / 4;      // <= 4 * UP_THREADS (rpad <= 64)
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (tid + i * UP_THREADS < cnt4) pre[i] = src[tid + i * UP_THREADS];
     }
+    // pass A: U and the step's draw into the tiles
     for (int t = tid; t < UP_ROWS * npr; t += UP_THREADS) {
-        int jj = t % UP_ROWS, l = t / UP_ROWS, j = j0 + jj;
-        double u = 0.0, g = 0.0;
-        double grF = 0.0;
-        if (gradFbase && j < npad && l < rpad) grF = (double)gst[jj * (rpad + 1) + l];
+        const int jj = t % UP_ROWS, l = t / UP_ROWS, j = j0 + jj;
+        double u = 0.0, z = 0.0;
         if (jj < rows && l < r) {
-            size_t e = (size_t)l * n + j;
+            const size_t e = (size_t)l * n + j;
             u = Uk[e];
-            double z = 0.0;
             if (langevin)
                 z = noise_U ? noise_U[(size_t)k * r * n + e]
                             : noise_at(key, GPTB_STREAM_NOISE_U | ((uint64_t)k << 40), step, (uint64_t)e);
-            double gr = have_grad ? gU[e] : 0.0;
-            if (gradFbase) gr = grF;
+        }
+        Us[(size_t)jj * ldt + l] = u;
+        Gs[(size_t)jj * ldt + l] = z;
+    }
+    if (gradFbase) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int t = tid + i * UP_THREADS;
+            if (t < cnt4) {
+                src[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+                const int row = (4 * t) / rpad, col = (4 * t) - row * rpad;
+                float *d = gst + row * (rpad + 1) + col;
+                d[0] = pre[i].x; d[1] = pre[i].y; d[2] = pre[i].z; d[3] = pre[i].w;
+            }
+        }
+        __syncthreads();
+    }
+    // pass B: G = sqrt(epsU)/2 * gradient + draw (:420), or the Euclidean update (:426 / :437); a thread revisits the
+    // tile entries it wrote in pass A
+    for (int t = tid; t < UP_ROWS * npr; t += UP_THREADS) {
+        const int jj = t % UP_ROWS, l = t / UP_ROWS, j = j0 + jj;
+        double g = 0.0;
+        if (jj < rows && l < r) {
+            const size_t e = (size_t)l * n + j;
+            const double z = Gs[(size_t)jj * ldt + l];
+            const double gr = gradFbase ? (double)gst[jj * (rpad + 1) + l] : (have_grad ? gU[e] : 0.0);
             if (stiefel) {
                 g = sqU * gr / 2 + z;                       // :420 argument of proj
                 Gk[e] = g;
             } else {
+                const double u = Us[(size_t)jj * ldt + l];
                 Uk[e] = u + epsU * (gr - n * u) / 2 + sqU * z;  // :426 / :437
             }
         }
-        Us[(size_t)jj * ldt + l] = u;
         Gs[(size_t)jj * ldt + l] = g;
     }
     if (!stiefel) return;
@@ -1096,8 +1117,6 @@ int gptb_update_alloc_noise(gptb_handle *h) {
     return GPTB_OK;
 }
 
-// The update of the dimensions [k0, k0 + kn) (and of w when with_w) on stream s.  The kernels address everything by
-// the global k, so that the Philox streams and hence the chain do not depend on how the dimensions are grouped.
 // The step's production-mode draws for the dimensions [k0, k0 + kn) (and w): they depend on the step counter only, so
 // the one-stream step generates them on a side stream under the forward / backward kernels.
 int gptb_launch_noise_range(gptb_handle *h, uint64_t step, int k0, int kn, bool with_w, cudaStream_t s) {
@@ -1111,13 +1130,14 @@ int gptb_launch_noise_range(gptb_handle *h, uint64_t step, int k0, int kn, bool 
     return GPTB_OK;
 }
 
+// The update of the dimensions [k0, k0 + kn) (and of w when with_w) on stream s.  The kernels address everything by
+// the global k, so that the Philox streams and hence the chain do not depend on how the dimensions are grouped.
 int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
                              const double *noise_U, uint64_t step, int k0, int kn, bool with_w, cudaStream_t s,
                              bool noise_ready) {
     const gptb_config &c = h->cfg;
     const int nb = (c.n + UP_ROWS - 1) / UP_ROWS;
     const bool stiefel = flags & GPTB_FLAG_STIEFEL, langevin = flags & GPTB_FLAG_LANGEVIN;
-    const size_t per_k = (size_t)c.r * c.n;
     const int gy = kn + (with_w ? 1 : 0);
     optin_smem();
     double *small_g = h->small + (size_t)k0 * h->small_stride;
