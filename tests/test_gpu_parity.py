@@ -477,3 +477,41 @@ def test_GPT_SGLDERMw_vs_oracle(prec):
     assert relerr(a[0], b[0]) < 1e-5 and np.array_equal(a[1], b[1])
     for k in range(P["D"]):
         assert np.abs(a[1][:, :, k].T @ a[1][:, :, k] - np.eye(P["r"])).max() < 1e-10
+
+
+@pytest.mark.parametrize("prec", PRECS, ids=IDS)
+def test_rmse_trajectory_powerplant(prec):
+    """North-star criterion "test RMSE trajectories of the SGLD chains within 1 % over the run": the reference's
+    PowerPlant experiment (whitened CCPP data of PPdata_full.h5, length_scale and signal_var of
+    PowerPlantDataExperiment.jl:20-24, the BASELINE config-1 shape n=50, r=10, Q=200, minibatch 500) run by the oracle
+    and by the library with the same draws; per epoch, pred of the epoch's last sample on held-out rows and
+    RMSE = ||ytest - fhat|| / sqrt(Ntest) as in kin40kExperiment.jl:75-87."""
+    pp = load_golden("powerplant.npz")
+    X = np.asfortranarray(pp["Xtrain"].astype(np.float64)); y = pp["ytrain"].astype(np.float64)
+    Ntr, Nte = 2500, 1500
+    Xtr, ytr, Xte, yte = X[:Ntr], y[:Ntr], X[Ntr:Ntr + Nte], y[Ntr:Ntr + Nte]
+    D, n, r, Q, m = 4, 50, 10, 200, 500
+    rng = np.random.default_rng(18)
+    Z = np.asfortranarray(rng.standard_normal((n, D))); b = np.asfortranarray(2 * np.pi * rng.random((n, D)))
+    ls, sig, signal_var = 1.4332, 1.0, 0.2299 ** 2
+    phi_scale = np.sqrt(n / Q ** (1.0 / D))
+    I = o.samplenz(r, D, Q, rng)
+    w0 = rng.standard_normal(Q)
+    U0 = np.asfortranarray(np.stack([o.stiefel_from_gaussian(rng.standard_normal((r, n))) for _ in range(D)], 2))
+    epochs, nb = 8, Ntr // m
+    perms = [rng.permutation(Ntr) for _ in range(epochs)]
+    NW = rng.standard_normal((epochs * nb, Q)); NU = rng.standard_normal((epochs * nb, n, r, D))
+    epsw, epsU = 2e-4, 2e-7
+    phitr = o.feature(Xtr, ls, sig, phi_scale, Z, b); phite = o.feature(Xte, ls, sig, phi_scale, Z, b)
+    ws, Us = o.GPTregression(phitr, ytr, signal_var, I, r, Q, m, epsw, epsU, 0, epochs, w0, U0, perms, NW, NU)
+    ftr = G.feature(Xtr, ls, sig, phi_scale, Z, b); fte = G.feature(Xte, ls, sig, phi_scale, Z, b)
+    gw, gU = G.GPTregression(ftr, ytr, signal_var, I, r, Q, m, epsw, epsU, 0, epochs, 1, precision=prec, w0=w0, U0=U0,
+                             perms=np.stack(perms), noise_w=NW, noise_U=NU)
+    ref_curve, got_curve = [], []
+    for ep in range(epochs):
+        col = (ep + 1) * nb - 1
+        ref_curve.append(np.linalg.norm(yte - o.pred(ws[:, col], Us[..., col], I, phite)) / np.sqrt(Nte))
+        got_curve.append(np.linalg.norm(yte - G.pred(gw[:, col], gU[..., col], I, fte, precision=prec)) / np.sqrt(Nte))
+    ref_curve, got_curve = np.array(ref_curve), np.array(got_curve)
+    assert np.isfinite(ref_curve).all() and ref_curve[-1] < 0.7 * ref_curve[0]        # the chain learns the data (0.60 -> 0.38)
+    assert np.abs(got_curve / ref_curve - 1).max() < (1e-7 if prec == L.PREC_FP64 else 1e-2)
