@@ -361,7 +361,7 @@ def main():
     roofline = {"kernel": {"fwd": "fwd_tc_kernel (K1)", "bwd": "bwd_tc_kernel (K3)"}[dom], "bound": "tensor",
                 "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": (ach / peak_tf) if ach else None,
                 # dram__bytes_read.sum + dram__bytes_write.sum of one K3 launch at this exact shape (ncu --set full,
-                # profiles/r1l_ncu_full_summary_C4_tc3.txt): 87.9 MB read (the E image, once per feature-block group)
+                # profiles/r1n_ncu_full_summary_C4_tc3.txt): 87.9 MB read (the E image, once per feature-block group)
                 # + 3.1 MB written; algorithmic bytes are 84 MB of E image + 2.6 MB of inputs + 1.3 MB of gradient
                 "traffic": 91066624 if (world == 1 and args.workload == "C4" and dom == "bwd") else None,
                 "peak_source": which_peak, "avg_launch_ms": dom_ms,
