@@ -225,7 +225,8 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
     const bool f64 = use_fp64(h, phi_mode);
     const int32_t *rows = rows_dev ? rows_dev + lo : nullptr;
     if (staged_host_batch) {
-        GPTB_TRY(gptb_launch_gather_from(h, Xstage_rm + (size_t)lo * c.D, ystage + lo, lbs, h->mpad, f64 ? h->Xb : nullptr,
+        const int64_t so = h->stage_share ? 0 : lo;   // (a share-only staging buffer starts at this rank's first row)
+        GPTB_TRY(gptb_launch_gather_from(h, Xstage_rm + (size_t)so * c.D, ystage + so, lbs, h->mpad, f64 ? h->Xb : nullptr,
                                          f64 ? nullptr : h->XbF, h->yb));
     } else if (phi_mode) {
         int blocks = (int)std::min<int64_t>((h->mpad + 255) / 256, 1024);
@@ -370,7 +371,8 @@ static int step_pipelined(gptb_handle *h, double signal_var, const int32_t *rows
     GPTB_TRY(refresh_shadows(h));
     const int32_t *rows = rows_dev ? rows_dev + lo : nullptr;
     if (staged_host_batch) {
-        GPTB_TRY(gptb_launch_gather_from(h, Xstage_rm + (size_t)lo * c.D, ystage + lo, lbs, h->mpad, nullptr, h->XbF, h->yb));
+        const int64_t so = h->stage_share ? 0 : lo;
+        GPTB_TRY(gptb_launch_gather_from(h, Xstage_rm + (size_t)so * c.D, ystage + so, lbs, h->mpad, nullptr, h->XbF, h->yb));
     } else {
         GPTB_TRY(gptb_launch_gather(h, rows, 0, lbs, lo));
     }
@@ -1354,14 +1356,23 @@ int gptb_sgld_step_host_submit(gptb_handle *h, double signal_var, const double *
     }
     const int slot = (int)(h->pipe_submitted & 1);
     // the slot's previous occupant (two submissions ago) has been waited for or retired above, so the copy may start now
-    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->pipe_cm[slot], Xb, sizeof(double) * bs * c.D, cudaMemcpyHostToDevice, h->copy_stream));
-    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->pipe_y[slot], yb, sizeof(double) * bs, cudaMemcpyHostToDevice, h->copy_stream));
+    // only this rank's rows [lo, hi) of the global minibatch cross the bus: one strided copy takes them out of the D
+    // columns of the column-major Xb (with 8 ranks the full 5.8 MB batch per rank and step was the e2e bottleneck)
+    const int64_t slo = (int64_t)h->rank * bs / h->nranks, shi = (int64_t)(h->rank + 1) * bs / h->nranks, sbs = shi - slo;
+    if (sbs > 0) {
+        GPTB_CUDA_OK(h, cudaMemcpy2DAsync(h->pipe_cm[slot], sizeof(double) * sbs, Xb + slo, sizeof(double) * bs,
+                                          sizeof(double) * sbs, c.D, cudaMemcpyHostToDevice, h->copy_stream));
+        GPTB_CUDA_OK(h, cudaMemcpyAsync(h->pipe_y[slot], yb + slo, sizeof(double) * sbs, cudaMemcpyHostToDevice, h->copy_stream));
+    }
     GPTB_CUDA_OK(h, cudaEventRecord(h->pipe_staged[slot], h->copy_stream));
     GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->pipe_staged[slot], 0));
-    GPTB_TRY(gptb_launch_transpose(h, h->pipe_cm[slot], bs, h->stage_rm));
+    GPTB_TRY(gptb_launch_transpose(h, h->pipe_cm[slot], sbs, h->stage_rm));
     const double *nw = nullptr, *nU = nullptr;
     GPTB_TRY(stage_noise(h, noise_w, noise_U, &nw, &nU));
-    GPTB_TRY(step_common(h, signal_var, nullptr, bs, N_total, true, h->stage_rm, h->pipe_y[slot], epsw, epsU, flags, nw, nU));
+    h->stage_share = true;
+    const int st_step = step_common(h, signal_var, nullptr, bs, N_total, true, h->stage_rm, h->pipe_y[slot], epsw, epsU, flags, nw, nU);
+    h->stage_share = false;
+    GPTB_TRY(st_step);
     // the step's read-backs follow its last group update on the tail stream; the main stream is free for the next step
     cudaStream_t ts = nullptr;
     GPTB_TRY(pipe_tail_begin(h, &ts));

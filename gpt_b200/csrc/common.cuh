@@ -85,6 +85,7 @@ struct gptb_handle {
     double *store_w = nullptr, *store_U = nullptr;   // device-side chain stores of gptb_sgld_run
     double *stage_cm = nullptr, *stage_rm = nullptr, *stage_y = nullptr;  // host-minibatch staging
     int64_t stage_cap = 0;
+    bool stage_share = false;          // the staged host minibatch holds this rank's rows only (gptb_sgld_step_host_submit)
     // pipelined host steps (gptb_sgld_step_host_submit / _wait): two staging slots filled on a copy stream
     cudaStream_t copy_stream = nullptr;
     double *pipe_cm[2] = {nullptr, nullptr}, *pipe_y[2] = {nullptr, nullptr};
