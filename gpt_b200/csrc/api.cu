@@ -1294,12 +1294,20 @@ int gptb_sgld_step_host(gptb_handle *h, double signal_var, const double *Xb, con
         GPTB_TRY(dev_alloc(h, &h->stage_y, (size_t)bs));
         h->stage_cap = bs;
     }
-    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->stage_cm, Xb, sizeof(double) * bs * c.D, cudaMemcpyHostToDevice, h->stream));
-    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->stage_y, yb, sizeof(double) * bs, cudaMemcpyHostToDevice, h->stream));
-    GPTB_TRY(gptb_launch_transpose(h, h->stage_cm, bs, h->stage_rm));
+    // this rank's rows [lo, hi) of the global minibatch only (see gptb_sgld_step_host_submit)
+    const int64_t slo = (int64_t)h->rank * bs / h->nranks, shi = (int64_t)(h->rank + 1) * bs / h->nranks, sbs = shi - slo;
+    if (sbs > 0) {
+        GPTB_CUDA_OK(h, cudaMemcpy2DAsync(h->stage_cm, sizeof(double) * sbs, Xb + slo, sizeof(double) * bs, sizeof(double) * sbs,
+                                          c.D, cudaMemcpyHostToDevice, h->stream));
+        GPTB_CUDA_OK(h, cudaMemcpyAsync(h->stage_y, yb + slo, sizeof(double) * sbs, cudaMemcpyHostToDevice, h->stream));
+    }
+    GPTB_TRY(gptb_launch_transpose(h, h->stage_cm, sbs, h->stage_rm));
     const double *nw = nullptr, *nU = nullptr;
     GPTB_TRY(stage_noise(h, noise_w, noise_U, &nw, &nU));
-    GPTB_TRY(step_common(h, signal_var, nullptr, bs, N_total, true, h->stage_rm, h->stage_y, epsw, epsU, flags, nw, nU));
+    h->stage_share = true;
+    const int st_step = step_common(h, signal_var, nullptr, bs, N_total, true, h->stage_rm, h->stage_y, epsw, epsU, flags, nw, nU);
+    h->stage_share = false;
+    GPTB_TRY(st_step);
     GPTB_TRY(pipe_join(h));
     if (w_out) GPTB_CUDA_OK(h, cudaMemcpyAsync(w_out, h->w, sizeof(double) * c.Q, cudaMemcpyDeviceToHost, h->stream));
     if (flags & GPTB_FLAG_STIEFEL) return check_nan(h);

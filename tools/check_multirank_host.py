@@ -52,6 +52,8 @@ def main():
             m.sgld_step_host_submit(P["signal_var"], Xb[t], yb[t], P["N"], epsw, epsU, w_out=wo[t])
             m.sgld_step_host_wait()
         m.sgld_step_host_wait()
+        for t in range(2):                                       # and the blocking entry
+            m.sgld_step_host(P["signal_var"], Xb[t], yb[t], P["N"], epsw, epsU, w_out=wo[t])
         a = m.get_params()
         m.sgld_advance(P["signal_var"], 700, epsw, epsU, 5)      # resident loop, ragged shares
         m.synchronize()
