@@ -144,7 +144,8 @@ int gptb_geod(int32_t device, int32_t n, int32_t r, const double *U, const doubl
 int gptb_sgld_step(gptb_handle *h, double signal_var, const int64_t *idx, int64_t start, int64_t bs,
                    double epsw, double epsU, int32_t flags, const double *noise_w, const double *noise_U);
 /* Same loop body with the minibatch passed from the host: Xb[bs,D], yb[bs]; N_total is the N of :393.
- * w_out[Q] (optional) receives the updated w.  This is the end-to-end entry bench.py times. */
+ * w_out[Q] (optional) receives the updated w.  With several ranks every rank passes the same GLOBAL minibatch
+ * (same composition as on one GPU) and copies only its own rows [rank*bs/nranks, (rank+1)*bs/nranks) to its device. */
 int gptb_sgld_step_host(gptb_handle *h, double signal_var, const double *Xb, const double *yb, int64_t bs,
                         int64_t N_total, double epsw, double epsU, int32_t flags, const double *noise_w,
                         const double *noise_U, double *w_out);
@@ -154,7 +155,8 @@ int gptb_sgld_step_host(gptb_handle *h, double signal_var, const double *Xb, con
  * returns without waiting; Xb, yb and w_out must stay valid until the matching _wait.  _wait blocks until the
  * OLDEST submitted step has finished: its w_out is then valid and its status (GPTB_OK / GPTB_GEODESIC_NAN) is
  * returned.  At most two steps are in flight; a third _submit first waits for the oldest (its status is then
- * reported by the next _wait).  Returns GPTB_ERR_STATE from _wait when nothing is in flight. */
+ * reported by the next _wait).  Returns GPTB_ERR_STATE from _wait when nothing is in flight.  This pair is the
+ * end-to-end entry bench.py times. */
 int gptb_sgld_step_host_submit(gptb_handle *h, double signal_var, const double *Xb, const double *yb, int64_t bs,
                                int64_t N_total, double epsw, double epsU, int32_t flags, const double *noise_w,
                                const double *noise_U, double *w_out);
