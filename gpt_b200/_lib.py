@@ -25,6 +25,8 @@ OK, ERR_ARG, ERR_SHAPE, ERR_STATE, ERR_CUDA, ERR_NCCL, ERR_NOMEM, GEODESIC_NAN, 
 PREC_FP64, PREC_TC3, PREC_TC1 = 0, 1, 2
 FEAT_COS, FEAT_SINCOS = 0, 1
 FLAG_LANGEVIN, FLAG_STIEFEL, FLAG_FIX_U = 1, 2, 4
+ALG_AUTO, ALG_DIRECT, ALG_NODES = 0, 1, 2
+OPT_PIPE_GROUPS, OPT_PIPE_RESERVE, OPT_ALGORITHM, OPT_NODE_ORDER, OPT_NODE_THETA = range(5)
 PHASES = ("gather", "fwd", "contract", "bwd", "reduce", "update")
 
 H = C.c_void_p
@@ -74,6 +76,7 @@ PROTOTYPES = {
                               C.c_uint64, c_double_p, c_int64_p, c_double_p, c_double_p]),
     "gptb_nt_last_run_stats": (C.c_int, [H, c_double_p, c_int64_p, c_int64_p]),
     "gptb_set_profiling": (C.c_int, [H, C.c_int32]),
+    "gptb_set_option": (C.c_int, [H, C.c_int32, C.c_double]),
     "gptb_get_phase_ms": (C.c_int, [H, c_float_p, c_int64_p, C.c_int32]),
 }
 

@@ -193,17 +193,25 @@ int forward_contract(gptb_handle *h, bool phi_mode, const int32_t *rows, const d
         GPTB_TRY(gptb_launch_fwd_tc(h, h->XbF, Uimg, bs, h->mpad, (float *)h->T));
     }
     if (pt) pt->done(GPTB_PHASE_FWD);
-    if (!f64 && want_grad && !h->tc_emax_valid) {
-        // first step after new parameters: one measuring pass establishes the fp16 scale of the E image
-        GPTB_TRY(gptb_launch_contract(h, h->T, w_dev, h->yb, bs, h->mpad, escale, true, h->fhat, h->grad, nullptr,
-                                      h->Eimg, false));
-        if (h->f32_grad) GPTB_CUDA_OK(h, cudaMemsetAsync(h->gradFbase, 0, sizeof(float) * h->gradF_qpad, h->stream));
-        else GPTB_CUDA_OK(h, cudaMemsetAsync(h->grad, 0, sizeof(double) * h->cfg.Q, h->stream));
+    // E-image scale: derived from the previous step's max|E| (scale 1 right after new parameters), then checked
+    // against this step's own max|E|; a minibatch whose residuals jumped out of the fp16 window triggers one
+    // conditional re-run of K2 that only rewrites the image (tc_path.cu: check_escale_kernel)
+    const bool img = !f64 && want_grad && !h->k2_Erow;
+    if (img) {
+        if (!h->tc_emax_valid) GPTB_CUDA_OK(h, cudaMemsetAsync(h->tc_state, 0, sizeof(float), h->stream));
         h->tc_emax_valid = true;
+        GPTB_TRY(gptb_tc_update_escale(h));
     }
-    if (!f64 && want_grad) GPTB_TRY(gptb_tc_update_escale(h));
     GPTB_TRY(gptb_launch_contract(h, h->T, w_dev, h->yb, bs, h->mpad, escale, want_grad, h->fhat, h->grad,
                                   f64 ? h->E : nullptr, f64 ? nullptr : h->Eimg, f64));
+    if (img) {
+        GPTB_TRY(gptb_tc_check_escale(h));
+        h->k2_redo = true;
+        const int st = gptb_launch_contract(h, h->T, w_dev, h->yb, bs, h->mpad, escale, want_grad, h->fhat, h->grad, nullptr,
+                                            h->Eimg, false);
+        h->k2_redo = false;
+        GPTB_TRY(st);
+    }
     if (pt) pt->done(GPTB_PHASE_CONTRACT);
     return GPTB_OK;
 }
@@ -271,17 +279,10 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
 // Results do not depend on G: every kernel addresses parameters, gradients and Philox streams by the global k.
 // With several ranks each group's gradient slice is all-reduced on one dedicated NCCL stream.
 // ------------------------------------------------------------------------------------------------------------
-// G = 2 unless GPTB_PIPE_GROUPS says otherwise (0 or 1 switches the pipeline off; setting it also forces the
-// pipeline on for the small and multi-rank steps it is normally not used for — that is how the tests drive it).
+// G = 2 unless gptb_set_option(GPTB_OPT_PIPE_GROUPS) says otherwise (0 or 1 switches the pipeline off; setting it also
+// forces the pipeline on for the small and multi-rank steps it is normally not used for — that is how the tests drive it).
 static int pipe_groups_for(gptb_handle *h) {
-    if (h->pipe_groups < 0) {
-        int g = 2;
-        if (const char *e = getenv("GPTB_PIPE_GROUPS")) {
-            g = atoi(e);
-            h->pipe_forced = true;
-        }
-        h->pipe_groups = std::max(0, std::min(g, (int)gptb_handle::PIPE_MAX));
-    }
+    if (h->pipe_groups < 0) h->pipe_groups = 2;
     return h->pipe_groups;
 }
 
@@ -387,8 +388,7 @@ static int step_pipelined(gptb_handle *h, double signal_var, const int32_t *rows
         ~ReserveGuard() { h->sm_reserve = 0; }
     } guard{h};
     {
-        int rsv = (c.D + G - 1) / G;
-        if (const char *e = getenv("GPTB_PIPE_RESERVE")) rsv = atoi(e);
+        int rsv = h->pipe_reserve >= 0 ? h->pipe_reserve : (c.D + G - 1) / G;
         h->sm_reserve = std::max(0, std::min(rsv, h->sm_count / 4));
     }
     // forward, group by group: K1_g needs the previous step's update of group g only
@@ -488,8 +488,13 @@ int stage_noise(gptb_handle *h, const double *noise_w, const double *noise_U, co
 
 int check_nan(gptb_handle *h) {
     GPTB_TRY(pipe_join(h));
-    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->nan_flag_host, h->nan_flag, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->nan_flag_host, h->nan_flag, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
     GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    if (h->nan_flag_host[3]) {   // raised by apply_perm_kernel (gptb_sgld_run with host permutations)
+        GPTB_CUDA_OK(h, cudaMemsetAsync(h->nan_flag + 3, 0, sizeof(int32_t), h->stream));
+        gptb_set_error(h, "permutation entry outside 0..N-1");
+        return GPTB_ERR_ARG;
+    }
     if (*h->nan_flag_host) {
         // GPT_SGLD.jl:25
         gptb_set_error(h, "Get NaN when moving along Geodesic. Try smaller epsU");
@@ -1433,7 +1438,10 @@ int gptb_sgld_run(gptb_handle *h, double signal_var, int64_t m, double epsw, dou
     }
     int64_t *perm_dev = nullptr;
     if (perms) GPTB_CUDA_OK(h, cudaMalloc((void **)&perm_dev, sizeof(int64_t) * N));
-    int st = GPTB_OK;
+    // every call starts from the caller's data order, as each GPTregression call does (phi=phi[:,:,perm] rebinds a
+    // local, GPT_SGLD.jl:374); gptb_sgld_advance is the entry that continues a chain's epochs
+    int st = gptb_reset_order(h);
+    h->batch_cursor = 0;
     uint64_t step = 0;
     for (int epoch = 1; st == GPTB_OK && epoch <= burnin + maxepoch; ++epoch) {
         if (perms) {
@@ -1464,7 +1472,7 @@ int gptb_sgld_run(gptb_handle *h, double signal_var, int64_t m, double epsw, dou
         }
         // the reference tests for the NaN abort after every geodesic (:422); the device flag is sticky and
         // freezes the parameters, so looking at it once per epoch returns the same all-zero result
-        if (st == GPTB_OK && (flags & GPTB_FLAG_STIEFEL)) st = check_nan(h);
+        if (st == GPTB_OK && ((flags & GPTB_FLAG_STIEFEL) || perms)) st = check_nan(h);
     }
     if (pipe_join(h) != GPTB_OK && st == GPTB_OK) st = GPTB_ERR_CUDA;
     if (st == GPTB_OK) {
@@ -1508,6 +1516,39 @@ int gptb_sgld_advance(gptb_handle *h, double signal_var, int64_t m, double epsw,
     }
     GPTB_TRY(pipe_join(h));   // work queued on the caller's stream after this call sees the final parameters
     return GPTB_OK;
+}
+
+int gptb_set_option(gptb_handle *h, int32_t option, double value) {
+    if (!h) return GPTB_ERR_ARG;
+    cudaSetDevice(h->device);
+    GPTB_TRY(pipe_join(h));
+    switch (option) {
+        case GPTB_OPT_PIPE_GROUPS:
+            h->pipe_groups = std::max(0, std::min((int)value, (int)gptb_handle::PIPE_MAX));
+            h->pipe_forced = true;
+            return GPTB_OK;
+        case GPTB_OPT_PIPE_RESERVE:
+            h->pipe_reserve = (int)value;
+            return GPTB_OK;
+        case GPTB_OPT_ALGORITHM:
+            if (value != GPTB_ALG_AUTO && value != GPTB_ALG_DIRECT && value != GPTB_ALG_NODES) break;
+            h->algorithm = (int)value;
+            return GPTB_OK;
+        case GPTB_OPT_NODE_ORDER:
+            if (value < 4 || value > 16) break;
+            h->node_P = (int)value;
+            h->grid_valid = false;
+            return GPTB_OK;
+        case GPTB_OPT_NODE_THETA:
+            if (!(value > 0.0) || value > 8.0) break;
+            h->node_theta = value;
+            h->grid_valid = false;
+            return GPTB_OK;
+        default:
+            break;
+    }
+    gptb_set_error(h, "gptb_set_option: unknown option %d or value %g out of range", option, value);
+    return GPTB_ERR_ARG;
 }
 
 int gptb_set_profiling(gptb_handle *h, int32_t on) {

@@ -49,9 +49,16 @@ __global__ void perm_keys_kernel(uint64_t *keys, int64_t N, uint64_t key, uint64
 }
 
 // order_out[i] = order_in[perm[i]]  — the cumulative application of :374
-__global__ void apply_perm_kernel(const int32_t *order_in, const int64_t *perm, int64_t N, int32_t *order_out) {
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x)
-        order_out[i] = order_in[perm[i]];
+// (entries outside 0..N-1 raise *bad and read row 0: a bad host permutation must not become an out-of-bounds read)
+__global__ void apply_perm_kernel(const int32_t *order_in, const int64_t *perm, int64_t N, int32_t *order_out, int32_t *bad) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t v = perm[i];
+        if (v < 0 || v >= N) {
+            *bad = 1;
+            v = 0;
+        }
+        order_out[i] = order_in[v];
+    }
 }
 
 }  // namespace
@@ -121,7 +128,7 @@ int gptb_shuffle_order(gptb_handle *h, uint64_t epoch) {
 // Host-supplied permutation (0-based, N entries, already on the device as int64).
 int gptb_apply_perm(gptb_handle *h, const int64_t *perm_dev) {
     if (!h->order_tmp) GPTB_CUDA_OK(h, cudaMalloc(&h->order_tmp, sizeof(int32_t) * h->N));
-    apply_perm_kernel<<<grid_for(h, h->N, 256), 256, 0, h->stream>>>(h->order, perm_dev, h->N, h->order_tmp);
+    apply_perm_kernel<<<grid_for(h, h->N, 256), 256, 0, h->stream>>>(h->order, perm_dev, h->N, h->order_tmp, h->nan_flag + 3);
     std::swap(h->order, h->order_tmp);
     h->launches++;
     GPTB_CUDA_OK(h, cudaGetLastError());

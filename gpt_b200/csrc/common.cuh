@@ -114,6 +114,8 @@ struct gptb_handle {
     float *tc_state = nullptr;         // [0] max|E| of the running step, [1] escale (2^k), [2] 1/escale,
                                        // [3] uscale (2^k applied to U in Uimg), [4] 1/uscale
     bool tc_emax_valid = false;
+    bool k2_redo = false;              // set around the conditional second K2 launch (E-image scale guard, api.cu)
+    float *k2_Erow = nullptr;          // when set, K2 writes plain FP32 E [D][mpad][rpad] instead of the operand image
 
     // update scratch
     double *G = nullptr;               // [D][r][n]
@@ -129,7 +131,13 @@ struct gptb_handle {
     // the main stream goes on with the next group's back-projection / the next step's forward pass
     static constexpr int PIPE_MAX = 4;
     int pipe_groups = -1;              // -1: not decided yet; 0/1: off
-    bool pipe_forced = false;          // GPTB_PIPE_GROUPS set: use the pipeline for every eligible step
+    bool pipe_forced = false;          // GPTB_OPT_PIPE_GROUPS set: use the pipeline for every eligible step
+    int pipe_reserve = -1;             // GPTB_OPT_PIPE_RESERVE: SMs left to the concurrent update (-1 = one per dimension of a group)
+    // node-grid algorithm (nodes.cu)
+    int algorithm = GPTB_ALG_AUTO;
+    int node_P = 12;                   // Chebyshev nodes per cell
+    double node_theta = 2.0;           // cell half-width times the largest |frequency| of the dimension
+    bool grid_valid = false;
     cudaStream_t side[PIPE_MAX] = {nullptr, nullptr, nullptr, nullptr};
     cudaStream_t tail_stream = nullptr, ar_stream = nullptr;
     cudaEvent_t evG[PIPE_MAX] = {}, evU[PIPE_MAX] = {}, evR[PIPE_MAX] = {};
@@ -257,6 +265,7 @@ int gptb_shuffle_order(gptb_handle *h, uint64_t epoch);
 int gptb_tc_pack_params(gptb_handle *h);
 int gptb_tc_pack_U(gptb_handle *h, const double *U, void *Uimg);
 int gptb_tc_update_escale(gptb_handle *h);
+int gptb_tc_check_escale(gptb_handle *h);
 int gptb_launch_fwd_tc(gptb_handle *h, const float *XbF, const void *Uimg, int64_t bs, int64_t mpad, float *T);
 int gptb_launch_fwd_tc_cols(gptb_handle *h, const float *XbF, const void *Uimg, const float *uscale, int64_t bs,
                             int64_t mpad, float *T, int ncols, int NC);

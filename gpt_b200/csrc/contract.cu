@@ -45,6 +45,8 @@ struct ContractParams {
     int64_t bs, mpad;
     double escale;
     int D, r, rpad, Q, want_grad;
+    const int *redo_flag;    // see contract_tc.cu: a conditional second launch that only rewrites the E image
+    int redo;
 };
 
 template <typename real, int DT>
@@ -54,6 +56,7 @@ __global__ void __launch_bounds__(CT_THREADS) contract_kernel(const ContractPara
     constexpr int DU = DT > 0 ? DT : 16;
     const int r = p.r, rpad = p.rpad, Q = p.Q, DR = D * r;
     const int tid = threadIdx.x, row = tid & 31, s = tid >> 5;
+    if (p.redo && *p.redo_flag == 0) return;
     const int64_t i = (int64_t)blockIdx.x * RB + row;
     const bool live = i < p.bs;
     const real *T = reinterpret_cast<const real *>(p.T);
@@ -92,14 +95,14 @@ __global__ void __launch_bounds__(CT_THREADS) contract_kernel(const ContractPara
     f = 0;
 #pragma unroll
     for (int t = 0; t < NS; ++t) f += Fs[t * RB + row];
-    if (s == 0 && live) p.fhat[i] = (double)f;
+    if (s == 0 && live && !p.redo) p.fhat[i] = (double)f;
     if (!p.want_grad) return;
     const real e = live ? (real)(p.escale * (p.yb[i] - (double)f)) : (real)0;
     if (s == 0) Es[row] = e;
     __syncthreads();
 
     // ---- gradw: sum over the CTA's rows of e_i V[q,i]
-    for (int q = tid; q < Q; q += CT_THREADS) {
+    for (int q = tid; q < Q && !p.redo; q += CT_THREADS) {
         double g = 0.0;
 #pragma unroll 8
         for (int ii = 0; ii < RB; ++ii) g += (double)(Es[ii] * Vs[(size_t)q * VS + ii]);
@@ -171,7 +174,7 @@ __global__ void __launch_bounds__(CT_THREADS) contract_kernel(const ContractPara
     if (p.Eimg != nullptr) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-        if (row == 0 && mx > 0.f) atomicMax(reinterpret_cast<int *>(p.emax_out), __float_as_int(mx));
+        if (row == 0 && mx > 0.f && !p.redo) atomicMax(reinterpret_cast<int *>(p.emax_out), __float_as_int(mx));
     }
 }
 
@@ -236,5 +239,7 @@ int gptb_launch_contract(gptb_handle *h, const void *T, const void *w, const dou
     p.escale = escale;
     p.D = h->cfg.D; p.r = h->cfg.r; p.rpad = h->rpad; p.Q = h->cfg.Q;
     p.want_grad = want_grad ? 1 : 0;
+    p.redo = (!real_is_double && h->k2_redo) ? 1 : 0;
+    p.redo_flag = h->nan_flag + 2;
     return real_is_double ? launch_typed<double>(h, p) : launch_typed<float>(h, p);
 }

@@ -57,6 +57,10 @@ struct ContractTcParams {
     double escale;
     int DP, r, rpad, Q, want_grad;
     int n_lists;             // entries of `lists` (multiple of 4)
+    const int *redo_flag;    // redo != 0: the launch only rewrites the E image with a corrected fp16 scale, and only if
+    int redo;                //   *redo_flag says the first pass left the safe range (tc_path.cu: check_escale_kernel)
+    float *Erow;             // optional plain FP32 copy of E, [D][mpad][rpad] (row-major per sample: the node-grid
+                             //   spreading kernel reads one 4*rpad-byte line per row), instead of the operand image
 };
 
 __device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
@@ -71,6 +75,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     constexpr int DP4 = (DT + 3) / 4;
     const int r = p.r, rpad = p.rpad, Q = p.Q, DR = D * r;
     const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    if (p.redo && *p.redo_flag == 0) return;                     // (uniform across the grid)
     const int64_t i0 = (int64_t)blockIdx.x * CRB + 2 * lane;     // this lane's rows: i0, i0 + 1
     const bool live0 = i0 < p.bs, live1 = i0 + 1 < p.bs;
 
@@ -149,7 +154,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     f = Fs[lane];
 #pragma unroll
     for (int t = 1; t < CNW; ++t) f = add2(f, Fs[t * 32 + lane]);
-    if (wp == 0) {
+    if (wp == 0 && !p.redo) {
         if (live0) p.fhat[i0] = (double)f.x;
         if (live1) p.fhat[i0 + 1] = (double)f.y;
     }
@@ -188,7 +193,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
 #pragma unroll
         for (int off = NB; off < 32; off <<= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], off);
         const int q = qb + CNW * (lane % NB);
-        if (lane < NB && q < Q) {
+        if (lane < NB && q < Q && !p.redo) {
             if (p.gradwF) atomicAdd(&p.gradwF[(size_t)(blockIdx.x % GPTB_GW_SLOTS) * p.gw_stride + q], v[0]);
             else atomicAdd(&p.gradw[q], (double)v[0]);
         }
@@ -272,6 +277,14 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
             lo[j / 2] = *reinterpret_cast<const uint32_t *>(&l0);
             lo[LU / 2 + j / 2] = *reinterpret_cast<const uint32_t *>(&l1);
         }
+        if (p.Erow) {   // node-grid path: E itself, [k][i][rpad]
+            mx = fmaxf(mx, fmaxf(fmaxf(fabsf(out[0].x), fabsf(out[0].y)), fmaxf(fabsf(out[1].x), fabsf(out[1].y))));
+            mx = fmaxf(mx, fmaxf(fmaxf(fabsf(out[2].x), fabsf(out[2].y)), fmaxf(fabsf(out[3].x), fabsf(out[3].y))));
+            float *er = p.Erow + ((size_t)k * p.mpad + i0) * rpad + lu * LU;
+            *reinterpret_cast<float4 *>(er) = make_float4(out[0].x, out[1].x, out[2].x, out[3].x);
+            *reinterpret_cast<float4 *>(er + rpad) = make_float4(out[0].y, out[1].y, out[2].y, out[3].y);
+            continue;
+        }
         const int lb = (lu * LU) >> 3, lin = (lu * LU) & 7;
         __half *base = p.Eimg + gptb_eimg_offset(k, i0, p.mpad, rpad) + lin;
         uint2 *dh = reinterpret_cast<uint2 *>(base + (size_t)lb * 64);
@@ -283,7 +296,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (lane == 0 && mx > 0.f) atomicMax(reinterpret_cast<int *>(p.emax_out), __float_as_int(mx));
+    if (lane == 0 && mx > 0.f && !p.redo) atomicMax(reinterpret_cast<int *>(p.emax_out), __float_as_int(mx));
 }
 
 }  // namespace
@@ -363,6 +376,9 @@ int gptb_launch_contract_tc(gptb_handle *h, const float *T, const double *w, con
     p.DP = (c.D + 3) & ~3; p.r = c.r; p.rpad = h->rpad; p.Q = c.Q;
     p.want_grad = want_grad ? 1 : 0;
     p.n_lists = h->ct_nlists;
+    p.redo = h->k2_redo ? 1 : 0;
+    p.redo_flag = h->nan_flag + 2;
+    p.Erow = want_grad ? h->k2_Erow : nullptr;
     const int64_t mext = (bs + 127) / 128 * 128;  // rows beyond bs inside the last 128-tile are dead (zeros)
     dim3 grid((unsigned)(mext / CRB));
 #define GPTB_CONTRACT_CASE(DT)                                                                              \

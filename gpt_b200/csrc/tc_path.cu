@@ -619,6 +619,21 @@ __global__ void set_scale_kernel(float *state_max, float *state_scale, int reset
     if (reset_max) *state_max = 0.f;
 }
 
+// E-image scale guard.  The image is written with the scale derived from the PREVIOUS step's max|E| (128x headroom to
+// fp16 overflow, 128x down to where the lo parts leave fp16's normal range).  After K2 this kernel looks at the max|E|
+// the step actually produced: outside [2, 32768) after scaling it installs the exact scale and raises the flag that
+// makes the (otherwise empty) second K2 launch rewrite the image.
+__global__ void check_escale_kernel(float *state /*[0] max|E|, [1] scale, [2] 1/scale*/, int *flag) {
+    const float mx = state[0], M = mx * state[1];
+    const int redo = (mx > 0.f && isfinite(mx) && !(M >= 2.f && M < 32768.f)) ? 1 : 0;
+    if (redo) {
+        const float s = pow2_scale_for(mx);
+        state[1] = s;
+        state[2] = 1.f / s;
+    }
+    *flag = redo;
+}
+
 __global__ void pack_U_kernel(const double *__restrict__ U /*[D][r][n]*/, int D, int n, int r, int npad, int rpad,
                               const float *__restrict__ scale, __half *__restrict__ Uimg) {
     const float sc = scale[0];
@@ -677,6 +692,13 @@ int gptb_tc_pack_U(gptb_handle *h, const double *U, void *Uimg) { return gptb_tc
 // Turn the max|E| measured by the previous contraction into this step's power-of-two image scale.
 int gptb_tc_update_escale(gptb_handle *h) {
     set_scale_kernel<<<1, 1, 0, h->stream>>>(h->tc_state + 0, h->tc_state + 1, 1);
+    h->launches++;
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    return GPTB_OK;
+}
+
+int gptb_tc_check_escale(gptb_handle *h) {
+    check_escale_kernel<<<1, 1, 0, h->stream>>>(h->tc_state + 0, h->nan_flag + 2);
     h->launches++;
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;

@@ -28,7 +28,7 @@ import numpy as np
 from . import _lib as L
 
 __all__ = ["feature", "feature2", "samplenz", "pred", "pred_samples", "GPTregression", "proj", "geod",
-           "datawhitening", "RFFFeatures", "Model", "GptbError", "GeodesicNaN"]
+           "datawhitening", "RFFFeatures", "Model", "GptbError", "GeodesicNaN", "shard_range"]
 
 
 class GptbError(RuntimeError):
@@ -347,6 +347,10 @@ class Model:
     def synchronize(self):
         _check(self.lib.gptb_synchronize(self.h), self.h)
 
+    def set_option(self, option: int, value: float):
+        """gptb_set_option: L.OPT_* (algorithm selection, node-grid order, pipeline knobs)."""
+        _check(self.lib.gptb_set_option(self.h, int(option), float(value)), self.h)
+
     def set_profiling(self, on: bool):
         _check(self.lib.gptb_set_profiling(self.h, int(on)), self.h)
 
@@ -363,7 +367,13 @@ def comm_unique_id() -> bytes:
     return buf.raw
 
 
-def _model_for(phi, r, Q, I, precision=None, seed=0) -> Model:
+def shard_range(rank: int, nranks: int, bs: int):
+    """Rows [lo, hi) of a global minibatch (or test set) that rank `rank` of `nranks` owns — the split libgptb200
+    applies internally (compute_grad in csrc/api.cu; GPT_SGLD_p.jl:70-108 splits the batch rows over workers)."""
+    return rank * bs // nranks, (rank + 1) * bs // nranks
+
+
+def _model_for(phi, r, Q, I, precision=None, seed=0, options=None) -> Model:
     if isinstance(phi, RFFFeatures):
         n, D, _ = phi.shape
         mdl = Model(D, n, r, Q, precision=precision, feature_kind=phi.kind, seed=seed)
@@ -372,40 +382,43 @@ def _model_for(phi, r, Q, I, precision=None, seed=0) -> Model:
         n, D, _ = phi.shape
         mdl = Model(D, n, r, Q, precision=precision, seed=seed)
     mdl.set_index(I)
+    for k, v in (options or {}).items():
+        mdl.set_option(k, v)
     return mdl
 
 
-def pred(w, U, I, phitest, precision: Optional[int] = None):
+def pred(w, U, I, phitest, precision: Optional[int] = None, options=None):
     """GPT_SGLD.jl:233-243.  phitest: RFFFeatures (lazy) or a dense n x D x Nt array."""
     U = np.asarray(U)
     w = np.ravel(w)
-    with _model_for(phitest, U.shape[1], w.size, I, precision) as mdl:
+    with _model_for(phitest, U.shape[1], w.size, I, precision, options=options) as mdl:
         if isinstance(phitest, RFFFeatures):
             return mdl.pred(w, U, phitest.X)
         return mdl.pred_phi(w, U, phitest)
 
 
 def pred_samples(w_store, U_store, I, phitest: RFFFeatures, cols: Optional[Sequence[int]] = None,
-                 per_sample=False, precision: Optional[int] = None):
+                 per_sample=False, precision: Optional[int] = None, options=None):
     """kin40kExperiment.jl:75-87 / GPT_SGLD_p.jl:124-132: mean over stored samples of pred(w_s,U_s,I,phitest)."""
     if cols is not None:
         w_store = w_store[:, list(cols)]
         U_store = U_store[:, :, :, list(cols)]
-    with _model_for(phitest, U_store.shape[1], w_store.shape[0], I, precision) as mdl:
+    with _model_for(phitest, U_store.shape[1], w_store.shape[0], I, precision, options=options) as mdl:
         return mdl.pred_samples(np.asfortranarray(w_store), np.asfortranarray(U_store), phitest.X, per_sample)
 
 
 def GPTregression(phi, y, signal_var, I, r, Q, m, epsw, epsU, burnin, maxepoch, param_seed, langevin=True,
                   stiefel=True, *, precision: Optional[int] = None, w0=None, U0=None, perms=None, noise_w=None,
-                  noise_U=None):
+                  noise_U=None, options=None):
     """GPT_SGLD.jl:345-448.  Returns (w_store[Q,T], U_store[n,r,D,T]), T = maxepoch*ceil(N/m); all zeros (after
     printing the reference's warning) if the geodesic produced NaN.
 
     Keyword-only extras (not in the reference): precision; w0/U0 to start from given parameters instead of the
-    param_seed draw; perms / noise_w / noise_U to inject the random draws (parity tests)."""
+    param_seed draw; perms / noise_w / noise_U to inject the random draws (parity tests); options = {L.OPT_*: value}
+    passed to gptb_set_option."""
     y = np.ravel(np.asarray(y, dtype=np.float64))
     N = y.size
-    with _model_for(phi, r, Q, I, precision, seed=int(param_seed)) as mdl:
+    with _model_for(phi, r, Q, I, precision, seed=int(param_seed), options=options) as mdl:
         if isinstance(phi, RFFFeatures):
             mdl.set_train(phi.X, y)
         else:

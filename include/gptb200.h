@@ -139,8 +139,9 @@ int gptb_geod(int32_t device, int32_t n, int32_t r, const double *U, const doubl
 /* ---- sampler ------------------------------------------------------------------------------- */
 /* One loop body of GPTregression (GPT_SGLD.jl:378-439) on the resident training set.
  * noise_w[Q], noise_U[n,r,D]: the randn draws of :412/:420 supplied by the caller (test mode);
- * NULL = draw from Philox(seed, step).  Returns GPTB_GEODESIC_NAN if the geodesic failed (params
- * are left untouched in that case). */
+ * NULL = draw from Philox(seed, step).  Returns GPTB_GEODESIC_NAN if the geodesic failed: the factors are
+ * frozen from then on (the flag is sticky; every later update is skipped), w has taken this step's update —
+ * the reference likewise updates w (:412) before it tests the geodesic (:422) and then discards the chain. */
 int gptb_sgld_step(gptb_handle *h, double signal_var, const int64_t *idx, int64_t start, int64_t bs,
                    double epsw, double epsU, int32_t flags, const double *noise_w, const double *noise_U);
 /* Same loop body with the minibatch passed from the host: Xb[bs,D], yb[bs]; N_total is the N of :393.
@@ -235,6 +236,21 @@ enum gptb_phase {
     GPTB_PHASE_COUNT = 6
 };
 int gptb_set_profiling(gptb_handle *h, int32_t on);
+
+/* ---- options ---------------------------------------------------------------------------------- */
+enum gptb_algorithm {
+    GPTB_ALG_AUTO = 0,    /* node grid when it pays (many more minibatch rows than nodes and a known input domain) */
+    GPTB_ALG_DIRECT = 1,  /* features of every minibatch row generated on the fly (K1 / K3 over the rows)          */
+    GPTB_ALG_NODES = 2    /* node grid wherever it is applicable                                                 */
+};
+enum gptb_option {
+    GPTB_OPT_PIPE_GROUPS = 0,   /* dimension groups of the pipelined step (0/1 = off); also forces it on for small steps */
+    GPTB_OPT_PIPE_RESERVE = 1,  /* SMs the persistent kernels leave to the concurrent group update                        */
+    GPTB_OPT_ALGORITHM = 2,     /* enum gptb_algorithm                                                                    */
+    GPTB_OPT_NODE_ORDER = 3,    /* Chebyshev nodes per cell of the node grid (4..16, default 12)                          */
+    GPTB_OPT_NODE_THETA = 4     /* cell half-width x max |Zt| of the dimension (default 2)                                */
+};
+int gptb_set_option(gptb_handle *h, int32_t option, double value);
 int gptb_get_phase_ms(gptb_handle *h, float *ms_out /*GPTB_PHASE_COUNT*/, int64_t *launches_out, int32_t reset);
 
 #ifdef __cplusplus

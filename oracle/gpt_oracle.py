@@ -222,33 +222,59 @@ def geod(U, mom, t):
 
 
 # --------------------------------------------------------------------------- sampler
-def sgld_step(phi_batch, y_batch, w, U, I, N_total, signal_var, epsw, epsU,
-              noise_w=None, noise_U=None, langevin=True, stiefel=True):
-    """One iteration of the loop body GPT_SGLD.jl:378-439.  noise_w[Q], noise_U[n,r,D] are the
-    randn draws of :412 and :420/:426 (supplied by the caller).  Returns (w, U, fhat, nan_flag).
-    Gradients use the pre-update w (:399 precedes :412)."""
+def sgld_update(w, U, gradw, gradU, epsw, epsU, noise_w=None, noise_U=None, langevin=True, stiefel=True):
+    """The update half of the loop body, GPT_SGLD.jl:411-439, from given gradients.  Returns (w, U, nan_flag)."""
     n, r, D = U.shape
-    gradw, gradU, fhat = gradients(phi_batch, y_batch, w, U, I, N_total, signal_var)
     if langevin:
-        w_new = w + epsw * gradw / 2 + np.sqrt(epsw) * noise_w
+        w_new = w + epsw * gradw / 2 + np.sqrt(epsw) * noise_w          # :412
     else:
-        w_new = w + epsw * gradw / 2
+        w_new = w + epsw * gradw / 2                                    # :414
     U_new = U.copy()
     if stiefel:
         for k in range(D):
             G = np.sqrt(epsU) * gradU[:, :, k] / 2
             if langevin:
                 G = G + noise_U[:, :, k]
-            mom = proj(U[:, :, k], G)
-            Uk, bad = geod(U[:, :, k], mom, np.sqrt(epsU))
+            mom = proj(U[:, :, k], G)                                   # :420 / :431
+            Uk, bad = geod(U[:, :, k], mom, np.sqrt(epsU))              # :421 / :432
             if bad:
-                return w_new, U_new, fhat, True
+                return w_new, U_new, True                               # :422-424
             U_new[:, :, k] = Uk
     else:
-        U_new = U + epsU * (gradU - n * U) / 2
+        U_new = U + epsU * (gradU - n * U) / 2                          # :437
         if langevin:
-            U_new = U_new + np.sqrt(epsU) * noise_U
-    return w_new, U_new, fhat, False
+            U_new = U_new + np.sqrt(epsU) * noise_U                     # :426
+    return w_new, U_new, False
+
+
+def sgld_step(phi_batch, y_batch, w, U, I, N_total, signal_var, epsw, epsU,
+              noise_w=None, noise_U=None, langevin=True, stiefel=True):
+    """One iteration of the loop body GPT_SGLD.jl:378-439.  noise_w[Q], noise_U[n,r,D] are the
+    randn draws of :412 and :420/:426 (supplied by the caller).  Returns (w, U, fhat, nan_flag).
+    Gradients use the pre-update w (:399 precedes :412)."""
+    gradw, gradU, fhat = gradients(phi_batch, y_batch, w, U, I, N_total, signal_var)
+    w_new, U_new, bad = sgld_update(w, U, gradw, gradU, epsw, epsU, noise_w, noise_U, langevin, stiefel)
+    return w_new, U_new, fhat, bad
+
+
+def gradients_chunked(phi_fn, X_batch, y_batch, w, U, I, N_total, signal_var, chunk=4096):
+    """`gradients` for a minibatch too large to hold phi (n x D x bs): the sums over rows of :393 and :405-408 are
+    accumulated over row chunks in FP64; phi_fn(X_chunk) returns the chunk's feature tensor.  Same result as
+    gradients(phi_fn(X_batch), ...) up to summation order."""
+    bs = len(y_batch)
+    gw = np.zeros_like(np.asarray(w, dtype=np.float64))
+    gU = np.zeros_like(np.asarray(U, dtype=np.float64))
+    fhat = np.empty(bs)
+    for i0 in range(0, bs, chunk):
+        sl = slice(i0, min(i0 + chunk, bs))
+        cb = sl.stop - sl.start
+        # with N_total = chunk length the (N/bs) factor is 1: raw sums of this chunk (the prior term is taken out again)
+        g1, g2, fh = gradients(phi_fn(X_batch[sl]), y_batch[sl], w, U, I, cb, signal_var)
+        gw += g1 + w
+        gU += g2
+        fhat[sl] = fh
+    scale = N_total / bs
+    return scale * gw - w, scale * gU, fhat
 
 
 def GPTregression(phi, y, signal_var, I, r, Q, m, epsw, epsU, burnin, maxepoch,

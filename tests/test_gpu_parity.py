@@ -308,7 +308,7 @@ def test_GPTregression_production_mode_and_nan_abort():
 
 
 @pytest.mark.parametrize("groups", [2, 3])
-def test_dimension_group_pipeline(groups, monkeypatch):
+def test_dimension_group_pipeline(groups):
     """The dimension-group pipeline of the step (api.cu: step_pipelined — the update of a group of dimensions runs on
     a side stream under the next group's back-projection and the next step's forward pass) must not change the
     chain: same Philox draws, same parameters as the one-stream step, in every driver of the step."""
@@ -321,13 +321,17 @@ def test_dimension_group_pipeline(groups, monkeypatch):
     yb = [np.ascontiguousarray(P["y"][i]) for i in idx]
 
     def drive(g):
-        monkeypatch.setenv("GPTB_PIPE_GROUPS", str(g))
+        opts = {L.OPT_PIPE_GROUPS: g, L.OPT_ALGORITHM: L.ALG_DIRECT}
         out = {}
         with _model(P, L.PREC_TC3) as m:                       # resident data, library-side loop
+            for k_, v_ in opts.items():
+                m.set_option(k_, v_)
             m.sgld_advance(P["signal_var"], m_, epsw, epsU, 7)
             out["advance"] = m.get_params()
         wouts = [np.zeros(P["Q"]) for _ in idx]
         with _model(P, L.PREC_TC3, train=False) as m:          # host minibatches, submit / wait
+            for k_, v_ in opts.items():
+                m.set_option(k_, v_)
             m.sgld_step_host_submit(P["signal_var"], Xb[0], yb[0], P["N"], epsw, epsU, w_out=wouts[0])
             for t in range(1, len(idx)):
                 m.sgld_step_host_submit(P["signal_var"], Xb[t], yb[t], P["N"], epsw, epsU, w_out=wouts[t])
@@ -337,9 +341,9 @@ def test_dimension_group_pipeline(groups, monkeypatch):
             assert np.array_equal(wouts[-1], out["host"][0])
         out["host_w"] = np.stack(wouts)
         out["run"] = G.GPTregression(f, P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m_, epsw, epsU, 1, 2, 7,
-                                     precision=L.PREC_TC3)
+                                     precision=L.PREC_TC3, options=opts)
         z = G.GPTregression(f, P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m_, epsw, 1e300, 0, 1, 7,
-                            precision=L.PREC_TC3)
+                            precision=L.PREC_TC3, options=opts)
         assert not z[0].any() and not z[1].any()               # NaN abort (:422-424) through the pipeline
         return out
 
@@ -515,3 +519,21 @@ def test_rmse_trajectory_powerplant(prec):
     ref_curve, got_curve = np.array(ref_curve), np.array(got_curve)
     assert np.isfinite(ref_curve).all() and ref_curve[-1] < 0.7 * ref_curve[0]        # the chain learns the data (0.60 -> 0.38)
     assert np.abs(got_curve / ref_curve - 1).max() < (1e-7 if prec == L.PREC_FP64 else 1e-2)
+
+
+def test_sgld_run_starts_from_data_order_and_rejects_bad_perms():
+    """Each gptb_sgld_run starts from the caller's data order, as each GPTregression call does (GPT_SGLD.jl:374 rebinds
+    a local): the same host permutations give the same minibatches on a second run of the same handle.  A permutation
+    entry outside 0..N-1 is an argument error, not an out-of-bounds read."""
+    P = make_problem(3, 120, 12, 3, Q=10, seed=14)
+    rng = np.random.default_rng(5)
+    perms = np.stack([rng.permutation(120) for _ in range(2)])
+    with _model(P, L.PREC_FP64) as m:
+        a = m.sgld_run(P["signal_var"], 50, 1e-5, 1e-8, 0, 2, langevin=False, perms=perms, N=120)
+        m.set_params(P["w0"], P["U0"])
+        b = m.sgld_run(P["signal_var"], 50, 1e-5, 1e-8, 0, 2, langevin=False, perms=perms, N=120)
+        assert relerr(b[0], a[0]) < 1e-12 and relerr(b[1], a[1]) < 1e-12
+        bad = perms.copy(); bad[1, 7] = 120
+        m.set_params(P["w0"], P["U0"])
+        with pytest.raises(G.GptbError):
+            m.sgld_run(P["signal_var"], 50, 1e-5, 1e-8, 0, 2, langevin=False, perms=bad, N=120)

@@ -20,7 +20,7 @@ def _free_port():
 def _worker(rank, world, port, out):
     sys.path[:0] = [ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")]
     import gpt_oracle as o
-    from gpt_b200.sharding import shard_range
+    from gpt_b200.gpt_sgld import shard_range
     from util import make_problem
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -66,7 +66,7 @@ def test_two_rank_gradient_allreduce():
 
 
 def test_shard_range_covers_batch():
-    from gpt_b200.sharding import shard_range
+    from gpt_b200.gpt_sgld import shard_range
     for bs in (1, 7, 500, 65536, 65537):
         for G in (1, 2, 3, 4, 8):
             edges = [shard_range(g, G, bs) for g in range(G)]

@@ -198,3 +198,21 @@ def test_fulltheta_oracle_gradient_and_chain():
     g0 = o.nt_grad(phi[:, p0], y[p0], th, N, 0.1, 1.5)
     assert np.allclose(st[:, 0], th + 1e-4 * g0 / 2 + np.sqrt(1e-4) * noise[0], rtol=0, atol=1e-14)
     assert not o.GPNT_SGLD(phi, y, 0.1, 1.5, 16, 1e300, 0.0, 0, 1, th, perms, noise).any()      # NaN -> zeros(n), :839-842
+
+
+def test_chunked_gradients_and_update_split_match_the_one_piece_oracle():
+    """gradients_chunked (used by the GPU tests at the benchmarked minibatch sizes, where phi does not fit in memory)
+    and sgld_update (the update half of sgld_step) restate the same lines as gradients / sgld_step."""
+    from util import make_problem
+    P = make_problem(3, 300, 12, 3, Q=15, seed=33)
+    idx = np.arange(37, 260)
+    phi = P["phi_fn"](P["X"][idx])
+    a = o.gradients(phi, P["y"][idx], P["w0"], P["U0"], P["I"], P["N"], P["signal_var"])
+    b = o.gradients_chunked(P["phi_fn"], P["X"][idx], P["y"][idx], P["w0"], P["U0"], P["I"], P["N"], P["signal_var"], chunk=50)
+    for x, y_ in zip(a, b):
+        assert np.allclose(x, y_, rtol=1e-11, atol=1e-9 * np.abs(x).max())
+    rng = np.random.default_rng(0)
+    nw, nU = rng.standard_normal(P["Q"]), rng.standard_normal(P["U0"].shape)
+    s1 = o.sgld_step(phi, P["y"][idx], P["w0"], P["U0"], P["I"], P["N"], P["signal_var"], 1e-5, 1e-8, nw, nU)
+    s2 = o.sgld_update(P["w0"], P["U0"], a[0], a[1], 1e-5, 1e-8, nw, nU)
+    assert np.array_equal(s1[0], s2[0]) and np.array_equal(s1[1], s2[1])
