@@ -40,6 +40,7 @@ PROTOTYPES = {
     "gptb_set_features": (C.c_int, [H, c_double_p, c_double_p, c_double_p, C.c_int32, C.c_double, C.c_double]),
     "gptb_set_index": (C.c_int, [H, c_int32_p]),
     "gptb_set_train": (C.c_int, [H, c_double_p, c_double_p, C.c_int64]),
+    "gptb_set_domain": (C.c_int, [H, c_double_p, c_double_p]),
     "gptb_set_train_phi": (C.c_int, [H, c_double_p, c_double_p, C.c_int64]),
     "gptb_set_params": (C.c_int, [H, c_double_p, c_double_p]),
     "gptb_get_params": (C.c_int, [H, c_double_p, c_double_p]),

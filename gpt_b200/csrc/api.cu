@@ -216,6 +216,19 @@ int forward_contract(gptb_handle *h, bool phi_mode, const int32_t *rows, const d
     return GPTB_OK;
 }
 
+static int pipe_init(gptb_handle *h, int G);
+
+// Node-grid step (nodes.cu): when the features can be generated at the nodes of a grid instead of at every row.
+// AUTO uses it when the rank's share has many more rows than the grid has nodes (K1 + K3 over the rows cost ~6.8 ns per
+// row at BASELINE config 4, the interpolation and spreading kernels ~0.7 ns per row plus ~45 us of fixed cost).
+static bool nodes_usable(gptb_handle *h, int64_t lbs, bool phi_mode) {
+    if (h->algorithm == GPTB_ALG_DIRECT || use_fp64(h, phi_mode) || !h->have_domain || !gptb_contract_tc_usable(h)) return false;
+    if (!h->grid_valid && gptb_nodes_setup(h) != GPTB_OK) return false;
+    if (h->nodes.m == 0) return false;
+    if (h->algorithm == GPTB_ALG_NODES) return true;
+    return lbs >= std::max<int64_t>(8192, 4 * (int64_t)h->nodes.m);
+}
+
 // Gradient of the rank's share of the minibatch into h->grad (likelihood part only, all-reduced).
 // rows_dev: device row ids of the *global* batch or null (= order[start..] / identity when staged).
 int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int64_t bs, int64_t N_total,
@@ -231,7 +244,14 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
     if (h->f32_grad) GPTB_TRY(gptb_tc_ensure_gradF(h));   // FP32 gradient flow: the buffer is cleared by its reader (k_prepare)
     else GPTB_CUDA_OK(h, cudaMemsetAsync(h->grad, 0, gcount * sizeof(double), h->stream));
     const bool f64 = use_fp64(h, phi_mode);
+    const bool nodes = lbs > 0 && nodes_usable(h, lbs, phi_mode);
+    if (nodes) GPTB_TRY(gptb_nodes_ensure_batch(h));
     const int32_t *rows = rows_dev ? rows_dev + lo : nullptr;
+    struct CellGuard {
+        gptb_handle *h;
+        ~CellGuard() { h->gather_cells = false; h->k2_Erow = nullptr; }
+    } cell_guard{h};
+    h->gather_cells = nodes;
     if (staged_host_batch) {
         const int64_t so = h->stage_share ? 0 : lo;   // (a share-only staging buffer starts at this rank's first row)
         GPTB_TRY(gptb_launch_gather_from(h, Xstage_rm + (size_t)so * c.D, ystage + so, lbs, h->mpad, f64 ? h->Xb : nullptr,
@@ -243,18 +263,45 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
     } else {
         GPTB_TRY(gptb_launch_gather(h, rows, 0, lbs, lo));
     }
+    h->gather_cells = false;
+    // the cell order of the batch is needed by the spreading kernel only: it runs beside K1 / interpolation / K2
+    const bool sort_aside = nodes && !skip_bwd && !h->profiling;
+    if (nodes && !skip_bwd) {
+        if (sort_aside) {
+            GPTB_TRY(pipe_init(h, 2));
+            GPTB_CUDA_OK(h, cudaEventRecord(h->evG[1], h->stream));
+            GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->side[1], h->evG[1], 0));
+            GPTB_TRY(gptb_nodes_sort(h, lbs, h->side[1]));
+            GPTB_CUDA_OK(h, cudaEventRecord(h->evR[1], h->side[1]));
+        } else {
+            GPTB_TRY(gptb_nodes_sort(h, lbs, h->stream));
+        }
+    }
     pt.done(GPTB_PHASE_GATHER);
     const double escale = ((double)N_total / (double)bs) / signal_var;  // (N/bs)/signal_var of :393,:407
     if (lbs > 0) {
-        GPTB_TRY(forward_contract(h, phi_mode, rows, h->w, h->U, h->Uimg, lbs, escale, true, &pt));
         double *gU = h->grad + c.Q;
-        if (skip_bwd) {
-            // GPTB_FLAG_FIX_U: the w-only sampler needs fhat and gradw only
-        } else if (f64) {
-            GPTB_TRY(gptb_launch_bwd_fp64(h, h->Xb, phi_mode ? h->phi : nullptr, rows, (const double *)h->E, lbs,
-                                          h->mpad, gU));
+        if (nodes) {
+            GPTB_TRY(gptb_nodes_forward_range(h, h->Uimg, 0, c.D, h->stream));
+            GPTB_TRY(gptb_nodes_interp(h, lbs, (float *)h->T));
+            h->k2_Erow = skip_bwd ? nullptr : h->nodes.Erow;   // K2 writes plain E rows instead of the operand image
+            GPTB_TRY(forward_contract(h, false, rows, h->w, h->U, h->Uimg, lbs, escale, true, &pt, true));
+            h->k2_Erow = nullptr;
+            if (!skip_bwd) {
+                if (sort_aside) GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->evR[1], 0));
+                GPTB_TRY(gptb_nodes_spread(h, lbs));
+                GPTB_TRY(gptb_nodes_backward_range(h, gU, 0, c.D));
+            }
         } else {
-            GPTB_TRY(gptb_launch_bwd_tc(h, h->XbF, h->Eimg, lbs, h->mpad, gU));
+            GPTB_TRY(forward_contract(h, phi_mode, rows, h->w, h->U, h->Uimg, lbs, escale, true, &pt));
+            if (skip_bwd) {
+                // GPTB_FLAG_FIX_U: the w-only sampler needs fhat and gradw only
+            } else if (f64) {
+                GPTB_TRY(gptb_launch_bwd_fp64(h, h->Xb, phi_mode ? h->phi : nullptr, rows, (const double *)h->E, lbs,
+                                              h->mpad, gU));
+            } else {
+                GPTB_TRY(gptb_launch_bwd_tc(h, h->XbF, h->Eimg, lbs, h->mpad, gU));
+            }
         }
     }
     pt.done(GPTB_PHASE_BWD);
@@ -347,6 +394,10 @@ static bool pipe_usable(gptb_handle *h, int64_t bs, bool staged_host_batch, int3
     const bool phi_mode = h->have_phi && !staged_host_batch;
     const int G = pipe_groups_for(h);
     if (flags & GPTB_FLAG_FIX_U) return false;
+    {   // the node-grid step has no row-proportional K3 to hide an update under: one stream
+        const int64_t lbs = (int64_t)(h->rank + 1) * bs / h->nranks - (int64_t)h->rank * bs / h->nranks;
+        if (lbs > 0 && nodes_usable(h, lbs, phi_mode)) return false;
+    }
     if (!(G >= 2 && h->cfg.D >= G && !h->profiling && !use_fp64(h, phi_mode) && (flags & GPTB_FLAG_STIEFEL) &&
           bs >= h->nranks))
         return false;
@@ -488,11 +539,16 @@ int stage_noise(gptb_handle *h, const double *noise_w, const double *noise_U, co
 
 int check_nan(gptb_handle *h) {
     GPTB_TRY(pipe_join(h));
-    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->nan_flag_host, h->nan_flag, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->nan_flag_host, h->nan_flag, 8 * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
     GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
     if (h->nan_flag_host[3]) {   // raised by apply_perm_kernel (gptb_sgld_run with host permutations)
         GPTB_CUDA_OK(h, cudaMemsetAsync(h->nan_flag + 3, 0, sizeof(int32_t), h->stream));
         gptb_set_error(h, "permutation entry outside 0..N-1");
+        return GPTB_ERR_ARG;
+    }
+    if (h->nan_flag_host[4]) {   // raised by the gather of a node-grid step
+        GPTB_CUDA_OK(h, cudaMemsetAsync(h->nan_flag + 4, 0, sizeof(int32_t), h->stream));
+        gptb_set_error(h, "a minibatch row lies outside the input domain of the node grid (gptb_set_domain / gptb_set_train)");
         return GPTB_ERR_ARG;
     }
     if (*h->nan_flag_host) {
@@ -580,8 +636,8 @@ int gptb_create(const gptb_config *cfg, gptb_handle **out) {
     A(dev_alloc(h, &h->grad, (size_t)c.Q + (size_t)c.D * c.r * c.n));
     h->small_stride = gptb_update_small_stride(c.r);
     A(dev_alloc(h, &h->small, h->small_stride * c.D));
-    A(dev_alloc(h, &h->nan_flag, 4));
-    A(dev_alloc(h, &h->tc_state, 16));
+    A(dev_alloc(h, &h->nan_flag, 8));   // [0] geodesic NaN (sticky) [1] bad batch index [2] K2 redo [3] bad permutation [4] row outside the node-grid domain
+    A(dev_alloc(h, &h->tc_state, 16));   // [10..11] max|node weight| of alternating steps (nodes.cu)
     A(dev_alloc(h, &h->pw, (size_t)c.Q));
     A(dev_alloc(h, &h->pU, (size_t)c.D * c.r * c.n));
     if (st == GPTB_OK && gptb_is_tc(h)) {
@@ -593,8 +649,8 @@ int gptb_create(const gptb_config *cfg, gptb_handle **out) {
         gptb_destroy(h);
         return st;
     }
-    CREATE_OK(cudaMallocHost((void **)&h->nan_flag_host, 4 * sizeof(int32_t)));
-    CREATE_OK(cudaMemsetAsync(h->nan_flag, 0, 4 * sizeof(int32_t), h->stream));
+    CREATE_OK(cudaMallocHost((void **)&h->nan_flag_host, 8 * sizeof(int32_t)));
+    CREATE_OK(cudaMemsetAsync(h->nan_flag, 0, 8 * sizeof(int32_t), h->stream));
     CREATE_OK(cudaMemsetAsync(h->tc_state, 0, 16 * sizeof(float), h->stream));
     CREATE_OK(cudaStreamSynchronize(h->stream));
 #undef CREATE_OK
@@ -619,6 +675,7 @@ int gptb_destroy(gptb_handle *h) {
         cudaEventDestroy(h->evTail);
     }
     gptb_comm_destroy(h);
+    gptb_nodes_free(h);
     dev_free(&h->Zt); dev_free(&h->b); dev_free(&h->ZtF); dev_free(&h->bF); dev_free(&h->I); dev_free(&h->grp_ptr); dev_free(&h->grp_q);
     dev_free(&h->ct_off1); dev_free(&h->ct_lptr); dev_free(&h->ct_lists);
     dev_free(&h->X); dev_free(&h->y); dev_free(&h->phi); dev_free(&h->order); dev_free(&h->order_tmp);
@@ -699,8 +756,10 @@ int gptb_set_features(gptb_handle *h, const double *Z, const double *b, const do
     std::vector<float> ztf((size_t)c.D * h->npad, 0.f), bf((size_t)c.D * h->npad, 0.f);
     for (int k = 0; k < c.D; ++k) {
         const double inv = 1.0 / length_scale[ls_len == 1 ? 0 : k];  // scale(Z, 1./length_scale), :75
+        h->zmax[k] = 0.0;
         for (int j = 0; j < c.n; ++j) {
             zt[(size_t)k * c.n + j] = Z[(size_t)k * c.n + j] * inv;
+            h->zmax[k] = std::max(h->zmax[k], fabs(zt[(size_t)k * c.n + j]));
             if (b) bb[(size_t)k * c.n + j] = b[(size_t)k * c.n + j];
             ztf[(size_t)k * h->npad + j] = (float)zt[(size_t)k * c.n + j];
             bf[(size_t)k * h->npad + j] = (float)bb[(size_t)k * c.n + j];
@@ -717,6 +776,7 @@ int gptb_set_features(gptb_handle *h, const double *Z, const double *b, const do
     GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
     h->have_features = true;
     h->ZbF_valid = false;
+    h->grid_valid = false;
     return GPTB_OK;
 }
 
@@ -790,6 +850,40 @@ int gptb_set_train(gptb_handle *h, const double *X, const double *y, int64_t N) 
     cudaFree(tmp);
     if (st != GPTB_OK) return st;
     h->have_train = true;
+    // input domain of the node grid: the range of every column (X[N,D] is column-major: column k is contiguous)
+    for (int k = 0; k < c.D; ++k) {
+        const double *col = X + (size_t)k * N;
+        double lo = col[0], hi = col[0];
+        for (int64_t i = 1; i < N; ++i) {
+            lo = col[i] < lo ? col[i] : lo;
+            hi = col[i] > hi ? col[i] : hi;
+        }
+        h->dom_lo[k] = lo;
+        h->dom_hi[k] = hi;
+    }
+    h->have_domain = true;
+    h->grid_valid = false;
+    return GPTB_OK;
+}
+
+int gptb_set_domain(gptb_handle *h, const double *lo, const double *hi) {
+    if (!h) return GPTB_ERR_ARG;
+    GPTB_CUDA_OK(h, cudaSetDevice(h->device));
+    GPTB_TRY(pipe_join(h));
+    h->grid_valid = false;
+    if (!lo || !hi) {
+        h->have_domain = false;
+        return GPTB_OK;
+    }
+    for (int k = 0; k < h->cfg.D; ++k) {
+        if (!(lo[k] <= hi[k]) || !std::isfinite(lo[k]) || !std::isfinite(hi[k])) {
+            gptb_set_error(h, "gptb_set_domain: need finite lo[k] <= hi[k] (k=%d: %g, %g)", k, lo[k], hi[k]);
+            return GPTB_ERR_ARG;
+        }
+        h->dom_lo[k] = lo[k];
+        h->dom_hi[k] = hi[k];
+    }
+    h->have_domain = true;
     return GPTB_OK;
 }
 
@@ -1325,7 +1419,11 @@ static int pipe_wait_oldest(gptb_handle *h, int *step_status) {
     GPTB_CUDA_OK(h, cudaEventSynchronize(h->pipe_done[slot]));
     ++h->pipe_waited;
     *step_status = GPTB_OK;
-    if (h->pipe_stiefel[slot] && h->pipe_nan_host[slot]) {
+    if (h->pipe_nan_host[slot * 8 + 4]) {
+        cudaMemsetAsync(h->nan_flag + 4, 0, sizeof(int32_t), h->stream);
+        gptb_set_error(h, "a minibatch row lies outside the input domain of the node grid (gptb_set_domain / gptb_set_train)");
+        *step_status = GPTB_ERR_ARG;
+    } else if (h->pipe_stiefel[slot] && h->pipe_nan_host[slot * 8]) {
         gptb_set_error(h, "Get NaN when moving along Geodesic. Try smaller epsU");   // GPT_SGLD.jl:25
         *step_status = GPTB_GEODESIC_NAN;
     }
@@ -1348,8 +1446,8 @@ int gptb_sgld_step_host_submit(gptb_handle *h, double signal_var, const double *
             GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&h->pipe_staged[s], cudaEventDisableTiming));
             GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&h->pipe_done[s], cudaEventDisableTiming));
         }
-        GPTB_CUDA_OK(h, cudaMallocHost((void **)&h->pipe_nan_host, 2 * sizeof(int32_t)));
-        h->pipe_nan_host[0] = h->pipe_nan_host[1] = 0;
+        GPTB_CUDA_OK(h, cudaMallocHost((void **)&h->pipe_nan_host, 16 * sizeof(int32_t)));
+        memset(h->pipe_nan_host, 0, 16 * sizeof(int32_t));
     }
     if (h->pipe_submitted - h->pipe_waited >= 2) {   // both slots busy: retire the oldest (status kept sticky on the device)
         int st_old;
@@ -1391,8 +1489,7 @@ int gptb_sgld_step_host_submit(gptb_handle *h, double signal_var, const double *
     GPTB_TRY(pipe_tail_begin(h, &ts));
     if (w_out) GPTB_CUDA_OK(h, cudaMemcpyAsync(w_out, h->w, sizeof(double) * c.Q, cudaMemcpyDeviceToHost, ts));
     h->pipe_stiefel[slot] = (flags & GPTB_FLAG_STIEFEL) != 0;
-    if (h->pipe_stiefel[slot])
-        GPTB_CUDA_OK(h, cudaMemcpyAsync(h->pipe_nan_host + slot, h->nan_flag, sizeof(int32_t), cudaMemcpyDeviceToHost, ts));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->pipe_nan_host + slot * 8, h->nan_flag, 8 * sizeof(int32_t), cudaMemcpyDeviceToHost, ts));
     GPTB_CUDA_OK(h, cudaEventRecord(h->pipe_done[slot], ts));
     GPTB_TRY(pipe_tail_end(h, ts));
     ++h->pipe_submitted;

@@ -12,7 +12,11 @@ namespace {
 __global__ void gather_kernel(const double *__restrict__ X /*[N][D]*/, const double *__restrict__ y,
                               const int32_t *__restrict__ rows /*may be null: identity from row_base*/,
                               int64_t row_base, int64_t bs, int64_t mpad, int D, double *__restrict__ Xb,
-                              float *__restrict__ XbF, double *__restrict__ yb) {
+                              float *__restrict__ XbF, double *__restrict__ yb, const double *__restrict__ glo,
+                              const double *__restrict__ ginvh, int G, int32_t *__restrict__ cell, float *__restrict__ uu,
+                              int32_t *__restrict__ oob) {
+    // cell != null: the node-grid position of every entry, computed from the FP64 input — cell c = floor((x-lo)/(2h)),
+    // u = (x-lo)/h - (2c+1) in [-1,1] (nodes.cu); a row outside the domain raises *oob
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < mpad; i += (int64_t)gridDim.x * blockDim.x) {
         const bool live = i < bs;
         int64_t src = 0;
@@ -21,6 +25,19 @@ __global__ void gather_kernel(const double *__restrict__ X /*[N][D]*/, const dou
             double v = live ? X[src * D + k] : 0.0;
             if (Xb) Xb[(size_t)k * mpad + i] = v;
             if (XbF) XbF[(size_t)k * mpad + i] = (float)v;
+            if (cell) {
+                int c = 0;
+                double u = 0.0;
+                if (live) {
+                    const double t = (v - glo[k]) * ginvh[k];
+                    c = min(max((int)floor(0.5 * t), 0), G - 1);
+                    u = t - (2.0 * c + 1.0);
+                    if (!(u >= -1.000001 && u <= 1.000001)) *oob = 1;
+                    u = fmin(fmax(u, -1.0), 1.0);
+                }
+                cell[(size_t)k * mpad + i] = c;
+                uu[(size_t)k * mpad + i] = (float)u;
+            }
         }
         if (y && yb) yb[i] = live ? y[src] : 0.0;
     }
@@ -72,8 +89,11 @@ int gptb_launch_gather(gptb_handle *h, const int32_t *rows, int64_t start, int64
     // rows (device) already points at the first row of this rank's share, or is null for identity.
     (void)row_off;
     const bool tc = gptb_is_tc(h);
+    const gptb_nodes &g = h->nodes;
+    const bool gc = h->gather_cells;
     gather_kernel<<<grid_for(h, h->mpad, 128), 128, 0, h->stream>>>(h->X, h->y, rows, start, bs, h->mpad, h->cfg.D,
-                                                                    tc ? nullptr : h->Xb, tc ? h->XbF : nullptr, h->yb);
+                                                                    tc ? nullptr : h->Xb, tc ? h->XbF : nullptr, h->yb, g.lo,
+                                                                    g.invh, g.G, gc ? g.cell : nullptr, g.uu, h->nan_flag + 4);
     h->launches++;
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;
@@ -81,7 +101,10 @@ int gptb_launch_gather(gptb_handle *h, const int32_t *rows, int64_t start, int64
 
 int gptb_launch_gather_from(gptb_handle *h, const double *Xrm, const double *y, int64_t bs, int64_t mpad, double *Xb,
                             float *XbF, double *yb) {
-    gather_kernel<<<grid_for(h, mpad, 128), 128, 0, h->stream>>>(Xrm, y, nullptr, 0, bs, mpad, h->cfg.D, Xb, XbF, yb);
+    const gptb_nodes &g = h->nodes;
+    const bool gc = h->gather_cells;
+    gather_kernel<<<grid_for(h, mpad, 128), 128, 0, h->stream>>>(Xrm, y, nullptr, 0, bs, mpad, h->cfg.D, Xb, XbF, yb, g.lo, g.invh,
+                                                                 g.G, gc ? g.cell : nullptr, g.uu, h->nan_flag + 4);
     h->launches++;
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;

@@ -43,6 +43,24 @@ void gptb_set_error(const gptb_handle *h, const char *fmt, ...);
 //     fhat double [mpad]
 //   grad   double [Q + n*r*D]      [gradw | gradU] in Julia order — the all-reduce buffer
 // ------------------------------------------------------------------------------------------
+// Node grid of the tensor-core path (nodes.cu): the features are generated at G*P Chebyshev nodes per dimension
+// instead of at every minibatch row.
+struct gptb_nodes {
+    int G = 0, P = 0, m = 0, mnpad = 0;      // cells, nodes per cell, nodes per dimension (0 = grid not applicable), padded to 128
+    double *lo = nullptr, *invh = nullptr;   // [D] lower end of the domain, 1 / cell half-width
+    float *XnF = nullptr;                    // [D][mnpad] node coordinates (the "minibatch" K1 / K3 run on)
+    float *Tn = nullptr;                     // [D][r][mnpad] K1 output on the nodes
+    float *Cf = nullptr;                     // [D][m][rpad] Chebyshev coefficients per cell
+    float *Mn = nullptr;                     // [D][mnpad][rpad] moment / node-weight table of the backward pass
+    void *Enimg = nullptr;                   // fp16 hi|lo operand image of the node weights (K3's B operand)
+    int32_t *cell = nullptr;                 // [D][mpad] cell of every batch row
+    float *uu = nullptr;                     // [D][mpad] position inside the cell, in [-1, 1]
+    int32_t *sorted = nullptr;               // [D][mpad] batch rows in cell order
+    float *Erow = nullptr;                   // [D][mpad][rpad] FP32 E as K2 writes it for the spreading kernel
+    int64_t batch_mpad = 0;
+    uint64_t steps = 0;
+};
+
 struct gptb_handle {
     gptb_config cfg;
     int device = 0;
@@ -114,6 +132,7 @@ struct gptb_handle {
     float *tc_state = nullptr;         // [0] max|E| of the running step, [1] escale (2^k), [2] 1/escale,
                                        // [3] uscale (2^k applied to U in Uimg), [4] 1/uscale
     bool tc_emax_valid = false;
+    bool gather_cells = false;         // set around a node-grid step: the gather also writes nodes.cell / nodes.uu
     bool k2_redo = false;              // set around the conditional second K2 launch (E-image scale guard, api.cu)
     float *k2_Erow = nullptr;          // when set, K2 writes plain FP32 E [D][mpad][rpad] instead of the operand image
 
@@ -138,6 +157,10 @@ struct gptb_handle {
     int node_P = 12;                   // Chebyshev nodes per cell
     double node_theta = 2.0;           // cell half-width times the largest |frequency| of the dimension
     bool grid_valid = false;
+    gptb_nodes nodes;
+    bool have_domain = false;          // input domain known: from gptb_set_train (min / max of X) or gptb_set_domain
+    double dom_lo[16] = {0}, dom_hi[16] = {0};
+    double zmax[16] = {0};             // max_j |Zt[j,k]|
     cudaStream_t side[PIPE_MAX] = {nullptr, nullptr, nullptr, nullptr};
     cudaStream_t tail_stream = nullptr, ar_stream = nullptr;
     cudaEvent_t evG[PIPE_MAX] = {}, evU[PIPE_MAX] = {}, evR[PIPE_MAX] = {};
@@ -260,6 +283,7 @@ int gptb_proj_geod_device(gptb_handle *scratch_owner, cudaStream_t s, int n, int
                           double t, double *out, int mode /*0 proj, 1 geod*/, int32_t *nan_flag);
 // batch.cu
 int gptb_launch_gather(gptb_handle *h, const int32_t *rows, int64_t start, int64_t bs, int64_t row_off);
+// (both gathers also emit the node-grid cell / offset of every row when h->gather_cells is set)
 int gptb_shuffle_order(gptb_handle *h, uint64_t epoch);
 // tc_path.cu
 int gptb_tc_pack_params(gptb_handle *h);
@@ -283,6 +307,15 @@ int gptb_launch_fwd_tc_range(gptb_handle *h, const float *XbF, const void *Uimg,
                              int kn);
 size_t gptb_tc_uimg_bytes(const gptb_handle *h);
 size_t gptb_tc_eimg_bytes(const gptb_handle *h, int64_t mpad);
+// nodes.cu
+void gptb_nodes_free(gptb_handle *h);
+int gptb_nodes_setup(gptb_handle *h);
+int gptb_nodes_ensure_batch(gptb_handle *h);
+int gptb_nodes_forward_range(gptb_handle *h, const void *Uimg, int k0, int kn, cudaStream_t s);
+int gptb_nodes_interp(gptb_handle *h, int64_t bs, float *T);
+int gptb_nodes_sort(gptb_handle *h, int64_t bs, cudaStream_t s);
+int gptb_nodes_spread(gptb_handle *h, int64_t bs);
+int gptb_nodes_backward_range(gptb_handle *h, double *gradU, int k0, int kn);
 // comm.cu
 int gptb_allreduce_grad(gptb_handle *h);
 int gptb_allreduce_range(gptb_handle *h, double *buf, size_t count, cudaStream_t stream);

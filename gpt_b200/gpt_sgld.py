@@ -214,6 +214,15 @@ class Model:
             raise ValueError("X and y disagree on N")
         _check(self.lib.gptb_set_train(self.h, _dp(X), _dp(y), X.shape[0]), self.h)
 
+    def set_domain(self, lo=None, hi=None):
+        """Bounds of every input column for the node grid (gptb_set_domain); None, None forgets them."""
+        if lo is None or hi is None:
+            _check(self.lib.gptb_set_domain(self.h, None, None), self.h)
+            return
+        lo = np.ascontiguousarray(np.broadcast_to(np.asarray(lo, dtype=np.float64), (self.cfg.D,)))
+        hi = np.ascontiguousarray(np.broadcast_to(np.asarray(hi, dtype=np.float64), (self.cfg.D,)))
+        _check(self.lib.gptb_set_domain(self.h, _dp(lo), _dp(hi)), self.h)
+
     def set_train_phi(self, phi, y):
         phi = _f64(phi); y = _f64(np.ravel(y))
         _check(self.lib.gptb_set_train_phi(self.h, _dp(phi), _dp(y), phi.shape[2]), self.h)

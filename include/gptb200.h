@@ -96,6 +96,11 @@ int gptb_set_features(gptb_handle *h, const double *Z, const double *b, const do
 int gptb_set_index(gptb_handle *h, const int32_t *I);
 /* Training set: raw inputs X[N,D] (features are generated on the fly, never stored) and y[N]. */
 int gptb_set_train(gptb_handle *h, const double *X, const double *y, int64_t N);
+/* Input domain of the node grid (nodes.cu): lo[D] <= hi[D] bound every input the handle will see.  gptb_set_train
+ * sets it to the column ranges of X; callers that only pass host minibatches (gptb_sgld_step_host*) set it here.
+ * NULL, NULL forgets the domain (direct evaluation at every row).  A row outside the domain makes the step's next
+ * synchronising call return GPTB_ERR_ARG. */
+int gptb_set_domain(gptb_handle *h, const double *lo, const double *hi);
 /* Compatibility: a materialised phi[n,D,N] exactly as `feature` returns it (GPT_SGLD.jl:345 takes phi). */
 int gptb_set_train_phi(gptb_handle *h, const double *phi, const double *y, int64_t N);
 

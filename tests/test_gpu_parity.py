@@ -537,3 +537,81 @@ def test_sgld_run_starts_from_data_order_and_rejects_bad_perms():
         m.set_params(P["w0"], P["U0"])
         with pytest.raises(G.GptbError):
             m.sgld_run(P["signal_var"], 50, 1e-5, 1e-8, 0, 2, langevin=False, perms=bad, N=120)
+
+
+# ------------------------------------------------------------------ node-grid algorithm (csrc/nodes.cu)
+@pytest.mark.parametrize("shape", list(SHAPES))
+def test_nodes_grad_and_step_vs_oracle(shape):
+    """GPTB_ALG_NODES: features generated at the Chebyshev nodes of a grid over the input domain, T interpolated to the
+    rows, E spread back to the nodes (nodes.cu).  Same tolerances as the direct tensor-core path."""
+    P = make_problem(seed=2, **SHAPES[shape])
+    N = P["N"]
+    rng = np.random.default_rng(0)
+    idx = rng.permutation(N)[: max(1, (2 * N) // 3)]
+    phi = P["phi_fn"](P["X"][idx])
+    want = o.gradients(phi, P["y"][idx], P["w0"], P["U0"], P["I"], N, P["signal_var"])
+    nw = rng.standard_normal(P["Q"]); nU = np.asfortranarray(rng.standard_normal((P["n"], P["r"], P["D"])))
+    step = o.sgld_step(phi, P["y"][idx], P["w0"], P["U0"], P["I"], N, P["signal_var"], 1e-5, 1e-8, nw, nU)
+    with _model(P, L.PREC_TC3) as m:
+        m.set_option(L.OPT_ALGORITHM, L.ALG_NODES)
+        gw, gU, fh = m.grad(P["signal_var"], idx=idx)
+        assert relerr(fh, want[2]) < 1e-4 and relerr(gw, want[0]) < 1e-4 and relerr(gU, want[1]) < 1e-4
+        full = o.gradients(P["phi_fn"](P["X"]), P["y"], P["w0"], P["U0"], P["I"], N, P["signal_var"])
+        gw, gU, fh = m.grad(P["signal_var"], start=0, bs=N)
+        assert relerr(fh, full[2]) < 1e-4 and relerr(gw, full[0]) < 1e-4 and relerr(gU, full[1]) < 1e-4
+        m.sgld_step(P["signal_var"], 1e-5, 1e-8, idx=idx, noise_w=nw, noise_U=nU)
+        w, U = m.get_params()
+    assert relerr(w - P["w0"], step[0] - P["w0"]) < 1e-4 and relerr(U - P["U0"], step[1] - P["U0"]) < 1e-4
+
+
+@pytest.mark.parametrize("order,theta,tol", [(12, 2.0, 1e-4), (16, 2.0, 1e-4), (8, 1.0, 1e-4), (4, 4.0, None)])
+def test_nodes_orders_and_host_domain(order, theta, tol):
+    """Grid options (nodes per cell, cell width), feature2, and the host-minibatch entry with an explicit domain; a
+    grid that is far too coarse (4 nodes on cells of half-width 4/zmax) must visibly miss the tolerance — i.e. the
+    options really select the grid."""
+    P = make_problem(5, 900, 60, 6, Q=40, seed=15, feature2=True)
+    idx = np.arange(100, 800)
+    want = o.gradients(P["phi_fn"](P["X"][idx]), P["y"][idx], P["w0"], P["U0"], P["I"], P["N"], P["signal_var"])
+    with _model(P, L.PREC_TC3, train=False) as m:
+        m.set_option(L.OPT_ALGORITHM, L.ALG_NODES)
+        m.set_option(L.OPT_NODE_ORDER, order)
+        m.set_option(L.OPT_NODE_THETA, theta)
+        m.set_domain(P["X"].min(0) - 0.1, P["X"].max(0) + 0.1)
+        m.set_train(P["X"], P["y"])                     # (set_train replaces the domain by the exact column ranges)
+        gw, gU, fh = m.grad(P["signal_var"], idx=idx)
+        err = max(relerr(gw, want[0]), relerr(gU, want[1]), relerr(fh, want[2]))
+        if tol is None:
+            assert err > 1e-4
+            return
+        assert err < tol
+    # host minibatches: the domain comes from gptb_set_domain; a row outside it is an argument error
+    rng = np.random.default_rng(2)
+    nw = rng.standard_normal(P["Q"]); nU = np.asfortranarray(rng.standard_normal((P["n"], P["r"], P["D"])))
+    Xb = np.asfortranarray(P["X"][idx]); yb = np.ascontiguousarray(P["y"][idx])
+    step = o.sgld_step(P["phi_fn"](P["X"][idx]), yb, P["w0"], P["U0"], P["I"], P["N"], P["signal_var"], 1e-5, 1e-8, nw, nU)
+    with _model(P, L.PREC_TC3, train=False) as m:
+        m.set_option(L.OPT_ALGORITHM, L.ALG_NODES)
+        m.set_option(L.OPT_NODE_ORDER, order)
+        m.set_option(L.OPT_NODE_THETA, theta)
+        m.set_domain(P["X"].min(0), P["X"].max(0))
+        m.sgld_step_host(P["signal_var"], Xb, yb, P["N"], 1e-5, 1e-8, noise_w=nw, noise_U=nU)
+        w, U = m.get_params()
+        assert relerr(w - P["w0"], step[0] - P["w0"]) < 1e-4 and relerr(U - P["U0"], step[1] - P["U0"]) < 1e-4
+        Xbad = Xb.copy(); Xbad[3, 1] = P["X"][:, 1].max() + 1.0
+        with pytest.raises(G.GptbError):
+            m.sgld_step_host(P["signal_var"], Xbad, yb, P["N"], 1e-5, 1e-8, noise_w=nw, noise_U=nU)
+
+
+def test_nodes_GPTregression_vs_oracle():
+    P = make_problem(3, 150, 16, 4, Q=20, seed=8)
+    N, m, burnin, maxepoch = 150, 64, 1, 2
+    rng = np.random.default_rng(2)
+    perms = [rng.permutation(N) for _ in range(burnin + maxepoch)]
+    steps = (burnin + maxepoch) * 3
+    NW = rng.standard_normal((steps, P["Q"])); NU = rng.standard_normal((steps, P["n"], P["r"], P["D"]))
+    ws, Us = o.GPTregression(P["phi_fn"](P["X"]), P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m, 1e-5, 1e-8, burnin,
+                             maxepoch, P["w0"], P["U0"], perms, NW, NU)
+    gw, gU = G.GPTregression(_feat(P), P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m, 1e-5, 1e-8, burnin, maxepoch, 1,
+                             precision=L.PREC_TC3, w0=P["w0"], U0=P["U0"], perms=np.stack(perms), noise_w=NW, noise_U=NU,
+                             options={L.OPT_ALGORITHM: L.ALG_NODES})
+    assert relerr(gw, ws) < 1e-4 and relerr(gU, Us) < 1e-4

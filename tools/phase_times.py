@@ -20,6 +20,7 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--N", type=int, default=2_000_000)
     ap.add_argument("--precision", default="tc3")
+    ap.add_argument("--alg", default="auto", choices=["auto", "direct", "nodes"])
     a = ap.parse_args()
     from gpt_b200 import _lib as L
     from gpt_b200 import gpt_sgld as G
@@ -37,13 +38,14 @@ def main():
         with G.Model(D, n, r, B.Q, precision=prec, device=0, seed=1234) as model:
             model.set_features(feat); model.set_index(mdl["I"]); model.set_train(X, y)
             model.set_params(mdl["w0"], mdl["U0"])
+            model.set_option(L.OPT_ALGORITHM, {"auto": L.ALG_AUTO, "direct": L.ALG_DIRECT, "nodes": L.ALG_NODES}[a.alg])
             model.sgld_advance(B.SIGNAL_VAR, m, EPSW, EPSU, 5)
             model.synchronize()
             import time
             t0 = time.perf_counter()
             model.sgld_advance(B.SIGNAL_VAR, m, EPSW, EPSU, a.steps)
             model.synchronize()
-            print(pname, "unprofiled ms/step %.4f (pipelined when GPTB_PIPE_GROUPS >= 2, default 2)" %
+            print(a.alg, pname, "unprofiled ms/step %.4f (pipelined when GPTB_PIPE_GROUPS >= 2, default 2)" %
                   ((time.perf_counter() - t0) * 1e3 / a.steps), flush=True)
             model.set_profiling(True)
             model.phase_ms(reset=True)
@@ -51,7 +53,7 @@ def main():
             model.synchronize()
             ms, launches = model.phase_ms(reset=True)
             tot = sum(ms.values()) / a.steps
-            print(pname, "ms/step %.4f" % tot, {k: round(v / a.steps, 4) for k, v in ms.items()},
+            print(a.alg, pname, "ms/step %.4f" % tot, {k: round(v / a.steps, 4) for k, v in ms.items()},
                   "launches/step", launches / a.steps, flush=True)
 
 

@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--N", type=int, default=1_000_000)
     ap.add_argument("--precision", default="tc3")
+    ap.add_argument("--alg", default="auto", choices=["auto", "direct", "nodes"])
     ap.add_argument("--pred", action="store_true")
     a = ap.parse_args()
     from gpt_b200 import _lib as L
@@ -53,6 +54,7 @@ def main():
     EPSW, EPSU = B.eps_for(W["N"])
     with G.Model(D, n, r, B.Q, precision=prec, device=0, seed=1234) as model:
         model.set_features(feat); model.set_index(mdl["I"]); model.set_train(X, y); model.set_params(mdl["w0"], mdl["U0"])
+        model.set_option(L.OPT_ALGORITHM, {"auto": L.ALG_AUTO, "direct": L.ALG_DIRECT, "nodes": L.ALG_NODES}[a.alg])
         model.sgld_advance(B.SIGNAL_VAR, m, EPSW, EPSU, a.warmup)
         model.synchronize()
         model.sgld_advance(B.SIGNAL_VAR, m, EPSW, EPSU, a.steps)
