@@ -106,49 +106,121 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(self.rows)}
 
 
-def cpu_reference_steps_per_sec(W, mdl, budget_s=20.0, sample_rows=2048):
-    """The reference path's CPU restatement (oracle/gpt_oracle.c, FP64, OpenMP over rows like GPT_SGLD_p.jl) timed
-    on the host cores on a bounded row sample of the same workload, scaled linearly in rows to the full minibatch."""
+def host_threads():
+    """All host cores, whatever OMP_NUM_THREADS says (torch.distributed.run exports OMP_NUM_THREADS=1 to every rank)."""
+    return max(1, os.cpu_count() or 1)
+
+
+def cpu_reference_timing(W, mdl, rows, threads, budget_s, X=None, y=None, seed=7):
+    """Times the reference path's CPU restatement (oracle/gpt_oracle.c: FP64, OpenMP over minibatch rows like
+    GPT_SGLD_p.jl:70-108) on `rows` rows of the workload's minibatch with `threads` threads.
+
+    The loop body of GPT_SGLD.jl:378-439 has a row-proportional part (phidotU .. grad-U, :384-408) and a fixed part
+    (w update, D x proj/geod with their expm calls, :411-439).  They are timed separately — t_grad on `rows` rows,
+    t_update as (step - gradient) on a 64-row batch — so that a scaled figure multiplies only the row-proportional
+    part.  The features of the rows are precomputed and untimed, as in the reference (phi is formed once per run, :71)."""
     import c_oracle as co
     D, n, r, m = W["D"], W["n"], W["r"], W["m"]
-    ms = min(m, sample_rows)
-    rng = np.random.default_rng(7)
-    X = rng.standard_normal((ms, D))
-    y = rng.standard_normal(ms)
-    threads = co.max_threads()
+    rows = int(min(rows, m))
+    rng = np.random.default_rng(seed)
     EPSW, EPSU = eps_for(W["N"])
+    if X is None:       # the workload's own generative process (SURVEY.md 8d): X ~ N(0,1), y = f*(X) + noise
+        X = rng.standard_normal((rows, D))
+    X = np.ascontiguousarray(X[:rows])
     phi = co.feature(X, mdl["ls"], 1.0, mdl["phi_scale"], mdl["Z"], mdl["b"], threads)
+    if y is None:
+        y = co.pred(mdl["w_true"], mdl["U_true"], mdl["I"], phi, threads) + np.sqrt(SIGNAL_VAR) * rng.standard_normal(rows)
+    y = np.ascontiguousarray(y[:rows])
     nw = rng.standard_normal(Q); nU = rng.standard_normal((n, r, D))
     w, U = mdl["w0"].copy(), mdl["U0"].copy()
-    t0 = time.perf_counter()
-    w, U, _, _ = co.sgld_step(phi, y, w, U, mdl["I"], W["N"], SIGNAL_VAR, EPSW, EPSU, nw, nU, True, threads)  # warm
-    t_first = time.perf_counter() - t0
-    reps = int(max(1, min(20, budget_s / max(t_first, 1e-3) - 1)))
-    t0 = time.perf_counter()
-    for _ in range(reps):
-        w, U, _, _ = co.sgld_step(phi, y, w, U, mdl["I"], W["N"], SIGNAL_VAR, EPSW, EPSU, nw, nU, True, threads)
-    t_step = (time.perf_counter() - t0) / reps
-    full = t_step * (m / ms)
-    return 1.0 / full, threads, f"{reps} steps on {ms} of {m} minibatch rows (features precomputed as the reference does), scaled x{m / ms:g} in rows"
+
+    def timed(fn, min_reps, max_reps, budget):
+        fn()                                   # warm (page faults, thread pool)
+        t0 = time.perf_counter(); fn(); t1 = time.perf_counter() - t0
+        reps = int(max(min_reps, min(max_reps, budget / max(t1, 1e-4))))
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        return (time.perf_counter() - t0) / reps, reps
+
+    t_grad, reps = timed(lambda: co.gradients(phi, y, w, U, mdl["I"], W["N"], SIGNAL_VAR, threads), 1, 20, budget_s)
+    small = slice(0, min(64, rows))
+    phis = np.asfortranarray(phi[:, :, small]); ys = y[small]
+    t_s, _ = timed(lambda: co.sgld_step(phis, ys, w, U, mdl["I"], W["N"], SIGNAL_VAR, EPSW, EPSU, nw, nU, True, threads), 3, 20, 2.0)
+    t_g, _ = timed(lambda: co.gradients(phis, ys, w, U, mdl["I"], W["N"], SIGNAL_VAR, threads), 3, 20, 1.0)
+    t_update = max(t_s - t_g, 0.0)
+    return {"rows": rows, "threads": threads, "t_grad_s": t_grad, "t_update_s": t_update, "reps": reps,
+            "t_step_full_s": t_grad * (m / rows) + t_update, "extrapolated": rows < m}
+
+
+def cpu_baseline_object(W, mdl, rows_all, rows_one, budget_s, X=None, y=None):
+    """cpu_baseline of the JSON line: all host cores (the value) and one thread (the reference module itself is
+    single-threaded apart from BLAS), both as gradient-rows x (m/rows) + update."""
+    thr = host_threads()
+    a = cpu_reference_timing(W, mdl, rows_all, thr, budget_s, X, y)
+    o1 = cpu_reference_timing(W, mdl, rows_one, 1, budget_s / 4, X, y)
+    m = W["m"]
+    return {"value": 1.0 / a["t_step_full_s"], "unit": "steps/s", "cores": thr, "kind": "port",
+            "extrapolated": a["extrapolated"], "measured_rows": a["rows"],
+            "t_grad_measured_s": a["t_grad_s"], "t_update_measured_s": a["t_update_s"],
+            "one_thread": {"value": 1.0 / o1["t_step_full_s"], "measured_rows": o1["rows"], "extrapolated": o1["extrapolated"],
+                           "t_grad_measured_s": o1["t_grad_s"], "t_update_measured_s": o1["t_update_s"]},
+            "sample": f"oracle/gpt_oracle.c (C restatement of GPT_SGLD.jl:378-439; the Julia 0.3 reference cannot run here): "
+                      f"gradient part timed over {a['reps']} repetitions on {a['rows']} of the {m} minibatch rows "
+                      f"({thr} OpenMP threads) and multiplied by {m / a['rows']:g}; the row-independent update "
+                      f"(w, {W['D']} x proj/geod/expm) timed once and added unscaled; features precomputed (untimed) as "
+                      f"the reference does"}, a
 
 
 def run_reference(args, W, emit):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    import c_oracle as co
     mdl = synth_model(W["D"], W["n"], W["r"], seed=3)
-    K = max(1, args.steps)
+    K, Wm = max(1, args.steps), max(0, args.warmup)
     t0 = time.perf_counter()
-    v, threads, sample = cpu_reference_steps_per_sec(W, mdl, budget_s=min(60.0, 4.0 * K))
+    thr = host_threads()
+    # how many rows of the minibatch fit the run: probe 1024 rows, then take the whole minibatch if K+W such steps end
+    # within ~150 s, else the largest power-of-two share that does
+    probe = cpu_reference_timing(W, mdl, 1024, thr, 1.0)
+    per_row = probe["t_grad_s"] / probe["rows"]
+    rows = W["m"]
+    while rows > 1024 and (K + Wm) * (per_row * rows + probe["t_update_s"]) > 150.0:
+        rows //= 2
+    D, n, r, m = W["D"], W["n"], W["r"], W["m"]
+    rng = np.random.default_rng(7)
+    X = rng.standard_normal((rows, D))
+    phi = co.feature(X, mdl["ls"], 1.0, mdl["phi_scale"], mdl["Z"], mdl["b"], thr)
+    y = co.pred(mdl["w_true"], mdl["U_true"], mdl["I"], phi, thr) + np.sqrt(SIGNAL_VAR) * rng.standard_normal(rows)
+    EPSW, EPSU = eps_for(W["N"])
+    w, U = mdl["w0"].copy(), mdl["U0"].copy()
+    nw = rng.standard_normal(Q); nU = rng.standard_normal((n, r, D))
+    for _ in range(Wm):
+        w, U, _, _ = co.sgld_step(phi, y, w, U, mdl["I"], W["N"], SIGNAL_VAR, EPSW, EPSU, nw, nU, True, thr)
+    ts = time.perf_counter()
+    for _ in range(K):
+        w, U, _, _ = co.sgld_step(phi, y, w, U, mdl["I"], W["N"], SIGNAL_VAR, EPSW, EPSU, nw, nU, True, thr)
+    t_step = (time.perf_counter() - ts) / K                  # one loop body on `rows` rows
+    t_full = (t_step - probe["t_update_s"]) * (m / rows) + probe["t_update_s"] if rows < m else t_step
+    v = 1.0 / t_full
+    one = cpu_reference_timing(W, mdl, 1024, 1, 3.0)
     line = {
         "impl": "reference", "metric": "sgld_steps_per_sec", "value": v, "unit": "steps/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / v, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": workload_config(args, W),
-        "cpu_baseline": {"value": v, "unit": "steps/s", "cores": threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "steps/s", "cores": thr, "kind": "port", "extrapolated": rows < m,
+                         "measured_rows": rows, "measured_ms_per_step_on_those_rows": 1e3 * t_step,
+                         "t_update_measured_s": probe["t_update_s"],
+                         "one_thread": {"value": 1.0 / one["t_step_full_s"], "measured_rows": one["rows"], "extrapolated": True},
+                         "sample": f"{K} timed loop bodies (after {Wm} warm-up) of oracle/gpt_oracle.c on {rows} of the {m} "
+                                   f"minibatch rows with {thr} OpenMP threads"
+                                   + ("" if rows == m else f"; row-proportional part scaled x{m / rows:g}, the update added unscaled")
+                                   + "; features precomputed (untimed) as the reference does"},
         "e2e": {"value": v, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference Julia 0.3 runtime unavailable on this box; timed: oracle/gpt_oracle.c (loop-faithful C "
-                "restatement of GPT_SGLD.jl:378-439, OpenMP over minibatch rows)",
+                "restatement of GPT_SGLD.jl:378-439, OpenMP over minibatch rows like GPT_SGLD_p.jl:70-108)",
         "wall_s": time.perf_counter() - t0,
     }
     emit(line)
@@ -159,7 +231,9 @@ def workload_config(args, W):
             "precision": args.precision, "langevin": True, "stiefel": True,
             "signal_var": SIGNAL_VAR, "epsw": eps_for(W["N"])[0], "epsU": eps_for(W["N"])[1],
             "l2": "inputs larger than L2: resident X is %.0f MB and every step gathers different random rows" % (W["N"] * W["D"] * 8 / 1e6),
-            "parallelism": f"row-sharded minibatch x{args.gpus} + NCCL all-reduce of Q+n*r*D doubles"}
+            "algorithm": args.alg,
+            "parallelism": f"minibatch rows sharded x{args.gpus}; NCCL all-reduce of the FP32 gradient buffer "
+                           f"(32*ceil32(Q) + D*npad*rpad floats) once per step; replicated FP64 update"}
 
 
 def main():
@@ -173,6 +247,8 @@ def main():
     ap.add_argument("--no-pred", action="store_true", help="skip the C5 prediction sweep")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline")
     ap.add_argument("--pred-samples", type=int, default=C5["S"])
+    ap.add_argument("--alg", default="auto", choices=["auto", "direct", "nodes"],
+                    help="gptb_set_option(GPTB_OPT_ALGORITHM): auto picks the node grid for large minibatches")
     args = ap.parse_args()
     W = WORKLOADS[args.workload]
     # stdout carries exactly ONE line (the JSON): libraries that print to fd 1 (NCCL's "NCCL version ..." banner under
@@ -221,6 +297,7 @@ def main():
     y = model.pred(mdl["w_true"], mdl["U_true"], X) + np.sqrt(SIGNAL_VAR) * rng.standard_normal(N)
     model.set_train(X, y)
     model.set_params(mdl["w0"], mdl["U0"])
+    model.set_option(L.OPT_ALGORITHM, {"auto": L.ALG_AUTO, "direct": L.ALG_DIRECT, "nodes": L.ALG_NODES}[args.alg])
     if world > 1:
         idt = torch.zeros(128, dtype=torch.uint8, device=dev)
         if rank == 0:
@@ -248,6 +325,12 @@ def main():
         barrier()
     ms_total = ev0.elapsed_time(ev1)
     _, launches = model.phase_ms(reset=True)
+    # the chain after warm-up + timed steps: identical at every GPU count up to summation order (same global
+    # minibatches, same Philox draws), so SCALE lines can be compared across N
+    w_chk, U_chk = model.get_params()
+    chain_checksum = {"w_norm2": float(np.linalg.norm(w_chk)), "U_normF": float(np.linalg.norm(U_chk.ravel())),
+                      "w_first3": [float(v) for v in w_chk[:3]], "U_dist_from_start": float(np.linalg.norm((U_chk - mdl["U0"]).ravel())),
+                      "steps_taken": int(max(3, args.warmup) + args.steps)}
     # per-phase device times come from a second, untimed pass: the phase events live on the main stream, so the
     # profiled step is the one-stream step (no dimension-group pipelining)
     kp = max(3, min(args.steps, 50))
@@ -301,6 +384,35 @@ def main():
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_s = float(te.item())
+    # the reference keeps EVERY post-burn-in sample (w and U, GPT_SGLD.jl:441-444): the same through gptb_sgld_run on a
+    # slice of the resident training set (one epoch of `ks` minibatches, thinning 1, stores copied back to the host)
+    stored = None
+    if rank == 0 or world > 1:
+        ks = max(2, min(args.steps, 40))
+        with G.Model(D, n, r, Q, precision=prec, device=local, seed=1234) as sm:
+            sm.set_features(feat); sm.set_index(mdl["I"])
+            sm.set_train(X[:ks * m], y[:ks * m]); sm.set_params(mdl["w0"], mdl["U0"])
+            sm.set_option(L.OPT_ALGORITHM, {"auto": L.ALG_AUTO, "direct": L.ALG_DIRECT, "nodes": L.ALG_NODES}[args.alg])
+            if world > 1:
+                idt2 = torch.zeros(128, dtype=torch.uint8, device=dev)
+                if rank == 0:
+                    idt2.copy_(torch.frombuffer(bytearray(G.comm_unique_id()), dtype=torch.uint8))
+                dist.broadcast(idt2, 0)
+                sm.comm_init(world, rank, bytes(idt2.cpu().numpy().tobytes()))
+            sm.sgld_run(SIGNAL_VAR, m, EPSW, EPSU, 0, 1, N=ks * m)          # warm (allocations)
+            sm.set_params(mdl["w0"], mdl["U0"])
+            barrier()
+            t0 = time.perf_counter()
+            ws_, Us_ = sm.sgld_run(SIGNAL_VAR, m, EPSW, EPSU, 0, 1, N=ks * m)
+            barrier()
+            dt_st = time.perf_counter() - t0
+        tst = torch.tensor([dt_st], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tst, op=dist.ReduceOp.MAX)
+        stored = {"value": ks / float(tst.item()), "unit": "steps/s", "steps": ks, "thin": 1,
+                  "d2h_bytes_per_step": int(8 * (Q + n * r * D)),
+                  "api": "gptb_sgld_run (resident data, w_store and U_store of every step copied back at the end of the run; "
+                         "includes the epoch's permutation)", "finite": bool(np.isfinite(ws_).all() and np.isfinite(Us_).all())}
 
     # ------------------------------------------------------------------ C5 posterior-predictive sweep (rows sharded)
     pred = None
@@ -351,35 +463,56 @@ def main():
     which_peak = "measured (MEASURED_PEAKS.json bf16_tflops_sustained: the kernels issue kind::f16 MMAs inside a long step)" \
         if peaks else "fallback (B200_PROFILING.md 1.4 PF sustained)"
     ml = m / world                                     # rows per rank
-    per_launch_flops = 2.0 * ml * n * r * D            # algorithmic tensor flops of ONE K1 or K3 launch
-    dom = "bwd" if phases["bwd"] >= phases["fwd"] else "fwd"
+    rpad = (r + 15) // 16 * 16
+    dom = max(("fwd", "contract", "bwd"), key=lambda k_: phases[k_])
     dom_ms = phases[dom] / args.steps
-    ach = per_launch_flops / (dom_ms * 1e-3) / 1e12 if dom_ms > 0 else None
-    peak_tf = bf16_sust
     sm_mhz = clk.summary()["sm_mhz"] or 1965.0
-    cos_peak = 16 * 148 * sm_mhz * 1e6                  # MUFU.COS: 16 / clk / SM (nominal), at the clock seen
-    roofline = {"kernel": {"fwd": "fwd_tc_kernel (K1)", "bwd": "bwd_tc_kernel (K3)"}[dom], "bound": "tensor",
-                "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": (ach / peak_tf) if ach else None,
-                # dram__bytes_read.sum + dram__bytes_write.sum of one K3 launch at this exact shape (ncu --set full,
-                # profiles/r1n_ncu_full_summary_C4_tc3.txt): 87.9 MB read (the E image, once per feature-block group)
-                # + 3.1 MB written; algorithmic bytes are 84 MB of E image + 2.6 MB of inputs + 1.3 MB of gradient
-                "traffic": 91066624 if (world == 1 and args.workload == "C4" and dom == "bwd") else None,
-                "peak_source": which_peak, "avg_launch_ms": dom_ms,
-                "algorithmic_flops_per_launch": per_launch_flops,
-                "sfu": {"cos_per_launch": ml * n * D, "achieved_Tcos_s": ml * n * D / (dom_ms * 1e-3) / 1e12 if dom_ms else None,
-                        "peak_Tcos_s": cos_peak / 1e12, "frac": (ml * n * D / (dom_ms * 1e-3)) / cos_peak if dom_ms else None,
-                        "peak_source": "nominal 16 MUFU/clk/SM x 148 SMs x sampled SM clock"},
-                "step": {"t_roof_us": max(4.0 * ml * n * r * D / (peak_tf * 1e12), ml * n * D / cos_peak) * 1e6,
-                         "t_step_us": ms_step * 1e3,
-                         "frac": max(4.0 * ml * n * r * D / (peak_tf * 1e12), ml * n * D / cos_peak) * 1e3 / ms_step,
-                         "definition": "SURVEY.md §8d: max(4mnrD/P_tc, mnD/P_sfu) / measured step; each feature credited once "
-                                       "although K3 re-evaluates it"},
-                "phase_ms_per_step": {k: v / args.steps for k, v in phases.items()}}
+    # MUFU.COS peak: measured by tools/ubench/pipes.cu on this pool (profiles/r2_ubench_pipes.txt: 15.2 / clk / SM)
+    cos_per_clk_sm = 15.2
+    cos_peak = cos_per_clk_sm * 148 * sm_mhz * 1e6
+    hbm = peaks.get("hbm_gbs", 6500.0)
+    traffic_tab = {}
+    try:
+        traffic_tab = json.load(open(os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")))
+    except Exception:
+        pass
+    kname = {"fwd": "fwd_tc_kernel", "contract": "contract_tc_kernel", "bwd": "bwd_tc_kernel"}[dom]
+    tkey = f"{args.workload}:{args.alg}:{kname}"
+    traffic = traffic_tab.get(tkey) if world == 1 else None
+    t_roof_step = max(4.0 * ml * n * r * D / (bf16_sust * 1e12), ml * n * D / cos_peak)
+    if dom == "contract":
+        # K2 is a gather machine bound by shared-memory bandwidth; the contract's roofline is its HBM figure: it reads
+        # T (D*r floats per row) and y, writes E (D*rpad floats per row, or the fp16 hi|lo image: same bytes) and fhat
+        alg_bytes = ml * (4.0 * D * r + 4.0 * D * rpad + 16.0)
+        ach = alg_bytes / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else None
+        roofline = {"kernel": "contract_tc_kernel (K2)", "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s",
+                    "frac": (ach / hbm) if ach else None, "traffic": traffic,
+                    "traffic_source": "profiles/r2_ncu_traffic.json" if traffic else None,
+                    "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback (B200_PROFILING.md)",
+                    "avg_launch_ms": dom_ms, "algorithmic_bytes_per_launch": alg_bytes,
+                    "smem": {"gathers_per_launch": ml * 2.0 * Q * D,
+                             "floor_us": ml / 64.0 * 15800.0 / 148.0 / (sm_mhz * 1e6) * 1e6,
+                             "note": "the binding resource: 15.8k LSU wavefronts per 64-row tile (ncu), one per clock per SM"}}
+    else:
+        per_launch_flops = 2.0 * ml * n * r * D        # algorithmic tensor flops of ONE K1 or K3 launch over the rows
+        ach = per_launch_flops / (dom_ms * 1e-3) / 1e12 if dom_ms > 0 else None
+        roofline = {"kernel": {"fwd": "fwd_tc_kernel (K1)", "bwd": "bwd_tc_kernel (K3)"}[dom], "bound": "sfu",
+                    "achieved": ach, "peak": bf16_sust, "unit": "TFLOP/s", "frac": (ach / bf16_sust) if ach else None,
+                    "traffic": traffic, "traffic_source": "profiles/r2_ncu_traffic.json" if traffic else None,
+                    "peak_source": which_peak, "avg_launch_ms": dom_ms, "algorithmic_flops_per_launch": per_launch_flops,
+                    "sfu": {"cos_per_launch": ml * n * D, "achieved_Tcos_s": ml * n * D / (dom_ms * 1e-3) / 1e12 if dom_ms else None,
+                            "peak_Tcos_s": cos_peak / 1e12, "frac": (ml * n * D / (dom_ms * 1e-3)) / cos_peak if dom_ms else None,
+                            "peak_source": "measured 15.2 MUFU.COS/clk/SM (tools/ubench/pipes.cu, profiles/r2_ubench_pipes.txt) "
+                                           "x 148 SMs x sampled SM clock"}}
+    roofline["step"] = {"t_roof_us": t_roof_step * 1e6, "t_step_us": ms_step * 1e3, "frac": t_roof_step * 1e3 / ms_step,
+                        "definition": "SURVEY.md 8d: max(4mnrD/P_tc, mnD/P_sfu) / measured step, each feature of each "
+                                      "minibatch row credited once whatever the algorithm evaluates"}
+    roofline["phase_ms_per_step"] = {k: v / args.steps for k, v in phases.items()}
 
     cpu = None
     if not args.no_cpu:
-        v, threads, sample = cpu_reference_steps_per_sec(W, mdl)
-        cpu = {"value": v, "unit": "steps/s", "cores": threads, "kind": "port", "sample": sample}
+        # the first rows of the e2e minibatch: the workload's own data
+        cpu, _ = cpu_baseline_object(W, mdl, 8192, 1024, 6.0, X[rows[0][:8192]], y[rows[0][:8192]])
 
     line = {
         "metric": "sgld_steps_per_sec", "value": value, "unit": "steps/s", "n_gpus": world, "steps": args.steps,
@@ -392,8 +525,9 @@ def main():
                 "d2h_bytes_per_step": int(Q * 8), "steps": ke,
                 "api": "gptb_sgld_step_host_submit / _wait (pinned host minibatch in, updated w out, every step; the copy of "
                        "minibatch s+1 overlaps step s)",
-                "blocking_api_value": 1.0 / e2e_blocking_s},
-        "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "pred": pred,
+                "blocking_api_value": 1.0 / e2e_blocking_s,
+                "stored_chain": stored},
+        "gpu_launches": launches, "chain_checksum": chain_checksum, "roofline": roofline, "cpu_baseline": cpu, "pred": pred,
     }
     emit(line)
     if world > 1:

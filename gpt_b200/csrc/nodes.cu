@@ -50,9 +50,10 @@ __device__ __forceinline__ void cheb_basis(float u, float (&t)[P]) {
 }
 
 // ------------------------------------------------------------------------------------------------ coefficients
-// grid (ceil(G*rpad/256), kn).  Tn[k][l][c*P + j] -> Cf[k][c*P + p][l]  (l fastest; columns r..rpad-1 are zero).
+// grid (ceil(G*rpad/256), kn).  Tn[k][l][c*P + j] -> Cf[k][c][l][PP]  (PP = P rounded up to 4: a lane reads the
+// coefficients of its column with 16-byte loads; columns r..rpad-1 and entries P..PP-1 are zero).
 __global__ void __launch_bounds__(256) node_coef_kernel(const float *__restrict__ Tn, float *__restrict__ Cf, int G, int P,
-                                                        int r, int rpad, int mnode, int mnpad) {
+                                                        int PP, int r, int rpad, int mnpad) {
     const int k = blockIdx.y;
     const int t = blockIdx.x * 256 + threadIdx.x;
     if (t >= G * rpad) return;
@@ -60,12 +61,12 @@ __global__ void __launch_bounds__(256) node_coef_kernel(const float *__restrict_
     float f[PMAX];
 #pragma unroll
     for (int j = 0; j < PMAX; ++j) f[j] = (j < P && l < r) ? Tn[((size_t)k * r + l) * mnpad + c * P + j] : 0.f;
-    float *out = Cf + ((size_t)k * mnode + (size_t)c * P) * rpad + l;
-    for (int p = 0; p < P; ++p) {
+    float *out = Cf + (((size_t)k * G + c) * rpad + l) * PP;
+    for (int p = 0; p < PP; ++p) {
         float a = 0.f;
 #pragma unroll
-        for (int j = 0; j < PMAX; ++j) a = fmaf(c_cheb[p * PMAX + j], f[j], a);   // (entries j >= P of the matrix are zero)
-        out[(size_t)p * rpad] = a;
+        for (int j = 0; j < PMAX; ++j) a = fmaf(c_cheb[p * PMAX + j], f[j], a);   // (rows / entries >= P of the matrix are zero)
+        out[p] = a;
     }
 }
 
@@ -73,21 +74,22 @@ __global__ void __launch_bounds__(256) node_coef_kernel(const float *__restrict_
 // grid (ceil(mext / IROWS), kn), 256 threads.  A CTA holds the coefficient table of its dimension in shared memory;
 // a warp takes 32 consecutive rows at a time, lane = column l: per row P conflict-free LDS + P FFMA, and the 32 x 32
 // block of results goes through a padded shared-memory tile so that T[k][l][i] is written with unit stride over rows.
-constexpr int IROWS = 1024;
+constexpr int IROWS = 512;
 constexpr int ITHREADS = 256;
 
 template <int P, int NL /* 32-column passes: rpad / 32 rounded up */>
 __global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restrict__ Cf, const int32_t *__restrict__ cell,
                                                           const float *__restrict__ uu, float *__restrict__ T, int r, int rpad,
-                                                          int mnode, int64_t bs, int64_t mpad, int64_t mext) {
+                                                          int G, int64_t bs, int64_t mpad, int64_t mext) {
     extern __shared__ __align__(16) float sm[];
+    constexpr int PP = (P + 3) & ~3;
     const int k = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    float *tab = sm;                                              // [mnode][rpad]
-    float *tile = sm + (size_t)mnode * rpad + warp * (32 * 33);   // per-warp [32][33]
+    float *tab = sm;                                                   // [G][rpad][PP]
+    float *tile = sm + (size_t)G * rpad * PP + warp * (32 * 33);       // per-warp [32][33]
     {
-        const float4 *src = reinterpret_cast<const float4 *>(Cf + (size_t)k * mnode * rpad);
+        const float4 *src = reinterpret_cast<const float4 *>(Cf + (size_t)k * G * rpad * PP);
         float4 *dst = reinterpret_cast<float4 *>(tab);
-        for (int t = tid; t < mnode * rpad / 4; t += ITHREADS) dst[t] = src[t];
+        for (int t = tid; t < G * rpad * PP / 4; t += ITHREADS) dst[t] = src[t];
     }
     __syncthreads();
     const int64_t row0 = (int64_t)blockIdx.x * IROWS;
@@ -100,23 +102,29 @@ __global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restric
 #pragma unroll
         for (int pass = 0; pass < NL; ++pass) {
             const int l = pass * 32 + lane;
-            const bool lv = l < rpad;
-            const float *tl = tab + (lv ? l : 0);
+            const float4 *tl = reinterpret_cast<const float4 *>(tab) + (size_t)(l < rpad ? l : 0) * (PP / 4);
 #pragma unroll 4
             for (int j = 0; j < 32; ++j) {
                 const int c = __shfl_sync(0xffffffffu, c_l, j);
                 const float u = __shfl_sync(0xffffffffu, u_l, j);
-                float tb[P];
-                cheb_basis<P>(u, tb);
-                const float *a = tl + (size_t)c * P * rpad;
-                float acc = 0.f;
+                float tb[PP];
+                cheb_basis<PP>(u, tb);                                // (entries P..PP-1 meet zero coefficients)
+                const float4 *a = tl + (size_t)c * rpad * (PP / 4);
+                float acc0 = 0.f, acc1 = 0.f;
 #pragma unroll
-                for (int p = 0; p < P; ++p) acc = fmaf(tb[p], a[(size_t)p * rpad], acc);
-                tile[j * 33 + lane] = acc;
+                for (int q = 0; q < PP / 4; ++q) {
+                    const float4 v = a[q];
+                    acc0 = fmaf(tb[4 * q], v.x, acc0);
+                    acc1 = fmaf(tb[4 * q + 1], v.y, acc1);
+                    acc0 = fmaf(tb[4 * q + 2], v.z, acc0);
+                    acc1 = fmaf(tb[4 * q + 3], v.w, acc1);
+                }
+                tile[j * 33 + lane] = acc0 + acc1;
             }
             __syncwarp();
             // rows beyond bs (dead rows of the last tile) hold T = 0, as K1 leaves them
             const bool live = i0 + lane < bs;
+#pragma unroll 8
             for (int ll = 0; ll < 32; ++ll) {
                 const int lo = pass * 32 + ll;
                 if (lo < r) Tk[(size_t)lo * mpad + i0 + lane] = live ? tile[lane * 33 + ll] : 0.f;
@@ -195,7 +203,7 @@ __global__ void __launch_bounds__(1024) cell_sort_kernel(const int32_t *__restri
 // grid (ceil(bs / SROWS), kn), 256 threads; lane = column l.  A warp walks 32 * SITER consecutive rows of the
 // dimension's cell-sorted order; the P moment sums of the current cell stay in registers and go to the global
 // table (FP32 RED, one 4*rpad-byte line per p) only when the cell changes.
-constexpr int SROWS = 1024;
+constexpr int SROWS = 512;
 constexpr int STHREADS = 256;
 
 template <int P, int NL>
@@ -203,6 +211,8 @@ __global__ void __launch_bounds__(STHREADS) spread_kernel(const float *__restric
                                                           const float *__restrict__ uu, const int32_t *__restrict__ sorted,
                                                           float *__restrict__ Mn, int rpad, int mnpad, int64_t bs,
                                                           int64_t mpad) {
+    extern __shared__ __align__(16) float sm[];
+    float (*stage)[NL][32][32] = reinterpret_cast<float (*)[NL][32][32]>(sm);   // per warp: the E rows of 32 batch rows
     const int k = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int32_t *ck = cell + (size_t)k * mpad, *sk = sorted + (size_t)k * mpad;
     const float *uk = uu + (size_t)k * mpad;
@@ -239,10 +249,24 @@ __global__ void __launch_bounds__(STHREADS) spread_kernel(const float *__restric
             c_l = ck[row_l];
             u_l = uk[row_l];
         }
+        // all 32 row loads of the block are issued before any is used (one row = one 4*rpad-byte line; the rows of a
+        // cell are scattered over the batch, so every load is a separate trip to L2)
+#pragma unroll
+        for (int a = 0; a < NL; ++a) {
+            const int l = a * 32 + lane;
+            float ev[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int row = __shfl_sync(0xffffffffu, row_l, j);      // (row 0 for the lanes past the end: a valid address)
+                ev[j] = l < rpad ? Ek[(size_t)row * rpad + l] : 0.f;
+            }
+#pragma unroll
+            for (int j = 0; j < 32; ++j) stage[warp][a][j][lane] = ev[j];
+        }
+        __syncwarp();
         const int cnt = (int)min((int64_t)32, s1 - sb);
         for (int j = 0; j < cnt; ++j) {
             const int c = __shfl_sync(0xffffffffu, c_l, j);
-            const int row = __shfl_sync(0xffffffffu, row_l, j);
             const float u = __shfl_sync(0xffffffffu, u_l, j);
             if (c != cur) {   // warp-uniform
                 flush();
@@ -252,12 +276,12 @@ __global__ void __launch_bounds__(STHREADS) spread_kernel(const float *__restric
             cheb_basis<P>(u, tb);
 #pragma unroll
             for (int a = 0; a < NL; ++a) {
-                const int l = a * 32 + lane;
-                const float e = l < rpad ? Ek[(size_t)row * rpad + l] : 0.f;
+                const float e = stage[warp][a][j][lane];
 #pragma unroll
                 for (int p = 0; p < P; ++p) acc[a][p] = fmaf(tb[p], e, acc[a][p]);
             }
         }
+        __syncwarp();
     }
     flush();
 }
@@ -374,7 +398,8 @@ int gptb_nodes_setup(gptb_handle *h) {
     const int64_t m = (int64_t)G * P;
     // the interpolation kernel keeps one dimension's table (m x rpad floats) plus its transpose tiles in shared memory;
     // the sort keeps 33 x G counters
-    if ((size_t)m * h->rpad * 4 + (ITHREADS / 32) * 32 * 33 * 4 > 200 * 1024 || (size_t)33 * G * 4 > 200 * 1024) return GPTB_OK;
+    const int PP = (P + 3) & ~3;
+    if ((size_t)G * PP * h->rpad * 4 + (ITHREADS / 32) * 32 * 33 * 4 > 200 * 1024 || (size_t)33 * G * 4 > 200 * 1024) return GPTB_OK;
     const int mnpad = (int)((m + 127) / 128 * 128);
     std::vector<double> lo(c.D), invh(c.D);
     std::vector<float> xn((size_t)c.D * mnpad, 0.f);
@@ -398,7 +423,7 @@ int gptb_nodes_setup(gptb_handle *h) {
     GPTB_TRY(nd_alloc(h, &g.invh, c.D));
     GPTB_TRY(nd_alloc(h, &g.XnF, (size_t)c.D * mnpad));
     GPTB_TRY(nd_alloc(h, &g.Tn, (size_t)c.D * c.r * mnpad));
-    GPTB_TRY(nd_alloc(h, &g.Cf, (size_t)c.D * m * h->rpad));
+    GPTB_TRY(nd_alloc(h, &g.Cf, (size_t)c.D * G * PP * h->rpad));
     GPTB_TRY(nd_alloc(h, &g.Mn, (size_t)c.D * mnpad * h->rpad));
     GPTB_TRY(nd_alloc(h, (unsigned char **)&g.Enimg, gptb_tc_eimg_bytes(h, mnpad)));
     GPTB_CUDA_OK(h, cudaMemcpy(g.lo, lo.data(), sizeof(double) * c.D, cudaMemcpyHostToDevice));
@@ -453,8 +478,9 @@ int gptb_nodes_forward_range(gptb_handle *h, const void *Uimg, int k0, int kn, c
     const gptb_config &c = h->cfg;
     (void)s;
     GPTB_TRY(gptb_launch_fwd_tc_range(h, g.XnF, Uimg, g.m, g.mnpad, g.Tn, k0, kn));
+    const int PP = (g.P + 3) & ~3;
     node_coef_kernel<<<dim3((g.G * h->rpad + 255) / 256, kn), 256, 0, h->stream>>>(
-        g.Tn + (size_t)k0 * c.r * g.mnpad, g.Cf + (size_t)k0 * g.m * h->rpad, g.G, g.P, c.r, h->rpad, g.m, g.mnpad);
+        g.Tn + (size_t)k0 * c.r * g.mnpad, g.Cf + (size_t)k0 * g.G * PP * h->rpad, g.G, g.P, PP, c.r, h->rpad, g.mnpad);
     h->launches++;
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;
@@ -465,12 +491,13 @@ int gptb_nodes_interp(gptb_handle *h, int64_t bs, float *T) {
     const gptb_config &c = h->cfg;
     const int64_t mext = (bs + 127) / 128 * 128;
     const int NL = (h->rpad + 31) / 32;
-    const size_t smem = ((size_t)g.m * h->rpad + (ITHREADS / 32) * 32 * 33) * sizeof(float);
+    const int PP = (g.P + 3) & ~3;
+    const size_t smem = ((size_t)g.G * PP * h->rpad + (ITHREADS / 32) * 32 * 33) * sizeof(float);
     const dim3 grid((unsigned)((mext + IROWS - 1) / IROWS), c.D);
 #define GPTB_CALL(PP, NN)                                                                                         \
     auto kfn = interp_kernel<PP, NN>;                                                                             \
     GPTB_CUDA_OK(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));           \
-    kfn<<<grid, ITHREADS, smem, h->stream>>>(g.Cf, g.cell, g.uu, T, c.r, h->rpad, g.m, bs, h->mpad, mext);
+    kfn<<<grid, ITHREADS, smem, h->stream>>>(g.Cf, g.cell, g.uu, T, c.r, h->rpad, g.G, bs, h->mpad, mext);
     GPTB_P_SWITCH(g.P, NL, GPTB_CALL)
 #undef GPTB_CALL
     h->launches++;
@@ -499,8 +526,11 @@ int gptb_nodes_spread(gptb_handle *h, int64_t bs) {
     const gptb_config &c = h->cfg;
     const int NL = (h->rpad + 31) / 32;
     const dim3 grid((unsigned)((bs + SROWS - 1) / SROWS), c.D);
-#define GPTB_CALL(PP, NN) \
-    spread_kernel<PP, NN><<<grid, STHREADS, 0, h->stream>>>(g.Erow, g.cell, g.uu, g.sorted, g.Mn, h->rpad, g.mnpad, bs, h->mpad);
+    const size_t smem = (size_t)(STHREADS / 32) * NL * 32 * 32 * sizeof(float);
+#define GPTB_CALL(PP, NN)                                                                                       \
+    auto kfn = spread_kernel<PP, NN>;                                                                           \
+    GPTB_CUDA_OK(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));         \
+    kfn<<<grid, STHREADS, smem, h->stream>>>(g.Erow, g.cell, g.uu, g.sorted, g.Mn, h->rpad, g.mnpad, bs, h->mpad);
     GPTB_P_SWITCH(g.P, NL, GPTB_CALL)
 #undef GPTB_CALL
     const int slot = (int)(g.steps & 1);
