@@ -1255,3 +1255,85 @@ int gptb_proj_geod_device(gptb_handle *h, cudaStream_t s, int n, int r, const do
     }
     return GPTB_OK;
 }
+
+// ================================================================================================
+// gptb_proj_noalloc — proj(U,V) for callers that must not allocate (CUDA graph capture, serving loops).
+// No counterpart in the reference (see include/gptb200.h).
+//
+// Same two kernels as gptb_proj (k_reduce_only -> k_proj_apply), but the r x r Gram scratch lives in the file-scope
+// device array below instead of a cudaMalloc'd block.  Every GPU that loads the library holds the array until exit.
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, taken once per device with that device current.
+// ================================================================================================
+constexpr int NOALLOC_MAX_R = 64;
+constexpr size_t NOALLOC_SCRATCH_DOUBLES = 3 * (size_t)NOALLOC_MAX_R * NOALLOC_MAX_R + NOALLOC_MAX_R;   // 98,816 bytes
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_SCRATCH_DOUBLES];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+double *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};   // device address of g_noalloc_scratch, per device ordinal
+}  // namespace
+
+// Set-up, once per device (the calling thread's current device): resolves the scratch address and opts the reduction
+// kernel into the dynamic shared memory it needs at r = 64.  Not thread-safe against a concurrent first call on the
+// same device (like the handles of this library: one caller at a time).
+static int noalloc_setup(int dev, double **out) {
+    if (g_noalloc_ptr[dev]) {
+        *out = g_noalloc_ptr[dev];
+        return GPTB_OK;
+    }
+    double *ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || !ptr) {
+        gptb_set_error(nullptr, "gptb_proj_noalloc: cudaGetSymbolAddress(scratch) on device %d: %s", dev, cudaGetErrorString(e));
+        return GPTB_ERR_CUDA;
+    }
+    e = cudaFuncSetAttribute(k_reduce_only, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    if (e != cudaSuccess) {
+        gptb_set_error(nullptr, "gptb_proj_noalloc: cudaFuncSetAttribute on device %d: %s", dev, cudaGetErrorString(e));
+        return GPTB_ERR_CUDA;
+    }
+    g_noalloc_ptr[dev] = ptr;
+    *out = ptr;
+    return GPTB_OK;
+}
+
+extern "C" int gptb_proj_noalloc(int32_t n, int32_t r, const double *U_dev, const double *V_dev, double *out_dev,
+                                 void *cuda_stream) {
+    if (!U_dev || !V_dev || !out_dev || n < 1 || r < 1) {
+        gptb_set_error(nullptr, "gptb_proj_noalloc: NULL pointer or n < 1 or r < 1 (n=%d, r=%d)", n, r);
+        return GPTB_ERR_ARG;
+    }
+    if (r > NOALLOC_MAX_R) {
+        gptb_set_error(nullptr, "gptb_proj_noalloc: r=%d exceeds the static scratch (r <= %d: %zu bytes per GPU); use gptb_proj",
+                       r, NOALLOC_MAX_R, NOALLOC_SCRATCH_DOUBLES * sizeof(double));
+        return GPTB_ERR_UNSUPPORTED;
+    }
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= NOALLOC_MAX_DEVICES) {
+        gptb_set_error(nullptr, "gptb_proj_noalloc: no usable current CUDA device (%s)", cudaGetErrorString(e));
+        return GPTB_ERR_CUDA;
+    }
+    double *scratch = nullptr;
+    GPTB_TRY(noalloc_setup(dev, &scratch));
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    SmallLayout L(r);
+    // the array keeps the previous call's sums: the accumulators this call adds into must start at zero
+    e = cudaMemsetAsync(scratch, 0, L.zero_count() * sizeof(double), s);
+    if (e != cudaSuccess) {
+        gptb_set_error(nullptr, "gptb_proj_noalloc: clearing the scratch: %s", cudaGetErrorString(e));
+        return GPTB_ERR_CUDA;
+    }
+    const int nb = (n + UP_ROWS - 1) / UP_ROWS;
+    const size_t sm1 = 2 * (size_t)UP_ROWS * r * sizeof(double);
+    k_reduce_only<<<nb, UP_THREADS, sm1, s>>>(U_dev, V_dev, scratch, n, r);
+    const int fb = (int)std::min<size_t>(((size_t)r * n + 255) / 256, 1024);
+    k_proj_apply<<<fb, 256, 0, s>>>(U_dev, V_dev, scratch + L.S1, n, r, out_dev);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        gptb_set_error(nullptr, "gptb_proj_noalloc: kernel launch: %s", cudaGetErrorString(e));
+        return GPTB_ERR_CUDA;
+    }
+    return GPTB_OK;
+}

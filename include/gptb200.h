@@ -138,6 +138,19 @@ int gptb_grad(gptb_handle *h, double signal_var, const int64_t *idx, int64_t sta
 /* ---- Stiefel manifold ---------------------------------------------------------------------- */
 /* proj(U,V) = V - U(U'V+V'U)/2, GPT_SGLD.jl:14-16.  Uses device `device` (-1 = current). */
 int gptb_proj(int32_t device, int32_t n, int32_t r, const double *U, const double *V, double *out);
+/* proj(U,V) without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same kernels and result as gptb_proj, but:
+ *   - U_dev, V_dev, out_dev are DEVICE pointers (n x r, column-major Float64) on the calling thread's CURRENT device,
+ *     and the work is only queued on cuda_stream (a cudaStream_t passed as void*; NULL = the default stream): the
+ *     call does not synchronise and calls no cudaMalloc / cudaFree / allocating library routine;
+ *   - the r x r Gram scratch is a static device array inside the library (98,816 bytes held by every GPU that loads
+ *     the library, until exit), so r <= 64; a larger r returns GPTB_ERR_UNSUPPORTED with a message (use gptb_proj);
+ *   - every call shares that array: it is cleared at the start of each call, and two calls whose work OVERLAPS on
+ *     the GPU (different streams, or concurrent host threads) race — queue them on one stream or order them with
+ *     events.  out_dev must not alias U_dev or V_dev. */
+int gptb_proj_noalloc(int32_t n, int32_t r, const double *U_dev, const double *V_dev, double *out_dev,
+                      void *cuda_stream);
 /* geod(U,mom,t), GPT_SGLD.jl:19-37.  Returns GPTB_GEODESIC_NAN and zeros(n,r) when expm gives NaN. */
 int gptb_geod(int32_t device, int32_t n, int32_t r, const double *U, const double *mom, double t, double *out);
 
