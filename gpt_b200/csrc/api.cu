@@ -249,7 +249,7 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
     const int32_t *rows = rows_dev ? rows_dev + lo : nullptr;
     struct CellGuard {
         gptb_handle *h;
-        ~CellGuard() { h->gather_cells = false; h->k2_Erow = nullptr; }
+        ~CellGuard() { h->gather_cells = false; h->k2_Erow = nullptr; h->k2_T_rowmajor = false; }
     } cell_guard{h};
     h->gather_cells = nodes;
     if (staged_host_batch) {
@@ -264,31 +264,26 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
         GPTB_TRY(gptb_launch_gather(h, rows, 0, lbs, lo));
     }
     h->gather_cells = false;
-    // the cell order of the batch is needed by the spreading kernel only: it runs beside K1 / interpolation / K2
-    const bool sort_aside = nodes && !skip_bwd && !h->profiling;
-    if (nodes && !skip_bwd) {
-        if (sort_aside) {
-            GPTB_TRY(pipe_init(h, 2));
-            GPTB_CUDA_OK(h, cudaEventRecord(h->evG[1], h->stream));
-            GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->side[1], h->evG[1], 0));
-            GPTB_TRY(gptb_nodes_sort(h, lbs, h->side[1]));
-            GPTB_CUDA_OK(h, cudaEventRecord(h->evR[1], h->side[1]));
-        } else {
-            GPTB_TRY(gptb_nodes_sort(h, lbs, h->stream));
-        }
-    }
+    if (nodes) GPTB_TRY(gptb_nodes_sort(h, lbs, h->stream));   // cell-sorted records: both row kernels walk them
     pt.done(GPTB_PHASE_GATHER);
     const double escale = ((double)N_total / (double)bs) / signal_var;  // (N/bs)/signal_var of :393,:407
     if (lbs > 0) {
         double *gU = h->grad + c.Q;
         if (nodes) {
             GPTB_TRY(gptb_nodes_forward_range(h, h->Uimg, 0, c.D, h->stream));
-            GPTB_TRY(gptb_nodes_interp(h, lbs, (float *)h->T));
+            GPTB_TRY(gptb_nodes_interp(h, lbs));
             h->k2_Erow = skip_bwd ? nullptr : h->nodes.Erow;   // K2 writes plain E rows instead of the operand image
-            GPTB_TRY(forward_contract(h, false, rows, h->w, h->U, h->Uimg, lbs, escale, true, &pt, true));
-            h->k2_Erow = nullptr;
+            h->k2_T_rowmajor = true;                           // ... and reads the interpolated T, row-major per sample
+            {
+                void *T_keep = h->T;
+                h->T = h->nodes.T2;
+                const int st = forward_contract(h, false, rows, h->w, h->U, h->Uimg, lbs, escale, true, &pt, true);
+                h->T = T_keep;
+                h->k2_Erow = nullptr;
+                h->k2_T_rowmajor = false;
+                GPTB_TRY(st);
+            }
             if (!skip_bwd) {
-                if (sort_aside) GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->evR[1], 0));
                 GPTB_TRY(gptb_nodes_spread(h, lbs));
                 GPTB_TRY(gptb_nodes_backward_range(h, gU, 0, c.D));
             }

@@ -55,8 +55,10 @@ struct gptb_nodes {
     void *Enimg = nullptr;                   // fp16 hi|lo operand image of the node weights (K3's B operand)
     int32_t *cell = nullptr;                 // [D][mpad] cell of every batch row
     float *uu = nullptr;                     // [D][mpad] position inside the cell, in [-1, 1]
-    int32_t *sorted = nullptr;               // [D][mpad] batch rows in cell order
+    int32_t *srow = nullptr, *sc = nullptr;  // [D][mpad] records (row, cell, u) of the batch in cell order (inside chunks)
+    float *su = nullptr;
     float *Erow = nullptr;                   // [D][mpad][rpad] FP32 E as K2 writes it for the spreading kernel
+    float *T2 = nullptr;                     // [D][mpad][rpad] interpolated T, row-major per sample (K2 transposes its tile)
     int64_t batch_mpad = 0;
     uint64_t steps = 0;
 };
@@ -134,6 +136,7 @@ struct gptb_handle {
     bool tc_emax_valid = false;
     bool gather_cells = false;         // set around a node-grid step: the gather also writes nodes.cell / nodes.uu
     bool k2_redo = false;              // set around the conditional second K2 launch (E-image scale guard, api.cu)
+    bool k2_T_rowmajor = false;        // K2 reads T as [D][mpad][rpad] (nodes.cu) instead of [D][r][mpad]
     float *k2_Erow = nullptr;          // when set, K2 writes plain FP32 E [D][mpad][rpad] instead of the operand image
 
     // update scratch
@@ -312,7 +315,12 @@ void gptb_nodes_free(gptb_handle *h);
 int gptb_nodes_setup(gptb_handle *h);
 int gptb_nodes_ensure_batch(gptb_handle *h);
 int gptb_nodes_forward_range(gptb_handle *h, const void *Uimg, int k0, int kn, cudaStream_t s);
-int gptb_nodes_interp(gptb_handle *h, int64_t bs, float *T);
+int gptb_nodes_interp(gptb_handle *h, int64_t bs);
+int gptb_nodes_launch_interp(gptb_handle *h, int P, const float *Cf, const int32_t *srow, const int32_t *sc, const float *su,
+                             float *T2, int ctot, int col0, int ncols, int G, int64_t row0, int64_t nrows, int64_t rec_stride,
+                             int64_t t2_stride, cudaStream_t s);
+int gptb_nodes_launch_sort(gptb_handle *h, const int32_t *cell, const float *uu, int32_t *srow, int32_t *sc, float *su, int G,
+                           int64_t bs, int64_t stride, cudaStream_t s);
 int gptb_nodes_sort(gptb_handle *h, int64_t bs, cudaStream_t s);
 int gptb_nodes_spread(gptb_handle *h, int64_t bs);
 int gptb_nodes_backward_range(gptb_handle *h, double *gradU, int k0, int kn);

@@ -59,6 +59,7 @@ struct ContractTcParams {
     int n_lists;             // entries of `lists` (multiple of 4)
     const int *redo_flag;    // redo != 0: the launch only rewrites the E image with a corrected fp16 scale, and only if
     int redo;                //   *redo_flag says the first pass left the safe range (tc_path.cu: check_escale_kernel)
+    int t_rowmajor;          // T is [D][mpad][rpad] (row-major per sample, written by the node-grid interpolation)
     float *Erow;             // optional plain FP32 copy of E, [D][mpad][rpad] (row-major per sample: the node-grid
                              //   spreading kernel reads one 4*rpad-byte line per row), instead of the operand image
 };
@@ -90,7 +91,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
 
     // ---- prologue: the 64-row tile of T (one 256-byte row piece per (k,l)) arrives by 16-byte cp.async, all pieces in
     // flight at once and no registers held; the tables are staged meanwhile
-    {
+    if (!p.t_rowmajor) {
         const float *src = p.T + (size_t)blockIdx.x * CRB;
         const uint32_t dst = tcx::smem_u32(Ts);
         for (int t = tid; t < DR * 16; t += CT_THREADS) {
@@ -100,6 +101,23 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
                          : "memory");
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
+    } else {
+        // [k][row][rpad] -> Ts[k*r + l][row]: a thread takes one row and four columns at a time (16-byte loads); lanes
+        // run along the rows, so the shared-memory stores are conflict-free and the eight loads that share a 128-byte
+        // line hit L1 after the first
+        float *Tf = reinterpret_cast<float *>(Ts);
+        const int q4 = rpad >> 2, total = CRB * D * q4;
+        for (int t = tid; t < total; t += CT_THREADS) {
+            const int rowt = t & (CRB - 1), rest = t >> 6;
+            const int k = rest / q4, q = rest - k * q4;
+            const float4 v = __ldg(reinterpret_cast<const float4 *>(p.T + ((size_t)k * p.mpad + (size_t)blockIdx.x * CRB + rowt) * rpad) + q);
+            const int l0 = 4 * q;
+            float *d = Tf + (size_t)(k * r + l0) * CRB + rowt;
+            if (l0 < r) d[0] = v.x;
+            if (l0 + 1 < r) d[CRB] = v.y;
+            if (l0 + 2 < r) d[2 * CRB] = v.z;
+            if (l0 + 3 < r) d[3 * CRB] = v.w;
+        }
     }
     for (int t = tid; t < Q * DP4; t += CT_THREADS) {
         int4 v = __ldg(reinterpret_cast<const int4 *>(p.off1) + t);
@@ -379,6 +397,7 @@ int gptb_launch_contract_tc(gptb_handle *h, const float *T, const double *w, con
     p.redo = h->k2_redo ? 1 : 0;
     p.redo_flag = h->nan_flag + 2;
     p.Erow = want_grad ? h->k2_Erow : nullptr;
+    p.t_rowmajor = h->k2_T_rowmajor ? 1 : 0;
     const int64_t mext = (bs + 127) / 128 * 128;  // rows beyond bs inside the last 128-tile are dead (zeros)
     dim3 grid((unsigned)(mext / CRB));
 #define GPTB_CONTRACT_CASE(DT)                                                                              \

@@ -8,7 +8,8 @@
 //
 //   forward   K1 (tc_path.cu, unchanged) runs on the G*P nodes  ->  Tn[k][l][node]
 //             node_coef_kernel : node values -> Chebyshev coefficients per cell (a P x P cosine transform)
-//             interp_kernel    : T[k][l][i] = sum_p T_p(u_ik) * coef[k][cell_ik][p][l]          (u in [-1,1] inside the cell)
+//             cell_sort_kernel : records (row, cell, u) of the batch in cell order, per dimension
+//             interp_kernel    : T2[k][i][l] = sum_p T_p(u_ik) * coef[k][cell_ik][l][p]         (u in [-1,1] inside the cell)
 //   backward  spread_kernel    : M[k][cell][p][l] += T_p(u_ik) * E[k][i][l]     (the adjoint of the interpolation, rows
 //                                visited in cell order so that a warp keeps the sums of a cell in registers)
 //             node_adj_kernel  : moments -> node weights (adjoint cosine transform), max|.| for the fp16 image scale
@@ -70,84 +71,26 @@ __global__ void __launch_bounds__(256) node_coef_kernel(const float *__restrict_
     }
 }
 
-// ------------------------------------------------------------------------------------------------ interpolation
-// grid (ceil(mext / IROWS), kn), 256 threads.  A CTA holds the coefficient table of its dimension in shared memory;
-// a warp takes 32 consecutive rows at a time, lane = column l: per row P conflict-free LDS + P FFMA, and the 32 x 32
-// block of results goes through a padded shared-memory tile so that T[k][l][i] is written with unit stride over rows.
-constexpr int IROWS = 512;
-constexpr int ITHREADS = 256;
+// ------------------------------------------------------------------------------------------------ cell sort
+// grid (ceil(bs / SCHUNK), D), 256 threads: the batch rows of one dimension are sorted by cell inside chunks of SCHUNK
+// rows (a stable counting sort: warp w owns 256 contiguous rows and a private histogram, equal cells inside a warp are
+// aggregated with match_any) and written out as records (row, cell, u) in sorted order.  Both row kernels below walk
+// the records: consecutive records share their cell, so a warp keeps that cell's coefficients / sums in registers.
+constexpr int SCHUNK = 2048;
+constexpr int SORT_T = 256;
 
-template <int P, int NL /* 32-column passes: rpad / 32 rounded up */>
-__global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restrict__ Cf, const int32_t *__restrict__ cell,
-                                                          const float *__restrict__ uu, float *__restrict__ T, int r, int rpad,
-                                                          int G, int64_t bs, int64_t mpad, int64_t mext) {
-    extern __shared__ __align__(16) float sm[];
-    constexpr int PP = (P + 3) & ~3;
+__global__ void __launch_bounds__(SORT_T) cell_sort_kernel(const int32_t *__restrict__ cell, const float *__restrict__ uu,
+                                                           int32_t *__restrict__ srow, int32_t *__restrict__ sc,
+                                                           float *__restrict__ su, int G, int64_t bs, int64_t mpad) {
+    extern __shared__ int hist[];          // [8][G] per-warp counts, then [G] cell bases
+    constexpr int NW = SORT_T / 32;
     const int k = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    float *tab = sm;                                                   // [G][rpad][PP]
-    float *tile = sm + (size_t)G * rpad * PP + warp * (32 * 33);       // per-warp [32][33]
-    {
-        const float4 *src = reinterpret_cast<const float4 *>(Cf + (size_t)k * G * rpad * PP);
-        float4 *dst = reinterpret_cast<float4 *>(tab);
-        for (int t = tid; t < G * rpad * PP / 4; t += ITHREADS) dst[t] = src[t];
-    }
-    __syncthreads();
-    const int64_t row0 = (int64_t)blockIdx.x * IROWS;
     const int32_t *ck = cell + (size_t)k * mpad;
     const float *uk = uu + (size_t)k * mpad;
-    float *Tk = T + (size_t)k * r * mpad;
-    for (int64_t i0 = row0 + warp * 32; i0 < min(row0 + IROWS, mext); i0 += (ITHREADS / 32) * 32) {
-        const int c_l = ck[i0 + lane];
-        const float u_l = uk[i0 + lane];
-#pragma unroll
-        for (int pass = 0; pass < NL; ++pass) {
-            const int l = pass * 32 + lane;
-            const float4 *tl = reinterpret_cast<const float4 *>(tab) + (size_t)(l < rpad ? l : 0) * (PP / 4);
-#pragma unroll 4
-            for (int j = 0; j < 32; ++j) {
-                const int c = __shfl_sync(0xffffffffu, c_l, j);
-                const float u = __shfl_sync(0xffffffffu, u_l, j);
-                float tb[PP];
-                cheb_basis<PP>(u, tb);                                // (entries P..PP-1 meet zero coefficients)
-                const float4 *a = tl + (size_t)c * rpad * (PP / 4);
-                float acc0 = 0.f, acc1 = 0.f;
-#pragma unroll
-                for (int q = 0; q < PP / 4; ++q) {
-                    const float4 v = a[q];
-                    acc0 = fmaf(tb[4 * q], v.x, acc0);
-                    acc1 = fmaf(tb[4 * q + 1], v.y, acc1);
-                    acc0 = fmaf(tb[4 * q + 2], v.z, acc0);
-                    acc1 = fmaf(tb[4 * q + 3], v.w, acc1);
-                }
-                tile[j * 33 + lane] = acc0 + acc1;
-            }
-            __syncwarp();
-            // rows beyond bs (dead rows of the last tile) hold T = 0, as K1 leaves them
-            const bool live = i0 + lane < bs;
-#pragma unroll 8
-            for (int ll = 0; ll < 32; ++ll) {
-                const int lo = pass * 32 + ll;
-                if (lo < r) Tk[(size_t)lo * mpad + i0 + lane] = live ? tile[lane * 33 + ll] : 0.f;
-            }
-            __syncwarp();
-        }
-    }
-}
-
-// ------------------------------------------------------------------------------------------------ cell sort
-// grid (kn), 1024 threads: a stable counting sort of the batch rows of one dimension by cell.  Warp w owns the
-// contiguous rows [w*chunk, (w+1)*chunk) and a private histogram, so there are no shared-memory atomics between warps;
-// equal cells inside a warp are aggregated with match_any.
-__global__ void __launch_bounds__(1024) cell_sort_kernel(const int32_t *__restrict__ cell, int32_t *__restrict__ sorted, int G,
-                                                         int64_t bs, int64_t mpad) {
-    extern __shared__ int hist[];          // [32][G]
-    const int k = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int32_t *ck = cell + (size_t)k * mpad;
-    int32_t *sk = sorted + (size_t)k * mpad;
-    for (int t = tid; t < 32 * G; t += 1024) hist[t] = 0;
+    const int64_t c0 = (int64_t)blockIdx.x * SCHUNK;
+    for (int t = tid; t < (NW + 1) * G; t += SORT_T) hist[t] = 0;
     __syncthreads();
-    const int64_t chunk = ((bs + 31) / 32 + 31) / 32 * 32;   // rows per warp, a multiple of 32
-    const int64_t lo = (int64_t)warp * chunk, hi = min(bs, lo + chunk);
+    const int64_t lo = c0 + warp * (SCHUNK / NW), hi = min(bs, lo + SCHUNK / NW);
     int *hw = hist + warp * G;
     for (int64_t i0 = lo; i0 < hi; i0 += 32) {
         const int64_t i = i0 + lane;
@@ -158,40 +101,44 @@ __global__ void __launch_bounds__(1024) cell_sort_kernel(const int32_t *__restri
         __syncwarp();
     }
     __syncthreads();
-    // exclusive prefix over (cell, warp) in cell-major order
-    for (int c = tid; c < G; c += 1024) {
+    for (int c = tid; c < G; c += SORT_T) {    // exclusive prefix over the warps of each cell, total into hist[NW][c]
         int run = 0;
-        for (int w = 0; w < 32; ++w) {
+#pragma unroll
+        for (int w = 0; w < NW; ++w) {
             const int v = hist[w * G + c];
             hist[w * G + c] = run;
             run += v;
         }
-        hist[32 * G + c] = run;            // total of the cell
+        hist[NW * G + c] = run;
     }
     __syncthreads();
-    if (warp == 0) {                        // scan of the cell totals, 32 at a time
+    if (warp == 0) {                            // exclusive scan of the cell totals, 32 at a time
         int base = 0;
-        for (int c0 = 0; c0 < G; c0 += 32) {
-            const int c = c0 + lane;
-            int v = c < G ? hist[32 * G + c] : 0, inc = v;
+        for (int cb = 0; cb < G; cb += 32) {
+            const int c = cb + lane;
+            const int v = c < G ? hist[NW * G + c] : 0;
+            int inc = v;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const int nb = __shfl_up_sync(0xffffffffu, inc, o);
                 if (lane >= o) inc += nb;
             }
-            if (c < G) hist[32 * G + c] = base + inc - v;
+            if (c < G) hist[NW * G + c] = base + inc - v;
             base += __shfl_sync(0xffffffffu, inc, 31);
         }
     }
     __syncthreads();
+    const size_t ob = (size_t)k * mpad + c0;
     for (int64_t i0 = lo; i0 < hi; i0 += 32) {
         const int64_t i = i0 + lane;
         const bool v = i < hi;
         const int c = v ? ck[i] : -1;
         const unsigned m = __match_any_sync(0xffffffffu, c);
         if (v) {
-            const int pos = hist[32 * G + c] + hw[c] + __popc(m & ((1u << lane) - 1u));
-            sk[pos] = (int32_t)i;
+            const int pos = hist[NW * G + c] + hw[c] + __popc(m & ((1u << lane) - 1u));
+            srow[ob + pos] = (int32_t)i;
+            sc[ob + pos] = c;
+            su[ob + pos] = uk[i];
         }
         __syncwarp();
         if (v && lane == __ffs(m) - 1) hw[c] += __popc(m);
@@ -199,24 +146,96 @@ __global__ void __launch_bounds__(1024) cell_sort_kernel(const int32_t *__restri
     }
 }
 
-// ------------------------------------------------------------------------------------------------ spreading
-// grid (ceil(bs / SROWS), kn), 256 threads; lane = column l.  A warp walks 32 * SITER consecutive rows of the
-// dimension's cell-sorted order; the P moment sums of the current cell stay in registers and go to the global
-// table (FP32 RED, one 4*rpad-byte line per p) only when the cell changes.
-constexpr int SROWS = 512;
-constexpr int STHREADS = 256;
+// ------------------------------------------------------------------------------------------------ interpolation
+// grid (ceil(nrows / (8 * IWROWS)), D), 256 threads.  A warp walks IWROWS consecutive records of one dimension; lane
+// = column (NL blocks of 32 columns: the sampler has ncols = rpad, the posterior sweep packs the columns of several
+// samples side by side).  The PP Chebyshev coefficients of (cell, column) sit in registers and are reloaded (16-byte
+// loads from L2) only when the cell changes; per row there is one basis recurrence shared by all columns, PP FFMA per
+// column and one 128-byte store per column block: T2[k][row][ncols] is row-major per sample, so the scattered rows
+// of a cell are still written as whole lines (the contraction kernels transpose while staging their tile).
+//   Cf: [k][cell][ctot][PP], this launch uses the columns [col0, col0 + ncols);  records / T2 rows start at row0.
+constexpr int ITHREADS = 256;
+constexpr int IWROWS = 64;
 
 template <int P, int NL>
-__global__ void __launch_bounds__(STHREADS) spread_kernel(const float *__restrict__ Erow, const int32_t *__restrict__ cell,
-                                                          const float *__restrict__ uu, const int32_t *__restrict__ sorted,
+__global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restrict__ Cf, const int32_t *__restrict__ srow,
+                                                          const int32_t *__restrict__ sc, const float *__restrict__ su,
+                                                          float *__restrict__ T2, int ctot, int col0, int ncols, int G,
+                                                          int64_t row0, int64_t nrows, int64_t rec_stride,
+                                                          int64_t t2_stride) {
+    constexpr int PP = (P + 3) & ~3;
+    const int k = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const size_t kb = (size_t)k * rec_stride + row0;
+    const float4 *Ck = reinterpret_cast<const float4 *>(Cf + (size_t)k * G * ctot * PP);
+    float *Tk = T2 + (size_t)k * t2_stride * ncols;
+    const int64_t s0 = ((int64_t)blockIdx.x * (ITHREADS / 32) + warp) * IWROWS, s1 = min(nrows, s0 + IWROWS);
+    float4 cf[NL][PP / 4];
+    int cur = -1;
+    for (int64_t sb = s0; sb < s1; sb += 32) {
+        const int64_t s = sb + lane;
+        int row_l = 0, c_l = -1;
+        float u_l = 0.f;
+        if (s < s1) {
+            row_l = srow[kb + s] - (int32_t)row0;   // records hold batch-global rows; T2 rows are relative to row0
+            c_l = sc[kb + s];
+            u_l = su[kb + s];
+        }
+        const int cnt = (int)min((int64_t)32, s1 - sb);
+        for (int j = 0; j < cnt; ++j) {
+            const int c = __shfl_sync(0xffffffffu, c_l, j);
+            const int row = __shfl_sync(0xffffffffu, row_l, j);
+            const float u = __shfl_sync(0xffffffffu, u_l, j);
+            if (c != cur) {   // warp-uniform
+                cur = c;
+#pragma unroll
+                for (int a = 0; a < NL; ++a) {
+                    const int col = col0 + min(a * 32 + lane, ncols - 1);
+#pragma unroll
+                    for (int q = 0; q < PP / 4; ++q) cf[a][q] = __ldg(Ck + ((size_t)c * ctot + col) * (PP / 4) + q);
+                }
+            }
+            float tb[PP];
+            cheb_basis<PP>(u, tb);                                // (entries P..PP-1 meet zero coefficients)
+#pragma unroll
+            for (int a = 0; a < NL; ++a) {
+                float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+                for (int q = 0; q < PP / 4; ++q) {
+                    acc0 = fmaf(tb[4 * q], cf[a][q].x, acc0);
+                    acc1 = fmaf(tb[4 * q + 1], cf[a][q].y, acc1);
+                    acc0 = fmaf(tb[4 * q + 2], cf[a][q].z, acc0);
+                    acc1 = fmaf(tb[4 * q + 3], cf[a][q].w, acc1);
+                }
+                const int l = a * 32 + lane;
+                if (l < ncols) Tk[(size_t)row * ncols + l] = acc0 + acc1;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ spreading
+// grid (ceil(bs / SROWS), D), 128 threads; lane = column l.  A warp walks 128 consecutive records in blocks of 32; the
+// E rows of a block (one 4*rpad-byte line per row, scattered over the batch) are brought into shared memory with
+// 16-byte cp.async, the next block in flight while the current one is used.  The P moment sums of the current cell
+// stay in registers and go to the global table (FP32 RED, one line per p) only when the cell changes.
+constexpr int SROWS = 512;
+constexpr int STHREADS = 128;
+
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src)
+                 : "memory");
+}
+
+template <int P, int NL>
+__global__ void __launch_bounds__(STHREADS) spread_kernel(const float *__restrict__ Erow, const int32_t *__restrict__ srow,
+                                                          const int32_t *__restrict__ sc, const float *__restrict__ su,
                                                           float *__restrict__ Mn, int rpad, int mnpad, int64_t bs,
                                                           int64_t mpad) {
     extern __shared__ __align__(16) float sm[];
-    float (*stage)[NL][32][32] = reinterpret_cast<float (*)[NL][32][32]>(sm);   // per warp: the E rows of 32 batch rows
     const int k = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int32_t *ck = cell + (size_t)k * mpad, *sk = sorted + (size_t)k * mpad;
-    const float *uk = uu + (size_t)k * mpad;
-    const float *Ek = Erow + (size_t)k * mpad * rpad;
+    float *stage = sm + (size_t)warp * 2 * 32 * rpad;     // [2][32][rpad] per warp
+    const size_t kb = (size_t)k * mpad;
+    const float *Ek = Erow + kb * rpad;
     float *Mk = Mn + (size_t)k * mnpad * rpad;
     constexpr int per_warp = SROWS / (STHREADS / 32);
     const int64_t s0 = (int64_t)blockIdx.x * SROWS + warp * per_warp, s1 = min(bs, s0 + per_warp);
@@ -240,30 +259,39 @@ __global__ void __launch_bounds__(STHREADS) spread_kernel(const float *__restric
             }
         }
     };
-    for (int64_t sb = s0; sb < s1; sb += 32) {
+    int row_n = 0, c_n = -1;
+    float u_n = 0.f;
+    // records of block `sb` into (row_n, c_n, u_n), its E rows into stage buffer `buf` (asynchronously)
+    auto fetch = [&](int64_t sb, int buf) {
         const int64_t s = sb + lane;
-        int row_l = 0, c_l = -1;
-        float u_l = 0.f;
+        row_n = 0; c_n = -1; u_n = 0.f;
         if (s < s1) {
-            row_l = sk[s];
-            c_l = ck[row_l];
-            u_l = uk[row_l];
+            row_n = srow[kb + s];
+            c_n = sc[kb + s];
+            u_n = su[kb + s];
         }
-        // all 32 row loads of the block are issued before any is used (one row = one 4*rpad-byte line; the rows of a
-        // cell are scattered over the batch, so every load is a separate trip to L2)
-#pragma unroll
-        for (int a = 0; a < NL; ++a) {
-            const int l = a * 32 + lane;
-            float ev[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const int row = __shfl_sync(0xffffffffu, row_l, j);      // (row 0 for the lanes past the end: a valid address)
-                ev[j] = l < rpad ? Ek[(size_t)row * rpad + l] : 0.f;
-            }
-#pragma unroll
-            for (int j = 0; j < 32; ++j) stage[warp][a][j][lane] = ev[j];
+        const int ppr = rpad / 4;                               // 16-byte pieces per row
+        float *dst = stage + (size_t)buf * 32 * rpad;
+        for (int t = lane; t < 32 * ppr; t += 32) {             // (32 * ppr is a multiple of 32: the shuffle is convergent)
+            const int j = t / ppr, part = t - j * ppr;
+            const int row = __shfl_sync(0xffffffffu, row_n, j);   // (row 0 for records past the end: a valid address)
+            cp_async16(dst + j * rpad + part * 4, Ek + (size_t)row * rpad + part * 4);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    if (s0 < s1) fetch(s0, 0);
+    int buf = 0;
+    for (int64_t sb = s0; sb < s1; sb += 32, buf ^= 1) {
+        const int c_l = c_n;
+        const float u_l = u_n;
+        if (sb + 32 < s1) {
+            fetch(sb + 32, buf ^ 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncwarp();
+        const float *src = stage + (size_t)buf * 32 * rpad;
         const int cnt = (int)min((int64_t)32, s1 - sb);
         for (int j = 0; j < cnt; ++j) {
             const int c = __shfl_sync(0xffffffffu, c_l, j);
@@ -276,7 +304,8 @@ __global__ void __launch_bounds__(STHREADS) spread_kernel(const float *__restric
             cheb_basis<P>(u, tb);
 #pragma unroll
             for (int a = 0; a < NL; ++a) {
-                const float e = stage[warp][a][j][lane];
+                const int l = a * 32 + lane;
+                const float e = l < rpad ? src[j * rpad + l] : 0.f;
 #pragma unroll
                 for (int p = 0; p < P; ++p) acc[a][p] = fmaf(tb[p], e, acc[a][p]);
             }
@@ -376,7 +405,7 @@ int nd_alloc(gptb_handle *h, T **p, size_t count) {
 void gptb_nodes_free(gptb_handle *h) {
     gptb_nodes &g = h->nodes;
     cudaFree(g.lo); cudaFree(g.invh); cudaFree(g.XnF); cudaFree(g.Tn); cudaFree(g.Cf); cudaFree(g.Mn); cudaFree(g.Enimg);
-    cudaFree(g.cell); cudaFree(g.uu); cudaFree(g.sorted); cudaFree(g.Erow);
+    cudaFree(g.cell); cudaFree(g.uu); cudaFree(g.srow); cudaFree(g.sc); cudaFree(g.su); cudaFree(g.Erow); cudaFree(g.T2);
     g = gptb_nodes();
 }
 
@@ -399,7 +428,9 @@ int gptb_nodes_setup(gptb_handle *h) {
     // the interpolation kernel keeps one dimension's table (m x rpad floats) plus its transpose tiles in shared memory;
     // the sort keeps 33 x G counters
     const int PP = (P + 3) & ~3;
-    if ((size_t)G * PP * h->rpad * 4 + (ITHREADS / 32) * 32 * 33 * 4 > 200 * 1024 || (size_t)33 * G * 4 > 200 * 1024) return GPTB_OK;
+    // bounds of convenience: the sort keeps 9 x G counters in shared memory, and a grid with more nodes than that is
+    // no shortcut any more
+    if ((size_t)(SORT_T / 32 + 1) * G * 4 > 64 * 1024 || (size_t)G * PP * h->rpad * 4 > (size_t)8 << 20) return GPTB_OK;
     const int mnpad = (int)((m + 127) / 128 * 128);
     std::vector<double> lo(c.D), invh(c.D);
     std::vector<float> xn((size_t)c.D * mnpad, 0.f);
@@ -444,31 +475,38 @@ int gptb_nodes_ensure_batch(gptb_handle *h) {
     GPTB_CUDA_OK(h, cudaStreamSynchronize(h->stream));
     GPTB_TRY(nd_alloc(h, &g.cell, (size_t)c.D * h->mpad));
     GPTB_TRY(nd_alloc(h, &g.uu, (size_t)c.D * h->mpad));
-    GPTB_TRY(nd_alloc(h, &g.sorted, (size_t)c.D * h->mpad));
+    GPTB_TRY(nd_alloc(h, &g.srow, (size_t)c.D * h->mpad));
+    GPTB_TRY(nd_alloc(h, &g.sc, (size_t)c.D * h->mpad));
+    GPTB_TRY(nd_alloc(h, &g.su, (size_t)c.D * h->mpad));
     GPTB_TRY(nd_alloc(h, &g.Erow, (size_t)c.D * h->mpad * h->rpad));
+    GPTB_TRY(nd_alloc(h, &g.T2, (size_t)c.D * h->mpad * h->rpad));
+    GPTB_CUDA_OK(h, cudaMemset(g.T2, 0, sizeof(float) * (size_t)c.D * h->mpad * h->rpad));   // dead rows stay finite
     g.batch_mpad = h->mpad;
     return GPTB_OK;
 }
 
-#define GPTB_P_SWITCH(P, NL, CALL)                \
-    switch ((P) * 4 + (NL)) {                     \
-        case 4 * 4 + 1: { CALL(4, 1); } break;    \
-        case 6 * 4 + 1: { CALL(6, 1); } break;    \
-        case 8 * 4 + 1: { CALL(8, 1); } break;    \
-        case 10 * 4 + 1: { CALL(10, 1); } break;  \
-        case 12 * 4 + 1: { CALL(12, 1); } break;  \
-        case 14 * 4 + 1: { CALL(14, 1); } break;  \
-        case 16 * 4 + 1: { CALL(16, 1); } break;  \
-        case 4 * 4 + 2: { CALL(4, 2); } break;    \
-        case 6 * 4 + 2: { CALL(6, 2); } break;    \
-        case 8 * 4 + 2: { CALL(8, 2); } break;    \
-        case 10 * 4 + 2: { CALL(10, 2); } break;  \
-        case 12 * 4 + 2: { CALL(12, 2); } break;  \
-        case 14 * 4 + 2: { CALL(14, 2); } break;  \
-        case 16 * 4 + 2: { CALL(16, 2); } break;  \
-        default:                                  \
-            gptb_set_error(h, "node grid: unsupported order P=%d", (P)); \
-            return GPTB_ERR_UNSUPPORTED;          \
+#define GPTB_P_SWITCH(P, NL, CALL) \
+    switch ((P) * 8 + (NL)) { \
+        case 4 * 8 + 1: { CALL(4, 1); } break; \
+        case 4 * 8 + 2: { CALL(4, 2); } break; \
+        case 6 * 8 + 1: { CALL(6, 1); } break; \
+        case 6 * 8 + 2: { CALL(6, 2); } break; \
+        case 8 * 8 + 1: { CALL(8, 1); } break; \
+        case 8 * 8 + 2: { CALL(8, 2); } break; \
+        case 10 * 8 + 1: { CALL(10, 1); } break; \
+        case 10 * 8 + 2: { CALL(10, 2); } break; \
+        case 12 * 8 + 1: { CALL(12, 1); } break; \
+        case 12 * 8 + 2: { CALL(12, 2); } break; \
+        case 14 * 8 + 1: { CALL(14, 1); } break; \
+        case 14 * 8 + 2: { CALL(14, 2); } break; \
+        case 16 * 8 + 1: { CALL(16, 1); } break; \
+        case 16 * 8 + 2: { CALL(16, 2); } break; \
+        case 12 * 8 + 3: { CALL(12, 3); } break; \
+        case 12 * 8 + 4: { CALL(12, 4); } break; \
+        case 12 * 8 + 5: { CALL(12, 5); } break; \
+        default: \
+            gptb_set_error(h, "node grid: unsupported order / column count (P=%d, %d column blocks)", (P), (NL)); \
+            return GPTB_ERR_UNSUPPORTED; \
     }
 
 // Forward for the dimensions [k0, k0+kn): K1 on the nodes, coefficients.  (The interpolation needs every dimension's
@@ -486,38 +524,47 @@ int gptb_nodes_forward_range(gptb_handle *h, const void *Uimg, int k0, int kn, c
     return GPTB_OK;
 }
 
-int gptb_nodes_interp(gptb_handle *h, int64_t bs, float *T) {
-    gptb_nodes &g = h->nodes;
-    const gptb_config &c = h->cfg;
-    const int64_t mext = (bs + 127) / 128 * 128;
-    const int NL = (h->rpad + 31) / 32;
-    const int PP = (g.P + 3) & ~3;
-    const size_t smem = ((size_t)g.G * PP * h->rpad + (ITHREADS / 32) * 32 * 33) * sizeof(float);
-    const dim3 grid((unsigned)((mext + IROWS - 1) / IROWS), c.D);
-#define GPTB_CALL(PP, NN)                                                                                         \
-    auto kfn = interp_kernel<PP, NN>;                                                                             \
-    GPTB_CUDA_OK(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));           \
-    kfn<<<grid, ITHREADS, smem, h->stream>>>(g.Cf, g.cell, g.uu, T, c.r, h->rpad, g.G, bs, h->mpad, mext);
-    GPTB_P_SWITCH(g.P, NL, GPTB_CALL)
+// Launches the interpolation over the records [row0, row0 + nrows) of every dimension, columns [col0, col0 + ncols)
+// of a coefficient table with ctot columns, into T2[k][row - row0][ncols] (t2_stride rows per dimension).
+int gptb_nodes_launch_interp(gptb_handle *h, int P, const float *Cf, const int32_t *srow, const int32_t *sc, const float *su,
+                             float *T2, int ctot, int col0, int ncols, int G, int64_t row0, int64_t nrows, int64_t rec_stride,
+                             int64_t t2_stride, cudaStream_t s) {
+    const int NL = (ncols + 31) / 32;
+    const dim3 grid((unsigned)((nrows + (ITHREADS / 32) * IWROWS - 1) / ((ITHREADS / 32) * IWROWS)), h->cfg.D);
+#define GPTB_CALL(PP, NN) \
+    interp_kernel<PP, NN><<<grid, ITHREADS, 0, s>>>(Cf, srow, sc, su, T2, ctot, col0, ncols, G, row0, nrows, rec_stride, t2_stride);
+    GPTB_P_SWITCH(P, NL, GPTB_CALL)
 #undef GPTB_CALL
     h->launches++;
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;
 }
 
-// Cell-sorted row order of the staged batch (depends on the batch only, not on the parameters).
-int gptb_nodes_sort(gptb_handle *h, int64_t bs, cudaStream_t s) {
+int gptb_nodes_interp(gptb_handle *h, int64_t bs) {
     gptb_nodes &g = h->nodes;
-    const size_t smem = (size_t)33 * g.G * sizeof(int);
+    return gptb_nodes_launch_interp(h, g.P, g.Cf, g.srow, g.sc, g.su, g.T2, h->rpad, 0, h->rpad, g.G, 0, bs, h->mpad, h->mpad,
+                                    h->stream);
+}
+
+// Cell-sorted records of `bs` rows (they depend on the rows only, not on the parameters).
+int gptb_nodes_launch_sort(gptb_handle *h, const int32_t *cell, const float *uu, int32_t *srow, int32_t *sc, float *su, int G,
+                           int64_t bs, int64_t stride, cudaStream_t s) {
+    const size_t smem = (size_t)(SORT_T / 32 + 1) * G * sizeof(int);
     static bool optin = false;
     if (!optin) {
-        cudaFuncSetAttribute(cell_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(cell_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
         optin = true;
     }
-    cell_sort_kernel<<<h->cfg.D, 1024, smem, s>>>(g.cell, g.sorted, g.G, bs, h->mpad);
+    cell_sort_kernel<<<dim3((unsigned)((bs + SCHUNK - 1) / SCHUNK), h->cfg.D), SORT_T, smem, s>>>(cell, uu, srow, sc, su, G, bs,
+                                                                                                  stride);
     h->launches++;
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;
+}
+
+int gptb_nodes_sort(gptb_handle *h, int64_t bs, cudaStream_t s) {
+    gptb_nodes &g = h->nodes;
+    return gptb_nodes_launch_sort(h, g.cell, g.uu, g.srow, g.sc, g.su, g.G, bs, h->mpad, s);
 }
 
 // Backward: spread the FP32 E rows K2 wrote (g.Erow) onto the nodes, build the node image, run K3 on the nodes.
@@ -526,11 +573,11 @@ int gptb_nodes_spread(gptb_handle *h, int64_t bs) {
     const gptb_config &c = h->cfg;
     const int NL = (h->rpad + 31) / 32;
     const dim3 grid((unsigned)((bs + SROWS - 1) / SROWS), c.D);
-    const size_t smem = (size_t)(STHREADS / 32) * NL * 32 * 32 * sizeof(float);
+    const size_t smem = (size_t)(STHREADS / 32) * 2 * 32 * h->rpad * sizeof(float);
 #define GPTB_CALL(PP, NN)                                                                                       \
     auto kfn = spread_kernel<PP, NN>;                                                                           \
     GPTB_CUDA_OK(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));         \
-    kfn<<<grid, STHREADS, smem, h->stream>>>(g.Erow, g.cell, g.uu, g.sorted, g.Mn, h->rpad, g.mnpad, bs, h->mpad);
+    kfn<<<grid, STHREADS, smem, h->stream>>>(g.Erow, g.srow, g.sc, g.su, g.Mn, h->rpad, g.mnpad, bs, h->mpad);
     GPTB_P_SWITCH(g.P, NL, GPTB_CALL)
 #undef GPTB_CALL
     const int slot = (int)(g.steps & 1);
