@@ -671,6 +671,7 @@ int gptb_destroy(gptb_handle *h) {
     }
     gptb_comm_destroy(h);
     gptb_nodes_free(h);
+    gptb_pred_nodes_free(h);
     dev_free(&h->Zt); dev_free(&h->b); dev_free(&h->ZtF); dev_free(&h->bF); dev_free(&h->I); dev_free(&h->grp_ptr); dev_free(&h->grp_q);
     dev_free(&h->ct_off1); dev_free(&h->ct_lptr); dev_free(&h->ct_lists);
     dev_free(&h->X); dev_free(&h->y); dev_free(&h->phi); dev_free(&h->order); dev_free(&h->order_tmp);
@@ -1152,6 +1153,8 @@ static int pred_impl(gptb_handle *h, const double *w_store, const double *U_stor
     if (Nt == 0) return GPTB_OK;
     const bool f64 = use_fp64(h, phi_mode);
     if (!f64) {
+        const int sn = gptb_pred_nodes(h, w_store, U_store, S, Xtest, Nt, mean_out, per_sample_out);
+        if (sn != GPTB_ERR_UNSUPPORTED) return sn;   // node grid not applicable (small sweeps, GPTB_ALG_DIRECT): direct path
         const int st = pred_tc_grouped(h, w_store, U_store, S, Xtest, Nt, mean_out, per_sample_out);
         if (st != GPTB_ERR_UNSUPPORTED) return st;   // shapes it does not cover use the per-sample path below
     }

@@ -43,6 +43,8 @@ void gptb_set_error(const gptb_handle *h, const char *fmt, ...);
 //     fhat double [mpad]
 //   grad   double [Q + n*r*D]      [gradw | gradU] in Julia order — the all-reduce buffer
 // ------------------------------------------------------------------------------------------
+struct gptb_pred_cache;   // pred_nodes.cu
+
 // Node grid of the tensor-core path (nodes.cu): the features are generated at G*P Chebyshev nodes per dimension
 // instead of at every minibatch row.
 struct gptb_nodes {
@@ -161,6 +163,7 @@ struct gptb_handle {
     double node_theta = 2.0;           // cell half-width times the largest |frequency| of the dimension
     bool grid_valid = false;
     gptb_nodes nodes;
+    gptb_pred_cache *pred_cache = nullptr;   // buffers of the node-grid posterior sweep (pred_nodes.cu), kept between calls
     bool have_domain = false;          // input domain known: from gptb_set_train (min / max of X) or gptb_set_domain
     double dom_lo[16] = {0}, dom_hi[16] = {0};
     double zmax[16] = {0};             // max_j |Zt[j,k]|
@@ -299,6 +302,14 @@ int gptb_launch_fwd_tc_cols(gptb_handle *h, const float *XbF, const void *Uimg, 
 int gptb_tc_pred_scale(gptb_handle *h, const double *U, size_t cnt, bool first);
 int gptb_tc_pred_scale_commit(gptb_handle *h);
 int gptb_tc_pack_group(gptb_handle *h, const double *Ug, int Sg, int NC, void *img);
+int gptb_tc_pack_group_scaled(gptb_handle *h, const double *Ug, int Sg, int NC, void *img, float *state, cudaStream_t s);
+int gptb_launch_contract_fwd2(gptb_handle *h, const float *T2, const double *w_group, int ns, int col0, int ncols, int64_t nrows,
+                              int64_t t2_stride, double *fh /*[ns][fh_stride] or null*/, int64_t fh_stride,
+                              double *mean_acc /*[nrows] or null*/, double mean_scale, cudaStream_t s);
+// pred_nodes.cu
+int gptb_pred_nodes(gptb_handle *h, const double *w_store, const double *U_store, int32_t S, const double *Xtest, int64_t Nt,
+                    double *mean_out, double *per_sample_out);
+void gptb_pred_nodes_free(gptb_handle *h);
 int gptb_launch_contract_fwd(gptb_handle *h, const float *T, const double *w_group, int Sg, int64_t bs, int64_t mpad,
                              int ncols_total, double *fh_group /*[Sg][mpad] or null*/, double *mean_acc /*[mpad] or null*/,
                              double mean_scale);
@@ -319,6 +330,9 @@ int gptb_nodes_interp(gptb_handle *h, int64_t bs);
 int gptb_nodes_launch_interp(gptb_handle *h, int P, const float *Cf, const int32_t *srow, const int32_t *sc, const float *su,
                              float *T2, int ctot, int col0, int ncols, int G, int64_t row0, int64_t nrows, int64_t rec_stride,
                              int64_t t2_stride, cudaStream_t s);
+int gptb_nodes_launch_coef_cols(gptb_handle *h, const float *Tn, float *Cf, int G, int P, int ncols, int tn_cols, int ctot,
+                                int col0, int mnpad, cudaStream_t s);
+int gptb_nodes_upload_cheb(gptb_handle *h, int P);
 int gptb_nodes_launch_sort(gptb_handle *h, const int32_t *cell, const float *uu, int32_t *srow, int32_t *sc, float *su, int G,
                            int64_t bs, int64_t stride, cudaStream_t s);
 int gptb_nodes_sort(gptb_handle *h, int64_t bs, cudaStream_t s);

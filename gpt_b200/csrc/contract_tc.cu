@@ -524,3 +524,128 @@ int gptb_launch_contract_fwd(gptb_handle *h, const float *T, const double *w_gro
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Forward-only contraction of the node-grid posterior sweep (pred_nodes.cu): the same sum as contract_fwd_kernel,
+//     fhat_s[i] = sum_q w_s[q] prod_k T[k, s*r + I[q,k], i]                       (computeV, computefhat :208-230)
+// but T comes row-major per sample from the interpolation kernel, T2[k][row][ncols] with the columns of sample s at
+// col0 + s*r, and is transposed into the [k*r + l][row] tile while it is staged.  grid = (64-row tiles, samples).
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+struct ContractFwd2Params {
+    const float *T2;
+    const double *w;         // [ns][Q]
+    const int32_t *off1;     // [Q][DP]
+    double *fh;              // [ns][fh_stride] or null
+    double *mean_acc;        // [nrows] or null
+    double mean_scale;
+    int64_t nrows, t2_stride, fh_stride;
+    int DP, r, Q, ncols, col0;
+};
+
+template <int DT>
+__global__ void __launch_bounds__(256) contract_fwd2_kernel(const ContractFwd2Params p) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int D = DT;
+    constexpr int DP4 = (DT + 3) / 4;
+    constexpr int NW = 8;
+    const int r = p.r, Q = p.Q, DR = D * r;
+    const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5, s = blockIdx.y;
+    const int64_t tile0 = (int64_t)blockIdx.x * CRB;
+    const int64_t i0 = tile0 + 2 * lane;
+    float2 *Ts = reinterpret_cast<float2 *>(smem_raw);           // [DR][32]
+    float *Tf = reinterpret_cast<float *>(Ts);                   // the same as [DR][64 rows]
+    float *ws = reinterpret_cast<float *>(Ts + (size_t)DR * 32); // [Q rounded up to 4]
+    float2 *Fs = reinterpret_cast<float2 *>(ws + ((Q + 3) & ~3)); // [NW][32]
+    for (int t = tid; t < Q; t += 256) ws[t] = (float)p.w[(size_t)s * Q + t];
+    const int cbase = p.col0 + s * r;
+    if (((r | p.ncols | cbase) & 3) == 0) {
+        // 16-byte pieces: thread = (row, k, piece); lanes along the rows (conflict-free stores)
+        const int q4 = r >> 2, total = CRB * D * q4;
+        for (int t = tid; t < total; t += 256) {
+            const int rowt = t & (CRB - 1), rest = t >> 6;
+            const int k = rest / q4, q = rest - k * q4;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (tile0 + rowt < p.nrows)
+                v = __ldg(reinterpret_cast<const float4 *>(p.T2 + ((size_t)k * p.t2_stride + tile0 + rowt) * p.ncols + cbase) + q);
+            float *d = Tf + (size_t)(k * r + 4 * q) * CRB + rowt;
+            d[0] = v.x; d[CRB] = v.y; d[2 * CRB] = v.z; d[3 * CRB] = v.w;
+        }
+    } else {
+        for (int t = tid; t < CRB * DR; t += 256) {
+            const int rowt = t & (CRB - 1), c = t >> 6;
+            const int k = c / r, l = c - k * r;
+            float v = 0.f;
+            if (tile0 + rowt < p.nrows) v = __ldg(p.T2 + ((size_t)k * p.t2_stride + tile0 + rowt) * p.ncols + cbase + l);
+            Tf[(size_t)c * CRB + rowt] = v;
+        }
+    }
+    __syncthreads();
+    const float2 *Trow = Ts + lane;
+    float2 f = make_float2(0.f, 0.f);
+#pragma unroll 2
+    for (int q = wp; q < Q; q += NW) {
+        const int4 *o = reinterpret_cast<const int4 *>(p.off1) + (size_t)q * DP4;
+        float2 v = make_float2(1.f, 1.f);
+#pragma unroll
+        for (int g4 = 0; g4 < DP4; ++g4) {
+            const int4 oo = __ldg(o + g4);
+            if (g4 * 4 + 0 < D) v = mul2(v, Trow[oo.x]);
+            if (g4 * 4 + 1 < D) v = mul2(v, Trow[oo.y]);
+            if (g4 * 4 + 2 < D) v = mul2(v, Trow[oo.z]);
+            if (g4 * 4 + 3 < D) v = mul2(v, Trow[oo.w]);
+        }
+        const float wq = ws[q];
+        f = __ffma2_rn(make_float2(wq, wq), v, f);
+    }
+    Fs[wp * 32 + lane] = f;
+    __syncthreads();
+    if (wp == 0) {
+        f = Fs[lane];
+#pragma unroll
+        for (int t = 1; t < NW; ++t) f = add2(f, Fs[t * 32 + lane]);
+        const bool live0 = i0 < p.nrows, live1 = i0 + 1 < p.nrows;
+        if (p.fh) {
+            if (live0) p.fh[(size_t)s * p.fh_stride + i0] = (double)f.x;
+            if (live1) p.fh[(size_t)s * p.fh_stride + i0 + 1] = (double)f.y;
+        }
+        if (p.mean_acc) {
+            if (live0) atomicAdd(&p.mean_acc[i0], p.mean_scale * (double)f.x);
+            if (live1) atomicAdd(&p.mean_acc[i0 + 1], p.mean_scale * (double)f.y);
+        }
+    }
+}
+
+}  // namespace
+
+int gptb_launch_contract_fwd2(gptb_handle *h, const float *T2, const double *w_group, int ns, int col0, int ncols, int64_t nrows,
+                              int64_t t2_stride, double *fh, int64_t fh_stride, double *mean_acc, double mean_scale,
+                              cudaStream_t s) {
+    const gptb_config &c = h->cfg;
+    const size_t smem = (size_t)c.D * c.r * 32 * sizeof(float2) + (size_t)((c.Q + 3) & ~3) * sizeof(float) +
+                        8 * 32 * sizeof(float2) + 64;
+    if (smem > 227 * 1024 || !h->ct_off1) return GPTB_ERR_UNSUPPORTED;
+    ContractFwd2Params p;
+    p.T2 = T2; p.w = w_group; p.off1 = h->ct_off1; p.fh = fh; p.mean_acc = mean_acc; p.mean_scale = mean_scale;
+    p.nrows = nrows; p.t2_stride = t2_stride; p.fh_stride = fh_stride;
+    p.DP = (c.D + 3) & ~3; p.r = c.r; p.Q = c.Q; p.ncols = ncols; p.col0 = col0;
+    dim3 grid((unsigned)((nrows + CRB - 1) / CRB), (unsigned)ns);
+#define GPTB_CONTRACT_CASE(DT)                                                                              \
+    case DT: {                                                                                              \
+        auto kfn = contract_fwd2_kernel<DT>;                                                                \
+        GPTB_CUDA_OK(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        kfn<<<grid, 256, smem, s>>>(p);                                                                     \
+    } break;
+    switch (c.D) {
+        GPTB_CONTRACT_CASE(1) GPTB_CONTRACT_CASE(2) GPTB_CONTRACT_CASE(3) GPTB_CONTRACT_CASE(4)
+        GPTB_CONTRACT_CASE(5) GPTB_CONTRACT_CASE(6) GPTB_CONTRACT_CASE(7) GPTB_CONTRACT_CASE(8)
+        GPTB_CONTRACT_CASE(9) GPTB_CONTRACT_CASE(10) GPTB_CONTRACT_CASE(11) GPTB_CONTRACT_CASE(12)
+        GPTB_CONTRACT_CASE(13) GPTB_CONTRACT_CASE(14) GPTB_CONTRACT_CASE(15) GPTB_CONTRACT_CASE(16)
+        default: return GPTB_ERR_UNSUPPORTED;
+    }
+#undef GPTB_CONTRACT_CASE
+    h->launches++;
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    return GPTB_OK;
+}

@@ -71,6 +71,27 @@ __global__ void __launch_bounds__(256) node_coef_kernel(const float *__restrict_
     }
 }
 
+// The same for `ncols` columns of a wider table (posterior sweep: the columns of several samples side by side):
+// Tn[k][col][c*P + j] (tn_cols columns per dimension) -> Cf[k][c][col0 + col][PP] of a table with ctot columns.
+// grid (ceil(G*ncols/256), D).
+__global__ void __launch_bounds__(256) node_coef_cols_kernel(const float *__restrict__ Tn, float *__restrict__ Cf, int G, int P,
+                                                             int PP, int ncols, int tn_cols, int ctot, int col0, int mnpad) {
+    const int k = blockIdx.y;
+    const int t = blockIdx.x * 256 + threadIdx.x;
+    if (t >= G * ncols) return;
+    const int col = t % ncols, c = t / ncols;
+    float f[PMAX];
+#pragma unroll
+    for (int j = 0; j < PMAX; ++j) f[j] = j < P ? Tn[((size_t)k * tn_cols + col) * mnpad + c * P + j] : 0.f;
+    float *out = Cf + (((size_t)k * G + c) * ctot + col0 + col) * PP;
+    for (int p = 0; p < PP; ++p) {
+        float a = 0.f;
+#pragma unroll
+        for (int j = 0; j < PMAX; ++j) a = fmaf(c_cheb[p * PMAX + j], f[j], a);
+        out[p] = a;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ cell sort
 // grid (ceil(bs / SCHUNK), D), 256 threads: the batch rows of one dimension are sorted by cell inside chunks of SCHUNK
 // rows (a stable counting sort: warp w owns 256 contiguous rows and a private histogram, equal cells inside a warp are
@@ -147,7 +168,7 @@ __global__ void __launch_bounds__(SORT_T) cell_sort_kernel(const int32_t *__rest
 }
 
 // ------------------------------------------------------------------------------------------------ interpolation
-// grid (ceil(nrows / (8 * IWROWS)), D), 256 threads.  A warp walks IWROWS consecutive records of one dimension; lane
+// grid (ceil(nrows / (8 * IWROWS)), D), 256 threads.  A warp walks IWROWS (8..64) consecutive records of one dimension; lane
 // = column (NL blocks of 32 columns: the sampler has ncols = rpad, the posterior sweep packs the columns of several
 // samples side by side).  The PP Chebyshev coefficients of (cell, column) sit in registers and are reloaded (16-byte
 // loads from L2) only when the cell changes; per row there is one basis recurrence shared by all columns, PP FFMA per
@@ -155,14 +176,16 @@ __global__ void __launch_bounds__(SORT_T) cell_sort_kernel(const int32_t *__rest
 // of a cell are still written as whole lines (the contraction kernels transpose while staging their tile).
 //   Cf: [k][cell][ctot][PP], this launch uses the columns [col0, col0 + ncols);  records / T2 rows start at row0.
 constexpr int ITHREADS = 256;
-constexpr int IWROWS = 64;
 
 template <int P, int NL>
 __global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restrict__ Cf, const int32_t *__restrict__ srow,
                                                           const int32_t *__restrict__ sc, const float *__restrict__ su,
                                                           float *__restrict__ T2, int ctot, int col0, int ncols, int G,
                                                           int64_t row0, int64_t nrows, int64_t rec_stride,
-                                                          int64_t t2_stride) {
+                                                          int64_t t2_stride, int IWROWS) {
+    // IWROWS records per warp, chosen by the launcher: few enough that the grid fills the chip with ~32 warps per SM
+    // (a chunk of the posterior sweep has only 65536 (row, dimension) items), many enough that a cell's coefficients
+    // are reused
     constexpr int PP = (P + 3) & ~3;
     const int k = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const size_t kb = (size_t)k * rec_stride + row0;
@@ -524,15 +547,36 @@ int gptb_nodes_forward_range(gptb_handle *h, const void *Uimg, int k0, int kn, c
     return GPTB_OK;
 }
 
+int gptb_nodes_launch_coef_cols(gptb_handle *h, const float *Tn, float *Cf, int G, int P, int ncols, int tn_cols, int ctot,
+                                int col0, int mnpad, cudaStream_t s) {
+    node_coef_cols_kernel<<<dim3((G * ncols + 255) / 256, h->cfg.D), 256, 0, s>>>(Tn, Cf, G, P, (P + 3) & ~3, ncols, tn_cols, ctot,
+                                                                                  col0, mnpad);
+    h->launches++;
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    return GPTB_OK;
+}
+
+// The cosine-transform matrix of order P (shared by every grid of the library: the sampler's and the sweep's).
+int gptb_nodes_upload_cheb(gptb_handle *h, int P) {
+    std::vector<float> cm((size_t)PMAX * PMAX, 0.f);
+    for (int p = 0; p < P; ++p)
+        for (int j = 0; j < P; ++j) cm[(size_t)p * PMAX + j] = (float)((p == 0 ? 1.0 : 2.0) / P * std::cos(M_PI * p * (j + 0.5) / P));
+    GPTB_CUDA_OK(h, cudaMemcpyToSymbol(c_cheb, cm.data(), sizeof(float) * PMAX * PMAX));
+    return GPTB_OK;
+}
+
 // Launches the interpolation over the records [row0, row0 + nrows) of every dimension, columns [col0, col0 + ncols)
 // of a coefficient table with ctot columns, into T2[k][row - row0][ncols] (t2_stride rows per dimension).
 int gptb_nodes_launch_interp(gptb_handle *h, int P, const float *Cf, const int32_t *srow, const int32_t *sc, const float *su,
                              float *T2, int ctot, int col0, int ncols, int G, int64_t row0, int64_t nrows, int64_t rec_stride,
                              int64_t t2_stride, cudaStream_t s) {
     const int NL = (ncols + 31) / 32;
+    int IWROWS = 64;
+    while (IWROWS > 8 && nrows * h->cfg.D / IWROWS < (int64_t)h->sm_count * 32) IWROWS >>= 1;
     const dim3 grid((unsigned)((nrows + (ITHREADS / 32) * IWROWS - 1) / ((ITHREADS / 32) * IWROWS)), h->cfg.D);
-#define GPTB_CALL(PP, NN) \
-    interp_kernel<PP, NN><<<grid, ITHREADS, 0, s>>>(Cf, srow, sc, su, T2, ctot, col0, ncols, G, row0, nrows, rec_stride, t2_stride);
+#define GPTB_CALL(PP, NN)                                                                                                   \
+    interp_kernel<PP, NN><<<grid, ITHREADS, 0, s>>>(Cf, srow, sc, su, T2, ctot, col0, ncols, G, row0, nrows, rec_stride, t2_stride, \
+                                                    IWROWS);
     GPTB_P_SWITCH(P, NL, GPTB_CALL)
 #undef GPTB_CALL
     h->launches++;

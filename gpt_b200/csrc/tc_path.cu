@@ -857,6 +857,21 @@ int gptb_tc_pack_group(gptb_handle *h, const double *Ug, int Sg, int NC, void *i
     return GPTB_OK;
 }
 
+// Scale and pack one sample group on its own: state -> {max|U| of the group, 2^k, 2^-k}; the forward kernel is given
+// state + 1 as its scale.  (The node-grid sweep uploads U_store group by group, so no global maximum exists up front.)
+int gptb_tc_pack_group_scaled(gptb_handle *h, const double *Ug, int Sg, int NC, void *img, float *state, cudaStream_t s) {
+    const gptb_config &c = h->cfg;
+    const size_t cnt = (size_t)Sg * c.D * c.r * c.n, total = (size_t)c.D * h->npad * NC;
+    GPTB_CUDA_OK(h, cudaMemsetAsync(state, 0, sizeof(float), s));
+    absmax_kernel<<<std::min<int>(h->sm_count, (int)((cnt + 1023) / 1024)), 1024, 0, s>>>(Ug, cnt, state);
+    set_scale_kernel<<<1, 1, 0, s>>>(state, state + 1, 0);
+    pack_Ugroup_kernel<<<(int)std::min<size_t>((total + 255) / 256, (size_t)h->sm_count * 8), 256, 0, s>>>(
+        Ug, Sg, c.D, c.n, c.r, h->npad, NC, state + 1, (__half *)img);
+    h->launches += 3;
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    return GPTB_OK;
+}
+
 int gptb_tc_ensure_gradF(gptb_handle *h) {
     if (h->gradFbase) return GPTB_OK;
     const size_t gf = (size_t)h->cfg.D * h->npad * h->rpad;

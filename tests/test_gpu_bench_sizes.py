@@ -90,10 +90,12 @@ def test_c4_escale_guard_residual_jumps(c4, alg):
             assert np.isfinite(w).all() and np.isfinite(U).all()
 
 
-@pytest.mark.parametrize("prec", [L.PREC_TC3, L.PREC_FP64], ids=["tc3", "fp64"])
-def test_c5_pred_samples_200(prec):
-    """C5 geometry: D=8, n=500, r=20, Q=200, S=200 stored samples (50 sample groups on the direct tensor-core path),
-    Nt = 40000 test rows (several row chunks); mean and per-sample predictions against oracle.pred on a row subset."""
+@pytest.mark.parametrize("prec,alg", [(L.PREC_TC3, L.ALG_DIRECT), (L.PREC_TC3, L.ALG_NODES), (L.PREC_FP64, L.ALG_DIRECT)],
+                         ids=["tc3-direct", "tc3-nodes", "fp64"])
+def test_c5_pred_samples_200(prec, alg):
+    """C5 geometry: D=8, n=500, r=20, Q=200, S=200 stored samples (50 sample groups on the direct tensor-core path, 25
+    column groups of 8 samples on the node grid), Nt = 40000 test rows (several row chunks on both paths); mean and
+    per-sample predictions against oracle.pred on a row subset."""
     D, n, r, Q, S, Nt = 8, 500, 20, 200, 200, 40000
     if prec == L.PREC_FP64:
         S, Nt = 24, 6000                       # the FP64 path is the per-sample validation loop: keep it short
@@ -106,7 +108,7 @@ def test_c5_pred_samples_200(prec):
         for k in range(D):
             Us[:, :, k, s] = np.linalg.qr(P["U_true"][:, :, k] + 0.01 * rng.standard_normal((n, r)))[0]
     f = G.feature(Xt, P["ls"], 1.0, P["phi_scale"], P["Z"], P["b"])
-    mean, per = G.pred_samples(ws, Us, P["I"], f, per_sample=True, precision=prec)
+    mean, per = G.pred_samples(ws, Us, P["I"], f, per_sample=True, precision=prec, options={L.OPT_ALGORITHM: alg})
     assert mean.shape == (Nt,) and per.shape == (Nt, S)
     sub = np.arange(0, Nt, 20)                 # 2000 rows spread over all row chunks
     phi = P["phi_fn"](Xt[sub])

@@ -615,3 +615,31 @@ def test_nodes_GPTregression_vs_oracle():
                              precision=L.PREC_TC3, w0=P["w0"], U0=P["U0"], perms=np.stack(perms), noise_w=NW, noise_U=NU,
                              options={L.OPT_ALGORITHM: L.ALG_NODES})
     assert relerr(gw, ws) < 1e-4 and relerr(gU, Us) < 1e-4
+
+
+@pytest.mark.parametrize("r,S,order,feature2", [(4, 5, 12, True), (5, 37, 12, False), (20, 11, 8, False), (33, 3, 16, False)])
+def test_nodes_pred_samples_vs_oracle(r, S, order, feature2):
+    """Posterior sweep on the node grid (pred_nodes.cu) forced on at small sizes: r not a multiple of 4 (scalar tile
+    loads), more samples than one column group (ragged last group), orders other than 12 (64-column groups), r > 32;
+    mean, per-sample output and the mean-only call against oracle.pred."""
+    P = make_problem(4, 3000, 24 if feature2 else 40, r, Q=30, seed=31, feature2=feature2)
+    rng = np.random.default_rng(1)
+    ws = np.asfortranarray(rng.standard_normal((P["Q"], S)))
+    Us = np.asfortranarray(np.stack([np.stack([o.stiefel_from_gaussian(rng.standard_normal((P["r"], P["n"])))
+                                               for _ in range(P["D"])], 2) for _ in range(S)], 3))
+    phi = P["phi_fn"](P["X"])
+    want = np.stack([o.pred(ws[:, s], Us[:, :, :, s], P["I"], phi) for s in range(S)], 1)
+    opts = {L.OPT_ALGORITHM: L.ALG_NODES, L.OPT_NODE_ORDER: order}
+    mean, per = G.pred_samples(ws, Us, P["I"], _feat(P), per_sample=True, precision=L.PREC_TC3, options=opts)
+    assert relerr(per, want) < 1e-4 and relerr(mean, want.mean(1)) < 1e-4
+    for s in (0, S - 1):
+        assert relerr(per[:, s], want[:, s]) < 1e-4, s
+    only_mean = G.pred_samples(ws, Us, P["I"], _feat(P), precision=L.PREC_TC3, options=opts)
+    assert relerr(only_mean, want.mean(1)) < 1e-4
+    # a single parameter set through pred(), and a second call on the same handle with fewer rows (cached buffers)
+    with _model(P, L.PREC_TC3, train=False) as m:
+        m.set_option(L.OPT_ALGORITHM, L.ALG_NODES)
+        m.set_option(L.OPT_NODE_ORDER, order)
+        a = m.pred(ws[:, 0], Us[:, :, :, 0], P["X"])
+        b = m.pred(ws[:, 1], Us[:, :, :, 1], P["X"][:777])
+    assert relerr(a, want[:, 0]) < 1e-4 and relerr(b, want[:777, 1]) < 1e-4

@@ -16,8 +16,10 @@ Xt = np.asfortranarray(rng.standard_normal((Nt, C["D"])))
 ws = np.asfortranarray(pm["w_true"][:, None] + 0.05 * rng.standard_normal((B.Q, S)))
 Us = np.asfortranarray(np.repeat(pm["U_true"][:, :, :, None], S, axis=3))
 pf = G.feature(Xt, pm["ls"], 1.0, pm["phi_scale"], pm["Z"], pm["b"])
+ALG = {"auto": L.ALG_AUTO, "direct": L.ALG_DIRECT, "nodes": L.ALG_NODES}[sys.argv[3] if len(sys.argv) > 3 else "auto"]
 with G.Model(C["D"], C["n"], C["r"], B.Q, precision=L.PREC_TC3, device=0) as m:
     m.set_features(pf); m.set_index(pm["I"])
+    m.set_option(L.OPT_ALGORITHM, ALG)
     for it in range(3):
         t0 = time.perf_counter()
         mean = m.pred_samples(ws, Us, Xt)
