@@ -24,9 +24,9 @@ class Config(C.Structure):
 OK, ERR_ARG, ERR_SHAPE, ERR_STATE, ERR_CUDA, ERR_NCCL, ERR_NOMEM, GEODESIC_NAN, ERR_UNSUPPORTED = range(9)
 PREC_FP64, PREC_TC3, PREC_TC1 = 0, 1, 2
 FEAT_COS, FEAT_SINCOS = 0, 1
-FLAG_LANGEVIN, FLAG_STIEFEL, FLAG_FIX_U = 1, 2, 4
+FLAG_LANGEVIN, FLAG_STIEFEL, FLAG_FIX_U, FLAG_RMSPROP = 1, 2, 4, 8
 ALG_AUTO, ALG_DIRECT, ALG_NODES = 0, 1, 2
-OPT_PIPE_GROUPS, OPT_PIPE_RESERVE, OPT_ALGORITHM, OPT_NODE_ORDER, OPT_NODE_THETA = range(5)
+OPT_PIPE_GROUPS, OPT_PIPE_RESERVE, OPT_ALGORITHM, OPT_NODE_ORDER, OPT_NODE_THETA, OPT_RMS_ALPHA, OPT_RMS_LAMBDA = range(7)
 PHASES = ("gather", "fwd", "contract", "bwd", "reduce", "update")
 
 H = C.c_void_p

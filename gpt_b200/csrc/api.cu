@@ -206,10 +206,23 @@ int forward_contract(gptb_handle *h, bool phi_mode, const int32_t *rows, const d
                                   f64 ? h->E : nullptr, f64 ? nullptr : h->Eimg, f64));
     if (img) {
         GPTB_TRY(gptb_tc_check_escale(h));
-        h->k2_redo = true;
+        h->k2_redo = 1;
         const int st = gptb_launch_contract(h, h->T, w_dev, h->yb, bs, h->mpad, escale, want_grad, h->fhat, h->grad, nullptr,
                                             h->Eimg, false);
-        h->k2_redo = false;
+        h->k2_redo = 0;
+        GPTB_TRY(st);
+    }
+    if (h->rms_active && want_grad) {
+        // GPT_SGLDERM_RMSprop: w moves as soon as its gradient is complete (:1172-1188), and computeA then sees the NEW w
+        // (:1194) while fhat and the residual stay those of the old w — a second K2 launch that only rewrites E
+        GPTB_TRY(gptb_allreduce_range(h, h->grad, (size_t)h->cfg.Q, h->stream));
+        GPTB_TRY(gptb_launch_rms_w(h, h->rms_flags, h->rms_noise_w, h->step_counter, h->stream));
+        h->k2_redo = 2;
+        h->k2_wA = h->w;
+        const int st = gptb_launch_contract(h, h->T, h->w_old, h->yb, bs, h->mpad, escale, true, h->fhat, h->grad,
+                                            f64 ? h->E : nullptr, f64 ? nullptr : h->Eimg, f64);
+        h->k2_redo = 0;
+        h->k2_wA = nullptr;
         GPTB_TRY(st);
     }
     if (pt) pt->done(GPTB_PHASE_CONTRACT);
@@ -388,7 +401,7 @@ static int pipe_tail_end(gptb_handle *h, cudaStream_t s) {
 static bool pipe_usable(gptb_handle *h, int64_t bs, bool staged_host_batch, int32_t flags) {
     const bool phi_mode = h->have_phi && !staged_host_batch;
     const int G = pipe_groups_for(h);
-    if (flags & GPTB_FLAG_FIX_U) return false;
+    if (flags & (GPTB_FLAG_FIX_U | GPTB_FLAG_RMSPROP)) return false;
     {   // the node-grid step has no row-proportional K3 to hide an update under: one stream
         const int64_t lbs = (int64_t)(h->rank + 1) * bs / h->nranks - (int64_t)h->rank * bs / h->nranks;
         if (lbs > 0 && nodes_usable(h, lbs, phi_mode)) return false;
@@ -699,6 +712,7 @@ int gptb_destroy(gptb_handle *h) {
     dev_free(&h->G); dev_free(&h->small); dev_free(&h->colnorm); dev_free(&h->nan_flag);
     dev_free(&h->noise_w); dev_free(&h->noise_U); dev_free(&h->pred_acc);
     dev_free(&h->gen_noise_w); dev_free(&h->gen_noise_U);
+    dev_free(&h->rms_gw); dev_free(&h->rms_gU); dev_free(&h->rms_epsk); dev_free(&h->w_old);
     dev_free(&h->store_w); dev_free(&h->store_U);
     if (h->nan_flag_host) cudaFreeHost(h->nan_flag_host);
     if (h->pin) cudaFreeHost(h->pin);
@@ -911,6 +925,10 @@ int gptb_set_params(gptb_handle *h, const double *w, const double *U) {
     h->have_params = true;
     h->shadows_valid = false;
     h->tc_emax_valid = false;
+    if (h->rms_gw) {   // a new chain starts with empty moving averages (:1143-1144)
+        GPTB_CUDA_OK(h, cudaMemsetAsync(h->rms_gw, 0, sizeof(double) * c.Q, h->stream));
+        GPTB_CUDA_OK(h, cudaMemsetAsync(h->rms_gU, 0, sizeof(double) * c.D * c.r * c.n, h->stream));
+    }
     return GPTB_OK;
 }
 
@@ -1329,7 +1347,33 @@ static int step_common(gptb_handle *h, double signal_var, const int32_t *rows, i
         gptb_handle *h;
         ~F32Guard() { h->f32_grad = false; }
     } f32guard{h};
-    h->f32_grad = !use_fp64(h, h->have_phi && !staged) && gptb_contract_tc_usable(h);
+    const bool rms = (flags & GPTB_FLAG_RMSPROP) != 0;
+    if (rms && (!(flags & GPTB_FLAG_STIEFEL) || (flags & GPTB_FLAG_FIX_U))) {
+        gptb_set_error(h, "GPTB_FLAG_RMSPROP is the Stiefel sampler of GPT_SGLD.jl:1121-1237: set GPTB_FLAG_STIEFEL, not GPTB_FLAG_FIX_U");
+        return GPTB_ERR_ARG;
+    }
+    // (the RMSprop step reads the complete FP64 gradient twice before the update: no FP32 gradient flow)
+    h->f32_grad = !rms && !use_fp64(h, h->have_phi && !staged) && gptb_contract_tc_usable(h);
+    struct RmsGuard {
+        gptb_handle *h;
+        ~RmsGuard() { h->rms_active = false; h->rms_noise_w = nullptr; }
+    } rmsguard{h};
+    if (rms) {
+        const gptb_config &c = h->cfg;
+        if (!h->rms_gw) {
+            GPTB_TRY(dev_alloc(h, &h->rms_gw, (size_t)c.Q));
+            GPTB_TRY(dev_alloc(h, &h->rms_gU, (size_t)c.D * c.r * c.n));
+            GPTB_TRY(dev_alloc(h, &h->rms_epsk, (size_t)c.D));
+            GPTB_TRY(dev_alloc(h, &h->w_old, (size_t)c.Q));
+            GPTB_CUDA_OK(h, cudaMemsetAsync(h->rms_gw, 0, sizeof(double) * c.Q, h->stream));
+            GPTB_CUDA_OK(h, cudaMemsetAsync(h->rms_gU, 0, sizeof(double) * c.D * c.r * c.n, h->stream));
+        }
+        h->rms_active = true;
+        h->rms_eps = epsw;            // the sampler's single step size epsilon (:1121)
+        h->rms_N = (double)N_total;
+        h->rms_noise_w = nw_dev;
+        h->rms_flags = flags;
+    }
     if (pipe_usable(h, bs, staged, flags))
         return step_pipelined(h, signal_var, rows, bs, N_total, staged, Xstage, ystage, epsw, epsU, flags, nw_dev, nU_dev);
     GPTB_TRY(pipe_join(h));
@@ -1348,7 +1392,8 @@ static int step_common(gptb_handle *h, double signal_var, const int32_t *rows, i
     const int kn_upd = fix_U ? 0 : h->cfg.D;          // GPT_SGLDERMw: only w moves (:1108)
     GPTB_TRY(compute_grad(h, signal_var, rows, bs, N_total, staged, Xstage, ystage, pt, fix_U));
     if (side_noise) GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->evR[0], 0));
-    GPTB_TRY(gptb_launch_update_range(h, epsw, epsU, flags, nw_dev, nU_dev, h->step_counter, 0, kn_upd, true, h->stream,
+    if (rms) GPTB_TRY(gptb_launch_rms_U(h, h->stream));     // gU, per-dimension step sizes (:1210-1212); w has moved already
+    GPTB_TRY(gptb_launch_update_range(h, epsw, epsU, flags, nw_dev, nU_dev, h->step_counter, 0, kn_upd, !rms, h->stream,
                                       side_noise));
     pt.done(GPTB_PHASE_UPDATE);
     pt.finish();
@@ -1537,6 +1582,10 @@ int gptb_sgld_run(gptb_handle *h, double signal_var, int64_t m, double epsw, dou
     // local, GPT_SGLD.jl:374); gptb_sgld_advance is the entry that continues a chain's epochs
     int st = gptb_reset_order(h);
     h->batch_cursor = 0;
+    if (h->rms_gw) {   // gw = zeros(Q); gU = zeros(n,r,D) at the start of every run (:1143-1144)
+        cudaMemsetAsync(h->rms_gw, 0, sizeof(double) * c.Q, h->stream);
+        cudaMemsetAsync(h->rms_gU, 0, sizeof(double) * ucnt, h->stream);
+    }
     uint64_t step = 0;
     for (int epoch = 1; st == GPTB_OK && epoch <= burnin + maxepoch; ++epoch) {
         if (perms) {
@@ -1633,6 +1682,14 @@ int gptb_set_option(gptb_handle *h, int32_t option, double value) {
             if (value < 4 || value > 16) break;
             h->node_P = (int)value;
             h->grid_valid = false;
+            return GPTB_OK;
+        case GPTB_OPT_RMS_ALPHA:
+            if (!(value >= 0.0 && value < 1.0)) break;
+            h->rms_alpha = value;
+            return GPTB_OK;
+        case GPTB_OPT_RMS_LAMBDA:
+            if (!(value > 0.0)) break;
+            h->rms_lambda = value;
             return GPTB_OK;
         case GPTB_OPT_NODE_THETA:
             if (!(value > 0.0) || value > 8.0) break;

@@ -137,7 +137,18 @@ struct gptb_handle {
                                        // [3] uscale (2^k applied to U in Uimg), [4] 1/uscale
     bool tc_emax_valid = false;
     bool gather_cells = false;         // set around a node-grid step: the gather also writes nodes.cell / nodes.uu
-    bool k2_redo = false;              // set around the conditional second K2 launch (E-image scale guard, api.cu)
+    int k2_redo = 0;                   // set around a second K2 launch that only rewrites E: 1 = if the scale guard asks
+                                       // for it (api.cu), 2 = unconditionally (RMSprop sampler: E with the updated w)
+    const double *k2_wA = nullptr;     // weights of computeA when they differ from w
+    // RMSprop sampler (GPT_SGLDERM_RMSprop, GPT_SGLD.jl:1121-1237)
+    double rms_alpha = 0.9, rms_lambda = 1e-5;
+    double *rms_gw = nullptr, *rms_gU = nullptr;   // moving averages of the squared unnormalised gradients [Q], [D][r][n]
+    double *rms_epsk = nullptr;        // [D] sum over the elements of U^(k) of epsilon/(sqrt(gU)+lambda)
+    double *w_old = nullptr;           // w before the step's update (fhat and the residual use it)
+    bool rms_active = false;           // set for the duration of an RMSprop step
+    double rms_eps = 0.0, rms_N = 1.0;
+    const double *rms_noise_w = nullptr;
+    int rms_flags = 0;
     bool k2_T_rowmajor = false;        // K2 reads T as [D][mpad][rpad] (nodes.cu) instead of [D][r][mpad]
     float *k2_Erow = nullptr;          // when set, K2 writes plain FP32 E [D][mpad][rpad] instead of the operand image
 
@@ -285,6 +296,8 @@ int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags
                              bool noise_ready = false);
 int gptb_launch_noise_range(gptb_handle *h, uint64_t step, int k0, int kn, bool with_w, cudaStream_t s);
 int gptb_update_alloc_noise(gptb_handle *h);
+int gptb_launch_rms_w(gptb_handle *h, int flags, const double *noise_w, uint64_t step, cudaStream_t s);
+int gptb_launch_rms_U(gptb_handle *h, cudaStream_t s);
 int gptb_proj_geod_device(gptb_handle *scratch_owner, cudaStream_t s, int n, int r, const double *U, const double *V,
                           double t, double *out, int mode /*0 proj, 1 geod*/, int32_t *nan_flag);
 // batch.cu

@@ -45,8 +45,9 @@ struct ContractParams {
     int64_t bs, mpad;
     double escale;
     int D, r, rpad, Q, want_grad;
-    const int *redo_flag;    // see contract_tc.cu: a conditional second launch that only rewrites the E image
+    const int *redo_flag;    // see contract_tc.cu: a conditional (1) or unconditional (2) second launch that only rewrites E
     int redo;
+    const double *wA;        // weights of computeA when they differ from w (RMSprop sampler), or null
 };
 
 template <typename real, int DT>
@@ -56,7 +57,7 @@ __global__ void __launch_bounds__(CT_THREADS) contract_kernel(const ContractPara
     constexpr int DU = DT > 0 ? DT : 16;
     const int r = p.r, rpad = p.rpad, Q = p.Q, DR = D * r;
     const int tid = threadIdx.x, row = tid & 31, s = tid >> 5;
-    if (p.redo && *p.redo_flag == 0) return;
+    if (p.redo == 1 && *p.redo_flag == 0) return;
     const int64_t i = (int64_t)blockIdx.x * RB + row;
     const bool live = i < p.bs;
     const real *T = reinterpret_cast<const real *>(p.T);
@@ -70,6 +71,7 @@ __global__ void __launch_bounds__(CT_THREADS) contract_kernel(const ContractPara
     uint16_t *gq = reinterpret_cast<uint16_t *>(gp + ((D * rpad + 4) & ~3));  // [Q*D]
     unsigned char *I8 = reinterpret_cast<unsigned char *>(gq + (((size_t)Q * D + 7) & ~(size_t)7));  // [Q][D]
 
+    real *wsA = ws;            // weights of pass 2
     for (int t = tid; t < Q; t += CT_THREADS) ws[t] = (real)p.w[t];
     for (int t = tid; t < Q * D; t += CT_THREADS) {
         I8[t] = (unsigned char)p.I[(size_t)(t % D) * Q + t / D];
@@ -126,7 +128,7 @@ __global__ void __launch_bounds__(CT_THREADS) contract_kernel(const ContractPara
                 real sum = 0;
                 for (int pp = p0; pp < p1; ++pp) {
                     const int q = gq[pp];
-                    sum += ws[q] * Vs[(size_t)q * VS + row];
+                    sum += (p.wA ? (real)p.wA[q] : wsA[q]) * Vs[(size_t)q * VS + row];
                 }
                 const real t = Ts[(size_t)(k * r + l) * RB + row];
                 if (t != (real)0) {
@@ -136,7 +138,7 @@ __global__ void __launch_bounds__(CT_THREADS) contract_kernel(const ContractPara
                     for (int pp = p0; pp < p1; ++pp) {
                         const int q = gq[pp];
                         const unsigned char *iq = I8 + q * D;
-                        real v = ws[q];
+                        real v = p.wA ? (real)p.wA[q] : wsA[q];
                         for (int kk = 0; kk < D; ++kk)
                             if (kk != k) v *= Ts[(size_t)(kk * r + iq[kk]) * RB + row];
                         acc += v;
@@ -239,7 +241,8 @@ int gptb_launch_contract(gptb_handle *h, const void *T, const void *w, const dou
     p.escale = escale;
     p.D = h->cfg.D; p.r = h->cfg.r; p.rpad = h->rpad; p.Q = h->cfg.Q;
     p.want_grad = want_grad ? 1 : 0;
-    p.redo = (!real_is_double && h->k2_redo) ? 1 : 0;
+    p.redo = (!real_is_double && h->k2_redo == 1) ? 1 : (h->k2_redo == 2 ? 2 : 0);
+    p.wA = h->k2_wA;
     p.redo_flag = h->nan_flag + 2;
     return real_is_double ? launch_typed<double>(h, p) : launch_typed<float>(h, p);
 }

@@ -43,6 +43,7 @@ constexpr int CT_THREADS = 32 * CNW;
 struct ContractTcParams {
     const float *T;          // [D][r][mpad]
     const double *w;
+    const double *wA;        // weights of computeA when they differ from w (RMSprop sampler: A sees the updated w, :1194), or null
     const int32_t *off1;     // [Q][DP]  (k*r + I[q,k]) * 32  (float2 index into Ts), DP = D rounded up to 4
     const int32_t *lptr;     // [D*rpad + 1] start of each (k,l) list in `lists` (lists padded to multiples of 4)
     const int32_t *lists;    // q * 32 (float2 index into Vs) for the q of each list; padding entries -> zero row q = Q
@@ -76,7 +77,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     constexpr int DP4 = (DT + 3) / 4;
     const int r = p.r, rpad = p.rpad, Q = p.Q, DR = D * r;
     const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
-    if (p.redo && *p.redo_flag == 0) return;                     // (uniform across the grid)
+    if (p.redo == 1 && *p.redo_flag == 0) return;                // (uniform across the grid; redo == 2: unconditional)
     const int64_t i0 = (int64_t)blockIdx.x * CRB + 2 * lane;     // this lane's rows: i0, i0 + 1
     const bool live0 = i0 < p.bs, live1 = i0 + 1 < p.bs;
 
@@ -192,7 +193,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
             if (q < Q) {
                 const float2 vv = Vs[(size_t)q * 32 + lane];
                 val = fmaf(e.x, vv.x, e.y * vv.y);
-                const float wq = ws[q];
+                const float wq = p.wA ? (float)p.wA[q] : ws[q];
                 Vs[(size_t)q * 32 + lane] = mul2(vv, make_float2(wq, wq));
             }
             v[j] = val;
@@ -266,7 +267,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
                     for (int pp = p0; pp < p1; ++pp) {
                         const int q = __ldg(p.lists + pp) >> 5;
                         if (q >= Q) continue;
-                        float2 v = make_float2(ws[q], ws[q]);
+                        const float wq0 = p.wA ? (float)p.wA[q] : ws[q];
+                        float2 v = make_float2(wq0, wq0);
                         for (int kk = 0; kk < D; ++kk)
                             if (kk != k) v = mul2(v, Ts[__ldg(p.off1 + (size_t)q * p.DP + kk) + lane]);
                         acc = add2(acc, v);
@@ -377,6 +379,7 @@ int gptb_launch_contract_tc(gptb_handle *h, const float *T, const double *w, con
     ContractTcParams p;
     p.T = T;
     p.w = w;
+    p.wA = nullptr;
     p.off1 = h->ct_off1;
     p.lptr = h->ct_lptr;
     p.lists = h->ct_lists;
@@ -394,7 +397,8 @@ int gptb_launch_contract_tc(gptb_handle *h, const float *T, const double *w, con
     p.DP = (c.D + 3) & ~3; p.r = c.r; p.rpad = h->rpad; p.Q = c.Q;
     p.want_grad = want_grad ? 1 : 0;
     p.n_lists = h->ct_nlists;
-    p.redo = h->k2_redo ? 1 : 0;
+    p.redo = h->k2_redo;
+    p.wA = h->k2_wA;
     p.redo_flag = h->nan_flag + 2;
     p.Erow = want_grad ? h->k2_Erow : nullptr;
     p.t_rowmajor = h->k2_T_rowmajor ? 1 : 0;

@@ -122,7 +122,9 @@ k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ 
           double *__restrict__ G, double *__restrict__ small, size_t small_stride, int n, int r, int D, int Q,
           double epsw, double epsU, int flags, const double *__restrict__ noise_w,
           const double *__restrict__ noise_U, uint64_t key, uint64_t step, int have_grad, int k0, int kn,
-          float *__restrict__ gradFbase, int qpad, int qstride, int npad, int rpad) {
+          float *__restrict__ gradFbase, int qpad, int qstride, int npad, int rpad,
+          const double *__restrict__ epsk_sum, double inv_cnt) {
+    // epsk_sum != null (RMSprop sampler): dimension k moves with its own step size epsk_sum[k] * inv_cnt (:1212)
     // gradFbase != null: the FP32 gradient flow — gradw in gradFbase[0..Q), gradU as K3 left it in
     // gradFbase + qpad ([D][npad][rpad]); every entry is read once here and cleared for the next step
     // grid.y = kn (+ 1): rows 0..kn-1 are the dimensions k0.., row kn (if launched) is w
@@ -154,6 +156,7 @@ k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ 
     const int rows = min(UP_ROWS, n - j0);
     const double *gU = grad + Q + (size_t)k * r * n;
     double *Uk = U + (size_t)k * r * n, *Gk = G + (size_t)k * r * n;
+    if (epsk_sum) epsU = epsk_sum[k] * inv_cnt;
     const double sqU = sqrt(epsU);
     const int npr = (r + 15) & ~15, ldt = dmm_ld(npr);   // tile layout [jj][l], zero padded to npr columns
     double *Us = sm, *Gs = sm + (size_t)UP_ROWS * ldt;
@@ -533,9 +536,10 @@ __device__ void sexpm(double *M, int n2, double *buf, int *bad_s) {
 // tangent vector `mom` of geod(U,mom,t) (GPT_SGLD.jl:19-37 called directly).
 __global__ void __launch_bounds__(1024)
 k_small(double *__restrict__ small, size_t small_stride, int r, double t, int use_sym, int32_t *nan_flag,
-        int use_smem) {
+        int use_smem, const double *__restrict__ epsk_sum = nullptr, double inv_cnt = 0.0) {
     extern __shared__ double sm[];
     __shared__ int bad;
+    if (epsk_sum) t = sqrt(epsk_sum[blockIdx.x] * inv_cnt);
     double *sk = small + (size_t)blockIdx.x * small_stride;
     SmallLayout L(r);
     const int r2 = 2 * r, rr = r * r;
@@ -706,6 +710,52 @@ k_reduce_only(const double *__restrict__ U, const double *__restrict__ G, double
     }
 }
 
+
+// ================================================================================================
+// RMSprop sampler (GPT_SGLDERM_RMSprop, GPT_SGLD.jl:1121-1237): step sizes from moving averages of the squared
+// UNNORMALISED gradients (the reference's (1/batch_size)-scaled ones, :1172/:1202: our likelihood gradients / N).
+// ================================================================================================
+// w: gw = alpha gw + (1-alpha) raw^2;  epsw = eps/(sqrt(gw)+lambda);  w += epsw (N raw - w)/2 + sqrt(epsw) z   (:1175-1188).
+// The pre-update w is kept in w_old: fhat and the residual of this step belong to it, computeA sees the new w.
+__global__ void k_rms_w(const double *__restrict__ grad, double *__restrict__ w, double *__restrict__ w_old,
+                        double *__restrict__ gw, int Q, double N, double eps, double alpha, double lambda,
+                        const double *__restrict__ noise_w, uint64_t key, uint64_t step, int langevin) {
+    for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < Q; q += gridDim.x * blockDim.x) {
+        const double lik = grad[q], raw = lik / N;
+        const double g2 = alpha * gw[q] + (1.0 - alpha) * raw * raw;
+        gw[q] = g2;
+        const double e = eps / (sqrt(g2) + lambda);
+        const double wq = w[q];
+        w_old[q] = wq;
+        double z = 0.0;
+        if (langevin) z = noise_w ? noise_w[q] : noise_at(key, GPTB_STREAM_NOISE_W, step, (uint64_t)q);
+        w[q] = wq + e * (lik - wq) / 2 + sqrt(e) * z;
+    }
+}
+
+// U: gU = alpha gU + (1-alpha) raw^2 element-wise, and the sum over each U^(k) of eps/(sqrt(gU)+lambda) (:1210-1212).
+// grid (blocks, D); gradU and gU are [D][r][n].
+__global__ void __launch_bounds__(256) k_rms_U(const double *__restrict__ gradU, double *__restrict__ gU,
+                                               double *__restrict__ epsk_sum, size_t per_k, double N, double eps, double alpha,
+                                               double lambda) {
+    const int k = blockIdx.y;
+    double acc = 0.0;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < per_k; e += (size_t)gridDim.x * blockDim.x) {
+        const double raw = gradU[(size_t)k * per_k + e] / N;
+        const double g2 = alpha * gU[(size_t)k * per_k + e] + (1.0 - alpha) * raw * raw;
+        gU[(size_t)k * per_k + e] = g2;
+        acc += eps / (sqrt(g2) + lambda);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    __shared__ double part[8];
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) acc += part[w];
+        atomicAdd(&epsk_sum[k], acc);
+    }
+}
 
 // ================================================================================================
 // Fast path of the sampler's update (r <= 32): noise -> prepare -> small2 -> apply2.
@@ -891,10 +941,12 @@ struct Small2Geo {
 };
 
 __global__ void __launch_bounds__(1024)
-k_small2(double *__restrict__ small, size_t small_stride, int r, double t, int32_t *nan_flag) {
+k_small2(double *__restrict__ small, size_t small_stride, int r, double t, int32_t *nan_flag,
+         const double *__restrict__ epsk_sum, double inv_cnt) {
     extern __shared__ double sm[];
     __shared__ int bad;
     __shared__ double cn[64];
+    if (epsk_sum) t = sqrt(epsk_sum[blockIdx.x] * inv_cnt);
     double *sk = small + (size_t)blockIdx.x * small_stride;
     SmallLayout L(r);
     const Small2Geo g(r);
@@ -1177,12 +1229,15 @@ int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags
         if (!noise_w) noise_w = h->gen_noise_w;
         if (!noise_U) noise_U = h->gen_noise_U;
     }
+    // RMSprop step: every dimension has its own step size (the kernels index the array by their global / local k)
+    const double *epsk = h->rms_active ? h->rms_epsk : nullptr;
+    const double inv_cnt = 1.0 / ((double)c.n * c.r);
     size_t sm1 = 2 * (size_t)UP_ROWS * dmm_ld((c.r + 15) & ~15) * sizeof(double) +
                  (h->f32_grad ? (size_t)UP_ROWS * (h->rpad + 1) * sizeof(float) : 0);
     k_prepare<<<dim3(nb, gy), UP_THREADS, sm1, s>>>(h->grad, h->w, h->U, h->G, h->small, h->small_stride, c.n, c.r, c.D, c.Q,
                                                    epsw, epsU, flags, noise_w, noise_U, c.seed, step, 1, k0, kn,
                                                    h->f32_grad ? h->gradFbase : nullptr, h->gradF_qpad, h->gradF_qstride,
-                                                   h->npad, h->rpad);
+                                                   h->npad, h->rpad, epsk, inv_cnt);
     h->launches++;
     if (kn > 0) h->shadows_valid = false;
     if (stiefel && kn > 0) {
@@ -1190,7 +1245,8 @@ int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags
         const Small2Geo sg(c.r);
         const size_t koff = (size_t)k0 * c.r * c.n;
         if (sg.ok(c.r) && sg.bytes() <= 225 * 1024) {
-            k_small2<<<kn, 1024, sg.bytes(), s>>>(small_g, h->small_stride, c.r, sqrt(epsU), h->nan_flag);
+            k_small2<<<kn, 1024, sg.bytes(), s>>>(small_g, h->small_stride, c.r, sqrt(epsU), h->nan_flag, epsk ? epsk + k0 : nullptr,
+                                                  inv_cnt);
             const bool tc = gptb_is_tc(h);
             const int npr = (c.r + 15) & ~15;
             size_t sm3 = ((size_t)dmm_ld(UP_ROWS) * 3 * npr + (size_t)dmm_ld(2 * npr) * npr) * sizeof(double);
@@ -1201,7 +1257,8 @@ int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags
             h->launches += 2;
             if (tc) h->shadows_valid = true;   // k_apply2 refreshed the operand image
         } else {
-            k_small<<<kn, 1024, sb, s>>>(small_g, h->small_stride, c.r, sqrt(epsU), 1, h->nan_flag, sb ? 1 : 0);
+            k_small<<<kn, 1024, sb, s>>>(small_g, h->small_stride, c.r, sqrt(epsU), 1, h->nan_flag, sb ? 1 : 0,
+                                         epsk ? epsk + k0 : nullptr, inv_cnt);
             size_t sm3 = (2 * (size_t)UP_ROWS * c.r + 2 * (size_t)c.r * c.r + c.r) * sizeof(double);
             k_apply<<<dim3(nb, kn), UP_THREADS, sm3, s>>>(h->U + koff, h->G + koff, small_g, h->small_stride, c.n, c.r,
                                                          h->nan_flag);
@@ -1210,6 +1267,29 @@ int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags
             h->launches += 3;
         }
     }
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    return GPTB_OK;
+}
+
+// RMSprop: the w half of the step (after the gradient of w is complete in h->grad, before computeA).
+int gptb_launch_rms_w(gptb_handle *h, int flags, const double *noise_w, uint64_t step, cudaStream_t s) {
+    const gptb_config &c = h->cfg;
+    k_rms_w<<<(c.Q + 255) / 256, 256, 0, s>>>(h->grad, h->w, h->w_old, h->rms_gw, c.Q, h->rms_N, h->rms_eps, h->rms_alpha,
+                                              h->rms_lambda, noise_w, c.seed, step, (flags & GPTB_FLAG_LANGEVIN) ? 1 : 0);
+    h->launches++;
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    return GPTB_OK;
+}
+
+// RMSprop: moving average of gradU^2 and the per-dimension step-size sums (before the update kernels).
+int gptb_launch_rms_U(gptb_handle *h, cudaStream_t s) {
+    const gptb_config &c = h->cfg;
+    const size_t per_k = (size_t)c.r * c.n;
+    GPTB_CUDA_OK(h, cudaMemsetAsync(h->rms_epsk, 0, sizeof(double) * c.D, s));
+    k_rms_U<<<dim3((unsigned)std::min<size_t>((per_k + 255) / 256, 64), c.D), 256, 0, s>>>(h->grad + c.Q, h->rms_gU, h->rms_epsk, per_k,
+                                                                                          h->rms_N, h->rms_eps, h->rms_alpha,
+                                                                                          h->rms_lambda);
+    h->launches++;
     GPTB_CUDA_OK(h, cudaGetLastError());
     return GPTB_OK;
 }

@@ -27,7 +27,7 @@ import numpy as np
 
 from . import _lib as L
 
-__all__ = ["feature", "feature2", "samplenz", "pred", "pred_samples", "GPTregression", "proj", "geod",
+__all__ = ["feature", "feature2", "samplenz", "pred", "pred_samples", "GPTregression", "GPT_SGLDERMw", "GPT_SGLDERM_RMSprop", "proj", "geod",
            "datawhitening", "RFFFeatures", "Model", "GptbError", "GeodesicNaN", "shard_range"]
 
 
@@ -313,9 +313,10 @@ class Model:
         _check(self.lib.gptb_sgld_step_host_wait(self.h), self.h)
 
     def sgld_run(self, signal_var, m, epsw, epsU, burnin, maxepoch, langevin=True, stiefel=True, perms=None,
-                 noise_w=None, noise_U=None, store=True, N=None, fix_U=False):
+                 noise_w=None, noise_U=None, store=True, N=None, fix_U=False, rmsprop=False):
         Q, n, r, D = self.cfg.Q, self.cfg.n, self.cfg.r, self.cfg.D
-        flags = (L.FLAG_LANGEVIN if langevin else 0) | (L.FLAG_STIEFEL if stiefel else 0) | (L.FLAG_FIX_U if fix_U else 0)
+        flags = ((L.FLAG_LANGEVIN if langevin else 0) | (L.FLAG_STIEFEL if stiefel else 0) | (L.FLAG_FIX_U if fix_U else 0)
+                 | (L.FLAG_RMSPROP if rmsprop else 0))
         numbatches = -(-int(N) // int(m))
         T = maxepoch * numbatches
         w_store = np.zeros((Q, T), order="F") if store else None
@@ -459,6 +460,28 @@ def GPT_SGLDERMw(phi, y, signal_var, I, r, Q, m, epsw, burnin, maxepoch, param_s
         w_store, _ = mdl.sgld_run(signal_var, m, epsw, 0.0, burnin, maxepoch, True, True, perms, noise_w, None, store=True,
                                   N=N, fix_U=True)
         return w_store, mdl.get_params()[1]
+
+
+def GPT_SGLDERM_RMSprop(phi, y, signal_var, I, r, Q, m, epsilon, alpha, burnin, maxepoch, param_seed=0, *,
+                        precision: Optional[int] = None, w0=None, U0=None, perms=None, noise_w=None, noise_U=None, options=None):
+    """GPT_SGLD.jl:1121-1237: SGLD-ERM with RMSprop step sizes (one per element of w, one per U^(k)); `epsilon` is the
+    base step size, `alpha` the moving-average coefficient.  Returns (w_store, U_store) like GPTregression.  The
+    reference draws from the global RNG; here param_seed names the draws (keyword-only extras as in GPTregression)."""
+    y = np.ravel(np.asarray(y, dtype=np.float64))
+    N = y.size
+    opts = {L.OPT_RMS_ALPHA: float(alpha)}
+    opts.update(options or {})
+    with _model_for(phi, r, Q, I, precision, seed=int(param_seed), options=opts) as mdl:
+        if isinstance(phi, RFFFeatures):
+            mdl.set_train(phi.X, y)
+        else:
+            mdl.set_train_phi(phi, y)
+        if w0 is not None:
+            mdl.set_params(w0, U0)
+        else:
+            mdl.init_params(param_seed, True)
+        return mdl.sgld_run(signal_var, m, epsilon, 0.0, burnin, maxepoch, True, True, perms, noise_w, noise_U, store=True,
+                            N=N, rmsprop=True)
 
 
 def proj(U, V):

@@ -57,8 +57,14 @@ enum gptb_feature_kind {
 enum gptb_flags {
     GPTB_FLAG_LANGEVIN = 1, /* keyword langevin of GPTregression (GPT_SGLD.jl:345)        */
     GPTB_FLAG_STIEFEL = 2,  /* keyword stiefel                                             */
-    GPTB_FLAG_FIX_U = 4     /* GPT_SGLDERMw (GPT_SGLD.jl:1065-1118): SGLD on w only, the factors U stay as they are
+    GPTB_FLAG_FIX_U = 4,    /* GPT_SGLDERMw (GPT_SGLD.jl:1065-1118): SGLD on w only, the factors U stay as they are
                                (no factor gradient, no U update; U_store may be NULL)      */
+    GPTB_FLAG_RMSPROP = 8   /* GPT_SGLDERM_RMSprop (GPT_SGLD.jl:1121-1237), with GPTB_FLAG_STIEFEL: `epsw` is the sampler's
+                               single step size epsilon (`epsU` is ignored); every w[q] moves with epsilon/(sqrt(gw[q])+lambda),
+                               every U^(k) with the mean of its elements' step sizes (:1212); gw, gU are moving averages
+                               (coefficient alpha: GPTB_OPT_RMS_ALPHA, default 0.9; lambda: GPTB_OPT_RMS_LAMBDA, 1e-5 as :1146)
+                               of the squared gradients scaled by 1/batch_size (:1172), zero at the start of every
+                               gptb_sgld_run and after gptb_set_params; computeA sees the updated w (:1188 before :1194) */
 };
 
 typedef struct gptb_config {
@@ -266,7 +272,9 @@ enum gptb_option {
     GPTB_OPT_PIPE_RESERVE = 1,  /* SMs the persistent kernels leave to the concurrent group update                        */
     GPTB_OPT_ALGORITHM = 2,     /* enum gptb_algorithm                                                                    */
     GPTB_OPT_NODE_ORDER = 3,    /* Chebyshev nodes per cell of the node grid (4..16, default 12)                          */
-    GPTB_OPT_NODE_THETA = 4     /* cell half-width x max |Zt| of the dimension (default 2)                                */
+    GPTB_OPT_NODE_THETA = 4,    /* cell half-width x max |Zt| of the dimension (default 2)                                */
+    GPTB_OPT_RMS_ALPHA = 5,     /* moving-average coefficient of GPTB_FLAG_RMSPROP (`alpha` of GPT_SGLD.jl:1121), default 0.9 */
+    GPTB_OPT_RMS_LAMBDA = 6     /* its smoothing constant (`lambda` of :1146), default 1e-5                                */
 };
 int gptb_set_option(gptb_handle *h, int32_t option, double value);
 int gptb_get_phase_ms(gptb_handle *h, float *ms_out /*GPTB_PHASE_COUNT*/, int64_t *launches_out, int32_t reset);

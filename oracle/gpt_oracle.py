@@ -17,10 +17,13 @@ Pinning status (see tests/test_oracle_golden.py):
                     exact cosine in X[:,k] of amplitude phi_scale*sqrt(2/n)); Z,b were not saved.
   * gradients     — pinned against finite differences of the reference's own log-likelihood
                     restatement (Diagnostic_gradients.jl:5-37, :133-150).
-  * `geod`/`expm`/`sqrtm`/RNG — **parity unpinned**: Julia 0.3 Base `expm` (Pade-13 scaling and
-                    squaring) is replaced by scipy.linalg.expm (same algorithm family); the
-                    reference holds no known-answer test for these call sites
-                    (GPT_SGLD.jl:23,28,366).  Checked through invariants instead.
+  * `geod`/`expm` — the reference holds no known-answer test for these call sites (GPT_SGLD.jl:23,28) and
+                    Julia 0.3 Base `expm` (Pade-13 scaling and squaring) is replaced by scipy.linalg.expm
+                    (same algorithm family).  Pinned independently instead: against the closed-form great
+                    circle for r = 1 (`geod_great_circle`) and against a 40-digit mpmath evaluation of the
+                    same lines (`expm_mp`, `geod_mp`) at r in {2, 10, 32}, t in {1e-7, 1e-3, 0.3}.
+  * `sqrtm`/RNG   — **parity unpinned**: `sqrtm` (:366) only enters the initial draw, which the tests inject;
+                    Julia's dSFMT streams cannot be reproduced (draws are injected on both sides).
 """
 from __future__ import annotations
 
@@ -221,6 +224,48 @@ def geod(U, mom, t):
     return tmpU / np.linalg.norm(tmpU, axis=0, keepdims=True), False
 
 
+def geod_great_circle(U, mom, t):
+    """Closed form of geod for r = 1 (V_{n,1} is the unit sphere): with u'm = 0 the geodesic of GPT_SGLD.jl:19-37 is the
+    great circle  u cos(t|m|) + (m/|m|) sin(t|m|).  An independent pin of `geod` (no expm involved)."""
+    u = np.asarray(U, dtype=np.float64).reshape(-1)
+    m = np.asarray(mom, dtype=np.float64).reshape(-1)
+    nm = np.linalg.norm(m)
+    return (u * np.cos(t * nm) + (m / nm) * np.sin(t * nm)).reshape(-1, 1)
+
+
+def expm_mp(A, dps=40):
+    """Matrix exponential in arbitrary precision (mpmath, `dps` digits) — the pin for the expm calls of GPT_SGLD.jl:23,28
+    that is independent of SciPy / LAPACK and of every double-precision algorithm."""
+    import mpmath as mp
+    with mp.workdps(dps):
+        E = mp.expm(mp.matrix(np.asarray(A, dtype=np.float64).tolist()))
+        return np.array([[float(E[i, j]) for j in range(E.cols)] for i in range(E.rows)])
+
+
+def geod_mp(U, mom, t, dps=40):
+    """GPT_SGLD.jl:19-37 with both exponentials and all products carried in `dps`-digit arithmetic (mpmath)."""
+    import mpmath as mp
+    n, r = U.shape
+    with mp.workdps(dps):
+        Um, Mm = mp.matrix(U.tolist()), mp.matrix(mom.tolist())
+        A = Um.T * Mm                                                   # :20
+        T = mp.zeros(2 * r)
+        MM = Mm.T * Mm
+        for a in range(r):
+            for b in range(r):
+                T[a, b] = A[a, b]; T[a, r + b] = -MM[a, b]; T[r + a, r + b] = A[a, b]
+            T[r + a, a] = 1                                             # :21-22
+        E = mp.expm(mp.mpf(t) * T)                                      # :23
+        mexp = mp.expm(-mp.mpf(t) * A)                                  # :28
+        UM = mp.zeros(n, 2 * r)
+        for j in range(n):
+            for a in range(r):
+                UM[j, a] = Um[j, a]; UM[j, r + a] = Mm[j, a]
+        tmp = UM * E[:, 0:r] * mexp                                     # :29
+        out = np.array([[float(tmp[j, a]) for a in range(r)] for j in range(n)])
+    return out / np.linalg.norm(out, axis=0, keepdims=True)            # :30-35
+
+
 # --------------------------------------------------------------------------- sampler
 def sgld_update(w, U, gradw, gradU, epsw, epsU, noise_w=None, noise_U=None, langevin=True, stiefel=True):
     """The update half of the loop body, GPT_SGLD.jl:411-439, from given gradients.  Returns (w, U, nan_flag)."""
@@ -404,3 +449,136 @@ def GPT_SGLDERMw(phi, y, signal_var, I, r, Q, m, epsw, burnin, maxepoch, w0, U0,
                 w_store[:, (epoch - burnin - 1) * numbatches + batch - 1] = w               # :1111-1113
             step += 1
     return w_store, U
+
+
+def GPT_SGLDERM_RMSprop(phi, y, signal_var, I, r, Q, m, epsilon, alpha, burnin, maxepoch, w0, U0, perms, noise_w, noise_U,
+                        lam=1e-5):
+    """GPT_SGLD.jl:1121-1237 with the draws injected (w0/U0 for :1135-1141, perms for :1151, noise_w[step][Q] for :1188,
+    noise_U[step][n,r,D] for :1221).  RMSprop-preconditioned SGLD-ERM:
+      * gw, gU are moving averages of the squared UNNORMALISED gradients (1/batch_size) ... (:1172-1176, :1204-1211);
+      * w takes a per-element step size epsw = epsilon/(sqrt(gw)+lambda) (:1177, :1188);
+      * every U^(k) takes the mean of its elements' step sizes (:1212-1213), since a geodesic needs a scalar time;
+      * computeA is called AFTER the w update and therefore sees the new w (:1188 precedes :1194), while the residual
+        y_batch - fhat still comes from the old w (:1169).
+    Returns (w_store, U_store) like GPTregression; all zeros after a NaN in the geodesic (:1223-1225)."""
+    phi = np.array(phi, dtype=np.float64, order="F")
+    y = np.array(y, dtype=np.float64)
+    n, D, N = phi.shape
+    numbatches = int(np.ceil(N / m))
+    T = maxepoch * numbatches
+    w_store = np.zeros((Q, T)); U_store = np.zeros((n, r, D, T))
+    w = np.array(w0, dtype=np.float64); U = np.array(U0, dtype=np.float64)
+    gw = np.zeros(Q); gU = np.zeros((n, r, D))
+    step = 0
+    for epoch in range(1, burnin + maxepoch + 1):
+        perm = perms[epoch - 1]
+        phi = phi[:, :, perm]; y = y[perm]
+        for batch in range(1, numbatches + 1):
+            lo, hi = m * (batch - 1), min(m * batch, N)
+            pb, yb = phi[:, :, lo:hi], y[lo:hi]
+            bs = hi - lo
+            temp = phidotU(U, pb)
+            V = computeV(temp, I)
+            fhat = computefhat(V, w)
+            gradw = (1.0 / bs) * (V @ (yb - fhat)) / signal_var                      # :1172
+            gw = alpha * gw + (1 - alpha) * gradw ** 2                                # :1175
+            epsw = epsilon / (np.sqrt(gw) + lam)                                      # :1176
+            gradw = N * gradw - w                                                     # :1186 (sigma_w = 1)
+            w = w + epsw * gradw / 2 + np.sqrt(epsw) * np.asarray(noise_w[step])      # :1188
+            A = computeA(computeU_phi(V, temp, I), w, I, r)                           # :1191-1194: the NEW w
+            gradU = (1.0 / bs) * np.einsum("jki,lki,i->jlk", pb, A, yb - fhat, optimize=True) / signal_var   # :1200-1203
+            gU = alpha * gU + (1 - alpha) * gradU ** 2                                # :1210
+            epsU = epsilon / (np.sqrt(gU) + lam)                                      # :1211
+            meanepsU = epsU.mean(axis=(0, 1))                                         # :1212
+            gradU = N * gradU                                                         # :1221
+            for k in range(D):
+                t = np.sqrt(meanepsU[k])
+                mom = proj(U[:, :, k], t * gradU[:, :, k] / 2 + np.asarray(noise_U[step])[:, :, k])   # :1225
+                Uk, bad = geod(U[:, :, k], mom, t)                                    # :1226
+                if bad:
+                    return np.zeros((Q, T)), np.zeros((n, r, D, T))                   # :1227-1229
+                U[:, :, k] = Uk
+            if epoch > burnin:
+                col = (epoch - burnin - 1) * numbatches + batch - 1                   # :1231-1234
+                w_store[:, col] = w
+                U_store[:, :, :, col] = U
+            step += 1
+    return w_store, U_store
+
+
+def geodboth(U, mom, t):
+    """GPT_SGLD.jl:40-59: the geodesic and the parallel-transported momentum.  Returns (Unew, momnew, nan_flag);
+    Unew has its columns renormalised (:51-56), momnew = [U mom] E[:, r+1:2r] expm(-tA) is returned as it is (:50)."""
+    n, r = U.shape
+    A = U.T @ mom
+    temp = np.block([[A, -mom.T @ mom], [np.eye(r), A]])
+    with np.errstate(all="ignore"):
+        E = _expm(t * temp)
+    if np.isnan(E).any():
+        return np.zeros((n, r)), np.zeros((n, r)), True
+    mexp = _expm(-t * A)
+    UM = np.hstack([U, mom])
+    tmpU = UM @ E[:, :r] @ mexp
+    tmpV = UM @ E[:, r:] @ mexp
+    return tmpU / np.linalg.norm(tmpU, axis=0, keepdims=True), tmpV, False
+
+
+def GPT_GMC(phi, y, signal_var, I, r, Q, epsw, epsU, burnin, maxepoch, L, w0, U0, noise_p, noise_mom, unif,
+            restore_U_on_reject=False):
+    """GPT_SGLD.jl:684-805, geodesic Monte Carlo (full-batch HMC on w and on the Stiefel factors), draws injected:
+    w0/U0 for :697-704, noise_p[epoch][Q] for :709, noise_mom[epoch][n,r,D] for :711, unif[epoch] for :787.
+    Returns (w_store[Q,maxepoch], U_store[n,r,D,maxepoch], accept_prob[burnin+maxepoch]).
+
+    Reference quirk kept by default: `w_old=w; U_old=U` (:707) are aliases in Julia; `w+=...` (:742) rebinds w, but
+    `U[:,:,k],mom[:,:,k]=geodboth(...)` (:745) writes into the array U_old also names — so a rejected proposal (:793-795)
+    restores w and leaves U at the proposed value.  restore_U_on_reject=True gives the textbook behaviour instead."""
+    phi = np.asarray(phi, dtype=np.float64)
+    y = np.asarray(y, dtype=np.float64)
+    n, D, N = phi.shape
+    w = np.array(w0, dtype=np.float64); U = np.array(U0, dtype=np.float64)
+    w_store = np.zeros((Q, maxepoch)); U_store = np.zeros((n, r, D, maxepoch))
+    accept = np.zeros(burnin + maxepoch)
+
+    def grads(w_, U_):
+        temp = phidotU(U_, phi); V = computeV(temp, I); fhat = computefhat(V, w_)
+        gradw = V @ (y - fhat) / signal_var - w_                                              # :723 / :762
+        A = computeA(computeU_phi(V, temp, I), w_, I, r)
+        gradU = np.einsum("jki,lki,i->jlk", phi, A, (y - fhat) / signal_var, optimize=True)   # :733-736 / :772-775
+        return gradw, gradU, fhat
+
+    for epoch in range(1, burnin + maxepoch + 1):
+        w_old = w.copy(); U_old = U.copy()
+        p = np.array(noise_p[epoch - 1], dtype=np.float64)                                    # :709
+        mom = np.stack([proj(U[:, :, k], np.asarray(noise_mom[epoch - 1])[:, :, k]) for k in range(D)], 2)   # :710-712
+        H_old = (-np.sum(w * w) / 2 - np.linalg.norm(y - pred(w, U, I, phi)) ** 2 / (2 * signal_var)
+                 - np.sum(mom * mom) / 2 - np.sum(p * p) / 2)                                 # :713
+        pred_new = None
+        for l in range(L):
+            gradw, gradU, _ = grads(w, U)
+            p = p + np.sqrt(epsw) * gradw / 2                                                 # :725
+            for k in range(D):
+                mom[:, :, k] = proj(U[:, :, k], mom[:, :, k] + np.sqrt(epsU) * gradU[:, :, k] / 2)   # :738-740
+            w = w + np.sqrt(epsw) * p                                                         # :742
+            for k in range(D):
+                Uk, mk, bad = geodboth(U[:, :, k], mom[:, :, k], np.sqrt(epsU))               # :745
+                if bad:
+                    return np.zeros((Q, maxepoch)), np.zeros((n, r, D, maxepoch)), np.full(burnin + maxepoch, np.nan)   # :746-748
+                U[:, :, k] = Uk; mom[:, :, k] = mk
+            gradw, gradU, fhat = grads(w, U)
+            p = p + np.sqrt(epsw) * gradw / 2                                                 # :764
+            for k in range(D):
+                mom[:, :, k] = proj(U[:, :, k], mom[:, :, k] + np.sqrt(epsU) * gradU[:, :, k] / 2)   # :777-779
+            if l == L - 1:
+                pred_new = fhat                                                               # :782-784
+        H = (-np.sum(w * w) / 2 - np.linalg.norm(y - pred_new) ** 2 / (2 * signal_var)
+             - np.sum(mom * mom) / 2 - np.sum(p * p) / 2)                                     # :787
+        with np.errstate(over="ignore"):
+            accept[epoch - 1] = np.exp(H - H_old)                                             # :790
+        if unif[epoch - 1] > accept[epoch - 1]:                                               # :793: reject
+            w = w_old
+            if restore_U_on_reject:
+                U = U_old
+        if epoch > burnin:
+            w_store[:, epoch - burnin - 1] = w
+            U_store[:, :, :, epoch - burnin - 1] = U
+    return w_store, U_store, accept

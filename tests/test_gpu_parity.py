@@ -643,3 +643,54 @@ def test_nodes_pred_samples_vs_oracle(r, S, order, feature2):
         a = m.pred(ws[:, 0], Us[:, :, :, 0], P["X"])
         b = m.pred(ws[:, 1], Us[:, :, :, 1], P["X"][:777])
     assert relerr(a, want[:, 0]) < 1e-4 and relerr(b, want[:777, 1]) < 1e-4
+
+
+def test_geod_vs_independent_pins():
+    """gptb_geod against the two pins of `geod` that do not involve the oracle's expm: the great circle for r = 1 and
+    the 40-digit mpmath evaluations of GPT_SGLD.jl:19-37 in tests/golden/geod_mp.npz (r in {2,10,32}, t in {1e-7,1e-3,0.3})."""
+    rng = np.random.default_rng(4)
+    for n in (2, 7, 300):
+        u = rng.standard_normal((n, 1)); u /= np.linalg.norm(u)
+        m = o.proj(u, rng.standard_normal((n, 1)))
+        for t in (1e-7, 1e-3, 0.3, 2.5):
+            assert np.abs(G.geod(u, m, t) - o.geod_great_circle(u, m, t)).max() < 1e-12
+    g = load_golden("geod_mp.npz")
+    for c in range(int(g["ncases"])):
+        got = G.geod(g[f"U{c}"], g[f"M{c}"], float(g[f"t{c}"]))
+        assert relerr(got, g[f"geod{c}"]) < 1e-10, c
+
+
+@pytest.mark.parametrize("prec,alg,phi_mode", [(L.PREC_FP64, L.ALG_DIRECT, False), (L.PREC_FP64, L.ALG_DIRECT, True),
+                                               (L.PREC_TC3, L.ALG_DIRECT, False), (L.PREC_TC3, L.ALG_NODES, False)],
+                         ids=["fp64", "fp64-densephi", "tc3-direct", "tc3-nodes"])
+def test_GPT_SGLDERM_RMSprop_vs_oracle(prec, alg, phi_mode):
+    """RMSprop-preconditioned sampler (GPT_SGLD.jl:1121-1237, GPTB_FLAG_RMSPROP) with injected draws: per-element step
+    sizes for w, one mean step size per U^(k), computeA on the already-updated w, moving averages carried over the
+    steps (short last batch, burn-in, store layout as in GPTregression)."""
+    P = make_problem(3, 150, 16, 4, Q=20, seed=8)
+    N, m, burnin, maxepoch, eps, alpha = 150, 64, 1, 2, 2e-5, 0.9
+    rng = np.random.default_rng(2)
+    perms = [rng.permutation(N) for _ in range(burnin + maxepoch)]
+    steps = (burnin + maxepoch) * 3
+    NW = rng.standard_normal((steps, P["Q"])); NU = rng.standard_normal((steps, P["n"], P["r"], P["D"]))
+    phi = P["phi_fn"](P["X"])
+    ws, Us = o.GPT_SGLDERM_RMSprop(phi, P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m, eps, alpha, burnin, maxepoch,
+                                   P["w0"], P["U0"], perms, NW, NU)
+    assert np.isfinite(ws).all() and ws.any()
+    gw, gU = G.GPT_SGLDERM_RMSprop(phi if phi_mode else _feat(P), P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m, eps, alpha,
+                                   burnin, maxepoch, 1, precision=prec, w0=P["w0"], U0=P["U0"], perms=np.stack(perms),
+                                   noise_w=NW, noise_U=NU, options={L.OPT_ALGORITHM: alg})
+    assert gw.shape == ws.shape and gU.shape == Us.shape
+    # FP64 pins the logic.  In TC3 the gradient is within 1e-4 NORM-wise, and RMSprop divides every element by the running
+    # magnitude of its own gradient: elements with small gradients carry a larger relative error into the update, so
+    # the accumulated update is compared at 1e-3 and the chain values themselves at 1e-4
+    tol = 1e-8 if prec == L.PREC_FP64 else 1e-3
+    assert relerr(gw - P["w0"][:, None], ws - P["w0"][:, None]) < tol
+    assert relerr(gU - P["U0"][..., None], Us - P["U0"][..., None]) < tol
+    assert relerr(gw, ws) < min(tol, 1e-4) and relerr(gU, Us) < min(tol, 1e-4)
+    # production mode: reproducible, on the manifold, and a second run on the same seed starts from fresh averages
+    a = G.GPT_SGLDERM_RMSprop(_feat(P), P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m, eps, alpha, 0, 2, 5, precision=prec)
+    b = G.GPT_SGLDERM_RMSprop(_feat(P), P["y"], P["signal_var"], P["I"], P["r"], P["Q"], m, eps, alpha, 0, 2, 5, precision=prec)
+    assert relerr(a[0], b[0]) < 1e-5 and relerr(a[1], b[1]) < 1e-5
+    for k in range(P["D"]):
+        assert np.abs(a[1][:, :, k, -1].T @ a[1][:, :, k, -1] - np.eye(P["r"])).max() < 1e-10

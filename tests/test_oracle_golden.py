@@ -216,3 +216,29 @@ def test_chunked_gradients_and_update_split_match_the_one_piece_oracle():
     s1 = o.sgld_step(phi, P["y"][idx], P["w0"], P["U0"], P["I"], P["N"], P["signal_var"], 1e-5, 1e-8, nw, nU)
     s2 = o.sgld_update(P["w0"], P["U0"], a[0], a[1], 1e-5, 1e-8, nw, nU)
     assert np.array_equal(s1[0], s2[0]) and np.array_equal(s1[1], s2[1])
+
+
+def test_geod_pinned_by_closed_form_and_arbitrary_precision():
+    """`geod` (GPT_SGLD.jl:19-37) has no known-answer test in the reference.  Two independent pins: the great circle for
+    r = 1, and 40-digit mpmath evaluations of the same lines (tests/golden/geod_mp.npz, made by make_geod_golden.py) —
+    for the NumPy oracle (SciPy expm), the C oracle (its own Pade-13) and the 2r x 2r exponential by itself."""
+    import c_oracle as co
+    rng = np.random.default_rng(4)
+    for n in (2, 7, 300):
+        u = rng.standard_normal((n, 1)); u /= np.linalg.norm(u)
+        m = o.proj(u, rng.standard_normal((n, 1)))
+        for t in (1e-7, 1e-3, 0.3, 2.5):
+            want = o.geod_great_circle(u, m, t)
+            assert np.abs(o.geod(u, m, t)[0] - want).max() < 1e-14
+            assert np.abs(co.geod(u, m, t)[0] - want).max() < 1e-14
+    g = load_golden("geod_mp.npz")
+    for c in range(int(g["ncases"])):
+        U, M, t = g[f"U{c}"], g[f"M{c}"], float(g[f"t{c}"])
+        r = U.shape[1]
+        A = U.T @ M
+        blk = t * np.block([[A, -M.T @ M], [np.eye(r), A]])
+        from scipy.linalg import expm
+        assert relerr(expm(blk), g[f"expm{c}"]) < 1e-14, c
+        assert relerr(co.expm(blk), g[f"expm{c}"]) < 1e-13, c
+        assert relerr(o.geod(U, M, t)[0], g[f"geod{c}"]) < 1e-14, c
+        assert relerr(co.geod(U, M, t)[0], g[f"geod{c}"]) < 1e-13, c
