@@ -53,6 +53,9 @@ PROTOTYPES = {
     "gptb_proj": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, c_double_p, c_double_p, c_double_p]),
     "gptb_proj_noalloc": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gptb_geod": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, c_double_p, c_double_p, C.c_double, c_double_p]),
+    "gptb_geodboth": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, c_double_p, c_double_p, C.c_double, c_double_p, c_double_p]),
+    "gptb_gmc_run": (C.c_int, [H, C.c_double, C.c_double, C.c_double, C.c_int32, C.c_int32, C.c_int32, C.c_int32, c_double_p,
+                               c_double_p, c_double_p, c_double_p, c_double_p, c_double_p]),
     "gptb_sgld_step": (C.c_int, [H, C.c_double, c_int64_p, C.c_int64, C.c_int64, C.c_double, C.c_double, C.c_int32,
                                  c_double_p, c_double_p]),
     "gptb_sgld_step_host": (C.c_int, [H, C.c_double, c_double_p, c_double_p, C.c_int64, C.c_int64, C.c_double,

@@ -1282,11 +1282,9 @@ int gptb_grad(gptb_handle *h, double signal_var, const int64_t *idx, int64_t sta
     return GPTB_OK;
 }
 
-int gptb_proj(int32_t device, int32_t n, int32_t r, const double *U, const double *V, double *out);
-int gptb_geod(int32_t device, int32_t n, int32_t r, const double *U, const double *mom, double t, double *out);
 
 static int proj_geod_host(int32_t device, int32_t n, int32_t r, const double *U, const double *V, double t, double *out,
-                          int mode) {
+                          int mode, double *out2 = nullptr) {
     if (!U || !V || !out || n < 1 || r < 1 || r > 64) {
         gptb_set_error(nullptr, "proj/geod: bad argument (need n>=1, 1<=r<=64)");
         return GPTB_ERR_ARG;
@@ -1300,31 +1298,34 @@ static int proj_geod_host(int32_t device, int32_t n, int32_t r, const double *U,
     if (device >= 0) cudaSetDevice(device);
     cudaStream_t s;
     if (cudaStreamCreate(&s) != cudaSuccess) return GPTB_ERR_CUDA;
-    double *dU = nullptr, *dV = nullptr, *dO = nullptr;
+    double *dU = nullptr, *dV = nullptr, *dO = nullptr, *dO2 = nullptr;
     int32_t *flag = nullptr;
     size_t bytes = sizeof(double) * (size_t)n * r;
     int st = GPTB_OK;
     if (cudaMalloc(&dU, bytes) != cudaSuccess || cudaMalloc(&dV, bytes) != cudaSuccess ||
-        cudaMalloc(&dO, bytes) != cudaSuccess || cudaMalloc(&flag, sizeof(int32_t)) != cudaSuccess)
+        cudaMalloc(&dO, bytes) != cudaSuccess || cudaMalloc(&flag, sizeof(int32_t)) != cudaSuccess ||
+        (out2 && cudaMalloc(&dO2, bytes) != cudaSuccess))
         st = GPTB_ERR_NOMEM;
     if (st == GPTB_OK) {
         cudaMemcpyAsync(dU, U, bytes, cudaMemcpyHostToDevice, s);
         cudaMemcpyAsync(dV, V, bytes, cudaMemcpyHostToDevice, s);
         cudaMemsetAsync(flag, 0, sizeof(int32_t), s);
-        st = gptb_proj_geod_device(&tmp, s, n, r, dU, dV, t, dO, mode, flag);
+        st = gptb_proj_geod_device(&tmp, s, n, r, dU, dV, t, dO, mode, flag, dO2);
     }
     int32_t bad = 0;
     if (st == GPTB_OK) {
         cudaMemcpyAsync(&bad, flag, sizeof(int32_t), cudaMemcpyDeviceToHost, s);
         cudaMemcpyAsync(out, dO, bytes, cudaMemcpyDeviceToHost, s);
+        if (out2) cudaMemcpyAsync(out2, dO2, bytes, cudaMemcpyDeviceToHost, s);
         if (cudaStreamSynchronize(s) != cudaSuccess) st = GPTB_ERR_CUDA;
     }
     if (st == GPTB_OK && bad) {
         memset(out, 0, bytes);  // return zeros(n,r), GPT_SGLD.jl:26
+        if (out2) memset(out2, 0, bytes);   // ... and zeros(n,r) for the momentum, :45
         gptb_set_error(nullptr, "Get NaN when moving along Geodesic. Try smaller epsU");
         st = GPTB_GEODESIC_NAN;
     }
-    cudaFree(dU); cudaFree(dV); cudaFree(dO); cudaFree(flag);
+    cudaFree(dU); cudaFree(dV); cudaFree(dO); cudaFree(dO2); cudaFree(flag);
     cudaStreamDestroy(s);
     return st;
 }
@@ -1335,6 +1336,12 @@ int gptb_proj(int32_t device, int32_t n, int32_t r, const double *U, const doubl
 
 int gptb_geod(int32_t device, int32_t n, int32_t r, const double *U, const double *mom, double t, double *out) {
     return proj_geod_host(device, n, r, U, mom, t, out, 1);
+}
+
+int gptb_geodboth(int32_t device, int32_t n, int32_t r, const double *U, const double *mom, double t, double *U_out,
+                  double *mom_out) {
+    if (!mom_out) return GPTB_ERR_ARG;
+    return proj_geod_host(device, n, r, U, mom, t, U_out, 1, mom_out);
 }
 
 static int step_common(gptb_handle *h, double signal_var, const int32_t *rows, int64_t bs, int64_t N_total,

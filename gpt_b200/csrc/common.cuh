@@ -299,7 +299,8 @@ int gptb_update_alloc_noise(gptb_handle *h);
 int gptb_launch_rms_w(gptb_handle *h, int flags, const double *noise_w, uint64_t step, cudaStream_t s);
 int gptb_launch_rms_U(gptb_handle *h, cudaStream_t s);
 int gptb_proj_geod_device(gptb_handle *scratch_owner, cudaStream_t s, int n, int r, const double *U, const double *V,
-                          double t, double *out, int mode /*0 proj, 1 geod*/, int32_t *nan_flag);
+                          double t, double *out, int mode /*0 proj, 1 geod*/, int32_t *nan_flag,
+                          double *out2 = nullptr /*geodboth: the transported momentum*/);
 // batch.cu
 int gptb_launch_gather(gptb_handle *h, const int32_t *rows, int64_t start, int64_t bs, int64_t row_off);
 // (both gathers also emit the node-grid cell / offset of every row when h->gather_cells is set)

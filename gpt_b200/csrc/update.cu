@@ -536,7 +536,9 @@ __device__ void sexpm(double *M, int n2, double *buf, int *bad_s) {
 // tangent vector `mom` of geod(U,mom,t) (GPT_SGLD.jl:19-37 called directly).
 __global__ void __launch_bounds__(1024)
 k_small(double *__restrict__ small, size_t small_stride, int r, double t, int use_sym, int32_t *nan_flag,
-        int use_smem, const double *__restrict__ epsk_sum = nullptr, double inv_cnt = 0.0) {
+        int use_smem, const double *__restrict__ epsk_sum = nullptr, double inv_cnt = 0.0, int both = 0) {
+    // both != 0 (geodboth, GPT_SGLD.jl:40-59): also leaves C1' = W'[0:r], C2' = W'[r:2r] of W' = E[:, r+1:2r] expm(-tA) in
+    // the A / MM slots, so that the transported momentum is U C1' + mom C2' (:50)
     extern __shared__ double sm[];
     __shared__ int bad;
     if (epsk_sum) t = sqrt(epsk_sum[blockIdx.x] * inv_cnt);
@@ -611,6 +613,16 @@ k_small(double *__restrict__ small, size_t small_stride, int r, double t, int us
         C1[i] = W[a + r2 * b] - s;
         C2[i] = W[(a + r) + r2 * b];
     }
+    if (both) {
+        __syncthreads();
+        double *Wp = sk + L.E;                       // scratch again now that E sits in Tm
+        bmm(Tm + (size_t)r2 * r, X, Wp, r2, r, r);   // columns r..2r-1 of E (col-major: entries from r2*r on)
+        for (int i = threadIdx.x; i < rr; i += blockDim.x) {
+            int a = i % r, b = i / r;
+            A[i] = Wp[a + r2 * b];
+            MM[i] = Wp[(a + r) + r2 * b];
+        }
+    }
 }
 
 // ---------------------------------------------------------------- P3: Unew = U C1 + G C2 -> G ; column norms
@@ -664,6 +676,18 @@ __global__ void k_finish(double *__restrict__ U, const double *__restrict__ G, c
     for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
         int l = (int)(e / n);
         U[(size_t)k * total + e] = G[(size_t)k * total + e] / sqrt(cn[l]);
+    }
+}
+
+// out = U C1 + V C2 for r x r matrices C1, C2 in global memory (the transported momentum of geodboth, :50)
+__global__ void k_apply_plain(const double *__restrict__ U, const double *__restrict__ V, const double *__restrict__ C1,
+                              const double *__restrict__ C2, int n, int r, double *__restrict__ out) {
+    const size_t total = (size_t)r * n;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const int j = (int)(e % n), l = (int)(e / n);
+        double s = 0.0;
+        for (int a = 0; a < r; ++a) s += U[(size_t)a * n + j] * C1[a + r * l] + V[(size_t)a * n + j] * C2[a + r * l];
+        out[e] = s;
     }
 }
 
@@ -1301,7 +1325,7 @@ int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, cons
 
 // Standalone proj (mode 0) / geod (mode 1) on device buffers U, V (n x r col-major); scratch from `h`.
 int gptb_proj_geod_device(gptb_handle *h, cudaStream_t s, int n, int r, const double *U, const double *V, double t,
-                          double *out, int mode, int32_t *nan_flag) {
+                          double *out, int mode, int32_t *nan_flag, double *out2) {
     SmallLayout L(r);
     double *small = nullptr;
     optin_smem();
@@ -1316,7 +1340,11 @@ int gptb_proj_geod_device(gptb_handle *h, cudaStream_t s, int n, int r, const do
     } else {
         {
             size_t sb = small_smem_bytes(r);
-            k_small<<<1, 1024, sb, s>>>(small, L.total, r, t, 0, nan_flag, sb ? 1 : 0);
+            k_small<<<1, 1024, sb, s>>>(small, L.total, r, t, 0, nan_flag, sb ? 1 : 0, nullptr, 0.0, out2 ? 1 : 0);
+        }
+        if (out2) {   // geodboth: tmpV = [U mom] E[:, r+1:2r] expm(-tA), not normalised (:50)
+            int fb2 = (int)std::min<size_t>(((size_t)r * n + 255) / 256, 1024);
+            k_apply_plain<<<fb2, 256, 0, s>>>(U, V, small + L.A, small + L.MM, n, r, out2);
         }
         // Unew = U C1 + V C2 written over a copy of V (k_apply overwrites its G argument)
         cudaMemcpyAsync(out, V, sizeof(double) * (size_t)n * r, cudaMemcpyDeviceToDevice, s);

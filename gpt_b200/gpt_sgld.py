@@ -27,7 +27,7 @@ import numpy as np
 
 from . import _lib as L
 
-__all__ = ["feature", "feature2", "samplenz", "pred", "pred_samples", "GPTregression", "GPT_SGLDERMw", "GPT_SGLDERM_RMSprop", "proj", "geod",
+__all__ = ["feature", "feature2", "samplenz", "pred", "pred_samples", "GPTregression", "GPT_SGLDERMw", "GPT_SGLDERM_RMSprop", "GPT_GMC", "proj", "geod", "geodboth",
            "datawhitening", "RFFFeatures", "Model", "GptbError", "GeodesicNaN", "shard_range"]
 
 
@@ -502,6 +502,53 @@ def geod(U, mom, t):
         return out
     _check(st, None)
     return out
+
+
+def geodboth(U, mom, t):
+    """GPT_SGLD.jl:40-59: (geodesic point with unit columns, transported momentum).  On NaN prints the reference's
+    warning and returns zeros for both."""
+    U = _f64(U); mom = _f64(mom)
+    out = np.empty(U.shape, order="F"); out2 = np.empty(U.shape, order="F")
+    st = L.load().gptb_geodboth(_default_device, U.shape[0], U.shape[1], _dp(U), _dp(mom), float(t), _dp(out), _dp(out2))
+    if st == L.GEODESIC_NAN:
+        print("Get NaN when moving along Geodesic. Try smaller epsU")
+        return out, out2
+    _check(st, None)
+    return out, out2
+
+
+def GPT_GMC(phi, y, signal_var, I, r, Q, epsw, epsU, burnin, maxepoch, L_, param_seed, *, precision: Optional[int] = None,
+            w0=None, U0=None, noise_p=None, noise_mom=None, unif=None, restore_U_on_reject=False, options=None):
+    """GPT_SGLD.jl:684-805, geodesic Monte Carlo with L_ leapfrog steps per epoch.  Returns (w_store[Q,maxepoch],
+    U_store[n,r,D,maxepoch], accept_prob[burnin+maxepoch]) like the reference; after a NaN in the geodesic it prints the
+    reference's warning and returns zero stores and NaN acceptance probabilities (:746-748).  Keyword-only extras inject
+    the draws; restore_U_on_reject=False keeps the reference's aliasing behaviour (see include/gptb200.h)."""
+    y = np.ravel(np.asarray(y, dtype=np.float64))
+    with _model_for(phi, r, Q, I, precision, seed=int(param_seed), options=options) as mdl:
+        if isinstance(phi, RFFFeatures):
+            mdl.set_train(phi.X, y)
+            n, D = phi.shape[0], phi.shape[1]
+        else:
+            mdl.set_train_phi(phi, y)
+            n, D = phi.shape[0], phi.shape[1]
+        if w0 is not None:
+            mdl.set_params(w0, U0)
+        else:
+            mdl.init_params(param_seed, True)
+        T = burnin + maxepoch
+        w_store = np.zeros((Q, maxepoch), order="F"); U_store = np.zeros((n, r, D, maxepoch), order="F")
+        acc = np.zeros(T)
+        npq = None if noise_p is None else np.ascontiguousarray(np.asarray(noise_p, dtype=np.float64).reshape(T, Q))
+        nm = None if noise_mom is None else np.ascontiguousarray(
+            np.stack([np.asarray(a, dtype=np.float64).ravel(order="F") for a in noise_mom]))
+        un = None if unif is None else np.ascontiguousarray(np.asarray(unif, dtype=np.float64))
+        st = mdl.lib.gptb_gmc_run(mdl.h, float(signal_var), float(epsw), float(epsU), int(burnin), int(maxepoch), int(L_),
+                                  int(bool(restore_U_on_reject)), _dp(npq), _dp(nm), _dp(un), _dp(w_store), _dp(U_store), _dp(acc))
+        if st == L.GEODESIC_NAN:
+            print("Get NaN when moving along Geodesic. Try smaller epsU")
+            return w_store, U_store, acc
+        _check(st, mdl.h)
+        return w_store, U_store, acc
 
 
 # ------------------------------------------------------------------------------------------------

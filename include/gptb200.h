@@ -160,6 +160,12 @@ int gptb_proj_noalloc(int32_t n, int32_t r, const double *U_dev, const double *V
 /* geod(U,mom,t), GPT_SGLD.jl:19-37.  Returns GPTB_GEODESIC_NAN and zeros(n,r) when expm gives NaN. */
 int gptb_geod(int32_t device, int32_t n, int32_t r, const double *U, const double *mom, double t, double *out);
 
+/* geodboth(U,mom,t), GPT_SGLD.jl:40-59: the geodesic point U_out (columns renormalised, :51-56) and the transported
+ * momentum mom_out = [U mom] E[:, r+1:2r] expm(-tA) (:50, returned as it is).  GPTB_GEODESIC_NAN and zeros for both
+ * when expm gives NaN (:43-45). */
+int gptb_geodboth(int32_t device, int32_t n, int32_t r, const double *U, const double *mom, double t, double *U_out,
+                  double *mom_out);
+
 /* ---- sampler ------------------------------------------------------------------------------- */
 /* One loop body of GPTregression (GPT_SGLD.jl:378-439) on the resident training set.
  * noise_w[Q], noise_U[n,r,D]: the randn draws of :412/:420 supplied by the caller (test mode);
@@ -196,6 +202,19 @@ int gptb_sgld_step_host_wait(gptb_handle *h);
 int gptb_sgld_run(gptb_handle *h, double signal_var, int64_t m, double epsw, double epsU, int32_t burnin,
                   int32_t maxepoch, int32_t flags, const int64_t *perms, const double *noise_w,
                   const double *noise_U, double *w_store, double *U_store);
+
+/* GPT_GMC (GPT_SGLD.jl:684-805): geodesic Monte Carlo on the resident training set, starting from the handle's
+ * current parameters: per epoch fresh momenta (p = randn(Q), mom_k = proj(U_k, randn(n,r)), :709-712), L leapfrog steps
+ * with full-batch gradients (:715-785), Metropolis test on the Hamiltonian (:787-795).
+ *   noise_p[(burnin+maxepoch)*Q], noise_mom[(burnin+maxepoch)*n*r*D] (each epoch's block in Julia order), unif[burnin+maxepoch]:
+ *   the draws of :709, :711, :788 supplied by the caller, or NULL (Philox).
+ *   w_store[Q,maxepoch], U_store[n,r,D,maxepoch] (either may be NULL), accept_prob[burnin+maxepoch] = exp(H - H_old) (:790).
+ * restore_U_on_reject = 0 reproduces the reference: `U_old=U` (:707) aliases the array that :745 then writes into, so a
+ * rejected proposal restores w only; non-zero restores U as well.  On GPTB_GEODESIC_NAN the stores are zero-filled and
+ * accept_prob is NaN (:746-748).  The handle's parameters end at the chain's last state. */
+int gptb_gmc_run(gptb_handle *h, double signal_var, double epsw, double epsU, int32_t burnin, int32_t maxepoch, int32_t L,
+                 int32_t restore_U_on_reject, const double *noise_p, const double *noise_mom, const double *unif,
+                 double *w_store, double *U_store, double *accept_prob);
 
 /* The next nsteps loop bodies of the same sampler, continuing the epoch structure where the previous call
  * stopped (a fresh Philox permutation whenever an epoch starts), nothing stored — what burn-in epochs do.

@@ -694,3 +694,51 @@ def test_GPT_SGLDERM_RMSprop_vs_oracle(prec, alg, phi_mode):
     assert relerr(a[0], b[0]) < 1e-5 and relerr(a[1], b[1]) < 1e-5
     for k in range(P["D"]):
         assert np.abs(a[1][:, :, k, -1].T @ a[1][:, :, k, -1] - np.eye(P["r"])).max() < 1e-10
+
+
+def test_geodboth_vs_oracle():
+    """gptb_geodboth (GPT_SGLD.jl:40-59): geodesic point and transported momentum; the momentum stays tangent and keeps
+    its norm; the point equals geod's."""
+    rng = np.random.default_rng(12)
+    for n, r in ((50, 10), (300, 32), (9, 2), (40, 40)):
+        U = o.stiefel_from_gaussian(rng.standard_normal((r, n)))
+        M = o.proj(U, rng.standard_normal((n, r)))
+        for t in (1e-4, 0.05):
+            Un, Mn = G.geodboth(U, M, t)
+            wU, wM, _ = o.geodboth(U, M, t)
+            assert relerr(Un, wU) < 1e-10 and relerr(Mn, wM) < 1e-10
+            assert relerr(Un, G.geod(U, M, t)) < 1e-12
+            assert np.abs(Un.T @ Mn + Mn.T @ Un).max() < 1e-9 * max(1.0, np.abs(Mn).max() ** 2)
+    Z, Zm = G.geodboth(U, M * 1e200, 1e200)                               # NaN -> zeros for both (:43-45)
+    assert not Z.any() and not Zm.any()
+
+
+@pytest.mark.parametrize("prec", PRECS, ids=IDS)
+def test_GPT_GMC_vs_oracle(prec):
+    """Geodesic Monte Carlo (GPT_SGLD.jl:684-805) with injected momenta and uniforms: acceptance probabilities and the
+    stored chain against the oracle, including a REJECTED epoch (where the reference, through its aliasing of U_old,
+    restores w only) in both settings of restore_U_on_reject."""
+    P = make_problem(3, 120, 12, 3, Q=15, seed=8, signal_var=0.05)
+    rng = np.random.default_rng(2)
+    burnin, maxepoch, Lf = 1, 4, 3
+    T = burnin + maxepoch
+    NP = rng.standard_normal((T, P["Q"])); NM = rng.standard_normal((T, P["n"], P["r"], P["D"]))
+    un = rng.random(T)
+    un[2] = 1e9                                   # epoch 3 is rejected whatever its acceptance probability
+    phi = P["phi_fn"](P["X"])
+    tol = 1e-8 if prec == L.PREC_FP64 else 1e-4
+    for restore in (False, True):
+        ws, Us, acc = o.GPT_GMC(phi, P["y"], P["signal_var"], P["I"], P["r"], P["Q"], 1e-5, 1e-7, burnin, maxepoch, Lf, P["w0"],
+                                P["U0"], NP, NM, un, restore_U_on_reject=restore)
+        gw, gU, gacc = G.GPT_GMC(_feat(P), P["y"], P["signal_var"], P["I"], P["r"], P["Q"], 1e-5, 1e-7, burnin, maxepoch, Lf, 3,
+                                 precision=prec, w0=P["w0"], U0=P["U0"], noise_p=NP, noise_mom=NM, unif=un,
+                                 restore_U_on_reject=restore)
+        assert gw.shape == ws.shape and gU.shape == Us.shape and gacc.shape == acc.shape
+        # H is a difference of sums of ~N/signal_var: the acceptance probability inherits the gradient tolerance
+        assert np.abs(gacc / acc - 1).max() < (1e-7 if prec == L.PREC_FP64 else 2e-2)
+        assert relerr(gw, ws) < tol and relerr(gU, Us) < tol
+        # the rejected epoch: w equals the previous column; U does so only when restore_U_on_reject
+        assert np.array_equal(gw[:, 1], gw[:, 0])
+        assert np.array_equal(gU[..., 1], gU[..., 0]) == restore
+    z = G.GPT_GMC(_feat(P), P["y"], P["signal_var"], P["I"], P["r"], P["Q"], 1e-5, 1e300, 0, 2, 1, 3, precision=L.PREC_FP64)
+    assert not z[0].any() and not z[1].any() and np.isnan(z[2]).all()      # :746-748
