@@ -19,7 +19,9 @@
 module GPT_SGLD
 
 export datawhitening, feature, feature2, samplenz, pred, GPTregression, proj, geod, RFFFeatures,
-       featureNotensor, GPNT_SGLD, NTFeatures, GPT_SGLDERMw
+       featureNotensor, GPNT_SGLD, NTFeatures, GPT_SGLDERMw, GPT_SGLDERM_RMSprop, GPT_GMC, geodboth,
+       Model, pred_samples, posterior_mean, gradients, sgld_step!, sgld_advance!, synchronize, get_params, set_params!,
+       set_option!, set_domain!, comm_unique_id, comm_init!
 
 using Random, Statistics
 
@@ -273,6 +275,181 @@ function GPNT_SGLD(phi::NTFeatures, y::Array, signal_var::Real, sigma_theta::Rea
         return store
     finally
         ccall((:gptb_nt_destroy, LIB), Cint, (Ptr{Cvoid},), h)
+    end
+end
+
+# ---- a persistent handle: what long-running scripts hold instead of re-creating a handle per call ----------------
+# (kin40kExperiment.jl:74-87 trains, then predicts with many stored samples; one Model serves both and keeps the
+#  training set, the node grid and the sweep's buffers on the device between calls.)
+const FLAG_RMSPROP = Cint(8)
+const OPT_PIPE_GROUPS, OPT_PIPE_RESERVE, OPT_ALGORITHM, OPT_NODE_ORDER, OPT_NODE_THETA, OPT_RMS_ALPHA, OPT_RMS_LAMBDA =
+    Cint(0), Cint(1), Cint(2), Cint(3), Cint(4), Cint(5), Cint(6)
+const ALG_AUTO, ALG_DIRECT, ALG_NODES = 0.0, 1.0, 2.0
+
+mutable struct Model
+    h::Ptr{Cvoid}
+    D::Int; n::Int; r::Int; Q::Int; N::Int
+    function Model(phi::RFFFeatures, I::Array, r::Integer, Q::Integer; precision = PREC_TC3, device = -1, seed = 0)
+        n, D, N = size(phi)
+        h = create(D, n, r, Q; precision = precision, kind = phi.kind, device = device, seed = seed)
+        m = new(h, D, n, r, Q, 0)
+        finalizer(x -> (x.h == C_NULL || (destroy(x.h); x.h = C_NULL)), m)
+        set_features!(h, phi)
+        check(ccall((:gptb_set_index, LIB), Cint, (Ptr{Cvoid}, Ptr{Int32}), h, Matrix{Int32}(I)), h)
+        m
+    end
+end
+Base.close(m::Model) = (m.h == C_NULL || (destroy(m.h); m.h = C_NULL); nothing)
+
+set_option!(m::Model, option::Integer, value::Real) =
+    check(ccall((:gptb_set_option, LIB), Cint, (Ptr{Cvoid}, Int32, Float64), m.h, option, value), m.h)
+# bounds of every input column for the node grid when only host minibatches are passed (set_train! sets them itself)
+set_domain!(m::Model, lo::Vector{Float64}, hi::Vector{Float64}) =
+    check(ccall((:gptb_set_domain, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}), m.h, lo, hi), m.h)
+function set_train!(m::Model, X::Matrix{Float64}, y::Array)
+    m.N = size(X, 1)
+    check(ccall((:gptb_set_train, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int64), m.h, X, Vector{Float64}(vec(y)), m.N), m.h)
+end
+set_params!(m::Model, w::Vector{Float64}, U::Array{Float64,3}) =
+    check(ccall((:gptb_set_params, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}), m.h, w, U), m.h)
+init_params!(m::Model, param_seed::Integer; stiefel::Bool = true) =
+    check(ccall((:gptb_init_params, LIB), Cint, (Ptr{Cvoid}, UInt64, Int32), m.h, param_seed, stiefel ? 1 : 0), m.h)
+function get_params(m::Model)
+    w = zeros(m.Q); U = zeros(m.n, m.r, m.D)
+    check(ccall((:gptb_get_params, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}), m.h, w, U), m.h)
+    w, U
+end
+function synchronize(m::Model)
+    st = ccall((:gptb_synchronize, LIB), Cint, (Ptr{Cvoid},), m.h)
+    st == GPTB_GEODESIC_NAN && (println("Get NaN when moving along Geodesic. Try smaller epsU"); return false)
+    check(st, m.h); true
+end
+
+# The sample loop of kin40kExperiment.jl:75-87 / GPT_SGLD_p.jl:124-132 in one call: pred for every stored sample
+# (columns `cols` of the stores), mean over the samples and, on request, the Nt x S matrix of per-sample predictions.
+function pred_samples(m::Model, w_store::Matrix{Float64}, U_store::Array{Float64,4}, Xtest::Matrix{Float64};
+                      cols = 1:size(w_store, 2), per_sample::Bool = false)
+    ws = w_store[:, cols]; Us = U_store[:, :, :, cols]; S = size(ws, 2); Nt = size(Xtest, 1)
+    mean_out = Vector{Float64}(undef, Nt)
+    per = per_sample ? Matrix{Float64}(undef, Nt, S) : nothing
+    check(ccall((:gptb_pred_samples, LIB), Cint,
+                (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int32, Ptr{Float64}, Int64, Ptr{Float64}, Ptr{Float64}),
+                m.h, ws, Us, S, Xtest, Nt, mean_out, per_sample ? pointer(per) : Ptr{Float64}(C_NULL)), m.h)
+    per_sample ? (mean_out, per) : mean_out
+end
+# "average the last `last` epochs' samples" exactly as kin40kExperiment.jl:78-86 does: the last sample of each epoch
+posterior_mean(m::Model, w_store, U_store, Xtest, numbatches::Integer; last::Integer = 50) =
+    pred_samples(m, w_store, U_store, Xtest; cols = [e * numbatches for e in (size(w_store, 2) ÷ numbatches - last + 1):(size(w_store, 2) ÷ numbatches)])
+
+# minibatch gradients of the log posterior (GPT_SGLD.jl:384-408) at the model's current parameters;
+# idx: 1-based rows of the training set, or a contiguous range of the current (permuted) order
+function gradients(m::Model, signal_var::Real; idx::Union{Nothing,Vector{Int}} = nothing, start::Integer = 1,
+                   bs::Integer = m.N, include_prior::Bool = true)
+    gw = zeros(m.Q); gU = zeros(m.n, m.r, m.D)
+    i0 = idx === nothing ? Ptr{Int64}(C_NULL) : pointer(Int64.(idx .- 1))
+    nb = idx === nothing ? bs : length(idx)
+    fhat = zeros(nb)
+    check(ccall((:gptb_grad, LIB), Cint,
+                (Ptr{Cvoid}, Float64, Ptr{Int64}, Int64, Int64, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Int32),
+                m.h, signal_var, i0, start - 1, nb, gw, gU, fhat, include_prior ? 1 : 0), m.h)
+    gw, gU, fhat
+end
+
+# one loop body of GPTregression (GPT_SGLD.jl:378-439) on the resident training set; returns false after a geodesic NaN
+function sgld_step!(m::Model, signal_var::Real, epsw::Real, epsU::Real; idx::Union{Nothing,Vector{Int}} = nothing,
+                    start::Integer = 1, bs::Integer = m.N, langevin::Bool = true, stiefel::Bool = true, rmsprop::Bool = false,
+                    noise_w = nothing, noise_U = nothing)
+    flags = (langevin ? FLAG_LANGEVIN : Cint(0)) | (stiefel ? FLAG_STIEFEL : Cint(0)) | (rmsprop ? FLAG_RMSPROP : Cint(0))
+    i0 = idx === nothing ? Ptr{Int64}(C_NULL) : pointer(Int64.(idx .- 1))
+    p(x) = x === nothing ? Ptr{Float64}(C_NULL) : pointer(x)
+    st = ccall((:gptb_sgld_step, LIB), Cint,
+               (Ptr{Cvoid}, Float64, Ptr{Int64}, Int64, Int64, Float64, Float64, Int32, Ptr{Float64}, Ptr{Float64}),
+               m.h, signal_var, i0, start - 1, idx === nothing ? bs : length(idx), epsw, epsU, flags, p(noise_w), p(noise_U))
+    st == GPTB_GEODESIC_NAN && (println("Get NaN when moving along Geodesic. Try smaller epsU"); return false)
+    check(st, m.h); true
+end
+# the next nsteps loop bodies, nothing stored (burn-in); asynchronous — call synchronize(m)
+sgld_advance!(m::Model, signal_var::Real, mb::Integer, epsw::Real, epsU::Real, nsteps::Integer; langevin = true, stiefel = true) =
+    check(ccall((:gptb_sgld_advance, LIB), Cint, (Ptr{Cvoid}, Float64, Int64, Float64, Float64, Int32, Int64), m.h, signal_var, mb,
+                epsw, epsU, (langevin ? FLAG_LANGEVIN : Cint(0)) | (stiefel ? FLAG_STIEFEL : Cint(0)), nsteps), m.h)
+
+# ---- several GPUs: one Julia worker process per GPU (`julia -p G`, as the reference's GPT_SGLD_p.jl is run), every
+# worker owns a Model on its device; rank 1's id is sent to the others with the usual remotecall machinery.
+function comm_unique_id()
+    id = Vector{UInt8}(undef, 128)
+    check(ccall((:gptb_comm_unique_id, LIB), Cint, (Ptr{UInt8},), id)); id
+end
+comm_init!(m::Model, nranks::Integer, rank0::Integer, id::Vector{UInt8}) =
+    check(ccall((:gptb_comm_init, LIB), Cint, (Ptr{Cvoid}, Int32, Int32, Ptr{UInt8}), m.h, nranks, rank0, id), m.h)
+
+# GPT_SGLD.jl:40-59
+function geodboth(U::Array, mom::Array, t::Real)
+    n, r = size(U); Un = similar(U); Mn = similar(U)
+    st = ccall((:gptb_geodboth, LIB), Cint, (Int32, Int32, Int32, Ptr{Float64}, Ptr{Float64}, Float64, Ptr{Float64}, Ptr{Float64}),
+               -1, n, r, U, mom, t, Un, Mn)
+    if st == GPTB_GEODESIC_NAN
+        println("Get NaN when moving along Geodesic. Try smaller epsU")        # :44
+        return zeros(n, r), zeros(n, r)                                         # :45
+    end
+    check(st); Un, Mn
+end
+
+# shared set-up of the samplers below: handle with features, index, training set and initial parameters
+function sampler_handle(phi, y, I, r, Q, param_seed, precision)
+    n, D, N = size(phi); lazy = phi isa RFFFeatures
+    h = create(D, n, r, Q; precision = lazy ? precision : PREC_FP64, kind = lazy ? phi.kind : FEAT_COS, seed = param_seed)
+    check(ccall((:gptb_set_index, LIB), Cint, (Ptr{Cvoid}, Ptr{Int32}), h, Matrix{Int32}(I)), h)
+    yv = Vector{Float64}(vec(y))
+    if lazy
+        set_features!(h, phi)
+        check(ccall((:gptb_set_train, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int64), h, phi.X, yv, N), h)
+    else
+        check(ccall((:gptb_set_train_phi, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int64), h, phi, yv, N), h)
+    end
+    check(ccall((:gptb_init_params, LIB), Cint, (Ptr{Cvoid}, UInt64, Int32), h, param_seed, 1), h)
+    h, n, D, N
+end
+
+# GPT_SGLD.jl:1121-1237  GPT_SGLDERM_RMSprop(phi,y,signal_var,I,r,Q,m,epsilon,alpha,burnin,maxepoch)
+function GPT_SGLDERM_RMSprop(phi::Union{RFFFeatures,Array{Float64,3}}, y::Array, signal_var::Real, I::Array, r::Integer, Q::Integer,
+                             m::Integer, epsilon::Real, alpha::Real, burnin::Integer, maxepoch::Integer;
+                             param_seed::Integer = 0, precision = PREC_TC3)
+    h, n, D, N = sampler_handle(phi, y, I, r, Q, param_seed, precision)
+    try
+        check(ccall((:gptb_set_option, LIB), Cint, (Ptr{Cvoid}, Int32, Float64), h, OPT_RMS_ALPHA, alpha), h)
+        T = maxepoch * cld(N, m); w_store = zeros(Q, T); U_store = zeros(n, r, D, T)
+        st = ccall((:gptb_sgld_run, LIB), Cint,
+                   (Ptr{Cvoid}, Float64, Int64, Float64, Float64, Int32, Int32, Int32, Ptr{Int64}, Ptr{Float64}, Ptr{Float64},
+                    Ptr{Float64}, Ptr{Float64}),
+                   h, signal_var, m, epsilon, 0.0, burnin, maxepoch, FLAG_LANGEVIN | FLAG_STIEFEL | FLAG_RMSPROP, C_NULL, C_NULL, C_NULL,
+                   w_store, U_store)
+        st == GPTB_GEODESIC_NAN && (println("Get NaN when moving along Geodesic. Try smaller epsU"); return w_store, U_store)   # :1227-1229
+        check(st, h)
+        return w_store, U_store
+    finally
+        destroy(h)
+    end
+end
+
+# GPT_SGLD.jl:684-805  GPT_GMC(phi,y,signal_var,I,r,Q,epsw,epsU,burnin,maxepoch,L,param_seed)
+# restore_U_on_reject=false keeps the reference's behaviour (its `U_old=U` is an alias of the array the leapfrog writes into).
+function GPT_GMC(phi::Union{RFFFeatures,Array{Float64,3}}, y::Array, signal_var::Real, I::Array, r::Integer, Q::Integer,
+                 epsw::Real, epsU::Real, burnin::Integer, maxepoch::Integer, L::Integer, param_seed::Integer;
+                 precision = PREC_TC3, restore_U_on_reject::Bool = false)
+    h, n, D, N = sampler_handle(phi, y, I, r, Q, param_seed, precision)
+    try
+        w_store = zeros(Q, maxepoch); U_store = zeros(n, r, D, maxepoch); accept_prob = zeros(maxepoch + burnin)
+        st = ccall((:gptb_gmc_run, LIB), Cint,
+                   (Ptr{Cvoid}, Float64, Float64, Float64, Int32, Int32, Int32, Int32, Ptr{Float64}, Ptr{Float64}, Ptr{Float64},
+                    Ptr{Float64}, Ptr{Float64}, Ptr{Float64}),
+                   h, signal_var, epsw, epsU, burnin, maxepoch, L, restore_U_on_reject ? 1 : 0, C_NULL, C_NULL, C_NULL,
+                   w_store, U_store, accept_prob)
+        st == GPTB_GEODESIC_NAN && (println("Get NaN when moving along Geodesic. Try smaller epsU"); return w_store, U_store, accept_prob)  # :746-748
+        check(st, h)
+        for a in accept_prob; println("accept_prob=", a); end                                             # :791
+        return w_store, U_store, accept_prob
+    finally
+        destroy(h)
     end
 end
 

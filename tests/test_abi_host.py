@@ -99,3 +99,38 @@ def test_datawhitening_and_feature_handles():
         G.feature2(X, 1.0, 1.0, 1.0, Z[:5])                               # n not even
     with pytest.raises(ValueError):
         G.feature(X, 1.0, 1.0, 1.0, Z, b[:5])
+
+
+def test_julia_shim_binds_declared_symbols_with_matching_arity():
+    """julia/GPT_SGLD.jl cannot be executed in this image (no julia binary): statically check that every ccall names a
+    symbol include/gptb200.h declares and passes as many argument types as the C prototype has parameters."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "gptb200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", " ", hdr, flags=re.S)
+    protos = {}
+    for mt in re.finditer(r"\b(?:int|const char \*)\s*(gptb_\w+)\s*\(([^;{]*?)\)\s*;", hdr, flags=re.S):
+        args = mt.group(2).strip()
+        protos[mt.group(1)] = 0 if args in ("", "void") else args.count(",") + 1
+    jl = open(os.path.join(root, "julia", "GPT_SGLD.jl")).read()
+    calls = re.findall(r"ccall\(\(:(gptb_\w+), LIB\),\s*\w+,\s*\(((?:[^()]|\([^()]*\)|\{[^{}]*\})*?)\)\s*,", jl, flags=re.S)
+    assert len(calls) > 40
+    seen = set()
+    for name, types in calls:
+        assert name in protos, f"{name} is not declared in include/gptb200.h"
+        depth, n = 0, 1 if types.strip() else 0
+        for ch in types:
+            depth += ch in "({"
+            depth -= ch in ")}"
+            n += ch == "," and depth == 0
+        if types.strip().endswith(","):       # one-element tuple: (T,)
+            n -= 1
+        assert n == protos[name], f"{name}: {n} ccall argument types, {protos[name]} C parameters"
+        seen.add(name)
+    # every entry a reference-style script needs is bound (introspection / bench-only / device-pointer entries are not)
+    must = {"gptb_create", "gptb_destroy", "gptb_set_features", "gptb_set_index", "gptb_set_train", "gptb_set_train_phi",
+            "gptb_set_params", "gptb_get_params", "gptb_init_params", "gptb_features", "gptb_pred", "gptb_pred_phi",
+            "gptb_pred_samples", "gptb_grad", "gptb_proj", "gptb_geod", "gptb_geodboth", "gptb_sgld_step", "gptb_sgld_run",
+            "gptb_sgld_advance", "gptb_gmc_run", "gptb_set_option", "gptb_set_domain", "gptb_comm_unique_id", "gptb_comm_init",
+            "gptb_synchronize", "gptb_nt_create", "gptb_nt_run", "gptb_nt_features"}
+    assert must <= seen, must - seen
