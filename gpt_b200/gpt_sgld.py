@@ -340,9 +340,10 @@ class Model:
         _check(st, self.h)
         return w_store, U_store
 
-    def sgld_advance(self, signal_var, m, epsw, epsU, nsteps, langevin=True, stiefel=True):
-        """Queue the next nsteps loop bodies (no store, no host sync); call synchronize() to wait."""
-        flags = (L.FLAG_LANGEVIN if langevin else 0) | (L.FLAG_STIEFEL if stiefel else 0)
+    def sgld_advance(self, signal_var, m, epsw, epsU, nsteps, langevin=True, stiefel=True, rmsprop=False):
+        """Queue the next nsteps loop bodies (no store, no host sync); call synchronize() to wait.  rmsprop=True: the
+        steps of GPT_SGLDERM_RMSprop (epsw is its epsilon)."""
+        flags = (L.FLAG_LANGEVIN if langevin else 0) | (L.FLAG_STIEFEL if stiefel else 0) | (L.FLAG_RMSPROP if rmsprop else 0)
         _check(self.lib.gptb_sgld_advance(self.h, float(signal_var), int(m), float(epsw), float(epsU), flags,
                                           int(nsteps)), self.h)
 
