@@ -1690,6 +1690,10 @@ int gptb_set_option(gptb_handle *h, int32_t option, double value) {
             h->node_P = (int)value;
             h->grid_valid = false;
             return GPTB_OK;
+        case GPTB_OPT_PRED_CHUNK_MB:
+            if (!(value >= 1.0 && value <= 4096.0)) break;
+            h->pred_chunk_mb = (int)value;
+            return GPTB_OK;
         case GPTB_OPT_RMS_ALPHA:
             if (!(value >= 0.0 && value < 1.0)) break;
             h->rms_alpha = value;

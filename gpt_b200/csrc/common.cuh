@@ -174,6 +174,7 @@ struct gptb_handle {
     double node_theta = 2.0;           // cell half-width times the largest |frequency| of the dimension
     bool grid_valid = false;
     gptb_nodes nodes;
+    int pred_chunk_mb = 256;           // size of the sweep's T2 chunk (GPTB_OPT_PRED_CHUNK_MB); measured: larger is faster up to ~160 MB
     gptb_pred_cache *pred_cache = nullptr;   // buffers of the node-grid posterior sweep (pred_nodes.cu), kept between calls
     bool have_domain = false;          // input domain known: from gptb_set_train (min / max of X) or gptb_set_domain
     double dom_lo[16] = {0}, dom_hi[16] = {0};

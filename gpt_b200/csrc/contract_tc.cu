@@ -562,6 +562,10 @@ __global__ void __launch_bounds__(256) contract_fwd2_kernel(const ContractFwd2Pa
     float *Tf = reinterpret_cast<float *>(Ts);                   // the same as [DR][64 rows]
     float *ws = reinterpret_cast<float *>(Ts + (size_t)DR * 32); // [Q rounded up to 4]
     float2 *Fs = reinterpret_cast<float2 *>(ws + ((Q + 3) & ~3)); // [NW][32]
+    // the (uniform) gather offsets, staged once per CTA: with ~200 KB of the SM's 228 KB in shared memory the L1 is too
+    // small to keep them beside the streaming tile loads (ncu: long_scoreboard led the stalls when they were __ldg'd)
+    int4 *off1s = reinterpret_cast<int4 *>(Fs + NW * 32);        // [Q][DP4]
+    for (int t = tid; t < Q * DP4; t += 256) off1s[t] = __ldg(reinterpret_cast<const int4 *>(p.off1) + t);
     for (int t = tid; t < Q; t += 256) ws[t] = (float)p.w[(size_t)s * Q + t];
     const int cbase = p.col0 + s * r;
     if (((r | p.ncols | cbase) & 3) == 0) {
@@ -590,11 +594,11 @@ __global__ void __launch_bounds__(256) contract_fwd2_kernel(const ContractFwd2Pa
     float2 f = make_float2(0.f, 0.f);
 #pragma unroll 2
     for (int q = wp; q < Q; q += NW) {
-        const int4 *o = reinterpret_cast<const int4 *>(p.off1) + (size_t)q * DP4;
+        const int4 *o = off1s + (size_t)q * DP4;
         float2 v = make_float2(1.f, 1.f);
 #pragma unroll
         for (int g4 = 0; g4 < DP4; ++g4) {
-            const int4 oo = __ldg(o + g4);
+            const int4 oo = o[g4];
             if (g4 * 4 + 0 < D) v = mul2(v, Trow[oo.x]);
             if (g4 * 4 + 1 < D) v = mul2(v, Trow[oo.y]);
             if (g4 * 4 + 2 < D) v = mul2(v, Trow[oo.z]);
@@ -628,7 +632,7 @@ int gptb_launch_contract_fwd2(gptb_handle *h, const float *T2, const double *w_g
                               cudaStream_t s) {
     const gptb_config &c = h->cfg;
     const size_t smem = (size_t)c.D * c.r * 32 * sizeof(float2) + (size_t)((c.Q + 3) & ~3) * sizeof(float) +
-                        8 * 32 * sizeof(float2) + 64;
+                        8 * 32 * sizeof(float2) + (size_t)c.Q * ((c.D + 3) / 4) * 16 + 64;
     if (smem > 227 * 1024 || !h->ct_off1) return GPTB_ERR_UNSUPPORTED;
     ContractFwd2Params p;
     p.T2 = T2; p.w = w_group; p.off1 = h->ct_off1; p.fh = fh; p.mean_acc = mean_acc; p.mean_scale = mean_scale;

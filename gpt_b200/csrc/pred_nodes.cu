@@ -9,7 +9,10 @@
 //   - the Q*D shared-memory gathers of the contraction (contract_fwd2_kernel) — the floor of the sweep: 4*Q*D bytes of
 //     shared-memory bandwidth per pair, 35 ms for 2e8 pairs on 148 SMs.
 // Loop order: sample groups outside (U_store goes up group by group, 5 MB at a time), row
-// chunks inside, sized so that the chunk's T2 block (rows x D x 160 floats) stays in L2 between the two kernels.
+// chunks inside.  The chunk's T2 block (rows x D x 160 floats) is GPTB_OPT_PRED_CHUNK_MB large, 256 MB by default: an
+// L2-sized chunk (40 MB) was measured SLOWER (198.9 ms at C5 against 168.6 ms at 160 MB and 163.8 ms at 640 MB) — the
+// contraction is bound by its shared-memory gathers, not by where T2 comes from, and 2000 short launch pairs each pay
+// a partial last wave.
 #include <math.h>
 
 #include <algorithm>
@@ -184,7 +187,7 @@ int gptb_pred_nodes(gptb_handle *h, const double *w_store, const double *U_store
     const int NC1 = std::max(h->rpad, (Sg1 * c.r + 15) / 16 * 16);
     const int CGs = std::max(1, std::min<int>(max_cols / c.r, S));        // samples per column group
     const int ctot_max = (CGs * c.r + 3) & ~3;
-    int64_t RC = (int64_t)(((size_t)40 << 20) / ((size_t)c.D * ctot_max * 4)) / PRED_CHUNK_ALIGN * PRED_CHUNK_ALIGN;
+    int64_t RC = (int64_t)(((size_t)h->pred_chunk_mb << 20) / ((size_t)c.D * ctot_max * 4)) / PRED_CHUNK_ALIGN * PRED_CHUNK_ALIGN;
     RC = std::max<int64_t>(PRED_CHUNK_ALIGN, std::min<int64_t>(RC, ntpad));
     GPTB_TRY(pc_grow(h, &pc.Tn, &pc.cap[PC::B_TN], (size_t)c.D * Sg1 * c.r * mnpad));
     GPTB_TRY(pc_grow(h, &pc.Cf, &pc.cap[PC::B_CF], (size_t)c.D * G * ctot_max * PP));

@@ -20,6 +20,7 @@ ALG = {"auto": L.ALG_AUTO, "direct": L.ALG_DIRECT, "nodes": L.ALG_NODES}[sys.arg
 with G.Model(C["D"], C["n"], C["r"], B.Q, precision=L.PREC_TC3, device=0) as m:
     m.set_features(pf); m.set_index(pm["I"])
     m.set_option(L.OPT_ALGORITHM, ALG)
+    if len(sys.argv) > 4: m.set_option(L.OPT_PRED_CHUNK_MB, float(sys.argv[4]))
     for it in range(3):
         t0 = time.perf_counter()
         mean = m.pred_samples(ws, Us, Xt)
