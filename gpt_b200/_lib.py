@@ -24,7 +24,7 @@ class Config(C.Structure):
 OK, ERR_ARG, ERR_SHAPE, ERR_STATE, ERR_CUDA, ERR_NCCL, ERR_NOMEM, GEODESIC_NAN, ERR_UNSUPPORTED = range(9)
 PREC_FP64, PREC_TC3, PREC_TC1 = 0, 1, 2
 FEAT_COS, FEAT_SINCOS = 0, 1
-FLAG_LANGEVIN, FLAG_STIEFEL, FLAG_FIX_U, FLAG_RMSPROP = 1, 2, 4, 8
+FLAG_LANGEVIN, FLAG_STIEFEL, FLAG_FIX_U, FLAG_RMSPROP, FLAG_CLS_SINGLE_UPDATE = 1, 2, 4, 8, 16
 ALG_AUTO, ALG_DIRECT, ALG_NODES = 0, 1, 2
 OPT_PIPE_GROUPS, OPT_PIPE_RESERVE, OPT_ALGORITHM, OPT_NODE_ORDER, OPT_NODE_THETA, OPT_RMS_ALPHA, OPT_RMS_LAMBDA, OPT_PRED_CHUNK_MB = range(8)
 PHASES = ("gather", "fwd", "contract", "bwd", "reduce", "update")
@@ -56,6 +56,8 @@ PROTOTYPES = {
     "gptb_geodboth": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, c_double_p, c_double_p, C.c_double, c_double_p, c_double_p]),
     "gptb_gmc_run": (C.c_int, [H, C.c_double, C.c_double, C.c_double, C.c_int32, C.c_int32, C.c_int32, C.c_int32, c_double_p,
                                c_double_p, c_double_p, c_double_p, c_double_p, c_double_p]),
+    "gptb_classify_run": (C.c_int, [C.POINTER(H), C.c_int32, c_int32_p, C.c_int64, C.c_double, C.c_double, C.c_int32, C.c_int32,
+                                    C.c_int32, c_int64_p, c_double_p, c_double_p, c_double_p, c_double_p]),
     "gptb_sgld_step": (C.c_int, [H, C.c_double, c_int64_p, C.c_int64, C.c_int64, C.c_double, C.c_double, C.c_int32,
                                  c_double_p, c_double_p]),
     "gptb_sgld_step_host": (C.c_int, [H, C.c_double, c_double_p, c_double_p, C.c_int64, C.c_int64, C.c_double,

@@ -246,7 +246,11 @@ static bool nodes_usable(gptb_handle *h, int64_t lbs, bool phi_mode) {
 // rows_dev: device row ids of the *global* batch or null (= order[start..] / identity when staged).
 int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int64_t bs, int64_t N_total,
                  bool staged_host_batch, const double *Xstage_rm, const double *ystage, PhaseTimer &pt,
-                 bool skip_bwd = false) {
+                 bool skip_bwd = false, int stage = 0) {
+    // stage 0: the whole gradient.  The classification driver (classify.cu) splits it around its softmax:
+    // stage 1 = gather, forward pass and fhat only (T, the batch inputs and the cell-sorted records stay in place),
+    // stage 2 = K2 with the residual of the targets now in yb, back-projection, reduction.
+    const bool do_front = stage != 2, do_back = stage != 1;
     const gptb_config &c = h->cfg;
     const bool phi_mode = h->have_phi && !staged_host_batch;
     const int64_t lo = (int64_t)h->rank * bs / h->nranks, hi = (int64_t)(h->rank + 1) * bs / h->nranks;
@@ -255,7 +259,7 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
     GPTB_TRY(refresh_shadows(h));
     const size_t gcount = (size_t)c.Q + (size_t)c.n * c.r * c.D;
     if (h->f32_grad) GPTB_TRY(gptb_tc_ensure_gradF(h));   // FP32 gradient flow: the buffer is cleared by its reader (k_prepare)
-    else GPTB_CUDA_OK(h, cudaMemsetAsync(h->grad, 0, gcount * sizeof(double), h->stream));
+    else if (do_back) GPTB_CUDA_OK(h, cudaMemsetAsync(h->grad, 0, gcount * sizeof(double), h->stream));
     const bool f64 = use_fp64(h, phi_mode);
     const bool nodes = lbs > 0 && nodes_usable(h, lbs, phi_mode);
     if (nodes) GPTB_TRY(gptb_nodes_ensure_batch(h));
@@ -265,7 +269,9 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
         ~CellGuard() { h->gather_cells = false; h->k2_Erow = nullptr; h->k2_T_rowmajor = false; }
     } cell_guard{h};
     h->gather_cells = nodes;
-    if (staged_host_batch) {
+    if (!do_front) {
+        // batch inputs, yb and the sorted records are those of stage 1
+    } else if (staged_host_batch) {
         const int64_t so = h->stage_share ? 0 : lo;   // (a share-only staging buffer starts at this rank's first row)
         GPTB_TRY(gptb_launch_gather_from(h, Xstage_rm + (size_t)so * c.D, ystage + so, lbs, h->mpad, f64 ? h->Xb : nullptr,
                                          f64 ? nullptr : h->XbF, h->yb));
@@ -277,32 +283,34 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
         GPTB_TRY(gptb_launch_gather(h, rows, 0, lbs, lo));
     }
     h->gather_cells = false;
-    if (nodes) GPTB_TRY(gptb_nodes_sort(h, lbs, h->stream));   // cell-sorted records: both row kernels walk them
+    if (nodes && do_front) GPTB_TRY(gptb_nodes_sort(h, lbs, h->stream));   // cell-sorted records: both row kernels walk them
     pt.done(GPTB_PHASE_GATHER);
     const double escale = ((double)N_total / (double)bs) / signal_var;  // (N/bs)/signal_var of :393,:407
     if (lbs > 0) {
         double *gU = h->grad + c.Q;
         if (nodes) {
-            GPTB_TRY(gptb_nodes_forward_range(h, h->Uimg, 0, c.D, h->stream));
-            GPTB_TRY(gptb_nodes_interp(h, lbs));
-            h->k2_Erow = skip_bwd ? nullptr : h->nodes.Erow;   // K2 writes plain E rows instead of the operand image
+            if (do_front) {
+                GPTB_TRY(gptb_nodes_forward_range(h, h->Uimg, 0, c.D, h->stream));
+                GPTB_TRY(gptb_nodes_interp(h, lbs));
+            }
+            h->k2_Erow = (skip_bwd || !do_back) ? nullptr : h->nodes.Erow;   // K2 writes plain E rows instead of the operand image
             h->k2_T_rowmajor = true;                           // ... and reads the interpolated T, row-major per sample
             {
                 void *T_keep = h->T;
                 h->T = h->nodes.T2;
-                const int st = forward_contract(h, false, rows, h->w, h->U, h->Uimg, lbs, escale, true, &pt, true);
+                const int st = forward_contract(h, false, rows, h->w, h->U, h->Uimg, lbs, escale, do_back, &pt, true);
                 h->T = T_keep;
                 h->k2_Erow = nullptr;
                 h->k2_T_rowmajor = false;
                 GPTB_TRY(st);
             }
-            if (!skip_bwd) {
+            if (!skip_bwd && do_back) {
                 GPTB_TRY(gptb_nodes_spread(h, lbs));
                 GPTB_TRY(gptb_nodes_backward_range(h, gU, 0, c.D));
             }
         } else {
-            GPTB_TRY(forward_contract(h, phi_mode, rows, h->w, h->U, h->Uimg, lbs, escale, true, &pt));
-            if (skip_bwd) {
+            GPTB_TRY(forward_contract(h, phi_mode, rows, h->w, h->U, h->Uimg, lbs, escale, do_back, &pt, !do_front));
+            if (skip_bwd || !do_back) {
                 // GPTB_FLAG_FIX_U: the w-only sampler needs fhat and gradw only
             } else if (f64) {
                 GPTB_TRY(gptb_launch_bwd_fp64(h, h->Xb, phi_mode ? h->phi : nullptr, rows, (const double *)h->E, lbs,
@@ -313,6 +321,7 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
         }
     }
     pt.done(GPTB_PHASE_BWD);
+    if (!do_back) return GPTB_OK;
     if (h->f32_grad)
         GPTB_TRY(gptb_allreduce_range_f32(h, h->gradFbase, (size_t)h->gradF_qpad + (size_t)c.D * h->npad * h->rpad, h->stream));
     else
@@ -568,6 +577,19 @@ int check_nan(gptb_handle *h) {
 }
 
 }  // namespace
+
+// ---- hooks for the classification driver (classify.cu): the split gradient pass, noise staging, flag read-back
+int gptb_i_grad_stage(gptb_handle *h, const int32_t *rows_dev, int64_t bs, int64_t N_total, int stage) {
+    GPTB_TRY(pipe_join(h));
+    PhaseTimer pt(h);
+    h->f32_grad = false;   // the gradient is read by two updates: FP64 buffer, not cleared by its reader
+    return compute_grad(h, 1.0, rows_dev, bs, N_total, false, nullptr, nullptr, pt, false, stage);
+}
+int gptb_i_stage_noise(gptb_handle *h, const double *noise_w, const double *noise_U, const double **nw_dev, const double **nU_dev) {
+    return stage_noise(h, noise_w, noise_U, nw_dev, nU_dev);
+}
+int gptb_i_check_nan(gptb_handle *h) { return check_nan(h); }
+int gptb_i_check_ready(gptb_handle *h) { return check_ready(h, true, true); }
 
 extern "C" {
 

@@ -292,6 +292,7 @@ int gptb_launch_contract_tc(gptb_handle *h, const float *T, const double *w, con
 // update.cu
 int gptb_launch_update(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
                        const double *noise_U, uint64_t step);
+constexpr int GPTB_IFLAG_PRIOR_IN_GRAD = 1 << 16;   // internal update flag: grad[0..Q) already holds gradw - w/sigma_w^2
 int gptb_launch_update_range(gptb_handle *h, double epsw, double epsU, int flags, const double *noise_w,
                              const double *noise_U, uint64_t step, int k0, int kn, bool with_w, cudaStream_t s,
                              bool noise_ready = false);

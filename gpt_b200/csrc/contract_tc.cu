@@ -39,6 +39,10 @@ constexpr int CNW = GPTB_CNW;    // warps per CTA.  The tiles (128+ KB at C4) al
                                  // brings the warps that hide the LDS -> FMUL2 / FADD2 chains; 20 divides the work of
                                  // the headline shape evenly (Q = 200 -> 10 q per warp, D*rpad/8 = 40 units -> 2 per warp)
 constexpr int CT_THREADS = 32 * CNW;
+#ifndef GPTB_K2_CHAINS
+#define GPTB_K2_CHAINS 2
+#endif
+constexpr int NCH = GPTB_K2_CHAINS;   // independent V products per warp and iteration of pass 1
 
 struct ContractTcParams {
     const float *T;          // [D][r][mpad]
@@ -108,16 +112,29 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
         // line hit L1 after the first
         float *Tf = reinterpret_cast<float *>(Ts);
         const int q4 = rpad >> 2, total = CRB * D * q4;
-        for (int t = tid; t < total; t += CT_THREADS) {
-            const int rowt = t & (CRB - 1), rest = t >> 6;
-            const int k = rest / q4, q = rest - k * q4;
-            const float4 v = __ldg(reinterpret_cast<const float4 *>(p.T + ((size_t)k * p.mpad + (size_t)blockIdx.x * CRB + rowt) * rpad) + q);
-            const int l0 = 4 * q;
-            float *d = Tf + (size_t)(k * r + l0) * CRB + rowt;
-            if (l0 < r) d[0] = v.x;
-            if (l0 + 1 < r) d[CRB] = v.y;
-            if (l0 + 2 < r) d[2 * CRB] = v.z;
-            if (l0 + 3 < r) d[3 * CRB] = v.w;
+        // (four loads in flight per thread before the first store: the loop is latency-, not bandwidth-bound)
+        constexpr int TB = 4;
+        for (int t0 = tid; t0 < total; t0 += TB * CT_THREADS) {
+            float4 v[TB];
+            float *d[TB];
+            int l0[TB];
+#pragma unroll
+            for (int j = 0; j < TB; ++j) {
+                const int t = t0 + j * CT_THREADS;
+                const int tt = t < total ? t : 0;                 // (past the end: a valid address, nothing stored)
+                const int rowt = tt & (CRB - 1), rest = tt >> 6;
+                const int k = rest / q4, q = rest - k * q4;
+                v[j] = __ldg(reinterpret_cast<const float4 *>(p.T + ((size_t)k * p.mpad + (size_t)blockIdx.x * CRB + rowt) * rpad) + q);
+                l0[j] = t < total ? 4 * q : r;                    // past the end: nothing is stored
+                d[j] = Tf + (size_t)(k * r + 4 * q) * CRB + rowt;
+            }
+#pragma unroll
+            for (int j = 0; j < TB; ++j) {
+                if (l0[j] < r) d[j][0] = v[j].x;
+                if (l0[j] + 1 < r) d[j][CRB] = v[j].y;
+                if (l0[j] + 2 < r) d[j][2 * CRB] = v[j].z;
+                if (l0[j] + 3 < r) d[j][3 * CRB] = v[j].w;
+            }
         }
     }
     for (int t = tid; t < Q * DP4; t += CT_THREADS) {
@@ -146,26 +163,45 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     // ---- pass 1: V and fhat
     const char *Tb = reinterpret_cast<const char *>(Ts + lane);
     float2 f = make_float2(0.f, 0.f);
-    for (int q0 = wp; q0 < Q; q0 += 2 * CNW) {       // two independent product chains per iteration
-        const int q1 = q0 + CNW;
-        const bool has1 = q1 < Q;
-        const int4 *o0 = off1s + (size_t)q0 * DP4, *o1 = off1s + (size_t)(has1 ? q1 : q0) * DP4;
-        float2 v0 = make_float2(1.f, 1.f), v1 = make_float2(1.f, 1.f);
+    for (int q0 = wp; q0 < Q; q0 += NCH * CNW) {     // NCH independent product chains per iteration
+        const int4 *o[NCH];
+        float2 v[NCH];
+#pragma unroll
+        for (int j = 0; j < NCH; ++j) {
+            const int qj = q0 + j * CNW;
+            o[j] = off1s + (size_t)(qj < Q ? qj : q0) * DP4;
+            v[j] = make_float2(1.f, 1.f);
+        }
 #pragma unroll
         for (int g4 = 0; g4 < DP4; ++g4) {
-            const int4 a = o0[g4], b = o1[g4];
-            if (g4 * 4 + 0 < D) { v0 = mul2(v0, lds2(Tb, a.x)); v1 = mul2(v1, lds2(Tb, b.x)); }
-            if (g4 * 4 + 1 < D) { v0 = mul2(v0, lds2(Tb, a.y)); v1 = mul2(v1, lds2(Tb, b.y)); }
-            if (g4 * 4 + 2 < D) { v0 = mul2(v0, lds2(Tb, a.z)); v1 = mul2(v1, lds2(Tb, b.z)); }
-            if (g4 * 4 + 3 < D) { v0 = mul2(v0, lds2(Tb, a.w)); v1 = mul2(v1, lds2(Tb, b.w)); }
+            int4 a[NCH];
+#pragma unroll
+            for (int j = 0; j < NCH; ++j) a[j] = o[j][g4];
+            if (g4 * 4 + 0 < D) {
+#pragma unroll
+                for (int j = 0; j < NCH; ++j) v[j] = mul2(v[j], lds2(Tb, a[j].x));
+            }
+            if (g4 * 4 + 1 < D) {
+#pragma unroll
+                for (int j = 0; j < NCH; ++j) v[j] = mul2(v[j], lds2(Tb, a[j].y));
+            }
+            if (g4 * 4 + 2 < D) {
+#pragma unroll
+                for (int j = 0; j < NCH; ++j) v[j] = mul2(v[j], lds2(Tb, a[j].z));
+            }
+            if (g4 * 4 + 3 < D) {
+#pragma unroll
+                for (int j = 0; j < NCH; ++j) v[j] = mul2(v[j], lds2(Tb, a[j].w));
+            }
         }
-        Vs[(size_t)q0 * 32 + lane] = v0;
-        const float w0 = ws[q0];
-        f = __ffma2_rn(make_float2(w0, w0), v0, f);
-        if (has1) {
-            Vs[(size_t)q1 * 32 + lane] = v1;
-            const float w1 = ws[q1];
-            f = __ffma2_rn(make_float2(w1, w1), v1, f);
+#pragma unroll
+        for (int j = 0; j < NCH; ++j) {
+            const int qj = q0 + j * CNW;
+            if (qj < Q) {
+                Vs[(size_t)qj * 32 + lane] = v[j];
+                const float wj = ws[qj];
+                f = __ffma2_rn(make_float2(wj, wj), v[j], f);
+            }
         }
     }
     Fs[wp * 32 + lane] = f;

@@ -50,6 +50,17 @@ __device__ __forceinline__ void cheb_basis(float u, float (&t)[P]) {
     for (int p = 2; p < P; ++p) t[p] = fmaf(u2, t[p - 1], -t[p - 2]);
 }
 
+// The same for two records at once: packed FP32 (FFMA2 takes the negated third operand and a scalar multiplier for free).
+template <int P>
+__device__ __forceinline__ void cheb_basis2(float2 u, float2 (&t)[P]) {
+    t[0] = make_float2(1.f, 1.f);
+    if (P > 1) t[1] = u;
+    const float2 u2 = make_float2(2.f * u.x, 2.f * u.y);
+#pragma unroll
+    for (int p = 2; p < P; ++p) t[p] = __ffma2_rn(u2, t[p - 1], make_float2(-t[p - 2].x, -t[p - 2].y));
+}
+__device__ __forceinline__ float2 splat(float c) { return make_float2(c, c); }
+
 // ------------------------------------------------------------------------------------------------ coefficients
 // grid (ceil(G*rpad/256), kn).  Tn[k][l][c*P + j] -> Cf[k][c][l][PP]  (PP = P rounded up to 4: a lane reads the
 // coefficients of its column with 16-byte loads; columns r..rpad-1 and entries P..PP-1 are zero).
@@ -204,19 +215,18 @@ __global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restric
             u_l = su[kb + s];
         }
         const int cnt = (int)min((int64_t)32, s1 - sb);
-        for (int j = 0; j < cnt; ++j) {
-            const int c = __shfl_sync(0xffffffffu, c_l, j);
-            const int row = __shfl_sync(0xffffffffu, row_l, j);
-            const float u = __shfl_sync(0xffffffffu, u_l, j);
-            if (c != cur) {   // warp-uniform
-                cur = c;
+        // two records per iteration: when both lie in the same cell (the records are cell-sorted, so nearly always)
+        // one packed recurrence and PP packed FMAs per column block serve both rows
+        auto load_cell = [&](int c) {
+            cur = c;
 #pragma unroll
-                for (int a = 0; a < NL; ++a) {
-                    const int col = col0 + min(a * 32 + lane, ncols - 1);
+            for (int a = 0; a < NL; ++a) {
+                const int col = col0 + min(a * 32 + lane, ncols - 1);
 #pragma unroll
-                    for (int q = 0; q < PP / 4; ++q) cf[a][q] = __ldg(Ck + ((size_t)c * ctot + col) * (PP / 4) + q);
-                }
+                for (int q = 0; q < PP / 4; ++q) cf[a][q] = __ldg(Ck + ((size_t)c * ctot + col) * (PP / 4) + q);
             }
+        };
+        auto single = [&](int row, float u) {
             float tb[PP];
             cheb_basis<PP>(u, tb);                                // (entries P..PP-1 meet zero coefficients)
 #pragma unroll
@@ -231,6 +241,37 @@ __global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restric
                 }
                 const int l = a * 32 + lane;
                 if (l < ncols) Tk[(size_t)row * ncols + l] = acc0 + acc1;
+            }
+        };
+        for (int j = 0; j < cnt; j += 2) {
+            const int jb = min(j + 1, cnt - 1);
+            const int c_a = __shfl_sync(0xffffffffu, c_l, j), c_b = __shfl_sync(0xffffffffu, c_l, jb);
+            const int row_a = __shfl_sync(0xffffffffu, row_l, j), row_b = __shfl_sync(0xffffffffu, row_l, jb);
+            const float u_a = __shfl_sync(0xffffffffu, u_l, j), u_b = __shfl_sync(0xffffffffu, u_l, jb);
+            if (c_a != cur) load_cell(c_a);   // warp-uniform
+            if (c_b != c_a) {
+                single(row_a, u_a);
+                load_cell(c_b);
+                single(row_b, u_b);
+                continue;
+            }
+            float2 tb[PP];
+            cheb_basis2<PP>(make_float2(u_a, u_b), tb);
+#pragma unroll
+            for (int a = 0; a < NL; ++a) {
+                float2 acc0 = make_float2(0.f, 0.f), acc1 = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int q = 0; q < PP / 4; ++q) {
+                    acc0 = __ffma2_rn(tb[4 * q], splat(cf[a][q].x), acc0);
+                    acc1 = __ffma2_rn(tb[4 * q + 1], splat(cf[a][q].y), acc1);
+                    acc0 = __ffma2_rn(tb[4 * q + 2], splat(cf[a][q].z), acc0);
+                    acc1 = __ffma2_rn(tb[4 * q + 3], splat(cf[a][q].w), acc1);
+                }
+                const int l = a * 32 + lane;
+                if (l < ncols) {
+                    Tk[(size_t)row_a * ncols + l] = acc0.x + acc1.x;
+                    if (jb != j) Tk[(size_t)row_b * ncols + l] = acc0.y + acc1.y;
+                }
             }
         }
     }
@@ -262,11 +303,11 @@ __global__ void __launch_bounds__(STHREADS) spread_kernel(const float *__restric
     float *Mk = Mn + (size_t)k * mnpad * rpad;
     constexpr int per_warp = SROWS / (STHREADS / 32);
     const int64_t s0 = (int64_t)blockIdx.x * SROWS + warp * per_warp, s1 = min(bs, s0 + per_warp);
-    float acc[NL][P];
+    float2 acc[NL][P];     // two partial sums per moment (records are taken in pairs), added at the flush
 #pragma unroll
     for (int a = 0; a < NL; ++a)
 #pragma unroll
-        for (int p = 0; p < P; ++p) acc[a][p] = 0.f;
+        for (int p = 0; p < P; ++p) acc[a][p] = make_float2(0.f, 0.f);
     int cur = -1;
     auto flush = [&]() {
         if (cur < 0) return;
@@ -276,8 +317,8 @@ __global__ void __launch_bounds__(STHREADS) spread_kernel(const float *__restric
             if (l < rpad) {
 #pragma unroll
                 for (int p = 0; p < P; ++p) {
-                    atomicAdd(Mk + ((size_t)cur * P + p) * rpad + l, acc[a][p]);
-                    acc[a][p] = 0.f;
+                    atomicAdd(Mk + ((size_t)cur * P + p) * rpad + l, acc[a][p].x + acc[a][p].y);
+                    acc[a][p] = make_float2(0.f, 0.f);
                 }
             }
         }
@@ -316,13 +357,7 @@ __global__ void __launch_bounds__(STHREADS) spread_kernel(const float *__restric
         __syncwarp();
         const float *src = stage + (size_t)buf * 32 * rpad;
         const int cnt = (int)min((int64_t)32, s1 - sb);
-        for (int j = 0; j < cnt; ++j) {
-            const int c = __shfl_sync(0xffffffffu, c_l, j);
-            const float u = __shfl_sync(0xffffffffu, u_l, j);
-            if (c != cur) {   // warp-uniform
-                flush();
-                cur = c;
-            }
+        auto single = [&](int j, float u) {
             float tb[P];
             cheb_basis<P>(u, tb);
 #pragma unroll
@@ -330,7 +365,36 @@ __global__ void __launch_bounds__(STHREADS) spread_kernel(const float *__restric
                 const int l = a * 32 + lane;
                 const float e = l < rpad ? src[j * rpad + l] : 0.f;
 #pragma unroll
-                for (int p = 0; p < P; ++p) acc[a][p] = fmaf(tb[p], e, acc[a][p]);
+                for (int p = 0; p < P; ++p) acc[a][p].x = fmaf(tb[p], e, acc[a][p].x);
+            }
+        };
+        for (int j = 0; j < cnt; j += 2) {   // two records per iteration (packed FP32) when they share a cell
+            const int jb = min(j + 1, cnt - 1);
+            const int c_a = __shfl_sync(0xffffffffu, c_l, j), c_b = __shfl_sync(0xffffffffu, c_l, jb);
+            const float u_a = __shfl_sync(0xffffffffu, u_l, j), u_b = __shfl_sync(0xffffffffu, u_l, jb);
+            if (c_a != cur) {   // warp-uniform
+                flush();
+                cur = c_a;
+            }
+            if (c_b != c_a) {
+                single(j, u_a);
+                flush();
+                cur = c_b;
+                single(jb, u_b);
+                continue;
+            }
+            float2 tb[P];
+            cheb_basis2<P>(make_float2(u_a, u_b), tb);
+#pragma unroll
+            for (int a = 0; a < NL; ++a) {
+                const int l = a * 32 + lane;
+                float2 e = make_float2(0.f, 0.f);
+                if (l < rpad) {
+                    e.x = src[j * rpad + l];
+                    if (jb != j) e.y = src[jb * rpad + l];
+                }
+#pragma unroll
+                for (int p = 0; p < P; ++p) acc[a][p] = __ffma2_rn(tb[p], e, acc[a][p]);
             }
         }
         __syncwarp();

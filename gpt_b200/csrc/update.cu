@@ -144,7 +144,9 @@ k_prepare(const double *__restrict__ grad /*[Q | D r n]*/, double *__restrict__ 
                     gradFbase[(size_t)s_ * qstride + q] = 0.f;
                 }
             }
-            double g = gl - w[q];  // prior term of :393 (sigma_w = 1, :354), added once after the all-reduce
+            // prior term of :393 (sigma_w = 1, :354), added once after the all-reduce — unless the caller has folded it
+            // into grad already (GPTclassification's second move uses the prior of the w before its first move, :524)
+            double g = (flags & GPTB_IFLAG_PRIOR_IN_GRAD) ? gl : gl - w[q];
             double z = 0.0;
             if (langevin) z = noise_w ? noise_w[q] : noise_at(key, GPTB_STREAM_NOISE_W, step, (uint64_t)q);
             w[q] += epsw * g / 2 + sq * z;

@@ -27,7 +27,7 @@ import numpy as np
 
 from . import _lib as L
 
-__all__ = ["feature", "feature2", "samplenz", "pred", "pred_samples", "GPTregression", "GPT_SGLDERMw", "GPT_SGLDERM_RMSprop", "GPT_GMC", "proj", "geod", "geodboth",
+__all__ = ["feature", "feature2", "samplenz", "pred", "pred_samples", "GPTregression", "GPT_SGLDERMw", "GPT_SGLDERM_RMSprop", "GPT_GMC", "GPTclassification", "logsumexp", "proj", "geod", "geodboth",
            "datawhitening", "RFFFeatures", "Model", "GptbError", "GeodesicNaN", "shard_range"]
 
 
@@ -550,6 +550,81 @@ def GPT_GMC(phi, y, signal_var, I, r, Q, epsw, epsU, burnin, maxepoch, L_, param
             return w_store, U_store, acc
         _check(st, mdl.h)
         return w_store, U_store, acc
+
+
+def logsumexp(x):
+    """GPT_SGLD.jl export (BloodTransfusionExperiment.jl:53-56): log(sum(exp(x))), the maximum taken out first."""
+    x = np.asarray(x, dtype=np.float64)
+    a = np.max(x)
+    return float(a + np.log(np.sum(np.exp(x - a))))
+
+
+def GPTclassification(phi, y, I, r, Q, m, epsw, epsU, burnin, maxepoch, param_seed, langevin=True, stiefel=True, *,
+                      precision: Optional[int] = None, w0=None, U0=None, perms=None, noise_w=None, noise_U=None,
+                      double_update=True, options=None):
+    """GPT_SGLD.jl:452-680: C = max(y)-min(y)+1 independent (w, U) sets under a softmax likelihood.  Returns
+    (w_store[Q,C,T], U_store[n,r,D,C,T]), T = maxepoch*ceil(N/m); all zeros (after the reference's warning) if a geodesic
+    produced NaN.  y: integer class labels (the reference's 1..C; any consecutive range works, min(y) is class 0).
+
+    Keyword-only extras (not in the reference): precision; w0[Q,C] / U0[n,r,D,C]; perms; noise_w[step][move] of shape
+    (Q,C) and noise_U[step][move] of shape (n,r,D,C) for the TWO moves the reference makes per minibatch (:624-636 and
+    :639-671); double_update=False keeps only the second; options = {L.OPT_*: value}."""
+    y = np.ravel(np.asarray(y))
+    labels = np.ascontiguousarray(np.rint(y - y.min()).astype(np.int32))
+    Ccls = int(labels.max()) + 1                                           # :460
+    N = labels.size
+    models = []
+    try:
+        for c in range(Ccls):
+            mdl = _model_for(phi, r, Q, I, precision, seed=int(param_seed) + 7919 * c, options=options)
+            models.append(mdl)
+            if isinstance(phi, RFFFeatures):
+                mdl.set_train(phi.X, np.zeros(N))
+            else:
+                mdl.set_train_phi(phi, np.zeros(N))
+            if w0 is not None:
+                mdl.set_params(np.asarray(w0)[:, c], np.asarray(U0)[:, :, :, c])
+            else:
+                mdl.init_params(int(param_seed) + 7919 * c, stiefel)
+        n, D = phi.shape[0], phi.shape[1]
+        numbatches = -(-N // int(m))
+        T = int(maxepoch) * numbatches
+        steps = (int(burnin) + int(maxepoch)) * numbatches
+        moves = 2 if double_update else 1
+        w_store = np.zeros((Q, Ccls, T), order="F")
+        U_store = np.zeros((n, r, D, Ccls, T), order="F")
+        pm = None if perms is None else np.ascontiguousarray(np.asarray(perms, dtype=np.int64).reshape(int(burnin) + int(maxepoch), N))
+
+        def pack(noise, shape):
+            if noise is None:
+                return None
+            out = np.empty((steps, moves, int(np.prod(shape))))
+            for s_ in range(steps):
+                for u in range(moves):
+                    a = np.asarray(noise[s_][u if double_update else -1], dtype=np.float64)
+                    if a.shape != shape:
+                        raise ValueError(f"noise entry of shape {a.shape}, expected {shape}")
+                    out[s_, u] = a.ravel(order="F")
+            return out
+
+        nw = pack(noise_w, (Q, Ccls))
+        nU = pack(noise_U, (n, r, D, Ccls))
+        flags = (L.FLAG_LANGEVIN if langevin else 0) | (L.FLAG_STIEFEL if stiefel else 0) | \
+            (0 if double_update else L.FLAG_CLS_SINGLE_UPDATE)
+        import ctypes as _C
+        harr = (_C.c_void_p * Ccls)(*[mdl.h for mdl in models])
+        lib = models[0].lib
+        st = lib.gptb_classify_run(_C.cast(harr, _C.POINTER(_C.c_void_p)), Ccls, labels.ctypes.data_as(L.c_int32_p), int(m),
+                                   float(epsw), float(epsU), int(burnin), int(maxepoch), int(flags),
+                                   None if pm is None else pm.ctypes.data_as(L.c_int64_p), _dp(nw), _dp(nU), _dp(w_store), _dp(U_store))
+        if st == L.GEODESIC_NAN:
+            print("Get NaN when moving along Geodesic. Try smaller epsU")
+            return w_store, U_store
+        _check(st, models[0].h)
+        return w_store, U_store
+    finally:
+        for mdl in models:
+            mdl.close()
 
 
 # ------------------------------------------------------------------------------------------------

@@ -59,12 +59,14 @@ enum gptb_flags {
     GPTB_FLAG_STIEFEL = 2,  /* keyword stiefel                                             */
     GPTB_FLAG_FIX_U = 4,    /* GPT_SGLDERMw (GPT_SGLD.jl:1065-1118): SGLD on w only, the factors U stay as they are
                                (no factor gradient, no U update; U_store may be NULL)      */
-    GPTB_FLAG_RMSPROP = 8   /* GPT_SGLDERM_RMSprop (GPT_SGLD.jl:1121-1237), with GPTB_FLAG_STIEFEL: `epsw` is the sampler's
+    GPTB_FLAG_RMSPROP = 8,  /* GPT_SGLDERM_RMSprop (GPT_SGLD.jl:1121-1237), with GPTB_FLAG_STIEFEL: `epsw` is the sampler's
                                single step size epsilon (`epsU` is ignored); every w[q] moves with epsilon/(sqrt(gw[q])+lambda),
                                every U^(k) with the mean of its elements' step sizes (:1212); gw, gU are moving averages
                                (coefficient alpha: GPTB_OPT_RMS_ALPHA, default 0.9; lambda: GPTB_OPT_RMS_LAMBDA, 1e-5 as :1146)
                                of the squared gradients scaled by 1/batch_size (:1172), zero at the start of every
                                gptb_sgld_run and after gptb_set_params; computeA sees the updated w (:1188 before :1194) */
+    GPTB_FLAG_CLS_SINGLE_UPDATE = 16 /* gptb_classify_run only: skip the first of GPTclassification's two moves per
+                               minibatch (GPT_SGLD.jl:624-636), i.e. update like the regression samplers do */
 };
 
 typedef struct gptb_config {
@@ -215,6 +217,25 @@ int gptb_sgld_run(gptb_handle *h, double signal_var, int64_t m, double epsw, dou
 int gptb_gmc_run(gptb_handle *h, double signal_var, double epsw, double epsU, int32_t burnin, int32_t maxepoch, int32_t L,
                  int32_t restore_U_on_reject, const double *noise_p, const double *noise_mom, const double *unif,
                  double *w_store, double *U_store, double *accept_prob);
+
+/* GPTclassification (GPT_SGLD.jl:452-680): C independent parameter sets (w_c, U_c) under a softmax likelihood.
+ * hc[0..C): one handle per class, all on one device and one rank, with the same shape, features, core index table and
+ * training inputs (gptb_set_train; the handles' y is not read) and their own parameters (gptb_init_params with
+ * different seeds, or gptb_set_params) — the chain starts from them and they end at its last state.
+ *   labels[N]: 0-based class of every training row (the reference's y - minimum(y), :460);
+ *   the class-c gradients are the regression gradients with the residual (N/bs)(1[y_i = c] - softmax_c(fhat[i,:]))
+ *   (:506-524, :546-564), signal_var plays no part;
+ *   every minibatch moves (w, U) TWICE with that one gradient, as the reference does: first with noise on the Stiefel
+ *   manifold whatever the flags (:624-636), then under GPTB_FLAG_LANGEVIN / GPTB_FLAG_STIEFEL (:639-671);
+ *   GPTB_FLAG_CLS_SINGLE_UPDATE keeps the second move only;
+ *   perms as in gptb_sgld_run (all classes walk the same order, :480-481);
+ *   noise_w[step][move][C][Q], noise_U[step][move][C][n,r,D] (move = 0, 1 — or one move with
+ *   GPTB_FLAG_CLS_SINGLE_UPDATE), steps counted over all epochs, or NULL (Philox, each handle's own seed);
+ *   w_store[Q,C,T], U_store[n,r,D,C,T] (Julia order), T = maxepoch*numbatches (:464-465, :673-676), either may be NULL.
+ * On GPTB_GEODESIC_NAN the stores are zero-filled (:631-633). */
+int gptb_classify_run(gptb_handle *const *hc, int32_t C, const int32_t *labels, int64_t m, double epsw, double epsU,
+                      int32_t burnin, int32_t maxepoch, int32_t flags, const int64_t *perms, const double *noise_w,
+                      const double *noise_U, double *w_store, double *U_store);
 
 /* The next nsteps loop bodies of the same sampler, continuing the epoch structure where the previous call
  * stopped (a fresh Philox permutation whenever an epoch starts), nothing stored — what burn-in epochs do.

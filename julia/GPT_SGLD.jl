@@ -19,7 +19,7 @@
 module GPT_SGLD
 
 export datawhitening, feature, feature2, samplenz, pred, GPTregression, proj, geod, RFFFeatures,
-       featureNotensor, GPNT_SGLD, NTFeatures, GPT_SGLDERMw, GPT_SGLDERM_RMSprop, GPT_GMC, geodboth,
+       featureNotensor, GPNT_SGLD, NTFeatures, GPT_SGLDERMw, GPT_SGLDERM_RMSprop, GPT_GMC, GPTclassification, logsumexp, geodboth,
        Model, pred_samples, posterior_mean, gradients, sgld_step!, sgld_advance!, synchronize, get_params, set_params!,
        set_option!, set_domain!, comm_unique_id, comm_init!
 
@@ -282,6 +282,7 @@ end
 # (kin40kExperiment.jl:74-87 trains, then predicts with many stored samples; one Model serves both and keeps the
 #  training set, the node grid and the sweep's buffers on the device between calls.)
 const FLAG_RMSPROP = Cint(8)
+const FLAG_CLS_SINGLE_UPDATE = Cint(16)
 const OPT_PIPE_GROUPS, OPT_PIPE_RESERVE, OPT_ALGORITHM, OPT_NODE_ORDER, OPT_NODE_THETA, OPT_RMS_ALPHA, OPT_RMS_LAMBDA =
     Cint(0), Cint(1), Cint(2), Cint(3), Cint(4), Cint(5), Cint(6)
 const ALG_AUTO, ALG_DIRECT, ALG_NODES = 0.0, 1.0, 2.0
@@ -450,6 +451,43 @@ function GPT_GMC(phi::Union{RFFFeatures,Array{Float64,3}}, y::Array, signal_var:
         return w_store, U_store, accept_prob
     finally
         destroy(h)
+    end
+end
+
+# GPT_SGLD.jl export / BloodTransfusionExperiment.jl:53-56
+function logsumexp(x::Array)
+    a = maximum(x)
+    a + log(sum(exp.(x .- a)))
+end
+
+# GPT_SGLD.jl:452-680  GPTclassification(phi,y,I,r,Q,m,epsw,epsU,burnin,maxepoch,param_seed;langevin=true,stiefel=true)
+# One library handle per class (own parameters, same features / index table / inputs); y holds the labels 1..C (:460).
+# double_update=true makes the reference's two moves per minibatch (:624-636 and :639-671).
+function GPTclassification(phi::Union{RFFFeatures,Array{Float64,3}}, y::Array, I::Array, r::Integer, Q::Integer, m::Integer,
+                           epsw::Real, epsU::Real, burnin::Integer, maxepoch::Integer, param_seed::Integer;
+                           langevin = true, stiefel = true, precision = PREC_TC3, double_update::Bool = true)
+    labels = Vector{Int32}(vec(round.(Int32, y .- minimum(y))))
+    C = Int(maximum(labels)) + 1
+    hs = Ptr{Cvoid}[]
+    n = D = N = 0
+    try
+        for c in 1:C
+            h, n, D, N = sampler_handle(phi, zeros(length(labels)), I, r, Q, param_seed + 7919 * (c - 1), precision)
+            push!(hs, h)
+            stiefel || check(ccall((:gptb_init_params, LIB), Cint, (Ptr{Cvoid}, UInt64, Int32), h, param_seed + 7919 * (c - 1), 0), h)
+        end
+        T = maxepoch * cld(N, m); w_store = zeros(Q, C, T); U_store = zeros(n, r, D, C, T)
+        flags = (langevin ? FLAG_LANGEVIN : Cint(0)) | (stiefel ? FLAG_STIEFEL : Cint(0)) |
+                (double_update ? Cint(0) : FLAG_CLS_SINGLE_UPDATE)
+        st = ccall((:gptb_classify_run, LIB), Cint,
+                   (Ptr{Ptr{Cvoid}}, Int32, Ptr{Int32}, Int64, Float64, Float64, Int32, Int32, Int32, Ptr{Int64}, Ptr{Float64},
+                    Ptr{Float64}, Ptr{Float64}, Ptr{Float64}),
+                   hs, C, labels, m, epsw, epsU, burnin, maxepoch, flags, C_NULL, C_NULL, C_NULL, w_store, U_store)
+        st == GPTB_GEODESIC_NAN && (println("Get NaN when moving along Geodesic. Try smaller epsU"); return w_store, U_store)   # :631-633
+        check(st, hs[1])
+        return w_store, U_store
+    finally
+        for h in hs; destroy(h); end
     end
 end
 

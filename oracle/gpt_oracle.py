@@ -582,3 +582,108 @@ def GPT_GMC(phi, y, signal_var, I, r, Q, epsw, epsU, burnin, maxepoch, L, w0, U0
             w_store[:, epoch - burnin - 1] = w
             U_store[:, :, :, epoch - burnin - 1] = U
     return w_store, U_store, accept
+
+
+# ------------------------------------------------------------------------------------------------
+# Classification: C independent (w, U) sets under a softmax likelihood.
+# Pinning: **parity unpinned** — the reference holds no caller, fixture or known-answer test for
+# GPTclassification; the restatement is checked against finite differences of its own log posterior (the check the
+# reference keeps commented out at GPT_SGLD.jl:566-622).
+# ------------------------------------------------------------------------------------------------
+def logsumexp(x):
+    """BloodTransfusionExperiment.jl:53-56 / GPT_SGLD.jl export: log(sum(exp(x))) with the maximum taken out."""
+    x = np.asarray(x, dtype=np.float64)
+    a = np.max(x)
+    return a + np.log(np.sum(np.exp(x - a)))
+
+
+def class_gradients(phi_batch, y_batch, w, U, I, N_total, sigma_w=1.0):
+    """GPT_SGLD.jl:487-563 for one minibatch.  w[Q,C], U[n,r,D,C], y_batch 0-based class labels.
+    Returns (gradw[Q,C], gradU[n,r,D,C], fhat[bs,C]).
+
+    With p[i,c] = exp(fhat[i,c] - logsumexp(fhat[i,:])) (:506-516) the class-c gradients are the regression ones
+    with the residual e[i,c] = (N/bs) (1[y_i = c] - p[i,c]):
+        gradw[:,c] = sum_i e[i,c] V[:,i,c] - w[:,c]/sigma_w^2          (:519-524)
+        gradU[:,:,k,c] = sum_i e[i,c] Psi[:,i,k,c]                      (:546-564)"""
+    n, D, bs = phi_batch.shape
+    Q, C = w.shape
+    r = U.shape[1]
+    temp = [phidotU(U[:, :, :, c], phi_batch) for c in range(C)]                          # :490-493
+    V = [computeV(temp[c], I) for c in range(C)]                                           # :496-499
+    fhat = np.stack([computefhat(V[c], w[:, c]) for c in range(C)], axis=1)                # :502-505
+    lse = np.array([logsumexp(fhat[i, :]) for i in range(bs)])                             # :508-511
+    p = np.exp(fhat - lse[:, None])
+    onehot = np.zeros((bs, C))
+    onehot[np.arange(bs), np.asarray(y_batch, dtype=np.int64)] = 1.0
+    e = (N_total / bs) * (onehot - p)
+    gradw = np.empty((Q, C))
+    gradU = np.empty((n, r, D, C))
+    for c in range(C):
+        gradw[:, c] = V[c] @ e[:, c] - w[:, c] / sigma_w ** 2
+        A = computeA(computeU_phi(V[c], temp[c], I), w[:, c], I, r)                        # :527-536
+        gradU[:, :, :, c] = np.einsum("jki,lki,i->jlk", phi_batch, A, e[:, c], optimize=True)
+    return gradw, gradU, fhat
+
+
+def class_loglik(phi, y, w, U, I):
+    """sum_i fhat[i,y_i] - logsumexp(fhat[i,:])  (the quantity the commented-out check differentiates, :611-616)."""
+    C = w.shape[1]
+    fhat = np.stack([pred(w[:, c], U[:, :, :, c], I, phi) for c in range(C)], axis=1)
+    return float(sum(fhat[i, int(y[i])] - logsumexp(fhat[i, :]) for i in range(fhat.shape[0])))
+
+
+def GPTclassification(phi, y, I, r, Q, m, epsw, epsU, burnin, maxepoch, w0, U0, perms, noise_w, noise_U,
+                      langevin=True, stiefel=True, double_update=True):
+    """GPT_SGLD.jl:452-680 with the random draws made explicit.  y: 0-based labels in 0..C-1 (the reference's 1..C).
+
+    w0[Q,C], U0[n,r,D,C] replace :463-476; perms[epoch] replaces randperm (:480), applied cumulatively (:481);
+    noise_w[step][2][Q,C], noise_U[step][2][n,r,D,C]: the draws of the reference's TWO updates per minibatch — it moves
+    w and U once unconditionally with noise on the Stiefel manifold (:624-636) and then again under the langevin /
+    stiefel switches (:639-671), both times with the gradient evaluated before the first move.
+    double_update=False skips the first (what the regression samplers do).  Stores: w_store[Q,C,T], U_store[n,r,D,C,T]."""
+    phi = np.array(phi, dtype=np.float64, order="F")
+    y = np.array(y, dtype=np.int64)
+    n, D, N = phi.shape
+    C = w0.shape[1]
+    numbatches = int(np.ceil(N / m))
+    T = maxepoch * numbatches
+    w_store = np.zeros((Q, C, T))
+    U_store = np.zeros((n, r, D, C, T))
+    w = np.array(w0, dtype=np.float64)
+    U = np.array(U0, dtype=np.float64)
+    step = 0
+
+    def move(w, U, gradw, gradU, nw, nU, lang, stief):
+        w2 = np.empty_like(w)
+        U2 = np.empty_like(U)
+        for c in range(C):
+            wc, Uc, bad = sgld_update(w[:, c], U[:, :, :, c], gradw[:, c], gradU[:, :, :, c], epsw, epsU,
+                                      None if nw is None else nw[:, c], None if nU is None else nU[:, :, :, c], lang, stief)
+            if bad:
+                return None, None, True
+            w2[:, c] = wc
+            U2[:, :, :, c] = Uc
+        return w2, U2, False
+
+    for epoch in range(1, burnin + maxepoch + 1):
+        perm = perms[epoch - 1]
+        phi = phi[:, :, perm]
+        y = y[perm]
+        for batch in range(1, numbatches + 1):
+            lo, hi = m * (batch - 1), min(m * batch, N)
+            gradw, gradU, _ = class_gradients(phi[:, :, lo:hi], y[lo:hi], w, U, I, N)
+            # (:524: gradw -= w/sigma_w^2 uses the w before either move; class_gradients holds it)
+            if double_update:
+                w, U, bad = move(w, U, gradw, gradU, noise_w[step][0], noise_U[step][0], True, True)     # :624-636
+                if bad:
+                    return np.zeros((Q, C, T)), np.zeros((n, r, D, C, T))
+            w, U, bad = move(w, U, gradw, gradU, None if noise_w is None else noise_w[step][1],
+                             None if noise_U is None else noise_U[step][1], langevin, stiefel)           # :639-671
+            if bad:
+                return np.zeros((Q, C, T)), np.zeros((n, r, D, C, T))
+            if epoch > burnin:
+                col = (epoch - burnin - 1) * numbatches + batch - 1
+                w_store[:, :, col] = w
+                U_store[:, :, :, :, col] = U
+            step += 1
+    return w_store, U_store

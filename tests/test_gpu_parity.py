@@ -742,3 +742,55 @@ def test_GPT_GMC_vs_oracle(prec):
         assert np.array_equal(gU[..., 1], gU[..., 0]) == restore
     z = G.GPT_GMC(_feat(P), P["y"], P["signal_var"], P["I"], P["r"], P["Q"], 1e-5, 1e300, 0, 2, 1, 3, precision=L.PREC_FP64)
     assert not z[0].any() and not z[1].any() and np.isnan(z[2]).all()      # :746-748
+
+
+# ------------------------------------------------------------------------------------------------ classification (§8 f3)
+def _class_problem(C=3, seed=12):
+    P = make_problem(3, 150, 16, 4, Q=20, seed=seed)
+    rng = np.random.default_rng(seed + 100)
+    P["labels"] = rng.integers(0, C, P["N"])
+    P["labels"][:C] = np.arange(C)                        # every class present
+    P["W0"] = rng.standard_normal((P["Q"], C))
+    P["UU0"] = np.stack([np.stack([np.linalg.qr(rng.standard_normal((P["n"], P["r"])))[0] for _ in range(P["D"])], axis=2)
+                         for _ in range(C)], axis=3)
+    return P, C
+
+
+@pytest.mark.parametrize("prec,alg", [(L.PREC_FP64, L.ALG_DIRECT), (L.PREC_TC3, L.ALG_DIRECT), (L.PREC_TC3, L.ALG_NODES)],
+                         ids=["fp64", "tc3-direct", "tc3-nodes"])
+@pytest.mark.parametrize("langevin,stiefel,double", [(True, True, True), (False, True, True), (True, False, True), (True, True, False)],
+                         ids=["ref", "nolangevin", "euclid", "single"])
+def test_GPTclassification_vs_oracle(prec, alg, langevin, stiefel, double):
+    """GPT_SGLD.jl:452-680 with injected permutations and draws: softmax residual, the reference's two moves per minibatch
+    (the second under the langevin / stiefel switches), short last batch, burn-in, store layout [Q,C,T] / [n,r,D,C,T]."""
+    P, C = _class_problem()
+    N, m, burnin, maxepoch = P["N"], 64, 1, 2
+    rng = np.random.default_rng(4)
+    perms = [rng.permutation(N) for _ in range(burnin + maxepoch)]
+    steps = (burnin + maxepoch) * 3
+    NW = rng.standard_normal((steps, 2, P["Q"], C)); NU = rng.standard_normal((steps, 2, P["n"], P["r"], P["D"], C))
+    ws, Us = o.GPTclassification(P["phi_fn"](P["X"]), P["labels"], P["I"], P["r"], P["Q"], m, 1e-4, 1e-6, burnin, maxepoch,
+                                 P["W0"], P["UU0"], perms, NW, NU, langevin, stiefel, double)
+    gw, gU = G.GPTclassification(_feat(P), P["labels"] + 1, P["I"], P["r"], P["Q"], m, 1e-4, 1e-6, burnin, maxepoch, 5,
+                                 langevin, stiefel, precision=prec, w0=P["W0"], U0=P["UU0"], perms=np.stack(perms),
+                                 noise_w=NW, noise_U=NU, double_update=double, options={L.OPT_ALGORITHM: alg})
+    assert gw.shape == ws.shape == (P["Q"], C, 6) and gU.shape == Us.shape
+    tol = 1e-9 if prec == L.PREC_FP64 else 1e-4
+    assert relerr(gw, ws) < tol and relerr(gU, Us) < tol
+    # the update relative to the start, too (w0 dominates w after six small steps)
+    d_ref = ws[:, :, -1] - P["W0"]
+    assert relerr(gw[:, :, -1] - P["W0"], d_ref) < (1e-7 if prec == L.PREC_FP64 else 2e-3)
+
+
+def test_GPTclassification_philox_and_nan():
+    """Production draws (Philox, one seed per class): finite chain, factors on the manifold, classes differ; a huge epsU
+    trips the geodesic's NaN abort and zero-fills the stores (:631-633)."""
+    P, C = _class_problem(C=2, seed=21)
+    gw, gU = G.GPTclassification(_feat(P), P["labels"], P["I"], P["r"], P["Q"], 50, 1e-4, 1e-6, 0, 2, 9, precision=L.PREC_TC3)
+    assert gw.shape == (P["Q"], C, 6) and np.isfinite(gw).all() and np.isfinite(gU).all()
+    for c in range(C):
+        Uc = gU[:, :, 1, c, -1]
+        assert np.abs(Uc.T @ Uc - np.eye(P["r"])).max() < 1e-9
+    assert np.abs(gw[:, 0, -1] - gw[:, 1, -1]).max() > 1e-3
+    zw, zU = G.GPTclassification(_feat(P), P["labels"], P["I"], P["r"], P["Q"], 50, 1e-4, 1e300, 0, 1, 9, precision=L.PREC_FP64)
+    assert not zw.any() and not zU.any()

@@ -242,3 +242,30 @@ def test_geod_pinned_by_closed_form_and_arbitrary_precision():
         assert relerr(co.expm(blk), g[f"expm{c}"]) < 1e-13, c
         assert relerr(o.geod(U, M, t)[0], g[f"geod{c}"]) < 1e-14, c
         assert relerr(co.geod(U, M, t)[0], g[f"geod{c}"]) < 1e-13, c
+
+
+def test_class_gradients_finite_differences():
+    """GPTclassification's gradients (GPT_SGLD.jl:487-563) against finite differences of the softmax log likelihood —
+    the check the reference keeps commented out at :566-622 — and the softmax residual's sum-to-zero over classes."""
+    rng = np.random.default_rng(0)
+    n, D, N, r, Q, C = 6, 3, 20, 2, 5, 3
+    phi = rng.standard_normal((n, D, N)); y = rng.integers(0, C, N)
+    I = rng.integers(0, r, (Q, D))
+    w = rng.standard_normal((Q, C))
+    U = np.stack([np.stack([np.linalg.qr(rng.standard_normal((n, r)))[0] for _ in range(D)], axis=2) for _ in range(C)], axis=3)
+    gw, gU, fhat = o.class_gradients(phi, y, w, U, I, N)
+    l0 = o.class_loglik(phi, y, w, U, I)
+    h = 1e-6
+    for (q, c) in [(2, 1), (0, 0), (4, 2)]:
+        wp = w.copy(); wp[q, c] += h
+        assert abs((o.class_loglik(phi, y, wp, U, I) - l0) / h - (gw[q, c] + w[q, c])) < 1e-4
+    for (j, l, k, c) in [(3, 1, 2, 0), (0, 0, 0, 2), (5, 1, 1, 1)]:
+        Up = U.copy(); Up[j, l, k, c] += h
+        assert abs((o.class_loglik(phi, y, w, Up, I) - l0) / h - gU[j, l, k, c]) < 1e-4
+    assert abs(o.logsumexp(np.array([1000.0, 1000.0])) - (1000.0 + np.log(2.0))) < 1e-12
+    # double update with zero noise and zero step sizes is the identity; stores have the reference's shapes
+    perms = [np.arange(N)]
+    NW = np.zeros((2, 2, Q, C)); NU = np.zeros((2, 2, n, r, D, C))
+    ws, Us = o.GPTclassification(phi, y, I, r, Q, 10, 0.0, 0.0, 0, 1, w, U, perms, NW, NU)
+    assert ws.shape == (Q, C, 2) and Us.shape == (n, r, D, C, 2)
+    assert np.allclose(ws[:, :, -1], w) and np.allclose(Us[..., -1], U, atol=1e-12)
