@@ -242,6 +242,32 @@ static bool nodes_usable(gptb_handle *h, int64_t lbs, bool phi_mode) {
     return lbs >= std::max<int64_t>(8192, 4 * (int64_t)h->nodes.m);
 }
 
+// Front of a node-grid step on the side stream (see common.cuh: front_stream).  dep: an event the rows wait for (the
+// staged host minibatch), or null — then h->front_dep_mode says whether the front follows everything queued on the main
+// stream so far (0) or nothing but the previous readers of the batch buffers (1: resident rows inside an epoch).
+static int front_begin(gptb_handle *h, int64_t lbs, bool phi_mode, cudaEvent_t dep, bool *on_side) {
+    *on_side = h->front_active;
+    if (h->front_active) return GPTB_OK;
+    if (h->profiling || !h->front_enabled || lbs <= 0 || !nodes_usable(h, lbs, phi_mode)) return GPTB_OK;
+    if (!h->front_stream) {
+        GPTB_CUDA_OK(h, cudaStreamCreateWithFlags(&h->front_stream, cudaStreamNonBlocking));
+        GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&h->ev_front_dep, cudaEventDisableTiming));
+        GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&h->ev_front_done, cudaEventDisableTiming));
+        GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&h->ev_rows_free, cudaEventDisableTiming));
+    }
+    if (dep) GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->front_stream, dep, 0));
+    if ((!dep && h->front_dep_mode == 0) || !h->rows_free_valid) {
+        // (also the first front ever: the earlier steps' readers of the batch buffers have recorded nothing yet)
+        GPTB_CUDA_OK(h, cudaEventRecord(h->ev_front_dep, h->stream));
+        GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->front_stream, h->ev_front_dep, 0));
+    } else {
+        GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->front_stream, h->ev_rows_free, 0));
+    }
+    h->front_active = true;
+    *on_side = true;
+    return GPTB_OK;
+}
+
 // Gradient of the rank's share of the minibatch into h->grad (likelihood part only, all-reduced).
 // rows_dev: device row ids of the *global* batch or null (= order[start..] / identity when staged).
 int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int64_t bs, int64_t N_total,
@@ -269,6 +295,15 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
         ~CellGuard() { h->gather_cells = false; h->k2_Erow = nullptr; h->k2_T_rowmajor = false; }
     } cell_guard{h};
     h->gather_cells = nodes;
+    bool side_front = false;
+    if (do_front && stage == 0) GPTB_TRY(front_begin(h, lbs, phi_mode, nullptr, &side_front));
+    struct StreamSwap {   // the front's launchers use h->stream
+        gptb_handle *h;
+        cudaStream_t main;
+        bool on;
+        ~StreamSwap() { if (on) { h->stream = main; h->front_active = false; } }
+    } swap{h, h->stream, side_front};
+    if (side_front) h->stream = h->front_stream;
     if (!do_front) {
         // batch inputs, yb and the sorted records are those of stage 1
     } else if (staged_host_batch) {
@@ -284,6 +319,13 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
     }
     h->gather_cells = false;
     if (nodes && do_front) GPTB_TRY(gptb_nodes_sort(h, lbs, h->stream));   // cell-sorted records: both row kernels walk them
+    if (side_front) {
+        h->stream = swap.main;
+        swap.on = false;
+        h->front_active = false;
+        GPTB_CUDA_OK(h, cudaEventRecord(h->ev_front_done, h->front_stream));
+        GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->ev_front_done, 0));
+    }
     pt.done(GPTB_PHASE_GATHER);
     const double escale = ((double)N_total / (double)bs) / signal_var;  // (N/bs)/signal_var of :393,:407
     if (lbs > 0) {
@@ -319,6 +361,10 @@ int compute_grad(gptb_handle *h, double signal_var, const int32_t *rows_dev, int
                 GPTB_TRY(gptb_launch_bwd_tc(h, h->XbF, h->Eimg, lbs, h->mpad, gU));
             }
         }
+    }
+    if (h->front_stream) {   // the batch buffers (yb, XbF, cell records) have had their last reader
+        GPTB_CUDA_OK(h, cudaEventRecord(h->ev_rows_free, h->stream));
+        h->rows_free_valid = true;
     }
     pt.done(GPTB_PHASE_BWD);
     if (!do_back) return GPTB_OK;
@@ -724,6 +770,10 @@ int gptb_destroy(gptb_handle *h) {
     }
     if (h->pipe_nan_host) cudaFreeHost(h->pipe_nan_host);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    if (h->front_stream) {
+        cudaStreamSynchronize(h->front_stream); cudaStreamDestroy(h->front_stream);
+        cudaEventDestroy(h->ev_front_dep); cudaEventDestroy(h->ev_front_done); cudaEventDestroy(h->ev_rows_free);
+    }
     dev_free(&h->Xb); dev_free(&h->yb); dev_free(&h->fhat); dev_free(&h->XbF);
     if (h->T) cudaFree(h->T);
     if (h->E) cudaFree(h->E);
@@ -1548,13 +1598,26 @@ int gptb_sgld_step_host_submit(gptb_handle *h, double signal_var, const double *
         GPTB_CUDA_OK(h, cudaMemcpyAsync(h->pipe_y[slot], yb + slo, sizeof(double) * sbs, cudaMemcpyHostToDevice, h->copy_stream));
     }
     GPTB_CUDA_OK(h, cudaEventRecord(h->pipe_staged[slot], h->copy_stream));
-    GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->pipe_staged[slot], 0));
-    GPTB_TRY(gptb_launch_transpose(h, h->pipe_cm[slot], sbs, h->stage_rm));
+    {   // node-grid step: the batch's transpose, gather and cell sort follow the copy on the front stream, under the
+        // previous step's tail; otherwise the main stream waits for the copy
+        bool side = false;
+        GPTB_TRY(front_begin(h, sbs, false, h->pipe_staged[slot], &side));
+        if (!side) GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->pipe_staged[slot], 0));
+        cudaStream_t keep = h->stream;
+        if (side) h->stream = h->front_stream;
+        const int st_tr = gptb_launch_transpose(h, h->pipe_cm[slot], sbs, h->stage_rm);
+        h->stream = keep;
+        if (st_tr != GPTB_OK) {
+            h->front_active = false;
+            return st_tr;
+        }
+    }
     const double *nw = nullptr, *nU = nullptr;
     GPTB_TRY(stage_noise(h, noise_w, noise_U, &nw, &nU));
     h->stage_share = true;
     const int st_step = step_common(h, signal_var, nullptr, bs, N_total, true, h->stage_rm, h->pipe_y[slot], epsw, epsU, flags, nw, nU);
     h->stage_share = false;
+    h->front_active = false;
     GPTB_TRY(st_step);
     // the step's read-backs follow its last group update on the tail stream; the main stream is free for the next step
     cudaStream_t ts = nullptr;
@@ -1630,7 +1693,9 @@ int gptb_sgld_run(gptb_handle *h, double signal_var, int64_t m, double epsw, dou
             st = stage_noise(h, noise_w ? noise_w + (size_t)step * c.Q : nullptr,
                              noise_U ? noise_U + (size_t)step * ucnt : nullptr, &nw, &nU);
             if (st != GPTB_OK) break;
+            h->front_dep_mode = batch > 1 ? 1 : 0;   // the epoch's row order is fixed once its permutation has run
             st = step_common(h, signal_var, h->order + lo, hi - lo, N, false, nullptr, nullptr, epsw, epsU, flags, nw, nU);
+            h->front_dep_mode = 0;
             if (st != GPTB_OK) break;
             if (epoch > burnin && keep) {
                 const int64_t col = (int64_t)(epoch - burnin - 1) * numbatches + batch - 1;  // :442-443
@@ -1683,8 +1748,11 @@ int gptb_sgld_advance(gptb_handle *h, double signal_var, int64_t m, double epsw,
             h->epoch_counter++;
         }
         const int64_t lo = m * h->batch_cursor, hi = std::min(m * (h->batch_cursor + 1), N);
-        GPTB_TRY(step_common(h, signal_var, h->order + lo, hi - lo, N, false, nullptr, nullptr, epsw, epsU, flags,
-                             nullptr, nullptr));
+        h->front_dep_mode = h->batch_cursor > 0 ? 1 : 0;
+        const int st_step = step_common(h, signal_var, h->order + lo, hi - lo, N, false, nullptr, nullptr, epsw, epsU, flags,
+                                        nullptr, nullptr);
+        h->front_dep_mode = 0;
+        GPTB_TRY(st_step);
         h->batch_cursor = (h->batch_cursor + 1) % numbatches;
     }
     GPTB_TRY(pipe_join(h));   // work queued on the caller's stream after this call sees the final parameters
@@ -1702,6 +1770,9 @@ int gptb_set_option(gptb_handle *h, int32_t option, double value) {
             return GPTB_OK;
         case GPTB_OPT_PIPE_RESERVE:
             h->pipe_reserve = (int)value;
+            return GPTB_OK;
+        case GPTB_OPT_FRONT_PREFETCH:
+            h->front_enabled = value != 0.0;
             return GPTB_OK;
         case GPTB_OPT_ALGORITHM:
             if (value != GPTB_ALG_AUTO && value != GPTB_ALG_DIRECT && value != GPTB_ALG_NODES) break;

@@ -137,6 +137,14 @@ struct gptb_handle {
                                        // [3] uscale (2^k applied to U in Uimg), [4] 1/uscale
     bool tc_emax_valid = false;
     bool gather_cells = false;         // set around a node-grid step: the gather also writes nodes.cell / nodes.uu
+    // front of the node-grid step (transpose of a staged host batch, gather, cell sort) on its own stream: it depends on
+    // the minibatch rows only, so it runs under the previous step's back-projection tail, all-reduce and update
+    cudaStream_t front_stream = nullptr;
+    cudaEvent_t ev_front_dep = nullptr, ev_front_done = nullptr, ev_rows_free = nullptr;
+    bool front_enabled = true;         // GPTB_OPT_FRONT_PREFETCH
+    bool front_active = false;         // between front_begin and the end of the step's front
+    bool rows_free_valid = false;      // ev_rows_free has been recorded (after the last reader of the batch buffers)
+    int front_dep_mode = 0;            // 0: the front follows everything queued so far; 1: the rows need nothing new
     int k2_redo = 0;                   // set around a second K2 launch that only rewrites E: 1 = if the scale guard asks
                                        // for it (api.cu), 2 = unconditionally (RMSprop sampler: E with the updated w)
     const double *k2_wA = nullptr;     // weights of computeA when they differ from w

@@ -315,7 +315,9 @@ enum gptb_option {
     GPTB_OPT_NODE_THETA = 4,    /* cell half-width x max |Zt| of the dimension (default 2)                                */
     GPTB_OPT_RMS_ALPHA = 5,     /* moving-average coefficient of GPTB_FLAG_RMSPROP (`alpha` of GPT_SGLD.jl:1121), default 0.9 */
     GPTB_OPT_RMS_LAMBDA = 6,    /* its smoothing constant (`lambda` of :1146), default 1e-5                                */
-    GPTB_OPT_PRED_CHUNK_MB = 7  /* MB of interpolated values the posterior sweep produces per row chunk (default 256)      */
+    GPTB_OPT_PRED_CHUNK_MB = 7, /* MB of interpolated values the posterior sweep produces per row chunk (default 256)      */
+    GPTB_OPT_FRONT_PREFETCH = 8 /* 1 (default): gather and cell sort of a node-grid step run on a side stream under the
+                                   previous step's tail; 0: everything on the handle's stream                              */
 };
 int gptb_set_option(gptb_handle *h, int32_t option, double value);
 int gptb_get_phase_ms(gptb_handle *h, float *ms_out /*GPTB_PHASE_COUNT*/, int64_t *launches_out, int32_t reset);

@@ -283,8 +283,8 @@ end
 #  training set, the node grid and the sweep's buffers on the device between calls.)
 const FLAG_RMSPROP = Cint(8)
 const FLAG_CLS_SINGLE_UPDATE = Cint(16)
-const OPT_PIPE_GROUPS, OPT_PIPE_RESERVE, OPT_ALGORITHM, OPT_NODE_ORDER, OPT_NODE_THETA, OPT_RMS_ALPHA, OPT_RMS_LAMBDA =
-    Cint(0), Cint(1), Cint(2), Cint(3), Cint(4), Cint(5), Cint(6)
+const OPT_PIPE_GROUPS, OPT_PIPE_RESERVE, OPT_ALGORITHM, OPT_NODE_ORDER, OPT_NODE_THETA, OPT_RMS_ALPHA, OPT_RMS_LAMBDA,
+      OPT_PRED_CHUNK_MB, OPT_FRONT_PREFETCH = Cint(0), Cint(1), Cint(2), Cint(3), Cint(4), Cint(5), Cint(6), Cint(7), Cint(8)
 const ALG_AUTO, ALG_DIRECT, ALG_NODES = 0.0, 1.0, 2.0
 
 mutable struct Model

@@ -794,3 +794,34 @@ def test_GPTclassification_philox_and_nan():
     assert np.abs(gw[:, 0, -1] - gw[:, 1, -1]).max() > 1e-3
     zw, zU = G.GPTclassification(_feat(P), P["labels"], P["I"], P["r"], P["Q"], 50, 1e-4, 1e300, 0, 1, 9, precision=L.PREC_FP64)
     assert not zw.any() and not zU.any()
+
+
+def test_nodes_front_prefetch_same_chain():
+    """The node-grid step's gather and cell sort run on a side stream under the previous step's tail
+    (GPTB_OPT_FRONT_PREFETCH): resident epochs (gptb_sgld_run, gptb_sgld_advance) and pipelined host minibatches
+    (gptb_sgld_step_host_submit) give the chain of the one-stream step (FP32 atomics reorder sums: 1e-6, not bits)."""
+    P = make_problem(4, 6000, 48, 8, Q=40, seed=17)
+    m = 1500
+    out = {}
+    for pre in (1, 0):
+        with _model(P, L.PREC_TC3) as mdl:
+            mdl.set_option(L.OPT_ALGORITHM, L.ALG_NODES)
+            mdl.set_option(L.OPT_FRONT_PREFETCH, pre)
+            mdl.set_params(P["w0"], P["U0"])
+            ws, Us = mdl.sgld_run(P["signal_var"], m, 1e-6, 1e-9, 0, 2, True, True, None, None, None, store=True, N=P["N"])
+            mdl.sgld_advance(P["signal_var"], m, 1e-6, 1e-9, 7)
+            mdl.synchronize()
+            wa, Ua = mdl.get_params()
+            rng = np.random.default_rng(5)
+            keep = []
+            for s_ in range(5):
+                idx = rng.permutation(P["N"])[:m]
+                keep.append((np.asfortranarray(P["X"][idx]), np.ascontiguousarray(P["y"][idx])))
+                mdl.sgld_step_host_submit(P["signal_var"], keep[-1][0], keep[-1][1], P["N"], 1e-6, 1e-9)
+                if s_ >= 1:
+                    mdl.sgld_step_host_wait()
+            mdl.sgld_step_host_wait()
+            wb, Ub = mdl.get_params()
+            out[pre] = (ws, Us, wa, Ua, wb, Ub)
+    for a, b in zip(out[1], out[0]):
+        assert np.isfinite(a).all() and relerr(a, b) < 1e-6
