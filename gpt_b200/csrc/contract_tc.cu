@@ -39,6 +39,9 @@ constexpr int CNW = GPTB_CNW;    // warps per CTA.  The tiles (128+ KB at C4) al
                                  // brings the warps that hide the LDS -> FMUL2 / FADD2 chains; 20 divides the work of
                                  // the headline shape evenly (Q = 200 -> 10 q per warp, D*rpad/8 = 40 units -> 2 per warp)
 constexpr int CT_THREADS = 32 * CNW;
+#ifndef GPTB_K2_TLOAD
+#define GPTB_K2_TLOAD 1
+#endif
 #ifndef GPTB_K2_CHAINS
 #define GPTB_K2_CHAINS 2
 #endif
@@ -122,8 +125,17 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
             for (int j = 0; j < TB; ++j) {
                 const int t = t0 + j * CT_THREADS;
                 const int tt = t < total ? t : 0;                 // (past the end: a valid address, nothing stored)
-                const int rowt = tt & (CRB - 1), rest = tt >> 6;
+#if GPTB_K2_TLOAD == 0
+                const int rowt = tt & (CRB - 1), rest = tt >> 6;   // a warp: 32 rows x one 16-byte column group
                 const int k = rest / q4, q = rest - k * q4;
+#else
+                // a warp: RS rows x (32 / RS) adjacent column groups — fewer lines per load instruction, at the price of
+                // a (32 / RS)-way bank conflict in the transposing stores
+                constexpr int RS = GPTB_K2_TLOAD == 1 ? 8 : 16, QS = 32 / RS;
+                const int ln = tt & 31, rowgrp = (tt >> 5) % (CRB / RS), kq = tt / (32 * (CRB / RS));
+                const int qh = q4 / QS, k = kq / qh, q = (kq - k * qh) * QS + (ln % QS);
+                const int rowt = rowgrp * RS + ln / QS;
+#endif
                 v[j] = __ldg(reinterpret_cast<const float4 *>(p.T + ((size_t)k * p.mpad + (size_t)blockIdx.x * CRB + rowt) * rpad) + q);
                 l0[j] = t < total ? 4 * q : r;                    // past the end: nothing is stored
                 d[j] = Tf + (size_t)(k * r + 4 * q) * CRB + rowt;
