@@ -27,7 +27,7 @@ FEAT_COS, FEAT_SINCOS = 0, 1
 FLAG_LANGEVIN, FLAG_STIEFEL, FLAG_FIX_U, FLAG_RMSPROP, FLAG_CLS_SINGLE_UPDATE = 1, 2, 4, 8, 16
 ALG_AUTO, ALG_DIRECT, ALG_NODES = 0, 1, 2
 OPT_PIPE_GROUPS, OPT_PIPE_RESERVE, OPT_ALGORITHM, OPT_NODE_ORDER, OPT_NODE_THETA, OPT_RMS_ALPHA, OPT_RMS_LAMBDA, OPT_PRED_CHUNK_MB, \
-    OPT_FRONT_PREFETCH = range(9)
+    OPT_FRONT_PREFETCH, OPT_PRED_LAYOUT, OPT_PRED_WARPS = range(11)
 PHASES = ("gather", "fwd", "contract", "bwd", "reduce", "update")
 
 H = C.c_void_p

@@ -1771,6 +1771,14 @@ int gptb_set_option(gptb_handle *h, int32_t option, double value) {
         case GPTB_OPT_PIPE_RESERVE:
             h->pipe_reserve = (int)value;
             return GPTB_OK;
+        case GPTB_OPT_PRED_LAYOUT:
+            if (value != 0.0 && value != 1.0) break;
+            h->pred_layout = (int)value;
+            return GPTB_OK;
+        case GPTB_OPT_PRED_WARPS:
+            if (!(value >= 0.0 && value <= 16.0)) break;
+            h->pred_warps = (int)value;
+            return GPTB_OK;
         case GPTB_OPT_FRONT_PREFETCH:
             h->front_enabled = value != 0.0;
             return GPTB_OK;
@@ -1784,7 +1792,7 @@ int gptb_set_option(gptb_handle *h, int32_t option, double value) {
             h->grid_valid = false;
             return GPTB_OK;
         case GPTB_OPT_PRED_CHUNK_MB:
-            if (!(value >= 1.0 && value <= 4096.0)) break;
+            if (!(value >= 1.0 && value <= 65536.0)) break;
             h->pred_chunk_mb = (int)value;
             return GPTB_OK;
         case GPTB_OPT_RMS_ALPHA:

@@ -182,7 +182,9 @@ struct gptb_handle {
     double node_theta = 2.0;           // cell half-width times the largest |frequency| of the dimension
     bool grid_valid = false;
     gptb_nodes nodes;
-    int pred_chunk_mb = 256;           // size of the sweep's T2 chunk (GPTB_OPT_PRED_CHUNK_MB); measured: larger is faster up to ~160 MB
+    int pred_layout = 0;               // GPTB_OPT_PRED_LAYOUT: 0 samples on the lanes (contract_fwd3), 1 row tiles (contract_fwd2)
+    int pred_warps = 0;                // GPTB_OPT_PRED_WARPS: warps per CTA of contract_fwd3 (0 = from the row size)
+    int pred_chunk_mb = 4096;          // T2 budget of the posterior sweep (GPTB_OPT_PRED_CHUNK_MB), see pred_nodes.cu
     gptb_pred_cache *pred_cache = nullptr;   // buffers of the node-grid posterior sweep (pred_nodes.cu), kept between calls
     bool have_domain = false;          // input domain known: from gptb_set_train (min / max of X) or gptb_set_domain
     double dom_lo[16] = {0}, dom_hi[16] = {0};
@@ -354,6 +356,11 @@ int gptb_nodes_interp(gptb_handle *h, int64_t bs);
 int gptb_nodes_launch_interp(gptb_handle *h, int P, const float *Cf, const int32_t *srow, const int32_t *sc, const float *su,
                              float *T2, int ctot, int col0, int ncols, int G, int64_t row0, int64_t nrows, int64_t rec_stride,
                              int64_t t2_stride, cudaStream_t s);
+int gptb_nodes_launch_coef_lanes(gptb_handle *h, const float *Tn, float *Cf, int G, int P, int ns, int tn_cols, int SL, int s0,
+                                 int mnpad, cudaStream_t s);
+int gptb_launch_contract_fwd3(gptb_handle *h, const float *T2, const double *w_group, int ns, int SL, int64_t nrows,
+                              int64_t t2_stride, double *fh, int64_t fh_stride, double *mean_acc, double mean_scale,
+                              cudaStream_t s);
 int gptb_nodes_launch_coef_cols(gptb_handle *h, const float *Tn, float *Cf, int G, int P, int ncols, int tn_cols, int ctot,
                                 int col0, int mnpad, cudaStream_t s);
 int gptb_nodes_upload_cheb(gptb_handle *h, int P);

@@ -673,6 +673,112 @@ __global__ void __launch_bounds__(256) contract_fwd2_kernel(const ContractFwd2Pa
     }
 }
 
+
+// ------------------------------------------------------------------------------------------------------------
+// Posterior sweep with the samples on the lanes: T2[k][row][l][SL] (SL = 8, 16 or 32 samples side by side, written
+// by the interpolation as whole 4*SL-byte pieces).  A warp owns 32/SL rows at a time, lane = (row, sample), and
+// brings their D*r lines (20 KB at BASELINE config 5) into its own shared-memory tile [k*r + l][32 lanes] with 16-byte
+// cp.async — a straight copy, no transposition; a gather T[k][I[q,k]] is then one conflict-free LDS.32 of every
+// lane's own sample.  Warps are independent (load / compute phases of different warps overlap); one CTA per SM, as
+// many warps as tiles fit.  (Gathering straight from global memory through L1 was measured 4x slower: the lines of a
+// row are re-read ~Q/r times each and did not stay in L1 — 1.4 TB of L2 traffic at C5.)
+struct ContractFwd3Params {
+    const float *T2;
+    const double *w;         // [ns][Q]
+    const int32_t *off1;     // [Q][DP]: (k*r + I[q,k]) * 32 = float index of the (k,l) line in a warp's tile
+    double *fh;              // [ns][fh_stride] or null
+    double *mean_acc;        // [nrows] or null (plain read-modify-write: one warp per row, groups run in stream order)
+    double mean_scale;
+    int64_t nrows, t2_stride, fh_stride;
+    int DP, r, Q, ns, SL, sl_shift;
+};
+
+template <int DT>
+__global__ void __launch_bounds__(512) contract_fwd3_kernel(const ContractFwd3Params p) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int D = DT;
+    constexpr int DP4 = (DT + 3) / 4;
+    const int r = p.r, Q = p.Q, SL = p.SL, DR = D * r;
+    const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5, nw = blockDim.x >> 5;
+    int4 *offs = reinterpret_cast<int4 *>(smem_raw);                      // [Q][DP4] byte offsets of the (k,l) lines
+    float *ws = reinterpret_cast<float *>(offs + (size_t)Q * DP4);        // [Q][SL]
+    float *tiles = ws + (((size_t)Q * SL + 31) & ~(size_t)31);            // [nw][DR][32]
+    for (int t = tid; t < Q * DP4; t += blockDim.x) {
+        int4 v = __ldg(reinterpret_cast<const int4 *>(p.off1) + t);
+        v.x <<= 2; v.y <<= 2; v.z <<= 2; v.w <<= 2;
+        offs[t] = v;
+    }
+    for (int t = tid; t < Q * SL; t += blockDim.x) {
+        const int q = t >> p.sl_shift, sidx = t & (SL - 1);
+        ws[t] = sidx < p.ns ? (float)p.w[(size_t)sidx * Q + q] : 0.f;
+    }
+    __syncthreads();
+    const int rpw = 32 >> p.sl_shift;                     // rows per warp and iteration
+    const int sidx = lane & (SL - 1), rsub = lane >> p.sl_shift;
+    const int64_t ngrp = (p.nrows + rpw - 1) / rpw;
+    const float *wl = ws + sidx;
+    float *tile = tiles + (size_t)wp * DR * 32;
+    const char *tb = reinterpret_cast<const char *>(tile + lane);
+    const uint32_t tile_s = tcx::smem_u32(tile);
+    // this lane's 16-byte pieces of the copy: piece (kl, within) with kl = it*4 + lane/8, within = lane%8 -> lanes
+    // 4*within .. 4*within+3 of line kl, i.e. row (4*within) >> sl_shift, samples (4*within) & (SL-1) ..
+    const int within = lane & 7, c_rsub = (4 * within) >> p.sl_shift, c_s = (4 * within) & (SL - 1);
+    for (int64_t gi = (int64_t)blockIdx.x * nw + wp; gi < ngrp; gi += (int64_t)gridDim.x * nw) {
+        const int64_t row0 = gi * rpw;
+        {
+            const int64_t crow = min(row0 + c_rsub, p.nrows - 1);         // rows past the end: a valid row, never stored
+            for (int kl = lane >> 3; kl < DR; kl += 4) {
+                const int k = kl / r, l = kl - k * r;
+                const float *src = p.T2 + (((size_t)k * p.t2_stride + crow) * r + l) * SL + c_s;
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tile_s + (uint32_t)(kl * 32 + 4 * within) * 4u), "l"(src)
+                             : "memory");
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            __syncwarp();
+        }
+        float f0 = 0.f, f1 = 0.f;
+        int q = 0;
+        for (; q + 1 < Q; q += 2) {                       // two independent product chains
+            const int4 *o0 = offs + (size_t)q * DP4, *o1 = o0 + DP4;
+            float v0 = 1.f, v1 = 1.f;
+#pragma unroll
+            for (int g4 = 0; g4 < DP4; ++g4) {
+                const int4 a = o0[g4], b = o1[g4];
+                if (g4 * 4 + 0 < D) { v0 *= *reinterpret_cast<const float *>(tb + a.x); v1 *= *reinterpret_cast<const float *>(tb + b.x); }
+                if (g4 * 4 + 1 < D) { v0 *= *reinterpret_cast<const float *>(tb + a.y); v1 *= *reinterpret_cast<const float *>(tb + b.y); }
+                if (g4 * 4 + 2 < D) { v0 *= *reinterpret_cast<const float *>(tb + a.z); v1 *= *reinterpret_cast<const float *>(tb + b.z); }
+                if (g4 * 4 + 3 < D) { v0 *= *reinterpret_cast<const float *>(tb + a.w); v1 *= *reinterpret_cast<const float *>(tb + b.w); }
+            }
+            f0 = fmaf(wl[(size_t)q * SL], v0, f0);
+            f1 = fmaf(wl[(size_t)(q + 1) * SL], v1, f1);
+        }
+        if (q < Q) {
+            const int4 *o0 = offs + (size_t)q * DP4;
+            float v0 = 1.f;
+#pragma unroll
+            for (int g4 = 0; g4 < DP4; ++g4) {
+                const int4 a = o0[g4];
+                if (g4 * 4 + 0 < D) v0 *= *reinterpret_cast<const float *>(tb + a.x);
+                if (g4 * 4 + 1 < D) v0 *= *reinterpret_cast<const float *>(tb + a.y);
+                if (g4 * 4 + 2 < D) v0 *= *reinterpret_cast<const float *>(tb + a.z);
+                if (g4 * 4 + 3 < D) v0 *= *reinterpret_cast<const float *>(tb + a.w);
+            }
+            f0 = fmaf(wl[(size_t)q * SL], v0, f0);
+        }
+        __syncwarp();                                     // every lane is done with the tile before the next copy
+        const float f = f0 + f1;
+        const int64_t row = row0 + rsub;
+        const bool out = row < p.nrows && sidx < p.ns;
+        if (p.fh && out) p.fh[(size_t)sidx * p.fh_stride + row] = (double)f;
+        if (p.mean_acc) {
+            double sum = out ? (double)f : 0.0;
+            for (int o = SL >> 1; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            if (row < p.nrows && sidx == 0) p.mean_acc[row] += p.mean_scale * sum;
+        }
+    }
+}
+
 }  // namespace
 
 int gptb_launch_contract_fwd2(gptb_handle *h, const float *T2, const double *w_group, int ns, int col0, int ncols, int64_t nrows,
@@ -692,6 +798,41 @@ int gptb_launch_contract_fwd2(gptb_handle *h, const float *T2, const double *w_g
         auto kfn = contract_fwd2_kernel<DT>;                                                                \
         GPTB_CUDA_OK(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
         kfn<<<grid, 256, smem, s>>>(p);                                                                     \
+    } break;
+    switch (c.D) {
+        GPTB_CONTRACT_CASE(1) GPTB_CONTRACT_CASE(2) GPTB_CONTRACT_CASE(3) GPTB_CONTRACT_CASE(4)
+        GPTB_CONTRACT_CASE(5) GPTB_CONTRACT_CASE(6) GPTB_CONTRACT_CASE(7) GPTB_CONTRACT_CASE(8)
+        GPTB_CONTRACT_CASE(9) GPTB_CONTRACT_CASE(10) GPTB_CONTRACT_CASE(11) GPTB_CONTRACT_CASE(12)
+        GPTB_CONTRACT_CASE(13) GPTB_CONTRACT_CASE(14) GPTB_CONTRACT_CASE(15) GPTB_CONTRACT_CASE(16)
+        default: return GPTB_ERR_UNSUPPORTED;
+    }
+#undef GPTB_CONTRACT_CASE
+    h->launches++;
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    return GPTB_OK;
+}
+
+int gptb_launch_contract_fwd3(gptb_handle *h, const float *T2, const double *w_group, int ns, int SL, int64_t nrows,
+                              int64_t t2_stride, double *fh, int64_t fh_stride, double *mean_acc, double mean_scale,
+                              cudaStream_t s) {
+    const gptb_config &c = h->cfg;
+    if (!h->ct_off1 || (SL != 8 && SL != 16 && SL != 32) || ns > SL) return GPTB_ERR_UNSUPPORTED;
+    const size_t tables = (size_t)c.Q * ((c.D + 3) / 4) * 16 + (((size_t)c.Q * SL + 31) & ~(size_t)31) * sizeof(float);
+    const size_t tile = (size_t)c.D * c.r * 32 * sizeof(float);
+    if (tables + tile > 227 * 1024) return GPTB_ERR_UNSUPPORTED;
+    int nwarps = (int)std::min<size_t>(16, (227 * 1024 - tables) / tile);
+    if (h->pred_warps > 0) nwarps = std::min(nwarps, h->pred_warps);
+    const size_t smem = tables + (size_t)nwarps * tile;
+    ContractFwd3Params p;
+    p.T2 = T2; p.w = w_group; p.off1 = h->ct_off1; p.fh = fh; p.mean_acc = mean_acc; p.mean_scale = mean_scale;
+    p.nrows = nrows; p.t2_stride = t2_stride; p.fh_stride = fh_stride;
+    p.DP = (c.D + 3) & ~3; p.r = c.r; p.Q = c.Q; p.ns = ns; p.SL = SL; p.sl_shift = SL == 8 ? 3 : (SL == 16 ? 4 : 5);
+    const dim3 grid((unsigned)h->sm_count);
+#define GPTB_CONTRACT_CASE(DT)                                                                              \
+    case DT: {                                                                                              \
+        auto kfn = contract_fwd3_kernel<DT>;                                                                \
+        GPTB_CUDA_OK(h, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        kfn<<<grid, nwarps * 32, smem, s>>>(p);                                                             \
     } break;
     switch (c.D) {
         GPTB_CONTRACT_CASE(1) GPTB_CONTRACT_CASE(2) GPTB_CONTRACT_CASE(3) GPTB_CONTRACT_CASE(4)

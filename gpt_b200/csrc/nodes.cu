@@ -103,6 +103,28 @@ __global__ void __launch_bounds__(256) node_coef_cols_kernel(const float *__rest
     }
 }
 
+// The same with the samples on the fastest axis (posterior sweep, pred_nodes.cu): Tn holds ns samples x r columns
+// (column s*r + l); coefficient column l*SL + s0 + s of a table with r*SL columns.
+__global__ void __launch_bounds__(256) node_coef_lanes_kernel(const float *__restrict__ Tn, float *__restrict__ Cf, int G, int P,
+                                                              int PP, int r, int ns, int tn_cols, int SL, int s0, int mnpad) {
+    const int k = blockIdx.y;
+    const int t = blockIdx.x * 256 + threadIdx.x;
+    const int ncols = ns * r;
+    if (t >= G * ncols) return;
+    const int col = t % ncols, c = t / ncols;
+    const int sl = col / r, l = col - sl * r;
+    float f[PMAX];
+#pragma unroll
+    for (int j = 0; j < PMAX; ++j) f[j] = j < P ? Tn[((size_t)k * tn_cols + col) * mnpad + c * P + j] : 0.f;
+    float *out = Cf + (((size_t)k * G + c) * (r * SL) + l * SL + s0 + sl) * PP;
+    for (int p = 0; p < PP; ++p) {
+        float a = 0.f;
+#pragma unroll
+        for (int j = 0; j < PMAX; ++j) a = fmaf(c_cheb[p * PMAX + j], f[j], a);
+        out[p] = a;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ cell sort
 // grid (ceil(bs / SCHUNK), D), 256 threads: the batch rows of one dimension are sorted by cell inside chunks of SCHUNK
 // rows (a stable counting sort: warp w owns 256 contiguous rows and a private histogram, equal cells inside a warp are
@@ -194,6 +216,7 @@ __global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restric
                                                           float *__restrict__ T2, int ctot, int col0, int ncols, int G,
                                                           int64_t row0, int64_t nrows, int64_t rec_stride,
                                                           int64_t t2_stride, int IWROWS) {
+    // blockIdx.z: block of NL*32 columns of the ncols this launch produces (the T2 rows are ncols wide)
     // IWROWS records per warp, chosen by the launcher: few enough that the grid fills the chip with ~32 warps per SM
     // (a chunk of the posterior sweep has only 65536 (row, dimension) items), many enough that a cell's coefficients
     // are reused
@@ -201,7 +224,10 @@ __global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restric
     const int k = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const size_t kb = (size_t)k * rec_stride + row0;
     const float4 *Ck = reinterpret_cast<const float4 *>(Cf + (size_t)k * G * ctot * PP);
-    float *Tk = T2 + (size_t)k * t2_stride * ncols;
+    const int zoff = blockIdx.z * NL * 32;
+    float *Tk = T2 + (size_t)k * t2_stride * ncols + zoff;
+    const int zcols = min(NL * 32, ncols - zoff);       // columns of this block
+    col0 += zoff;
     const int64_t s0 = ((int64_t)blockIdx.x * (ITHREADS / 32) + warp) * IWROWS, s1 = min(nrows, s0 + IWROWS);
     float4 cf[NL][PP / 4];
     int cur = -1;
@@ -221,7 +247,7 @@ __global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restric
             cur = c;
 #pragma unroll
             for (int a = 0; a < NL; ++a) {
-                const int col = col0 + min(a * 32 + lane, ncols - 1);
+                const int col = col0 + min(a * 32 + lane, zcols - 1);
 #pragma unroll
                 for (int q = 0; q < PP / 4; ++q) cf[a][q] = __ldg(Ck + ((size_t)c * ctot + col) * (PP / 4) + q);
             }
@@ -240,7 +266,7 @@ __global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restric
                     acc1 = fmaf(tb[4 * q + 3], cf[a][q].w, acc1);
                 }
                 const int l = a * 32 + lane;
-                if (l < ncols) Tk[(size_t)row * ncols + l] = acc0 + acc1;
+                if (l < zcols) Tk[(size_t)row * ncols + l] = acc0 + acc1;
             }
         };
         for (int j = 0; j < cnt; j += 2) {
@@ -268,7 +294,7 @@ __global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restric
                     acc1 = __ffma2_rn(tb[4 * q + 3], splat(cf[a][q].w), acc1);
                 }
                 const int l = a * 32 + lane;
-                if (l < ncols) {
+                if (l < zcols) {
                     Tk[(size_t)row_a * ncols + l] = acc0.x + acc1.x;
                     if (jb != j) Tk[(size_t)row_b * ncols + l] = acc0.y + acc1.y;
                 }
@@ -620,6 +646,15 @@ int gptb_nodes_launch_coef_cols(gptb_handle *h, const float *Tn, float *Cf, int 
     return GPTB_OK;
 }
 
+int gptb_nodes_launch_coef_lanes(gptb_handle *h, const float *Tn, float *Cf, int G, int P, int ns, int tn_cols, int SL, int s0,
+                                 int mnpad, cudaStream_t s) {
+    node_coef_lanes_kernel<<<dim3((G * ns * h->cfg.r + 255) / 256, h->cfg.D), 256, 0, s>>>(Tn, Cf, G, P, (P + 3) & ~3, h->cfg.r, ns,
+                                                                                           tn_cols, SL, s0, mnpad);
+    h->launches++;
+    GPTB_CUDA_OK(h, cudaGetLastError());
+    return GPTB_OK;
+}
+
 // The cosine-transform matrix of order P (shared by every grid of the library: the sampler's and the sweep's).
 int gptb_nodes_upload_cheb(gptb_handle *h, int P) {
     std::vector<float> cm((size_t)PMAX * PMAX, 0.f);
@@ -634,10 +669,13 @@ int gptb_nodes_upload_cheb(gptb_handle *h, int P) {
 int gptb_nodes_launch_interp(gptb_handle *h, int P, const float *Cf, const int32_t *srow, const int32_t *sc, const float *su,
                              float *T2, int ctot, int col0, int ncols, int G, int64_t row0, int64_t nrows, int64_t rec_stride,
                              int64_t t2_stride, cudaStream_t s) {
-    const int NL = (ncols + 31) / 32;
+    // column blocks per warp: up to 5 (160 columns) at order 12, 2 otherwise (what interp_kernel is instantiated for);
+    // wider tables take several blocks along grid.z
+    const int nl_all = (ncols + 31) / 32, nl_max = P == 12 ? 5 : 2;
+    const int NL = std::min(nl_all, nl_max), nz = (nl_all + NL - 1) / NL;
     int IWROWS = 64;
-    while (IWROWS > 8 && nrows * h->cfg.D / IWROWS < (int64_t)h->sm_count * 32) IWROWS >>= 1;
-    const dim3 grid((unsigned)((nrows + (ITHREADS / 32) * IWROWS - 1) / ((ITHREADS / 32) * IWROWS)), h->cfg.D);
+    while (IWROWS > 8 && nrows * h->cfg.D * nz / IWROWS < (int64_t)h->sm_count * 32) IWROWS >>= 1;
+    const dim3 grid((unsigned)((nrows + (ITHREADS / 32) * IWROWS - 1) / ((ITHREADS / 32) * IWROWS)), h->cfg.D, nz);
 #define GPTB_CALL(PP, NN)                                                                                                   \
     interp_kernel<PP, NN><<<grid, ITHREADS, 0, s>>>(Cf, srow, sc, su, T2, ctot, col0, ncols, G, row0, nrows, rec_stride, t2_stride, \
                                                     IWROWS);

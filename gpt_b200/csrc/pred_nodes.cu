@@ -4,15 +4,15 @@
 // The direct tensor-core path (api.cu: pred_tc_grouped) generates the features of every test row once per group of four
 // samples: 50 x the algorithmic cosine count at BASELINE config 5.  Here the features are generated at the G*P nodes of
 // a grid over the test inputs' domain only (nodes.cu), once per sample group, and every (row, sample) pair costs
-//   - D*r*P FMAs of interpolation  (interp_kernel on the cell-sorted records of the test rows, the columns of eight
-//     samples side by side so that one basis recurrence serves 160 columns), and
-//   - the Q*D shared-memory gathers of the contraction (contract_fwd2_kernel) — the floor of the sweep: 4*Q*D bytes of
-//     shared-memory bandwidth per pair, 35 ms for 2e8 pairs on 148 SMs.
-// Loop order: sample groups outside (U_store goes up group by group, 5 MB at a time), row
-// chunks inside.  The chunk's T2 block (rows x D x 160 floats) is GPTB_OPT_PRED_CHUNK_MB large, 256 MB by default: an
-// L2-sized chunk (40 MB) was measured SLOWER (198.9 ms at C5 against 168.6 ms at 160 MB and 163.8 ms at 640 MB) — the
-// contraction is bound by its shared-memory gathers, not by where T2 comes from, and 2000 short launch pairs each pay
-// a partial last wave.
+//   - D*r*P FMAs of interpolation  (interp_kernel on the cell-sorted records of the test rows: one basis recurrence
+//     serves the 160 columns a warp owns), 4*D*r bytes of T2 written and read back (2 x 128 GB at config 5), and
+//   - the Q*D shared-memory gathers of the contraction (contract_fwd3_kernel; contract_fwd2_kernel for the row-tile
+//     layout): 4*Q*D bytes of shared-memory bandwidth per pair, 35 ms for 2e8 pairs on 148 SMs.
+// Loop order: sample groups outside (up to 32 samples side by side on the fastest axis of T2: column l*SL + s, so
+// that the contraction gathers one coalesced line per (k, l) for all samples at once), row chunks inside.  The T2 budget
+// is GPTB_OPT_PRED_CHUNK_MB (4096 MB by default, two half-buffers): larger chunks are faster — the contraction is a
+// persistent one-CTA-per-SM kernel whose launch stages 32 KB of tables per CTA and ends in a partial wave, and an
+// L2-sized chunk (40 MB) buys nothing because the contraction is bound by its shared-memory gathers.
 #include <math.h>
 
 #include <algorithm>
@@ -33,6 +33,8 @@ struct gptb_pred_cache {
     double *lohi = nullptr, *lo = nullptr, *invh = nullptr, *Ud = nullptr, *wd = nullptr, *fh = nullptr;
     unsigned char *img = nullptr;
     double *lohi_host = nullptr;                          // pinned
+    cudaStream_t st2 = nullptr;                           // contraction stream (two T2 half-buffers alternate)
+    cudaEvent_t ev_i[2] = {nullptr, nullptr}, ev_c[2] = {nullptr, nullptr}, ev_g = nullptr;
 };
 
 namespace {
@@ -103,6 +105,11 @@ void gptb_pred_nodes_free(gptb_handle *h) {
     cudaFree(pc->XnF); cudaFree(pc->Tn); cudaFree(pc->Cf); cudaFree(pc->T2); cudaFree(pc->state); cudaFree(pc->lohi);
     cudaFree(pc->lo); cudaFree(pc->invh); cudaFree(pc->Ud); cudaFree(pc->wd); cudaFree(pc->fh); cudaFree(pc->img);
     if (pc->lohi_host) cudaFreeHost(pc->lohi_host);
+    if (pc->st2) {
+        cudaStreamDestroy(pc->st2);
+        for (int i = 0; i < 2; ++i) { cudaEventDestroy(pc->ev_i[i]); cudaEventDestroy(pc->ev_c[i]); }
+        cudaEventDestroy(pc->ev_g);
+    }
     delete pc;
     h->pred_cache = nullptr;
 }
@@ -114,7 +121,7 @@ int gptb_pred_nodes(gptb_handle *h, const double *w_store, const double *U_store
     if (!gptb_is_tc(h) || !h->ct_off1 || h->algorithm == GPTB_ALG_DIRECT) return GPTB_ERR_UNSUPPORTED;
     if (h->algorithm == GPTB_ALG_AUTO && (Nt < 8192 || Nt * (int64_t)S < (1 << 20))) return GPTB_ERR_UNSUPPORTED;
     const int P = h->node_P, PP = (P + 3) & ~3;
-    const int max_cols = P == 12 ? 160 : 64;              // column blocks interp_kernel is instantiated for
+    const int max_cols = P == 12 ? 160 : 64;              // widest column group of the tiles layout (interp_kernel instances)
     if (c.r > max_cols || Nt > 2147483647LL - PRED_CHUNK_ALIGN) return GPTB_ERR_UNSUPPORTED;
     if (!h->pred_cache) h->pred_cache = new gptb_pred_cache();
     gptb_pred_cache &pc = *h->pred_cache;
@@ -185,13 +192,38 @@ int gptb_pred_nodes(gptb_handle *h, const double *w_store, const double *U_store
     if (nc_max < h->rpad) return GPTB_ERR_UNSUPPORTED;
     const int Sg1 = std::max(1, std::min<int>(nc_max / c.r, S));          // samples per K1 launch
     const int NC1 = std::max(h->rpad, (Sg1 * c.r + 15) / 16 * 16);
-    const int CGs = std::max(1, std::min<int>(max_cols / c.r, S));        // samples per column group
-    const int ctot_max = (CGs * c.r + 3) & ~3;
-    int64_t RC = (int64_t)(((size_t)h->pred_chunk_mb << 20) / ((size_t)c.D * ctot_max * 4)) / PRED_CHUNK_ALIGN * PRED_CHUNK_ALIGN;
+    // Column layout of a sample group.  lanes (default): up to 32 samples side by side on the fastest axis, column
+    // l*SL + s — the contraction then needs no transposed tile (contract_fwd3).  tiles: the samples' r columns one after
+    // the other, 160/r samples per group, one 64-row tile per (tile, sample) CTA (contract_fwd2).
+    // (the lanes contraction keeps one D*r*128-byte tile per warp beside its tables: very wide models use the tiles)
+    const bool lanes = h->pred_layout == 0 && (size_t)c.Q * ((c.D + 3) / 4) * 16 + (size_t)c.Q * 128 + (size_t)c.D * c.r * 128 <= 220 * 1024;
+    const int CGs = lanes ? std::min<int>(32, S) : std::max(1, std::min<int>(max_cols / c.r, S));   // samples per group
+    auto sl_for = [](int gs) { return gs <= 8 ? 8 : (gs <= 16 ? 16 : 32); };
+    const int ctot_max = lanes ? c.r * sl_for(CGs) : ((CGs * c.r + 3) & ~3);
+    // two half-buffers of GPTB_OPT_PRED_CHUNK_MB / 2 each: the interpolation of chunk p+1 (HBM-write bound) runs on the
+    // main stream beside the contraction of chunk p (shared-memory bound) on a second one
+    // (measured at C5, 1M x 200: 150 ms with 256 MB, 130 ms with 1 GB, 123 ms with 2 GB, 117 ms with 4 GB of T2; without
+    // the second stream 130 ms at 1 GB, 124 ms at 4 GB.  The budget is capped at an eighth of the free device memory.)
+    const bool overlap = lanes;
+    const int nbuf = overlap ? 2 : 1;
+    size_t chunk_bytes = (size_t)h->pred_chunk_mb << 20;
+    {
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) chunk_bytes = std::min(chunk_bytes, std::max<size_t>(free_b / 8, (size_t)64 << 20));
+    }
+    int64_t RC = (int64_t)(chunk_bytes / nbuf / ((size_t)c.D * ctot_max * 4)) / PRED_CHUNK_ALIGN * PRED_CHUNK_ALIGN;
     RC = std::max<int64_t>(PRED_CHUNK_ALIGN, std::min<int64_t>(RC, ntpad));
+    if (overlap && !pc.st2) {
+        GPTB_CUDA_OK(h, cudaStreamCreateWithFlags(&pc.st2, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) {
+            GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&pc.ev_i[i], cudaEventDisableTiming));
+            GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&pc.ev_c[i], cudaEventDisableTiming));
+        }
+        GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&pc.ev_g, cudaEventDisableTiming));
+    }
     GPTB_TRY(pc_grow(h, &pc.Tn, &pc.cap[PC::B_TN], (size_t)c.D * Sg1 * c.r * mnpad));
     GPTB_TRY(pc_grow(h, &pc.Cf, &pc.cap[PC::B_CF], (size_t)c.D * G * ctot_max * PP));
-    GPTB_TRY(pc_grow(h, &pc.T2, &pc.cap[PC::B_T2], (size_t)c.D * RC * ctot_max));
+    GPTB_TRY(pc_grow(h, &pc.T2, &pc.cap[PC::B_T2], (size_t)nbuf * c.D * RC * ctot_max));
     GPTB_TRY(pc_grow(h, &pc.img, &pc.cap[PC::B_IMG], (size_t)c.D * h->npad * 2 * NC1 * 2));
     GPTB_TRY(pc_grow(h, &pc.Ud, &pc.cap[PC::B_UD], (size_t)CGs * ucnt));
     GPTB_TRY(pc_grow(h, &pc.wd, &pc.cap[PC::B_WD], (size_t)S * c.Q));
@@ -206,26 +238,49 @@ int gptb_pred_nodes(gptb_handle *h, const double *w_store, const double *U_store
     // ---- sample groups outside, row chunks inside, everything on the handle's stream.  (Running the interpolation of
     // chunk p+1 on a second stream beside the contraction of chunk p was measured SLOWER, 215 vs 198 ms at C5: both
     // kernels queue on the LSU / L1 path — ncu: mio_throttle and long_scoreboard lead the contraction's stalls.)
+    int64_t chunk_no = 0;
     for (int g0 = 0; g0 < S; g0 += CGs) {
         const int gs = std::min(CGs, S - g0);
-        const int ctot = (gs * c.r + 3) & ~3;
+        const int SL = sl_for(gs);
+        const int ctot = lanes ? c.r * SL : ((gs * c.r + 3) & ~3);
         GPTB_CUDA_OK(h, cudaMemcpyAsync(pc.Ud, U_store + (size_t)g0 * ucnt, sizeof(double) * gs * ucnt, cudaMemcpyHostToDevice, st));
+        if (lanes && gs < SL)   // unused sample slots of a ragged group: zero coefficients, so their T2 columns are zero
+            GPTB_CUDA_OK(h, cudaMemsetAsync(pc.Cf, 0, sizeof(float) * (size_t)c.D * G * ctot * PP, st));
         for (int s0 = 0; s0 < gs; s0 += Sg1) {
             const int sg = std::min(Sg1, gs - s0);
             GPTB_TRY(gptb_tc_pack_group_scaled(h, pc.Ud + (size_t)s0 * ucnt, sg, NC1, pc.img, pc.state, st));
             GPTB_TRY(gptb_launch_fwd_tc_cols(h, pc.XnF, pc.img, pc.state + 1, m, mnpad, pc.Tn, sg * c.r, NC1));
-            GPTB_TRY(gptb_nodes_launch_coef_cols(h, pc.Tn, pc.Cf, G, P, sg * c.r, sg * c.r, ctot, s0 * c.r, mnpad, st));
+            if (lanes) GPTB_TRY(gptb_nodes_launch_coef_lanes(h, pc.Tn, pc.Cf, G, P, sg, sg * c.r, SL, s0, mnpad, st));
+            else GPTB_TRY(gptb_nodes_launch_coef_cols(h, pc.Tn, pc.Cf, G, P, sg * c.r, sg * c.r, ctot, s0 * c.r, mnpad, st));
         }
-        for (int64_t row0 = 0; row0 < Nt; row0 += RC) {
+        cudaStream_t cs = overlap ? pc.st2 : st;           // the contractions' stream
+        for (int64_t row0 = 0; row0 < Nt; row0 += RC, ++chunk_no) {
             const int64_t nr = std::min(RC, Nt - row0);
-            GPTB_TRY(gptb_nodes_launch_interp(h, P, pc.Cf, pc.srow, pc.sc, pc.su, pc.T2, ctot, 0, ctot, G, row0, nr, ntpad, RC, st));
-            GPTB_TRY(gptb_launch_contract_fwd2(h, pc.T2, pc.wd + (size_t)g0 * c.Q, gs, 0, ctot, nr, RC,
-                                               per_sample_out ? pc.fh + row0 : nullptr, ntpad, mean_out ? pc.acc + row0 : nullptr,
-                                               1.0 / S, st));
+            const int b = overlap ? (int)(chunk_no & 1) : 0;
+            float *T2b = pc.T2 + (size_t)b * c.D * RC * ctot_max;
+            if (overlap && chunk_no >= 2) GPTB_CUDA_OK(h, cudaStreamWaitEvent(st, pc.ev_c[b], 0));   // half-buffer free again
+            GPTB_TRY(gptb_nodes_launch_interp(h, P, pc.Cf, pc.srow, pc.sc, pc.su, T2b, ctot, 0, ctot, G, row0, nr, ntpad, RC, st));
+            if (overlap) {
+                GPTB_CUDA_OK(h, cudaEventRecord(pc.ev_i[b], st));
+                GPTB_CUDA_OK(h, cudaStreamWaitEvent(cs, pc.ev_i[b], 0));
+            }
+            if (lanes)
+                GPTB_TRY(gptb_launch_contract_fwd3(h, T2b, pc.wd + (size_t)g0 * c.Q, gs, SL, nr, RC,
+                                                   per_sample_out ? pc.fh + row0 : nullptr, ntpad, mean_out ? pc.acc + row0 : nullptr,
+                                                   1.0 / S, cs));
+            else
+                GPTB_TRY(gptb_launch_contract_fwd2(h, T2b, pc.wd + (size_t)g0 * c.Q, gs, 0, ctot, nr, RC,
+                                                   per_sample_out ? pc.fh + row0 : nullptr, ntpad, mean_out ? pc.acc + row0 : nullptr,
+                                                   1.0 / S, cs));
+            if (overlap) GPTB_CUDA_OK(h, cudaEventRecord(pc.ev_c[b], cs));
         }
         if (per_sample_out)   // (the next group's contractions overwrite fh: they follow this copy on the same stream)
             GPTB_CUDA_OK(h, cudaMemcpy2DAsync(per_sample_out + (size_t)g0 * Nt, Nt * sizeof(double), pc.fh, ntpad * sizeof(double),
-                                              Nt * sizeof(double), gs, cudaMemcpyDeviceToHost, st));
+                                              Nt * sizeof(double), gs, cudaMemcpyDeviceToHost, cs));
+    }
+    if (overlap) {   // the main stream continues after the last contraction
+        GPTB_CUDA_OK(h, cudaEventRecord(pc.ev_g, pc.st2));
+        GPTB_CUDA_OK(h, cudaStreamWaitEvent(st, pc.ev_g, 0));
     }
     if (mean_out) GPTB_CUDA_OK(h, cudaMemcpyAsync(mean_out, pc.acc, sizeof(double) * Nt, cudaMemcpyDeviceToHost, st));
     GPTB_CUDA_OK(h, cudaStreamSynchronize(st));

@@ -617,8 +617,9 @@ def test_nodes_GPTregression_vs_oracle():
     assert relerr(gw, ws) < 1e-4 and relerr(gU, Us) < 1e-4
 
 
+@pytest.mark.parametrize("layout", [0, 1], ids=["lanes", "tiles"])
 @pytest.mark.parametrize("r,S,order,feature2", [(4, 5, 12, True), (5, 37, 12, False), (20, 11, 8, False), (33, 3, 16, False)])
-def test_nodes_pred_samples_vs_oracle(r, S, order, feature2):
+def test_nodes_pred_samples_vs_oracle(r, S, order, feature2, layout):
     """Posterior sweep on the node grid (pred_nodes.cu) forced on at small sizes: r not a multiple of 4 (scalar tile
     loads), more samples than one column group (ragged last group), orders other than 12 (64-column groups), r > 32;
     mean, per-sample output and the mean-only call against oracle.pred."""
@@ -629,7 +630,9 @@ def test_nodes_pred_samples_vs_oracle(r, S, order, feature2):
                                                for _ in range(P["D"])], 2) for _ in range(S)], 3))
     phi = P["phi_fn"](P["X"])
     want = np.stack([o.pred(ws[:, s], Us[:, :, :, s], P["I"], phi) for s in range(S)], 1)
-    opts = {L.OPT_ALGORITHM: L.ALG_NODES, L.OPT_NODE_ORDER: order}
+    # both column layouts of a sample group: samples on the lanes (8 / 16 / 32 side by side: S = 5, 11, 37 reach all
+    # three and a ragged last group) and one row tile per sample
+    opts = {L.OPT_ALGORITHM: L.ALG_NODES, L.OPT_NODE_ORDER: order, L.OPT_PRED_LAYOUT: layout}
     mean, per = G.pred_samples(ws, Us, P["I"], _feat(P), per_sample=True, precision=L.PREC_TC3, options=opts)
     assert relerr(per, want) < 1e-4 and relerr(mean, want.mean(1)) < 1e-4
     for s in (0, S - 1):
@@ -640,6 +643,7 @@ def test_nodes_pred_samples_vs_oracle(r, S, order, feature2):
     with _model(P, L.PREC_TC3, train=False) as m:
         m.set_option(L.OPT_ALGORITHM, L.ALG_NODES)
         m.set_option(L.OPT_NODE_ORDER, order)
+        m.set_option(L.OPT_PRED_LAYOUT, layout)
         a = m.pred(ws[:, 0], Us[:, :, :, 0], P["X"])
         b = m.pred(ws[:, 1], Us[:, :, :, 1], P["X"][:777])
     assert relerr(a, want[:, 0]) < 1e-4 and relerr(b, want[:777, 1]) < 1e-4

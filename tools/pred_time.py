@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""Timing of the C5 posterior-predictive sweep (gptb_pred_samples), repeated calls."""
+"""Timing of the C5 posterior-predictive sweep (gptb_pred_samples), repeated calls.
+    python tools/pred_time.py [S] [Nt] [auto|direct|nodes] [chunk MB] [layout 0|1] [warps]"""
 import os, sys, time
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -21,6 +22,8 @@ with G.Model(C["D"], C["n"], C["r"], B.Q, precision=L.PREC_TC3, device=0) as m:
     m.set_features(pf); m.set_index(pm["I"])
     m.set_option(L.OPT_ALGORITHM, ALG)
     if len(sys.argv) > 4: m.set_option(L.OPT_PRED_CHUNK_MB, float(sys.argv[4]))
+    if len(sys.argv) > 5: m.set_option(L.OPT_PRED_LAYOUT, float(sys.argv[5]))      # 0 lanes, 1 tiles
+    if len(sys.argv) > 6: m.set_option(L.OPT_PRED_WARPS, float(sys.argv[6]))
     for it in range(3):
         t0 = time.perf_counter()
         mean = m.pred_samples(ws, Us, Xt)
