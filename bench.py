@@ -247,6 +247,9 @@ def main():
     ap.add_argument("--no-pred", action="store_true", help="skip the C5 prediction sweep")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline")
     ap.add_argument("--pred-samples", type=int, default=C5["S"])
+    ap.add_argument("--replicas", type=int, default=1,
+                    help="R > 1: R independent chains (handles with their own streams and seeds, one host thread each) on "
+                         "one GPU; prints their aggregate steps/s instead of the single-chain line (small workloads)")
     ap.add_argument("--alg", default="auto", choices=["auto", "direct", "nodes"],
                     help="gptb_set_option(GPTB_OPT_ALGORITHM): auto picks the node grid for large minibatches")
     args = ap.parse_args()
@@ -310,19 +313,63 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    if args.replicas > 1:
+        # R independent chains — the reference's sweeps over seeds / step sizes (kin40kExperiment.jl:67-91) map to one
+        # handle per worker.  Every handle queues its steps asynchronously on its own stream; one host thread per handle
+        # (ctypes releases the GIL) keeps R launch queues busy, so the small kernels of different chains share the SMs.
+        import threading
+        R = args.replicas
+        reps = [model]
+        for i in range(1, R):
+            mi = G.Model(D, n, r, Q, precision=prec, device=local, seed=1234 + i)
+            mi.set_features(feat); mi.set_index(mdl["I"]); mi.set_train(X, y); mi.set_params(mdl["w0"], mdl["U0"])
+            reps.append(mi)
+        model.set_stream(None)
+
+        def run(mi, k):
+            mi.sgld_advance(SIGNAL_VAR, m, EPSW, EPSU, k)
+            mi.synchronize()
+        for mi in reps:
+            run(mi, max(3, args.warmup))
+        t1 = time.perf_counter()
+        run(reps[0], args.steps)
+        single = args.steps / (time.perf_counter() - t1)
+        torch.cuda.synchronize()
+        with ClockSampler(local) as clk:
+            t0 = time.perf_counter()
+            th = [threading.Thread(target=run, args=(mi, args.steps)) for mi in reps]
+            for t_ in th:
+                t_.start()
+            for t_ in th:
+                t_.join()
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+        finite = all(bool(np.isfinite(mi.get_params()[0]).all()) for mi in reps)
+        emit({"metric": "sgld_steps_per_sec", "value": R * args.steps / dt, "unit": "steps/s (sum over chains)", "n_gpus": 1,
+              "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3 / args.steps, "higher_is_better": True,
+              "scaling": "replicas", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+              "config": dict(workload_config(args, W), replicas=R, timing="wall clock around R host threads, device synchronised on both sides"),
+              "single_chain_steps_per_sec": single, "finite": finite, "clocks": clk.summary()})
+        for mi in reps[1:]:
+            mi.close()
+        return
+
     # ------------------------------------------------------------------ resident-data steps/s (device timed)
     model.sgld_advance(SIGNAL_VAR, m, EPSW, EPSU, max(3, args.warmup))
     model.synchronize()
     model.phase_ms(reset=True)               # zero the launch counter
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
-    with ClockSampler(local) as clk:
-        with torch.cuda.stream(stream):
-            ev0.record(stream)
-            model.sgld_advance(SIGNAL_VAR, m, EPSW, EPSU, args.steps)   # returns with the stream ordered after the last update
-            ev1.record(stream)
-        model.synchronize()
-        barrier()
+    # clocks and throttle reasons are sampled from here to the end of the last timed region (steps, e2e, stored chain,
+    # posterior sweep): the K timed steps alone last a few milliseconds, less than one nvidia-smi query
+    clk = ClockSampler(local)
+    clk.__enter__()
+    with torch.cuda.stream(stream):
+        ev0.record(stream)
+        model.sgld_advance(SIGNAL_VAR, m, EPSW, EPSU, args.steps)   # returns with the stream ordered after the last update
+        ev1.record(stream)
+    model.synchronize()
+    barrier()
     ms_total = ev0.elapsed_time(ev1)
     _, launches = model.phase_ms(reset=True)
     # the chain after warm-up + timed steps: identical at every GPU count up to summation order (same global
@@ -349,7 +396,7 @@ def main():
     value = 1e3 / ms_step
 
     # ------------------------------------------------------------------ e2e: host minibatches through the C ABI
-    ke = max(3, min(args.steps, 30))
+    ke = max(100, min(args.steps, 400))   # enough steps that the pipeline's fill (one un-overlapped copy) is amortised
     Xb = [torch.empty((D, m), dtype=torch.float64).pin_memory() for _ in range(2)]   # (D,m) C-order == (m,D) F-order
     yb = [torch.empty(m, dtype=torch.float64).pin_memory() for _ in range(2)]
     w_out = [torch.empty(Q, dtype=torch.float64).pin_memory() for _ in range(2)]
@@ -448,6 +495,7 @@ def main():
                 "config": {"workload": f"C5: D={C5['D']} Nt={C5['Nt']} S={S} n={C5['n']} r={C5['r']} Q={Q}, test rows sharded x{world}, host buffers in/out"},
                 "checksum": float(np.abs(mean).sum()), "seconds_each_call": dts}
 
+    clk.__exit__()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

@@ -94,7 +94,19 @@ def drive_nodes(P, device, world, rank, idbytes):
         m.sgld_advance(P["signal_var"], 1500, 1e-6, 1e-9, 4)
         m.synchronize()
         w, U = m.get_params()
-    return {"nodes_gw": gw, "nodes_gU": gU, "nodes_w": w, "nodes_U": U}
+        # pipelined host minibatches on the node grid: each rank stages its share only, and the batch's transpose, gather
+        # and cell sort run on the front stream under the previous step's all-reduce and update
+        rng = np.random.default_rng(3)
+        keep = []
+        for t in range(4):
+            i = rng.permutation(P["N"])[:1501]
+            keep.append((np.asfortranarray(P["X"][i]), np.ascontiguousarray(P["y"][i])))
+            m.sgld_step_host_submit(P["signal_var"], keep[-1][0], keep[-1][1], P["N"], 1e-6, 1e-9)
+            if t >= 1:
+                m.sgld_step_host_wait()
+        m.sgld_step_host_wait()
+        wh, Uh = m.get_params()
+    return {"nodes_gw": gw, "nodes_gU": gU, "nodes_w": w, "nodes_U": U, "nodes_host_w": wh, "nodes_host_U": Uh}
 
 
 def get_id(world, rank, idfile, tag):

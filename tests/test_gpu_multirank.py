@@ -42,7 +42,7 @@ def test_two_rank_chain_equals_one_rank_chain():
         got = _run(2, tmp)
     w0, U0 = P["w0"], P["U0"]
     tol = 2e-5   # of the accumulated update: FP32 atomics / a different summation split, not a different chain
-    for key in ("host", "adv", "s1", "pipe", "nodes"):
+    for key in ("host", "adv", "s1", "pipe", "nodes", "nodes_host"):
         assert relerr(got[0][f"{key}_w"] - w0, ref[f"{key}_w"] - w0) < tol, key
         assert relerr(got[0][f"{key}_U"] - U0, ref[f"{key}_U"] - U0) < tol, key
     assert relerr(got[0]["host_wout"] - w0, ref["host_wout"] - w0) < tol
