@@ -70,6 +70,12 @@ PROTOTYPES = {
                                 c_int64_p, c_double_p, c_double_p, c_double_p, c_double_p]),
     "gptb_sgld_advance": (C.c_int, [H, C.c_double, C.c_int64, C.c_double, C.c_double, C.c_int32, C.c_int64]),
     "gptb_comm_unique_id": (C.c_int, [C.c_void_p]),
+    "gptb_comm_init_local": (C.c_int, [C.POINTER(H), C.c_int32]),
+    "gptb_multi_sgld_run": (C.c_int, [C.POINTER(H), C.c_int32, C.c_double, C.c_int64, C.c_double, C.c_double, C.c_int32, C.c_int32,
+                                      C.c_int32, c_int64_p, c_double_p, c_double_p, c_double_p, c_double_p]),
+    "gptb_multi_sgld_advance": (C.c_int, [C.POINTER(H), C.c_int32, C.c_double, C.c_int64, C.c_double, C.c_double, C.c_int32, C.c_int64]),
+    "gptb_multi_pred_samples": (C.c_int, [C.POINTER(H), C.c_int32, c_double_p, c_double_p, C.c_int32, c_double_p, C.c_int64,
+                                          c_double_p, c_double_p]),
     "gptb_comm_init": (C.c_int, [H, C.c_int32, C.c_int32, C.c_void_p]),
     "gptb_comm_destroy": (C.c_int, [H]),
     # full-theta ("no tensor") RFF model

@@ -24,7 +24,9 @@ struct NcclApi {
     void *lib = nullptr;
     ncclResult (*GetUniqueId)(ncclUniqueId_t *) = nullptr;
     ncclResult (*CommInitRank)(ncclComm_p *, int, ncclUniqueId_t, int) = nullptr;
+    ncclResult (*CommInitAll)(ncclComm_p *, int, const int *) = nullptr;
     ncclResult (*CommDestroy)(ncclComm_p) = nullptr;
+    ncclResult (*CommAbort)(ncclComm_p) = nullptr;
     ncclResult (*AllReduce)(const void *, void *, size_t, int, int, ncclComm_p, cudaStream_t) = nullptr;
     const char *(*GetErrorString)(ncclResult) = nullptr;
     bool ok = false;
@@ -41,7 +43,9 @@ NcclApi &api() {
     if (!a.lib) return a;
     a.GetUniqueId = (decltype(a.GetUniqueId))dlsym(a.lib, "ncclGetUniqueId");
     a.CommInitRank = (decltype(a.CommInitRank))dlsym(a.lib, "ncclCommInitRank");
+    a.CommInitAll = (decltype(a.CommInitAll))dlsym(a.lib, "ncclCommInitAll");
     a.CommDestroy = (decltype(a.CommDestroy))dlsym(a.lib, "ncclCommDestroy");
+    a.CommAbort = (decltype(a.CommAbort))dlsym(a.lib, "ncclCommAbort");
     a.AllReduce = (decltype(a.AllReduce))dlsym(a.lib, "ncclAllReduce");
     a.GetErrorString = (decltype(a.GetErrorString))dlsym(a.lib, "ncclGetErrorString");
     a.ok = a.GetUniqueId && a.CommInitRank && a.CommDestroy && a.AllReduce && a.GetErrorString;
@@ -96,6 +100,61 @@ extern "C" int gptb_comm_init(gptb_handle *h, int32_t nranks, int32_t rank, cons
     h->nranks = nranks;
     h->rank = rank;
     return GPTB_OK;
+}
+
+// Single-process multi-GPU: the n handles (on n different devices of this process) become ranks 0..n-1 of one
+// communicator.  Calls that contain a collective must then be made for all of them concurrently: multi.cu does that
+// with one host thread per handle.
+extern "C" int gptb_comm_init_local(gptb_handle *const *hs, int32_t n) {
+    if (!hs || n < 1 || n > 64) return GPTB_ERR_ARG;
+    for (int i = 0; i < n; ++i) {
+        if (!hs[i]) return GPTB_ERR_ARG;
+        if (hs[i]->nccl_comm) {
+            gptb_set_error(hs[i], "communicator already initialised");
+            return GPTB_ERR_STATE;
+        }
+        for (int j = 0; j < i; ++j)
+            if (hs[j]->device == hs[i]->device) {
+                gptb_set_error(hs[0], "gptb_comm_init_local: handles %d and %d share device %d", j, i, hs[i]->device);
+                return GPTB_ERR_ARG;
+            }
+    }
+    if (n == 1) {
+        hs[0]->nranks = 1;
+        hs[0]->rank = 0;
+        return GPTB_OK;
+    }
+    NcclApi &a = api();
+    if (!a.ok || !a.CommInitAll) {
+        gptb_set_error(hs[0], "NCCL not found (dlopen libnccl.so.2 failed)");
+        return GPTB_ERR_NCCL;
+    }
+    int devs[64];
+    ncclComm_p comms[64];
+    for (int i = 0; i < n; ++i) devs[i] = hs[i]->device;
+    ncclResult r = a.CommInitAll(comms, n, devs);
+    if (r != 0) {
+        gptb_set_error(hs[0], "ncclCommInitAll: %s", a.GetErrorString(r));
+        return GPTB_ERR_NCCL;
+    }
+    for (int i = 0; i < n; ++i) {
+        hs[i]->nccl_comm = comms[i];
+        hs[i]->nranks = n;
+        hs[i]->rank = i;
+    }
+    return GPTB_OK;
+}
+
+// A rank of a single-process group failed outside a collective: abort every communicator of the group, so that the
+// ranks waiting inside an all-reduce return instead of waiting for ever (multi.cu).  The handles fall back to one rank.
+void gptb_comm_abort_group(gptb_handle *const *hs, int n) {
+    NcclApi &a = api();
+    for (int i = 0; i < n; ++i) {
+        if (hs[i]->nccl_comm && a.CommAbort) a.CommAbort((ncclComm_p)hs[i]->nccl_comm);
+        hs[i]->nccl_comm = nullptr;
+        hs[i]->nranks = 1;
+        hs[i]->rank = 0;
+    }
 }
 
 extern "C" int gptb_comm_destroy(gptb_handle *h) {

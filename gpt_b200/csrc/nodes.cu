@@ -696,11 +696,8 @@ int gptb_nodes_interp(gptb_handle *h, int64_t bs) {
 int gptb_nodes_launch_sort(gptb_handle *h, const int32_t *cell, const float *uu, int32_t *srow, int32_t *sc, float *su, int G,
                            int64_t bs, int64_t stride, cudaStream_t s) {
     const size_t smem = (size_t)(SORT_T / 32 + 1) * G * sizeof(int);
-    static bool optin = false;
-    if (!optin) {
-        cudaFuncSetAttribute(cell_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-        optin = true;
-    }
+    // (per launch: function attributes are per device, and a process may drive several)
+    cudaFuncSetAttribute(cell_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     cell_sort_kernel<<<dim3((unsigned)((bs + SCHUNK - 1) / SCHUNK), h->cfg.D), SORT_T, smem, s>>>(cell, uu, srow, sc, su, G, bs,
                                                                                                   stride);
     h->launches++;

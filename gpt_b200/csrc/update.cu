@@ -17,6 +17,8 @@
 // M = proj(U,G) is formed implicitly; the algebra is the reference's, re-associated (agreement ~1e-15).
 #include <cuda_fp16.h>
 
+#include <atomic>
+
 #include "common.cuh"
 #include "tc_layout.cuh"
 
@@ -1195,15 +1197,19 @@ size_t gptb_update_small_stride(int r) { return SmallLayout(r).total; }
 
 // k_prepare / k_apply / k_reduce_only use up to ~99 KB of dynamic shared memory at r = 64: opt in once.
 static void optin_smem() {
-    static bool done = false;
-    if (done) return;
+    // (function attributes are per device: a process that drives several GPUs opts in on each)
+    static std::atomic<uint64_t> done{0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const uint64_t bit = 1ull << (dev & 63);
+    if (done.load(std::memory_order_acquire) & bit) return;
     cudaFuncSetAttribute(k_prepare, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(k_apply, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(k_reduce_only, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(k_small, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     cudaFuncSetAttribute(k_small2, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024);
     cudaFuncSetAttribute(k_apply2, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-    done = true;
+    done.fetch_or(bit, std::memory_order_release);
 }
 
 // shared-memory expm workspace for the 2r x 2r exponential (0 = does not fit, use the global-memory Pade path)

@@ -28,7 +28,7 @@ import numpy as np
 from . import _lib as L
 
 __all__ = ["feature", "feature2", "samplenz", "pred", "pred_samples", "GPTregression", "GPT_SGLDERMw", "GPT_SGLDERM_RMSprop", "GPT_GMC", "GPTclassification", "logsumexp", "proj", "geod", "geodboth",
-           "datawhitening", "RFFFeatures", "Model", "GptbError", "GeodesicNaN", "shard_range"]
+           "datawhitening", "RFFFeatures", "Model", "ModelGroup", "GptbError", "GeodesicNaN", "shard_range"]
 
 
 class GptbError(RuntimeError):
@@ -173,6 +173,7 @@ class Model:
                        feature_kind=int(feature_kind), device=_default_device if device is None else int(device),
                        reserved=0, seed=int(seed))
         self.cfg = cfg
+        self._group = None          # (handle array, n) when this model leads a ModelGroup
         self.h = L.H()
         st = self.lib.gptb_create(C.byref(cfg), C.byref(self.h))
         if st != L.OK:
@@ -263,8 +264,12 @@ class Model:
         Nt = Xtest.shape[0]
         mean = np.empty(Nt)
         per = np.empty((Nt, S), order="F") if per_sample else None
-        _check(self.lib.gptb_pred_samples(self.h, _dp(w_store), _dp(U_store), S, _dp(Xtest), Nt, _dp(mean), _dp(per)),
-               self.h)
+        if self._group is not None:   # test rows sharded over the group's devices
+            _check(self.lib.gptb_multi_pred_samples(self._group[0], self._group[1], _dp(w_store), _dp(U_store), S, _dp(Xtest), Nt,
+                                                    _dp(mean), _dp(per)), self.h)
+        else:
+            _check(self.lib.gptb_pred_samples(self.h, _dp(w_store), _dp(U_store), S, _dp(Xtest), Nt, _dp(mean), _dp(per)),
+                   self.h)
         return (mean, per) if per_sample else mean
 
     def grad(self, signal_var, idx=None, start=0, bs=None, include_prior=True, want_fhat=True):
@@ -330,9 +335,12 @@ class Model:
         nU = None
         if noise_U is not None:   # [step][n,r,D] with each step's block in Julia (F) order
             nU = np.ascontiguousarray(np.stack([np.asarray(a, dtype=np.float64).ravel(order="F") for a in noise_U]))
-        st = self.lib.gptb_sgld_run(self.h, float(signal_var), int(m), float(epsw), float(epsU), int(burnin),
-                                    int(maxepoch), flags, pp.ctypes.data_as(L.c_int64_p) if pp is not None else None,
-                                    _dp(nw), _dp(nU), _dp(w_store), _dp(U_store))
+        args = (float(signal_var), int(m), float(epsw), float(epsU), int(burnin), int(maxepoch), flags,
+                pp.ctypes.data_as(L.c_int64_p) if pp is not None else None, _dp(nw), _dp(nU), _dp(w_store), _dp(U_store))
+        if self._group is not None:
+            st = self.lib.gptb_multi_sgld_run(self._group[0], self._group[1], *args)
+        else:
+            st = self.lib.gptb_sgld_run(self.h, *args)
         if st == L.GEODESIC_NAN:
             # GPT_SGLD.jl:25, :422-424 — print the warning and hand back all-zero stores
             print("Get NaN when moving along Geodesic. Try smaller epsU")
@@ -344,6 +352,10 @@ class Model:
         """Queue the next nsteps loop bodies (no store, no host sync); call synchronize() to wait.  rmsprop=True: the
         steps of GPT_SGLDERM_RMSprop (epsw is its epsilon)."""
         flags = (L.FLAG_LANGEVIN if langevin else 0) | (L.FLAG_STIEFEL if stiefel else 0) | (L.FLAG_RMSPROP if rmsprop else 0)
+        if self._group is not None:
+            _check(self.lib.gptb_multi_sgld_advance(self._group[0], self._group[1], float(signal_var), int(m), float(epsw),
+                                                    float(epsU), flags, int(nsteps)), self.h)
+            return
         _check(self.lib.gptb_sgld_advance(self.h, float(signal_var), int(m), float(epsw), float(epsU), flags,
                                           int(nsteps)), self.h)
 
@@ -384,10 +396,59 @@ def shard_range(rank: int, nranks: int, bs: int):
     return rank * bs // nranks, (rank + 1) * bs // nranks
 
 
-def _model_for(phi, r, Q, I, precision=None, seed=0, options=None) -> Model:
+class ModelGroup:
+    """Several GPUs driven from THIS process (gptb_comm_init_local / gptb_multi_*): one handle per device, every setter
+    goes to all of them, the samplers and the posterior sweep run on all of them at once (rows of each minibatch, or of
+    the test set, sharded).  Everything else (get_params, pred, ...) is answered by the first handle."""
+
+    _FORWARD = ("set_features", "set_index", "set_train", "set_train_phi", "set_params", "init_params", "set_option",
+                "set_domain", "synchronize")
+
+    def __init__(self, devices, D, n, r, Q, precision=None, feature_kind=L.FEAT_COS, seed=0):
+        self.models = [Model(D, n, r, Q, precision=precision, feature_kind=feature_kind, device=int(d), seed=seed) for d in devices]
+        lead = self.models[0]
+        self.lib, self.cfg, self.h = lead.lib, lead.cfg, lead.h
+        self._arr = (C.c_void_p * len(self.models))(*[m.h.value for m in self.models])
+        harr = C.cast(self._arr, C.POINTER(C.c_void_p))
+        st = self.lib.gptb_comm_init_local(harr, len(self.models))
+        if st != L.OK:
+            self.close()
+            _check(st, None)
+        lead._group = (harr, len(self.models))
+
+    def __getattr__(self, name):
+        if name in ("models", "lib", "cfg", "h", "_arr"):
+            raise AttributeError(name)
+        if name in ModelGroup._FORWARD:
+            def call(*a, **kw):
+                out = None
+                for m in self.models:
+                    out = getattr(m, name)(*a, **kw)
+                return out
+            return call
+        return getattr(self.models[0], name)
+
+    def close(self):
+        for m in getattr(self, "models", []):
+            m._group = None
+            m.close()
+        self.models = []
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+def _model_for(phi, r, Q, I, precision=None, seed=0, options=None, devices=None) -> Model:
     if isinstance(phi, RFFFeatures):
         n, D, _ = phi.shape
-        mdl = Model(D, n, r, Q, precision=precision, feature_kind=phi.kind, seed=seed)
+        if devices is not None and len(devices) > 1:
+            mdl = ModelGroup(devices, D, n, r, Q, precision=precision, feature_kind=phi.kind, seed=seed)
+        else:
+            mdl = Model(D, n, r, Q, precision=precision, feature_kind=phi.kind, seed=seed,
+                        device=None if not devices else int(devices[0]))
         mdl.set_features(phi)
     else:
         n, D, _ = phi.shape
@@ -409,27 +470,28 @@ def pred(w, U, I, phitest, precision: Optional[int] = None, options=None):
 
 
 def pred_samples(w_store, U_store, I, phitest: RFFFeatures, cols: Optional[Sequence[int]] = None,
-                 per_sample=False, precision: Optional[int] = None, options=None):
+                 per_sample=False, precision: Optional[int] = None, options=None, devices=None):
     """kin40kExperiment.jl:75-87 / GPT_SGLD_p.jl:124-132: mean over stored samples of pred(w_s,U_s,I,phitest)."""
     if cols is not None:
         w_store = w_store[:, list(cols)]
         U_store = U_store[:, :, :, list(cols)]
-    with _model_for(phitest, U_store.shape[1], w_store.shape[0], I, precision, options=options) as mdl:
+    with _model_for(phitest, U_store.shape[1], w_store.shape[0], I, precision, options=options, devices=devices) as mdl:
         return mdl.pred_samples(np.asfortranarray(w_store), np.asfortranarray(U_store), phitest.X, per_sample)
 
 
 def GPTregression(phi, y, signal_var, I, r, Q, m, epsw, epsU, burnin, maxepoch, param_seed, langevin=True,
                   stiefel=True, *, precision: Optional[int] = None, w0=None, U0=None, perms=None, noise_w=None,
-                  noise_U=None, options=None):
+                  noise_U=None, options=None, devices=None):
     """GPT_SGLD.jl:345-448.  Returns (w_store[Q,T], U_store[n,r,D,T]), T = maxepoch*ceil(N/m); all zeros (after
     printing the reference's warning) if the geodesic produced NaN.
 
     Keyword-only extras (not in the reference): precision; w0/U0 to start from given parameters instead of the
     param_seed draw; perms / noise_w / noise_U to inject the random draws (parity tests); options = {L.OPT_*: value}
-    passed to gptb_set_option."""
+    passed to gptb_set_option; devices = [0, 1, ...]: several GPUs driven from this process, the rows of every minibatch
+    sharded over them (lazy features only)."""
     y = np.ravel(np.asarray(y, dtype=np.float64))
     N = y.size
-    with _model_for(phi, r, Q, I, precision, seed=int(param_seed), options=options) as mdl:
+    with _model_for(phi, r, Q, I, precision, seed=int(param_seed), options=options, devices=devices) as mdl:
         if isinstance(phi, RFFFeatures):
             mdl.set_train(phi.X, y)
         else:

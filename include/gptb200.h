@@ -251,6 +251,23 @@ int gptb_sgld_advance(gptb_handle *h, double signal_var, int64_t m, double epsw,
  * id is an opaque 128-byte NCCL unique id made by rank 0 and distributed by the host program. */
 int gptb_comm_unique_id(void *id_out_128);
 int gptb_comm_init(gptb_handle *h, int32_t nranks, int32_t rank, const void *id_128);
+
+/* ---- multi-GPU from ONE process (the reference is a single Julia process: SURVEY.md 8b) ---------- */
+/* hs[0..n): handles on n different devices of this process, each with the whole training set, the same parameters,
+ * features, index table and seed.  gptb_comm_init_local makes them ranks 0..n-1 of one communicator
+ * (ncclCommInitAll).  The gptb_multi_* entries then run the per-handle call of the same name on one host thread per
+ * handle (every step contains the gradient all-reduce, which all ranks must enter); the chain is the one-GPU chain
+ * up to summation order, stores come from rank 0.  Per-handle calls that contain no collective (gptb_set_params,
+ * gptb_get_params, gptb_synchronize, gptb_pred*) stay usable on each handle.
+ * gptb_multi_pred_samples shards the TEST ROWS over the handles (no communication; no communicator needed). */
+int gptb_comm_init_local(gptb_handle *const *hs, int32_t n);
+int gptb_multi_sgld_run(gptb_handle *const *hs, int32_t n, double signal_var, int64_t m, double epsw, double epsU,
+                        int32_t burnin, int32_t maxepoch, int32_t flags, const int64_t *perms, const double *noise_w,
+                        const double *noise_U, double *w_store, double *U_store);
+int gptb_multi_sgld_advance(gptb_handle *const *hs, int32_t n, double signal_var, int64_t m, double epsw, double epsU,
+                            int32_t flags, int64_t nsteps);
+int gptb_multi_pred_samples(gptb_handle *const *hs, int32_t n, const double *w_store, const double *U_store, int32_t S,
+                            const double *Xtest, int64_t Nt, double *mean_out, double *per_sample_out);
 int gptb_comm_destroy(gptb_handle *h);
 
 /* ---- full-theta ("no tensor") RFF model: the comparator of the tensor model ----------------------

@@ -136,34 +136,52 @@ end
 function GPTregression(phi::Union{RFFFeatures,Array{Float64,3}}, y::Array, signal_var::Real, I::Array, r::Integer,
                        Q::Integer, m::Integer, epsw::Real, epsU::Real, burnin::Integer, maxepoch::Integer,
                        param_seed::Integer; langevin::Bool = true, stiefel::Bool = true, precision = PREC_TC3,
-                       w0 = nothing, U0 = nothing, perms = nothing, noise_w = nothing, noise_U = nothing)
+                       w0 = nothing, U0 = nothing, perms = nothing, noise_w = nothing, noise_U = nothing,
+                       devices::Vector{Int} = Int[])
+    # devices = [0, 1, ...]: several GPUs driven from this one process (gptb_comm_init_local / gptb_multi_sgld_run); the
+    # rows of every minibatch are sharded over them, the chain is the one-GPU chain up to summation order
     n, D, N = size(phi)
     lazy = phi isa RFFFeatures
-    h = create(D, n, r, Q; precision = lazy ? precision : PREC_FP64, kind = lazy ? phi.kind : FEAT_COS, seed = param_seed)
+    devs = isempty(devices) ? [-1] : devices
+    hs = Ptr{Cvoid}[]
     try
-        check(ccall((:gptb_set_index, LIB), Cint, (Ptr{Cvoid}, Ptr{Int32}), h, Matrix{Int32}(I)), h)
         yv = Vector{Float64}(vec(y))
-        if lazy
-            set_features!(h, phi)
-            check(ccall((:gptb_set_train, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int64), h, phi.X, yv, N), h)
-        else
-            check(ccall((:gptb_set_train_phi, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int64), h, phi, yv, N), h)
+        for d in devs
+            h = create(D, n, r, Q; precision = lazy ? precision : PREC_FP64, kind = lazy ? phi.kind : FEAT_COS, device = d,
+                       seed = param_seed)
+            push!(hs, h)
+            check(ccall((:gptb_set_index, LIB), Cint, (Ptr{Cvoid}, Ptr{Int32}), h, Matrix{Int32}(I)), h)
+            if lazy
+                set_features!(h, phi)
+                check(ccall((:gptb_set_train, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int64), h, phi.X, yv, N), h)
+            else
+                check(ccall((:gptb_set_train_phi, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int64), h, phi, yv, N), h)
+            end
+            if w0 === nothing
+                check(ccall((:gptb_init_params, LIB), Cint, (Ptr{Cvoid}, UInt64, Int32), h, param_seed, stiefel ? 1 : 0), h)   # :357-369
+            else
+                check(ccall((:gptb_set_params, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}), h, w0, U0), h)
+            end
         end
-        if w0 === nothing
-            check(ccall((:gptb_init_params, LIB), Cint, (Ptr{Cvoid}, UInt64, Int32), h, param_seed, stiefel ? 1 : 0), h)   # :357-369
-        else
-            check(ccall((:gptb_set_params, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}), h, w0, U0), h)
-        end
+        h = hs[1]
         numbatches = cld(N, m)                                     # :353
         T = maxepoch * numbatches
         w_store = zeros(Q, T); U_store = zeros(n, r, D, T)         # :358-359
         flags = (langevin ? FLAG_LANGEVIN : Cint(0)) | (stiefel ? FLAG_STIEFEL : Cint(0))
         p(x) = x === nothing ? Ptr{Float64}(C_NULL) : pointer(x)
         pp = perms === nothing ? Ptr{Int64}(C_NULL) : pointer(perms)   # (burnin+maxepoch) x N, 0-based, row-major per epoch
-        st = ccall((:gptb_sgld_run, LIB), Cint,
-                   (Ptr{Cvoid}, Float64, Int64, Float64, Float64, Int32, Int32, Int32, Ptr{Int64}, Ptr{Float64}, Ptr{Float64},
-                    Ptr{Float64}, Ptr{Float64}),
-                   h, signal_var, m, epsw, epsU, burnin, maxepoch, flags, pp, p(noise_w), p(noise_U), w_store, U_store)
+        if length(hs) > 1
+            check(ccall((:gptb_comm_init_local, LIB), Cint, (Ptr{Ptr{Cvoid}}, Int32), hs, length(hs)), h)
+            st = ccall((:gptb_multi_sgld_run, LIB), Cint,
+                       (Ptr{Ptr{Cvoid}}, Int32, Float64, Int64, Float64, Float64, Int32, Int32, Int32, Ptr{Int64}, Ptr{Float64},
+                        Ptr{Float64}, Ptr{Float64}, Ptr{Float64}),
+                       hs, length(hs), signal_var, m, epsw, epsU, burnin, maxepoch, flags, pp, p(noise_w), p(noise_U), w_store, U_store)
+        else
+            st = ccall((:gptb_sgld_run, LIB), Cint,
+                       (Ptr{Cvoid}, Float64, Int64, Float64, Float64, Int32, Int32, Int32, Ptr{Int64}, Ptr{Float64}, Ptr{Float64},
+                        Ptr{Float64}, Ptr{Float64}),
+                       h, signal_var, m, epsw, epsU, burnin, maxepoch, flags, pp, p(noise_w), p(noise_U), w_store, U_store)
+        end
         if st == GPTB_GEODESIC_NAN
             println("Get NaN when moving along Geodesic. Try smaller epsU")    # :25
             return w_store, U_store                                            # zero-filled, :422-424
@@ -171,7 +189,7 @@ function GPTregression(phi::Union{RFFFeatures,Array{Float64,3}}, y::Array, signa
         check(st, h)
         return w_store, U_store
     finally
-        destroy(h)
+        for h in hs; destroy(h); end
     end
 end
 
