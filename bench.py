@@ -231,7 +231,7 @@ def workload_config(args, W):
             "precision": args.precision, "langevin": True, "stiefel": True,
             "signal_var": SIGNAL_VAR, "epsw": eps_for(W["N"])[0], "epsU": eps_for(W["N"])[1],
             "l2": "inputs larger than L2: resident X is %.0f MB and every step gathers different random rows" % (W["N"] * W["D"] * 8 / 1e6),
-            "algorithm": args.alg,
+            "algorithm": args.alg, "options": list(getattr(args, "opt", [])),
             "parallelism": f"minibatch rows sharded x{args.gpus}; NCCL all-reduce of the FP32 gradient buffer "
                            f"(32*ceil32(Q) + D*npad*rpad floats) once per step; replicated FP64 update"}
 
@@ -247,6 +247,8 @@ def main():
     ap.add_argument("--no-pred", action="store_true", help="skip the C5 prediction sweep")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline")
     ap.add_argument("--pred-samples", type=int, default=C5["S"])
+    ap.add_argument("--opt", action="append", default=[], metavar="ID=VALUE",
+                    help="gptb_set_option(ID, VALUE) on the benchmarked handle (experiments; the line records it)")
     ap.add_argument("--replicas", type=int, default=1,
                     help="R > 1: R independent chains (handles with their own streams and seeds, one host thread each) on "
                          "one GPU; prints their aggregate steps/s instead of the single-chain line (small workloads)")
@@ -301,6 +303,9 @@ def main():
     model.set_train(X, y)
     model.set_params(mdl["w0"], mdl["U0"])
     model.set_option(L.OPT_ALGORITHM, {"auto": L.ALG_AUTO, "direct": L.ALG_DIRECT, "nodes": L.ALG_NODES}[args.alg])
+    for kv in args.opt:
+        k_, v_ = kv.split("=")
+        model.set_option(int(k_), float(v_))
     if world > 1:
         idt = torch.zeros(128, dtype=torch.uint8, device=dev)
         if rank == 0:

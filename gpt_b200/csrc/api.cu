@@ -412,23 +412,33 @@ static int pipe_init(gptb_handle *h, int G) {
 static int pipe_tail_init(gptb_handle *h) {
     if (h->tail_stream) return GPTB_OK;
     GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&h->evTail, cudaEventDisableTiming));
+    GPTB_CUDA_OK(h, cudaEventCreateWithFlags(&h->evTailFork, cudaEventDisableTiming));
     GPTB_CUDA_OK(h, cudaStreamCreateWithFlags(&h->tail_stream, cudaStreamNonBlocking));
     return GPTB_OK;
 }
 
 // Order the main stream after everything the pipeline still has in flight.  Every entry point that reads or
 // writes parameters outside the step itself calls this first.
-int pipe_join(gptb_handle *h) {
+static int pipe_join_groups(gptb_handle *h) {
     for (int g = 0; g < gptb_handle::PIPE_MAX; ++g)
         if (h->pendU[g]) {
             GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->evU[g], 0));
             h->pendU[g] = false;
         }
+    return GPTB_OK;
+}
+// The read-backs of the previous step (tail stream) only have to finish before the parameters change again: the
+// one-stream step waits for them right before its update, not at its start.
+static int pipe_join_tail(gptb_handle *h) {
     if (h->tail_pending) {
         GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->evTail, 0));
         h->tail_pending = false;
     }
     return GPTB_OK;
+}
+int pipe_join(gptb_handle *h) {
+    GPTB_TRY(pipe_join_groups(h));
+    return pipe_join_tail(h);
 }
 
 // Stream for work that must follow the whole step (copies of the updated parameters, the NaN flag) without
@@ -436,11 +446,15 @@ int pipe_join(gptb_handle *h) {
 static int pipe_tail_begin(gptb_handle *h, cudaStream_t *out) {
     bool any = false;
     for (int g = 0; g < gptb_handle::PIPE_MAX; ++g) any = any || h->pendU[g];
+    GPTB_TRY(pipe_tail_init(h));
     if (!any) {
-        *out = h->stream;
+        // one-stream step: the tail forks off the main stream here, so that two small device-to-host copies (~25 us with
+        // their latencies) do not sit between this step's update and the next step's first kernel
+        GPTB_CUDA_OK(h, cudaEventRecord(h->evTailFork, h->stream));
+        GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->tail_stream, h->evTailFork, 0));
+        *out = h->tail_stream;
         return GPTB_OK;
     }
-    GPTB_TRY(pipe_tail_init(h));
     for (int g = 0; g < gptb_handle::PIPE_MAX; ++g)
         if (h->pendU[g]) GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->tail_stream, h->evU[g], 0));
     *out = h->tail_stream;
@@ -749,6 +763,7 @@ int gptb_destroy(gptb_handle *h) {
     if (h->tail_stream) {
         cudaStreamSynchronize(h->tail_stream); cudaStreamDestroy(h->tail_stream);
         cudaEventDestroy(h->evTail);
+        cudaEventDestroy(h->evTailFork);
     }
     gptb_comm_destroy(h);
     gptb_nodes_free(h);
@@ -1455,7 +1470,8 @@ static int step_common(gptb_handle *h, double signal_var, const int32_t *rows, i
     }
     if (pipe_usable(h, bs, staged, flags))
         return step_pipelined(h, signal_var, rows, bs, N_total, staged, Xstage, ystage, epsw, epsU, flags, nw_dev, nU_dev);
-    GPTB_TRY(pipe_join(h));
+    GPTB_TRY(pipe_join_groups(h));
+    if (rms) GPTB_TRY(pipe_join_tail(h));   // (the RMSprop step moves w in the middle of its gradient pass)
     PhaseTimer pt(h);
     // production-mode draws of this step: generated on a side stream under the gradient kernels (they depend on the
     // step counter only; the previous step's update, earlier on the main stream, has consumed the buffer)
@@ -1472,6 +1488,7 @@ static int step_common(gptb_handle *h, double signal_var, const int32_t *rows, i
     GPTB_TRY(compute_grad(h, signal_var, rows, bs, N_total, staged, Xstage, ystage, pt, fix_U));
     if (side_noise) GPTB_CUDA_OK(h, cudaStreamWaitEvent(h->stream, h->evR[0], 0));
     if (rms) GPTB_TRY(gptb_launch_rms_U(h, h->stream));     // gU, per-dimension step sizes (:1210-1212); w has moved already
+    GPTB_TRY(pipe_join_tail(h));                            // the previous step's read-backs of w / U are done
     GPTB_TRY(gptb_launch_update_range(h, epsw, epsU, flags, nw_dev, nU_dev, h->step_counter, 0, kn_upd, !rms, h->stream,
                                       side_noise));
     pt.done(GPTB_PHASE_UPDATE);

@@ -192,7 +192,7 @@ struct gptb_handle {
     cudaStream_t side[PIPE_MAX] = {nullptr, nullptr, nullptr, nullptr};
     cudaStream_t tail_stream = nullptr, ar_stream = nullptr;
     cudaEvent_t evG[PIPE_MAX] = {}, evU[PIPE_MAX] = {}, evR[PIPE_MAX] = {};
-    cudaEvent_t evTail = nullptr;
+    cudaEvent_t evTail = nullptr, evTailFork = nullptr;
     bool pendU[PIPE_MAX] = {false, false, false, false};
     bool tail_pending = false;
     int sm_reserve = 0;                // SMs the persistent K1 / K3 grids leave to the concurrent group update
