@@ -691,18 +691,24 @@ struct ContractFwd3Params {
     double mean_scale;
     int64_t nrows, t2_stride, fh_stride;
     int DP, r, Q, ns, SL, sl_shift;
+    int wpt;                 // warps per tile (1..4)
 };
 
 template <int DT>
-__global__ void __launch_bounds__(512) contract_fwd3_kernel(const ContractFwd3Params p) {
+__global__ void __launch_bounds__(1024) contract_fwd3_kernel(const ContractFwd3Params p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr int D = DT;
     constexpr int DP4 = (DT + 3) / 4;
     const int r = p.r, Q = p.Q, SL = p.SL, DR = D * r;
-    const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5, nw = blockDim.x >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    // wpt warps share a tile: each copies its part of it and takes its part of the q, the partial sums meet in shared
+    // memory.  (Shared memory holds 9 tiles at BASELINE config 5; one warp per tile left the LSU at 63 % with 13 %
+    // occupancy: 116 ms; two warps per tile 106 ms.)
+    const int wpt = p.wpt, pr = wp / wpt, half = wp - pr * wpt, npair = (blockDim.x >> 5) / wpt;
     int4 *offs = reinterpret_cast<int4 *>(smem_raw);                      // [Q][DP4] byte offsets of the (k,l) lines
     float *ws = reinterpret_cast<float *>(offs + (size_t)Q * DP4);        // [Q][SL]
-    float *tiles = ws + (((size_t)Q * SL + 31) & ~(size_t)31);            // [nw][DR][32]
+    float *fx = ws + (((size_t)Q * SL + 31) & ~(size_t)31);               // [npair][3][32] partial sums of the other warps
+    float *tiles = fx + (size_t)npair * 96;                               // [npair][DR][32]
     for (int t = tid; t < Q * DP4; t += blockDim.x) {
         int4 v = __ldg(reinterpret_cast<const int4 *>(p.off1) + t);
         v.x <<= 2; v.y <<= 2; v.z <<= 2; v.w <<= 2;
@@ -713,21 +719,24 @@ __global__ void __launch_bounds__(512) contract_fwd3_kernel(const ContractFwd3Pa
         ws[t] = sidx < p.ns ? (float)p.w[(size_t)sidx * Q + q] : 0.f;
     }
     __syncthreads();
-    const int rpw = 32 >> p.sl_shift;                     // rows per warp and iteration
+    const int rpw = 32 >> p.sl_shift;                     // rows per tile
     const int sidx = lane & (SL - 1), rsub = lane >> p.sl_shift;
     const int64_t ngrp = (p.nrows + rpw - 1) / rpw;
     const float *wl = ws + sidx;
-    float *tile = tiles + (size_t)wp * DR * 32;
+    float *tile = tiles + (size_t)pr * DR * 32;
     const char *tb = reinterpret_cast<const char *>(tile + lane);
     const uint32_t tile_s = tcx::smem_u32(tile);
-    // this lane's 16-byte pieces of the copy: piece (kl, within) with kl = it*4 + lane/8, within = lane%8 -> lanes
-    // 4*within .. 4*within+3 of line kl, i.e. row (4*within) >> sl_shift, samples (4*within) & (SL-1) ..
+    // this lane's 16-byte pieces of the copy: piece (kl, within) with kl = it*8 + 4*half + lane/8, within = lane%8 ->
+    // lanes 4*within .. 4*within+3 of line kl, i.e. row (4*within) >> sl_shift, samples (4*within) & (SL-1) ..
     const int within = lane & 7, c_rsub = (4 * within) >> p.sl_shift, c_s = (4 * within) & (SL - 1);
-    for (int64_t gi = (int64_t)blockIdx.x * nw + wp; gi < ngrp; gi += (int64_t)gridDim.x * nw) {
+    const int qh = ((Q + wpt - 1) / wpt + 1) & ~1;        // warp j of the tile: q in [j*qh, (j+1)*qh)
+    const int q_lo = min(half * qh, Q), q_hi = min(q_lo + qh, Q);
+    const int bar_id = 1 + pr, bar_n = 32 * wpt;
+    for (int64_t gi = (int64_t)blockIdx.x * npair + pr; gi < ngrp; gi += (int64_t)gridDim.x * npair) {
         const int64_t row0 = gi * rpw;
         {
             const int64_t crow = min(row0 + c_rsub, p.nrows - 1);         // rows past the end: a valid row, never stored
-            for (int kl = lane >> 3; kl < DR; kl += 4) {
+            for (int kl = (lane >> 3) + 4 * half; kl < DR; kl += 4 * wpt) {
                 const int k = kl / r, l = kl - k * r;
                 const float *src = p.T2 + (((size_t)k * p.t2_stride + crow) * r + l) * SL + c_s;
                 asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tile_s + (uint32_t)(kl * 32 + 4 * within) * 4u), "l"(src)
@@ -735,11 +744,11 @@ __global__ void __launch_bounds__(512) contract_fwd3_kernel(const ContractFwd3Pa
             }
             asm volatile("cp.async.commit_group;" ::: "memory");
             asm volatile("cp.async.wait_group 0;" ::: "memory");
-            __syncwarp();
+            asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(bar_n) : "memory");   // every part of the tile has landed
         }
         float f0 = 0.f, f1 = 0.f;
-        int q = 0;
-        for (; q + 1 < Q; q += 2) {                       // two independent product chains
+        int q = q_lo;
+        for (; q + 1 < q_hi; q += 2) {                    // two independent product chains
             const int4 *o0 = offs + (size_t)q * DP4, *o1 = o0 + DP4;
             float v0 = 1.f, v1 = 1.f;
 #pragma unroll
@@ -753,7 +762,7 @@ __global__ void __launch_bounds__(512) contract_fwd3_kernel(const ContractFwd3Pa
             f0 = fmaf(wl[(size_t)q * SL], v0, f0);
             f1 = fmaf(wl[(size_t)(q + 1) * SL], v1, f1);
         }
-        if (q < Q) {
+        if (q < q_hi) {
             const int4 *o0 = offs + (size_t)q * DP4;
             float v0 = 1.f;
 #pragma unroll
@@ -766,8 +775,11 @@ __global__ void __launch_bounds__(512) contract_fwd3_kernel(const ContractFwd3Pa
             }
             f0 = fmaf(wl[(size_t)q * SL], v0, f0);
         }
-        __syncwarp();                                     // every lane is done with the tile before the next copy
-        const float f = f0 + f1;
+        float f = f0 + f1;
+        if (half) fx[(pr * 3 + half - 1) * 32 + lane] = f;
+        asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(bar_n) : "memory");   // partial sums written; all warps are done with the tile
+        if (half) continue;
+        for (int j = 1; j < wpt; ++j) f += fx[(pr * 3 + j - 1) * 32 + lane];
         const int64_t row = row0 + rsub;
         const bool out = row < p.nrows && sidx < p.ns;
         if (p.fh && out) p.fh[(size_t)sidx * p.fh_stride + row] = (double)f;
@@ -817,16 +829,20 @@ int gptb_launch_contract_fwd3(gptb_handle *h, const float *T2, const double *w_g
                               cudaStream_t s) {
     const gptb_config &c = h->cfg;
     if (!h->ct_off1 || (SL != 8 && SL != 16 && SL != 32) || ns > SL) return GPTB_ERR_UNSUPPORTED;
-    const size_t tables = (size_t)c.Q * ((c.D + 3) / 4) * 16 + (((size_t)c.Q * SL + 31) & ~(size_t)31) * sizeof(float);
+    const size_t tables = (size_t)c.Q * ((c.D + 3) / 4) * 16 + (((size_t)c.Q * SL + 31) & ~(size_t)31) * sizeof(float) +
+                          15 * 96 * sizeof(float);
     const size_t tile = (size_t)c.D * c.r * 32 * sizeof(float);
     if (tables + tile > 227 * 1024) return GPTB_ERR_UNSUPPORTED;
-    int nwarps = (int)std::min<size_t>(16, (227 * 1024 - tables) / tile);
-    if (h->pred_warps > 0) nwarps = std::min(nwarps, h->pred_warps);
-    const size_t smem = tables + (size_t)nwarps * tile;
+    int npair = (int)std::min<size_t>(15, (227 * 1024 - tables) / tile);     // tiles (15 named barriers beside barrier 0)
+    int wpt = h->pred_warps > 0 ? std::min(h->pred_warps, 4) : 2;             // warps per tile (GPTB_OPT_PRED_WARPS; measured 1: 116 ms, 2: 106, 3: 109, 4: 112 at C5)
+    while (wpt > 1 && npair * wpt > 32) --wpt;
+    const int nwarps = wpt * npair;
+    const size_t smem = tables + (size_t)npair * tile;
     ContractFwd3Params p;
     p.T2 = T2; p.w = w_group; p.off1 = h->ct_off1; p.fh = fh; p.mean_acc = mean_acc; p.mean_scale = mean_scale;
     p.nrows = nrows; p.t2_stride = t2_stride; p.fh_stride = fh_stride;
     p.DP = (c.D + 3) & ~3; p.r = c.r; p.Q = c.Q; p.ns = ns; p.SL = SL; p.sl_shift = SL == 8 ? 3 : (SL == 16 ? 4 : 5);
+    p.wpt = wpt;
     const dim3 grid((unsigned)h->sm_count);
 #define GPTB_CONTRACT_CASE(DT)                                                                              \
     case DT: {                                                                                              \

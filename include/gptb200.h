@@ -334,7 +334,7 @@ enum gptb_option {
     GPTB_OPT_RMS_LAMBDA = 6,    /* its smoothing constant (`lambda` of :1146), default 1e-5                                */
     GPTB_OPT_PRED_CHUNK_MB = 7, /* MB of interpolated values the posterior sweep holds at a time (default 4096, capped at 1/8 of the free memory) */
     GPTB_OPT_PRED_LAYOUT = 9,   /* posterior sweep on the node grid: 0 (default) samples on the lanes, 1 row tiles per sample   */
-    GPTB_OPT_PRED_WARPS = 10,   /* warps per CTA of the lanes contraction (0 = chosen from the row size; tuning knob)         */
+    GPTB_OPT_PRED_WARPS = 10,   /* warps per tile of the lanes contraction (1..4, 0 = default 2; tuning knob)                  */
     GPTB_OPT_FRONT_PREFETCH = 8 /* 1 (default): gather and cell sort of a node-grid step run on a side stream under the
                                    previous step's tail; 0: everything on the handle's stream                              */
 };
