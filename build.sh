@@ -9,7 +9,7 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -ccbin /usr/bin/g++ $EXTRA_NVCC_FLAGS"
 OBJS=""
 pids=""
-for f in api batch classify comm contract contract_tc fp64_path fulltheta gmc multi nodes pred_nodes tc_path update; do
+for f in api batch classify comm contract contract_tc fp64_path fulltheta gmc multi nodes pred_nodes tc_path tgp update; do
   $NVCC $FLAGS -c gpt_b200/csrc/$f.cu -o "$OUT/$f.o" &
   pids="$pids $!"
   OBJS="$OBJS $OUT/$f.o"

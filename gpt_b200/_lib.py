@@ -57,6 +57,7 @@ PROTOTYPES = {
     "gptb_geodboth": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, c_double_p, c_double_p, C.c_double, c_double_p, c_double_p]),
     "gptb_gmc_run": (C.c_int, [H, C.c_double, C.c_double, C.c_double, C.c_int32, C.c_int32, C.c_int32, C.c_int32, c_double_p,
                                c_double_p, c_double_p, c_double_p, c_double_p, c_double_p]),
+    "gptb_tgp_gibbs": (C.c_int, [H, C.c_double, C.c_int32, C.c_int32, c_double_p, c_double_p, c_double_p, c_double_p]),
     "gptb_classify_run": (C.c_int, [C.POINTER(H), C.c_int32, c_int32_p, C.c_int64, C.c_double, C.c_double, C.c_int32, C.c_int32,
                                     C.c_int32, c_int64_p, c_double_p, c_double_p, c_double_p, c_double_p]),
     "gptb_sgld_step": (C.c_int, [H, C.c_double, c_int64_p, C.c_int64, C.c_int64, C.c_double, C.c_double, C.c_int32,

@@ -27,7 +27,7 @@ import numpy as np
 
 from . import _lib as L
 
-__all__ = ["feature", "feature2", "samplenz", "pred", "pred_samples", "GPTregression", "GPT_SGLDERMw", "GPT_SGLDERM_RMSprop", "GPT_GMC", "GPTclassification", "logsumexp", "proj", "geod", "geodboth",
+__all__ = ["feature", "feature2", "samplenz", "pred", "pred_samples", "GPTregression", "GPT_SGLDERMw", "GPT_SGLDERM_RMSprop", "GPT_GMC", "GPTclassification", "GPT_inf", "logsumexp", "proj", "geod", "geodboth",
            "datawhitening", "RFFFeatures", "Model", "ModelGroup", "GptbError", "GeodesicNaN", "shard_range"]
 
 
@@ -612,6 +612,36 @@ def GPT_GMC(phi, y, signal_var, I, r, Q, epsw, epsU, burnin, maxepoch, L_, param
             return w_store, U_store, acc
         _check(st, mdl.h)
         return w_store, U_store, acc
+
+
+def GPT_inf(X, y, sigma, n, r, sigmaRBF, q, generator, num_iterations, burnin, *, Z=None, b01=None, I=None, U0=None,
+            noise_w=None, noise_U=None, whiten=True):
+    """TGP.jl:37-86: Gibbs sampler of the tensor model with Gaussian factors.  Returns (W_array[q,T], V_array[n,r,D,T], I)
+    like the reference (T = num_iterations - burnin; I 1-based).  X and y are whitened first (:39-40) unless whiten=False.
+    The reference draws Z, b (feature :6-14), I (:57) and the initial factors (:56) from Julia's global RNG seeded with
+    `generator`; here a NumPy generator seeded with it does, unless Z (n x D), b01 (n x D in [0,1)), I (q x D, 1-based),
+    U0 (n x r x D) are given.  noise_w[m][q] / noise_U[m][D][n*r] inject the draws of :66 / :83."""
+    X = np.array(X, dtype=np.float64, order="F", copy=True)
+    y = np.array(y, dtype=np.float64, copy=True).reshape(-1)
+    if whiten:
+        X = datawhitening(X)
+        y = datawhitening(y.reshape(-1, 1)).ravel()
+    N, D = X.shape
+    rng = np.random.default_rng(int(generator))
+    Z = rng.standard_normal((n, D)) if Z is None else np.asarray(Z, dtype=np.float64)
+    b01 = rng.random((n, D)) if b01 is None else np.asarray(b01, dtype=np.float64)
+    I = (rng.integers(1, r + 1, size=(q, D)).astype(np.int32) if I is None else np.asarray(I, dtype=np.int32))
+    U0 = np.sqrt(1.0 / r) * rng.standard_normal((n, r, D)) if U0 is None else np.asarray(U0, dtype=np.float64)
+    f = tgp_feature(X, n, sigmaRBF, Z, b01)
+    T = int(num_iterations) - int(burnin)
+    W = np.zeros((q, T), order="F"); V = np.zeros((n, r, D, T), order="F")
+    nw = None if noise_w is None else np.ascontiguousarray(np.asarray(noise_w, dtype=np.float64).reshape(num_iterations, q))
+    nU = None if noise_U is None else np.ascontiguousarray(np.asarray(noise_U, dtype=np.float64).reshape(num_iterations, D, n * r))
+    with Model(D, n, r, q, precision=L.PREC_FP64, feature_kind=f.kind, seed=int(generator)) as mdl:
+        mdl.set_features(f); mdl.set_index(np.asfortranarray(I)); mdl.set_train(X, y)
+        mdl.set_params(np.zeros(q), U0)
+        _check(mdl.lib.gptb_tgp_gibbs(mdl.h, float(sigma), int(num_iterations), int(burnin), _dp(nw), _dp(nU), _dp(W), _dp(V)), mdl.h)
+    return W, V, I
 
 
 def logsumexp(x):

@@ -218,6 +218,19 @@ int gptb_gmc_run(gptb_handle *h, double signal_var, double epsw, double epsU, in
                  int32_t restore_U_on_reject, const double *noise_p, const double *noise_mom, const double *unif,
                  double *w_store, double *U_store, double *accept_prob);
 
+/* GPT_inf (TGP.jl:37-86): Gibbs sampler of the tensor model with Gaussian factors.  The handle holds the features
+ * (TGP.feature :6-14: gptb_set_features with length_scale = sigmaRBF, sigma_RBF = phi_scale = 1, b = 2 pi rand), the
+ * index table, the whitened training set and the initial factors (gptb_set_params; w is ignored) — and ends at the
+ * last draw.  Per iteration: w from its q x q Gaussian conditional (:62-66), then every U^(k) from its n*r x n*r
+ * conditional (:73-84), sigma_u = sqrt(1/r), sigma_w = sqrt(r^D/q) (:54-55).  FP64 throughout; the row-proportional
+ * work (T, V, the Gram matrices V V' and Ck Ck') runs on the device, the two small Cholesky solves on the host.
+ *   noise_w[num_iterations][Q], noise_U[num_iterations][D][n*r]: the randn of :66 and :83, or NULL (Philox);
+ *   W_array[Q, num_iterations-burnin], V_array[n,r,D,num_iterations-burnin] (Julia order; either may be NULL): the w of
+ *   iteration m and the factors it was drawn with (:68-71).
+ * As in the reference the factor draw is invSigma_U \ randn (:83), not a draw with covariance invSigma_U^-1. */
+int gptb_tgp_gibbs(gptb_handle *h, double sigma, int32_t num_iterations, int32_t burnin, const double *noise_w,
+                   const double *noise_U, double *W_array, double *V_array);
+
 /* GPTclassification (GPT_SGLD.jl:452-680): C independent parameter sets (w_c, U_c) under a softmax likelihood.
  * hc[0..C): one handle per class, all on one device and one rank, with the same shape, features, core index table and
  * training inputs (gptb_set_train; the handles' y is not read) and their own parameters (gptb_init_params with

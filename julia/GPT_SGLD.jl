@@ -19,7 +19,7 @@
 module GPT_SGLD
 
 export datawhitening, feature, feature2, samplenz, pred, GPTregression, proj, geod, RFFFeatures,
-       featureNotensor, GPNT_SGLD, NTFeatures, GPT_SGLDERMw, GPT_SGLDERM_RMSprop, GPT_GMC, GPTclassification, logsumexp, geodboth,
+       featureNotensor, GPNT_SGLD, NTFeatures, GPT_SGLDERMw, GPT_SGLDERM_RMSprop, GPT_GMC, GPTclassification, GPT_inf, logsumexp, geodboth,
        Model, pred_samples, posterior_mean, gradients, sgld_step!, sgld_advance!, synchronize, get_params, set_params!,
        set_option!, set_domain!, comm_unique_id, comm_init!
 
@@ -506,6 +506,35 @@ function GPTclassification(phi::Union{RFFFeatures,Array{Float64,3}}, y::Array, I
         return w_store, U_store
     finally
         for h in hs; destroy(h); end
+    end
+end
+
+# TGP.jl:37-86  GPT_inf(X,y,sigma,n,r,sigmaRBF,q,generator,num_iterations,burnin): Gibbs sampler of the tensor model with
+# Gaussian factors.  Z, b (TGP.feature :6-14: the same draw for every row), I (:57) and the initial factors (:56) come
+# from Julia's RNG seeded with `generator`; the row-proportional work runs on the device (gptb_tgp_gibbs), FP64.
+function GPT_inf(X::Matrix{Float64}, y::Vector{Float64}, sigma::Real, n::Integer, r::Integer, sigmaRBF::Real, q::Integer,
+                 generator::Integer, num_iterations::Integer, burnin::Integer)
+    X = datawhitening(copy(X)); yw = vec(datawhitening(reshape(copy(y), :, 1)))            # :39-40
+    N, D = size(X)
+    Random.seed!(generator)
+    Z = randn(n, D); b = rand(n, D)
+    f = RFFFeatures(X, [Float64(sigmaRBF)], 1.0, 1.0, Z, 2pi .* b, FEAT_COS)
+    U0 = sqrt(1 / r) .* randn(n, r, D)                                                    # :54, :56
+    I = Matrix{Int32}(rand(1:r, q, D))                                                    # :57
+    h = create(D, n, r, q; precision = PREC_FP64, kind = FEAT_COS, seed = generator)
+    try
+        check(ccall((:gptb_set_index, LIB), Cint, (Ptr{Cvoid}, Ptr{Int32}), h, I), h)
+        set_features!(h, f)
+        check(ccall((:gptb_set_train, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int64), h, X, yw, N), h)
+        check(ccall((:gptb_set_params, LIB), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}), h, zeros(q), U0), h)
+        T = num_iterations - burnin
+        W_array = zeros(q, T); V_array = zeros(n, r, D, T)                                # :45-46
+        check(ccall((:gptb_tgp_gibbs, LIB), Cint,
+                    (Ptr{Cvoid}, Float64, Int32, Int32, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}),
+                    h, sigma, num_iterations, burnin, C_NULL, C_NULL, W_array, V_array), h)
+        return W_array, V_array, I
+    finally
+        destroy(h)
     end
 end
 

@@ -687,3 +687,56 @@ def GPTclassification(phi, y, I, r, Q, m, epsw, epsU, burnin, maxepoch, w0, U0, 
                 U_store[:, :, :, :, col] = U
             step += 1
     return w_store, U_store
+
+
+# ------------------------------------------------------------------------------------------------
+# Gibbs sampler of TGP.jl (last row).  Pinning: **parity unpinned** — the reference holds no fixture
+# or known-answer test for GPT_inf; the restatement follows TGP.jl:37-86 line by line, and its conditional means are
+# checked against the normal equations they solve (tests/test_oracle_golden.py).
+# ------------------------------------------------------------------------------------------------
+def tgp_gibbs(b, y, sigma, r, I, U0, num_iterations, burnin, noise_w, noise_U):
+    """TGP.jl:37-86 (GPT_inf) with the random draws made explicit.
+
+    b[n,D,N]: features (TGP.feature, :6-14) of the whitened inputs; y[N] whitened targets; I[q,D] 0-based (:57);
+    U0[n,r,D] replaces sigma_u*randn(n,r) (:56); noise_w[m][q] and noise_U[m][D][n*r] replace the randn of :66 and :83.
+    Returns (W_array[q, T], V_array[n,r,D,T]), T = num_iterations-burnin: W of iteration m and the factors it was drawn
+    with (:68-71 store before the factors move).
+    Quirks kept: the factor draw is invSigma_U \\ randn (covariance invSigma_U^-2, :83), where the w draw uses the
+    Cholesky factor (:66); rows of C for values of l that no I[:,k] takes are uninitialised in the reference (:76-79) and
+    zero here."""
+    b = np.asarray(b, dtype=np.float64)
+    y = np.asarray(y, dtype=np.float64)
+    n, D, N = b.shape
+    q = I.shape[0]
+    sigma_u = np.sqrt(1.0 / r)                                             # :54
+    sigma_w = np.sqrt(float(r) ** D / q)                                   # :55
+    U = np.array(U0, dtype=np.float64)
+    T = num_iterations - burnin
+    W_array = np.zeros((q, T))
+    V_array = np.zeros((n, r, D, T))
+    for m in range(1, num_iterations + 1):
+        t = np.einsum("jlk,jki->kli", U, b)                                # t[k,l,i] = U_k[:,l]' b[:,k,i]
+        V = np.ones((q, N))
+        for k in range(D):
+            V *= t[k, I[:, k], :]                                          # :62
+        invSigma_w = V @ V.T / sigma ** 2 + np.eye(q) / sigma_w ** 2       # :64
+        Mu_w = np.linalg.solve(invSigma_w, V @ y / sigma ** 2)             # :65
+        R = np.linalg.cholesky(invSigma_w).T                               # chol(.,:U): invSigma_w = R'R
+        W = np.linalg.solve(R, noise_w[m - 1]) + Mu_w                      # :66
+        if m > burnin:
+            W_array[:, m - burnin - 1] = W                                 # :69
+            V_array[:, :, :, m - burnin - 1] = U                           # :70
+        for k in range(D):
+            tk = np.einsum("jl,ji->li", U[:, :, k], b[:, k, :])
+            V_k = V / tk[I[:, k], :]                                       # :74
+            V_kk = W[:, None] * V_k                                        # :75
+            C = np.zeros((r, N))
+            for l in np.unique(I[:, k]):
+                C[l, :] = V_kk[I[:, k] == l, :].sum(axis=0)                # :77-79
+            Ck = np.repeat(C, n, axis=0) * np.tile(b[:, k, :], (r, 1))     # :80: row l*n + j = C[l,:] .* b[j,k,:]
+            invSigma_U = Ck @ Ck.T / sigma ** 2 + np.eye(n * r) / sigma_u ** 2          # :81
+            Mu_U = np.linalg.solve(invSigma_U, Ck @ y / sigma ** 2)        # :82
+            U[:, :, k] = (np.linalg.solve(invSigma_U, noise_U[m - 1][k]) + Mu_U).reshape(n, r, order="F")   # :83
+            tk = np.einsum("jl,ji->li", U[:, :, k], b[:, k, :])
+            V = V_k * tk[I[:, k], :]                                       # :84
+    return W_array, V_array

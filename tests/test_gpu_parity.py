@@ -829,3 +829,24 @@ def test_nodes_front_prefetch_same_chain():
             out[pre] = (ws, Us, wa, Ua, wb, Ub)
     for a, b in zip(out[1], out[0]):
         assert np.isfinite(a).all() and relerr(a, b) < 1e-6
+
+
+def test_tgp_gibbs_vs_oracle():
+    """GPT_inf (TGP.jl:37-86) through gptb_tgp_gibbs with injected draws: W_array, V_array against the oracle, burn-in
+    and store layout; Philox mode stays finite."""
+    rng = np.random.default_rng(3)
+    n, D, N, r, q, M, burnin = 12, 3, 300, 4, 20, 5, 2
+    X = rng.standard_normal((N, D)); y = rng.standard_normal(N)
+    Z = rng.standard_normal((n, D)); b01 = rng.random((n, D))
+    I = rng.integers(1, r + 1, (q, D)).astype(np.int32)
+    U0 = np.sqrt(1 / r) * rng.standard_normal((n, r, D))
+    NW = rng.standard_normal((M, q)); NU = rng.standard_normal((M, D, n * r))
+    sigma, sigmaRBF = 0.3, 1.4
+    Xw = G.datawhitening(np.array(X, order="F")); yw = G.datawhitening(y.reshape(-1, 1).copy()).ravel()
+    b = np.stack([o.tgp_feature(Xw[i], Z / sigmaRBF, b01) for i in range(N)], axis=2)
+    Wr, Vr = o.tgp_gibbs(b, yw, sigma, r, I - 1, U0, M, burnin, NW, NU)
+    W, V, Iout = G.GPT_inf(X, y, sigma, n, r, sigmaRBF, q, 7, M, burnin, Z=Z, b01=b01, I=I, U0=U0, noise_w=NW, noise_U=NU)
+    assert W.shape == (q, M - burnin) and V.shape == (n, r, D, M - burnin) and np.array_equal(Iout, I)
+    assert relerr(W, Wr) < 1e-8 and relerr(V, Vr) < 1e-8
+    W2, V2, _ = G.GPT_inf(X, y, sigma, n, r, sigmaRBF, q, 7, 3, 1)
+    assert np.isfinite(W2).all() and np.isfinite(V2).all() and W2.shape == (q, 2)

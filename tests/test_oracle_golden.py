@@ -269,3 +269,28 @@ def test_class_gradients_finite_differences():
     ws, Us = o.GPTclassification(phi, y, I, r, Q, 10, 0.0, 0.0, 0, 1, w, U, perms, NW, NU)
     assert ws.shape == (Q, C, 2) and Us.shape == (n, r, D, C, 2)
     assert np.allclose(ws[:, :, -1], w) and np.allclose(Us[..., -1], U, atol=1e-12)
+
+
+def test_tgp_gibbs_restatement():
+    """TGP.jl:37-86 restated: with zero noise the w draw is the ridge solution of V'w ~ y (its normal equations hold),
+    stores are taken before the factors move, and a second call continues from stored factors identically."""
+    rng = np.random.default_rng(0)
+    n, D, N, r, q, M = 5, 3, 40, 2, 6, 3
+    X = rng.standard_normal((N, D)); y = rng.standard_normal(N)
+    Z = rng.standard_normal((n, D)) / 1.3; b01 = rng.random((n, D))
+    b = np.stack([o.tgp_feature(X[i], Z, b01) for i in range(N)], axis=2)
+    I = rng.integers(0, r, (q, D)); I[:r, 0] = np.arange(r)
+    U0 = np.sqrt(1 / r) * rng.standard_normal((n, r, D))
+    sigma = 0.5
+    W, V = o.tgp_gibbs(b, y, sigma, r, I, U0, M, 0, np.zeros((M, q)), np.zeros((M, D, n * r)))
+    assert W.shape == (q, M) and V.shape == (n, r, D, M)
+    assert np.array_equal(V[..., 0], U0)                                   # :68-71 store before the factors move
+    t = np.einsum("jlk,jki->kli", U0, b)
+    Vm = np.prod([t[k, I[:, k], :] for k in range(D)], axis=0)
+    sw2 = float(r) ** D / q
+    lhs = (Vm @ Vm.T / sigma ** 2 + np.eye(q) / sw2) @ W[:, 0]
+    assert np.allclose(lhs, Vm @ y / sigma ** 2, rtol=1e-10, atol=1e-12)
+    # chain property: running 3 iterations == running 1 and then 2 more from the stored state (noise-free)
+    W1, V1 = o.tgp_gibbs(b, y, sigma, r, I, U0, 2, 0, np.zeros((2, q)), np.zeros((2, D, n * r)))
+    W2, V2 = o.tgp_gibbs(b, y, sigma, r, I, V1[..., 1], 2, 0, np.zeros((2, q)), np.zeros((2, D, n * r)))
+    assert np.allclose(W2[:, 1], W[:, 2], rtol=1e-9) and np.allclose(V2[..., 1], V[..., 2], rtol=1e-9)
