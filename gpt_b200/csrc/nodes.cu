@@ -226,6 +226,10 @@ __global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restric
     const float4 *Ck = reinterpret_cast<const float4 *>(Cf + (size_t)k * G * ctot * PP);
     const int zoff = blockIdx.z * NL * 32;
     float *Tk = T2 + (size_t)k * t2_stride * ncols + zoff;
+    // stores: this lane's column of row `row` is at Tlane + row * rowbytes (+ 128 bytes per further column block) — one
+    // 32 x 32 -> 64-bit multiply-add per store instead of a 64-bit index computation
+    char *const Tlane = reinterpret_cast<char *>(Tk + lane);
+    const uint32_t rowbytes = (uint32_t)ncols * 4u;
     const int zcols = min(NL * 32, ncols - zoff);       // columns of this block
     col0 += zoff;
     const int64_t s0 = ((int64_t)blockIdx.x * (ITHREADS / 32) + warp) * IWROWS, s1 = min(nrows, s0 + IWROWS);
@@ -266,7 +270,7 @@ __global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restric
                     acc1 = fmaf(tb[4 * q + 3], cf[a][q].w, acc1);
                 }
                 const int l = a * 32 + lane;
-                if (l < zcols) Tk[(size_t)row * ncols + l] = acc0 + acc1;
+                if (l < zcols) *reinterpret_cast<float *>(Tlane + (uint64_t)(uint32_t)row * rowbytes + a * 128) = acc0 + acc1;
             }
         };
         for (int j = 0; j < cnt; j += 2) {
@@ -295,8 +299,8 @@ __global__ void __launch_bounds__(ITHREADS) interp_kernel(const float *__restric
                 }
                 const int l = a * 32 + lane;
                 if (l < zcols) {
-                    Tk[(size_t)row_a * ncols + l] = acc0.x + acc1.x;
-                    if (jb != j) Tk[(size_t)row_b * ncols + l] = acc0.y + acc1.y;
+                    *reinterpret_cast<float *>(Tlane + (uint64_t)(uint32_t)row_a * rowbytes + a * 128) = acc0.x + acc1.x;
+                    if (jb != j) *reinterpret_cast<float *>(Tlane + (uint64_t)(uint32_t)row_b * rowbytes + a * 128) = acc0.y + acc1.y;
                 }
             }
         }
