@@ -117,6 +117,10 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
         const int q4 = rpad >> 2, total = CRB * D * q4;
         // (four loads in flight per thread before the first store: the loop is latency-, not bandwidth-bound)
         constexpr int TB = 4;
+#if GPTB_K2_TLOAD != 0
+        const int qh = q4 / (GPTB_K2_TLOAD == 1 ? 4 : 2);                  // column groups per row and warp pass
+        const int qh_sh = (qh & (qh - 1)) == 0 ? 31 - __clz(qh) : -1;      // a power of two (rpad = 16, 32, 64): a shift, no division
+#endif
         for (int t0 = tid; t0 < total; t0 += TB * CT_THREADS) {
             float4 v[TB];
             float *d[TB];
@@ -133,7 +137,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
                 // a (32 / RS)-way bank conflict in the transposing stores
                 constexpr int RS = GPTB_K2_TLOAD == 1 ? 8 : 16, QS = 32 / RS;
                 const int ln = tt & 31, rowgrp = (tt >> 5) % (CRB / RS), kq = tt / (32 * (CRB / RS));
-                const int qh = q4 / QS, k = kq / qh, q = (kq - k * qh) * QS + (ln % QS);
+                const int k = qh_sh >= 0 ? (kq >> qh_sh) : kq / qh, q = (kq - k * qh) * QS + (ln % QS);
                 const int rowt = rowgrp * RS + ln / QS;
 #endif
                 v[j] = __ldg(reinterpret_cast<const float4 *>(p.T + ((size_t)k * p.mpad + (size_t)blockIdx.x * CRB + rowt) * rpad) + q);

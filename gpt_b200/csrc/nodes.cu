@@ -365,11 +365,14 @@ __global__ void __launch_bounds__(STHREADS) spread_kernel(const float *__restric
             u_n = su[kb + s];
         }
         const int ppr = rpad / 4;                               // 16-byte pieces per row
+        const int psh = (ppr & (ppr - 1)) == 0 ? 31 - __clz(ppr) : -1;   // a power of two (rpad = 16, 32, 64): shifts, no division
         float *dst = stage + (size_t)buf * 32 * rpad;
+        const char *Eb = reinterpret_cast<const char *>(Ek);
+        const uint32_t rowbytes = (uint32_t)rpad * 4u;
         for (int t = lane; t < 32 * ppr; t += 32) {             // (32 * ppr is a multiple of 32: the shuffle is convergent)
-            const int j = t / ppr, part = t - j * ppr;
+            const int j = psh >= 0 ? (t >> psh) : t / ppr, part = t - j * ppr;
             const int row = __shfl_sync(0xffffffffu, row_n, j);   // (row 0 for records past the end: a valid address)
-            cp_async16(dst + j * rpad + part * 4, Ek + (size_t)row * rpad + part * 4);
+            cp_async16(dst + j * rpad + part * 4, Eb + (uint64_t)(uint32_t)row * rowbytes + part * 16);
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
