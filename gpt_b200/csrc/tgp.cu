@@ -9,8 +9,8 @@
 //     V_k = V ./ T[k][I[:,k]], C[l][i] = sum_{q: I[q,k]=l} w_q V_k[q][i]  tgp_C_kernel        (:74-79)
 //     Ck[l*n+j][i] = C[l][i] b[j,k,i], Ck Ck', Ck y                       tgp_Ck_kernel, gram / gemv  (:80-82)
 //     V = V_k .* T_new[k][I[:,k]]                                         tgp_Vup_kernel      (:84)
-// The two small dense solves per conditional (Cholesky of a q x q and an n*r x n*r matrix) run on the host, as the
-// reference's `\` and `chol` do; only those matrices, their right-hand sides and the drawn parameters cross the bus.
+// So do the two small dense solves per conditional (Cholesky of a q x q and an n*r x n*r matrix: one CTA each, the matrix
+// in L2): the host only launches, and reads the stored draws back.
 //
 // Reference quirks kept: the factor draw is invSigma_U \ randn(n*r) (covariance invSigma_U^-2, :83) while the w draw
 // uses the Cholesky factor (:66); W and the factors are stored before the factors move (:68-71); rows of C for values
@@ -118,35 +118,75 @@ __global__ void tgp_Vup_kernel(double *__restrict__ V, const double *__restrict_
     V[(size_t)q * ld + i] *= Tk[(size_t)Ik[q] * ld + i];
 }
 
-// ---- host: S = R'R (upper R, as chol(.,:U)), solves with it.  S is M x M, symmetric positive definite, row-major.
-bool chol_upper(std::vector<double> &S, int M) {
-    for (int j = 0; j < M; ++j) {
-        double d = S[(size_t)j * M + j];
-        for (int t = 0; t < j; ++t) d -= S[(size_t)t * M + j] * S[(size_t)t * M + j];
-        if (!(d > 0.0)) return false;
-        d = sqrt(d);
-        S[(size_t)j * M + j] = d;
-        for (int c = j + 1; c < M; ++c) {
-            double v = S[(size_t)j * M + c];
-            for (int t = 0; t < j; ++t) v -= S[(size_t)t * M + j] * S[(size_t)t * M + c];
-            S[(size_t)j * M + c] = v / d;
+// ---- the small dense systems, on the device: one CTA of 1024 threads per system, the matrix in global memory (L2).
+// S (M x M, row-major, symmetric positive definite) <- S * scale + diag * I, then its upper Cholesky factor R in place
+// (S = R'R, as chol(.,:U)); *bad is raised when a pivot is not positive (NaN / Inf in the Gram matrix).
+__global__ void __launch_bounds__(1024) tgp_chol_kernel(double *__restrict__ S, int M, double scale, double diag, int32_t *bad) {
+    __shared__ double piv;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    for (size_t t = tid; t < (size_t)M * M; t += nt) {
+        const int a = (int)(t / M), c = (int)(t - (size_t)a * M);
+        S[t] = S[t] * scale + (a == c ? diag : 0.0);
+    }
+    __syncthreads();
+    for (int j = 0; j < M; ++j) {          // right-looking: row j of R, then the rank-one update of the trailing block
+        if (tid == 0) {
+            const double d = S[(size_t)j * M + j];
+            if (!(d > 0.0)) *bad = 1;
+            piv = sqrt(d);
+            S[(size_t)j * M + j] = piv;
         }
+        __syncthreads();
+        const double p = piv;
+        for (int c = j + 1 + tid; c < M; c += nt) S[(size_t)j * M + c] /= p;
+        __syncthreads();
+        for (int a = j + 1 + (tid >> 5); a < M; a += nt >> 5) {      // a warp per row a >= j+1, lanes along c >= a
+            const double ra = S[(size_t)j * M + a];
+            for (int c = a + (tid & 31); c < M; c += 32) S[(size_t)a * M + c] -= ra * S[(size_t)j * M + c];
+        }
+        __syncthreads();
     }
-    return true;
 }
-void solve_Rt(const std::vector<double> &R, int M, std::vector<double> &x) {   // R' x = b (forward)
-    for (int i = 0; i < M; ++i) {
-        double v = x[i];
-        for (int t = 0; t < i; ++t) v -= R[(size_t)t * M + i] * x[t];
-        x[i] = v / R[(size_t)i * M + i];
-    }
+
+// x <- pre * x, then x <- R' \ x (fwd != 0), then x <- R \ x (bwd != 0): column sweeps, one CTA
+__global__ void __launch_bounds__(1024) tgp_trsv_kernel(const double *__restrict__ R, int M, double *__restrict__ x, double pre, int fwd,
+                                                        int bwd) {
+    __shared__ double xi;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    for (int i = tid; i < M; i += nt) x[i] *= pre;
+    __syncthreads();
+    if (fwd)
+        for (int i = 0; i < M; ++i) {      // R' is lower triangular with column i of R' = row i of R
+            if (tid == 0) { xi = x[i] / R[(size_t)i * M + i]; x[i] = xi; }
+            __syncthreads();
+            const double v = xi;
+            for (int c = i + 1 + tid; c < M; c += nt) x[c] -= R[(size_t)i * M + c] * v;
+            __syncthreads();
+        }
+    if (bwd)
+        for (int i = M - 1; i >= 0; --i) {
+            if (tid == 0) { xi = x[i] / R[(size_t)i * M + i]; x[i] = xi; }
+            __syncthreads();
+            const double v = xi;
+            for (int a = tid; a < i; a += nt) x[a] -= R[(size_t)a * M + i] * v;
+            __syncthreads();
+        }
 }
-void solve_R(const std::vector<double> &R, int M, std::vector<double> &x) {    // R x = b (backward)
-    for (int i = M - 1; i >= 0; --i) {
-        double v = x[i];
-        for (int t = i + 1; t < M; ++t) v -= R[(size_t)i * M + t] * x[t];
-        x[i] = v / R[(size_t)i * M + i];
-    }
+
+// Philox draws of one conditional (production mode): out[0..M), two per block, counter (stream | i/2, step)
+__global__ void tgp_noise_kernel(double *__restrict__ out, int M, uint64_t key, uint64_t stream, uint64_t step) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (2 * p >= M) return;
+    double a, b;
+    philox_normal2(key, stream | (uint64_t)p, step, &a, &b);
+    out[2 * p] = a;
+    if (2 * p + 1 < M) out[2 * p + 1] = b;
+}
+
+// out = a + s * b
+__global__ void tgp_axpby_kernel(const double *__restrict__ a, const double *__restrict__ b, double s, int M, double *__restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < M) out[i] = a[i] + s * b[i];
 }
 
 template <typename T>
@@ -206,41 +246,31 @@ extern "C" int gptb_tgp_gibbs(gptb_handle *h, double sigma, int32_t num_iteratio
         tgp_T_kernel<<<dim3(nb, r), 128, 0, st>>>(phi, h->U + (size_t)k * r * n, N, D, n, r, k, ld, T.p + (size_t)k * r * ld);
         h->launches++;
     };
-    std::vector<double> Sq((size_t)Q * Q), bq(Q), W(Q), zq(Q), Su((size_t)nr * nr), bu(nr), zu(nr), Uhost((size_t)nr * D);
-    const int Tn = num_iterations - burnin;
+    DevBuf<double> zq, zu, mu;
+    DevBuf<int32_t> bad;
+    GPTB_TRY(zq.alloc(h, (size_t)Q));
+    GPTB_TRY(zu.alloc(h, (size_t)nr));
+    GPTB_TRY(mu.alloc(h, (size_t)Q));
+    GPTB_TRY(bad.alloc(h, 1));
+    GPTB_CUDA_OK(h, cudaMemsetAsync(bad.p, 0, sizeof(int32_t), st));
+    int32_t bad_host = 0;
     for (int m = 1; m <= num_iterations; ++m) {
         for (int k = 0; k < D; ++k) launch_T(k);
         tgp_V_kernel<<<dim3(nb, Q), 128, 0, st>>>(T.p, h->I, N, D, r, Q, ld, V.p);                    // :62
         tgp_gram_kernel<<<dim3((Q + 15) / 16, (Q + 15) / 16), 256, 0, st>>>(V.p, Q, N, ld, Gq.p);
         tgp_gemv_kernel<<<(Q + 7) / 8, 256, 0, st>>>(V.p, h->y, Q, N, ld, vq.p);
-        h->launches += 3;
-        GPTB_CUDA_OK(h, cudaMemcpyAsync(Sq.data(), Gq.p, sizeof(double) * Q * Q, cudaMemcpyDeviceToHost, st));
-        GPTB_CUDA_OK(h, cudaMemcpyAsync(bq.data(), vq.p, sizeof(double) * Q, cudaMemcpyDeviceToHost, st));
-        GPTB_CUDA_OK(h, cudaStreamSynchronize(st));
-        for (int a = 0; a < Q; ++a) {
-            for (int b = 0; b < Q; ++b) Sq[(size_t)a * Q + b] /= s2;
-            Sq[(size_t)a * Q + a] += 1.0 / (sigma_w * sigma_w);                                        // :64
-            bq[a] /= s2;
-        }
-        if (!chol_upper(Sq, Q)) {
-            gptb_set_error(h, "gptb_tgp_gibbs: invSigma_w of iteration %d is not positive definite (NaN / Inf in V?)", m);
-            return GPTB_ERR_ARG;
-        }
-        // Mu_w = invSigma_w \ b (:65);  W = R \ randn(q) + Mu_w (:66)
-        solve_Rt(Sq, Q, bq);
-        solve_R(Sq, Q, bq);
-        for (int a = 0; a < Q; a += 2) {
-            double z0, z1;
-            if (noise_w) { z0 = noise_w[(size_t)(m - 1) * Q + a]; z1 = a + 1 < Q ? noise_w[(size_t)(m - 1) * Q + a + 1] : 0.0; }
-            else philox_normal2(c.seed, GPTB_STREAM_NOISE_W | (uint64_t)(a / 2), (uint64_t)m | (2ull << 40), &z0, &z1);
-            zq[a] = z0;
-            if (a + 1 < Q) zq[a + 1] = z1;
-        }
-        solve_R(Sq, Q, zq);
-        for (int a = 0; a < Q; ++a) W[a] = zq[a] + bq[a];
-        GPTB_CUDA_OK(h, cudaMemcpyAsync(wd.p, W.data(), sizeof(double) * Q, cudaMemcpyHostToDevice, st));
+        // invSigma_w = V V'/sigma^2 + I/sigma_w^2 = R'R (:64);  Mu_w = invSigma_w \ (V y/sigma^2) (:65)
+        tgp_chol_kernel<<<1, 1024, 0, st>>>(Gq.p, Q, 1.0 / s2, 1.0 / (sigma_w * sigma_w), bad.p);
+        tgp_trsv_kernel<<<1, 1024, 0, st>>>(Gq.p, Q, vq.p, 1.0 / s2, 1, 1);
+        // W = R \ randn(q) + Mu_w (:66)
+        if (noise_w) GPTB_CUDA_OK(h, cudaMemcpyAsync(zq.p, noise_w + (size_t)(m - 1) * Q, sizeof(double) * Q, cudaMemcpyHostToDevice, st));
+        else tgp_noise_kernel<<<(Q / 2 + 128) / 128, 128, 0, st>>>(zq.p, Q, c.seed, GPTB_STREAM_NOISE_W, (uint64_t)m | (2ull << 40));
+        tgp_trsv_kernel<<<1, 1024, 0, st>>>(Gq.p, Q, zq.p, 1.0, 0, 1);
+        tgp_axpby_kernel<<<(Q + 127) / 128, 128, 0, st>>>(zq.p, vq.p, 1.0, Q, wd.p);
+        h->launches += 8;
         if (m > burnin) {                                                                              // :68-71
-            if (W_array) memcpy(W_array + (size_t)(m - burnin - 1) * Q, W.data(), sizeof(double) * Q);
+            if (W_array)
+                GPTB_CUDA_OK(h, cudaMemcpyAsync(W_array + (size_t)(m - burnin - 1) * Q, wd.p, sizeof(double) * Q, cudaMemcpyDeviceToHost, st));
             if (V_array)
                 GPTB_CUDA_OK(h, cudaMemcpyAsync(V_array + (size_t)(m - burnin - 1) * nr * D, h->U, sizeof(double) * nr * D,
                                                 cudaMemcpyDeviceToHost, st));
@@ -251,44 +281,31 @@ extern "C" int gptb_tgp_gibbs(gptb_handle *h, double sigma, int32_t num_iteratio
             tgp_Ck_kernel<<<dim3(nb, nr), 128, 0, st>>>(C.p, phi, N, D, n, r, k, ld, Ck.p);
             tgp_gram_kernel<<<dim3((nr + 15) / 16, (nr + 15) / 16), 256, 0, st>>>(Ck.p, nr, N, ld, Gu.p);
             tgp_gemv_kernel<<<(nr + 7) / 8, 256, 0, st>>>(Ck.p, h->y, nr, N, ld, vu.p);
-            h->launches += 4;
-            GPTB_CUDA_OK(h, cudaMemcpyAsync(Su.data(), Gu.p, sizeof(double) * nr * nr, cudaMemcpyDeviceToHost, st));
-            GPTB_CUDA_OK(h, cudaMemcpyAsync(bu.data(), vu.p, sizeof(double) * nr, cudaMemcpyDeviceToHost, st));
-            GPTB_CUDA_OK(h, cudaStreamSynchronize(st));
-            for (int a = 0; a < nr; ++a) {
-                for (int b = 0; b < nr; ++b) Su[(size_t)a * nr + b] /= s2;
-                Su[(size_t)a * nr + a] += 1.0 / (sigma_u * sigma_u);                                   // :81
-            }
-            for (int a = 0; a < nr; a += 2) {
-                double z0, z1;
-                if (noise_U) {
-                    const double *zz = noise_U + ((size_t)(m - 1) * D + k) * nr;
-                    z0 = zz[a]; z1 = a + 1 < nr ? zz[a + 1] : 0.0;
-                } else {
-                    philox_normal2(c.seed, GPTB_STREAM_NOISE_U | ((uint64_t)k << 40) | (uint64_t)(a / 2), (uint64_t)m | (2ull << 40), &z0, &z1);
-                }
-                zu[a] = z0;
-                if (a + 1 < nr) zu[a + 1] = z1;
-            }
-            // U_k = invSigma_U \ randn + invSigma_U \ (Ck y / sigma^2)   (:82-83): one solve of the summed right-hand side
-            for (int a = 0; a < nr; ++a) zu[a] += bu[a] / s2;
-            if (!chol_upper(Su, nr)) {
-                gptb_set_error(h, "gptb_tgp_gibbs: invSigma_U of iteration %d, dimension %d is not positive definite", m, k + 1);
-                return GPTB_ERR_ARG;
-            }
-            solve_Rt(Su, nr, zu);
-            solve_R(Su, nr, zu);
+            // invSigma_U = Ck Ck'/sigma^2 + I/sigma_u^2 (:81);  U_k = invSigma_U \ randn + invSigma_U \ (Ck y/sigma^2) (:82-83):
+            // one solve of the summed right-hand side
+            tgp_chol_kernel<<<1, 1024, 0, st>>>(Gu.p, nr, 1.0 / s2, 1.0 / (sigma_u * sigma_u), bad.p);
+            if (noise_U)
+                GPTB_CUDA_OK(h, cudaMemcpyAsync(zu.p, noise_U + ((size_t)(m - 1) * D + k) * nr, sizeof(double) * nr, cudaMemcpyHostToDevice, st));
+            else
+                tgp_noise_kernel<<<(nr / 2 + 128) / 128, 128, 0, st>>>(zu.p, nr, c.seed, GPTB_STREAM_NOISE_U | ((uint64_t)k << 40),
+                                                                       (uint64_t)m | (2ull << 40));
             // reshape(., n, r): entry l*n + j is U[j,l] — the handle's own layout of U^(k)
-            GPTB_CUDA_OK(h, cudaMemcpyAsync(h->U + (size_t)k * nr, zu.data(), sizeof(double) * nr, cudaMemcpyHostToDevice, st));
-            GPTB_CUDA_OK(h, cudaStreamSynchronize(st));       // (zu is reused by the next dimension)
+            tgp_axpby_kernel<<<(nr + 127) / 128, 128, 0, st>>>(zu.p, vu.p, 1.0 / s2, nr, h->U + (size_t)k * nr);
+            tgp_trsv_kernel<<<1, 1024, 0, st>>>(Gu.p, nr, h->U + (size_t)k * nr, 1.0, 1, 1);
             launch_T(k);
             tgp_Vup_kernel<<<dim3(nb, Q), 128, 0, st>>>(V.p, Tk, h->I + (size_t)k * Q, N, Q, ld);      // :84
-            h->launches++;
+            h->launches += 9;
+        }
+        // a pivot that is not positive (NaN / Inf in a Gram matrix): looked at once per iteration
+        GPTB_CUDA_OK(h, cudaMemcpyAsync(&bad_host, bad.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        GPTB_CUDA_OK(h, cudaStreamSynchronize(st));
+        if (bad_host) {
+            gptb_set_error(h, "gptb_tgp_gibbs: a conditional precision matrix of iteration %d is not positive definite (NaN / Inf in V?)", m);
+            return GPTB_ERR_ARG;
         }
     }
-    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->w, W.data(), sizeof(double) * Q, cudaMemcpyHostToDevice, st));
+    GPTB_CUDA_OK(h, cudaMemcpyAsync(h->w, wd.p, sizeof(double) * Q, cudaMemcpyDeviceToDevice, st));
     GPTB_CUDA_OK(h, cudaStreamSynchronize(st));
     h->shadows_valid = false;
-    (void)Tn;
     return GPTB_OK;
 }

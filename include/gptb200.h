@@ -223,7 +223,7 @@ int gptb_gmc_run(gptb_handle *h, double signal_var, double epsw, double epsU, in
  * index table, the whitened training set and the initial factors (gptb_set_params; w is ignored) — and ends at the
  * last draw.  Per iteration: w from its q x q Gaussian conditional (:62-66), then every U^(k) from its n*r x n*r
  * conditional (:73-84), sigma_u = sqrt(1/r), sigma_w = sqrt(r^D/q) (:54-55).  FP64 throughout; the row-proportional
- * work (T, V, the Gram matrices V V' and Ck Ck') runs on the device, the two small Cholesky solves on the host.
+ * work (T, V, the Gram matrices V V' and Ck Ck') and the two small Cholesky solves per conditional run on the device.
  *   noise_w[num_iterations][Q], noise_U[num_iterations][D][n*r]: the randn of :66 and :83, or NULL (Philox);
  *   W_array[Q, num_iterations-burnin], V_array[n,r,D,num_iterations-burnin] (Julia order; either may be NULL): the w of
  *   iteration m and the factors it was drawn with (:68-71).
