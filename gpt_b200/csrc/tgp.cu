@@ -218,6 +218,10 @@ extern "C" int gptb_tgp_gibbs(gptb_handle *h, double sigma, int32_t num_iteratio
     }
     const gptb_config &c = h->cfg;
     const int n = c.n, r = c.r, D = c.D, Q = c.Q, nr = n * r;
+    if (nr > 4096 || Q > 4096) {   // the factor's conditional is an n*r x n*r dense system (TGP.jl:81): a sampler for small n*r
+        gptb_set_error(h, "gptb_tgp_gibbs: n*r = %d (or q = %d) above 4096: the dense conditionals of TGP.jl:64,81 are out of reach", nr, Q);
+        return GPTB_ERR_UNSUPPORTED;
+    }
     const int64_t N = h->N, ld = (N + 31) / 32 * 32;
     GPTB_CUDA_OK(h, cudaSetDevice(h->device));
     GPTB_TRY(gptb_synchronize(h));
